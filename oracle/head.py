@@ -1,0 +1,462 @@
+"""TEST INFRASTRUCTURE ONLY — CPU restatement of the reference depth head (fp32, plain torch ops).
+
+Every function takes a reference-format ``state_dict`` (same keys/shapes as the reference modules,
+SURVEY.md F9) and follows the reference file:line cited in its docstring.  Nothing here imports the
+reference or the product package; ``oracle/make_golden.py`` pins these functions against the real
+reference modules run in the build container (fixtures under ``tests/golden``).
+
+Semantics restated are those of ``eval()`` + ``torch.no_grad()`` (inference): no dropout, and
+``nn.TransformerEncoder`` with a ``src_key_padding_mask`` returns 0 at padded rows (PyTorch nested
+tensor fast path).
+
+Parity status: pinned (a1–a7); chamfer in ``bins_chamfer_loss`` unpinned (see ``oracle/__init__``).
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional, Sequence
+
+import torch
+import torch.nn.functional as F
+
+SD = Dict[str, torch.Tensor]
+
+# ----------------------------------------------------------------------------------------------
+# transformer pieces (torch defaults restated: SURVEY.md F8)
+# ----------------------------------------------------------------------------------------------
+
+
+def mha(sd: SD, pre: str, query, key, value, num_heads: int = 4, key_padding_mask=None):
+    """``nn.MultiheadAttention`` forward, batch-first ``[B,S,E]`` operands, ``need_weights=False``.
+
+    Call sites: ``modules/ObjCAViT.py:195-207`` (cross attention) and inside every
+    ``nn.TransformerEncoderLayer`` (``modules/layers.py:8``, ``modules/ObjCAViT.py:155-161``).
+    Packed ``in_proj_weight [3E,E]`` rows ``[0,E)``=q, ``[E,2E)``=k, ``[2E,3E)``=v; head ``h`` owns
+    channels ``[h*d,(h+1)*d)``; scores scaled by ``1/sqrt(d)``; ``key_padding_mask`` True = ignore.
+    """
+    w, b = sd[pre + "in_proj_weight"], sd[pre + "in_proj_bias"]
+    E = query.shape[-1]
+    d = E // num_heads
+    q = query @ w[:E].T + b[:E]
+    k = key @ w[E:2 * E].T + b[E:2 * E]
+    v = value @ w[2 * E:].T + b[2 * E:]
+    B, Sq, _ = q.shape
+    Sk = k.shape[1]
+    q = q.view(B, Sq, num_heads, d).transpose(1, 2)
+    k = k.view(B, Sk, num_heads, d).transpose(1, 2)
+    v = v.view(B, Sk, num_heads, d).transpose(1, 2)
+    scores = (q * (1.0 / math.sqrt(d))) @ k.transpose(-1, -2)
+    if key_padding_mask is not None:
+        scores = scores.masked_fill(key_padding_mask[:, None, None, :], float("-inf"))
+    attn = torch.softmax(scores, dim=-1)
+    out = (attn @ v).transpose(1, 2).reshape(B, Sq, E)
+    return out @ sd[pre + "out_proj.weight"].T + sd[pre + "out_proj.bias"]
+
+
+def encoder_layer(sd: SD, pre: str, x, num_heads: int = 4, key_padding_mask=None):
+    """``nn.TransformerEncoderLayer`` (post-norm, ReLU, eps 1e-5), batch-first ``[B,S,E]``."""
+    a = mha(sd, pre + "self_attn.", x, x, x, num_heads, key_padding_mask)
+    x = F.layer_norm(x + a, (x.shape[-1],), sd[pre + "norm1.weight"], sd[pre + "norm1.bias"], 1e-5)
+    h = torch.relu(x @ sd[pre + "linear1.weight"].T + sd[pre + "linear1.bias"])
+    h = h @ sd[pre + "linear2.weight"].T + sd[pre + "linear2.bias"]
+    return F.layer_norm(x + h, (x.shape[-1],), sd[pre + "norm2.weight"], sd[pre + "norm2.bias"], 1e-5)
+
+
+def transformer_encoder(sd: SD, pre: str, x, num_layers: int = 4, num_heads: int = 4, key_padding_mask=None):
+    """``nn.TransformerEncoder(layer, num_layers=4)`` (no final norm).  With a padding mask the
+    inference fast path returns zeros at the padded rows (F7)."""
+    for i in range(num_layers):
+        x = encoder_layer(sd, f"{pre}layers.{i}.", x, num_heads, key_padding_mask)
+    if key_padding_mask is not None:
+        x = x.masked_fill(key_padding_mask[:, :, None], 0.0)
+    return x
+
+
+# ----------------------------------------------------------------------------------------------
+# a1 / a2 / a3: modules/layers.py, modules/miniViT.py
+# ----------------------------------------------------------------------------------------------
+
+
+def patch_transformer_encoder(sd: SD, pre: str, x, patch_size: int = 16):
+    """``PatchTransformerEncoder.forward`` (``modules/layers.py:16-24``); returns ``[B,S,E]``
+    (the reference returns the same values laid out ``[S,B,E]``)."""
+    emb = F.conv2d(x, sd[pre + "embedding_convPxP.weight"], sd[pre + "embedding_convPxP.bias"],
+                   stride=patch_size).flatten(2)                                  # layers.py:17
+    S = emb.shape[2]
+    emb = emb + sd[pre + "positional_encodings"][:S, :].T.unsqueeze(0)             # layers.py:19
+    tok = emb.permute(0, 2, 1)                                                     # layers.py:22 (B,S,E here)
+    return transformer_encoder(sd, pre + "transformer_encoder.", tok)              # layers.py:23
+
+
+def pixelwise_dot_product(x, K):
+    """``PixelWiseDotProduct.forward`` (``modules/layers.py:31-36``): ``[n,c,h,w]``,``[n,q,c]`` -> ``[n,q,h,w]``."""
+    n, c, h, w = x.shape
+    _, cout, ck = K.shape
+    assert c == ck, "Number of channels in x and Embedding dimension (at dim 2) of K matrix must match"
+    y = torch.matmul(x.view(n, c, h * w).permute(0, 2, 1), K.permute(0, 2, 1))
+    return y.permute(0, 2, 1).view(n, cout, h, w).contiguous()
+
+
+def regress_bins(sd: SD, pre: str, regression_head, norm: str = "linear"):
+    """Regressor MLP + bin-width normalisation (``modules/miniViT.py:33-42`` ≡ ``modules/ObjCAViT.py:378-388``)."""
+    y = F.leaky_relu(regression_head @ sd[pre + "0.weight"].T + sd[pre + "0.bias"], 0.01)
+    y = F.leaky_relu(y @ sd[pre + "2.weight"].T + sd[pre + "2.bias"], 0.01)
+    y = y @ sd[pre + "4.weight"].T + sd[pre + "4.bias"]
+    if norm == "linear":
+        y = torch.relu(y) + 0.1
+    elif norm == "softmax":
+        return torch.softmax(y, dim=1)
+    else:
+        y = torch.sigmoid(y)
+    return y / y.sum(dim=1, keepdim=True)
+
+
+def mvit_forward(sd: SD, x, pre: str = "", n_query_channels: int = 128, norm: str = "linear"):
+    """``mViT.forward`` (``modules/miniViT.py:22-44``) -> ``(bin_widths_normed [B,K], ram [B,Q,h,w])``."""
+    tgt = patch_transformer_encoder(sd, pre + "patch_transformer.", x)             # miniViT.py:24
+    xc = F.conv2d(x, sd[pre + "conv3x3.weight"], sd[pre + "conv3x3.bias"], padding=1)  # :25
+    regression_head, queries = tgt[:, 0, :], tgt[:, 1:n_query_channels + 1, :]     # :27
+    ram = pixelwise_dot_product(xc, queries.contiguous())                          # :31
+    y = regress_bins(sd, pre + "regressor.", regression_head, norm)                # :33-42
+    return y, ram
+
+
+# ----------------------------------------------------------------------------------------------
+# a7: head tail (modules/AdaBins.py:76-89 ≡ modules/GraphBins.py:105-121)
+# ----------------------------------------------------------------------------------------------
+
+
+def bin_edges_and_centres(bin_widths_normed, min_depth: float, max_depth: float):
+    """``AdaBins.py:79-85``: widths*(max-min) -> pad(min) -> cumsum -> edges; centres = mid-points."""
+    bw = (max_depth - min_depth) * bin_widths_normed
+    bw = F.pad(bw, (1, 0), mode="constant", value=min_depth)
+    edges = torch.cumsum(bw, dim=1)
+    centres = 0.5 * (edges[:, :-1] + edges[:, 1:])
+    return edges, centres
+
+
+def head_tail(sd: SD, ram, bin_widths_normed, min_depth: float, max_depth: float, pre: str = "conv_out."):
+    """``conv_out`` (1x1 conv + Softmax over bins, ``AdaBins.py:51-54``) and the bin-centre expectation
+    (``AdaBins.py:77-87``) -> ``(depth_pred [B,1,h,w], bin_edges [B,K+1])``."""
+    out = torch.softmax(F.conv2d(ram, sd[pre + "0.weight"], sd[pre + "0.bias"]), dim=1)
+    edges, centres = bin_edges_and_centres(bin_widths_normed, min_depth, max_depth)
+    depth = torch.sum(out * centres[:, :, None, None], dim=1, keepdim=True)
+    return depth, edges
+
+
+# ----------------------------------------------------------------------------------------------
+# a4: GridRandomPositionalEmbeddings (modules/ObjCAViT.py:18-147) — index mapping in explicit loops
+# ----------------------------------------------------------------------------------------------
+
+
+def _grid_for(table, feat_h: int, feat_w: int, patch_size: int = 16):
+    """``ObjCAViT.py:78-83``: first gh*gw rows of the table viewed as ``[gh,gw,E]``."""
+    gh, gw = math.ceil(feat_h / patch_size), math.ceil(feat_w / patch_size)
+    return table[: gh * gw].view(gh, gw, -1), gh, gw
+
+
+def grid_sample_points(grid_hwE, xs: Sequence[float], ys: Sequence[float]):
+    """``F.grid_sample(mode='bilinear', padding_mode='zeros', align_corners=False)`` at normalised
+    points, restated with explicit index arithmetic (torch defaults; call sites ``ObjCAViT.py:99,109``).
+    Returns ``(values [N,E], idx [N,4] (nw,ne,sw,se; flat y*W+x or -1 when out of bounds), wts [N,4])``."""
+    H, W, E = grid_hwE.shape
+    f32 = torch.float32
+    xs = torch.as_tensor(xs, dtype=f32)
+    ys = torch.as_tensor(ys, dtype=f32)
+    # ATen's vectorised CPU kernel (GridSamplerKernel.cpp, ComputeLocation<align_corners=false>):
+    # unnormalised = (coord + 1) * (size / 2) - 0.5
+    ix = (xs + 1) * (W / 2) - 0.5
+    iy = (ys + 1) * (H / 2) - 0.5
+    x0 = torch.floor(ix)
+    y0 = torch.floor(iy)
+    x1, y1 = x0 + 1, y0 + 1
+    w_nw = (x1 - ix) * (y1 - iy)
+    w_ne = (ix - x0) * (y1 - iy)
+    w_sw = (x1 - ix) * (iy - y0)
+    w_se = (ix - x0) * (iy - y0)
+    N = xs.numel()
+    idx = torch.full((N, 4), -1, dtype=torch.int64)
+    wts = torch.stack([w_nw, w_ne, w_sw, w_se], dim=1)
+    out = torch.zeros(N, E, dtype=f32)
+    flat = grid_hwE.reshape(H * W, E)
+    for n in range(N):
+        for j, (xx, yy) in enumerate(((x0[n], y0[n]), (x1[n], y0[n]), (x0[n], y1[n]), (x1[n], y1[n]))):
+            xi, yi = int(xx), int(yy)
+            if 0 <= xi < W and 0 <= yi < H:
+                idx[n, j] = yi * W + xi
+                out[n] = out[n] + flat[yi * W + xi] * wts[n, j]
+    return out, idx, wts
+
+
+def ps_roi_align_1x1(grid_hwE, xyxy, spatial_scale: float):
+    """``torchvision.ops.ps_roi_align(input, [xyxy], output_size=[1,1], spatial_scale, sampling_ratio=-1)``
+    restated (torchvision 0.13.1 pinned by the reference, 0.26.0 installed; the algorithm is the
+    published ``ps_roi_align_kernel.cpp``; call sites ``ObjCAViT.py:128,144``).  With a 1x1 output every
+    output channel reads the same input channel.  Zero-area boxes give 0/0 = NaN.
+    Returns ``(values [N,E], plan)`` where ``plan[n] = (grid_h, grid_w, [(y_low,x_low,y_high,x_high) or None...])``
+    is the bit-exact index mapping."""
+    H, W, E = grid_hwE.shape
+    f32 = torch.float32
+    xyxy = torch.as_tensor(xyxy, dtype=f32)
+    N = xyxy.shape[0]
+    out = torch.zeros(N, E, dtype=f32)
+    plans = []
+    sc = torch.tensor(spatial_scale, dtype=f32)
+    half = torch.tensor(0.5, dtype=f32)
+    for n in range(N):
+        rsw = xyxy[n, 0] * sc - half
+        rsh = xyxy[n, 1] * sc - half
+        rew = xyxy[n, 2] * sc - half
+        reh = xyxy[n, 3] * sc - half
+        rw, rh = rew - rsw, reh - rsh
+        bin_h, bin_w = rh / 1.0, rw / 1.0
+        gh = int(math.ceil(float(rh)))
+        gw = int(math.ceil(float(rw)))
+        count = gh * gw
+        acc = torch.zeros(E, dtype=f32)
+        samples = []
+        for iy in range(gh):
+            y = rsh + torch.tensor(iy + 0.5, dtype=f32) * bin_h / torch.tensor(float(gh), dtype=f32)
+            for ix in range(gw):
+                x = rsw + torch.tensor(ix + 0.5, dtype=f32) * bin_w / torch.tensor(float(gw), dtype=f32)
+                yy, xx = float(y), float(x)
+                if yy < -1.0 or yy > H or xx < -1.0 or xx > W:
+                    samples.append(None)
+                    continue
+                yv = y if yy > 0 else torch.tensor(0.0, dtype=f32)
+                xv = x if xx > 0 else torch.tensor(0.0, dtype=f32)
+                y_low, x_low = int(yv), int(xv)
+                if y_low >= H - 1:
+                    y_high = y_low = H - 1
+                    yv = torch.tensor(float(y_low), dtype=f32)
+                else:
+                    y_high = y_low + 1
+                if x_low >= W - 1:
+                    x_high = x_low = W - 1
+                    xv = torch.tensor(float(x_low), dtype=f32)
+                else:
+                    x_high = x_low + 1
+                ly = yv - y_low
+                lx = xv - x_low
+                hy, hx = 1.0 - ly, 1.0 - lx
+                w1, w2, w3, w4 = hy * hx, hy * lx, ly * hx, ly * lx
+                val = (w1 * grid_hwE[y_low, x_low] + w2 * grid_hwE[y_low, x_high]
+                       + w3 * grid_hwE[y_high, x_low] + w4 * grid_hwE[y_high, x_high])
+                acc = acc + val
+                samples.append((y_low, x_low, y_high, x_high))
+        out[n] = acc / torch.tensor(float(count), dtype=f32)  # 0/0 -> NaN when count == 0
+        plans.append((gh, gw, samples))
+    return out, plans
+
+
+def _xywh_to_clamped_xyxy(c):
+    """``ObjCAViT.py:115-124`` / ``134-143``: centre/size -> corners, clamp(min=0)."""
+    hw, hh = c[..., 2] / 2, c[..., 3] / 2
+    out = torch.stack([c[..., 0] - hw, c[..., 1] - hh, c[..., 0] + hw, c[..., 1] + hh], dim=-1)
+    return torch.clamp(out, min=0.0)
+
+
+def grid_random_pos(table, mode: str, coords, feat_h: int, feat_w: int, space: str,
+                    patch_size: int = 16, factor: float = 2.0):
+    """``GridRandomPositionalEmbeddings.forward`` (``ObjCAViT.py:50-147``) INCLUDING its quirks (F13).
+
+    ``space='img'``: ``coords [B,S,2|4]`` -> ``[B,S,E]``; ``space='obj'``: ``coords [N,2|4]`` -> ``[N,E]``.
+    """
+    grid, gh, gw = _grid_for(table, feat_h, feat_w, patch_size)
+    full_h, full_w = feat_h * factor, feat_w * factor
+    if mode == "centre":
+        nc = coords.clone().float()
+        if space == "img":
+            # ObjCAViT.py:95-96 index the TOKEN axis of the [B,S,2] tensor (F13a): token 0's (x,y) are
+            # both normalised by grid height, token 1's by grid width, every other token keeps raw pixels.
+            nc[:, 0] = ((nc[:, 0] / gh) * 2) - 1
+            nc[:, 1] = ((nc[:, 1] / gw) * 2) - 1
+            B, S, _ = nc.shape
+            vals = [grid_sample_points(grid, nc[b, :, 0], nc[b, :, 1])[0] for b in range(B)]
+            return torch.stack(vals, 0)
+        # ObjCAViT.py:104-105: x / full HEIGHT, y / full WIDTH (F13b)
+        nc[:, 0] = ((nc[:, 0] / full_h) * 2) - 1
+        nc[:, 1] = ((nc[:, 1] / full_w) * 2) - 1
+        return grid_sample_points(grid, nc[:, 0], nc[:, 1])[0]
+    assert mode == "roi_align"
+    if space == "img":
+        B = coords.shape[0]
+        return torch.stack([ps_roi_align_1x1(grid, _xywh_to_clamped_xyxy(coords[b].float()),
+                                             1.0 / patch_size)[0] for b in range(B)], 0)
+    return ps_roi_align_1x1(grid, _xywh_to_clamped_xyxy(coords.float()), 1.0 / (patch_size * factor))[0]
+
+
+# ----------------------------------------------------------------------------------------------
+# a5 / a6: SelfAttnCrossAttn + ObjCAViT (modules/ObjCAViT.py:150-390)
+# ----------------------------------------------------------------------------------------------
+
+
+def pad_objects(object_features, S: Optional[int] = None):
+    """``ObjCAViT.py:180-183`` (+ ``192-194`` when ``S`` is given): ragged list (or dense ``[B,n,E]``
+    tensor in block 2) -> ``(padded [B,N_max,E] pad 0.0001, mask [B,N_max] True=pad)``; with ``S``:
+    objects LEFT-padded / mask RIGHT-padded to length S (F5)."""
+    seqs = list(object_features.unbind(0)) if torch.is_tensor(object_features) else list(object_features)
+    B = len(seqs)
+    n_max = max(int(o.shape[0]) for o in seqs)
+    E = seqs[0].shape[1]
+    padded = torch.full((B, n_max, E), 0.0001, dtype=torch.float32)
+    mask = torch.ones(B, n_max, dtype=torch.bool)
+    for b, o in enumerate(seqs):
+        padded[b, : o.shape[0]] = o
+        mask[b, : o.shape[0]] = False
+    if S is None:
+        return padded, mask
+    amt = S - n_max
+    return F.pad(padded, (0, 0, amt, 0), value=0.0001), F.pad(mask, (0, amt), value=True)
+
+
+def saca_forward(sd: SD, pre: str, image_tokens, object_features, no_obj_sa: bool = False):
+    """``SelfAttnCrossAttn.forward`` (``ObjCAViT.py:167-213``)."""
+    att_img = transformer_encoder(sd, pre + "image_transformer_encoder.", image_tokens)        # :169
+    obj, mask = pad_objects(object_features)                                                   # :180-183
+    if no_obj_sa:
+        att_obj = obj                                                                          # :186
+    else:
+        att_obj = transformer_encoder(sd, pre + "obj_transformer_encoder.", obj, key_padding_mask=mask)  # :188
+    S = att_img.shape[1]
+    amt = S - att_obj.shape[1]                                                                 # :192
+    kpm = F.pad(mask, (0, amt), value=True)                                                    # :193 (right pad)
+    att_obj = F.pad(att_obj, (0, 0, amt, 0), value=0.0001)                                     # :194 (left pad)
+    final_img = mha(sd, pre + "cross_attn_obj_im.", att_img, att_obj, att_img, 4, kpm)         # :195-201
+    final_obj = mha(sd, pre + "cross_attn_im_obj.", att_obj, att_img, att_obj, 4, None)        # :202-207
+    return final_img, final_obj
+
+
+def _pos_mlp(sd: SD, pre: str, x):
+    """``positional_encoder`` MLP (``ObjCAViT.py:257-282``): Linear/LeakyReLU x4 + Linear."""
+    for i in (0, 2, 4, 6):
+        x = F.leaky_relu(x @ sd[f"{pre}{i}.weight"].T + sd[f"{pre}{i}.bias"], 0.01)
+    return x @ sd[pre + "8.weight"].T + sd[pre + "8.bias"]
+
+
+def patch_coords(B: int, gh: int, gw: int, patch_size: int = 16):
+    """``ObjCAViT.py:336-347``: ``[B,S,4]`` = (16x+8, 16y+8, 16, 16), row-major over (y,x)."""
+    xs = torch.arange(gw).view(1, -1).expand(gh, -1)
+    ys = torch.arange(gh).view(-1, 1).expand(-1, gw)
+    pc = torch.stack([xs, ys], 0) * patch_size + patch_size // 2
+    pc = pc.flatten(1).expand(B, -1, -1).permute(0, 2, 1).float()
+    return torch.cat([pc, torch.ones_like(pc) * patch_size], dim=2)
+
+
+def objcavit_forward(sd: SD, image_features, object_features: List[torch.Tensor],
+                     object_xywh_list: List[Optional[torch.Tensor]], strategy: str,
+                     pre: str = "", no_obj_sa: bool = False, use_2_saca: bool = False,
+                     n_query_channels: int = 128, norm: str = "linear", patch_size: int = 16):
+    """``ObjCAViT.forward`` (``ObjCAViT.py:306-390``) -> ``(bin_widths_normed, ram)``.
+    Does NOT mutate the caller's list (the reference does, F11; the product wrapper mimics that)."""
+    B, _, h, w = image_features.shape
+    objs = []
+    for i, xywhs in enumerate(object_xywh_list):                                   # :311-330
+        if xywhs is None:
+            xywhs = torch.zeros((1, 4)) - 1                                        # :313
+        xywhs = xywhs.float()
+        if strategy == "grid_random":
+            pos = grid_random_pos(sd[pre + "positional_encoder.positional_encodings"], "centre",
+                                  xywhs[:, 0:2], h, w, "obj", patch_size)
+        elif strategy == "grid_random_roi_align":
+            pos = grid_random_pos(sd[pre + "positional_encoder.positional_encodings"], "roi_align",
+                                  xywhs[:, 0:4], h, w, "obj", patch_size)
+        elif strategy == "learned_bbox_wh":
+            pos = _pos_mlp(sd, pre + "positional_encoder.", xywhs[:, 0:4])
+        else:
+            pos = _pos_mlp(sd, pre + "positional_encoder.", xywhs[:, 0:2])
+        emb = object_features[i].float() @ sd[pre + "obj_embedding_layer.weight"].T + sd[pre + "obj_embedding_layer.bias"]
+        objs.append(emb + pos)                                                     # :330
+
+    pe = F.conv2d(image_features, sd[pre + "image_embedding_convPxP.weight"],
+                  sd[pre + "image_embedding_convPxP.bias"], stride=patch_size)     # :333
+    gh, gw = pe.shape[2], pe.shape[3]
+    pc = patch_coords(B, gh, gw, patch_size)                                       # :336-347
+    if strategy == "grid_random":
+        ipos = grid_random_pos(sd[pre + "positional_encoder.positional_encodings"], "centre",
+                               pc[..., 0:2], h, w, "img", patch_size)
+    elif strategy == "grid_random_roi_align":
+        ipos = grid_random_pos(sd[pre + "positional_encoder.positional_encodings"], "roi_align",
+                               pc[..., 0:4], h, w, "img", patch_size)
+    elif strategy == "learned_bbox_wh":
+        ipos = _pos_mlp(sd, pre + "positional_encoder.", pc[..., 0:4])
+    else:
+        ipos = _pos_mlp(sd, pre + "positional_encoder.", pc[..., 0:2])
+    tok = pe.flatten(2).permute(0, 2, 1) + ipos                                    # :362-364
+
+    tok, obj_out = saca_forward(sd, pre + "saca_1.", tok, objs, no_obj_sa)         # :366
+    if use_2_saca:
+        tok, obj_out = saca_forward(sd, pre + "saca_2.", tok, obj_out, no_obj_sa)  # :368
+
+    regression_head, queries = tok[:, 0, :], tok[:, 1:n_query_channels + 1, :]     # :373
+    xc = F.conv2d(image_features, sd[pre + "conv3x3.weight"], sd[pre + "conv3x3.bias"], padding=1)  # :374
+    ram = pixelwise_dot_product(xc, queries.contiguous())                          # :375
+    y = regress_bins(sd, pre + "regressor.", regression_head, norm)                # :378-388
+    return y, ram
+
+
+def head_forward(sd: SD, cfg: dict, features, object_features=None, object_xywh_list=None):
+    """Whole head: (mViT | ObjCAViT) + tail.  ``cfg`` = dict(kind, strategy, no_obj_sa, use_2_saca,
+    min_depth, max_depth).  Returns ``(depth_pred, bin_edges, bin_widths_normed, ram)``."""
+    if cfg["kind"] == "adabins":
+        y, ram = mvit_forward(sd, features, pre="adaptive_bins_layer.")
+    else:
+        y, ram = objcavit_forward(sd, features, object_features, object_xywh_list, cfg["strategy"],
+                                  pre="objcavit.", no_obj_sa=cfg.get("no_obj_sa", False),
+                                  use_2_saca=cfg.get("use_2_saca", False))
+    depth, edges = head_tail(sd, ram, y, cfg["min_depth"], cfg["max_depth"])
+    return depth, edges, y, ram
+
+
+# ----------------------------------------------------------------------------------------------
+# a8: losses (config 5) — losses/SILogLoss.py:28-56, losses/BinsChamferLoss.py:21-37
+# ----------------------------------------------------------------------------------------------
+
+
+def silog_loss(depth_pred, depth_gt, depth_mask=None, alph: float = 10.0, lam: float = 0.85):
+    """``SILogLoss.forward`` (``losses/SILogLoss.py:43-56``)."""
+    depth_pred = F.interpolate(depth_pred, depth_gt.shape[-2:], mode="bilinear", align_corners=True)
+    if depth_mask is not None:
+        depth_pred = depth_pred[depth_mask]
+        depth_gt = depth_gt[depth_mask]
+    n = depth_pred.numel()
+    g = torch.log(depth_pred) - torch.log(depth_gt)
+    Dg = (torch.sum(g ** 2) / n) - ((lam / (n ** 2)) * (torch.sum(g) ** 2))
+    return alph * torch.sqrt(Dg)
+
+
+def bins_chamfer_loss(bin_edges, depth_gt, depth_mask):
+    """``BinsChamferLoss.forward`` (``losses/BinsChamferLoss.py:21-37``) with pytorch3d 0.7.0
+    ``chamfer_distance`` defaults restated (squared L2, point_reduction='mean',
+    batch_reduction='mean', both directions summed).  PARITY UNPINNED: pytorch3d is not available.
+    1-D: centres are sorted, so nearest neighbours come from ``searchsorted``."""
+    centres = 0.5 * (bin_edges[:, 1:] + bin_edges[:, :-1])
+    B, P = centres.shape
+    cham_x = torch.zeros(B)
+    cham_y = torch.zeros(B)
+    for b in range(B):
+        t = depth_gt[b].flatten()[depth_mask[b].flatten()]
+        c = centres[b]
+        ts, _ = torch.sort(t)
+        # x -> y
+        j = torch.searchsorted(ts, c).clamp(1, max(ts.numel() - 1, 1))
+        cand = torch.stack([ts[(j - 1).clamp(0, ts.numel() - 1)], ts[j.clamp(0, ts.numel() - 1)]], 1)
+        cham_x[b] = ((cand - c[:, None]) ** 2).min(dim=1).values.sum() / P
+        # y -> x
+        j = torch.searchsorted(c, t).clamp(1, P - 1)
+        cand = torch.stack([c[j - 1], c[j]], 1)
+        cham_y[b] = ((cand - t[:, None]) ** 2).min(dim=1).values.sum() / max(t.numel(), 1)
+    return cham_x.mean() + cham_y.mean()
+
+
+def bins_chamfer_loss_bruteforce(bin_edges, depth_gt, depth_mask):
+    """O(P*T) statement of the same formula (used only to pin ``bins_chamfer_loss``)."""
+    centres = 0.5 * (bin_edges[:, 1:] + bin_edges[:, :-1])
+    B, P = centres.shape
+    cx, cy = [], []
+    for b in range(B):
+        t = depth_gt[b].flatten()[depth_mask[b].flatten()]
+        d = (centres[b][:, None] - t[None, :]) ** 2
+        cx.append(d.min(dim=1).values.sum() / P)
+        cy.append(d.min(dim=0).values.sum() / max(t.numel(), 1))
+    return torch.stack(cx).mean() + torch.stack(cy).mean()
