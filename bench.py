@@ -1,0 +1,295 @@
+#!/usr/bin/env python
+"""Headline benchmark: ObjCAViT head depth-maps/s (BASELINE.json metric) on N GPUs of one node.
+
+    python bench.py --gpus N --steps K --warmup W            (N>1: launched by torchrun, one rank per GPU)
+    python bench.py --impl reference ...                      (the reference head's CPU implementation)
+
+A step = one pass of the head (ObjCAViT + conv_out + bin-centre expectation) over one batch of
+synthetic decoder features + synthetic YOLO boxes / CLIP embeddings (BASELINE.json configs[1]:
+nyu learned_bbox_wh, 32 boxes, batch 16 per GPU, 240x320 features of a 480x640 image).  Prints ONE
+JSON line on rank 0.  See DESIGN.md "Measurement" for how each field is obtained.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "ObjCAViT head depth-maps/sec @480x640"
+UNIT = "depth-maps/s"
+CFG_NAME = "nyu_ocv_learned_bbox_wh"
+H, W, NOBJ = 240, 320, 32
+# algorithmic FLOPs per image (general computation)
+GF_HEAD = 34.0
+GF_PIXEL = 22.649 + 2.517 + 5.033      # conv3x3 + dot-product + conv_out: the fused pixel kernel
+GF_CONV3 = 22.649
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            d = json.load(f)
+        return dict(hbm=d["hbm_gbs"], tf_burst=d["bf16_tflops"], tf_sust=d["bf16_tflops_sustained"], src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sust=1400.0, src="fallback")
+
+
+def load_weights(name):
+    from oracle import synth  # seeded synthetic weights only (no computation)
+    with open(os.path.join(ROOT, "tests", "golden", f"manifest_{name}.json")) as f:
+        return synth.make_state_dict(json.load(f), seed=0)
+
+
+def make_inputs(B, rank):
+    from oracle import synth
+    feats = synth.make_features(B, H, W, seed=1234 + rank)
+    objs, boxes = synth.make_objects(B, H, W, NOBJ, seed=1234 + rank)
+    return feats, objs, boxes
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def cpu_reference_rate(sample_images, threads, repeats=3):
+    """The reference head's algorithm (oracle port, fp32 torch CPU ops) on the host cores."""
+    from oracle import head as oh
+    torch.set_num_threads(threads)
+    sd = load_weights(CFG_NAME)
+    feats, objs, boxes = make_inputs(sample_images, 0)
+    cfg = dict(kind="graphbins", strategy="learned_bbox_wh", min_depth=0.001, max_depth=10.0)
+    best = float("inf")
+    with torch.no_grad():
+        oh.head_forward(sd, cfg, feats[:1], objs[:1], boxes[:1])          # warm-up
+        for _ in range(repeats):
+            t0 = time.perf_counter()
+            oh.head_forward(sd, cfg, feats, objs, boxes)
+            best = min(best, time.perf_counter() - t0)
+    return sample_images / best, best
+
+
+def run_reference(a):
+    """--impl reference: the reference's own CPU implementation of the path (oracle port: the reference
+    tree is not present on the GPU box), all host threads, each step a bounded sample of the workload."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    from oracle import head as oh
+    sample = 2
+    sd = load_weights(CFG_NAME)
+    feats, objs, boxes = make_inputs(sample, 0)
+    cfg = dict(kind="graphbins", strategy="learned_bbox_wh", min_depth=0.001, max_depth=10.0)
+    with torch.no_grad():
+        for _ in range(min(a.warmup, 2)):
+            oh.head_forward(sd, cfg, feats, objs, boxes)
+        steps = min(a.steps, 5)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            oh.head_forward(sd, cfg, feats, objs, boxes)
+        dt = (time.perf_counter() - t0) / steps
+    v = sample / dt
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": steps,
+        "warmup": min(a.warmup, 2), "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{CFG_NAME} head, {NOBJ} boxes, features 128x{H}x{W}, bounded sample of {sample} images per step"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                         "sample": f"{sample} images per step, {steps} steps, torch fp32 CPU ops of oracle/head.py"},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--precision", default=None, choices=[None, "bf16", "fp32"])
+    ap.add_argument("--batch", type=int, default=16, help="images per GPU per step")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    if a.impl == "reference":
+        return run_reference(a)
+
+    from objcavit_b200 import ops
+    from objcavit_b200.config import builtin_args
+    from objcavit_b200.modules import build_head
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    precision = a.precision
+    if precision is None:
+        try:
+            from objcavit_b200 import engine_bf16  # noqa: F401
+            precision = "bf16"
+        except ImportError:
+            precision = "fp32"
+    W_ = max(a.warmup, 3)
+    K = a.steps
+    B = a.batch
+
+    head = build_head(builtin_args(CFG_NAME), precision=precision).to(dev).eval()
+    head.load_state_dict(load_weights(CFG_NAME), strict=True)
+    feats, objs, boxes = make_inputs(B, rank)
+    # device-resident inputs for `value`: the dtype/layout the path consumes
+    if precision == "bf16":
+        x_host = feats.permute(0, 2, 3, 1).contiguous().bfloat16().pin_memory()   # NHWC bf16 ("channels_last" features)
+        x_dev = x_host.to(dev).permute(0, 3, 1, 2)                                 # logical NCHW view, NHWC memory
+    else:
+        x_host = feats.pin_memory()
+        x_dev = x_host.to(dev)
+    objs_host = [o.pin_memory() for o in objs]
+    boxes_host = [b.pin_memory() for b in boxes]
+    objs_dev = [o.to(dev) for o in objs_host]
+    boxes_dev = [b.to(dev) for b in boxes_host]
+
+    def step(x, ob, bx):
+        with torch.no_grad():
+            return head(x, list(ob), bx)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    # ---- device-resident throughput (`value`) ------------------------------------------------------
+    for _ in range(W_):
+        step(x_dev, objs_dev, boxes_dev)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ops.launch_count
+    ms = timed(lambda: step(x_dev, objs_dev, boxes_dev), K)
+    launches = ops.launch_count - l0
+    clocks = sampler.stop() if rank == 0 else None
+    value = world * B * K / (ms * 1e-3)
+
+    # ---- dominant kernel, timed live with CUDA events on the launching stream ------------------------
+    dom = "ocv_pixel_fused_bf16" if precision == "bf16" else "ocv_conv3x3_f32"
+    ops.timed_kernel = dom
+    ops.timed_events = []
+    for _ in range(min(K, 10)):
+        step(x_dev, objs_dev, boxes_dev)
+    torch.cuda.synchronize()
+    durs = [s.elapsed_time(e) for s, e in ops.timed_events]
+    ops.timed_kernel = None
+    dom_ms = sum(durs) / max(len(durs), 1)
+    pk = peaks()
+    gf = (GF_PIXEL if precision == "bf16" else GF_CONV3) * B
+    achieved = gf / dom_ms if dom_ms > 0 else 0.0     # GFLOP/ms == TFLOP/s
+    roofline = {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": pk["tf_sust"], "unit": "TFLOP/s",
+                "frac": achieved / pk["tf_sust"], "traffic": None, "peak_source": pk["src"] + " (bf16 sustained)",
+                "kernel_ms": dom_ms, "kernel_share_of_step": dom_ms / (ms / K),
+                "head_frac_of_roofline": (GF_HEAD * B * K / ms) / pk["tf_sust"]}
+
+    # ---- end to end through the public module API with HOST buffers ----------------------------------
+    def e2e_step():
+        if precision == "bf16":
+            x = x_host.to(dev, non_blocking=True).permute(0, 3, 1, 2)
+        else:
+            x = x_host.to(dev, non_blocking=True)
+        ob = [o.to(dev, non_blocking=True) for o in objs_host]
+        bx = [b.to(dev, non_blocking=True) for b in boxes_host]
+        out = step(x, ob, bx)
+        return out.depth_pred.to("cpu", non_blocking=False)
+
+    for _ in range(3):
+        e2e_step()
+    ms_e2e = timed(e2e_step, K)
+    e2e_value = world * B * K / (ms_e2e * 1e-3)
+    h2d = x_host.numel() * x_host.element_size() + sum(o.numel() * 4 for o in objs_host) + sum(b.numel() * 4 for b in boxes_host)
+    d2h = B * H * W * 4
+
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W_,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "bf16" if precision == "bf16" else "f32", "data": "synthetic",
+        "config": {"workload": f"{CFG_NAME} head (ObjCAViT + conv_out + bin expectation), {NOBJ} boxes/img, "
+                               f"features 128x{H}x{W} ({'bf16 NHWC' if precision == 'bf16' else 'fp32 NCHW'}), "
+                               f"batch {B}/GPU, inference",
+                   "batch_per_gpu": B, "parallelism": f"dp{world} (batch sharded, no collective)",
+                   "l2": f"inputs {x_host.numel() * x_host.element_size() / 1e6:.0f} MB/step > 126 MB L2, no explicit flush"},
+        "gpu_launches": launches, "roofline": roofline, "clocks": clocks,
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "ms_per_step": ms_e2e / K},
+    }
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        v, secs = cpu_reference_rate(2, threads)
+        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                               "sample": f"2 images of the same workload, best of 3 ({secs:.2f} s per pass), oracle/head.py fp32 on torch CPU"}
+    if rank == 0:
+        print(json.dumps(out))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,171 @@
+/*
+ * objcavit_b200 — C ABI of the B200 (sm_100a) ObjCAViT / AdaBins depth-head kernels.
+ *
+ * This is the drop-in boundary.  The reference has no native layer: its head is a
+ * chain of PyTorch nn.Module calls.  Each entry point below replaces the library calls of one stage of
+ * that chain; the "replaces" line names the reference site (path:line under the reference tree).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host; tensors are dense row-major in
+ *     the stated layout; fp32 unless stated; `stream` is a cudaStream_t passed as void*.
+ *   - return value: 0 = OK; negative = OCV_E_* (bad argument / unsupported shape / wrong arch);
+ *     positive = the cudaError_t of the failed launch.  Never throws, never calls exit().
+ *   - no entry point synchronises the device or allocates device memory; workspaces are caller-owned.
+ *   - all entry points are re-entrant; there is no global mutable state apart from the per-process
+ *     cache of function attributes (max dynamic smem) that is set once.
+ *   - there is NO CPU fallback: on a device that is not sm_100 every compute entry returns OCV_E_ARCH.
+ */
+#ifndef OBJCAVIT_B200_H_
+#define OBJCAVIT_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OCV_OK 0
+#define OCV_E_ARG (-1)      /* null pointer / non-positive size            */
+#define OCV_E_SHAPE (-2)    /* shape the kernel does not support            */
+#define OCV_E_ALIGN (-3)    /* pointer or stride alignment                  */
+#define OCV_E_ARCH (-4)     /* device is not sm_100                         */
+#define OCV_E_DRIVER (-5)   /* driver entry point (tensor map encode) unavailable */
+
+/* activation codes for ocv_linear_f32 */
+#define OCV_ACT_NONE 0
+#define OCV_ACT_RELU 1
+#define OCV_ACT_LEAKY_RELU 2 /* slope 0.01 (nn.LeakyReLU default) */
+
+/* bin-width normalisation (mViT/ObjCAViT `norm` argument) */
+#define OCV_NORM_LINEAR 0
+#define OCV_NORM_SOFTMAX 1
+#define OCV_NORM_SIGMOID 2
+#define OCV_NORM_NONE 3 /* input is already normalised widths: only edges / centres are produced */
+
+/* ---- library / device --------------------------------------------------------------------------- */
+int ocv_abi_version(void);                       /* bumps when a signature changes */
+int ocv_device_check(int device);                /* OCV_OK iff `device` is compute capability 10.x */
+const char* ocv_status_string(int status);
+
+/* ---- generic fp32 dense stage --------------------------------------------------------------------
+ * C[b] = act(A[b] @ op(Bm[b]) + bias) + residual[b]
+ *   A: [M,K] lda; Bm: transB ? [N,K] ldb (nn.Linear weight layout) : [K,N] ldb; C,residual: [M,N] ldc.
+ *   batch strides in elements (0 = shared operand).  bias [N] or NULL; residual NULL or same layout as C.
+ * replaces: nn.Linear / F.linear everywhere on the token path (modules/ObjCAViT.py:257-282,289,299-303;
+ *   modules/miniViT.py:16-20), the in/out projections and FFN of nn.TransformerEncoderLayer
+ *   (modules/layers.py:8; modules/ObjCAViT.py:155-164), torch.matmul in PixelWiseDotProduct
+ *   (modules/layers.py:35, transB=0 gives the [n,q,h*w] result directly, no permute copies). */
+int ocv_linear_f32(const float* A, const float* Bm, const float* bias, const float* residual, float* C,
+                   int M, int N, int K, int lda, int ldb, int ldc, int transB, int act,
+                   int batch, long long strideA, long long strideB, long long strideC, void* stream);
+
+/* ---- patch embedding -----------------------------------------------------------------------------
+ * tokens[b,s,e] = sum_{c,ky,kx} W[e,c,ky,kx] * X[b,c,ty*P+ky,tx*P+kx] + bias[e] + pos[s,e]   (s = ty*gw+tx)
+ *   X [B,C,h,w] NCHW; W [E,C,P,P]; pos [>=S,E] row-major or NULL; tokens [B,S,E]; gh=h/P, gw=w/P (floor).
+ *   workspace: ocv_patch_embed_f32_workspace() bytes (split-K partials; deterministic reduction).
+ * replaces: embedding_convPxP + positional add + permute (modules/layers.py:17-22) and
+ *   image_embedding_convPxP (+ the image positional add) (modules/ObjCAViT.py:333,362-364). */
+long long ocv_patch_embed_f32_workspace(int B, int C, int h, int w, int P, int E);
+int ocv_patch_embed_f32(const float* X, const float* W, const float* bias, const float* pos, float* tokens,
+                        int B, int C, int h, int w, int P, int E, void* workspace, void* stream);
+
+/* ---- transformer pieces --------------------------------------------------------------------------
+ * y = LayerNorm(x + r) * gamma + beta over the last dim E (eps 1e-5); r may be NULL.  rows = B*S.
+ * zero_rows (uint8 [rows], may be NULL): rows whose flag is non-zero are written as 0 — the padded rows
+ *   of nn.TransformerEncoder's inference fast path.
+ * replaces: norm1/norm2 of nn.TransformerEncoderLayer (post-norm). */
+int ocv_add_layernorm_f32(const float* x, const float* r, const float* gamma, const float* beta, float* y,
+                          int rows, int E, const uint8_t* zero_rows, void* stream);
+
+/* Scaled-dot-product attention core for nn.MultiheadAttention:
+ *   out[b,i,h*d:(h+1)*d] = softmax_j( q[b,i,h]·k[b,j,h] / sqrt(d) + (mask[b,j] ? -inf : 0) ) @ v[b,j,h]
+ *   q/k/v/out are [B,S,*] views with explicit row strides (elements) so they can alias a packed QKV
+ *   buffer; heads*d contiguous channels starting at the pointer.  d must be 32.  mask uint8 [B,Sk] or NULL.
+ * replaces: the attention inside F.multi_head_attention_forward (modules/ObjCAViT.py:195-207 and every
+ *   encoder layer). */
+int ocv_mha_core_f32(const float* q, const float* k, const float* v, float* out, const uint8_t* key_padding_mask,
+                     int B, int Sq, int Sk, int heads, int d,
+                     long long q_bstride, int q_rstride, long long k_bstride, int k_rstride,
+                     long long v_bstride, int v_rstride, long long o_bstride, int o_rstride, void* stream);
+
+/* ---- object-token bookkeeping (bit-exact index work) ----------------------------------------------
+ * Ragged -> padded: src [total,E] rows of image b are [offsets[b],offsets[b+1]) (CSR, int32, device).
+ *   dst [B,L,E] filled with pad_value, image b's rows copied to [left, left+n_b) with left = L-Nmax when
+ *   left_pad else 0;   mask [B,L] uint8 (optional) = 1 except [0,m_b) (i.e. ALWAYS right-padded)
+ *   where m_b comes from mask_offsets (CSR, optional; NULL -> m_b = n_b).
+ * replaces: pad_sequence x2 + F.pad x2 (modules/ObjCAViT.py:180-183,192-194). */
+int ocv_pad_objects_f32(const float* src, const int32_t* offsets, const int32_t* mask_offsets, float* dst,
+                        uint8_t* mask, int B, int L, int Nmax, int E, float pad_value, int left_pad, void* stream);
+
+/* patch-centre coordinates coords[s] = (16x+8, 16y+8, 16, 16), s = y*gw+x  -> [S,4]
+ * replaces: modules/ObjCAViT.py:336-347 (batch-invariant, so computed once, not per image). */
+int ocv_patch_coords_f32(float* coords, int gh, int gw, int P, void* stream);
+
+/* GridRandomPositionalEmbeddings.  table [rows,E]; grid = first gh*gw rows as [gh,gw,E].
+ * centre mode: bilinear grid_sample (zeros padding, align_corners=False) at points pts [N,2] (x,y) -> out [N,E];
+ *   norm_mode 0: pts already normalised to [-1,1];
+ *   norm_mode 1 ("obj", modules/ObjCAViT.py:104-105): x' = (x/div0)*2-1, y' = (y/div1)*2-1
+ *               (the caller passes div0 = full-res HEIGHT, div1 = full-res WIDTH: quirk F13b is the caller's);
+ *   norm_mode 2 ("img", modules/ObjCAViT.py:95-96, quirk F13a): point 0 -> both coords (c/div0)*2-1,
+ *               point 1 -> both coords (c/div1)*2-1, every other point keeps its raw pixel coordinates.
+ *   idx_out [N,4] int32 (nw,ne,sw,se flat index or -1) optional: the bit-exact index mapping.
+ * roi mode: ps_roi_align(output 1x1, sampling_ratio=-1) -> out [N,E].  boxes [N,4]: corner boxes (xyxy) or, when
+ *   boxes_are_xywh, centre/size boxes converted as modules/ObjCAViT.py:115-124 (corners, clamp(min=0)).
+ *   Zero-area boxes give NaN exactly like torchvision.  plan_out [N,2] int32 (grid_h,grid_w) optional.
+ * replaces: F.grid_sample (modules/ObjCAViT.py:99,109) / torchvision.ops.ps_roi_align (:128,144). */
+int ocv_grid_sample_pos_f32(const float* table, const float* pts, float* out, int32_t* idx_out,
+                            int N, int gh, int gw, int E, int norm_mode, float div0, float div1, void* stream);
+int ocv_ps_roi_align_pos_f32(const float* table, const float* boxes, float* out, int32_t* plan_out,
+                             int N, int gh, int gw, int E, float spatial_scale, int boxes_are_xywh, void* stream);
+
+/* ---- bins -----------------------------------------------------------------------------------------
+ * y_raw [B,K] (regressor output) -> widths_normed [B,K] (norm: relu+0.1 | softmax | sigmoid, then /sum),
+ *   edges [B,K+1] = cumsum(pad(min_depth, (max-min)*widths)), centres [B,K] = mid-points.  K <= 1024.
+ * replaces: modules/miniViT.py:34-42 ≡ modules/ObjCAViT.py:379-388 and modules/AdaBins.py:79-85. */
+int ocv_bins_f32(const float* y_raw, float* widths_normed, float* edges, float* centres,
+                 int B, int K, int norm, float min_depth, float max_depth, void* stream);
+
+/* ---- pixel path, fp32 (parity path) ---------------------------------------------------------------
+ * 3x3 / pad 1 / stride 1 convolution, NCHW fp32, C_in = C_out = 128.
+ * replaces: self.conv3x3 (modules/miniViT.py:25; modules/ObjCAViT.py:374). */
+int ocv_conv3x3_f32(const float* X, const float* W, const float* bias, float* Y,
+                    int B, int C, int h, int w, void* stream);
+
+/* depth[b,p] = sum_k softmax_k( Wout[k,:]·ram[b,:,p] + bout[k] ) * centres[b,k];  ram [B,Q,P] (NCHW).
+ * The [B,K,h,w] probability volume is never written to memory.
+ * replaces: conv_out (1x1 conv + Softmax) and torch.sum(out*centers) (modules/AdaBins.py:77,87). */
+int ocv_tail_f32(const float* ram, const float* Wout, const float* bout, const float* centres, float* depth,
+                 int B, int Q, int K, long long P, void* stream);
+
+/* ---- pixel path, bf16 tensor-core (throughput path) -----------------------------------------------
+ * NCHW fp32|bf16 -> NHWC bf16 feature map (the layout the tcgen05 kernels consume).  src_is_bf16 selects
+ * the source dtype. */
+int ocv_nchw_to_nhwc_bf16(const void* src, void* dst_bf16, int B, int C, int h, int w, int src_is_bf16, void* stream);
+
+/* Generic bf16 tensor-core GEMM (tcgen05.mma, TMA-fed, fp32 accumulation in TMEM):
+ *   C[M,N] = act(A[M,K] @ Wt[N,K]^T + bias) (+ residual),  A/Wt bf16 row-major (K contiguous),
+ *   C fp32 or bf16 (c_is_bf16), ldc in elements.  K % 64 == 0, N % 16 == 0, N <= 256 per tile column.
+ *   split_k > 1 writes fp32 partials to `workspace` ([split_k,M,N]) reduced deterministically.
+ * replaces: the same sites as ocv_linear_f32 on the throughput path, and the patch-embed GEMM. */
+long long ocv_gemm_bf16_workspace(int M, int N, int K, int split_k);
+int ocv_gemm_bf16(const void* A, const void* Wt, const float* bias, const float* residual, void* C,
+                  int M, int N, int K, int lda, int ldb, int ldc, int act, int c_is_bf16, int split_k,
+                  void* workspace, void* stream);
+
+/* Fused pixel kernel (one persistent tcgen05 kernel):
+ *   conv3x3 (implicit GEMM over an NHWC bf16 halo tile) -> per-image logits GEMM with
+ *   Mb[b] = Wout @ Q[b] (bins x channels, bf16) -> per-pixel softmax over K=256 bins -> sum p*centre.
+ *   X [B,h,w,128] bf16 NHWC; W3p: packed conv weights from ocv_pack_conv3x3_bf16; b3 [128] fp32;
+ *   Mb [B,256,128] bf16; blog [B,256] fp32 (= bout + Wout@(Q[b]@b3 ... see DESIGN.md); centres [B,256];
+ *   depth [B,h*w] fp32.
+ * replaces: conv3x3 + PixelWiseDotProduct + conv_out + Softmax + sum (modules/ObjCAViT.py:374-375;
+ *   modules/GraphBins.py:109,119; modules/miniViT.py:25,31; modules/AdaBins.py:77,87). */
+int ocv_pack_conv3x3_bf16(const float* W /*[128,128,3,3]*/, void* W3p /*bf16 [9,128,128]*/, void* stream);
+int ocv_fold_queries_bf16(const float* Wout /*[K,Q]*/, const float* bout /*[K]*/, const float* queries /*[B,Q,E] ld*/,
+                          long long q_bstride, int q_rstride, const float* b3 /*[E]*/,
+                          void* Mb /*bf16 [B,K,E]*/, float* blog /*[B,K]*/, int B, int K, int Q, int E, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OBJCAVIT_B200_H_ */

@@ -1,0 +1,78 @@
+"""ctypes binding of ``libobjcavit_b200.so`` (the C ABI declared in ``include/objcavit_b200.h``).
+
+There is no fallback: if the library is missing or a call fails, an exception is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import re
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libobjcavit_b200.so")
+HEADER_PATH = os.path.join(os.path.dirname(HERE), "include", "objcavit_b200.h")
+
+_lib = None
+
+p = C.c_void_p
+i32 = C.c_int
+i64 = C.c_longlong
+f32 = C.c_float
+
+# name -> (restype, argtypes): must mirror include/objcavit_b200.h
+PROTOTYPES = {
+    "ocv_abi_version": (i32, []),
+    "ocv_device_check": (i32, [i32]),
+    "ocv_status_string": (C.c_char_p, [i32]),
+    "ocv_linear_f32": (i32, [p, p, p, p, p, i32, i32, i32, i32, i32, i32, i32, i32, i32, i64, i64, i64, p]),
+    "ocv_patch_embed_f32_workspace": (i64, [i32, i32, i32, i32, i32, i32]),
+    "ocv_patch_embed_f32": (i32, [p, p, p, p, p, i32, i32, i32, i32, i32, i32, p, p]),
+    "ocv_add_layernorm_f32": (i32, [p, p, p, p, p, i32, i32, p, p]),
+    "ocv_mha_core_f32": (i32, [p, p, p, p, p, i32, i32, i32, i32, i32, i64, i32, i64, i32, i64, i32, i64, i32, p]),
+    "ocv_pad_objects_f32": (i32, [p, p, p, p, p, i32, i32, i32, i32, f32, i32, p]),
+    "ocv_patch_coords_f32": (i32, [p, i32, i32, i32, p]),
+    "ocv_grid_sample_pos_f32": (i32, [p, p, p, p, i32, i32, i32, i32, i32, f32, f32, p]),
+    "ocv_ps_roi_align_pos_f32": (i32, [p, p, p, p, i32, i32, i32, i32, f32, i32, p]),
+    "ocv_bins_f32": (i32, [p, p, p, p, i32, i32, i32, f32, f32, p]),
+    "ocv_conv3x3_f32": (i32, [p, p, p, p, i32, i32, i32, i32, p]),
+    "ocv_tail_f32": (i32, [p, p, p, p, p, i32, i32, i32, i64, p]),
+    "ocv_nchw_to_nhwc_bf16": (i32, [p, p, i32, i32, i32, i32, i32, p]),
+    "ocv_gemm_bf16_workspace": (i64, [i32, i32, i32, i32]),
+    "ocv_gemm_bf16": (i32, [p, p, p, p, p, i32, i32, i32, i32, i32, i32, i32, i32, i32, p, p]),
+    "ocv_pack_conv3x3_bf16": (i32, [p, p, p]),
+    "ocv_fold_queries_bf16": (i32, [p, p, p, i64, i32, p, p, p, i32, i32, i32, i32, p]),
+}
+
+
+def declared_symbols():
+    """Every ``ocv_*`` function the public header declares (used by the symbol-export test)."""
+    with open(HEADER_PATH) as f:
+        src = f.read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(ocv_[a-z0-9_]+)\s*\(", src)))
+
+
+class OcvError(RuntimeError):
+    pass
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise OcvError(
+                f"{LIB_PATH} is missing: build it with `python -m objcavit_b200.build` "
+                "(or __graft_entry__.build()). There is no CPU / PyTorch fallback for the kernels.")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in PROTOTYPES.items():
+            fn = getattr(L, name)  # AttributeError if the .so is stale -> loud
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(status: int, what: str = ""):
+    if status != 0:
+        msg = lib().ocv_status_string(status).decode()
+        raise OcvError(f"objcavit_b200 {what} failed: status {status} ({msg})")

@@ -1,0 +1,123 @@
+// Operand preparation for the tensor-core pixel path: feature-map layout change (NCHW -> NHWC bf16),
+// conv3x3 weight packing, and the per-image fold of the 128 range-attention queries into the 1x1
+// conv_out weights (logits = Wout @ (Q @ conv) + bout  ==  (Wout @ Q) @ conv + bout').
+// Contracts: include/objcavit_b200.h
+#include "common.cuh"
+
+namespace {
+
+template <typename T>
+__device__ __forceinline__ float to_f32(T v);
+template <>
+__device__ __forceinline__ float to_f32<float>(float v) { return v; }
+template <>
+__device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
+
+// block (32,8): tile of 32 x-positions x C channels of one image row
+template <typename T>
+__global__ void nchw_to_nhwc_bf16_kernel(const T* __restrict__ src, __nv_bfloat16* __restrict__ dst, int C, int h,
+                                         int w) {
+  extern __shared__ float tile[];  // [32][C+1]
+  const int b = blockIdx.z, y = blockIdx.y, x0 = blockIdx.x * 32;
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const T* s = src + (long long)b * C * h * w + (long long)y * w;
+  for (int c = ty; c < C; c += 8) {
+    const int x = x0 + tx;
+    tile[tx * (C + 1) + c] = (x < w) ? to_f32<T>(s[(long long)c * h * w + x]) : 0.f;
+  }
+  __syncthreads();
+  __nv_bfloat16* d = dst + (((long long)b * h + y) * w + x0) * C;
+  const int tid = ty * 32 + tx;
+  // C/2 bf16x2 words per pixel
+  const int words = C / 2;
+  for (int i = tid; i < 32 * words; i += 256) {
+    const int px = i / words, cw = i % words;
+    if (x0 + px < w) {
+      const __nv_bfloat162 v = __floats2bfloat162_rn(tile[px * (C + 1) + 2 * cw], tile[px * (C + 1) + 2 * cw + 1]);
+      reinterpret_cast<__nv_bfloat162*>(d + (long long)px * C)[cw] = v;
+    }
+  }
+}
+
+// W [128 o][128 c][3][3] fp32 -> W3p [9 tap][128 o][128 c] bf16
+__global__ void pack_conv3x3_kernel(const float* __restrict__ W, __nv_bfloat16* __restrict__ out) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 9 * 128 * 128) return;
+  const int tap = i / (128 * 128), o = (i / 128) % 128, c = i % 128;
+  out[i] = __float2bfloat16(W[((long long)o * 128 + c) * 9 + tap]);
+}
+
+// Mb[b,k,c] = sum_q Wout[k,q] * Q[b,q,c];  blog[b,k] = bout[k] + sum_c Mb[b,k,c] * b3[c]
+// block: 8 bins of one image, thread = channel c (E <= 1024 threads... E == blockDim.x)
+constexpr int FQ_BINS = 8;
+__global__ void fold_queries_kernel(const float* __restrict__ Wout, const float* __restrict__ bout,
+                                    const float* __restrict__ queries, long long q_bs, int q_rs,
+                                    const float* __restrict__ b3, __nv_bfloat16* __restrict__ Mb,
+                                    float* __restrict__ blog, int K, int Q, int E) {
+  extern __shared__ float ws[];  // [FQ_BINS][Q] then [FQ_BINS][nwarp]
+  const int b = blockIdx.y, k0 = blockIdx.x * FQ_BINS, c = threadIdx.x;
+  for (int i = threadIdx.x; i < FQ_BINS * Q; i += blockDim.x) {
+    const int kk = i / Q, q = i % Q;
+    ws[i] = (k0 + kk < K) ? Wout[(long long)(k0 + kk) * Q + q] : 0.f;
+  }
+  __syncthreads();
+  float acc[FQ_BINS] = {};
+  const float* qb = queries + b * q_bs;
+  for (int q = 0; q < Q; ++q) {
+    const float qv = qb[(long long)q * q_rs + c];
+#pragma unroll
+    for (int i = 0; i < FQ_BINS; ++i) acc[i] = fmaf(ws[i * Q + q], qv, acc[i]);
+  }
+  float* red = ws + FQ_BINS * Q;
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32, nwarp = blockDim.x / 32;
+  const float bc = b3 ? b3[c] : 0.f;
+#pragma unroll
+  for (int i = 0; i < FQ_BINS; ++i) {
+    if (k0 + i < K) Mb[((long long)b * K + k0 + i) * E + c] = __float2bfloat16(acc[i]);
+    const float s = warp_sum(acc[i] * bc);
+    if (lane == 0) red[i * nwarp + warp] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x < FQ_BINS && k0 + threadIdx.x < K) {
+    float s = bout ? bout[k0 + threadIdx.x] : 0.f;
+    for (int w = 0; w < nwarp; ++w) s += red[threadIdx.x * nwarp + w];
+    blog[(long long)b * K + k0 + threadIdx.x] = s;
+  }
+}
+
+}  // namespace
+
+extern "C" int ocv_nchw_to_nhwc_bf16(const void* src, void* dst_bf16, int B, int C, int h, int w, int src_is_bf16,
+                                     void* stream) {
+  OCV_CHECK_ARG(src && dst_bf16 && B > 0 && h > 0 && w > 0);
+  OCV_CHECK_SHAPE(C > 0 && C % 2 == 0 && C <= 256 && B <= 65535 && h <= 65535);
+  if (int s = ocv_require_sm100()) return s;
+  dim3 grid(ceil_div(w, 32), h, B), block(32, 8);
+  const size_t smem = 32 * (C + 1) * sizeof(float);
+  if (src_is_bf16)
+    nchw_to_nhwc_bf16_kernel<__nv_bfloat16><<<grid, block, smem, ocv_stream(stream)>>>(
+        static_cast<const __nv_bfloat16*>(src), static_cast<__nv_bfloat16*>(dst_bf16), C, h, w);
+  else
+    nchw_to_nhwc_bf16_kernel<float><<<grid, block, smem, ocv_stream(stream)>>>(
+        static_cast<const float*>(src), static_cast<__nv_bfloat16*>(dst_bf16), C, h, w);
+  return ocv_launch_status();
+}
+
+extern "C" int ocv_pack_conv3x3_bf16(const float* W, void* W3p, void* stream) {
+  OCV_CHECK_ARG(W && W3p);
+  if (int s = ocv_require_sm100()) return s;
+  pack_conv3x3_kernel<<<ceil_div(9 * 128 * 128, 256), 256, 0, ocv_stream(stream)>>>(W, static_cast<__nv_bfloat16*>(W3p));
+  return ocv_launch_status();
+}
+
+extern "C" int ocv_fold_queries_bf16(const float* Wout, const float* bout, const float* queries, long long q_bstride,
+                                     int q_rstride, const float* b3, void* Mb, float* blog, int B, int K, int Q, int E,
+                                     void* stream) {
+  OCV_CHECK_ARG(Wout && queries && Mb && blog && B > 0 && K > 0 && Q > 0);
+  OCV_CHECK_SHAPE(E % 32 == 0 && E >= 32 && E <= 1024 && B <= 65535);
+  if (int s = ocv_require_sm100()) return s;
+  const size_t smem = (FQ_BINS * Q + FQ_BINS * (E / 32)) * sizeof(float);
+  fold_queries_kernel<<<dim3(ceil_div(K, FQ_BINS), B), E, smem, ocv_stream(stream)>>>(
+      Wout, bout, queries, q_bstride, q_rstride, b3, static_cast<__nv_bfloat16*>(Mb), blog, K, Q, E);
+  return ocv_launch_status();
+}

@@ -1,0 +1,263 @@
+// bf16 tensor-core GEMM for the token path and the patch embedding:
+//   C[M,N] = act(A[M,K] @ Wt[N,K]^T + bias) (+ residual)
+// tcgen05.mma (kind::f16, M=128 x N=128 x K=16 per instruction, fp32 accumulators in TMEM), operands
+// staged by TMA with the 128-byte swizzle through a 4-stage mbarrier ring.  Warp roles: warp 0 = TMA
+// producer, warp 1 = MMA issuer (one elected lane), warp 2 = TMEM allocator, warps 4-7 = epilogue
+// (tcgen05.ld -> bias / activation / residual -> global).  Contract: include/objcavit_b200.h.
+#include "tc_common.cuh"
+
+namespace tc {
+
+EncodeTiledFn get_encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t ld,
+                      uint32_t box_rows, uint32_t box_cols, CUtensorMapSwizzle swz) {
+  EncodeTiledFn enc = get_encode_tiled();
+  if (!enc) return OCV_E_DRIVER;
+  if ((reinterpret_cast<uintptr_t>(base) & 15) || ((ld * 2) & 15)) return OCV_E_ALIGN;
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {box_cols, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? OCV_OK : OCV_E_DRIVER;
+}
+
+}  // namespace tc
+
+namespace {
+
+using namespace tc;
+
+constexpr int GM = 128, GN = 128, GK = 64, STAGES = 4;
+constexpr int A_BYTES = GM * GK * 2, B_BYTES = GN * GK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+
+struct GemmParams {
+  const float* bias;
+  const float* residual;
+  void* C;
+  int M, N, K, ldc, act, c_is_bf16, k_per_split;
+};
+
+__global__ void __launch_bounds__(256, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base_u32 = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024 - (base_u32 & 1023)) & 1023);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  uint64_t* empty = full + STAGES;
+  uint64_t* tmem_full = empty + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int m0 = blockIdx.y * GM, n0 = blockIdx.x * GN;
+  int k_begin = 0, k_end = p.K;
+  if (p.k_per_split > 0) {
+    k_begin = blockIdx.z * p.k_per_split;
+    k_end = min(p.K, k_begin + p.k_per_split);
+  }
+  const int n_k = (k_end > k_begin) ? (k_end - k_begin + GK - 1) / GK : 0;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(tmem_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, GN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_d = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      for (int it = 0; it < n_k; ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        mbar_arrive_expect_tx(&full[s], STAGE_BYTES);
+        uint8_t* a = smem + s * STAGE_BYTES;
+        tma_load_2d(a, &tmA, &full[s], k_begin + it * GK, m0);
+        tma_load_2d(a + A_BYTES, &tmB, &full[s], k_begin + it * GK, n0);
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16(GM, GN);
+      for (int it = 0; it < n_k; ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t a = smem_u32(smem + s * STAGE_BYTES);
+        const uint64_t da = desc_kmajor_sw128(a), db = desc_kmajor_sw128(a + A_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < GK / 16; ++kk)
+          umma_bf16(tmem_d, da + (uint64_t)(kk * 2), db + (uint64_t)(kk * 2), idesc, (it | kk) != 0);
+        umma_commit(&empty[s]);
+      }
+      umma_commit(tmem_full);
+    }
+  } else if (warp >= 4) {
+    const int quarter = warp % 4;
+    const int m = m0 + quarter * 32 + lane;
+    if (n_k > 0) {
+      mbar_wait(tmem_full, 0);
+      tc_fence_after();
+    }
+    const bool split = p.k_per_split > 0;
+#pragma unroll 1
+    for (int c = 0; c < GN / 32; ++c) {
+      uint32_t r[32];
+      if (n_k > 0) {
+        tmem_ld32(tmem_d + ((uint32_t)(quarter * 32) << 16) + c * 32, r);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = 0;
+      }
+      if (m >= p.M) continue;
+      const int nb = n0 + c * 32;
+      if (nb >= p.N) continue;
+      float v[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+      if (!split) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const int n = nb + j;
+          if (n < p.N) {
+            if (p.bias) v[j] += p.bias[n];
+            if (p.act == OCV_ACT_RELU) v[j] = fmaxf(v[j], 0.f);
+            else if (p.act == OCV_ACT_LEAKY_RELU) v[j] = v[j] > 0.f ? v[j] : 0.01f * v[j];
+            if (p.residual) v[j] += p.residual[(long long)m * p.ldc + n];
+          }
+        }
+      }
+      const bool full_chunk = (nb + 32 <= p.N);
+      if (split || !p.c_is_bf16) {
+        float* crow = static_cast<float*>(p.C) + (split ? (long long)blockIdx.z * p.M * p.ldc : 0) +
+                      (long long)m * p.ldc + nb;
+        if (full_chunk && (p.ldc % 4 == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<float4*>(crow + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        } else {
+          for (int j = 0; j < 32; ++j)
+            if (nb + j < p.N) crow[j] = v[j];
+        }
+      } else {
+        __nv_bfloat16* crow = static_cast<__nv_bfloat16*>(p.C) + (long long)m * p.ldc + nb;
+        if (full_chunk && (p.ldc % 8 == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint4 u;
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j], v[j + 1]), h1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
+            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]), h3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
+            u.x = *reinterpret_cast<uint32_t*>(&h0);
+            u.y = *reinterpret_cast<uint32_t*>(&h1);
+            u.z = *reinterpret_cast<uint32_t*>(&h2);
+            u.w = *reinterpret_cast<uint32_t*>(&h3);
+            *reinterpret_cast<uint4*>(crow + j) = u;
+          }
+        } else {
+          for (int j = 0; j < 32; ++j)
+            if (nb + j < p.N) crow[j] = __float2bfloat16(v[j]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_d, GN);
+}
+
+// out = act(sum_z part[z] + bias) + residual   (fixed order -> deterministic)
+__global__ void gemm_splitk_reduce_kernel(const float* __restrict__ part, const float* __restrict__ bias,
+                                          const float* __restrict__ residual, void* __restrict__ out, int M, int N,
+                                          int ldc, int splits, int act, int c_is_bf16) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)M * N) return;
+  const int m = (int)(i / N), n = (int)(i - (long long)m * N);
+  float v = 0.f;
+  for (int z = 0; z < splits; ++z) v += part[((long long)z * M + m) * N + n];
+  if (bias) v += bias[n];
+  if (act == OCV_ACT_RELU) v = fmaxf(v, 0.f);
+  else if (act == OCV_ACT_LEAKY_RELU) v = v > 0.f ? v : 0.01f * v;
+  if (residual) v += residual[(long long)m * ldc + n];
+  if (c_is_bf16) static_cast<__nv_bfloat16*>(out)[(long long)m * ldc + n] = __float2bfloat16(v);
+  else static_cast<float*>(out)[(long long)m * ldc + n] = v;
+}
+
+}  // namespace
+
+extern "C" long long ocv_gemm_bf16_workspace(int M, int N, int K, int split_k) {
+  if (split_k <= 1 || M <= 0 || N <= 0) return 0;
+  return (long long)split_k * M * N * (long long)sizeof(float);
+}
+
+extern "C" int ocv_gemm_bf16(const void* A, const void* Wt, const float* bias, const float* residual, void* C, int M,
+                             int N, int K, int lda, int ldb, int ldc, int act, int c_is_bf16, int split_k,
+                             void* workspace, void* stream) {
+  OCV_CHECK_ARG(A && Wt && C && M > 0 && N > 0 && K > 0);
+  OCV_CHECK_SHAPE(K % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0);
+  if (split_k < 1) split_k = 1;
+  OCV_CHECK_ARG(split_k == 1 || workspace);
+  if (int s = ocv_require_sm100()) return s;
+  CUtensorMap tmA, tmB;
+  if (int s = tc::make_tmap_2d_bf16(&tmA, A, M, K, lda, GM, GK, CU_TENSOR_MAP_SWIZZLE_128B)) return s;
+  if (int s = tc::make_tmap_2d_bf16(&tmB, Wt, N, K, ldb, GN, GK, CU_TENSOR_MAP_SWIZZLE_128B)) return s;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);
+    if (e != cudaSuccess) return (int)e;
+    attr_set = true;
+  }
+  GemmParams p{};
+  p.bias = bias;
+  p.residual = residual;
+  p.M = M; p.N = N; p.K = K; p.act = act;
+  dim3 grid(ceil_div(N, GN), ceil_div(M, GM), split_k);
+  if (split_k > 1) {
+    p.C = workspace;
+    p.ldc = N;
+    p.c_is_bf16 = 0;
+    p.k_per_split = ceil_div(ceil_div(K, split_k), GK) * GK;
+  } else {
+    p.C = C;
+    p.ldc = ldc;
+    p.c_is_bf16 = c_is_bf16;
+    p.k_per_split = 0;
+  }
+  gemm_bf16_kernel<<<grid, 256, GEMM_SMEM, ocv_stream(stream)>>>(tmA, tmB, p);
+  if (int s = ocv_launch_status()) return s;
+  if (split_k > 1) {
+    const long long n = (long long)M * N;
+    gemm_splitk_reduce_kernel<<<(unsigned)ceil_div<long long>(n, 256), 256, 0, ocv_stream(stream)>>>(
+        static_cast<const float*>(workspace), bias, residual, C, M, N, ldc, split_k, act, c_is_bf16);
+    return ocv_launch_status();
+  }
+  return OCV_OK;
+}

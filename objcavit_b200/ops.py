@@ -1,0 +1,286 @@
+"""Thin torch-tensor wrappers over the C ABI (``include/objcavit_b200.h``).
+
+PyTorch is used for device memory (the caching allocator), streams and dtypes only: every wrapper
+validates its tensors, allocates outputs/workspaces and passes raw ``data_ptr()``s plus the current
+stream to the kernel library.  No wrapper computes anything with torch ops.
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+ACT_NONE, ACT_RELU, ACT_LEAKY_RELU = 0, 1, 2
+NORM_CODES = {"linear": 0, "softmax": 1}  # anything else -> sigmoid (miniViT.py:40-41)
+
+# number of kernel launches issued through this module (bench.py reports it as gpu_launches)
+launch_count = 0
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _chk(t: torch.Tensor, dtype, name: str):
+    if not t.is_cuda:
+        raise _lib.OcvError(f"{name} must be a CUDA tensor: objcavit_b200 has no CPU path")
+    if t.dtype != dtype:
+        raise _lib.OcvError(f"{name} must be {dtype}, got {t.dtype}")
+
+
+# bench.py sets `timed_kernel` to an entry-point name to get CUDA-event durations of that kernel on
+# the launching stream (list of (start, stop) events in `timed_events`).
+timed_kernel = None
+timed_events = []
+
+
+def _call(name: str, *args, launches: int = 1):
+    global launch_count
+    launch_count += launches
+    if timed_kernel == name:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        _lib.check(getattr(_lib.lib(), name)(*args), name)
+        e1.record()
+        timed_events.append((e0, e1))
+        return
+    _lib.check(getattr(_lib.lib(), name)(*args), name)
+
+
+def _row_major_2d(t: torch.Tensor, name: str):
+    """(rows, cols, ld) of a 2-D view whose last dim is contiguous."""
+    if t.dim() != 2 or t.stride(1) != 1:
+        raise _lib.OcvError(f"{name}: expected a 2-D tensor with unit inner stride, got {tuple(t.shape)} {t.stride()}")
+    return t.shape[0], t.shape[1], t.stride(0)
+
+
+def linear(a: torch.Tensor, w: torch.Tensor, bias=None, act: int = ACT_NONE, residual=None, out=None):
+    """out[M,N] = act(a[M,K] @ w[N,K]^T + bias) + residual   (fp32)."""
+    _chk(a, torch.float32, "a"); _chk(w, torch.float32, "w")
+    M, K, lda = _row_major_2d(a, "a")
+    N, K2, ldb = _row_major_2d(w, "w")
+    assert K == K2, (a.shape, w.shape)
+    if out is None:
+        out = torch.empty(M, N, device=a.device, dtype=torch.float32)
+    _, _, ldc = _row_major_2d(out, "out")
+    if residual is not None:
+        assert residual.shape == out.shape and residual.stride() == out.stride()
+    _call("ocv_linear_f32", a.data_ptr(), w.data_ptr(), _ptr(bias), _ptr(residual), out.data_ptr(),
+          M, N, K, lda, ldb, ldc, 1, act, 1, 0, 0, 0, _stream())
+    return out
+
+
+def batched_matmul_nn(a: torch.Tensor, b: torch.Tensor, out=None):
+    """out[n] = a[n] ([M,K], any batch/row stride) @ b[n] ([K,N] contiguous)   (fp32)."""
+    _chk(a, torch.float32, "a"); _chk(b, torch.float32, "b")
+    Bn, M, K = a.shape
+    _, K2, N = b.shape
+    assert K == K2 and a.stride(2) == 1 and b.is_contiguous()
+    if out is None:
+        out = torch.empty(Bn, M, N, device=a.device, dtype=torch.float32)
+    _call("ocv_linear_f32", a.data_ptr(), b.data_ptr(), None, None, out.data_ptr(), M, N, K,
+          a.stride(1), N, N, 0, ACT_NONE, Bn, a.stride(0), K * N, M * N, _stream())
+    return out
+
+
+def patch_embed(x: torch.Tensor, w: torch.Tensor, bias, pos, P: int = 16):
+    """tokens [B,S,E] from NCHW fp32 features (patch conv + bias + positional rows)."""
+    _chk(x, torch.float32, "x"); _chk(w, torch.float32, "w")
+    assert x.is_contiguous() and w.is_contiguous()
+    B, Cc, h, wd = x.shape
+    E = w.shape[0]
+    S = (h // P) * (wd // P)
+    if pos is not None:
+        assert pos.is_contiguous() and pos.shape[0] >= S and pos.shape[1] == E
+    ws_bytes = _lib.lib().ocv_patch_embed_f32_workspace(B, Cc, h, wd, P, E)
+    ws = torch.empty(max(ws_bytes, 4) // 4, device=x.device, dtype=torch.float32)
+    out = torch.empty(B, S, E, device=x.device, dtype=torch.float32)
+    _call("ocv_patch_embed_f32", x.data_ptr(), w.data_ptr(), _ptr(bias), _ptr(pos), out.data_ptr(),
+          B, Cc, h, wd, P, E, ws.data_ptr(), _stream(), launches=2)
+    return out
+
+
+def add_layernorm(x: torch.Tensor, r, gamma, beta, zero_rows=None, out=None):
+    _chk(x, torch.float32, "x")
+    assert x.is_contiguous() and (r is None or r.is_contiguous())
+    E = x.shape[-1]
+    rows = x.numel() // E
+    if out is None:
+        out = torch.empty_like(x)
+    _call("ocv_add_layernorm_f32", x.data_ptr(), _ptr(r), gamma.data_ptr(), beta.data_ptr(), out.data_ptr(),
+          rows, E, _ptr(zero_rows), _stream())
+    return out
+
+
+def mha_core(q, k, v, key_padding_mask=None, heads: int = 4):
+    """q [B,Sq,E], k/v [B,Sk,E] views with unit channel stride -> [B,Sq,E]."""
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _chk(t, torch.float32, n)
+        assert t.dim() == 3 and t.stride(2) == 1
+    B, Sq, E = q.shape
+    Sk = k.shape[1]
+    out = torch.empty(B, Sq, E, device=q.device, dtype=torch.float32)
+    if key_padding_mask is not None:
+        _chk(key_padding_mask, torch.uint8, "key_padding_mask")
+        assert key_padding_mask.is_contiguous() and key_padding_mask.shape == (B, Sk)
+    _call("ocv_mha_core_f32", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), _ptr(key_padding_mask),
+          B, Sq, Sk, heads, E // heads, q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0),
+          v.stride(1), out.stride(0), out.stride(1), _stream())
+    return out
+
+
+def pad_objects(src: torch.Tensor, offsets: torch.Tensor, B: int, L: int, n_max: int, pad_value: float,
+                left_pad: bool, want_mask: bool = True, mask_offsets=None):
+    _chk(src, torch.float32, "src"); _chk(offsets, torch.int32, "offsets")
+    assert src.is_contiguous() and offsets.numel() == B + 1
+    E = src.shape[1]
+    dst = torch.empty(B, L, E, device=src.device, dtype=torch.float32)
+    mask = torch.empty(B, L, device=src.device, dtype=torch.uint8) if want_mask else None
+    _call("ocv_pad_objects_f32", src.data_ptr(), offsets.data_ptr(), _ptr(mask_offsets), dst.data_ptr(), _ptr(mask),
+          B, L, n_max, E,
+          float(pad_value), int(left_pad), _stream())
+    return dst, mask
+
+
+def patch_coords(gh: int, gw: int, P: int, device) -> torch.Tensor:
+    out = torch.empty(gh * gw, 4, device=device, dtype=torch.float32)
+    _call("ocv_patch_coords_f32", out.data_ptr(), gh, gw, P, _stream())
+    return out
+
+
+def grid_sample_pos(table: torch.Tensor, pts: torch.Tensor, gh: int, gw: int, norm_mode: int = 0,
+                    div0: float = 1.0, div1: float = 1.0, want_idx: bool = False):
+    _chk(table, torch.float32, "table"); _chk(pts, torch.float32, "pts")
+    assert table.is_contiguous() and pts.is_contiguous() and pts.shape[1] == 2
+    N, E = pts.shape[0], table.shape[1]
+    assert table.shape[0] >= gh * gw
+    out = torch.empty(N, E, device=table.device, dtype=torch.float32)
+    idx = torch.empty(N, 4, device=table.device, dtype=torch.int32) if want_idx else None
+    _call("ocv_grid_sample_pos_f32", table.data_ptr(), pts.data_ptr(), out.data_ptr(), _ptr(idx), N, gh, gw, E,
+          norm_mode, float(div0), float(div1), _stream())
+    return (out, idx) if want_idx else out
+
+
+def ps_roi_align_pos(table: torch.Tensor, boxes: torch.Tensor, gh: int, gw: int, spatial_scale: float,
+                     boxes_are_xywh: bool, want_plan: bool = False):
+    _chk(table, torch.float32, "table"); _chk(boxes, torch.float32, "boxes")
+    assert table.is_contiguous() and boxes.is_contiguous() and boxes.shape[1] == 4
+    N, E = boxes.shape[0], table.shape[1]
+    assert table.shape[0] >= gh * gw
+    out = torch.empty(N, E, device=table.device, dtype=torch.float32)
+    plan = torch.empty(N, 2, device=table.device, dtype=torch.int32) if want_plan else None
+    _call("ocv_ps_roi_align_pos_f32", table.data_ptr(), boxes.data_ptr(), out.data_ptr(), _ptr(plan), N, gh, gw, E,
+          float(spatial_scale), int(boxes_are_xywh), _stream())
+    return (out, plan) if want_plan else out
+
+
+def bins(y_raw: torch.Tensor, norm: str, min_depth: Optional[float] = None, max_depth: Optional[float] = None):
+    """-> (widths_normed [B,K], edges [B,K+1] | None, centres [B,K] | None)."""
+    _chk(y_raw, torch.float32, "y_raw")
+    assert y_raw.is_contiguous()
+    B, K = y_raw.shape
+    widths = torch.empty_like(y_raw)
+    code = NORM_CODES.get(norm, 2)
+    if min_depth is None:
+        _call("ocv_bins_f32", y_raw.data_ptr(), widths.data_ptr(), None, None, B, K, code, 0.0, 1.0, _stream())
+        return widths, None, None
+    edges = torch.empty(B, K + 1, device=y_raw.device, dtype=torch.float32)
+    centres = torch.empty(B, K, device=y_raw.device, dtype=torch.float32)
+    _call("ocv_bins_f32", y_raw.data_ptr(), widths.data_ptr(), edges.data_ptr(), centres.data_ptr(), B, K, code,
+          float(min_depth), float(max_depth), _stream())
+    return widths, edges, centres
+
+
+def edges_from_widths(widths: torch.Tensor, min_depth: float, max_depth: float):
+    """edges/centres from already-normalised widths (the AdaBins/GraphBins tail, AdaBins.py:79-85)."""
+    _chk(widths, torch.float32, "widths")
+    assert widths.is_contiguous()
+    B, K = widths.shape
+    edges = torch.empty(B, K + 1, device=widths.device, dtype=torch.float32)
+    centres = torch.empty(B, K, device=widths.device, dtype=torch.float32)
+    _call("ocv_bins_f32", widths.data_ptr(), None, edges.data_ptr(), centres.data_ptr(), B, K, 3,
+          float(min_depth), float(max_depth), _stream())
+    return edges, centres
+
+
+def conv3x3(x: torch.Tensor, w: torch.Tensor, bias):
+    _chk(x, torch.float32, "x"); _chk(w, torch.float32, "w")
+    assert x.is_contiguous() and w.is_contiguous()
+    B, Cc, h, wd = x.shape
+    out = torch.empty_like(x)
+    _call("ocv_conv3x3_f32", x.data_ptr(), w.data_ptr(), _ptr(bias), out.data_ptr(), B, Cc, h, wd, _stream())
+    return out
+
+
+def tail(ram: torch.Tensor, w_out: torch.Tensor, b_out, centres: torch.Tensor):
+    """depth [B,1,h,w] = sum_k softmax_k(conv1x1(ram)) * centres."""
+    _chk(ram, torch.float32, "ram")
+    assert ram.is_contiguous() and centres.is_contiguous()
+    B, Q, h, wd = ram.shape
+    K = w_out.shape[0]
+    w2 = w_out.view(K, Q)
+    assert w2.is_contiguous()
+    depth = torch.empty(B, 1, h, wd, device=ram.device, dtype=torch.float32)
+    _call("ocv_tail_f32", ram.data_ptr(), w2.data_ptr(), _ptr(b_out), centres.data_ptr(), depth.data_ptr(),
+          B, Q, K, h * wd, _stream())
+    return depth
+
+
+# ---- bf16 tensor-core path --------------------------------------------------------------------------
+
+def nchw_to_nhwc_bf16(x: torch.Tensor):
+    assert x.is_cuda and x.is_contiguous() and x.dtype in (torch.float32, torch.bfloat16)
+    B, Cc, h, wd = x.shape
+    out = torch.empty(B, h, wd, Cc, device=x.device, dtype=torch.bfloat16)
+    _call("ocv_nchw_to_nhwc_bf16", x.data_ptr(), out.data_ptr(), B, Cc, h, wd, int(x.dtype == torch.bfloat16), _stream())
+    return out
+
+
+def gemm_bf16(a: torch.Tensor, w: torch.Tensor, bias=None, act: int = ACT_NONE, residual=None,
+              out_dtype=torch.float32, split_k: int = 1, out=None):
+    """out[M,N] = act(a[M,K] @ w[N,K]^T + bias) + residual; a, w bf16; tcgen05 tensor cores."""
+    _chk(a, torch.bfloat16, "a"); _chk(w, torch.bfloat16, "w")
+    M, K, lda = _row_major_2d(a, "a")
+    N, K2, ldb = _row_major_2d(w, "w")
+    assert K == K2
+    if out is None:
+        out = torch.empty(M, N, device=a.device, dtype=out_dtype)
+    _, _, ldc = _row_major_2d(out, "out")
+    ws = None
+    if split_k > 1:
+        ws = torch.empty(split_k * M * N, device=a.device, dtype=torch.float32)
+    if residual is not None:
+        _chk(residual, torch.float32, "residual")
+        assert residual.stride(0) == ldc
+    _call("ocv_gemm_bf16", a.data_ptr(), w.data_ptr(), _ptr(bias), _ptr(residual), out.data_ptr(), M, N, K,
+          lda, ldb, ldc, act, int(out.dtype == torch.bfloat16), split_k, _ptr(ws), _stream(),
+          launches=2 if split_k > 1 else 1)
+    return out
+
+
+def pack_conv3x3_bf16(w: torch.Tensor):
+    _chk(w, torch.float32, "w")
+    assert w.is_contiguous() and tuple(w.shape) == (128, 128, 3, 3)
+    out = torch.empty(9, 128, 128, device=w.device, dtype=torch.bfloat16)
+    _call("ocv_pack_conv3x3_bf16", w.data_ptr(), out.data_ptr(), _stream())
+    return out
+
+
+def fold_queries_bf16(w_out: torch.Tensor, b_out, queries: torch.Tensor, b3):
+    """Mb [B,K,E] bf16, blog [B,K] fp32 from conv_out weights and the per-image queries view [B,Q,E]."""
+    _chk(queries, torch.float32, "queries")
+    B, Q, E = queries.shape
+    assert queries.stride(2) == 1
+    K = w_out.shape[0]
+    w2 = w_out.view(K, Q)
+    Mb = torch.empty(B, K, E, device=queries.device, dtype=torch.bfloat16)
+    blog = torch.empty(B, K, device=queries.device, dtype=torch.float32)
+    _call("ocv_fold_queries_bf16", w2.data_ptr(), _ptr(b_out), queries.data_ptr(), queries.stride(0), queries.stride(1),
+          _ptr(b3), Mb.data_ptr(), blog.data_ptr(), B, K, Q, E, _stream())
+    return Mb, blog

@@ -1,0 +1,211 @@
+"""GPU: every C-ABI stage against the CPU oracle / plain torch fp32 on the same seeded inputs.
+Index work is compared bit-exactly; fp32 stages to 1e-5..1e-4 relative (tolerances from north_star)."""
+import math
+import os
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from helpers import GOLD, rel_err
+from oracle import head as oh
+from oracle import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def g(seed):
+    return torch.Generator().manual_seed(seed)
+
+
+def test_linear_and_batched_matmul(cuda):
+    from objcavit_b200 import ops
+    a = torch.randn(301, 130, generator=g(1)); w = torch.randn(77, 130, generator=g(2)); b = torch.randn(77, generator=g(3))
+    r = torch.randn(301, 77, generator=g(4))
+    want = F.leaky_relu(a @ w.T + b, 0.01) + r
+    got = ops.linear(a.to(cuda), w.to(cuda), b.to(cuda), ops.ACT_LEAKY_RELU, r.to(cuda))
+    assert rel_err(got, want) < 1e-5
+    # strided A (token-0 view) and relu
+    tok = torch.randn(3, 20, 128, generator=g(5))
+    w2 = torch.randn(256, 128, generator=g(6))
+    got = ops.linear(tok.to(cuda)[:, 0, :], w2.to(cuda), None, ops.ACT_RELU)
+    assert rel_err(got, torch.relu(tok[:, 0, :] @ w2.T)) < 1e-5
+    # PixelWiseDotProduct form
+    q = torch.randn(2, 131, 128, generator=g(7)); x = torch.randn(2, 128, 333, generator=g(8))
+    got = ops.batched_matmul_nn(q.to(cuda)[:, 1:129, :], x.to(cuda))
+    assert rel_err(got, q[:, 1:129, :] @ x) < 1e-5
+
+
+def test_patch_embed(cuda):
+    from objcavit_b200 import ops
+    x = torch.randn(2, 128, 48, 64, generator=g(1)); w = torch.randn(128, 128, 16, 16, generator=g(2)) * 0.01
+    b = torch.randn(128, generator=g(3)); pos = torch.rand(50, 128, generator=g(4))
+    want = F.conv2d(x, w, b, stride=16).flatten(2).permute(0, 2, 1) + pos[:12]
+    got = ops.patch_embed(x.to(cuda), w.to(cuda), b.to(cuda), pos.to(cuda))
+    assert rel_err(got, want) < 1e-5
+
+
+def test_add_layernorm_and_zero_rows(cuda):
+    from objcavit_b200 import ops
+    x = torch.randn(37, 128, generator=g(1)); r = torch.randn(37, 128, generator=g(2))
+    gm = torch.randn(128, generator=g(3)); bt = torch.randn(128, generator=g(4))
+    z = (torch.arange(37) % 5 == 0).to(torch.uint8)
+    want = F.layer_norm(x + r, (128,), gm, bt, 1e-5).masked_fill(z.bool()[:, None], 0.0)
+    got = ops.add_layernorm(x.to(cuda), r.to(cuda), gm.to(cuda), bt.to(cuda), z.to(cuda))
+    assert rel_err(got, want) < 1e-5
+
+
+@pytest.mark.parametrize("Sq,Sk", [(300, 300), (45, 77), (9, 9)])
+def test_mha_core_with_key_padding(cuda, Sq, Sk):
+    from objcavit_b200 import ops
+    B = 3
+    qkv = torch.randn(B, max(Sq, Sk), 384, generator=g(Sq))
+    q, k, v = qkv[:, :Sq, 0:128], qkv[:, :Sk, 128:256], qkv[:, :Sk, 256:]
+    mask = torch.zeros(B, Sk, dtype=torch.bool)
+    mask[0, Sk // 2:] = True
+    mask[2, 1:] = True
+    sc = (q.view(B, Sq, 4, 32).transpose(1, 2) / math.sqrt(32)) @ k.reshape(B, Sk, 4, 32).transpose(1, 2).transpose(-1, -2)
+    sc = sc.masked_fill(mask[:, None, None, :], float("-inf"))
+    want = (torch.softmax(sc, -1) @ v.reshape(B, Sk, 4, 32).transpose(1, 2)).transpose(1, 2).reshape(B, Sq, 128)
+    d = qkv.to(cuda)
+    got = ops.mha_core(d[:, :Sq, 0:128], d[:, :Sk, 128:256], d[:, :Sk, 256:], mask.to(torch.uint8).to(cuda))
+    assert rel_err(got, want) < 1e-5
+
+
+def test_pad_objects_bit_exact(cuda):
+    from objcavit_b200 import engine, ops
+    counts = [3, 1, 7, 4]
+    rows = torch.randn(sum(counts), 128, generator=g(1))
+    seqs = list(torch.split(rows, counts))
+    want, wmask = oh.pad_objects(seqs)
+    ob = engine.ObjectBatch(rows.to(cuda), counts)
+    got, mask = ops.pad_objects(ob.rows, ob.offsets, 4, 7, 7, 0.0001, False)
+    assert torch.equal(got.cpu(), want) and torch.equal(mask.cpu().bool(), wmask)
+    want_s, wmask_s = oh.pad_objects(seqs, S=20)          # left-padded objects, right-padded mask (F5)
+    uni = torch.arange(0, 5 * 7, 7, dtype=torch.int32).to(cuda)
+    got_s, mask_s = ops.pad_objects(got.view(28, 128), uni, 4, 20, 7, 0.0001, True, mask_offsets=ob.offsets)
+    assert torch.equal(got_s.cpu(), want_s) and torch.equal(mask_s.cpu().bool(), wmask_s)
+
+
+def test_grid_sample_index_mapping_bit_exact(cuda):
+    from objcavit_b200 import ops
+    gold = torch.load(os.path.join(GOLD, "grid_ops.pt"))
+    table = gold["table"]
+    for (h, w) in ((176, 608), (240, 320)):
+        grid, gh, gw = oh._grid_for(table, h, w)
+        pts = gold["cases"][f"gs_{h}x{w}"]["pts"]
+        want, widx, _ = oh.grid_sample_points(grid, pts[:, 0], pts[:, 1])
+        got, idx = ops.grid_sample_pos(table.to(cuda), pts.to(cuda).contiguous(), gh, gw, 0, want_idx=True)
+        assert torch.equal(idx.cpu().long(), widx)
+        assert torch.equal(got.cpu(), want)                       # same op order as the restatement
+        assert float((got.cpu() - gold["cases"][f"gs_{h}x{w}"]["want"]).abs().max()) < 5e-6   # vs F.grid_sample
+
+
+def test_ps_roi_align_bit_exact_incl_nan(cuda):
+    from objcavit_b200 import ops
+    gold = torch.load(os.path.join(GOLD, "grid_ops.pt"))
+    table = gold["table"]
+    for (h, w) in ((176, 608), (240, 320)):
+        grid, gh, gw = oh._grid_for(table, h, w)
+        for tag, scale in (("obj", 1 / 32), ("img", 1 / 16)):
+            c = gold["cases"][f"roi_{tag}_{h}x{w}"]          # want = torchvision.ops.ps_roi_align itself
+            got, plan = ops.ps_roi_align_pos(table.to(cuda), c["xyxy"].to(cuda).contiguous(), gh, gw, scale, False,
+                                             want_plan=True)
+            _, plans = oh.ps_roi_align_1x1(grid, c["xyxy"], scale)
+            assert plan.cpu().tolist() == [[p[0], p[1]] for p in plans]
+            want = c["want"]
+            assert torch.equal(torch.isnan(got.cpu()), torch.isnan(want))
+            m = ~torch.isnan(want)
+            assert torch.equal(got.cpu()[m], want[m])
+
+
+def test_grid_random_module_quirks(cuda):
+    """GridRandomPositionalEmbeddings.forward through the module surface, 'img' and 'obj', both modes."""
+    from objcavit_b200.config import builtin_args
+    from objcavit_b200.modules import GridRandomPositionalEmbeddings
+    args = builtin_args("kitti_ocv_grid_random_roi_align")
+    feats = torch.zeros(2, 128, 176, 208)
+    _, boxes = synth.make_objects(1, 176, 208, 12, seed=3)
+    boxes = torch.cat([boxes[0], torch.tensor([[-1., -1., -1., -1.]])])
+    pc = oh.patch_coords(2, 11, 13)
+    for mode in ("centre", "roi_align"):
+        mod = GridRandomPositionalEmbeddings(args, 128, 16, mode).to(cuda)
+        table = mod.positional_encodings.data.cpu()
+        n = 2 if mode == "centre" else 4
+        want_obj = oh.grid_random_pos(table, mode, boxes[:, :n], 176, 208, "obj")
+        want_img = oh.grid_random_pos(table, mode, pc[..., :n], 176, 208, "img")
+        with torch.no_grad():
+            got_obj = mod(boxes[:, :n].to(cuda), feats.to(cuda), "obj").cpu()
+            got_img = mod(pc[..., :n].to(cuda), feats.to(cuda), "img").cpu()
+        assert torch.equal(torch.isnan(got_obj), torch.isnan(want_obj))
+        m = ~torch.isnan(want_obj)
+        assert torch.equal(got_obj[m], want_obj[m]) and torch.equal(got_img, want_img)
+
+
+@pytest.mark.parametrize("norm", ["linear", "softmax", "sigmoid"])
+def test_bins(cuda, norm):
+    from objcavit_b200 import ops
+    y = torch.randn(5, 256, generator=g(2)) * 3
+    if norm == "linear":
+        wn = torch.relu(y) + 0.1
+    elif norm == "softmax":
+        wn = torch.exp(y - y.max(1, keepdim=True).values)
+    else:
+        wn = torch.sigmoid(y)
+    wn = wn / wn.sum(1, keepdim=True)
+    edges, centres = oh.bin_edges_and_centres(wn, 0.001, 80.0)
+    w, e, c = ops.bins(y.to(cuda), norm, 0.001, 80.0)
+    assert rel_err(w, wn) < 1e-5 and rel_err(e, edges) < 1e-5 and rel_err(c, centres) < 1e-5
+    e2, c2 = ops.edges_from_widths(wn.to(cuda), 0.001, 80.0)
+    assert rel_err(e2, edges) < 1e-6 and rel_err(c2, centres) < 1e-6
+
+
+def test_conv3x3(cuda):
+    from objcavit_b200 import ops
+    x = torch.randn(2, 128, 37, 70, generator=g(1)); w = torch.randn(128, 128, 3, 3, generator=g(2)) * 0.03
+    b = torch.randn(128, generator=g(3))
+    got = ops.conv3x3(x.to(cuda), w.to(cuda), b.to(cuda))
+    assert rel_err(got, F.conv2d(x, w, b, padding=1)) < 1e-5
+
+
+def test_tail(cuda):
+    from objcavit_b200 import ops
+    ram = torch.randn(2, 128, 23, 41, generator=g(1)) * 2
+    w = torch.randn(256, 128, 1, 1, generator=g(2)) * 0.2; b = torch.randn(256, generator=g(3))
+    wn = torch.rand(2, 256, generator=g(4)) + 0.1
+    wn = wn / wn.sum(1, keepdim=True)
+    edges, centres = oh.bin_edges_and_centres(wn, 0.001, 10.0)
+    want = (torch.softmax(F.conv2d(ram, w, b), 1) * centres[:, :, None, None]).sum(1, keepdim=True)
+    got = ops.tail(ram.to(cuda), w.to(cuda), b.to(cuda), centres.to(cuda))
+    assert rel_err(got, want) < 1e-5
+
+
+@pytest.mark.parametrize("M,N,K,split", [(300, 128, 128, 1), (4800, 384, 128, 1), (520, 1024, 128, 1), (777, 128, 1024, 4),
+                                          (600, 128, 32768, 8)])
+def test_gemm_bf16_tcgen05(cuda, M, N, K, split):
+    """tcgen05 GEMM vs an fp32 matmul of the same bf16-rounded operands."""
+    from objcavit_b200 import ops
+    a = (torch.randn(M, K, generator=g(M)) * 0.5).bfloat16(); w = (torch.randn(N, K, generator=g(N + K)) * 0.5).bfloat16()
+    b = torch.randn(N, generator=g(3)); r = torch.randn(M, N, generator=g(4))
+    want = torch.relu(a.float() @ w.float().T + b) + r
+    got = ops.gemm_bf16(a.to(cuda), w.to(cuda), b.to(cuda), ops.ACT_RELU, r.to(cuda), split_k=split)
+    assert rel_err(got, want) < 2e-5 * max(1.0, math.sqrt(K / 128))
+    got16 = ops.gemm_bf16(a.to(cuda), w.to(cuda), b.to(cuda), ops.ACT_RELU, None, out_dtype=torch.bfloat16, split_k=split)
+    assert rel_err(got16.float(), torch.relu(a.float() @ w.float().T + b)) < 1e-2
+
+
+def test_layout_and_weight_packing(cuda):
+    from objcavit_b200 import ops
+    x = torch.randn(2, 128, 19, 45, generator=g(1))
+    got = ops.nchw_to_nhwc_bf16(x.to(cuda))
+    assert torch.equal(got.cpu(), x.permute(0, 2, 3, 1).contiguous().bfloat16())
+    got = ops.nchw_to_nhwc_bf16(x.bfloat16().to(cuda))
+    assert torch.equal(got.cpu(), x.bfloat16().permute(0, 2, 3, 1).contiguous())
+    w = torch.randn(128, 128, 3, 3, generator=g(2))
+    assert torch.equal(ops.pack_conv3x3_bf16(w.to(cuda)).cpu(), w.permute(2, 3, 0, 1).reshape(9, 128, 128).bfloat16())
+    wout = torch.randn(256, 128, 1, 1, generator=g(3)); bout = torch.randn(256, generator=g(4))
+    tok = torch.randn(2, 140, 128, generator=g(5)); b3 = torch.randn(128, generator=g(6))
+    Mb, blog = ops.fold_queries_bf16(wout.to(cuda), bout.to(cuda), tok.to(cuda)[:, 1:129, :], b3.to(cuda))
+    want = wout.view(256, 128) @ tok[:, 1:129, :]
+    assert rel_err(Mb.float(), want) < 1e-2
+    assert rel_err(blog, bout + want @ b3) < 1e-5
