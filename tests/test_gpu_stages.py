@@ -157,7 +157,7 @@ def test_bins(cuda, norm):
     w, e, c = ops.bins(y.to(cuda), norm, 0.001, 80.0)
     assert rel_err(w, wn) < 1e-5 and rel_err(e, edges) < 1e-5 and rel_err(c, centres) < 1e-5
     e2, c2 = ops.edges_from_widths(wn.to(cuda), 0.001, 80.0)
-    assert rel_err(e2, edges) < 1e-6 and rel_err(c2, centres) < 1e-6
+    assert rel_err(e2, edges) < 5e-6 and rel_err(c2, centres) < 5e-6   # 256-term fp32 running sum
 
 
 def test_conv3x3(cuda):
