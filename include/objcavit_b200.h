@@ -152,18 +152,23 @@ int ocv_gemm_bf16(const void* A, const void* Wt, const float* bias, const float*
                   int M, int N, int K, int lda, int ldb, int ldc, int act, int c_is_bf16, int split_k,
                   void* workspace, void* stream);
 
-/* Fused pixel kernel (one persistent tcgen05 kernel):
- *   conv3x3 (implicit GEMM over an NHWC bf16 halo tile) -> per-image logits GEMM with
- *   Mb[b] = Wout @ Q[b] (bins x channels, bf16) -> per-pixel softmax over K=256 bins -> sum p*centre.
- *   X [B,h,w,128] bf16 NHWC; W3p: packed conv weights from ocv_pack_conv3x3_bf16; b3 [128] fp32;
- *   Mb [B,256,128] bf16; blog [B,256] fp32 (= bout + Wout@(Q[b]@b3 ... see DESIGN.md); centres [B,256];
- *   depth [B,h*w] fp32.
+/* Fused pixel kernel (one persistent tcgen05 kernel, objcavit_b200/csrc/pixel_fused_bf16.cu):
+ *   conv3x3 (implicit GEMM over an NHWC bf16 halo tile, 9 shifted smem descriptors) -> per-image logits GEMM with
+ *   Mb[b] = s * Wout @ Q[b] (bins x channels, bf16) -> per-pixel softmax over K=256 bins -> sum p*centre.
+ *   X [B,h,w,128] bf16 NHWC (16-byte aligned); W3p: packed conv weights from ocv_pack_conv3x3_bf16;
+ *   Mb [B,256,128] bf16 and blog [B,256] fp32 from ocv_fold_queries_bf16 with logit_scale = log2(e)
+ *   (the kernel exponentiates with ex2); centres [B,256] fp32; depth [B,h*w] fp32.
+ *   max_ctas: 0 = one persistent CTA per SM; >0 caps the grid (tests exercise multi-tile CTAs with it).
  * replaces: conv3x3 + PixelWiseDotProduct + conv_out + Softmax + sum (modules/ObjCAViT.py:374-375;
  *   modules/GraphBins.py:109,119; modules/miniViT.py:25,31; modules/AdaBins.py:77,87). */
 int ocv_pack_conv3x3_bf16(const float* W /*[128,128,3,3]*/, void* W3p /*bf16 [9,128,128]*/, void* stream);
+/* Mb[b,k,c] = s * sum_q Wout[k,q] Q[b,q,c];  blog[b,k] = s * (bout[k] + sum_{q,c} Wout[k,q] Q[b,q,c] b3[c]).
+ * (conv_out(Q @ (conv + b3)) == (Wout Q) @ conv + blog: the 128 range-attention channels are folded away.) */
 int ocv_fold_queries_bf16(const float* Wout /*[K,Q]*/, const float* bout /*[K]*/, const float* queries /*[B,Q,E] ld*/,
-                          long long q_bstride, int q_rstride, const float* b3 /*[E]*/,
+                          long long q_bstride, int q_rstride, const float* b3 /*[E]*/, float logit_scale,
                           void* Mb /*bf16 [B,K,E]*/, float* blog /*[B,K]*/, int B, int K, int Q, int E, void* stream);
+int ocv_pixel_fused_bf16(const void* X, const void* W3p, const void* Mb, const float* blog, const float* centres,
+                         float* depth, int B, int h, int w, int max_ctas, void* stream);
 
 #ifdef __cplusplus
 }

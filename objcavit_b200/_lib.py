@@ -40,7 +40,8 @@ PROTOTYPES = {
     "ocv_gemm_bf16_workspace": (i64, [i32, i32, i32, i32]),
     "ocv_gemm_bf16": (i32, [p, p, p, p, p, i32, i32, i32, i32, i32, i32, i32, i32, i32, p, p]),
     "ocv_pack_conv3x3_bf16": (i32, [p, p, p]),
-    "ocv_fold_queries_bf16": (i32, [p, p, p, i64, i32, p, p, p, i32, i32, i32, i32, p]),
+    "ocv_fold_queries_bf16": (i32, [p, p, p, i64, i32, p, f32, p, p, i32, i32, i32, i32, p]),
+    "ocv_pixel_fused_bf16": (i32, [p, p, p, p, p, p, i32, i32, i32, i32, p]),
 }
 
 

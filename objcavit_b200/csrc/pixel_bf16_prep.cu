@@ -52,7 +52,7 @@ __global__ void pack_conv3x3_kernel(const float* __restrict__ W, __nv_bfloat16* 
 constexpr int FQ_BINS = 8;
 __global__ void fold_queries_kernel(const float* __restrict__ Wout, const float* __restrict__ bout,
                                     const float* __restrict__ queries, long long q_bs, int q_rs,
-                                    const float* __restrict__ b3, __nv_bfloat16* __restrict__ Mb,
+                                    const float* __restrict__ b3, float scale, __nv_bfloat16* __restrict__ Mb,
                                     float* __restrict__ blog, int K, int Q, int E) {
   extern __shared__ float ws[];  // [FQ_BINS][Q] then [FQ_BINS][nwarp]
   const int b = blockIdx.y, k0 = blockIdx.x * FQ_BINS, c = threadIdx.x;
@@ -73,7 +73,7 @@ __global__ void fold_queries_kernel(const float* __restrict__ Wout, const float*
   const float bc = b3 ? b3[c] : 0.f;
 #pragma unroll
   for (int i = 0; i < FQ_BINS; ++i) {
-    if (k0 + i < K) Mb[((long long)b * K + k0 + i) * E + c] = __float2bfloat16(acc[i]);
+    if (k0 + i < K) Mb[((long long)b * K + k0 + i) * E + c] = __float2bfloat16(acc[i] * scale);
     const float s = warp_sum(acc[i] * bc);
     if (lane == 0) red[i * nwarp + warp] = s;
   }
@@ -81,7 +81,7 @@ __global__ void fold_queries_kernel(const float* __restrict__ Wout, const float*
   if (threadIdx.x < FQ_BINS && k0 + threadIdx.x < K) {
     float s = bout ? bout[k0 + threadIdx.x] : 0.f;
     for (int w = 0; w < nwarp; ++w) s += red[threadIdx.x * nwarp + w];
-    blog[(long long)b * K + k0 + threadIdx.x] = s;
+    blog[(long long)b * K + k0 + threadIdx.x] = s * scale;
   }
 }
 
@@ -111,13 +111,13 @@ extern "C" int ocv_pack_conv3x3_bf16(const float* W, void* W3p, void* stream) {
 }
 
 extern "C" int ocv_fold_queries_bf16(const float* Wout, const float* bout, const float* queries, long long q_bstride,
-                                     int q_rstride, const float* b3, void* Mb, float* blog, int B, int K, int Q, int E,
-                                     void* stream) {
+                                     int q_rstride, const float* b3, float logit_scale, void* Mb, float* blog, int B, int K,
+                                     int Q, int E, void* stream) {
   OCV_CHECK_ARG(Wout && queries && Mb && blog && B > 0 && K > 0 && Q > 0);
   OCV_CHECK_SHAPE(E % 32 == 0 && E >= 32 && E <= 1024 && B <= 65535);
   if (int s = ocv_require_sm100()) return s;
   const size_t smem = (FQ_BINS * Q + FQ_BINS * (E / 32)) * sizeof(float);
   fold_queries_kernel<<<dim3(ceil_div(K, FQ_BINS), B), E, smem, ocv_stream(stream)>>>(
-      Wout, bout, queries, q_bstride, q_rstride, b3, static_cast<__nv_bfloat16*>(Mb), blog, K, Q, E);
+      Wout, bout, queries, q_bstride, q_rstride, b3, logit_scale, static_cast<__nv_bfloat16*>(Mb), blog, K, Q, E);
   return ocv_launch_status();
 }

@@ -272,7 +272,10 @@ def pack_conv3x3_bf16(w: torch.Tensor):
     return out
 
 
-def fold_queries_bf16(w_out: torch.Tensor, b_out, queries: torch.Tensor, b3):
+LOG2E = 1.4426950408889634
+
+
+def fold_queries_bf16(w_out: torch.Tensor, b_out, queries: torch.Tensor, b3, logit_scale: float = LOG2E):
     """Mb [B,K,E] bf16, blog [B,K] fp32 from conv_out weights and the per-image queries view [B,Q,E]."""
     _chk(queries, torch.float32, "queries")
     B, Q, E = queries.shape
@@ -282,5 +285,20 @@ def fold_queries_bf16(w_out: torch.Tensor, b_out, queries: torch.Tensor, b3):
     Mb = torch.empty(B, K, E, device=queries.device, dtype=torch.bfloat16)
     blog = torch.empty(B, K, device=queries.device, dtype=torch.float32)
     _call("ocv_fold_queries_bf16", w2.data_ptr(), _ptr(b_out), queries.data_ptr(), queries.stride(0), queries.stride(1),
-          _ptr(b3), Mb.data_ptr(), blog.data_ptr(), B, K, Q, E, _stream())
+          _ptr(b3), float(logit_scale), Mb.data_ptr(), blog.data_ptr(), B, K, Q, E, _stream())
     return Mb, blog
+
+
+def pixel_fused_bf16(x_nhwc: torch.Tensor, w3p: torch.Tensor, Mb: torch.Tensor, blog: torch.Tensor,
+                     centres: torch.Tensor, max_ctas: int = 0):
+    """depth [B,1,h,w] fp32 from NHWC bf16 features: conv3x3 -> logits -> softmax -> sum p*centre, one kernel."""
+    _chk(x_nhwc, torch.bfloat16, "x_nhwc"); _chk(w3p, torch.bfloat16, "w3p"); _chk(Mb, torch.bfloat16, "Mb")
+    _chk(blog, torch.float32, "blog"); _chk(centres, torch.float32, "centres")
+    B, h, w, Cc = x_nhwc.shape
+    assert Cc == 128 and x_nhwc.is_contiguous() and w3p.is_contiguous() and Mb.is_contiguous()
+    assert tuple(Mb.shape) == (B, 256, 128) and tuple(blog.shape) == (B, 256) and tuple(centres.shape) == (B, 256)
+    assert blog.is_contiguous() and centres.is_contiguous()
+    depth = torch.empty(B, 1, h, w, device=x_nhwc.device, dtype=torch.float32)
+    _call("ocv_pixel_fused_bf16", x_nhwc.data_ptr(), w3p.data_ptr(), Mb.data_ptr(), blog.data_ptr(),
+          centres.data_ptr(), depth.data_ptr(), B, h, w, int(max_ctas), _stream())
+    return depth

@@ -205,7 +205,47 @@ def test_layout_and_weight_packing(cuda):
     assert torch.equal(ops.pack_conv3x3_bf16(w.to(cuda)).cpu(), w.permute(2, 3, 0, 1).reshape(9, 128, 128).bfloat16())
     wout = torch.randn(256, 128, 1, 1, generator=g(3)); bout = torch.randn(256, generator=g(4))
     tok = torch.randn(2, 140, 128, generator=g(5)); b3 = torch.randn(128, generator=g(6))
-    Mb, blog = ops.fold_queries_bf16(wout.to(cuda), bout.to(cuda), tok.to(cuda)[:, 1:129, :], b3.to(cuda))
+    Mb, blog = ops.fold_queries_bf16(wout.to(cuda), bout.to(cuda), tok.to(cuda)[:, 1:129, :], b3.to(cuda), 1.0)
     want = wout.view(256, 128) @ tok[:, 1:129, :]
     assert rel_err(Mb.float(), want) < 1e-2
     assert rel_err(blog, bout + want @ b3) < 1e-5
+
+
+def _pixel_reference(x, w3, b3, wout, bout, queries, centres):
+    """conv3x3 -> dot product -> conv_out -> softmax -> sum p*c, fp32 torch on the bf16-rounded operands the
+    kernel consumes (x, conv weights, folded Mb, conv tile rounded to bf16)."""
+    xb = x.bfloat16().float()
+    conv = F.conv2d(xb, w3.bfloat16().float(), None, padding=1).bfloat16().float()          # [B,128,h,w]
+    Mb = (wout.view(256, 128) @ queries) * 1.4426950408889634                                 # [B,256,128]
+    blog = (bout + (wout.view(256, 128) @ queries) @ b3) * 1.4426950408889634                 # [B,256]
+    logits = torch.einsum("bkc,bchw->bkhw", Mb.bfloat16().float(), conv) + blog[:, :, None, None]
+    p = torch.softmax(logits * math.log(2.0), 1)
+    return (p * centres[:, :, None, None]).sum(1, keepdim=True)
+
+
+@pytest.mark.parametrize("B,h,w,max_ctas", [(1, 16, 8, 0), (2, 48, 40, 0), (3, 37, 29, 2), (2, 64, 96, 5)])
+def test_pixel_fused_bf16(cuda, B, h, w, max_ctas):
+    """The fused tcgen05 pixel kernel (conv3x3 halo tile + logits GEMM + softmax + expectation), incl. image
+    borders (zero padding through TMA OOB fill), ragged tiles and CTAs that loop over many tiles."""
+    from objcavit_b200 import ops
+    x = torch.randn(B, 128, h, w, generator=g(1))
+    w3 = torch.randn(128, 128, 3, 3, generator=g(2)) * 0.03; b3 = torch.randn(128, generator=g(3)) * 0.1
+    wout = torch.randn(256, 128, 1, 1, generator=g(4)) * 0.1; bout = torch.randn(256, generator=g(5)) * 0.1
+    tok = torch.randn(B, 140, 128, generator=g(6))
+    wn = torch.rand(B, 256, generator=g(7)) + 0.1
+    wn = wn / wn.sum(1, keepdim=True)
+    _, centres = oh.bin_edges_and_centres(wn, 0.001, 10.0)
+    queries = tok[:, 1:129, :]
+    want16 = _pixel_reference(x, w3, b3, wout, bout, queries, centres)
+    want32 = (torch.softmax(F.conv2d(torch.einsum("bqc,bchw->bqhw", queries, F.conv2d(x, w3, b3, padding=1)), wout, bout), 1)
+              * centres[:, :, None, None]).sum(1, keepdim=True)
+    xd = ops.nchw_to_nhwc_bf16(x.to(cuda))
+    w3p = ops.pack_conv3x3_bf16(w3.to(cuda))
+    Mb, blog = ops.fold_queries_bf16(wout.to(cuda), bout.to(cuda), tok.to(cuda)[:, 1:129, :], b3.to(cuda))
+    got = ops.pixel_fused_bf16(xd, w3p, Mb, blog, centres.to(cuda), max_ctas=max_ctas)
+    assert got.shape == (B, 1, h, w)
+    # same rounded operands: accumulation order / ex2.approx differ, and a 1-ulp flip of a bf16-rounded conv value
+    # moves an isolated pixel by a few 1e-3 -> tight on the mean, looser on the max
+    err = (got.cpu() - want16).abs()
+    assert float(err.mean() / want16.abs().mean()) < 1e-4 and rel_err(got, want16) < 1e-2
+    assert rel_err(got, want32) < 2e-2          # north_star bf16 tolerance vs the fp32 chain
