@@ -152,6 +152,43 @@ int ocv_gemm_bf16(const void* A, const void* Wt, const float* bias, const float*
                   int M, int N, int K, int lda, int ldb, int ldc, int act, int c_is_bf16, int split_k,
                   void* workspace, void* stream);
 
+/* ---- bf16 token path ------------------------------------------------------------------------------
+ * Attention core on bf16 operands (tensor-core scores and P@V, fp32 online softmax); same argument meaning as
+ * ocv_mha_core_f32 with q/k/v/out bf16 (strides in elements, multiples of 8; q/k/v 16-byte aligned). */
+int ocv_mha_core_bf16(const void* q, const void* k, const void* v, void* out, const uint8_t* key_padding_mask,
+                      int B, int Sq, int Sk, int heads, int d,
+                      long long q_bstride, int q_rstride, long long k_bstride, int k_rstride,
+                      long long v_bstride, int v_rstride, long long o_bstride, int o_rstride, void* stream);
+
+/* Patch embedding from the NHWC bf16 feature map (tcgen05 GEMM, A operand fetched by a 5-D TMA box, split-K over ky):
+ *   Wp = ocv_pack_patch_weights_bf16(W [E,C,P,P] fp32) -> bf16 [E, (ky,kx,c)];
+ *   tokens[b,s,:] = patch(b,s) . Wp^T + bias + pos[s,:]  -> tok32 fp32 [B,S,E] and/or tok16 bf16 [B,S,E].
+ *   E == 128, (P*C) % 64 == 0, w/P <= 128.  workspace: ocv_patch_embed_bf16_workspace() bytes.
+ * replaces: the same sites as ocv_patch_embed_f32. */
+int ocv_pack_patch_weights_bf16(const float* W, void* Wp, int E, int C, int P, void* stream);
+long long ocv_patch_embed_bf16_workspace(int B, int h, int w, int P);
+int ocv_patch_embed_bf16(const void* X_nhwc_bf16, const void* Wp, const float* bias, const float* pos, float* tok32,
+                         void* tok16, int B, int C, int h, int w, int P, int E, void* workspace, void* stream);
+
+/* Fused MLP chain (fp32 SIMT, one launch): x [R, dims[0]] (row pitch x_ld) -> Linear/LeakyReLU(0.01) x (n_layers-1)
+ *   -> Linear (+ residual [R, dims[n_layers]]) -> out32 fp32 and/or out16 bf16.  weights/biases/dims are HOST arrays
+ *   (of device pointers / ints); weights[l] is [dims[l+1], dims[l]] (nn.Linear layout); every width <= 512.
+ * replaces: the positional_encoder nn.Sequential (modules/ObjCAViT.py:257-282) and the regressor
+ *   (modules/miniViT.py:16-20,33; modules/ObjCAViT.py:299-303,378). */
+int ocv_mlp_f32(const float* x, long long x_ld, int R, int n_layers, const float* const* weights_host,
+                const float* const* biases_host, const int* dims_host, const float* residual, float* out32,
+                void* out16, void* stream);
+int ocv_cast_f32_to_bf16(const float* src, void* dst_bf16, long long n, void* stream);
+
+/* Extended epilogue of the same kernel (the bf16 token path):
+ *   y = act(A @ Wt^T + bias) + residual (fp32, row pitch ldr);  if ln_gamma: y = LayerNorm_128(y)*gamma+beta (eps 1e-5,
+ *   requires N == 128, act none), rows flagged in zero_rows (uint8 [M]) are written as 0.
+ *   y is written as fp32 to C32 (row pitch ldc32) and/or as bf16 to C16 (ldc16); either may be NULL, not both.
+ * replaces: out_proj + dropout-free residual + norm1, linear2 + residual + norm2 of nn.TransformerEncoderLayer. */
+int ocv_gemm_bf16_ex(const void* A, const void* Wt, const float* bias, const float* residual, int ldr,
+                     const float* ln_gamma, const float* ln_beta, const uint8_t* zero_rows, float* C32, int ldc32,
+                     void* C16, int ldc16, int M, int N, int K, int lda, int ldb, int act, void* stream);
+
 /* Fused pixel kernel (one persistent tcgen05 kernel, objcavit_b200/csrc/pixel_fused_bf16.cu):
  *   conv3x3 (implicit GEMM over an NHWC bf16 halo tile, 9 shifted smem descriptors) -> per-image logits GEMM with
  *   Mb[b] = s * Wout @ Q[b] (bins x channels, bf16) -> per-pixel softmax over K=256 bins -> sum p*centre.

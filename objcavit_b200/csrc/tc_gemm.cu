@@ -52,6 +52,12 @@ struct GemmParams {
   const float* residual;
   void* C;
   int M, N, K, ldc, act, c_is_bf16, k_per_split;
+  // extended epilogue (ocv_gemm_bf16_ex): LayerNorm over the N == 128 row, second (bf16) output, zeroed rows
+  const float* gamma;
+  const float* beta;
+  const uint8_t* zero_rows;
+  __nv_bfloat16* C16;
+  int ldc16, ldr;
 };
 
 __global__ void __launch_bounds__(256, 1)
@@ -128,6 +134,63 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       tc_fence_after();
     }
     const bool split = p.k_per_split > 0;
+    if (p.gamma) {
+      // LayerNorm epilogue: this thread owns the whole N == 128 row (post-norm encoder layer: LN(residual + A W^T + b))
+      float v[GN];
+#pragma unroll
+      for (int c = 0; c < GN / 32; ++c) {
+        uint32_t r[32];
+        tmem_ld32(tmem_d + ((uint32_t)(quarter * 32) << 16) + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[c * 32 + j] = __uint_as_float(r[j]);
+      }
+      if (m < p.M) {
+        const float4* b4 = reinterpret_cast<const float4*>(p.bias);
+        const float4* r4 = p.residual ? reinterpret_cast<const float4*>(p.residual + (long long)m * p.ldr) : nullptr;
+        float sum = 0.f;
+#pragma unroll
+        for (int j = 0; j < GN / 4; ++j) {
+          float4 b = p.bias ? __ldg(b4 + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+          if (r4) {
+            const float4 rr = __ldg(r4 + j);
+            b.x += rr.x; b.y += rr.y; b.z += rr.z; b.w += rr.w;
+          }
+          v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+          sum += (v[4 * j] + v[4 * j + 1]) + (v[4 * j + 2] + v[4 * j + 3]);
+        }
+        const float mean = sum * (1.f / GN);
+        float var = 0.f;
+#pragma unroll
+        for (int j = 0; j < GN; ++j) {
+          const float d = v[j] - mean;
+          var = fmaf(d, d, var);
+        }
+        const float rstd = rsqrtf(var * (1.f / GN) + 1e-5f);
+        const bool zero = p.zero_rows && p.zero_rows[m];
+        const float4* g4 = reinterpret_cast<const float4*>(p.gamma);
+        const float4* e4 = reinterpret_cast<const float4*>(p.beta);
+        float* c32 = p.C ? static_cast<float*>(p.C) + (long long)m * p.ldc : nullptr;
+        __nv_bfloat16* c16 = p.C16 ? p.C16 + (long long)m * p.ldc16 : nullptr;
+#pragma unroll
+        for (int j = 0; j < GN / 4; ++j) {
+          const float4 g = __ldg(g4 + j), e = __ldg(e4 + j);
+          float4 o;
+          o.x = zero ? 0.f : (v[4 * j] - mean) * rstd * g.x + e.x;
+          o.y = zero ? 0.f : (v[4 * j + 1] - mean) * rstd * g.y + e.y;
+          o.z = zero ? 0.f : (v[4 * j + 2] - mean) * rstd * g.z + e.z;
+          o.w = zero ? 0.f : (v[4 * j + 3] - mean) * rstd * g.w + e.w;
+          if (c32) *reinterpret_cast<float4*>(c32 + 4 * j) = o;
+          if (c16) {
+            __nv_bfloat162 h0 = __floats2bfloat162_rn(o.x, o.y), h1 = __floats2bfloat162_rn(o.z, o.w);
+            uint2 u;
+            u.x = *reinterpret_cast<uint32_t*>(&h0);
+            u.y = *reinterpret_cast<uint32_t*>(&h1);
+            *reinterpret_cast<uint2*>(c16 + 4 * j) = u;
+          }
+        }
+      }
+    } else
 #pragma unroll 1
     for (int c = 0; c < GN / 32; ++c) {
       uint32_t r[32];
@@ -152,7 +215,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (p.bias) v[j] += p.bias[n];
             if (p.act == OCV_ACT_RELU) v[j] = fmaxf(v[j], 0.f);
             else if (p.act == OCV_ACT_LEAKY_RELU) v[j] = v[j] > 0.f ? v[j] : 0.01f * v[j];
-            if (p.residual) v[j] += p.residual[(long long)m * p.ldc + n];
+            if (p.residual) v[j] += p.residual[(long long)m * p.ldr + n];
           }
         }
       }
@@ -167,6 +230,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         } else {
           for (int j = 0; j < 32; ++j)
             if (nb + j < p.N) crow[j] = v[j];
+        }
+        if (!split && p.C16) {  // second output: bf16 copy for the next GEMM's A operand
+          __nv_bfloat16* hrow = p.C16 + (long long)m * p.ldc16 + nb;
+          for (int j = 0; j < 32; ++j)
+            if (nb + j < p.N) hrow[j] = __float2bfloat16(v[j]);
         }
       } else {
         __nv_bfloat16* crow = static_cast<__nv_bfloat16*>(p.C) + (long long)m * p.ldc + nb;
@@ -218,6 +286,37 @@ extern "C" long long ocv_gemm_bf16_workspace(int M, int N, int K, int split_k) {
   return (long long)split_k * M * N * (long long)sizeof(float);
 }
 
+static int gemm_launch(const void* A, const void* Wt, int M, int N, int K, int lda, int ldb, GemmParams p, int split_k,
+                       void* workspace, void* C_final, int ldc_final, int c_final_bf16, void* stream);
+
+extern "C" int ocv_gemm_bf16_ex(const void* A, const void* Wt, const float* bias, const float* residual, int ldr,
+                                const float* ln_gamma, const float* ln_beta, const uint8_t* zero_rows, float* C32,
+                                int ldc32, void* C16, int ldc16, int M, int N, int K, int lda, int ldb, int act,
+                                void* stream) {
+  OCV_CHECK_ARG(A && Wt && (C32 || C16) && M > 0 && N > 0 && K > 0);
+  OCV_CHECK_ARG((ln_gamma == nullptr) == (ln_beta == nullptr));
+  OCV_CHECK_SHAPE(K % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0);
+  if (ln_gamma) {
+    OCV_CHECK_SHAPE(N == GN && act == OCV_ACT_NONE);
+    OCV_CHECK_ALIGN((!C32 || ldc32 % 4 == 0) && (!C16 || ldc16 % 4 == 0) && (!residual || ldr % 4 == 0));
+    OCV_CHECK_ALIGN(((reinterpret_cast<uintptr_t>(bias) | reinterpret_cast<uintptr_t>(residual) |
+                      reinterpret_cast<uintptr_t>(ln_gamma) | reinterpret_cast<uintptr_t>(ln_beta) |
+                      reinterpret_cast<uintptr_t>(C32)) & 15) == 0 && (reinterpret_cast<uintptr_t>(C16) & 7) == 0);
+  }
+  GemmParams p{};
+  p.bias = bias; p.residual = residual; p.ldr = ldr; p.gamma = ln_gamma; p.beta = ln_beta; p.zero_rows = zero_rows;
+  p.M = M; p.N = N; p.K = K; p.act = act;
+  if (C32) {
+    p.C = C32; p.ldc = ldc32; p.c_is_bf16 = 0;
+    p.C16 = static_cast<__nv_bfloat16*>(C16); p.ldc16 = ldc16;
+  } else if (ln_gamma) {
+    p.C = nullptr; p.C16 = static_cast<__nv_bfloat16*>(C16); p.ldc16 = ldc16;
+  } else {
+    p.C = C16; p.ldc = ldc16; p.c_is_bf16 = 1;
+  }
+  return gemm_launch(A, Wt, M, N, K, lda, ldb, p, 1, nullptr, nullptr, 0, 0, stream);
+}
+
 extern "C" int ocv_gemm_bf16(const void* A, const void* Wt, const float* bias, const float* residual, void* C, int M,
                              int N, int K, int lda, int ldb, int ldc, int act, int c_is_bf16, int split_k,
                              void* workspace, void* stream) {
@@ -225,6 +324,17 @@ extern "C" int ocv_gemm_bf16(const void* A, const void* Wt, const float* bias, c
   OCV_CHECK_SHAPE(K % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0);
   if (split_k < 1) split_k = 1;
   OCV_CHECK_ARG(split_k == 1 || workspace);
+  GemmParams p{};
+  p.bias = bias;
+  p.residual = residual;
+  p.ldr = ldc;
+  p.M = M; p.N = N; p.K = K; p.act = act;
+  p.C = C; p.ldc = ldc; p.c_is_bf16 = c_is_bf16;
+  return gemm_launch(A, Wt, M, N, K, lda, ldb, p, split_k, workspace, C, ldc, c_is_bf16, stream);
+}
+
+static int gemm_launch(const void* A, const void* Wt, int M, int N, int K, int lda, int ldb, GemmParams p, int split_k,
+                       void* workspace, void* C_final, int ldc_final, int c_final_bf16, void* stream) {
   if (int s = ocv_require_sm100()) return s;
   CUtensorMap tmA, tmB;
   if (int s = tc::make_tmap_2d_bf16(&tmA, A, M, K, lda, GM, GK, CU_TENSOR_MAP_SWIZZLE_128B)) return s;
@@ -235,10 +345,6 @@ extern "C" int ocv_gemm_bf16(const void* A, const void* Wt, const float* bias, c
     if (e != cudaSuccess) return (int)e;
     attr_set = true;
   }
-  GemmParams p{};
-  p.bias = bias;
-  p.residual = residual;
-  p.M = M; p.N = N; p.K = K; p.act = act;
   dim3 grid(ceil_div(N, GN), ceil_div(M, GM), split_k);
   if (split_k > 1) {
     p.C = workspace;
@@ -246,9 +352,6 @@ extern "C" int ocv_gemm_bf16(const void* A, const void* Wt, const float* bias, c
     p.c_is_bf16 = 0;
     p.k_per_split = ceil_div(ceil_div(K, split_k), GK) * GK;
   } else {
-    p.C = C;
-    p.ldc = ldc;
-    p.c_is_bf16 = c_is_bf16;
     p.k_per_split = 0;
   }
   gemm_bf16_kernel<<<grid, 256, GEMM_SMEM, ocv_stream(stream)>>>(tmA, tmB, p);
@@ -256,7 +359,8 @@ extern "C" int ocv_gemm_bf16(const void* A, const void* Wt, const float* bias, c
   if (split_k > 1) {
     const long long n = (long long)M * N;
     gemm_splitk_reduce_kernel<<<(unsigned)ceil_div<long long>(n, 256), 256, 0, ocv_stream(stream)>>>(
-        static_cast<const float*>(workspace), bias, residual, C, M, N, ldc, split_k, act, c_is_bf16);
+        static_cast<const float*>(workspace), p.bias, p.residual, C_final, M, N, ldc_final, split_k, p.act,
+        c_final_bf16);
     return ocv_launch_status();
   }
   return OCV_OK;

@@ -302,3 +302,96 @@ def pixel_fused_bf16(x_nhwc: torch.Tensor, w3p: torch.Tensor, Mb: torch.Tensor, 
     _call("ocv_pixel_fused_bf16", x_nhwc.data_ptr(), w3p.data_ptr(), Mb.data_ptr(), blog.data_ptr(),
           centres.data_ptr(), depth.data_ptr(), B, h, w, int(max_ctas), _stream())
     return depth
+
+
+# ---- bf16 token path --------------------------------------------------------------------------------
+
+def cast_bf16(x: torch.Tensor) -> torch.Tensor:
+    _chk(x, torch.float32, "x")
+    assert x.is_contiguous()
+    out = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16)
+    _call("ocv_cast_f32_to_bf16", x.data_ptr(), out.data_ptr(), x.numel(), _stream())
+    return out
+
+
+def gemm_bf16_ex(a: torch.Tensor, w: torch.Tensor, bias=None, act: int = ACT_NONE, residual=None, ln=None,
+                 zero_rows=None, want32: bool = False, want16: bool = True):
+    """(out32 | None, out16 | None) = [LayerNorm](act(a @ w^T + bias) + residual); a, w bf16, residual fp32."""
+    _chk(a, torch.bfloat16, "a"); _chk(w, torch.bfloat16, "w")
+    M, K, lda = _row_major_2d(a, "a")
+    N, K2, ldb = _row_major_2d(w, "w")
+    assert K == K2
+    o32 = torch.empty(M, N, device=a.device, dtype=torch.float32) if want32 else None
+    o16 = torch.empty(M, N, device=a.device, dtype=torch.bfloat16) if want16 else None
+    ldr = 0
+    if residual is not None:
+        _chk(residual, torch.float32, "residual")
+        _, _, ldr = _row_major_2d(residual, "residual")
+    g, be = (ln if ln is not None else (None, None))
+    _call("ocv_gemm_bf16_ex", a.data_ptr(), w.data_ptr(), _ptr(bias), _ptr(residual), ldr, _ptr(g), _ptr(be),
+          _ptr(zero_rows), _ptr(o32), N, _ptr(o16), N, M, N, K, lda, ldb, act, _stream())
+    return o32, o16
+
+
+def mha_core_bf16(q, k, v, key_padding_mask=None, heads: int = 4):
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _chk(t, torch.bfloat16, n)
+        assert t.dim() == 3 and t.stride(2) == 1
+    B, Sq, E = q.shape
+    Sk = k.shape[1]
+    out = torch.empty(B, Sq, E, device=q.device, dtype=torch.bfloat16)
+    if key_padding_mask is not None:
+        _chk(key_padding_mask, torch.uint8, "key_padding_mask")
+        assert key_padding_mask.is_contiguous() and key_padding_mask.shape == (B, Sk)
+    _call("ocv_mha_core_bf16", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), _ptr(key_padding_mask),
+          B, Sq, Sk, heads, E // heads, q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0),
+          v.stride(1), out.stride(0), out.stride(1), _stream())
+    return out
+
+
+def pack_patch_weights_bf16(w: torch.Tensor) -> torch.Tensor:
+    _chk(w, torch.float32, "w")
+    assert w.is_contiguous() and w.dim() == 4 and w.shape[2] == w.shape[3]
+    E, Cc, P, _ = w.shape
+    out = torch.empty(E, P * P * Cc, device=w.device, dtype=torch.bfloat16)
+    _call("ocv_pack_patch_weights_bf16", w.data_ptr(), out.data_ptr(), E, Cc, P, _stream())
+    return out
+
+
+def patch_embed_bf16(x_nhwc: torch.Tensor, wp: torch.Tensor, bias, pos, P: int = 16, want32=True, want16=True):
+    """tokens from NHWC bf16 features -> (tok32 [B,S,E] | None, tok16 | None)."""
+    _chk(x_nhwc, torch.bfloat16, "x_nhwc"); _chk(wp, torch.bfloat16, "wp")
+    assert x_nhwc.is_contiguous() and wp.is_contiguous()
+    B, h, w, Cc = x_nhwc.shape
+    E = wp.shape[0]
+    S = (h // P) * (w // P)
+    if pos is not None:
+        assert pos.is_contiguous() and pos.shape[0] >= S and pos.shape[1] == E
+    ws = torch.empty(max(_lib.lib().ocv_patch_embed_bf16_workspace(B, h, w, P), 4) // 4, device=x_nhwc.device,
+                     dtype=torch.float32)
+    t32 = torch.empty(B, S, E, device=x_nhwc.device, dtype=torch.float32) if want32 else None
+    t16 = torch.empty(B, S, E, device=x_nhwc.device, dtype=torch.bfloat16) if want16 else None
+    _call("ocv_patch_embed_bf16", x_nhwc.data_ptr(), wp.data_ptr(), _ptr(bias), _ptr(pos), _ptr(t32), _ptr(t16),
+          B, Cc, h, w, P, E, ws.data_ptr(), _stream(), launches=2)
+    return t32, t16
+
+
+def mlp(x: torch.Tensor, weights, biases, residual=None, want32=True, want16=False):
+    """Fused Linear/LeakyReLU chain (one launch).  x [R,in] fp32 with unit inner stride."""
+    import ctypes as C
+    _chk(x, torch.float32, "x")
+    R, K0, ld = _row_major_2d(x, "x")
+    n = len(weights)
+    dims = [K0] + [int(w.shape[0]) for w in weights]
+    for i, w in enumerate(weights):
+        _chk(w, torch.float32, "w")
+        assert w.is_contiguous() and w.shape[1] == dims[i]
+    Wp = (C.c_void_p * n)(*[w.data_ptr() for w in weights])
+    Bp = (C.c_void_p * n)(*[(b.data_ptr() if b is not None else None) for b in biases])
+    Dp = (C.c_int * (n + 1))(*dims)
+    o32 = torch.empty(R, dims[-1], device=x.device, dtype=torch.float32) if want32 else None
+    o16 = torch.empty(R, dims[-1], device=x.device, dtype=torch.bfloat16) if want16 else None
+    if residual is not None:
+        assert residual.is_contiguous() and tuple(residual.shape) == (R, dims[-1])
+    _call("ocv_mlp_f32", x.data_ptr(), ld, R, n, Wp, Bp, Dp, _ptr(residual), _ptr(o32), _ptr(o16), _stream())
+    return o32, o16

@@ -231,7 +231,7 @@ def test_pixel_fused_bf16(cuda, B, h, w, max_ctas):
     x = torch.randn(B, 128, h, w, generator=g(1))
     w3 = torch.randn(128, 128, 3, 3, generator=g(2)) * 0.03; b3 = torch.randn(128, generator=g(3)) * 0.1
     wout = torch.randn(256, 128, 1, 1, generator=g(4)) * 0.1; bout = torch.randn(256, generator=g(5)) * 0.1
-    tok = torch.randn(B, 140, 128, generator=g(6))
+    tok = torch.randn(B, 140, 128, generator=g(6)) * 0.2     # logits of std ~2.5: already sharper than the head's
     wn = torch.rand(B, 256, generator=g(7)) + 0.1
     wn = wn / wn.sum(1, keepdim=True)
     _, centres = oh.bin_edges_and_centres(wn, 0.001, 10.0)
@@ -249,3 +249,78 @@ def test_pixel_fused_bf16(cuda, B, h, w, max_ctas):
     err = (got.cpu() - want16).abs()
     assert float(err.mean() / want16.abs().mean()) < 1e-4 and rel_err(got, want16) < 1e-2
     assert rel_err(got, want32) < 2e-2          # north_star bf16 tolerance vs the fp32 chain
+
+
+def test_gemm_bf16_layernorm_epilogue(cuda):
+    """out_proj/linear2 + residual + LayerNorm fused in the tcgen05 GEMM epilogue; fp32 and bf16 outputs; zero rows."""
+    from objcavit_b200 import ops
+    for (M, K) in ((300, 128), (1111, 1024)):
+        a = (torch.randn(M, K, generator=g(M)) * 0.5).bfloat16(); w = (torch.randn(128, K, generator=g(K)) * 0.1).bfloat16()
+        b = torch.randn(128, generator=g(3)); r = torch.randn(M, 128, generator=g(4))
+        gm = torch.randn(128, generator=g(5)); bt = torch.randn(128, generator=g(6))
+        z = (torch.arange(M) % 7 == 0).to(torch.uint8)
+        want = F.layer_norm(a.float() @ w.float().T + b + r, (128,), gm, bt, 1e-5).masked_fill(z.bool()[:, None], 0.0)
+        o32, o16 = ops.gemm_bf16_ex(a.to(cuda), w.to(cuda), b.to(cuda), residual=r.to(cuda), ln=(gm.to(cuda), bt.to(cuda)),
+                                    zero_rows=z.to(cuda), want32=True, want16=True)
+        assert rel_err(o32, want) < 2e-5 * max(1.0, math.sqrt(K / 128))
+        assert torch.equal(o16.cpu(), o32.cpu().bfloat16())
+    # plain epilogue with both outputs + relu
+    a = (torch.randn(500, 128, generator=g(7)) * 0.5).bfloat16(); w = (torch.randn(1024, 128, generator=g(8)) * 0.1).bfloat16()
+    b = torch.randn(1024, generator=g(9))
+    o32, o16 = ops.gemm_bf16_ex(a.to(cuda), w.to(cuda), b.to(cuda), act=ops.ACT_RELU, want32=True, want16=True)
+    want = torch.relu(a.float() @ w.float().T + b)
+    assert rel_err(o32, want) < 2e-5 and torch.equal(o16.cpu(), o32.cpu().bfloat16())
+    _, o16b = ops.gemm_bf16_ex(a.to(cuda), w.to(cuda), b.to(cuda), act=ops.ACT_RELU)
+    assert torch.equal(o16b.cpu(), o16.cpu())
+
+
+@pytest.mark.parametrize("Sq,Sk", [(300, 300), (45, 77), (9, 9), (418, 418), (300, 32)])
+def test_mha_core_bf16(cuda, Sq, Sk):
+    from objcavit_b200 import ops
+    B = 3
+    qkv = torch.randn(B, max(Sq, Sk), 384, generator=g(Sq)).bfloat16()
+    qf = qkv.float()
+    q, k, v = qf[:, :Sq, 0:128], qf[:, :Sk, 128:256], qf[:, :Sk, 256:]
+    mask = torch.zeros(B, Sk, dtype=torch.bool)
+    mask[0, Sk // 2:] = True
+    mask[2, 1:] = True
+    sc = (q.reshape(B, Sq, 4, 32).transpose(1, 2) / math.sqrt(32)) @ k.reshape(B, Sk, 4, 32).transpose(1, 2).transpose(-1, -2)
+    sc = sc.masked_fill(mask[:, None, None, :], float("-inf"))
+    want = (torch.softmax(sc, -1) @ v.reshape(B, Sk, 4, 32).transpose(1, 2)).transpose(1, 2).reshape(B, Sq, 128)
+    d = qkv.to(cuda)
+    got = ops.mha_core_bf16(d[:, :Sq, 0:128], d[:, :Sk, 128:256], d[:, :Sk, 256:], mask.to(torch.uint8).to(cuda))
+    assert rel_err(got.float(), want) < 1.5e-2          # P and the output are rounded to bf16
+    assert float((got.float().cpu() - want).abs().mean() / want.abs().mean()) < 4e-3
+
+
+@pytest.mark.parametrize("B,h,w", [(2, 48, 64), (3, 240, 320), (2, 176, 608), (1, 37, 50)])
+def test_patch_embed_bf16(cuda, B, h, w):
+    from objcavit_b200 import ops
+    x = torch.randn(B, 128, h, w, generator=g(1)).bfloat16()
+    wt = (torch.randn(128, 128, 16, 16, generator=g(2)) * 0.01)
+    b = torch.randn(128, generator=g(3)); pos = torch.rand(500, 128, generator=g(4))
+    S = (h // 16) * (w // 16)
+    want = F.conv2d(x.float(), wt.bfloat16().float(), b, stride=16).flatten(2).permute(0, 2, 1) + pos[:S]
+    wp = ops.pack_patch_weights_bf16(wt.to(cuda))
+    assert torch.equal(wp.cpu(), wt.permute(0, 2, 3, 1).reshape(128, -1).bfloat16())
+    xn = x.permute(0, 2, 3, 1).contiguous().to(cuda)
+    t32, t16 = ops.patch_embed_bf16(xn, wp, b.to(cuda), pos.to(cuda))
+    assert rel_err(t32, want) < 1e-4 and torch.equal(t16.cpu(), t32.cpu().bfloat16())
+
+
+def test_mlp_chain(cuda):
+    from objcavit_b200 import ops
+    dims = [4, 32, 64, 128, 256, 128]
+    Ws = [torch.randn(dims[i + 1], dims[i], generator=g(i)) / math.sqrt(dims[i]) for i in range(5)]
+    bs = [torch.randn(dims[i + 1], generator=g(10 + i)) * 0.1 for i in range(5)]
+    x = torch.randn(77, 6, generator=g(20)) * 50
+    res = torch.randn(77, 128, generator=g(21))
+    want = x[:, :4]
+    for i in range(5):
+        want = want @ Ws[i].T + bs[i]
+        if i < 4:
+            want = F.leaky_relu(want, 0.01)
+    want = want + res
+    o32, o16 = ops.mlp(x.to(cuda)[:, :4], [w.to(cuda) for w in Ws], [b.to(cuda) for b in bs], residual=res.to(cuda),
+                       want32=True, want16=True)
+    assert rel_err(o32, want) < 1e-5 and torch.equal(o16.cpu(), o32.cpu().bfloat16())
