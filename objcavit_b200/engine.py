@@ -120,8 +120,15 @@ class ObjectBatch:
         for c in counts:
             offs.append(offs[-1] + c)
         self.offsets_host = offs
-        self.offsets = torch.tensor(offs, dtype=torch.int32).pin_memory().to(rows.device, non_blocking=True) \
-            if rows.is_cuda else torch.tensor(offs, dtype=torch.int32)
+        self.offsets = self._to_device(offs)
+
+    def _to_device(self, values):
+        t = torch.tensor(values, dtype=torch.int32)
+        return t.pin_memory().to(self.rows.device, non_blocking=True) if self.rows.is_cuda else t
+
+    def uniform_offsets(self, n_max: int) -> torch.Tensor:
+        """CSR offsets of the dense [B, n_max] padded layout (every image n_max rows)."""
+        return self._to_device(list(range(0, (self.B + 1) * n_max, n_max)))
 
 
 def marshal_objects(object_features: List[torch.Tensor], object_xywh_list: List[Optional[torch.Tensor]], device):
@@ -187,7 +194,7 @@ def saca_forward(P: Params, pre: str, img_tok: torch.Tensor, objs: ObjTokens, no
         if n_max > S:
             raise ValueError("more objects than image tokens: the reference's F.pad would crop; unsupported")
         # :192-194 objects LEFT-padded, mask RIGHT-padded to S (F5)
-        uni = torch.arange(0, (B + 1) * n_max, n_max, dtype=torch.int32).pin_memory().to(img_tok.device, non_blocking=True)
+        uni = objs.uniform_offsets(n_max)
         att_obj_s, kpm = ops.pad_objects(att_obj.view(B * n_max, E), uni, B, S, n_max, 0.0001, True,
                                          mask_offsets=objs.offsets)
     else:
