@@ -33,6 +33,8 @@ H, W, NOBJ = 240, 320, 32
 GF_HEAD = 34.0
 GF_PIXEL = 22.649 + 2.517 + 5.033      # conv3x3 + dot-product + conv_out: the fused pixel kernel
 GF_CONV3 = 22.649
+# dram__bytes_read+write of one pixel_fused launch at batch 16 (ncu --set full, profiles/): MB
+TRAFFIC_PIXEL_MB = 360.1
 
 
 def peaks():
@@ -232,20 +234,33 @@ def main():
     value = world * B * K / (ms * 1e-3)
 
     # ---- dominant kernel, timed live with CUDA events on the launching stream ------------------------
-    dom = "ocv_pixel_fused_bf16" if precision == "bf16" else "ocv_conv3x3_f32"
-    ops.timed_kernel = dom
-    ops.timed_events = []
-    for _ in range(min(K, 10)):
-        step(x_dev, objs_dev, boxes_dev)
-    torch.cuda.synchronize()
-    durs = [s.elapsed_time(e) for s, e in ops.timed_events]
-    ops.timed_kernel = None
+    durs = []
+    if precision == "bf16":
+        from objcavit_b200 import _lib
+        dom = "pixel_fused_kernel (inside ocv_head_forward)"
+        nh = head.__dict__["_ocv_native"]
+        _lib.check(_lib.lib().ocv_head_enable_timing(nh._h, 1), "ocv_head_enable_timing")
+        for _ in range(min(K, 10)):
+            step(x_dev, objs_dev, boxes_dev)
+            durs.append(float(_lib.lib().ocv_head_pixel_ms(nh._h)))
+        _lib.lib().ocv_head_enable_timing(nh._h, 0)
+    else:
+        dom = "ocv_conv3x3_f32"
+        ops.timed_kernel = dom
+        ops.timed_events = []
+        for _ in range(min(K, 10)):
+            step(x_dev, objs_dev, boxes_dev)
+        torch.cuda.synchronize()
+        durs = [s.elapsed_time(e) for s, e in ops.timed_events]
+        ops.timed_kernel = None
     dom_ms = sum(durs) / max(len(durs), 1)
     pk = peaks()
     gf = (GF_PIXEL if precision == "bf16" else GF_CONV3) * B
     achieved = gf / dom_ms if dom_ms > 0 else 0.0     # GFLOP/ms == TFLOP/s
     roofline = {"bound": "tensor", "kernel": dom, "achieved": achieved, "peak": pk["tf_sust"], "unit": "TFLOP/s",
-                "frac": achieved / pk["tf_sust"], "traffic": None, "peak_source": pk["src"] + " (bf16 sustained)",
+                "frac": achieved / pk["tf_sust"], "traffic": TRAFFIC_PIXEL_MB * 1e6 * B / 16 if precision == "bf16" else None,
+                "peak_source": pk["src"] + " (bf16 sustained: kernel timed inside the step)",
+                "frac_of_burst_peak": achieved / pk["tf_burst"],
                 "kernel_ms": dom_ms, "kernel_share_of_step": dom_ms / (ms / K),
                 "head_frac_of_roofline": (GF_HEAD * B * K / ms) / pk["tf_sust"]}
 

@@ -207,6 +207,56 @@ int ocv_fold_queries_bf16(const float* Wout /*[K,Q]*/, const float* bout /*[K]*/
 int ocv_pixel_fused_bf16(const void* X, const void* W3p, const void* Mb, const float* blog, const float* centres,
                          float* depth, int B, int h, int w, int max_ctas, void* stream);
 
+/* ---- whole head, one call (native host-side sequencing) -------------------------------------------------
+ * An ocv_head is a HOST-side plan: the head's configuration, the device pointers of its parameters keyed by the
+ * reference's own state_dict names, and two non-blocking side streams used to run the object branch next to the image
+ * branch.  It owns no device memory: packed weights and the workspace are caller buffers.  One ocv_head serves
+ * one caller thread at a time (it caches the batch-invariant image positional rows for the last (h, w)).
+ *
+ * replaces, as ONE call: ObjCAViT.forward (modules/ObjCAViT.py:306-390) or mViT.forward (modules/miniViT.py:22-44)
+ *   followed by the head tail of GraphBins.forward / AdaBins.forward (modules/GraphBins.py:107-119; modules/AdaBins.py:76-87),
+ *   on the bf16 tensor-core path.  Quirks F5/F6/F7/F13 of SURVEY.md are reproduced.
+ *
+ * kind: 0 = AdaBins mViT head (keys "adaptive_bins_layer.*", "conv_out.0.*"), 1 = ObjCAViT head ("objcavit.*", "conv_out.0.*").
+ * strategy (kind 1): 0 learned, 1 learned_bbox_wh, 2 grid_random, 3 grid_random_roi_align. */
+typedef struct ocv_head ocv_head;
+typedef struct ocv_head_config {
+  int kind, strategy, no_obj_sa, use_2_saca;
+  int n_bins;      /* 256 */
+  int obj_dim;     /* 512 */
+  float min_depth, max_depth;
+  int reserved[8]; /* zero */
+} ocv_head_config;
+
+int ocv_head_create(const ocv_head_config* cfg, ocv_head** out);
+void ocv_head_destroy(ocv_head* head);
+/* Register one fp32 parameter (device pointer, borrowed) under its state_dict key relative to the head module, e.g.
+ * "objcavit.saca_1.image_transformer_encoder.layers.0.linear1.weight".  Unknown keys are accepted (the never-executed
+ * prototype layers of SURVEY.md F9 are simply not used). */
+int ocv_head_set_param(ocv_head* head, const char* key, const float* device_ptr, long long numel);
+/* Derived operand copies (bf16 GEMM weights, packed conv weights): size, then fill `packed` (device, 256-byte aligned).
+ * Must be called again whenever a parameter changes.  Returns OCV_E_ARG naming nothing if a needed key is missing;
+ * ocv_head_missing_key() then returns that key. */
+long long ocv_head_packed_bytes(const ocv_head* head);
+int ocv_head_pack(ocv_head* head, void* packed, void* stream);
+const char* ocv_head_missing_key(const ocv_head* head);
+/* Workspace for one forward: total_obj = sum_i N_i, n_max = max_i N_i (0, 0 for kind 0). */
+long long ocv_head_workspace_bytes(const ocv_head* head, int B, int h, int w, int total_obj, int n_max);
+/* X: [B,h,w,128] bf16 NHWC.  obj_feat [total_obj, obj_dim] fp32, obj_xywh [total_obj,4] fp32 (images without detections
+ * carry the (-1,-1,-1,-1) placeholder row, modules/ObjCAViT.py:312-313), obj_offsets int32 [B+1] CSR (DEVICE).
+ * Outputs: depth [B,h*w] fp32, bin_edges [B,n_bins+1] fp32, obj_tokens_out [total_obj,128] fp32 or NULL (the embedded
+ * object tokens the reference writes back into the caller's list, F11).  Launches only; no sync, no allocation. */
+int ocv_head_forward(ocv_head* head, const void* X_nhwc_bf16, const float* obj_feat, const float* obj_xywh,
+                     const int32_t* obj_offsets, int total_obj, int n_max, int B, int h, int w, float* depth,
+                     float* bin_edges, float* obj_tokens_out, void* workspace, void* stream);
+/* number of kernel launches the last ocv_head_forward issued */
+int ocv_head_last_launches(const ocv_head* head);
+/* Measurement aid (bench.py): when enabled, ocv_head_forward brackets the fused pixel kernel with CUDA events on the
+ * caller's stream; ocv_head_pixel_ms() waits for the last pair and returns its duration in ms (the one entry point that
+ * blocks the calling thread), or -1 if none was recorded. */
+int ocv_head_enable_timing(ocv_head* head, int on);
+float ocv_head_pixel_ms(ocv_head* head);
+
 #ifdef __cplusplus
 }
 #endif

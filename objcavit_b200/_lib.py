@@ -49,7 +49,24 @@ PROTOTYPES = {
     "ocv_pack_conv3x3_bf16": (i32, [p, p, p]),
     "ocv_fold_queries_bf16": (i32, [p, p, p, i64, i32, p, f32, p, p, i32, i32, i32, i32, p]),
     "ocv_pixel_fused_bf16": (i32, [p, p, p, p, p, p, i32, i32, i32, i32, p]),
+    "ocv_head_create": (i32, [p, p]),
+    "ocv_head_destroy": (None, [p]),
+    "ocv_head_set_param": (i32, [p, C.c_char_p, p, i64]),
+    "ocv_head_packed_bytes": (i64, [p]),
+    "ocv_head_pack": (i32, [p, p, p]),
+    "ocv_head_missing_key": (C.c_char_p, [p]),
+    "ocv_head_workspace_bytes": (i64, [p, i32, i32, i32, i32, i32]),
+    "ocv_head_forward": (i32, [p, p, p, p, p, i32, i32, i32, i32, i32, p, p, p, p, p]),
+    "ocv_head_last_launches": (i32, [p]),
+    "ocv_head_enable_timing": (i32, [p, i32]),
+    "ocv_head_pixel_ms": (f32, [p]),
 }
+
+
+class HeadConfig(C.Structure):
+    """``ocv_head_config`` of include/objcavit_b200.h."""
+    _fields_ = [("kind", i32), ("strategy", i32), ("no_obj_sa", i32), ("use_2_saca", i32), ("n_bins", i32),
+                ("obj_dim", i32), ("min_depth", f32), ("max_depth", f32), ("reserved", i32 * 8)]
 
 
 def declared_symbols():

@@ -18,6 +18,10 @@ static inline int ocv_launch_status() {
 // OCV_OK iff the current device is sm_100 (cached per process).
 int ocv_require_sm100();
 
+// pad_objects with an optional second (bf16) copy of the padded rows (token_ops.cu); used by the head executor
+int ocv_pad_objects_impl(const float* src, const int32_t* offsets, const int32_t* mask_offsets, float* dst, void* dst16,
+                         uint8_t* mask, int B, int L, int Nmax, int E, float pad_value, int left_pad, void* stream);
+
 static inline cudaStream_t ocv_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
 __device__ __forceinline__ float warp_sum(float v) {

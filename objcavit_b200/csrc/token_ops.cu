@@ -102,7 +102,8 @@ mha_core_kernel(const float* __restrict__ q, const float* __restrict__ k, const 
 // ------------------------------------------------------------------------------------------------
 __global__ void pad_objects_kernel(const float* __restrict__ src, const int32_t* __restrict__ offsets,
                                    const int32_t* __restrict__ mask_offsets, float* __restrict__ dst,
-                                   uint8_t* __restrict__ mask, int L, int Nmax, int E, float pad_value, int left_pad) {
+                                   uint8_t* __restrict__ mask, int L, int Nmax, int E, float pad_value, int left_pad,
+                                   __nv_bfloat16* __restrict__ dst16) {
   const int b = blockIdx.y;
   const int row = blockIdx.x;  // 0..L-1
   const int beg = offsets[b], n = offsets[b + 1] - beg;
@@ -111,7 +112,11 @@ __global__ void pad_objects_kernel(const float* __restrict__ src, const int32_t*
   const bool real = (j >= 0 && j < n);
   float* d = dst + ((long long)b * L + row) * E;
   const float* s = real ? src + (long long)(beg + j) * E : nullptr;
-  for (int e = threadIdx.x; e < E; e += blockDim.x) d[e] = real ? s[e] : pad_value;
+  for (int e = threadIdx.x; e < E; e += blockDim.x) {
+    const float v = real ? s[e] : pad_value;
+    d[e] = v;
+    if (dst16) dst16[((long long)b * L + row) * E + e] = __float2bfloat16(v);
+  }
   if (mask && threadIdx.x == 0) {
     const int m = mask_offsets ? mask_offsets[b + 1] - mask_offsets[b] : n;
     mask[(long long)b * L + row] = (row < m) ? 0 : 1;
@@ -332,15 +337,21 @@ extern "C" int ocv_mha_core_f32(const float* q, const float* k, const float* v, 
   return ocv_launch_status();
 }
 
-extern "C" int ocv_pad_objects_f32(const float* src, const int32_t* offsets, const int32_t* mask_offsets, float* dst,
-                                   uint8_t* mask, int B, int L, int Nmax, int E, float pad_value, int left_pad,
-                                   void* stream) {
+int ocv_pad_objects_impl(const float* src, const int32_t* offsets, const int32_t* mask_offsets, float* dst, void* dst16,
+                         uint8_t* mask, int B, int L, int Nmax, int E, float pad_value, int left_pad, void* stream) {
   OCV_CHECK_ARG(src && offsets && dst && B > 0 && L > 0 && E > 0);
   OCV_CHECK_SHAPE(Nmax > 0 && Nmax <= L && B <= 65535);
   if (int s = ocv_require_sm100()) return s;
   pad_objects_kernel<<<dim3(L, B), 128, 0, ocv_stream(stream)>>>(src, offsets, mask_offsets, dst, mask, L, Nmax, E,
-                                                                pad_value, left_pad);
+                                                                pad_value, left_pad,
+                                                                static_cast<__nv_bfloat16*>(dst16));
   return ocv_launch_status();
+}
+
+extern "C" int ocv_pad_objects_f32(const float* src, const int32_t* offsets, const int32_t* mask_offsets, float* dst,
+                                   uint8_t* mask, int B, int L, int Nmax, int E, float pad_value, int left_pad,
+                                   void* stream) {
+  return ocv_pad_objects_impl(src, offsets, mask_offsets, dst, nullptr, mask, B, L, Nmax, E, pad_value, left_pad, stream);
 }
 
 extern "C" int ocv_patch_coords_f32(float* coords, int gh, int gw, int P, void* stream) {

@@ -192,8 +192,35 @@ def objcavit_tokens(P, pk, pre, x_nhwc, object_features, object_xywh_list, strat
     return t32
 
 
-def head_forward(head, P, pre, x, object_features, object_xywh_list, lo, hi):
-    """-> (depth [B,1,h,w] fp32, bin_edges [B,K+1] fp32)."""
+def head_forward(head, P, pre, x, object_features, object_xywh_list, lo, hi, mutate_inputs=True):
+    """-> (depth [B,1,h,w] fp32, bin_edges [B,K+1] fp32): ONE native call (``ocv_head_forward``) sequences every kernel;
+    python only marshals the ragged object lists into CSR form."""
+    x_nhwc = features_nhwc_bf16(x)
+    nh = head.__dict__.get("_ocv_native")
+    if nh is None:
+        if object_features is None:
+            nh = ops.NativeHead(0, "learned", False, False, head.n_bins, 512, lo, hi)
+        else:
+            oc = head.objcavit
+            nh = ops.NativeHead(1, oc.strategy, oc.no_obj_sa, oc.use_2_saca, head.args.graphbins.n_bins,
+                                oc.obj_embedding_layer.in_features, lo, hi)
+        head.__dict__["_ocv_native"] = nh
+    nh.bind(P)
+    if object_features is None:
+        return nh.forward(x_nhwc, None, None, None, 0, 0)
+    feats, boxes, counts = engine.marshal_objects(object_features, object_xywh_list, x_nhwc.device)
+    batch = engine.ObjectBatch(feats, counts)
+    obj_tok = torch.empty(feats.shape[0], E, device=feats.device, dtype=torch.float32) if mutate_inputs else None
+    depth, edges = nh.forward(x_nhwc, feats, boxes, batch.offsets, feats.shape[0], batch.n_max, obj_tok)
+    if mutate_inputs:  # F11: the reference overwrites the caller's list with the embedded tokens
+        for i in range(batch.B):
+            object_features[i] = obj_tok[batch.offsets_host[i]:batch.offsets_host[i + 1]]
+    return depth, edges
+
+
+def head_forward_staged(head, P, pre, x, object_features, object_xywh_list, lo, hi):
+    """Same computation sequenced stage by stage from python (one C-ABI call per kernel): kept for the stage-level
+    parity tests and for debugging; the module forward uses :func:`head_forward`."""
     x_nhwc = features_nhwc_bf16(x)
     pk = packed_for(head, P)
     if object_features is None:

@@ -24,6 +24,7 @@ class KernelModule(nn.Module):
         for m in self.modules():
             m.__dict__.pop("_ocv_param_cache", None)
             m.__dict__.pop("_ocv_packed", None)
+            m.__dict__.pop("_ocv_native", None)
         return super()._apply(fn, *a, **kw)
 
     def _guard_inference(self, *tensors):

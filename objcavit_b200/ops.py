@@ -395,3 +395,90 @@ def mlp(x: torch.Tensor, weights, biases, residual=None, want32=True, want16=Fal
         assert residual.is_contiguous() and tuple(residual.shape) == (R, dims[-1])
     _call("ocv_mlp_f32", x.data_ptr(), ld, R, n, Wp, Bp, Dp, _ptr(residual), _ptr(o32), _ptr(o16), _stream())
     return o32, o16
+
+
+# ---- whole head through the native executor (ocv_head_*) ----------------------------------------------
+
+STRATEGIES = {"learned": 0, "learned_bbox_wh": 1, "grid_random": 2, "grid_random_roi_align": 3}
+
+
+class NativeHead:
+    """Owner of one ``ocv_head`` plan plus the torch buffers it borrows (packed weights, workspace)."""
+
+    def __init__(self, kind: int, strategy: str, no_obj_sa: bool, use_2_saca: bool, n_bins: int, obj_dim: int,
+                 min_depth: float, max_depth: float):
+        import ctypes as C
+        if kind == 1 and strategy not in STRATEGIES:
+            raise SystemExit("Error: ObjCAViT positional embedding strategy not recognised.")  # ObjCAViT.py:284
+        cfg = _lib.HeadConfig(kind, STRATEGIES.get(strategy, 0), int(no_obj_sa), int(use_2_saca), n_bins, obj_dim,
+                              float(min_depth), float(max_depth))
+        self._h = C.c_void_p()
+        _lib.check(_lib.lib().ocv_head_create(C.byref(cfg), C.byref(self._h)), "ocv_head_create")
+        self.kind = kind
+        self.n_bins = n_bins
+        self.packed = None
+        self.sig = None
+        self.ws = None
+
+    def __del__(self):
+        try:
+            if self._h:
+                _lib.lib().ocv_head_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    def _check(self, status, what):
+        if status == -1:
+            key = _lib.lib().ocv_head_missing_key(self._h).decode()
+            if key:
+                raise _lib.OcvError(f"objcavit_b200 {what}: parameter '{key}' was not registered")
+        _lib.check(status, what)
+
+    def bind(self, P):
+        """(Re)register the parameters and rebuild the derived copies when any storage / version changed."""
+        sig = tuple((v.data_ptr(), v._version) for v in P.values())
+        if sig == self.sig:
+            return
+        L = _lib.lib()
+        for k, v in P.items():
+            _chk(v, torch.float32, k)
+            assert v.is_contiguous()
+            self._check(L.ocv_head_set_param(self._h, k.encode(), v.data_ptr(), v.numel()), "ocv_head_set_param")
+        dev = next(iter(P.values())).device
+        nbytes = L.ocv_head_packed_bytes(self._h)
+        self.packed = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+        global launch_count
+        launch_count += 2 + sum(1 for _ in P)  # upper bound; packing is outside any timed region
+        self._check(L.ocv_head_pack(self._h, self.packed.data_ptr(), _stream()), "ocv_head_pack")
+        self.sig = sig
+
+    def forward(self, x_nhwc, feats, boxes, offsets, total, n_max, obj_tokens_out=None):
+        global launch_count
+        _chk(x_nhwc, torch.bfloat16, "x_nhwc")
+        assert x_nhwc.is_contiguous() and x_nhwc.shape[3] == 128
+        B, h, w, _ = x_nhwc.shape
+        L = _lib.lib()
+        need = L.ocv_head_workspace_bytes(self._h, B, h, w, total, n_max)
+        if need < 0:
+            _lib.check(int(need), "ocv_head_workspace_bytes")
+        if self.ws is None or self.ws.numel() < need or self.ws.device != x_nhwc.device:
+            self.ws = torch.empty(need, device=x_nhwc.device, dtype=torch.uint8)
+        depth = torch.empty(B, 1, h, w, device=x_nhwc.device, dtype=torch.float32)
+        edges = torch.empty(B, self.n_bins + 1, device=x_nhwc.device, dtype=torch.float32)
+        if self.kind == 1:
+            _chk(feats, torch.float32, "object features"); _chk(boxes, torch.float32, "object boxes")
+            _chk(offsets, torch.int32, "offsets")
+            assert feats.is_contiguous() and boxes.is_contiguous() and boxes.shape == (total, 4) and feats.shape[0] == total
+        st = _stream()
+        if timed_kernel == "ocv_head_forward":
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+        self._check(L.ocv_head_forward(self._h, x_nhwc.data_ptr(), _ptr(feats), _ptr(boxes), _ptr(offsets), total, n_max,
+                                       B, h, w, depth.data_ptr(), edges.data_ptr(), _ptr(obj_tokens_out),
+                                       self.ws.data_ptr(), st), "ocv_head_forward")
+        if timed_kernel == "ocv_head_forward":
+            e1.record()
+            timed_events.append((e0, e1))
+        launch_count += L.ocv_head_last_launches(self._h)
+        return depth, edges
