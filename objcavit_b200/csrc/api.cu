@@ -1,5 +1,6 @@
 // Library-level entry points: ABI version, device check, status strings.
 #include "common.cuh"
+#include <cstdlib>
 
 int ocv_require_sm100() {
   static int cached = 1;  // 1 = unknown
@@ -12,6 +13,15 @@ int ocv_require_sm100() {
   if (e != cudaSuccess) return (int)e;
   cached = (major == 10) ? OCV_OK : OCV_E_ARCH;
   return cached;
+}
+
+bool ocv_pdl_enabled() {
+  static int cached = -1;
+  if (cached < 0) {
+    const char* e = getenv("OCV_NO_PDL");
+    cached = (e && e[0] == '1') ? 0 : 1;
+  }
+  return cached == 1;
 }
 
 extern "C" int ocv_abi_version(void) { return 1; }

@@ -51,10 +51,16 @@ mha_bf16_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __rest
                 const __nv_bfloat16* __restrict__ v, __nv_bfloat16* __restrict__ out,
                 const uint8_t* __restrict__ mask, int Sq, int Sk, long long q_bs, int q_rs, long long k_bs, int k_rs,
                 long long v_bs, int v_rs, long long o_bs, int o_rs) {
-  __shared__ __align__(16) __nv_bfloat16 Qs[QT][PITCH];
-  __shared__ __align__(16) __nv_bfloat16 Ks[KT][PITCH];
-  __shared__ __align__(16) __nv_bfloat16 Vs[KT][PITCH];
-  __shared__ float Msk[KT];
+  // The whole K and V of this (image, head) are staged ONCE (Sk <= ~1300 keys x 32 dims: <= 200 KB): one global-memory
+  // round trip per CTA instead of one per key tile — the stage is latency-bound, not bandwidth- or FLOP-bound.
+  extern __shared__ __align__(16) uint8_t att_smem[];
+  const int Skp = (Sk + KT - 1) / KT * KT;
+  __nv_bfloat16 (*Qs)[PITCH] = reinterpret_cast<__nv_bfloat16 (*)[PITCH]>(att_smem);
+  __nv_bfloat16 (*Kall)[PITCH] = Qs + QT;
+  __nv_bfloat16 (*Vall)[PITCH] = Kall + Skp;
+  float* Mall = reinterpret_cast<float*>(Vall + Skp);
+  pdl_launch();
+  pdl_wait();  // q, k, v come from the previous kernel of the chain
   const int b = blockIdx.z, hd = blockIdx.y, q0 = blockIdx.x * QT;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, t = lane & 3;
@@ -62,6 +68,19 @@ mha_bf16_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __rest
   const __nv_bfloat16* kb = k + b * k_bs + hd * D;
   const __nv_bfloat16* vb = v + b * v_bs + hd * D;
   load_tile(Qs, qb, q0, Sq, q_rs);
+#pragma unroll 4
+  for (int i = threadIdx.x; i < Skp * 4; i += 128) {  // independent 16-byte loads: several in flight per thread
+    const int r = i >> 2, c = (i & 3) * 8;
+    uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
+    if (r < Sk) {
+      kv = *reinterpret_cast<const uint4*>(kb + (long long)r * k_rs + c);
+      vv = *reinterpret_cast<const uint4*>(vb + (long long)r * v_rs + c);
+    }
+    *reinterpret_cast<uint4*>(&Kall[r][c]) = kv;
+    *reinterpret_cast<uint4*>(&Vall[r][c]) = vv;
+  }
+  for (int j = threadIdx.x; j < Skp; j += blockDim.x)
+    Mall[j] = (j >= Sk || (mask && mask[(long long)b * Sk + j])) ? 1.f : 0.f;
   __syncthreads();
   uint32_t qa[2][4];
   {
@@ -74,14 +93,9 @@ mha_bf16_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __rest
   float m_i[2] = {-INFINITY, -INFINITY}, l_i[2] = {0.f, 0.f};
   float o[4][4] = {};
   for (int k0 = 0; k0 < Sk; k0 += KT) {
-    __syncthreads();
-    load_tile(Ks, kb, k0, Sk, k_rs);
-    load_tile(Vs, vb, k0, Sk, v_rs);
-    if (threadIdx.x < KT) {
-      const int j = k0 + threadIdx.x;
-      Msk[threadIdx.x] = (j >= Sk || (mask && mask[(long long)b * Sk + j])) ? 1.f : 0.f;
-    }
-    __syncthreads();
+    __nv_bfloat16 (*Ks)[PITCH] = Kall + k0;
+    __nv_bfloat16 (*Vs)[PITCH] = Vall + k0;
+    const float* Msk = Mall + k0;
     float s[8][4];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
@@ -171,9 +185,17 @@ extern "C" int ocv_mha_core_bf16(const void* q, const void* k, const void* v, vo
                   ((o_bstride | o_rstride) & 1) == 0);
   if (int s = ocv_require_sm100()) return s;
   dim3 grid(ceil_div(Sq, QT), heads, B);
-  mha_bf16_kernel<<<grid, 128, 0, ocv_stream(stream)>>>(
-      static_cast<const __nv_bfloat16*>(q), static_cast<const __nv_bfloat16*>(k), static_cast<const __nv_bfloat16*>(v),
-      static_cast<__nv_bfloat16*>(out), key_padding_mask, Sq, Sk, q_bstride, q_rstride, k_bstride, k_rstride,
-      v_bstride, v_rstride, o_bstride, o_rstride);
-  return ocv_launch_status();
+  const int Skp = ceil_div(Sk, KT) * KT;
+  const size_t smem = (size_t)(QT + 2 * Skp) * PITCH * sizeof(__nv_bfloat16) + (size_t)Skp * sizeof(float);
+  OCV_CHECK_SHAPE(smem <= 227 * 1024);
+  static size_t smem_set = 0;
+  if (smem > 48 * 1024 && smem > smem_set) {
+    cudaError_t e = cudaFuncSetAttribute(mha_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    smem_set = smem;
+  }
+  return ocv_launch_pdl(mha_bf16_kernel, grid, dim3(128), smem, stream, static_cast<const __nv_bfloat16*>(q),
+                        static_cast<const __nv_bfloat16*>(k), static_cast<const __nv_bfloat16*>(v),
+                        static_cast<__nv_bfloat16*>(out), key_padding_mask, Sq, Sk, q_bstride, q_rstride, k_bstride,
+                        k_rstride, v_bstride, v_rstride, o_bstride, o_rstride);
 }

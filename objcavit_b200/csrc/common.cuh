@@ -37,3 +37,30 @@ __device__ __forceinline__ float warp_max(float v) {
 
 template <typename T>
 static inline T ceil_div(T a, T b) { return (a + b - 1) / b; }
+
+// ---- programmatic dependent launch (PDL) ---------------------------------------------------------------------------
+// The head is a chain of ~50 short dependent kernels: launch latency and each kernel's prologue (barrier init, TMEM
+// allocation, tensor-map fetch, weight tiles, bias vectors) would otherwise sit on the critical path.  Every kernel of
+// the chain calls pdl_launch() first (the next kernel in the stream may start its own prologue) and pdl_wait() before
+// it touches anything an earlier kernel produced (and before it writes anything an earlier kernel may still read).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool ocv_pdl_enabled();  // false when OCV_NO_PDL=1 is set in the environment (api.cu)
+
+template <typename... KArgs, typename... Args>
+static inline int ocv_launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, void* stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = ocv_stream(stream);
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = ocv_pdl_enabled() ? 1 : 0;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+  if (e != cudaSuccess) return (int)e;
+  return ocv_launch_status();
+}

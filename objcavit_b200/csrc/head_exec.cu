@@ -238,6 +238,8 @@ Workspace carve(const ocv_head* H, void* base, int B, int h, int w, int total, i
 }
 
 __global__ void uniform_offsets_kernel(int32_t* o, int n, int step) {
+  pdl_launch();
+  pdl_wait();
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) o[i] = i * step;
 }
@@ -428,8 +430,7 @@ extern "C" int ocv_head_forward(ocv_head* H, const void* X, const float* obj_fea
     if (!H->cfg.no_obj_sa) ocur = encoder(c, pre + "saca_1.obj_transformer_encoder.", W.obj, 0, B, n_max, W.mask, s1);
     // :192-194 objects LEFT-padded to S, mask RIGHT-padded (F5)
     if (c.ok()) {
-      uniform_offsets_kernel<<<ceil_div(B + 1, 128), 128, 0, ocv_stream(s1)>>>(W.uni, B + 1, n_max);
-      c.run(ocv_launch_status());
+      c.run(ocv_launch_pdl(uniform_offsets_kernel, dim3(ceil_div(B + 1, 128)), dim3(128), 0, s1, W.uni, B + 1, n_max));
     }
     c.run(ocv_pad_objects_impl(W.obj.x32[ocur], W.uni, obj_offsets, W.obj_s32, W.obj_s16, W.kpm, B, S, n_max, E, 0.0001f, 1,
                                s1));

@@ -55,11 +55,13 @@ __global__ void fold_queries_kernel(const float* __restrict__ Wout, const float*
                                     const float* __restrict__ b3, float scale, __nv_bfloat16* __restrict__ Mb,
                                     float* __restrict__ blog, int K, int Q, int E) {
   extern __shared__ float ws[];  // [FQ_BINS][Q] then [FQ_BINS][nwarp]
+  pdl_launch();
   const int b = blockIdx.y, k0 = blockIdx.x * FQ_BINS, c = threadIdx.x;
-  for (int i = threadIdx.x; i < FQ_BINS * Q; i += blockDim.x) {
+  for (int i = threadIdx.x; i < FQ_BINS * Q; i += blockDim.x) {  // conv_out weights: independent of the chain
     const int kk = i / Q, q = i % Q;
     ws[i] = (k0 + kk < K) ? Wout[(long long)(k0 + kk) * Q + q] : 0.f;
   }
+  pdl_wait();  // the queries are the previous kernels' tokens
   __syncthreads();
   float acc[FQ_BINS] = {};
   const float* qb = queries + b * q_bs;
@@ -117,7 +119,6 @@ extern "C" int ocv_fold_queries_bf16(const float* Wout, const float* bout, const
   OCV_CHECK_SHAPE(E % 32 == 0 && E >= 32 && E <= 1024 && B <= 65535);
   if (int s = ocv_require_sm100()) return s;
   const size_t smem = (FQ_BINS * Q + FQ_BINS * (E / 32)) * sizeof(float);
-  fold_queries_kernel<<<dim3(ceil_div(K, FQ_BINS), B), E, smem, ocv_stream(stream)>>>(
-      Wout, bout, queries, q_bstride, q_rstride, b3, logit_scale, static_cast<__nv_bfloat16*>(Mb), blog, K, Q, E);
-  return ocv_launch_status();
+  return ocv_launch_pdl(fold_queries_kernel, dim3(ceil_div(K, FQ_BINS), B), dim3(E), smem, stream, Wout, bout, queries,
+                        q_bstride, q_rstride, b3, logit_scale, static_cast<__nv_bfloat16*>(Mb), blog, K, Q, E);
 }

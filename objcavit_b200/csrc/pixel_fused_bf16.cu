@@ -7,20 +7,27 @@
 //   (modules/ObjCAViT.py:374-375, modules/GraphBins.py:109,119; modules/miniViT.py:25,31, modules/AdaBins.py:77,87).
 // Neither the [B,128,h,w] range-attention maps nor the [B,256,h,w] probability volume ever exist in HBM.
 //
-// Tile = 8 x 16 pixels (M = 128 TMEM lanes).  Per tile the CTA
-//   1. TMA-loads the (10 x 18 pixel) x 128-channel halo once (two 64-channel planes, 128B swizzle, OOB = conv zero padding);
-//      the 9 taps are 9 *shifted smem descriptors* into that halo (start + (dy*10+dx)*128 B, group stride 1280 B) —
-//      the swizzle is a function of the absolute smem address, so row shifts need no re-load (probes/probe_desc_shift.cu);
-//   2. streams the 18 (tap, k-half) weight slabs [128 x 64] through an mbarrier ring and issues 72 tcgen05.mma
-//      (M128 N128 K16) into one of two conv accumulators in TMEM;
-//   3. the epilogue warps read the accumulator (tcgen05.ld), round to bf16 and write it as the K-major A operand
-//      of the logits GEMM (swizzled smem staging);
-//   4. 16 more tcgen05.mma (4 slabs of Mb[b]) give the 128 x 256 logits in TMEM;
-//   5. the epilogue warps run an online softmax over the 256 columns of their own TMEM lane (one thread = one
-//      pixel) and store one fp32 depth per pixel.
-// Warp roles: 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator, 4..7 = convert + softmax epilogue.
-// The conv accumulator is double buffered, so conv(i+1) runs on the tensor pipe while the epilogue of tile i
-// and the conversion of tile i+1 run on the SIMT pipes.
+// Work unit = a PAIR of 8 x 16 pixel tiles (a 16 x 16 pixel block: tile A = columns 0..7, tile B = columns 8..15), M = 128
+// TMEM lanes each.  The kernel is bound by the L2 -> SM stream of the conv weights (288 KB per pass, they do not fit in
+// shared memory next to the operands), so every weight slab is used for BOTH tiles: 8 MMAs per 16 KB slab instead of 4.
+// Per pair the CTA
+//   1. TMA-loads the (18 x 18 pixel) x 128-channel halo as two 64-channel planes (128B swizzle, OOB = conv zero padding);
+//      the 9 taps x 2 tiles are 18 *shifted smem descriptors* into a plane (start + (dy*18+dx [+8])*128 B, 8-row group
+//      stride 18*128 B): the swizzle is a function of the absolute smem address, so shifts need no re-load
+//      (probes/probe_desc_shift.cu).  The k loop runs plane-major (all taps of channels 0..63, then of 64..127), so each
+//      plane buffer is free half a pair early and the next pair's plane lands while this pair still computes: two plane
+//      buffers give full double buffering;
+//   2. streams the 18 (k-half, tap) weight slabs [128 x 64] through a 4-slot mbarrier ring and issues 144 tcgen05.mma
+//      (M128 N128 K16) into the two conv accumulators in TMEM;
+//   3. the epilogue warps read the accumulators (tcgen05.ld), round to bf16 and write them as the K-major A operands of
+//      the logits GEMMs (two swizzled staging tiles);
+//   4. per tile 16 more tcgen05.mma (4 slabs of Mb[b]) give the 128 x 256 logits in TMEM;
+//   5. the epilogue warps run an online softmax over the 256 columns of their TMEM lane and store one fp32 depth per pixel.
+// Warp roles: 0 = TMA producer, 1 = MMA issuer, 2 = TMEM allocator, 4..11 = convert + softmax epilogue: two warpgroups,
+// each thread owns one pixel row and one half of the columns (conv channels 0..63 | 64..127, bins 0..127 | 128..255);
+// the two softmax halves are merged through shared memory.
+// MMA order per pair i:  conv(i) plane 0 | logits B(i-1) | conv(i) plane 1 | logits A(i)   — the logits GEMM of one tile
+// runs while the epilogue converts / soft-maxes the other, so the tensor pipe idles only while tile A is converted.
 #include "tc_common.cuh"
 
 namespace {
@@ -30,22 +37,24 @@ using namespace tc;
 constexpr int C = 128;                 // channels in = channels out of conv3x3 = E
 constexpr int NB = 256;                // bins
 constexpr int TW = 8, TH = 16;         // tile (pixels): M index m = ty*8 + tx
-constexpr int HW_ = TW + 2, HH = TH + 2;
-constexpr int HALO_PLANE = ((HW_ * HH * 128 + 1023) / 1024) * 1024;   // 23040 -> 23552 B per 64-channel plane
-constexpr int HALO_BYTES = 2 * HALO_PLANE;
-constexpr int HALO_TX = 2 * HW_ * HH * 128;                            // bytes TMA delivers per halo
+constexpr int PW = 2 * TW;             // pair block width
+constexpr int HW_ = PW + 2, HH = TH + 2;                               // halo 18 x 18
+constexpr int PLANE_TX = HW_ * HH * 128;                               // bytes TMA delivers per 64-channel plane
+constexpr int PLANE = ((PLANE_TX + 1023) / 1024) * 1024;               // 41472 -> 41984
 constexpr int SLAB = 128 * 64 * 2;     // 16 KB: [128 rows x 64 k] bf16, 128B swizzle
-constexpr int NS = 6;                  // slab ring stages
+constexpr int NS = 4;                  // slab ring slots
 constexpr int STG_BYTES = 2 * SLAB;    // bf16 conv tile as A operand: two K-halves
-constexpr int N_EPI = 128;
-constexpr int SMEM_BYTES = 2 * HALO_BYTES + NS * SLAB + STG_BYTES + 1024 /*align*/ + 256 /*barriers*/;
-constexpr uint32_t TM_CONV0 = 0, TM_LOGITS = 256, TM_COLS = 512;
+constexpr int N_EPI = 256;             // epilogue threads (warps 4..11)
+constexpr int THREADS = 128 + N_EPI;
+constexpr int MERGE_BYTES = 2 * 3 * 128 * 4;
+constexpr int SMEM_BYTES = 2 * PLANE + NS * SLAB + 2 * STG_BYTES + MERGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr uint32_t TM_CONVA = 0, TM_CONVB = 128, TM_LOGITS = 256, TM_COLS = 512;
 
 struct PixParams {
   const float* blog;     // [B,256]  log2e * (bout + Wout Q b3)
   const float* centres;  // [B,256]
   float* depth;          // [B,h*w]
-  int B, h, w, tiles_x, tiles_y, n_tiles;
+  int B, h, w, tiles_x, tiles_y, n_tiles;   // tiles = 16x16 pair blocks
 };
 
 __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2,
@@ -72,38 +81,75 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
+// packed fp32x2 arithmetic (FADD2 / FMUL2 / FFMA2, 3-input FMNMX3): the softmax epilogue is issue-bound, these halve it
+__device__ __forceinline__ uint64_t pk2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ uint64_t pk2u(uint32_t lo, uint32_t hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+  return r;
+}
+__device__ __forceinline__ void upk2(uint64_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
 struct TileCoord { int b, y0, x0; };
 __device__ __forceinline__ TileCoord tile_coord(const PixParams& p, int t) {
   const int per = p.tiles_x * p.tiles_y;
   const int b = t / per, r = t - b * per;
   const int ty = r / p.tiles_x;
-  return {b, ty * TH, (r - ty * p.tiles_x) * TW};
+  return {b, ty * TH, (r - ty * p.tiles_x) * PW};
 }
 
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(THREADS, 1)
 pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                    const __grid_constant__ CUtensorMap tmMb, PixParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base_u32 = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024 - (base_u32 & 1023)) & 1023);
-  uint8_t* halo = smem;                                // [2][2 planes]
-  uint8_t* ring = halo + 2 * HALO_BYTES;               // [NS] slabs
-  uint8_t* stg = ring + NS * SLAB;                     // [2 k-halves] bf16 conv tile
-  uint64_t* bars = reinterpret_cast<uint64_t*>(stg + STG_BYTES);
+  uint8_t* plane = smem;                               // [2] 64-channel halo planes
+  uint8_t* ring = plane + 2 * PLANE;                   // [NS] slabs
+  uint8_t* stg = ring + NS * SLAB;                     // [2 tiles][2 k-halves] bf16 conv tiles
+  float* merge = reinterpret_cast<float*>(stg + 2 * STG_BYTES);   // [2 parity][3][128]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stg + 2 * STG_BYTES + MERGE_BYTES);
   uint64_t* w_full = bars;                  // [NS]
   uint64_t* w_empty = w_full + NS;          // [NS]
-  uint64_t* halo_full = w_empty + NS;       // [2]
-  uint64_t* halo_empty = halo_full + 2;     // [2]
-  uint64_t* conv_full = halo_empty + 2;     // [2]
-  uint64_t* conv_empty = conv_full + 2;     // [2]
-  uint64_t* stg_full = conv_empty + 2;
-  uint64_t* stg_empty = stg_full + 1;
-  uint64_t* log_full = stg_empty + 1;
+  uint64_t* pl_full = w_empty + NS;         // [2]
+  uint64_t* pl_empty = pl_full + 2;         // [2]
+  uint64_t* stg_full = pl_empty + 2;        // [2]  (tile A, tile B)
+  uint64_t* stg_empty = stg_full + 2;       // [2]
+  uint64_t* conv_full = stg_empty + 2;
+  uint64_t* conv_empty = conv_full + 1;
+  uint64_t* log_full = conv_empty + 1;
   uint64_t* log_empty = log_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(log_empty + 1);
 
+  pdl_launch();
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
-  // contiguous chunk of tiles per CTA (neighbouring tiles share halo rows in L2 and the per-image operands)
+  // contiguous chunk of pair blocks per CTA (neighbours share halo rows in L2 and the per-image operands)
   const int per_cta = (p.n_tiles + gridDim.x - 1) / gridDim.x;
   const int t_begin = min(p.n_tiles, (int)blockIdx.x * per_cta);
   const int t_end = min(p.n_tiles, t_begin + per_cta);
@@ -120,13 +166,13 @@ pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
       mbar_init(&w_empty[s], 1);
     }
     for (int i = 0; i < 2; ++i) {
-      mbar_init(&halo_full[i], 1);
-      mbar_init(&halo_empty[i], 1);
-      mbar_init(&conv_full[i], 1);
-      mbar_init(&conv_empty[i], N_EPI);
+      mbar_init(&pl_full[i], 1);
+      mbar_init(&pl_empty[i], 1);
+      mbar_init(&stg_full[i], N_EPI);
+      mbar_init(&stg_empty[i], 1);
     }
-    mbar_init(stg_full, N_EPI);
-    mbar_init(stg_empty, 1);
+    mbar_init(conv_full, 1);
+    mbar_init(conv_empty, N_EPI);
     mbar_init(log_full, 1);
     mbar_init(log_empty, N_EPI);
     fence_barrier_init();
@@ -139,16 +185,15 @@ pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
 
   if (warp == 0) {
     // ================= TMA producer =================
+    // slab order == the MMA issuer's consumption order; the plane loads are slotted in where their buffer is known free
     if (elect_one() && n_my > 0) {
       uint32_t ring_n = 0;  // slabs issued so far
-      auto load_halo = [&](int it) {
-        const int buf = it & 1;
-        mbar_wait(&halo_empty[buf], ((it >> 1) & 1) ^ 1);
+      bool waited = false;
+      auto load_plane = [&](int it, int kh) {
+        mbar_wait(&pl_empty[kh], (it & 1) ^ 1);
         const TileCoord tc_ = tile_coord(p, t_begin + it);
-        mbar_arrive_expect_tx(&halo_full[buf], HALO_TX);
-        uint8_t* dst = halo + buf * HALO_BYTES;
-        tma_load_4d(dst, &tmX, &halo_full[buf], 0, tc_.x0 - 1, tc_.y0 - 1, tc_.b);
-        tma_load_4d(dst + HALO_PLANE, &tmX, &halo_full[buf], 64, tc_.x0 - 1, tc_.y0 - 1, tc_.b);
+        mbar_arrive_expect_tx(&pl_full[kh], PLANE_TX);
+        tma_load_4d(plane + kh * PLANE, &tmX, &pl_full[kh], kh * 64, tc_.x0 - 1, tc_.y0 - 1, tc_.b);
       };
       auto load_slab = [&](const CUtensorMap* m, int c0, int c1) {
         const int s = ring_n % NS;
@@ -158,29 +203,38 @@ pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
         ++ring_n;
       };
       auto load_logit_slabs = [&](int it) {
+        if (!waited) {  // Mb is produced by the previous kernel of the chain; features and conv weights are not
+          pdl_wait();
+          waited = true;
+        }
         const int b = tile_coord(p, t_begin + it).b;
         for (int nh = 0; nh < 2; ++nh)
           for (int kh = 0; kh < 2; ++kh) load_slab(&tmMb, kh * 64, b * NB + nh * 128);
       };
-      load_halo(0);
+      load_plane(0, 0);
       for (int it = 0; it < n_my; ++it) {
-        if (it + 1 < n_my) load_halo(it + 1);
-        for (int tap = 0; tap < 9; ++tap)
-          for (int kh = 0; kh < 2; ++kh) load_slab(&tmW, kh * 64, tap * C);
-        if (it > 0) load_logit_slabs(it - 1);
+        for (int tap = 0; tap < 5; ++tap) load_slab(&tmW, 0, tap * C);
+        load_plane(it, 1);
+        for (int tap = 5; tap < 9; ++tap) load_slab(&tmW, 0, tap * C);
+        if (it > 0) load_logit_slabs(it - 1);            // logits B(it-1)
+        for (int tap = 0; tap < 5; ++tap) load_slab(&tmW, 64, tap * C);
+        if (it + 1 < n_my) load_plane(it + 1, 0);
+        for (int tap = 5; tap < 9; ++tap) load_slab(&tmW, 64, tap * C);
+        load_logit_slabs(it);                            // logits A(it)
       }
-      load_logit_slabs(n_my - 1);
+      load_logit_slabs(n_my - 1);                        // logits B(n_my-1)
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
     if (elect_one() && n_my > 0) {
       constexpr uint32_t idesc = make_idesc_bf16(128, 128);
-      uint32_t ring_n = 0;
-      auto logits_mma = [&](int j) {
-        mbar_wait(stg_full, j & 1);
-        mbar_wait(log_empty, (j & 1) ^ 1);
+      uint32_t ring_n = 0, log_n = 0;
+      // logits of tile `tile` (0 = A, 1 = B) of pair `it`: 4 slabs of Mb[b] against the staged bf16 conv tile
+      auto logits_mma = [&](int it, int tile) {
+        mbar_wait(&stg_full[tile], it & 1);
+        mbar_wait(log_empty, (log_n & 1) ^ 1);
         tc_fence_after();
-        const uint32_t a_base = smem_u32(stg);
+        const uint32_t a_base = smem_u32(stg + tile * STG_BYTES);
         for (int nh = 0; nh < 2; ++nh)
           for (int kh = 0; kh < 2; ++kh) {
             const int s = ring_n % NS;
@@ -194,122 +248,167 @@ pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
             umma_commit(&w_empty[s]);
             ++ring_n;
           }
-        umma_commit(stg_empty);
+        umma_commit(&stg_empty[tile]);
         umma_commit(log_full);
+        ++log_n;
       };
-      for (int it = 0; it < n_my; ++it) {
-        const int buf = it & 1;
-        mbar_wait(&conv_empty[buf], ((it >> 1) & 1) ^ 1);
-        mbar_wait(&halo_full[buf], (it >> 1) & 1);
+      auto conv_half = [&](int it, int kh) {
+        mbar_wait(&pl_full[kh], it & 1);
         tc_fence_after();
-        const uint32_t h_base = smem_u32(halo + buf * HALO_BYTES);
-        const uint32_t acc = tmem + TM_CONV0 + buf * 128;
+        const uint32_t h_base = smem_u32(plane + kh * PLANE);
         for (int tap = 0; tap < 9; ++tap) {
           const int dy = tap / 3, dx = tap - dy * 3;
-          for (int kh = 0; kh < 2; ++kh) {
-            const int s = ring_n % NS;
-            mbar_wait(&w_full[s], (ring_n / NS) & 1);
-            tc_fence_after();
-            const uint32_t a_base = h_base + kh * HALO_PLANE + (dy * HW_ + dx) * 128;
-            const uint32_t b_base = smem_u32(ring + s * SLAB);
+          const int s = ring_n % NS;
+          mbar_wait(&w_full[s], (ring_n / NS) & 1);
+          tc_fence_after();
+          const uint32_t a_base = h_base + (dy * HW_ + dx) * 128;
+          const uint32_t b_base = smem_u32(ring + s * SLAB);
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk)
-              umma_bf16(acc, desc_sw128(a_base + kk * 32, HW_ * 128), desc_sw128(b_base + kk * 32, 1024), idesc,
-                        (tap | kh | kk) != 0);
-            umma_commit(&w_empty[s]);
-            ++ring_n;
-          }
+          for (int kk = 0; kk < 4; ++kk)
+            umma_bf16(tmem + TM_CONVA, desc_sw128(a_base + kk * 32, HW_ * 128), desc_sw128(b_base + kk * 32, 1024), idesc,
+                      (kh | tap | kk) != 0);
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk)
+            umma_bf16(tmem + TM_CONVB, desc_sw128(a_base + TW * 128 + kk * 32, HW_ * 128),
+                      desc_sw128(b_base + kk * 32, 1024), idesc, (kh | tap | kk) != 0);
+          umma_commit(&w_empty[s]);
+          ++ring_n;
         }
-        umma_commit(&halo_empty[buf]);
-        umma_commit(&conv_full[buf]);
-        if (it > 0) logits_mma(it - 1);
+        umma_commit(&pl_empty[kh]);
+      };
+      for (int it = 0; it < n_my; ++it) {
+        mbar_wait(conv_empty, (it & 1) ^ 1);   // both conv accumulators drained by the epilogue (pair it-1)
+        tc_fence_after();
+        conv_half(it, 0);
+        if (it > 0) logits_mma(it - 1, 1);
+        conv_half(it, 1);
+        umma_commit(conv_full);
+        logits_mma(it, 0);
       }
-      logits_mma(n_my - 1);
+      logits_mma(n_my - 1, 1);
     }
   } else if (warp >= 4) {
-    // ================= convert + softmax epilogue (one thread = one pixel = one TMEM lane) =================
-    const int q = warp - 4;
+    // ================= convert + softmax epilogue =================
+    // thread = one pixel row (TMEM lane) x one column half
+    const int e = warp - 4;
+    const int q = e & 3;            // == warp % 4: the TMEM lane quarter this warp may read
+    const int half = e >> 2;
     const int m = q * 32 + lane;
     const int ty = m >> 3, tx = m & 7;
     const uint32_t lane_base = (uint32_t)(q * 32) << 16;
-    auto convert = [&](int it) {
-      const int buf = it & 1;
-      mbar_wait(&conv_full[buf], (it >> 1) & 1);
-      tc_fence_after();
-      uint32_t packed[64];
+    uint32_t job = 0;
+    if (n_my > 0) pdl_wait();       // blog / centres are produced by the previous kernels of the chain
+    // conv accumulator of `tile`, channels [64*half, 64*half+64) -> bf16 -> K-half `half` of the staging tile
+    auto convert = [&](int it, int tile) {
+      uint32_t packed[32];
+      {
+        const uint32_t src = tmem + lane_base + (tile ? TM_CONVB : TM_CONVA) + half * 64;
+        uint32_t r0[32], r1[32];
+        tmem_ld32(src, r0);
+        tmem_ld_wait();
+        tmem_ld32(src + 32, r1);  // in flight while the first 32 columns are packed
 #pragma unroll
-      for (int c4 = 0; c4 < 4; ++c4) {
-        uint32_t r[32];
-        tmem_ld32(tmem + lane_base + TM_CONV0 + buf * 128 + c4 * 32, r);
+        for (int j = 0; j < 16; ++j) packed[j] = pack_bf16(__uint_as_float(r0[2 * j]), __uint_as_float(r0[2 * j + 1]));
         tmem_ld_wait();
 #pragma unroll
-        for (int j = 0; j < 16; ++j) packed[c4 * 16 + j] = pack_bf16(__uint_as_float(r[2 * j]), __uint_as_float(r[2 * j + 1]));
+        for (int j = 0; j < 16; ++j) packed[16 + j] = pack_bf16(__uint_as_float(r1[2 * j]), __uint_as_float(r1[2 * j + 1]));
       }
-      tc_fence_before();
-      mbar_arrive(&conv_empty[buf]);
-      mbar_wait(stg_empty, (it & 1) ^ 1);
-      uint8_t* row = stg + m * 128;
+      mbar_wait(&stg_empty[tile], (it & 1) ^ 1);
+      uint8_t* row = stg + tile * STG_BYTES + half * SLAB + m * 128;
 #pragma unroll
-      for (int kh = 0; kh < 2; ++kh)
-#pragma unroll
-        for (int ch = 0; ch < 8; ++ch) {
-          uint4 v = make_uint4(packed[(kh * 8 + ch) * 4], packed[(kh * 8 + ch) * 4 + 1], packed[(kh * 8 + ch) * 4 + 2],
-                               packed[(kh * 8 + ch) * 4 + 3]);
-          *reinterpret_cast<uint4*>(row + kh * SLAB + ((ch ^ (m & 7)) << 4)) = v;
-        }
+      for (int ch = 0; ch < 8; ++ch) {
+        uint4 v = make_uint4(packed[ch * 4], packed[ch * 4 + 1], packed[ch * 4 + 2], packed[ch * 4 + 3]);
+        *reinterpret_cast<uint4*>(row + ((ch ^ (m & 7)) << 4)) = v;
+      }
       fence_proxy_async_smem();
-      mbar_arrive(stg_full);
+      mbar_arrive(&stg_full[tile]);
     };
-    auto softmax_store = [&](int j) {
-      const TileCoord tc_ = tile_coord(p, t_begin + j);
-      const float4* bl = reinterpret_cast<const float4*>(p.blog + (long long)tc_.b * NB);
-      const float4* ce = reinterpret_cast<const float4*>(p.centres + (long long)tc_.b * NB);
-      mbar_wait(log_full, j & 1);
+    auto softmax_store = [&](int it, int tile) {
+      const TileCoord tc_ = tile_coord(p, t_begin + it);
+      const float4* bl = reinterpret_cast<const float4*>(p.blog + (long long)tc_.b * NB + half * 128);
+      const float4* ce = reinterpret_cast<const float4*>(p.centres + (long long)tc_.b * NB + half * 128);
+      mbar_wait(log_full, job & 1);
       tc_fence_after();
-      float mx = -INFINITY, s = 0.f, a = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < NB / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld32(tmem + lane_base + TM_LOGITS + c * 32, r);
+      float mx = -INFINITY;
+      uint64_t s2a = 0, s2b = 0, a2a = 0, a2b = 0;   // two (sum, weighted sum) accumulator pairs: shorter dependency chains
+      const uint32_t src = tmem + lane_base + TM_LOGITS + half * 128;
+      uint32_t rb[2][32];
+      tmem_ld32(src, rb[0]);
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
         tmem_ld_wait();
-        float v[32];
+        if (c < 3) tmem_ld32(src + (c + 1) * 32, rb[(c + 1) & 1]);  // next 32 bins in flight while these are processed
+        const uint32_t* r = rb[c & 1];
+        uint64_t v2[16];
         float cm = -INFINITY;
 #pragma unroll
         for (int j4 = 0; j4 < 8; ++j4) {
           const float4 b4 = __ldg(bl + c * 8 + j4);
-          v[4 * j4 + 0] = __uint_as_float(r[4 * j4 + 0]) + b4.x;
-          v[4 * j4 + 1] = __uint_as_float(r[4 * j4 + 1]) + b4.y;
-          v[4 * j4 + 2] = __uint_as_float(r[4 * j4 + 2]) + b4.z;
-          v[4 * j4 + 3] = __uint_as_float(r[4 * j4 + 3]) + b4.w;
-          cm = fmaxf(cm, fmaxf(fmaxf(v[4 * j4], v[4 * j4 + 1]), fmaxf(v[4 * j4 + 2], v[4 * j4 + 3])));
+          v2[2 * j4] = add2(pk2u(r[4 * j4], r[4 * j4 + 1]), pk2(b4.x, b4.y));
+          v2[2 * j4 + 1] = add2(pk2u(r[4 * j4 + 2], r[4 * j4 + 3]), pk2(b4.z, b4.w));
+          float x0, x1, x2, x3;
+          upk2(v2[2 * j4], x0, x1);
+          upk2(v2[2 * j4 + 1], x2, x3);
+          cm = max3(cm, x0, x1);
+          cm = max3(cm, x2, x3);
         }
         const float m_new = fmaxf(mx, cm);
         const float sc = ex2(mx - m_new);
-        s *= sc;
-        a *= sc;
+        const uint64_t sc2 = pk2(sc, sc), nm2 = pk2(-m_new, -m_new);
+        s2a = mul2(s2a, sc2); s2b = mul2(s2b, sc2);
+        a2a = mul2(a2a, sc2); a2b = mul2(a2b, sc2);
 #pragma unroll
         for (int j4 = 0; j4 < 8; ++j4) {
           const float4 c4 = __ldg(ce + c * 8 + j4);
-          const float e0 = ex2(v[4 * j4 + 0] - m_new), e1 = ex2(v[4 * j4 + 1] - m_new);
-          const float e2 = ex2(v[4 * j4 + 2] - m_new), e3 = ex2(v[4 * j4 + 3] - m_new);
-          s += (e0 + e1) + (e2 + e3);
-          a = fmaf(e0, c4.x, a);
-          a = fmaf(e1, c4.y, a);
-          a = fmaf(e2, c4.z, a);
-          a = fmaf(e3, c4.w, a);
+          float t0, t1, t2, t3;
+          upk2(add2(v2[2 * j4], nm2), t0, t1);
+          upk2(add2(v2[2 * j4 + 1], nm2), t2, t3);
+          const uint64_t e01 = pk2(ex2(t0), ex2(t1)), e23 = pk2(ex2(t2), ex2(t3));
+          s2a = add2(s2a, e01);
+          s2b = add2(s2b, e23);
+          a2a = fma2(e01, pk2(c4.x, c4.y), a2a);
+          a2b = fma2(e23, pk2(c4.z, c4.w), a2b);
         }
         mx = m_new;
       }
+      float s, a;
+      {
+        float p0, p1, q0, q1;
+        upk2(add2(s2a, s2b), p0, p1);
+        upk2(add2(a2a, a2b), q0, q1);
+        s = p0 + p1;
+        a = q0 + q1;
+      }
       tc_fence_before();
       mbar_arrive(log_empty);
-      const int y = tc_.y0 + ty, x = tc_.x0 + tx;
-      if (y < p.h && x < p.w) p.depth[((long long)tc_.b * p.h + y) * p.w + x] = a / s;
+      // merge the two bin halves of this pixel (upper half -> shared memory -> lower half)
+      float* mg = merge + (job & 1) * 3 * 128;
+      if (half == 1) {
+        mg[m] = mx;
+        mg[128 + m] = s;
+        mg[256 + m] = a;
+      }
+      epi_bar();
+      if (half == 0) {
+        const float mx1 = mg[m], s1 = mg[128 + m], a1 = mg[256 + m];
+        const float mm = fmaxf(mx, mx1);
+        const float f0 = ex2(mx - mm), f1 = ex2(mx1 - mm);
+        const float st = s * f0 + s1 * f1, at = a * f0 + a1 * f1;
+        const int y = tc_.y0 + ty, x = tc_.x0 + tile * TW + tx;
+        if (y < p.h && x < p.w) p.depth[((long long)tc_.b * p.h + y) * p.w + x] = at / st;
+      }
+      ++job;
     };
     for (int it = 0; it < n_my; ++it) {
-      convert(it);
-      if (it > 0) softmax_store(it - 1);
+      mbar_wait(conv_full, it & 1);
+      tc_fence_after();
+      convert(it, 0);
+      convert(it, 1);
+      tc_fence_before();
+      mbar_arrive(conv_empty);
+      softmax_store(it, 0);   // logits A(it) are issued right after conv(it)
+      softmax_store(it, 1);   // logits B(it) are issued in the middle of conv(it+1) (or last): before conv_full(it+1)
     }
-    if (n_my > 0) softmax_store(n_my - 1);
   }
   tc_fence_before();
   __syncthreads();
@@ -322,7 +421,7 @@ int make_tmap_features(CUtensorMap* out, const void* X, int B, int h, int w) {
   if (reinterpret_cast<uintptr_t>(X) & 15) return OCV_E_ALIGN;
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)w, (cuuint64_t)h, (cuuint64_t)B};
   cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)w * C * 2, (cuuint64_t)h * w * C * 2};
-  cuuint32_t box[4] = {64, HW_, HH, 1};
+  cuuint32_t box[4] = {64, HW_, HH, 1};  // one 64-channel plane of the 18 x 18 pixel halo
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(X), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
@@ -354,7 +453,7 @@ extern "C" int ocv_pixel_fused_bf16(const void* X, const void* W3p, const void* 
   PixParams p{};
   p.blog = blog; p.centres = centres; p.depth = depth;
   p.B = B; p.h = h; p.w = w;
-  p.tiles_x = ceil_div(w, TW);
+  p.tiles_x = ceil_div(w, PW);
   p.tiles_y = ceil_div(h, TH);
   const long long nt = (long long)p.tiles_x * p.tiles_y * B;
   OCV_CHECK_SHAPE(nt < (1ll << 30));
@@ -362,6 +461,5 @@ extern "C" int ocv_pixel_fused_bf16(const void* X, const void* W3p, const void* 
   int grid = n_sm;
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (grid > p.n_tiles) grid = p.n_tiles;
-  pixel_fused_kernel<<<grid, 256, SMEM_BYTES, ocv_stream(stream)>>>(tmX, tmW, tmMb, p);
-  return ocv_launch_status();
+  return ocv_launch_pdl(pixel_fused_kernel, dim3(grid), dim3(THREADS), SMEM_BYTES, stream, tmX, tmW, tmMb, p);
 }

@@ -45,7 +45,9 @@ using namespace tc;
 
 constexpr int GM = 128, GN = 128, GK = 64, STAGES = 4;
 constexpr int A_BYTES = GM * GK * 2, B_BYTES = GN * GK * 2, STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int TP = 132;  // fp32 staging-tile pitch (floats): 16-byte aligned rows, conflict-free 128-bit row accesses
+constexpr int TILE_BYTES = GM * TP * 4;
+constexpr int GEMM_SMEM = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/ + TILE_BYTES + 3 * GN * 4 /*bias, gamma, beta*/;
 
 struct GemmParams {
   const float* bias;
@@ -60,7 +62,7 @@ struct GemmParams {
   int ldc16, ldr;
 };
 
-__global__ void __launch_bounds__(256, 1)
+__global__ void __launch_bounds__(512, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base_u32 = smem_u32(smem_raw);
@@ -72,6 +74,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   const int m0 = blockIdx.y * GM, n0 = blockIdx.x * GN;
+  pdl_launch();  // the next kernel of the chain may start its prologue
   int k_begin = 0, k_end = p.K;
   if (p.k_per_split > 0) {
     k_begin = blockIdx.z * p.k_per_split;
@@ -96,10 +99,50 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_d = *tmem_slot;
+  float* tile = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES + 256);
+  float* s_bias = tile + GM * TP;  // [128] bias, [128] gamma, [128] beta of this column tile
+  const bool split = p.k_per_split > 0;
 
+  if (warp >= 2) {
+    // parameters do not depend on the previous kernel: fetch them before the grid dependency resolves
+    for (int i = threadIdx.x - 64; i < 3 * GN; i += 448) {
+      const int which = i / GN, j = i - which * GN;
+      const float* src = which == 0 ? p.bias : (which == 1 ? p.gamma : p.beta);
+      s_bias[i] = (src && n0 + j < p.N) ? __ldg(src + n0 + j) : 0.f;
+    }
+    pdl_wait();
+  }
+  if (warp >= 2 && p.residual && !split) {
+    // residual tile -> shared memory with coalesced 128-bit loads while the main loop runs (warps 2..15 are idle)
+    const bool vec = (p.ldr & 3) == 0 && (reinterpret_cast<uintptr_t>(p.residual) & 15) == 0;
+    for (int i = threadIdx.x - 64; i < GM * 32; i += 448) {
+      const int r = i >> 5, c = (i & 31) * 4;
+      const int m = m0 + r, n = n0 + c;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (m < p.M && n < p.N) {
+        const float* src = p.residual + (long long)m * p.ldr + n;
+        if (vec && n + 3 < p.N) v = __ldg(reinterpret_cast<const float4*>(src));
+        else {
+          v.x = src[0];
+          if (n + 1 < p.N) v.y = src[1];
+          if (n + 2 < p.N) v.z = src[2];
+          if (n + 3 < p.N) v.w = src[3];
+        }
+      }
+      *reinterpret_cast<float4*>(tile + r * TP + c) = v;
+    }
+  }
   if (warp == 0) {
     if (elect_one()) {
-      for (int it = 0; it < n_k; ++it) {
+      // weight tiles of the first stages before the grid dependency resolves, activations after it
+      const int n_pre = n_k < STAGES ? n_k : STAGES;
+      for (int it = 0; it < n_pre; ++it) {
+        mbar_arrive_expect_tx(&full[it], STAGE_BYTES);
+        tma_load_2d(smem + it * STAGE_BYTES + A_BYTES, &tmB, &full[it], k_begin + it * GK, n0);
+      }
+      pdl_wait();
+      for (int it = 0; it < n_pre; ++it) tma_load_2d(smem + it * STAGE_BYTES, &tmA, &full[it], k_begin + it * GK, m0);
+      for (int it = n_pre; it < n_k; ++it) {
         const int s = it % STAGES;
         const uint32_t ph = (it / STAGES) & 1;
         mbar_wait(&empty[s], ph ^ 1);
@@ -126,133 +169,123 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       umma_commit(tmem_full);
     }
-  } else if (warp >= 4) {
-    const int quarter = warp % 4;
-    const int m = m0 + quarter * 32 + lane;
+  }
+  // ================= epilogue: ALL 16 warps =================
+  // A warp may only read the TMEM lane quarter (warp % 4); the 4 warps of a quarter split the 128 accumulator columns
+  // (32 each), so one thread finishes 32 outputs of one row.  With 4 warps per scheduler the global-memory latency of
+  // the bias / residual / LayerNorm-parameter loads is hidden; the row-wide LayerNorm statistics are combined through
+  // shared memory (two passes: mean, then centred variance).
+  __syncwarp();
+  __syncthreads();  // residual tile + parameter vectors complete; the two role warps have issued everything
+  pdl_wait();       // every thread stores to global memory below
+  {
+    const int quarter = warp & 3, cg = warp >> 2;
+    const int row_l = quarter * 32 + lane;
+    const int m = m0 + row_l;
+    const int nb = n0 + cg * 32;
+    float* red = reinterpret_cast<float*>(smem);  // [2][4][128] floats: the pipeline stages are idle by then
     if (n_k > 0) {
       mbar_wait(tmem_full, 0);
       tc_fence_after();
     }
-    const bool split = p.k_per_split > 0;
-    if (p.gamma) {
-      // LayerNorm epilogue: this thread owns the whole N == 128 row (post-norm encoder layer: LN(residual + A W^T + b))
-      float v[GN];
+    uint32_t r[32];
+    if (n_k > 0) {
+      tmem_ld32(tmem_d + ((uint32_t)(quarter * 32) << 16) + cg * 32, r);
+      tmem_ld_wait();
+    } else {
 #pragma unroll
-      for (int c = 0; c < GN / 32; ++c) {
-        uint32_t r[32];
-        tmem_ld32(tmem_d + ((uint32_t)(quarter * 32) << 16) + c * 32, r);
-        tmem_ld_wait();
+      for (int j = 0; j < 32; ++j) r[j] = 0;
+    }
+    const bool row_ok = m < p.M;
+    float v[32];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[c * 32 + j] = __uint_as_float(r[j]);
-      }
-      if (m < p.M) {
-        const float4* b4 = reinterpret_cast<const float4*>(p.bias);
-        const float4* r4 = p.residual ? reinterpret_cast<const float4*>(p.residual + (long long)m * p.ldr) : nullptr;
-        float sum = 0.f;
+    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+    float* trow = tile + row_l * TP + cg * 32;
+    if (!split) {
 #pragma unroll
-        for (int j = 0; j < GN / 4; ++j) {
-          float4 b = p.bias ? __ldg(b4 + j) : make_float4(0.f, 0.f, 0.f, 0.f);
-          if (r4) {
-            const float4 rr = __ldg(r4 + j);
-            b.x += rr.x; b.y += rr.y; b.z += rr.z; b.w += rr.w;
-          }
+      for (int j = 0; j < 8; ++j) {
+        const int n = nb + 4 * j;
+        if (p.bias) {
+          const float4 b = *reinterpret_cast<const float4*>(s_bias + cg * 32 + 4 * j);
           v[4 * j] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
-          sum += (v[4 * j] + v[4 * j + 1]) + (v[4 * j + 2] + v[4 * j + 3]);
         }
-        const float mean = sum * (1.f / GN);
-        float var = 0.f;
+        if (p.act == OCV_ACT_RELU) {
 #pragma unroll
-        for (int j = 0; j < GN; ++j) {
-          const float d = v[j] - mean;
-          var = fmaf(d, d, var);
+          for (int t = 0; t < 4; ++t) v[4 * j + t] = fmaxf(v[4 * j + t], 0.f);
+        } else if (p.act == OCV_ACT_LEAKY_RELU) {
+#pragma unroll
+          for (int t = 0; t < 4; ++t) v[4 * j + t] = v[4 * j + t] > 0.f ? v[4 * j + t] : 0.01f * v[4 * j + t];
         }
-        const float rstd = rsqrtf(var * (1.f / GN) + 1e-5f);
-        const bool zero = p.zero_rows && p.zero_rows[m];
-        const float4* g4 = reinterpret_cast<const float4*>(p.gamma);
-        const float4* e4 = reinterpret_cast<const float4*>(p.beta);
-        float* c32 = p.C ? static_cast<float*>(p.C) + (long long)m * p.ldc : nullptr;
-        __nv_bfloat16* c16 = p.C16 ? p.C16 + (long long)m * p.ldc16 : nullptr;
-#pragma unroll
-        for (int j = 0; j < GN / 4; ++j) {
-          const float4 g = __ldg(g4 + j), e = __ldg(e4 + j);
-          float4 o;
-          o.x = zero ? 0.f : (v[4 * j] - mean) * rstd * g.x + e.x;
-          o.y = zero ? 0.f : (v[4 * j + 1] - mean) * rstd * g.y + e.y;
-          o.z = zero ? 0.f : (v[4 * j + 2] - mean) * rstd * g.z + e.z;
-          o.w = zero ? 0.f : (v[4 * j + 3] - mean) * rstd * g.w + e.w;
-          if (c32) *reinterpret_cast<float4*>(c32 + 4 * j) = o;
-          if (c16) {
-            __nv_bfloat162 h0 = __floats2bfloat162_rn(o.x, o.y), h1 = __floats2bfloat162_rn(o.z, o.w);
-            uint2 u;
-            u.x = *reinterpret_cast<uint32_t*>(&h0);
-            u.y = *reinterpret_cast<uint32_t*>(&h1);
-            *reinterpret_cast<uint2*>(c16 + 4 * j) = u;
-          }
+        if (p.residual) {
+          const float4 rr = *reinterpret_cast<const float4*>(trow + 4 * j);
+          v[4 * j] += rr.x; v[4 * j + 1] += rr.y; v[4 * j + 2] += rr.z; v[4 * j + 3] += rr.w;
         }
       }
-    } else
-#pragma unroll 1
-    for (int c = 0; c < GN / 32; ++c) {
-      uint32_t r[32];
-      if (n_k > 0) {
-        tmem_ld32(tmem_d + ((uint32_t)(quarter * 32) << 16) + c * 32, r);
-        tmem_ld_wait();
-      } else {
+    }
+    if (p.gamma) {  // LayerNorm over the N == 128 row (post-norm encoder layer: LN(residual + A W^T + b))
+      float sum = 0.f;
 #pragma unroll
-        for (int j = 0; j < 32; ++j) r[j] = 0;
+      for (int j = 0; j < 32; ++j) sum += v[j];
+      red[cg * 128 + row_l] = sum;
+      __syncthreads();
+      const float mean = ((red[row_l] + red[128 + row_l]) + (red[256 + row_l] + red[384 + row_l])) * (1.f / GN);
+      float var = 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        v[j] -= mean;
+        var = fmaf(v[j], v[j], var);
       }
-      if (m >= p.M) continue;
-      const int nb = n0 + c * 32;
-      if (nb >= p.N) continue;
-      float v[32];
+      red[512 + cg * 128 + row_l] = var;
+      __syncthreads();
+      const float rstd = rsqrtf(((red[512 + row_l] + red[640 + row_l]) + (red[768 + row_l] + red[896 + row_l])) * (1.f / GN) + 1e-5f);
+      const bool zero = row_ok && p.zero_rows && p.zero_rows[m];
+      const float4* g4 = reinterpret_cast<const float4*>(s_bias + GN + cg * 32);
+      const float4* e4 = reinterpret_cast<const float4*>(s_bias + 2 * GN + cg * 32);
 #pragma unroll
-      for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-      if (!split) {
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          const int n = nb + j;
-          if (n < p.N) {
-            if (p.bias) v[j] += p.bias[n];
-            if (p.act == OCV_ACT_RELU) v[j] = fmaxf(v[j], 0.f);
-            else if (p.act == OCV_ACT_LEAKY_RELU) v[j] = v[j] > 0.f ? v[j] : 0.01f * v[j];
-            if (p.residual) v[j] += p.residual[(long long)m * p.ldr + n];
-          }
-        }
+      for (int j = 0; j < 8; ++j) {
+        const float4 g = g4[j], e = e4[j];
+        v[4 * j] = zero ? 0.f : v[4 * j] * rstd * g.x + e.x;
+        v[4 * j + 1] = zero ? 0.f : v[4 * j + 1] * rstd * g.y + e.y;
+        v[4 * j + 2] = zero ? 0.f : v[4 * j + 2] * rstd * g.z + e.z;
+        v[4 * j + 3] = zero ? 0.f : v[4 * j + 3] * rstd * g.w + e.w;
       }
-      const bool full_chunk = (nb + 32 <= p.N);
-      if (split || !p.c_is_bf16) {
-        float* crow = static_cast<float*>(p.C) + (split ? (long long)blockIdx.z * p.M * p.ldc : 0) +
-                      (long long)m * p.ldc + nb;
-        if (full_chunk && (p.ldc % 4 == 0)) {
+    }
+    // results -> staging tile (each thread overwrites exactly the residual elements it consumed), then coalesced rows out
 #pragma unroll
-          for (int j = 0; j < 32; j += 4)
-            *reinterpret_cast<float4*>(crow + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+    for (int j = 0; j < 8; ++j)
+      *reinterpret_cast<float4*>(trow + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    __syncthreads();
+    float* c32 = nullptr;
+    __nv_bfloat16* c16 = nullptr;
+    int ld32 = p.ldc, ld16 = p.ldc16;
+    if (split) c32 = static_cast<float*>(p.C) + (long long)blockIdx.z * p.M * p.ldc;
+    else {
+      if (p.C && !p.c_is_bf16) c32 = static_cast<float*>(p.C);
+      if (p.C && p.c_is_bf16) { c16 = static_cast<__nv_bfloat16*>(p.C); ld16 = p.ldc; }
+      else if (p.C16) c16 = p.C16;
+    }
+    const bool v32 = c32 && (ld32 & 3) == 0 && (reinterpret_cast<uintptr_t>(c32) & 15) == 0;
+    const bool v16 = c16 && (ld16 & 3) == 0 && (reinterpret_cast<uintptr_t>(c16) & 7) == 0;
+    for (int i = threadIdx.x; i < GM * 32; i += 512) {
+      const int rr = i >> 5, c = (i & 31) * 4;
+      const int mm = m0 + rr, n = n0 + c;
+      if (mm >= p.M || n >= p.N) continue;
+      const float4 o = *reinterpret_cast<const float4*>(tile + rr * TP + c);
+      if (c32) {
+        float* d = c32 + (long long)mm * ld32 + n;
+        if (v32) *reinterpret_cast<float4*>(d) = o;
+        else { d[0] = o.x; d[1] = o.y; d[2] = o.z; d[3] = o.w; }
+      }
+      if (c16) {
+        __nv_bfloat16* d = c16 + (long long)mm * ld16 + n;
+        if (v16) {
+          __nv_bfloat162 h0 = __floats2bfloat162_rn(o.x, o.y), h1 = __floats2bfloat162_rn(o.z, o.w);
+          uint2 u;
+          u.x = *reinterpret_cast<uint32_t*>(&h0);
+          u.y = *reinterpret_cast<uint32_t*>(&h1);
+          *reinterpret_cast<uint2*>(d) = u;
         } else {
-          for (int j = 0; j < 32; ++j)
-            if (nb + j < p.N) crow[j] = v[j];
-        }
-        if (!split && p.C16) {  // second output: bf16 copy for the next GEMM's A operand
-          __nv_bfloat16* hrow = p.C16 + (long long)m * p.ldc16 + nb;
-          for (int j = 0; j < 32; ++j)
-            if (nb + j < p.N) hrow[j] = __float2bfloat16(v[j]);
-        }
-      } else {
-        __nv_bfloat16* crow = static_cast<__nv_bfloat16*>(p.C) + (long long)m * p.ldc + nb;
-        if (full_chunk && (p.ldc % 8 == 0)) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            uint4 u;
-            __nv_bfloat162 h0 = __floats2bfloat162_rn(v[j], v[j + 1]), h1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
-            __nv_bfloat162 h2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]), h3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
-            u.x = *reinterpret_cast<uint32_t*>(&h0);
-            u.y = *reinterpret_cast<uint32_t*>(&h1);
-            u.z = *reinterpret_cast<uint32_t*>(&h2);
-            u.w = *reinterpret_cast<uint32_t*>(&h3);
-            *reinterpret_cast<uint4*>(crow + j) = u;
-          }
-        } else {
-          for (int j = 0; j < 32; ++j)
-            if (nb + j < p.N) crow[j] = __float2bfloat16(v[j]);
+          d[0] = __float2bfloat16(o.x); d[1] = __float2bfloat16(o.y); d[2] = __float2bfloat16(o.z); d[3] = __float2bfloat16(o.w);
         }
       }
     }
@@ -266,6 +299,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 __global__ void gemm_splitk_reduce_kernel(const float* __restrict__ part, const float* __restrict__ bias,
                                           const float* __restrict__ residual, void* __restrict__ out, int M, int N,
                                           int ldc, int splits, int act, int c_is_bf16) {
+  pdl_launch();
+  pdl_wait();
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long long)M * N) return;
   const int m = (int)(i / N), n = (int)(i - (long long)m * N);
@@ -295,7 +330,8 @@ extern "C" int ocv_gemm_bf16_ex(const void* A, const void* Wt, const float* bias
                                 void* stream) {
   OCV_CHECK_ARG(A && Wt && (C32 || C16) && M > 0 && N > 0 && K > 0);
   OCV_CHECK_ARG((ln_gamma == nullptr) == (ln_beta == nullptr));
-  OCV_CHECK_SHAPE(K % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0);
+  OCV_CHECK_SHAPE(K % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0 && N % 4 == 0);
+  OCV_CHECK_ALIGN((reinterpret_cast<uintptr_t>(bias) & 15) == 0);
   if (ln_gamma) {
     OCV_CHECK_SHAPE(N == GN && act == OCV_ACT_NONE);
     OCV_CHECK_ALIGN((!C32 || ldc32 % 4 == 0) && (!C16 || ldc16 % 4 == 0) && (!residual || ldr % 4 == 0));
@@ -321,7 +357,8 @@ extern "C" int ocv_gemm_bf16(const void* A, const void* Wt, const float* bias, c
                              int N, int K, int lda, int ldb, int ldc, int act, int c_is_bf16, int split_k,
                              void* workspace, void* stream) {
   OCV_CHECK_ARG(A && Wt && C && M > 0 && N > 0 && K > 0);
-  OCV_CHECK_SHAPE(K % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0);
+  OCV_CHECK_SHAPE(K % 8 == 0 && lda % 8 == 0 && ldb % 8 == 0 && N % 4 == 0);
+  OCV_CHECK_ALIGN((reinterpret_cast<uintptr_t>(bias) & 15) == 0);
   if (split_k < 1) split_k = 1;
   OCV_CHECK_ARG(split_k == 1 || workspace);
   GemmParams p{};
@@ -354,14 +391,12 @@ static int gemm_launch(const void* A, const void* Wt, int M, int N, int K, int l
   } else {
     p.k_per_split = 0;
   }
-  gemm_bf16_kernel<<<grid, 256, GEMM_SMEM, ocv_stream(stream)>>>(tmA, tmB, p);
-  if (int s = ocv_launch_status()) return s;
+  if (int s = ocv_launch_pdl(gemm_bf16_kernel, grid, dim3(512), GEMM_SMEM, stream, tmA, tmB, p)) return s;
   if (split_k > 1) {
     const long long n = (long long)M * N;
-    gemm_splitk_reduce_kernel<<<(unsigned)ceil_div<long long>(n, 256), 256, 0, ocv_stream(stream)>>>(
-        static_cast<const float*>(workspace), p.bias, p.residual, C_final, M, N, ldc_final, split_k, p.act,
-        c_final_bf16);
-    return ocv_launch_status();
+    return ocv_launch_pdl(gemm_splitk_reduce_kernel, dim3((unsigned)ceil_div<long long>(n, 256)), dim3(256), 0, stream,
+                          static_cast<const float*>(workspace), p.bias, p.residual, C_final, M, N, ldc_final, split_k,
+                          p.act, c_final_bf16);
   }
   return OCV_OK;
 }

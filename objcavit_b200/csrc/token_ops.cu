@@ -104,6 +104,8 @@ __global__ void pad_objects_kernel(const float* __restrict__ src, const int32_t*
                                    const int32_t* __restrict__ mask_offsets, float* __restrict__ dst,
                                    uint8_t* __restrict__ mask, int L, int Nmax, int E, float pad_value, int left_pad,
                                    __nv_bfloat16* __restrict__ dst16) {
+  pdl_launch();
+  pdl_wait();
   const int b = blockIdx.y;
   const int row = blockIdx.x;  // 0..L-1
   const int beg = offsets[b], n = offsets[b + 1] - beg;
@@ -249,6 +251,8 @@ __global__ void bins_kernel(const float* __restrict__ y_raw, float* __restrict__
   __shared__ float sv[1024];
   __shared__ float red[32];
   __shared__ float bcast;
+  pdl_launch();
+  pdl_wait();
   const int b = blockIdx.x, tid = threadIdx.x;
   const float* yr = y_raw + (long long)b * K;
   const int warp = tid / 32, lane = tid % 32, nwarp = blockDim.x / 32;
@@ -342,10 +346,8 @@ int ocv_pad_objects_impl(const float* src, const int32_t* offsets, const int32_t
   OCV_CHECK_ARG(src && offsets && dst && B > 0 && L > 0 && E > 0);
   OCV_CHECK_SHAPE(Nmax > 0 && Nmax <= L && B <= 65535);
   if (int s = ocv_require_sm100()) return s;
-  pad_objects_kernel<<<dim3(L, B), 128, 0, ocv_stream(stream)>>>(src, offsets, mask_offsets, dst, mask, L, Nmax, E,
-                                                                pad_value, left_pad,
-                                                                static_cast<__nv_bfloat16*>(dst16));
-  return ocv_launch_status();
+  return ocv_launch_pdl(pad_objects_kernel, dim3(L, B), dim3(128), 0, stream, src, offsets, mask_offsets, dst, mask, L, Nmax,
+                        E, pad_value, left_pad, static_cast<__nv_bfloat16*>(dst16));
 }
 
 extern "C" int ocv_pad_objects_f32(const float* src, const int32_t* offsets, const int32_t* mask_offsets, float* dst,
@@ -388,6 +390,6 @@ extern "C" int ocv_bins_f32(const float* y_raw, float* widths_normed, float* edg
   OCV_CHECK_SHAPE(K > 0 && K <= 1024 && norm >= 0 && norm <= 3);
   OCV_CHECK_ARG(!(centres && !edges));
   if (int s = ocv_require_sm100()) return s;
-  bins_kernel<<<B, 256, 0, ocv_stream(stream)>>>(y_raw, widths_normed, edges, centres, K, norm, min_depth, max_depth);
-  return ocv_launch_status();
+  return ocv_launch_pdl(bins_kernel, dim3(B), dim3(256), 0, stream, y_raw, widths_normed, edges, centres, K, norm,
+                        min_depth, max_depth);
 }

@@ -31,6 +31,8 @@ __global__ void __launch_bounds__(MLP_THREADS)
 mlp_chain_kernel(MlpParams p) {
   __shared__ __align__(16) float buf[2][ROWS][MLP_MAXW];
   __shared__ float red[MLP_THREADS][ROWS];
+  pdl_launch();
+  pdl_wait();  // x (and the residual) may come from the previous kernel of the chain
   const int r0 = blockIdx.x * ROWS;
   const int in0 = p.dims[0];
   for (int i = threadIdx.x; i < ROWS * in0; i += MLP_THREADS) {
@@ -116,6 +118,8 @@ mlp_chain_kernel(MlpParams p) {
 }
 
 __global__ void cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+  pdl_launch();
+  pdl_wait();
   const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
   if (i + 3 < n) {
     const float4 v = *reinterpret_cast<const float4*>(src + i);
@@ -150,16 +154,14 @@ extern "C" int ocv_mlp_f32(const float* x, long long x_ld, int R, int n_layers, 
   p.n_layers = n_layers; p.x = x; p.x_ld = x_ld; p.residual = residual; p.out32 = out32;
   p.out16 = static_cast<__nv_bfloat16*>(out16); p.R = R;
   // few rows (the regressor: one row per image): one row per CTA so that every image gets its own SM
-  if (R <= 64) mlp_chain_kernel<1><<<R, MLP_THREADS, 0, ocv_stream(stream)>>>(p);
-  else mlp_chain_kernel<4><<<ceil_div(R, 4), MLP_THREADS, 0, ocv_stream(stream)>>>(p);
-  return ocv_launch_status();
+  if (R <= 64) return ocv_launch_pdl(mlp_chain_kernel<1>, dim3(R), dim3(MLP_THREADS), 0, stream, p);
+  return ocv_launch_pdl(mlp_chain_kernel<4>, dim3(ceil_div(R, 4)), dim3(MLP_THREADS), 0, stream, p);
 }
 
 extern "C" int ocv_cast_f32_to_bf16(const float* src, void* dst, long long n, void* stream) {
   OCV_CHECK_ARG(src && dst && n > 0);
   OCV_CHECK_ALIGN((reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 7) == 0);
   if (int s = ocv_require_sm100()) return s;
-  cast_bf16_kernel<<<(unsigned)ceil_div<long long>(ceil_div<long long>(n, 4), 256), 256, 0, ocv_stream(stream)>>>(
-      src, static_cast<__nv_bfloat16*>(dst), n);
-  return ocv_launch_status();
+  return ocv_launch_pdl(cast_bf16_kernel, dim3((unsigned)ceil_div<long long>(ceil_div<long long>(n, 4), 256)), dim3(256), 0,
+                        stream, src, static_cast<__nv_bfloat16*>(dst), n);
 }
