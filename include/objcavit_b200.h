@@ -178,6 +178,12 @@ int ocv_patch_embed_bf16(const void* X_nhwc_bf16, const void* Wp, const float* b
 int ocv_mlp_f32(const float* x, long long x_ld, int R, int n_layers, const float* const* weights_host,
                 const float* const* biases_host, const int* dims_host, const float* residual, float* out32,
                 void* out16, void* stream);
+/* Same chain for FEW rows (R ~ batch size: the regressor): one launch per layer, output neurons spread over the grid so each
+ * weight is read once.  Every dims[l] % 4 == 0 and <= 512 for l < n_layers; x 16-byte aligned, x_ld % 4 == 0.
+ * workspace: ocv_mlp_rows_f32_workspace() bytes (ping-pong activations). */
+long long ocv_mlp_rows_f32_workspace(int R, int n_layers, const int* dims_host);
+int ocv_mlp_rows_f32(const float* x, long long x_ld, int R, int n_layers, const float* const* weights_host,
+                     const float* const* biases_host, const int* dims_host, float* out32, void* workspace, void* stream);
 int ocv_cast_f32_to_bf16(const float* src, void* dst_bf16, long long n, void* stream);
 
 /* Extended epilogue of the same kernel (the bf16 token path):

@@ -67,20 +67,29 @@ mha_bf16_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __rest
   const __nv_bfloat16* qb = q + b * q_bs + hd * D;
   const __nv_bfloat16* kb = k + b * k_bs + hd * D;
   const __nv_bfloat16* vb = v + b * v_bs + hd * D;
-  load_tile(Qs, qb, q0, Sq, q_rs);
-#pragma unroll 4
-  for (int i = threadIdx.x; i < Skp * 4; i += 128) {  // independent 16-byte loads: several in flight per thread
+  // cp.async (LDGSTS): every 16-byte piece of Q, K and V is in flight at once, no staging registers
+  auto cp16 = [](void* dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+  };
+  for (int i = threadIdx.x; i < QT * 4; i += 128) {
     const int r = i >> 2, c = (i & 3) * 8;
-    uint4 kv = make_uint4(0, 0, 0, 0), vv = make_uint4(0, 0, 0, 0);
-    if (r < Sk) {
-      kv = *reinterpret_cast<const uint4*>(kb + (long long)r * k_rs + c);
-      vv = *reinterpret_cast<const uint4*>(vb + (long long)r * v_rs + c);
-    }
-    *reinterpret_cast<uint4*>(&Kall[r][c]) = kv;
-    *reinterpret_cast<uint4*>(&Vall[r][c]) = vv;
+    if (q0 + r < Sq) cp16(&Qs[r][c], qb + (long long)(q0 + r) * q_rs + c);
+    else *reinterpret_cast<uint4*>(&Qs[r][c]) = make_uint4(0, 0, 0, 0);
   }
+  for (int i = threadIdx.x; i < Skp * 4; i += 128) {
+    const int r = i >> 2, c = (i & 3) * 8;
+    if (r < Sk) {
+      cp16(&Kall[r][c], kb + (long long)r * k_rs + c);
+      cp16(&Vall[r][c], vb + (long long)r * v_rs + c);
+    } else {
+      *reinterpret_cast<uint4*>(&Kall[r][c]) = make_uint4(0, 0, 0, 0);
+      *reinterpret_cast<uint4*>(&Vall[r][c]) = make_uint4(0, 0, 0, 0);
+    }
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
   for (int j = threadIdx.x; j < Skp; j += blockDim.x)
     Mall[j] = (j >= Sk || (mask && mask[(long long)b * Sk + j])) ? 1.f : 0.f;
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
   __syncthreads();
   uint32_t qa[2][4];
   {

@@ -63,7 +63,7 @@ struct Scratch {
 
 struct Workspace {
   Scratch img, obj;
-  float *obj_pos, *obj_tok, *pad32, *obj_s32, *y_raw, *centres, *blog, *pe_ws, *pts;
+  float *obj_pos, *obj_tok, *pad32, *obj_s32, *y_raw, *centres, *blog, *pe_ws, *pts, *reg_ws;
   bf16 *feat16, *pad16, *obj_s16, *Mb;
   uint8_t *mask, *kpm;
   int32_t* uni;
@@ -217,6 +217,7 @@ Workspace carve(const ocv_head* H, void* base, int B, int h, int w, int total, i
   W.centres = a.take<float>((size_t)B * 256);
   W.blog = a.take<float>((size_t)B * 256);
   W.Mb = a.take<bf16>((size_t)B * 256 * E);
+  W.reg_ws = a.take<float>((size_t)2 * B * 256);
   W.pe_ws = a.take<float>((size_t)ocv_patch_embed_bf16_workspace(B, h, w, P) / 4 + 4);
   if (H->cfg.kind == 1) {
     const size_t Mo = (size_t)B * n_max;
@@ -513,7 +514,14 @@ extern "C" int ocv_head_forward(ocv_head* H, const void* X, const float* obj_fea
   const float* tok = W.img.x32[cur];
   {
     const int dims[4] = {E, 256, 256, H->cfg.n_bins};
-    mlp(c, pre + "regressor.", MLP_REG_IDX, 3, dims, tok, (long long)S * E, B, nullptr, W.y_raw, s0);
+    const float* Ws[3];
+    const float* bs[3];
+    for (int i = 0; i < 3; ++i) {
+      Ws[i] = H->f32(pre + "regressor." + std::to_string(MLP_REG_IDX[i]) + ".weight");
+      bs[i] = H->f32(pre + "regressor." + std::to_string(MLP_REG_IDX[i]) + ".bias");
+      if (!Ws[i] || !bs[i]) return OCV_E_ARG;
+    }
+    c.run(ocv_mlp_rows_f32(tok, (long long)S * E, B, 3, Ws, bs, dims, W.y_raw, W.reg_ws, s0), 3);
   }
   c.run(ocv_bins_f32(W.y_raw, W.blog /*normalised widths: scratch, overwritten below*/, bin_edges, W.centres, B, H->cfg.n_bins,
                      OCV_NORM_LINEAR, H->cfg.min_depth, H->cfg.max_depth, s0));

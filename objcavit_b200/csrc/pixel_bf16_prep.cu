@@ -48,29 +48,51 @@ __global__ void pack_conv3x3_kernel(const float* __restrict__ W, __nv_bfloat16* 
 }
 
 // Mb[b,k,c] = sum_q Wout[k,q] * Q[b,q,c];  blog[b,k] = bout[k] + sum_c Mb[b,k,c] * b3[c]
-// block: 8 bins of one image, thread = channel c (E <= 1024 threads... E == blockDim.x)
-constexpr int FQ_BINS = 8;
+// block = FQ_BINS bins of one image, thread = channel c (E == blockDim.x).  The image's whole query block Q[b] (Q x E fp32)
+// and the FQ_BINS rows of Wout are staged in shared memory with cp.async — every byte in flight at once: the stage is
+// latency-bound (a 256x128x128 GEMM per image), so one memory round trip per CTA instead of one per query row.
+constexpr int FQ_BINS = 32;
 __global__ void fold_queries_kernel(const float* __restrict__ Wout, const float* __restrict__ bout,
                                     const float* __restrict__ queries, long long q_bs, int q_rs,
                                     const float* __restrict__ b3, float scale, __nv_bfloat16* __restrict__ Mb,
                                     float* __restrict__ blog, int K, int Q, int E) {
-  extern __shared__ float ws[];  // [FQ_BINS][Q] then [FQ_BINS][nwarp]
+  extern __shared__ __align__(16) float fq_smem[];
+  float* ws = fq_smem;                 // [FQ_BINS][Q]
+  float* qs = ws + FQ_BINS * Q;        // [Q][E]
+  float* red = qs + (size_t)Q * E;     // [FQ_BINS][nwarp]
   pdl_launch();
   const int b = blockIdx.y, k0 = blockIdx.x * FQ_BINS, c = threadIdx.x;
-  for (int i = threadIdx.x; i < FQ_BINS * Q; i += blockDim.x) {  // conv_out weights: independent of the chain
-    const int kk = i / Q, q = i % Q;
-    ws[i] = (k0 + kk < K) ? Wout[(long long)(k0 + kk) * Q + q] : 0.f;
+  auto cp16 = [](void* dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(dst)), "l"(src) : "memory");
+  };
+  for (int i = threadIdx.x; i < FQ_BINS * Q / 4; i += blockDim.x) {  // conv_out weights: independent of the chain
+    const int kk = (i * 4) / Q, q = (i * 4) % Q;
+    if (k0 + kk < K) cp16(ws + i * 4, Wout + (long long)(k0 + kk) * Q + q);
+    else *reinterpret_cast<float4*>(ws + i * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   pdl_wait();  // the queries are the previous kernels' tokens
-  __syncthreads();
-  float acc[FQ_BINS] = {};
   const float* qb = queries + b * q_bs;
-  for (int q = 0; q < Q; ++q) {
-    const float qv = qb[(long long)q * q_rs + c];
-#pragma unroll
-    for (int i = 0; i < FQ_BINS; ++i) acc[i] = fmaf(ws[i * Q + q], qv, acc[i]);
+  for (int i = threadIdx.x; i < Q * E / 4; i += blockDim.x) {
+    const int q = (i * 4) / E, e = (i * 4) % E;
+    cp16(qs + i * 4, qb + (long long)q * q_rs + e);
   }
-  float* red = ws + FQ_BINS * Q;
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncthreads();
+  float acc[FQ_BINS];
+#pragma unroll
+  for (int i = 0; i < FQ_BINS; ++i) acc[i] = 0.f;
+  for (int q = 0; q < Q; q += 4) {
+    const float q0 = qs[(q + 0) * E + c], q1 = qs[(q + 1) * E + c], q2 = qs[(q + 2) * E + c], q3 = qs[(q + 3) * E + c];
+#pragma unroll
+    for (int i = 0; i < FQ_BINS; ++i) {
+      const float4 w = *reinterpret_cast<const float4*>(ws + i * Q + q);  // broadcast
+      acc[i] = fmaf(w.x, q0, acc[i]);
+      acc[i] = fmaf(w.y, q1, acc[i]);
+      acc[i] = fmaf(w.z, q2, acc[i]);
+      acc[i] = fmaf(w.w, q3, acc[i]);
+    }
+  }
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32, nwarp = blockDim.x / 32;
   const float bc = b3 ? b3[c] : 0.f;
 #pragma unroll
@@ -116,9 +138,18 @@ extern "C" int ocv_fold_queries_bf16(const float* Wout, const float* bout, const
                                      int q_rstride, const float* b3, float logit_scale, void* Mb, float* blog, int B, int K,
                                      int Q, int E, void* stream) {
   OCV_CHECK_ARG(Wout && queries && Mb && blog && B > 0 && K > 0 && Q > 0);
-  OCV_CHECK_SHAPE(E % 32 == 0 && E >= 32 && E <= 1024 && B <= 65535);
+  OCV_CHECK_SHAPE(E % 32 == 0 && E >= 32 && E <= 1024 && B <= 65535 && Q % 4 == 0);
+  OCV_CHECK_ALIGN(((reinterpret_cast<uintptr_t>(Wout) | reinterpret_cast<uintptr_t>(queries)) & 15) == 0 &&
+                  (q_bstride % 4) == 0 && (q_rstride % 4) == 0);
   if (int s = ocv_require_sm100()) return s;
-  const size_t smem = (FQ_BINS * Q + FQ_BINS * (E / 32)) * sizeof(float);
+  const size_t smem = ((size_t)FQ_BINS * Q + (size_t)Q * E + FQ_BINS * (E / 32)) * sizeof(float);
+  OCV_CHECK_SHAPE(smem <= 200 * 1024);
+  static size_t smem_set = 0;
+  if (smem > 48 * 1024 && smem > smem_set) {
+    cudaError_t e = cudaFuncSetAttribute(fold_queries_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    smem_set = smem;
+  }
   return ocv_launch_pdl(fold_queries_kernel, dim3(ceil_div(K, FQ_BINS), B), dim3(E), smem, stream, Wout, bout, queries,
                         q_bstride, q_rstride, b3, logit_scale, static_cast<__nv_bfloat16*>(Mb), blog, K, Q, E);
 }

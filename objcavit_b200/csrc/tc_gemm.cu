@@ -115,11 +115,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp >= 2 && p.residual && !split) {
     // residual tile -> shared memory with coalesced 128-bit loads while the main loop runs (warps 2..15 are idle)
     const bool vec = (p.ldr & 3) == 0 && (reinterpret_cast<uintptr_t>(p.residual) & 15) == 0;
-    for (int i = threadIdx.x - 64; i < GM * 32; i += 448) {
+    // all loads of a thread are issued before the first store (one L2 round trip, not ten)
+    float4 rv[10];
+#pragma unroll
+    for (int t = 0; t < 10; ++t) {
+      const int i = threadIdx.x - 64 + t * 448;
       const int r = i >> 5, c = (i & 31) * 4;
       const int m = m0 + r, n = n0 + c;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (m < p.M && n < p.N) {
+      if (i < GM * 32 && m < p.M && n < p.N) {
         const float* src = p.residual + (long long)m * p.ldr + n;
         if (vec && n + 3 < p.N) v = __ldg(reinterpret_cast<const float4*>(src));
         else {
@@ -129,7 +133,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (n + 3 < p.N) v.w = src[3];
         }
       }
-      *reinterpret_cast<float4*>(tile + r * TP + c) = v;
+      rv[t] = v;
+    }
+#pragma unroll
+    for (int t = 0; t < 10; ++t) {
+      const int i = threadIdx.x - 64 + t * 448;
+      if (i < GM * 32) *reinterpret_cast<float4*>(tile + (i >> 5) * TP + (i & 31) * 4) = rv[t];
     }
   }
   if (warp == 0) {

@@ -117,6 +117,64 @@ mlp_chain_kernel(MlpParams p) {
   }
 }
 
+// One Linear (+ LeakyReLU) layer for FEW rows (the bin-width regressor: one row per image).  The chain kernel above makes
+// every CTA stream all the weights; here the output neurons are spread over the grid instead (8 per CTA, one warp each, lanes
+// split K), so each weight is read once chip-wide, and the layers are separate PDL-chained launches.  The warp's weight row
+// is fetched before the grid dependency resolves.
+constexpr int MLPL_ROWS = 16, MLPL_MAXK = 512;
+__global__ void __launch_bounds__(256)
+mlp_layer_kernel(const float* __restrict__ x, long long x_ld, const float* __restrict__ W, const float* __restrict__ bias,
+                 float* __restrict__ out, int out_ld, int R, int K, int N, int leaky) {
+  __shared__ __align__(16) float xs[MLPL_ROWS][MLPL_MAXK];
+  pdl_launch();
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int n = blockIdx.x * 8 + warp;
+  const int r0 = blockIdx.y * MLPL_ROWS;
+  float4 w[MLPL_MAXK / 128];
+#pragma unroll
+  for (int j = 0; j < MLPL_MAXK / 128; ++j) {
+    const int k = (lane + 32 * j) * 4;
+    w[j] = (n < N && k < K) ? __ldg(reinterpret_cast<const float4*>(W + (long long)n * K + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  const float bv = (bias && n < N) ? __ldg(bias + n) : 0.f;
+  pdl_wait();
+  for (int i = threadIdx.x; i < MLPL_ROWS * (K / 4); i += 256) {
+    const int r = i / (K / 4), k = (i - r * (K / 4)) * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r0 + r < R) v = *reinterpret_cast<const float4*>(x + (long long)(r0 + r) * x_ld + k);
+    *reinterpret_cast<float4*>(&xs[r][k]) = v;
+  }
+  __syncthreads();
+  float acc[MLPL_ROWS];
+#pragma unroll
+  for (int r = 0; r < MLPL_ROWS; ++r) acc[r] = 0.f;
+#pragma unroll
+  for (int j = 0; j < MLPL_MAXK / 128; ++j) {
+    const int k = (lane + 32 * j) * 4;
+    if (k < K) {
+#pragma unroll
+      for (int r = 0; r < MLPL_ROWS; ++r) {
+        const float4 a = *reinterpret_cast<const float4*>(&xs[r][k]);
+        acc[r] = fmaf(w[j].x, a.x, acc[r]);
+        acc[r] = fmaf(w[j].y, a.y, acc[r]);
+        acc[r] = fmaf(w[j].z, a.z, acc[r]);
+        acc[r] = fmaf(w[j].w, a.w, acc[r]);
+      }
+    }
+  }
+  float mine = 0.f;
+#pragma unroll
+  for (int r = 0; r < MLPL_ROWS; ++r) {
+    const float v = warp_sum(acc[r]);
+    if (lane == r) mine = v;
+  }
+  if (lane < MLPL_ROWS && r0 + lane < R && n < N) {
+    float v = mine + bv;
+    if (leaky) v = v > 0.f ? v : 0.01f * v;
+    out[(long long)(r0 + lane) * out_ld + n] = v;
+  }
+}
+
 __global__ void cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
   pdl_launch();
   pdl_wait();
@@ -164,4 +222,40 @@ extern "C" int ocv_cast_f32_to_bf16(const float* src, void* dst, long long n, vo
   if (int s = ocv_require_sm100()) return s;
   return ocv_launch_pdl(cast_bf16_kernel, dim3((unsigned)ceil_div<long long>(ceil_div<long long>(n, 4), 256)), dim3(256), 0,
                         stream, src, static_cast<__nv_bfloat16*>(dst), n);
+}
+
+extern "C" long long ocv_mlp_rows_f32_workspace(int R, int n_layers, const int* dims) {
+  if (R <= 0 || n_layers < 1 || !dims) return 0;
+  int mx = 0;
+  for (int l = 1; l < n_layers; ++l) mx = dims[l] > mx ? dims[l] : mx;
+  return 2ll * R * mx * (long long)sizeof(float);
+}
+
+extern "C" int ocv_mlp_rows_f32(const float* x, long long x_ld, int R, int n_layers, const float* const* weights,
+                                const float* const* biases, const int* dims, float* out32, void* workspace, void* stream) {
+  OCV_CHECK_ARG(x && weights && biases && dims && out32 && R > 0 && (n_layers == 1 || workspace));
+  OCV_CHECK_SHAPE(n_layers >= 1 && n_layers <= MLP_MAXL);
+  for (int l = 0; l < n_layers; ++l) {
+    OCV_CHECK_SHAPE(dims[l] > 0 && dims[l] <= MLPL_MAXK && dims[l] % 4 == 0 && dims[l + 1] > 0);
+    OCV_CHECK_ARG(weights[l] != nullptr);
+    OCV_CHECK_ALIGN((reinterpret_cast<uintptr_t>(weights[l]) & 15) == 0);
+  }
+  OCV_CHECK_ALIGN((reinterpret_cast<uintptr_t>(x) & 15) == 0 && x_ld % 4 == 0);
+  if (int s = ocv_require_sm100()) return s;
+  int mx = 0;
+  for (int l = 1; l < n_layers; ++l) mx = dims[l] > mx ? dims[l] : mx;
+  float* buf[2] = {static_cast<float*>(workspace), static_cast<float*>(workspace) + (size_t)R * mx};
+  const float* in = x;
+  long long in_ld = x_ld;
+  for (int l = 0; l < n_layers; ++l) {
+    const bool last = l == n_layers - 1;
+    float* o = last ? out32 : buf[l & 1];
+    const int N = dims[l + 1];
+    if (int s = ocv_launch_pdl(mlp_layer_kernel, dim3(ceil_div(N, 8), ceil_div(R, MLPL_ROWS)), dim3(256), 0, stream, in, in_ld,
+                               weights[l], biases[l], o, N, R, dims[l], N, last ? 0 : 1))
+      return s;
+    in = o;
+    in_ld = N;
+  }
+  return OCV_OK;
 }

@@ -482,3 +482,19 @@ class NativeHead:
             timed_events.append((e0, e1))
         launch_count += L.ocv_head_last_launches(self._h)
         return depth, edges
+
+
+def mlp_rows(x: torch.Tensor, weights, biases):
+    """Linear/LeakyReLU chain for few rows (the regressor), one launch per layer.  x [R,K0] fp32 (row stride % 4 == 0)."""
+    import ctypes as C
+    _chk(x, torch.float32, "x")
+    R, K0, ld = _row_major_2d(x, "x")
+    n = len(weights)
+    dims = [K0] + [int(w.shape[0]) for w in weights]
+    Wp = (C.c_void_p * n)(*[w.data_ptr() for w in weights])
+    Bp = (C.c_void_p * n)(*[(b.data_ptr() if b is not None else None) for b in biases])
+    Dp = (C.c_int * (n + 1))(*dims)
+    ws = torch.empty(max(_lib.lib().ocv_mlp_rows_f32_workspace(R, n, Dp), 4) // 4, device=x.device, dtype=torch.float32)
+    out = torch.empty(R, dims[-1], device=x.device, dtype=torch.float32)
+    _call("ocv_mlp_rows_f32", x.data_ptr(), ld, R, n, Wp, Bp, Dp, out.data_ptr(), ws.data_ptr(), _stream(), launches=n)
+    return out

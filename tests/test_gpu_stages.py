@@ -324,3 +324,20 @@ def test_mlp_chain(cuda):
     o32, o16 = ops.mlp(x.to(cuda)[:, :4], [w.to(cuda) for w in Ws], [b.to(cuda) for b in bs], residual=res.to(cuda),
                        want32=True, want16=True)
     assert rel_err(o32, want) < 1e-5 and torch.equal(o16.cpu(), o32.cpu().bfloat16())
+
+
+@pytest.mark.parametrize("R", [1, 16, 37])
+def test_mlp_rows_regressor(cuda, R):
+    """The per-layer few-rows MLP (bin-width regressor, miniViT.py:16-20) on a strided token-0 view."""
+    from objcavit_b200 import ops
+    dims = [128, 256, 256, 256]
+    Ws = [torch.randn(dims[i + 1], dims[i], generator=g(i)) / math.sqrt(dims[i]) for i in range(3)]
+    bs = [torch.randn(dims[i + 1], generator=g(10 + i)) * 0.1 for i in range(3)]
+    tok = torch.randn(R, 5, 128, generator=g(30))
+    want = tok[:, 0, :]
+    for i in range(3):
+        want = want @ Ws[i].T + bs[i]
+        if i < 2:
+            want = F.leaky_relu(want, 0.01)
+    out = ops.mlp_rows(tok.to(cuda)[:, 0, :], [w.to(cuda) for w in Ws], [b.to(cuda) for b in bs])
+    assert rel_err(out, want) < 1e-5
