@@ -213,6 +213,11 @@ int ocv_fold_queries_bf16(const float* Wout /*[K,Q]*/, const float* bout /*[K]*/
 int ocv_pixel_fused_bf16(const void* X, const void* W3p, const void* Mb, const float* blog, const float* centres,
                          float* depth, int B, int h, int w, int max_ctas, void* stream);
 
+/* Same kernel, additionally writing the bin with the largest logit per pixel (uint8 [B,h*w], first maximum): used by the
+ * parity tests for the north star's "identical bin argmax" criterion; not on the throughput path. */
+int ocv_pixel_fused_bf16_argmax(const void* X, const void* W3p, const void* Mb, const float* blog, const float* centres,
+                                float* depth, uint8_t* argmax_bin, int B, int h, int w, void* stream);
+
 /* ---- whole head, one call (native host-side sequencing) -------------------------------------------------
  * An ocv_head is a HOST-side plan: the head's configuration, the device pointers of its parameters keyed by the
  * reference's own state_dict names, and two non-blocking side streams used to run the object branch next to the image

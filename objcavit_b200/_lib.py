@@ -51,6 +51,7 @@ PROTOTYPES = {
     "ocv_pack_conv3x3_bf16": (i32, [p, p, p]),
     "ocv_fold_queries_bf16": (i32, [p, p, p, i64, i32, p, f32, p, p, i32, i32, i32, i32, p]),
     "ocv_pixel_fused_bf16": (i32, [p, p, p, p, p, p, i32, i32, i32, i32, p]),
+    "ocv_pixel_fused_bf16_argmax": (i32, [p, p, p, p, p, p, p, i32, i32, i32, p]),
     "ocv_head_create": (i32, [p, p]),
     "ocv_head_destroy": (None, [p]),
     "ocv_head_set_param": (i32, [p, C.c_char_p, p, i64]),

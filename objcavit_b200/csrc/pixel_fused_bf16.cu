@@ -46,7 +46,7 @@ constexpr int NS = 4;                  // slab ring slots
 constexpr int STG_BYTES = 2 * SLAB;    // bf16 conv tile as A operand: two K-halves
 constexpr int N_EPI = 256;             // epilogue threads (warps 4..11)
 constexpr int THREADS = 128 + N_EPI;
-constexpr int MERGE_BYTES = 2 * 3 * 128 * 4;
+constexpr int MERGE_BYTES = 2 * 5 * 128 * 4;
 constexpr int SMEM_BYTES = 2 * PLANE + NS * SLAB + 2 * STG_BYTES + MERGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 constexpr uint32_t TM_CONVA = 0, TM_CONVB = 128, TM_LOGITS = 256, TM_COLS = 512;
 
@@ -54,6 +54,7 @@ struct PixParams {
   const float* blog;     // [B,256]  log2e * (bout + Wout Q b3)
   const float* centres;  // [B,256]
   float* depth;          // [B,h*w]
+  uint8_t* argmax;       // [B,h*w] bin with the largest logit (ARGMAX instantiation only: the parity tests' bin-agreement check)
   int B, h, w, tiles_x, tiles_y, n_tiles;   // tiles = 16x16 pair blocks
 };
 
@@ -124,6 +125,7 @@ __device__ __forceinline__ TileCoord tile_coord(const PixParams& p, int t) {
   return {b, ty * TH, (r - ty * p.tiles_x) * PW};
 }
 
+template <bool ARGMAX>
 __global__ void __launch_bounds__(THREADS, 1)
 pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                    const __grid_constant__ CUtensorMap tmMb, PixParams p) {
@@ -329,7 +331,8 @@ pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
       const float4* ce = reinterpret_cast<const float4*>(p.centres + (long long)tc_.b * NB + half * 128);
       mbar_wait(log_full, job & 1);
       tc_fence_after();
-      float mx = -INFINITY;
+      float mx = -INFINITY, best = -INFINITY;
+      int bidx = 0;
       uint64_t s2a = 0, s2b = 0, a2a = 0, a2b = 0;   // two (sum, weighted sum) accumulator pairs: shorter dependency chains
       const uint32_t src = tmem + lane_base + TM_LOGITS + half * 128;
       uint32_t rb[2][32];
@@ -351,6 +354,13 @@ pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
           upk2(v2[2 * j4 + 1], x2, x3);
           cm = max3(cm, x0, x1);
           cm = max3(cm, x2, x3);
+          if (ARGMAX) {
+            const int col = half * 128 + c * 32 + 4 * j4;
+            if (x0 > best) { best = x0; bidx = col; }
+            if (x1 > best) { best = x1; bidx = col + 1; }
+            if (x2 > best) { best = x2; bidx = col + 2; }
+            if (x3 > best) { best = x3; bidx = col + 3; }
+          }
         }
         const float m_new = fmaxf(mx, cm);
         const float sc = ex2(mx - m_new);
@@ -382,11 +392,15 @@ pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
       tc_fence_before();
       mbar_arrive(log_empty);
       // merge the two bin halves of this pixel (upper half -> shared memory -> lower half)
-      float* mg = merge + (job & 1) * 3 * 128;
+      float* mg = merge + (job & 1) * 5 * 128;
       if (half == 1) {
         mg[m] = mx;
         mg[128 + m] = s;
         mg[256 + m] = a;
+        if (ARGMAX) {
+          mg[384 + m] = best;
+          mg[512 + m] = __int_as_float(bidx);
+        }
       }
       epi_bar();
       if (half == 0) {
@@ -395,7 +409,13 @@ pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
         const float f0 = ex2(mx - mm), f1 = ex2(mx1 - mm);
         const float st = s * f0 + s1 * f1, at = a * f0 + a1 * f1;
         const int y = tc_.y0 + ty, x = tc_.x0 + tile * TW + tx;
-        if (y < p.h && x < p.w) p.depth[((long long)tc_.b * p.h + y) * p.w + x] = at / st;
+        if (y < p.h && x < p.w) {
+          p.depth[((long long)tc_.b * p.h + y) * p.w + x] = at / st;
+          if (ARGMAX) {  // first maximum, like torch.argmax: the upper half wins only when strictly larger
+            const int win = mg[384 + m] > best ? __float_as_int(mg[512 + m]) : bidx;
+            p.argmax[((long long)tc_.b * p.h + y) * p.w + x] = (uint8_t)win;
+          }
+        }
       }
       ++job;
     };
@@ -431,9 +451,8 @@ int make_tmap_features(CUtensorMap* out, const void* X, int B, int h, int w) {
 
 }  // namespace
 
-extern "C" int ocv_pixel_fused_bf16(const void* X, const void* W3p, const void* Mb, const float* blog,
-                                    const float* centres, float* depth, int B, int h, int w, int max_ctas,
-                                    void* stream) {
+static int pixel_launch(const void* X, const void* W3p, const void* Mb, const float* blog, const float* centres, float* depth,
+                        uint8_t* argmax, int B, int h, int w, int max_ctas, void* stream) {
   OCV_CHECK_ARG(X && W3p && Mb && blog && centres && depth && B > 0 && h > 0 && w > 0);
   OCV_CHECK_ALIGN(((reinterpret_cast<uintptr_t>(blog) | reinterpret_cast<uintptr_t>(centres)) & 15) == 0);
   if (int s = ocv_require_sm100()) return s;
@@ -447,11 +466,12 @@ extern "C" int ocv_pixel_fused_bf16(const void* X, const void* W3p, const void* 
     cudaGetDevice(&dev);
     cudaError_t e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(pixel_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    e = cudaFuncSetAttribute(pixel_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(pixel_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) { n_sm = 0; return (int)e; }
   }
   PixParams p{};
-  p.blog = blog; p.centres = centres; p.depth = depth;
+  p.blog = blog; p.centres = centres; p.depth = depth; p.argmax = argmax;
   p.B = B; p.h = h; p.w = w;
   p.tiles_x = ceil_div(w, PW);
   p.tiles_y = ceil_div(h, TH);
@@ -461,5 +481,19 @@ extern "C" int ocv_pixel_fused_bf16(const void* X, const void* W3p, const void* 
   int grid = n_sm;
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (grid > p.n_tiles) grid = p.n_tiles;
-  return ocv_launch_pdl(pixel_fused_kernel, dim3(grid), dim3(THREADS), SMEM_BYTES, stream, tmX, tmW, tmMb, p);
+  if (argmax) return ocv_launch_pdl(pixel_fused_kernel<true>, dim3(grid), dim3(THREADS), SMEM_BYTES, stream, tmX, tmW, tmMb, p);
+  return ocv_launch_pdl(pixel_fused_kernel<false>, dim3(grid), dim3(THREADS), SMEM_BYTES, stream, tmX, tmW, tmMb, p);
+}
+
+extern "C" int ocv_pixel_fused_bf16(const void* X, const void* W3p, const void* Mb, const float* blog,
+                                    const float* centres, float* depth, int B, int h, int w, int max_ctas,
+                                    void* stream) {
+  return pixel_launch(X, W3p, Mb, blog, centres, depth, nullptr, B, h, w, max_ctas, stream);
+}
+
+extern "C" int ocv_pixel_fused_bf16_argmax(const void* X, const void* W3p, const void* Mb, const float* blog,
+                                           const float* centres, float* depth, uint8_t* argmax_bin, int B, int h, int w,
+                                           void* stream) {
+  OCV_CHECK_ARG(argmax_bin);
+  return pixel_launch(X, W3p, Mb, blog, centres, depth, argmax_bin, B, h, w, 0, stream);
 }

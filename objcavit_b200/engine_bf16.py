@@ -218,7 +218,7 @@ def head_forward(head, P, pre, x, object_features, object_xywh_list, lo, hi, mut
     return depth, edges
 
 
-def head_forward_staged(head, P, pre, x, object_features, object_xywh_list, lo, hi):
+def head_forward_staged(head, P, pre, x, object_features, object_xywh_list, lo, hi, want_argmax=False):
     """Same computation sequenced stage by stage from python (one C-ABI call per kernel): kept for the stage-level
     parity tests and for debugging; the module forward uses :func:`head_forward`."""
     x_nhwc = features_nhwc_bf16(x)
@@ -235,5 +235,8 @@ def head_forward_staged(head, P, pre, x, object_features, object_xywh_list, lo, 
     w3p = pk.get(P, "w3p", lambda P: ops.pack_conv3x3_bf16(P[pre + "conv3x3.weight"].contiguous()))
     Mb, blog = ops.fold_queries_bf16(P["conv_out.0.weight"], P["conv_out.0.bias"], tok[:, 1:129, :],
                                      P[pre + "conv3x3.bias"])
+    if want_argmax:  # parity tests: the bin with the largest logit per pixel (north star: "identical bin argmax")
+        depth, amax = ops.pixel_fused_bf16(x_nhwc, w3p, Mb, blog, centres, want_argmax=True)
+        return depth, edges, amax
     depth = ops.pixel_fused_bf16(x_nhwc, w3p, Mb, blog, centres)
     return depth, edges

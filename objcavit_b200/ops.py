@@ -290,7 +290,7 @@ def fold_queries_bf16(w_out: torch.Tensor, b_out, queries: torch.Tensor, b3, log
 
 
 def pixel_fused_bf16(x_nhwc: torch.Tensor, w3p: torch.Tensor, Mb: torch.Tensor, blog: torch.Tensor,
-                     centres: torch.Tensor, max_ctas: int = 0):
+                     centres: torch.Tensor, max_ctas: int = 0, want_argmax: bool = False):
     """depth [B,1,h,w] fp32 from NHWC bf16 features: conv3x3 -> logits -> softmax -> sum p*centre, one kernel."""
     _chk(x_nhwc, torch.bfloat16, "x_nhwc"); _chk(w3p, torch.bfloat16, "w3p"); _chk(Mb, torch.bfloat16, "Mb")
     _chk(blog, torch.float32, "blog"); _chk(centres, torch.float32, "centres")
@@ -299,6 +299,11 @@ def pixel_fused_bf16(x_nhwc: torch.Tensor, w3p: torch.Tensor, Mb: torch.Tensor, 
     assert tuple(Mb.shape) == (B, 256, 128) and tuple(blog.shape) == (B, 256) and tuple(centres.shape) == (B, 256)
     assert blog.is_contiguous() and centres.is_contiguous()
     depth = torch.empty(B, 1, h, w, device=x_nhwc.device, dtype=torch.float32)
+    if want_argmax:
+        amax = torch.empty(B, 1, h, w, device=x_nhwc.device, dtype=torch.uint8)
+        _call("ocv_pixel_fused_bf16_argmax", x_nhwc.data_ptr(), w3p.data_ptr(), Mb.data_ptr(), blog.data_ptr(),
+              centres.data_ptr(), depth.data_ptr(), amax.data_ptr(), B, h, w, _stream())
+        return depth, amax
     _call("ocv_pixel_fused_bf16", x_nhwc.data_ptr(), w3p.data_ptr(), Mb.data_ptr(), blog.data_ptr(),
           centres.data_ptr(), depth.data_ptr(), B, h, w, int(max_ctas), _stream())
     return depth
