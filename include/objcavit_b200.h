@@ -218,6 +218,26 @@ int ocv_pixel_fused_bf16(const void* X, const void* W3p, const void* Mb, const f
 int ocv_pixel_fused_bf16_argmax(const void* X, const void* W3p, const void* Mb, const float* blog, const float* centres,
                                 float* depth, uint8_t* argmax_bin, int B, int h, int w, void* stream);
 
+/* ---- training losses (config 5), forward + gradients w.r.t. the head outputs ---------------------------------------
+ * SILog: depth_pred [B,1,h,w] is up-sampled bilinearly (align_corners=True) to the GT size [B,1,H,W]; mask uint8 (1 = valid)
+ *   or NULL; loss[0] = alph * sqrt(sum g^2 / n - lam (sum g)^2 / n^2), g = log p - log t over valid pixels of the WHOLE batch.
+ *   ocv_silog_backward must follow ocv_silog_forward on the same workspace (it reuses the reduction statistics) and writes
+ *   grad_pred [B,1,h,w] = grad_scale * d loss / d depth_pred.  Deterministic (fixed-order reductions, gather adjoint).
+ * replaces: losses/SILogLoss.py:43-56 (and its autograd). */
+long long ocv_silog_workspace(int B, int H, int W);
+int ocv_silog_forward(const float* depth_pred, const float* depth_gt, const uint8_t* depth_mask, int B, int h, int w, int H, int W,
+                      float alph, float lam, float* loss, void* workspace, void* stream);
+int ocv_silog_backward(const float* depth_pred, const float* depth_gt, const uint8_t* depth_mask, int B, int h, int w, int H,
+                       int W, float alph, float lam, float grad_scale, float* grad_pred, void* workspace, void* stream);
+/* BinsChamfer: centres = mid-points of bin_edges [B,K+1]; targets = depth_gt[b][mask[b]] (HW values per image);
+ *   loss[0] = mean_b (1/K) sum_k min_t (c_k - t)^2 + mean_b (1/T_b) sum_t min_k (c_k - t)^2   (pytorch3d chamfer_distance
+ *   defaults: squared L2, point mean, batch mean, both directions);  grad_edges [B,K+1] (optional) = grad_scale * d loss / d bin_edges.
+ *   Centres must be ascending (they are: cumulative sums of positive widths).  Targets must be > 0.  Deterministic.
+ * replaces: losses/BinsChamferLoss.py:21-37 + pytorch3d.loss.chamfer_distance (third party, not vendored: parity unpinned). */
+long long ocv_bins_chamfer_workspace(int B, int K);
+int ocv_bins_chamfer(const float* bin_edges, const float* depth_gt, const uint8_t* depth_mask, int B, int K, long long HW,
+                     float grad_scale, float* loss, float* grad_edges, void* workspace, void* stream);
+
 /* ---- whole head, one call (native host-side sequencing) -------------------------------------------------
  * An ocv_head is a HOST-side plan: the head's configuration, the device pointers of its parameters keyed by the
  * reference's own state_dict names, and two non-blocking side streams used to run the object branch next to the image

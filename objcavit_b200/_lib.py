@@ -52,6 +52,11 @@ PROTOTYPES = {
     "ocv_fold_queries_bf16": (i32, [p, p, p, i64, i32, p, f32, p, p, i32, i32, i32, i32, p]),
     "ocv_pixel_fused_bf16": (i32, [p, p, p, p, p, p, i32, i32, i32, i32, p]),
     "ocv_pixel_fused_bf16_argmax": (i32, [p, p, p, p, p, p, p, i32, i32, i32, p]),
+    "ocv_silog_workspace": (i64, [i32, i32, i32]),
+    "ocv_silog_forward": (i32, [p, p, p, i32, i32, i32, i32, i32, f32, f32, p, p, p]),
+    "ocv_silog_backward": (i32, [p, p, p, i32, i32, i32, i32, i32, f32, f32, f32, p, p, p]),
+    "ocv_bins_chamfer_workspace": (i64, [i32, i32]),
+    "ocv_bins_chamfer": (i32, [p, p, p, i32, i32, i64, f32, p, p, p, p]),
     "ocv_head_create": (i32, [p, p]),
     "ocv_head_destroy": (None, [p]),
     "ocv_head_set_param": (i32, [p, C.c_char_p, p, i64]),

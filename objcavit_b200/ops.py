@@ -503,3 +503,50 @@ def mlp_rows(x: torch.Tensor, weights, biases):
     out = torch.empty(R, dims[-1], device=x.device, dtype=torch.float32)
     _call("ocv_mlp_rows_f32", x.data_ptr(), ld, R, n, Wp, Bp, Dp, out.data_ptr(), ws.data_ptr(), _stream(), launches=n)
     return out
+
+
+# ---- training losses (config 5) ---------------------------------------------------------------------
+
+def _mask_u8(mask):
+    if mask is None:
+        return None
+    if mask.dtype == torch.bool:
+        return mask.contiguous().view(torch.uint8)
+    _chk(mask, torch.uint8, "depth_mask")
+    return mask.contiguous()
+
+
+def silog(depth_pred: torch.Tensor, depth_gt: torch.Tensor, depth_mask=None, alph: float = 10.0, lam: float = 0.85,
+          want_grad: bool = False, grad_scale: float = 1.0):
+    """-> loss [1] (and grad w.r.t. depth_pred when ``want_grad``)."""
+    _chk(depth_pred, torch.float32, "depth_pred"); _chk(depth_gt, torch.float32, "depth_gt")
+    assert depth_pred.is_contiguous() and depth_gt.is_contiguous()
+    B, _, h, w = depth_pred.shape
+    _, _, H, W = depth_gt.shape
+    m = _mask_u8(depth_mask)
+    ws = torch.empty(_lib.lib().ocv_silog_workspace(B, H, W), device=depth_pred.device, dtype=torch.uint8)
+    loss = torch.empty(1, device=depth_pred.device, dtype=torch.float32)
+    _call("ocv_silog_forward", depth_pred.data_ptr(), depth_gt.data_ptr(), _ptr(m), B, h, w, H, W, float(alph), float(lam),
+          loss.data_ptr(), ws.data_ptr(), _stream(), launches=2)
+    if not want_grad:
+        return loss
+    grad = torch.empty_like(depth_pred)
+    _call("ocv_silog_backward", depth_pred.data_ptr(), depth_gt.data_ptr(), _ptr(m), B, h, w, H, W, float(alph), float(lam),
+          float(grad_scale), grad.data_ptr(), ws.data_ptr(), _stream(), launches=2)
+    return loss, grad
+
+
+def bins_chamfer(bin_edges: torch.Tensor, depth_gt: torch.Tensor, depth_mask=None, want_grad: bool = False,
+                 grad_scale: float = 1.0):
+    """-> loss [1] (and grad w.r.t. bin_edges when ``want_grad``)."""
+    _chk(bin_edges, torch.float32, "bin_edges"); _chk(depth_gt, torch.float32, "depth_gt")
+    assert bin_edges.is_contiguous() and depth_gt.is_contiguous()
+    B, K1 = bin_edges.shape
+    HW = depth_gt.numel() // B
+    m = _mask_u8(depth_mask)
+    ws = torch.empty(_lib.lib().ocv_bins_chamfer_workspace(B, K1 - 1), device=bin_edges.device, dtype=torch.uint8)
+    loss = torch.empty(1, device=bin_edges.device, dtype=torch.float32)
+    grad = torch.empty_like(bin_edges) if want_grad else None
+    _call("ocv_bins_chamfer", bin_edges.data_ptr(), depth_gt.data_ptr(), _ptr(m), B, K1 - 1, HW, float(grad_scale),
+          loss.data_ptr(), _ptr(grad), ws.data_ptr(), _stream(), launches=3)
+    return (loss, grad) if want_grad else loss
