@@ -265,11 +265,17 @@ def main():
                 "head_frac_of_roofline": (GF_HEAD * B * K / ms) / pk["tf_sust"]}
 
     # ---- end to end through the public module API with HOST buffers ----------------------------------
+    pipe = None
+    if precision == "bf16":
+        from objcavit_b200.modules import HostPipeline
+        pipe = HostPipeline(head, chunks=4)   # chunked H2D / compute / D2H overlap (the public host-buffer entry point)
+        depth_host = torch.empty(B, 1, H, W, dtype=torch.float32).pin_memory()
+        edges_host = torch.empty(B, 257, dtype=torch.float32).pin_memory()
+
     def e2e_step():
-        if precision == "bf16":
-            x = x_host.to(dev, non_blocking=True).permute(0, 3, 1, 2)
-        else:
-            x = x_host.to(dev, non_blocking=True)
+        if pipe is not None:
+            return pipe(x_host, objs_host, boxes_host, depth_host, edges_host)
+        x = x_host.to(dev, non_blocking=True)
         ob = [o.to(dev, non_blocking=True) for o in objs_host]
         bx = [b.to(dev, non_blocking=True) for b in boxes_host]
         out = step(x, ob, bx)

@@ -3,7 +3,7 @@ keys and return tuples as the reference's ``modules/`` package).
 from .layers import PatchTransformerEncoder, PixelWiseDotProduct
 from .miniViT import mViT
 from .ObjCAViT import GridRandomPositionalEmbeddings, ObjCAViT, SelfAttnCrossAttn
-from .heads import AdaBinsHead, GraphBinsHead, build_head
+from .heads import AdaBinsHead, GraphBinsHead, HostPipeline, build_head
 
 __all__ = ["PatchTransformerEncoder", "PixelWiseDotProduct", "mViT", "GridRandomPositionalEmbeddings",
-           "SelfAttnCrossAttn", "ObjCAViT", "AdaBinsHead", "GraphBinsHead", "build_head"]
+           "SelfAttnCrossAttn", "ObjCAViT", "AdaBinsHead", "GraphBinsHead", "HostPipeline", "build_head"]

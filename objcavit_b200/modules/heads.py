@@ -96,6 +96,67 @@ class GraphBinsHead(_HeadBase):
         return self.ReturnType(depth_pred=depth, bin_edges=edges, detections=detections)
 
 
+class HostPipeline:
+    """Chunked host -> device -> host streaming of one batch through a bf16 head (the e2e path): the batch is cut into
+    chunks; chunk c+1's features cross PCIe on a copy stream while chunk c runs, and chunk c's depth map goes back on a
+    second copy stream.  Images are independent, so chunking changes nothing numerically (up to the patch-embedding
+    split-K plan, see tests/test_gpu_fullsize.py).  Host tensors must be pinned for the copies to be asynchronous."""
+
+    def __init__(self, head, chunks: int = 4):
+        assert head.precision == "bf16", "the streaming pipeline drives the bf16 throughput path"
+        self.head, self.chunks = head, chunks
+        self.h2d, self.d2h = torch.cuda.Stream(), torch.cuda.Stream()
+        self.xbuf = [None, None]
+        self.done = [None, None]
+
+    @torch.no_grad()
+    def __call__(self, feats_nhwc_host, object_features=None, object_xywh_list=None, depth_out=None, edges_out=None):
+        """feats_nhwc_host: pinned [B,h,w,128] bf16.  Returns (depth [B,1,h,w] fp32, bin_edges [B,K+1]) in pinned host memory."""
+        head = self.head
+        dev = head.device
+        B, h, w, C = feats_nhwc_host.shape
+        n = min(self.chunks, B)
+        bounds = [(B * i // n, B * (i + 1) // n) for i in range(n)]
+        if depth_out is None:
+            depth_out = torch.empty(B, 1, h, w, dtype=torch.float32).pin_memory()
+        if edges_out is None:
+            edges_out = torch.empty(B, head.conv_out[0].out_channels + 1, dtype=torch.float32).pin_memory()
+        cur = torch.cuda.current_stream()
+        self.h2d.wait_stream(cur)
+        results = []
+        for i, (lo, hi) in enumerate(bounds):
+            slot = i & 1
+            with torch.cuda.stream(self.h2d):
+                if self.done[slot] is not None:
+                    self.h2d.wait_event(self.done[slot])      # the chunk that used this buffer two steps ago has been consumed
+                if self.xbuf[slot] is None or self.xbuf[slot].shape[0] < hi - lo or self.xbuf[slot].shape[1:] != (h, w, C):
+                    self.xbuf[slot] = torch.empty(max(hi - lo, (B + n - 1) // n), h, w, C, device=dev, dtype=torch.bfloat16)
+                x = self.xbuf[slot][:hi - lo]
+                x.copy_(feats_nhwc_host[lo:hi], non_blocking=True)
+                objs = boxes = None
+                if object_features is not None:
+                    objs = [o.to(dev, non_blocking=True) for o in object_features[lo:hi]]
+                    boxes = [None if b is None else b.to(dev, non_blocking=True) for b in object_xywh_list[lo:hi]]
+                    for t in objs + [b for b in boxes if b is not None]:
+                        t.record_stream(cur)                  # allocated on the copy stream, consumed on the compute stream
+                ready = torch.cuda.Event()
+                ready.record(self.h2d)
+            cur.wait_event(ready)
+            xv = x.permute(0, 3, 1, 2)                         # logical NCHW view of NHWC memory: consumed in place
+            out = head(xv) if objs is None else head(xv, objs, boxes)
+            ev = torch.cuda.Event()
+            ev.record(cur)
+            self.done[slot] = ev
+            with torch.cuda.stream(self.d2h):
+                self.d2h.wait_event(ev)
+                depth_out[lo:hi].copy_(out.depth_pred, non_blocking=True)
+                edges_out[lo:hi].copy_(out.bin_edges, non_blocking=True)
+            results.append(out)                                # keep device tensors alive until the copies are done
+        cur.wait_stream(self.d2h)
+        self._keep = results
+        return depth_out, edges_out
+
+
 def build_head(args, precision: str = "fp32"):
     """Head for a params file: ``model.name == 'adabins'`` -> :class:`AdaBinsHead`, else :class:`GraphBinsHead`."""
     return AdaBinsHead(args, precision) if args.model.name == "adabins" else GraphBinsHead(args, precision)
