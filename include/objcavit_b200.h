@@ -218,6 +218,43 @@ int ocv_pixel_fused_bf16(const void* X, const void* W3p, const void* Mb, const f
 int ocv_pixel_fused_bf16_argmax(const void* X, const void* W3p, const void* Mb, const float* blog, const float* centres,
                                 float* depth, uint8_t* argmax_bin, int B, int h, int w, void* stream);
 
+/* ---- backward pass of the fp32 parity path (config 5) ----------------------------------------------------------------
+ * Every gradient entry writes  out = beta * out + value  where stated, so parameter gradients can accumulate in place.
+ *
+ * C[M,N] = beta*C + sum_{batch (if reduce_batch), k} op(A)[M,K] @ op(B)[K,N]:
+ *   transA: element (m,k) of op(A) is A[k*lda+m] (weight gradients dW = dY^T X) instead of A[m*lda+k];
+ *   opB: 0 = B[k*ldb+n];  1 = B[n*ldb+k];
+ *        2 = gathered patches of an NCHW map, B[m][k=(c,ky,kx)] = X[b,c,ty*P+ky,tx*P+kx] (patch-embedding weight gradient);
+ *        3 = gathered 3x3 neighbourhoods of ONE image (batch through strideB), B[p][j=(c,ky,kx)] = X[c,y+ky-1,x+kx-1] or 0
+ *            (conv3x3 weight gradient);  gather_geom_host = {C, h, w, P} for opB >= 2.
+ *   split_k > 1 / reduce_batch / beta != 0 go through `workspace` (ocv_gemm_f32_ex_workspace bytes), added in a fixed order.
+ * replaces: the autograd of nn.Linear / nn.Conv2d / torch.matmul on the path. */
+long long ocv_gemm_f32_ex_workspace(int M, int N, int batch, int split_k);
+int ocv_gemm_f32_ex(int transA, int opB, const float* A, const float* Bm, float* C, int M, int N, int K, int lda, int ldb, int ldc,
+                    float beta, int batch, long long strideA, long long strideB, long long strideC, int reduce_batch, int split_k,
+                    const int* gather_geom_host, void* workspace, void* stream);
+/* x viewed [groups, outer, C, inner] -> out[g,c] = beta*out[g,c] + sum_{o,i} x[g,o,c,i]   (bias / centre gradients) */
+int ocv_reduce_channels_f32(const float* x, float* out, int groups, int outer, int C, long long inner, float beta, void* stream);
+/* dx = dy * act'(.) from the activation OUTPUT (ReLU / LeakyReLU 0.01 keep the sign) */
+int ocv_act_bwd_f32(const float* dy, const float* out, float* dx, long long n, int act, void* stream);
+/* LayerNorm backward: z = pre-norm input [rows,E]; dz [rows,E]; dgamma/dbeta [E] (optional pair, beta-accumulated);
+ * workspace rows*2 floats. */
+int ocv_layernorm_bwd_f32(const float* dy, const float* z, const float* gamma, float* dz, float* dgamma, float* dbeta, int rows,
+                          int E, float beta, void* workspace, void* stream);
+/* Backward of ocv_mha_core_f32 (same view conventions; `out` = its forward result): dq, dk, dv.  workspace B*heads*Sq*3 floats. */
+int ocv_mha_core_bwd_f32(const float* q, const float* k, const float* v, const float* out, const float* dout,
+                         const uint8_t* key_padding_mask, float* dq, float* dk, float* dv, int B, int Sq, int Sk, int heads, int d,
+                         long long q_bstride, int q_rstride, long long k_bstride, int k_rstride, long long v_bstride, int v_rstride,
+                         long long o_bstride, int o_rstride, long long dq_bstride, int dq_rstride, long long dk_bstride,
+                         int dk_rstride, long long dv_bstride, int dv_rstride, void* workspace, void* stream);
+/* Backward of depth = sum_k softmax_k(l) c_k per pixel: logits l [B,K,P] are overwritten by dl = g p (c - depth);
+ * pg [B,K,P] = g p (its sum over pixels is d loss / d centres).   g = grad_depth [B,P]. */
+int ocv_tail_bwd_f32(float* logits_inout, float* pg_out, const float* centres, const float* grad_depth, int B, int K, long long P,
+                     void* stream);
+/* Backward of ocv_bins_f32 (norm 'linear'): grad_edges [B,K+1] and/or grad_centres [B,K] -> grad_y [B,K] (regressor output). */
+int ocv_bins_bwd_f32(const float* y_raw, const float* grad_edges, const float* grad_centres, float* grad_y, int B, int K,
+                     float min_depth, float max_depth, void* stream);
+
 /* ---- training losses (config 5), forward + gradients w.r.t. the head outputs ---------------------------------------
  * SILog: depth_pred [B,1,h,w] is up-sampled bilinearly (align_corners=True) to the GT size [B,1,H,W]; mask uint8 (1 = valid)
  *   or NULL; loss[0] = alph * sqrt(sum g^2 / n - lam (sum g)^2 / n^2), g = log p - log t over valid pixels of the WHOLE batch.

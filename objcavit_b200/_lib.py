@@ -52,6 +52,15 @@ PROTOTYPES = {
     "ocv_fold_queries_bf16": (i32, [p, p, p, i64, i32, p, f32, p, p, i32, i32, i32, i32, p]),
     "ocv_pixel_fused_bf16": (i32, [p, p, p, p, p, p, i32, i32, i32, i32, p]),
     "ocv_pixel_fused_bf16_argmax": (i32, [p, p, p, p, p, p, p, i32, i32, i32, p]),
+    "ocv_gemm_f32_ex_workspace": (i64, [i32, i32, i32, i32]),
+    "ocv_gemm_f32_ex": (i32, [i32, i32, p, p, p, i32, i32, i32, i32, i32, i32, f32, i32, i64, i64, i64, i32, i32, p, p, p]),
+    "ocv_reduce_channels_f32": (i32, [p, p, i32, i32, i32, i64, f32, p]),
+    "ocv_act_bwd_f32": (i32, [p, p, p, i64, i32, p]),
+    "ocv_layernorm_bwd_f32": (i32, [p, p, p, p, p, p, i32, i32, f32, p, p]),
+    "ocv_mha_core_bwd_f32": (i32, [p, p, p, p, p, p, p, p, p, i32, i32, i32, i32, i32, i64, i32, i64, i32, i64, i32, i64, i32,
+                                   i64, i32, i64, i32, i64, i32, p, p]),
+    "ocv_tail_bwd_f32": (i32, [p, p, p, p, i32, i32, i64, p]),
+    "ocv_bins_bwd_f32": (i32, [p, p, p, p, i32, i32, f32, f32, p]),
     "ocv_silog_workspace": (i64, [i32, i32, i32]),
     "ocv_silog_forward": (i32, [p, p, p, i32, i32, i32, i32, i32, f32, f32, p, p, p]),
     "ocv_silog_backward": (i32, [p, p, p, i32, i32, i32, i32, i32, f32, f32, f32, p, p, p]),

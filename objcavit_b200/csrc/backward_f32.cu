@@ -1,0 +1,319 @@
+// Backward kernels of the fp32 parity path that are not GEMMs (head forward + backward):
+// channel reductions (bias gradients), LayerNorm backward, activation backward, attention-core backward, the backward of
+// the softmax-over-bins expectation (head tail) and of the bin-width normalisation.  All reductions are fixed-order
+// (deterministic); gradients are written as  out = beta * out + value  so that parameter gradients can accumulate into
+// the flat gradient buffer.  Contract: include/objcavit_b200.h.
+#include "common.cuh"
+#include <math.h>
+
+namespace {
+
+__device__ __forceinline__ float block_sum_f(float v, float* sh) {  // result on every thread; sh >= 32 floats
+  v = warp_sum(v);
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32, nwarp = (blockDim.x + 31) / 32;
+  __syncthreads();
+  if (lane == 0) sh[warp] = v;
+  __syncthreads();
+  float t = 0.f;
+  for (int i = 0; i < nwarp; ++i) t += sh[i];
+  return t;
+}
+
+// x viewed [G, outer, C, inner] -> out[g, c] = beta * out[g, c] + sum_{o, i} x[g, o, c, i];  one block per (c, g)
+__global__ void reduce_channels_kernel(const float* __restrict__ x, float* __restrict__ out, int outer, int C, long long inner,
+                                       float beta) {
+  __shared__ float sh[32];
+  const int c = blockIdx.x, g = blockIdx.y;
+  const float* xg = x + (long long)g * outer * C * inner;
+  float acc = 0.f;
+  const long long n = (long long)outer * inner;
+  for (long long t = threadIdx.x; t < n; t += blockDim.x) {
+    const long long o = t / inner, i = t - o * inner;
+    acc += xg[(o * C + c) * inner + i];
+  }
+  const float s = block_sum_f(acc, sh);
+  if (threadIdx.x == 0) {
+    float* o = out + (long long)g * C + c;
+    *o = beta != 0.f ? beta * (*o) + s : s;
+  }
+}
+
+// dx = dy * act'(.) using the activation OUTPUT (sign-preserving activations)
+__global__ void act_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ out, float* __restrict__ dx, long long n,
+                               int act) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float o = out[i], g = dy[i];
+  dx[i] = act == OCV_ACT_RELU ? (o > 0.f ? g : 0.f) : (act == OCV_ACT_LEAKY_RELU ? (o > 0.f ? g : 0.01f * g) : g);
+}
+
+// LayerNorm backward, one warp per row (E <= 512, E % 32 == 0): z = pre-norm input, y = (z - mean) rstd gamma + beta
+//   dz = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma;  also stores (mean, rstd) per row for the parameter pass
+__global__ void layernorm_bwd_rows_kernel(const float* __restrict__ dy, const float* __restrict__ z, const float* __restrict__ gamma,
+                                          float* __restrict__ dz, float* __restrict__ stats, int rows, int E) {
+  const int row = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+  const int lane = threadIdx.x % 32;
+  if (row >= rows) return;
+  const int per = E / 32;
+  float v[16], g[16];
+  const float* zr = z + (long long)row * E;
+  const float* dr = dy + (long long)row * E;
+  float s = 0.f;
+  for (int i = 0; i < per; ++i) {
+    v[i] = zr[i * 32 + lane];
+    s += v[i];
+  }
+  const float mean = warp_sum(s) / E;
+  float q = 0.f;
+  for (int i = 0; i < per; ++i) {
+    v[i] -= mean;
+    q += v[i] * v[i];
+  }
+  const float rstd = rsqrtf(warp_sum(q) / E + 1e-5f);
+  float sg = 0.f, sgx = 0.f;
+  for (int i = 0; i < per; ++i) {
+    v[i] *= rstd;  // xhat
+    g[i] = dr[i * 32 + lane] * gamma[i * 32 + lane];
+    sg += g[i];
+    sgx += g[i] * v[i];
+  }
+  const float mg = warp_sum(sg) / E, mgx = warp_sum(sgx) / E;
+  float* o = dz + (long long)row * E;
+  for (int i = 0; i < per; ++i) o[i * 32 + lane] = rstd * (g[i] - mg - v[i] * mgx);
+  if (lane == 0) {
+    stats[2 * row] = mean;
+    stats[2 * row + 1] = rstd;
+  }
+}
+
+// dgamma[e] = beta*dgamma[e] + sum_rows dy * xhat,  dbeta[e] likewise;  block = 32 channels x 8 row lanes
+__global__ void layernorm_bwd_params_kernel(const float* __restrict__ dy, const float* __restrict__ z, const float* __restrict__ stats,
+                                            float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int E, float beta) {
+  __shared__ float sg[8][33], sb[8][33];
+  const int e = blockIdx.x * 32 + threadIdx.x, ry = threadIdx.y;
+  float ag = 0.f, ab = 0.f;
+  if (e < E)
+    for (int r = ry; r < rows; r += 8) {
+      const float d = dy[(long long)r * E + e];
+      ag += d * (z[(long long)r * E + e] - stats[2 * r]) * stats[2 * r + 1];
+      ab += d;
+    }
+  sg[ry][threadIdx.x] = ag;
+  sb[ry][threadIdx.x] = ab;
+  __syncthreads();
+  if (ry == 0 && e < E) {
+    float tg = 0.f, tb = 0.f;
+    for (int i = 0; i < 8; ++i) {
+      tg += sg[i][threadIdx.x];
+      tb += sb[i][threadIdx.x];
+    }
+    dgamma[e] = beta != 0.f ? beta * dgamma[e] + tg : tg;
+    dbeta[e] = beta != 0.f ? beta * dbeta[e] + tb : tb;
+  }
+}
+
+// ---- attention core backward (d = 32: lane = channel) --------------------------------------------------------------------
+// pass 1, warp per query row: softmax statistics (m, l), D = dO . O, and dq
+__global__ void mha_bwd_q_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
+                                 const float* __restrict__ o, const float* __restrict__ dout, const uint8_t* __restrict__ mask,
+                                 float* __restrict__ dq, float* __restrict__ stats, int Sq, int Sk, int heads, long long q_bs,
+                                 int q_rs, long long k_bs, int k_rs, long long v_bs, int v_rs, long long o_bs, int o_rs,
+                                 long long dq_bs, int dq_rs) {
+  const int b = blockIdx.z, hd = blockIdx.y;
+  const int i = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32, lane = threadIdx.x % 32;
+  if (i >= Sq) return;
+  const float scale = rsqrtf(32.f);
+  const float qi = q[b * q_bs + (long long)i * q_rs + hd * 32 + lane];
+  const float doi = dout[b * o_bs + (long long)i * o_rs + hd * 32 + lane];
+  const float oi = o[b * o_bs + (long long)i * o_rs + hd * 32 + lane];
+  const float D = warp_sum(doi * oi);
+  const float* kb = k + b * k_bs + hd * 32 + lane;
+  const float* vb = v + b * v_bs + hd * 32 + lane;
+  const uint8_t* mb = mask ? mask + (long long)b * Sk : nullptr;
+  float m = -INFINITY, l = 0.f;
+  for (int j = 0; j < Sk; ++j) {
+    if (mb && mb[j]) continue;
+    const float s = warp_sum(qi * kb[(long long)j * k_rs]) * scale;
+    const float mn = fmaxf(m, s);
+    l = l * __expf(m - mn) + __expf(s - mn);
+    m = mn;
+  }
+  float acc = 0.f;
+  for (int j = 0; j < Sk; ++j) {
+    if (mb && mb[j]) continue;
+    const float kj = kb[(long long)j * k_rs];
+    const float s = warp_sum(qi * kj) * scale;
+    const float p = __expf(s - m) / l;
+    const float dP = warp_sum(doi * vb[(long long)j * v_rs]);
+    acc = fmaf(p * (dP - D), kj, acc);
+  }
+  dq[b * dq_bs + (long long)i * dq_rs + hd * 32 + lane] = acc * scale;
+  if (lane == 0) {
+    float* st = stats + (((long long)b * heads + hd) * Sq + i) * 3;
+    st[0] = m; st[1] = l; st[2] = D;
+  }
+}
+
+// pass 2, warp per key row: dk, dv
+__global__ void mha_bwd_kv_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
+                                  const float* __restrict__ dout, const uint8_t* __restrict__ mask, const float* __restrict__ stats,
+                                  float* __restrict__ dk, float* __restrict__ dv, int Sq, int Sk, int heads, long long q_bs,
+                                  int q_rs, long long k_bs, int k_rs, long long v_bs, int v_rs, long long o_bs, int o_rs,
+                                  long long dk_bs, int dk_rs, long long dv_bs, int dv_rs) {
+  const int b = blockIdx.z, hd = blockIdx.y;
+  const int j = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32, lane = threadIdx.x % 32;
+  if (j >= Sk) return;
+  const float scale = rsqrtf(32.f);
+  float ak = 0.f, av = 0.f;
+  if (!(mask && mask[(long long)b * Sk + j])) {
+    const float kj = k[b * k_bs + (long long)j * k_rs + hd * 32 + lane];
+    const float vj = v[b * v_bs + (long long)j * v_rs + hd * 32 + lane];
+    const float* qb = q + b * q_bs + hd * 32 + lane;
+    const float* db = dout + b * o_bs + hd * 32 + lane;
+    const float* st = stats + ((long long)b * heads + hd) * Sq * 3;
+    for (int i = 0; i < Sq; ++i) {
+      const float qi = qb[(long long)i * q_rs], doi = db[(long long)i * o_rs];
+      const float s = warp_sum(qi * kj) * scale;
+      const float p = __expf(s - st[3 * i]) / st[3 * i + 1];
+      const float dP = warp_sum(doi * vj);
+      av = fmaf(p, doi, av);
+      ak = fmaf(p * (dP - st[3 * i + 2]), qi, ak);
+    }
+  }
+  dk[b * dk_bs + (long long)j * dk_rs + hd * 32 + lane] = ak * scale;
+  dv[b * dv_bs + (long long)j * dv_rs + hd * 32 + lane] = av;
+}
+
+// ---- head tail backward: depth = sum_k softmax_k(l) c_k -------------------------------------------------------------------
+// thread = pixel; logits [B,K,P] are overwritten by dl = gd * p * (c - depth); pg [B,K,P] = gd * p (its pixel sum is dcentres)
+__global__ void tail_bwd_kernel(float* __restrict__ logits, float* __restrict__ pg, const float* __restrict__ centres,
+                                const float* __restrict__ gdepth, int K, long long P) {
+  extern __shared__ float cs[];  // [K]
+  const int b = blockIdx.y;
+  for (int k = threadIdx.x; k < K; k += blockDim.x) cs[k] = centres[(long long)b * K + k];
+  __syncthreads();
+  const long long px = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (px >= P) return;
+  float* l = logits + (long long)b * K * P + px;
+  float* g = pg + (long long)b * K * P + px;
+  float m = -INFINITY;
+  for (int k = 0; k < K; ++k) m = fmaxf(m, l[(long long)k * P]);
+  float s = 0.f, a = 0.f;
+  for (int k = 0; k < K; ++k) {
+    const float e = __expf(l[(long long)k * P] - m);
+    s += e;
+    a = fmaf(e, cs[k], a);
+  }
+  const float inv = 1.f / s, d = a * inv, gd = gdepth[(long long)b * P + px];
+  for (int k = 0; k < K; ++k) {
+    const float p = __expf(l[(long long)k * P] - m) * inv;
+    g[(long long)k * P] = gd * p;
+    l[(long long)k * P] = gd * p * (cs[k] - d);
+  }
+}
+
+// ---- bin-width normalisation backward ('linear': w = (relu(y)+0.1)/sum; edges = min + (max-min) cumsum(w); centres = mid-points)
+// one block per image, K <= 1024 threads-strided
+__global__ void bins_bwd_kernel(const float* __restrict__ y_raw, const float* __restrict__ dedges, const float* __restrict__ dcentres,
+                                float* __restrict__ dy, int K, float range) {
+  __shared__ float de[1025], dw[1024], sh[32];
+  const int b = blockIdx.x;
+  const float* y = y_raw + (long long)b * K;
+  for (int j = threadIdx.x; j <= K; j += blockDim.x) {
+    float v = dedges ? dedges[(long long)b * (K + 1) + j] : 0.f;
+    if (dcentres) v += 0.5f * ((j > 0 ? dcentres[(long long)b * K + j - 1] : 0.f) + (j < K ? dcentres[(long long)b * K + j] : 0.f));
+    de[j] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {  // dw_k = range * sum_{j > k} de_j  (suffix sum, fixed order)
+    float run = 0.f;
+    for (int k = K - 1; k >= 0; --k) {
+      run += de[k + 1];
+      dw[k] = range * run;
+    }
+  }
+  __syncthreads();
+  float su = 0.f, sdw = 0.f;
+  for (int k = threadIdx.x; k < K; k += blockDim.x) {
+    const float u = fmaxf(y[k], 0.f) + 0.1f;
+    su += u;
+    sdw += dw[k] * u;
+  }
+  const float S = block_sum_f(su, sh);
+  const float dot = block_sum_f(sdw, sh) / S;  // sum_m dw_m w_m
+  for (int k = threadIdx.x; k < K; k += blockDim.x)
+    dy[(long long)b * K + k] = y[k] > 0.f ? (dw[k] - dot) / S : 0.f;
+}
+
+}  // namespace
+
+extern "C" int ocv_reduce_channels_f32(const float* x, float* out, int groups, int outer, int C, long long inner, float beta,
+                                       void* stream) {
+  OCV_CHECK_ARG(x && out && groups > 0 && outer > 0 && C > 0 && inner > 0);
+  OCV_CHECK_SHAPE(groups <= 65535);
+  if (int s = ocv_require_sm100()) return s;
+  reduce_channels_kernel<<<dim3(C, groups), 256, 0, ocv_stream(stream)>>>(x, out, outer, C, inner, beta);
+  return ocv_launch_status();
+}
+
+extern "C" int ocv_act_bwd_f32(const float* dy, const float* out, float* dx, long long n, int act, void* stream) {
+  OCV_CHECK_ARG(dy && out && dx && n > 0);
+  if (int s = ocv_require_sm100()) return s;
+  act_bwd_kernel<<<(unsigned)ceil_div<long long>(n, 256), 256, 0, ocv_stream(stream)>>>(dy, out, dx, n, act);
+  return ocv_launch_status();
+}
+
+extern "C" int ocv_layernorm_bwd_f32(const float* dy, const float* z, const float* gamma, float* dz, float* dgamma, float* dbeta,
+                                     int rows, int E, float beta, void* workspace /* rows*2 floats */, void* stream) {
+  OCV_CHECK_ARG(dy && z && gamma && dz && workspace && rows > 0);
+  OCV_CHECK_SHAPE(E > 0 && E % 32 == 0 && E <= 512);
+  OCV_CHECK_ARG((dgamma == nullptr) == (dbeta == nullptr));
+  if (int s = ocv_require_sm100()) return s;
+  float* stats = static_cast<float*>(workspace);
+  layernorm_bwd_rows_kernel<<<ceil_div(rows, 8), 256, 0, ocv_stream(stream)>>>(dy, z, gamma, dz, stats, rows, E);
+  if (int s = ocv_launch_status()) return s;
+  if (dgamma) {
+    layernorm_bwd_params_kernel<<<ceil_div(E, 32), dim3(32, 8), 0, ocv_stream(stream)>>>(dy, z, stats, dgamma, dbeta, rows, E, beta);
+    return ocv_launch_status();
+  }
+  return OCV_OK;
+}
+
+extern "C" int ocv_mha_core_bwd_f32(const float* q, const float* k, const float* v, const float* out, const float* dout,
+                                    const uint8_t* key_padding_mask, float* dq, float* dk, float* dv, int B, int Sq, int Sk,
+                                    int heads, int d, long long q_bstride, int q_rstride, long long k_bstride, int k_rstride,
+                                    long long v_bstride, int v_rstride, long long o_bstride, int o_rstride, long long dq_bstride,
+                                    int dq_rstride, long long dk_bstride, int dk_rstride, long long dv_bstride, int dv_rstride,
+                                    void* workspace /* B*heads*Sq*3 floats */, void* stream) {
+  OCV_CHECK_ARG(q && k && v && out && dout && dq && dk && dv && workspace && B > 0 && Sq > 0 && Sk > 0 && heads > 0);
+  OCV_CHECK_SHAPE(d == 32 && B <= 65535 && heads <= 65535);
+  if (int s = ocv_require_sm100()) return s;
+  float* stats = static_cast<float*>(workspace);
+  mha_bwd_q_kernel<<<dim3(ceil_div(Sq, 8), heads, B), 256, 0, ocv_stream(stream)>>>(
+      q, k, v, out, dout, key_padding_mask, dq, stats, Sq, Sk, heads, q_bstride, q_rstride, k_bstride, k_rstride, v_bstride,
+      v_rstride, o_bstride, o_rstride, dq_bstride, dq_rstride);
+  if (int s = ocv_launch_status()) return s;
+  mha_bwd_kv_kernel<<<dim3(ceil_div(Sk, 8), heads, B), 256, 0, ocv_stream(stream)>>>(
+      q, k, v, dout, key_padding_mask, stats, dk, dv, Sq, Sk, heads, q_bstride, q_rstride, k_bstride, k_rstride, v_bstride,
+      v_rstride, o_bstride, o_rstride, dk_bstride, dk_rstride, dv_bstride, dv_rstride);
+  return ocv_launch_status();
+}
+
+extern "C" int ocv_tail_bwd_f32(float* logits_inout, float* pg_out, const float* centres, const float* grad_depth, int B, int K,
+                                long long P, void* stream) {
+  OCV_CHECK_ARG(logits_inout && pg_out && centres && grad_depth && B > 0 && P > 0);
+  OCV_CHECK_SHAPE(K > 0 && K <= 4096 && B <= 65535);
+  if (int s = ocv_require_sm100()) return s;
+  tail_bwd_kernel<<<dim3((unsigned)ceil_div<long long>(P, 128), B), 128, K * sizeof(float), ocv_stream(stream)>>>(
+      logits_inout, pg_out, centres, grad_depth, K, P);
+  return ocv_launch_status();
+}
+
+extern "C" int ocv_bins_bwd_f32(const float* y_raw, const float* grad_edges, const float* grad_centres, float* grad_y, int B, int K,
+                                float min_depth, float max_depth, void* stream) {
+  OCV_CHECK_ARG(y_raw && grad_y && (grad_edges || grad_centres) && B > 0);
+  OCV_CHECK_SHAPE(K > 0 && K <= 1024);
+  if (int s = ocv_require_sm100()) return s;
+  bins_bwd_kernel<<<B, 256, 0, ocv_stream(stream)>>>(y_raw, grad_edges, grad_centres, grad_y, K, max_depth - min_depth);
+  return ocv_launch_status();
+}

@@ -550,3 +550,120 @@ def bins_chamfer(bin_edges: torch.Tensor, depth_gt: torch.Tensor, depth_mask=Non
     _call("ocv_bins_chamfer", bin_edges.data_ptr(), depth_gt.data_ptr(), _ptr(m), B, K1 - 1, HW, float(grad_scale),
           loss.data_ptr(), _ptr(grad), ws.data_ptr(), _stream(), launches=3)
     return (loss, grad) if want_grad else loss
+
+
+# ---- backward primitives of the fp32 parity path (config 5) --------------------------------------------
+
+_ws_cache = {}
+
+
+def _workspace(nbytes: int, device, tag: str = "bwd") -> torch.Tensor:
+    """Grow-only scratch (uint8) per (device, tag): backward temporaries are stream-ordered, so reuse is safe."""
+    key = (str(device), tag)
+    t = _ws_cache.get(key)
+    if t is None or t.numel() < nbytes:
+        t = torch.empty(max(int(nbytes), 256), device=device, dtype=torch.uint8)
+        _ws_cache[key] = t
+    return t
+
+
+def gemm_ex(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, lda: int, ldb: int, out: torch.Tensor, ldc: int,
+            trans_a: bool = False, op_b: int = 0, beta: float = 0.0, batch: int = 1, stride_a: int = 0, stride_b: int = 0,
+            stride_c: int = 0, reduce_batch: bool = False, split_k: int = 1, geom=None):
+    """out = beta*out + op(a) @ op(b) (raw-stride form of ``ocv_gemm_f32_ex``; see the header for the operand modes)."""
+    import ctypes as C
+    _chk(a, torch.float32, "a"); _chk(b, torch.float32, "b"); _chk(out, torch.float32, "out")
+    L = _lib.lib()
+    need = L.ocv_gemm_f32_ex_workspace(M, N, batch, split_k)
+    ws = _workspace(need, a.device, "gemm_ex")
+    g = (C.c_int * 4)(*geom) if geom is not None else None
+    _call("ocv_gemm_f32_ex", int(trans_a), int(op_b), a.data_ptr(), b.data_ptr(), out.data_ptr(), M, N, K, lda, ldb, ldc,
+          float(beta), batch, stride_a, stride_b, stride_c, int(reduce_batch), split_k, g, ws.data_ptr(), _stream(), launches=2)
+    return out
+
+
+def linear_dgrad(dy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """dx [M,K] = dy [M,N] @ w [N,K]."""
+    M, N, ldy = _row_major_2d(dy, "dy")
+    N2, K, ldw = _row_major_2d(w, "w")
+    assert N == N2
+    dx = torch.empty(M, K, device=dy.device, dtype=torch.float32)
+    return gemm_ex(dy, w, M, K, N, ldy, ldw, dx, K)
+
+
+def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, db=None, beta: float = 1.0):
+    """dw [N,K] = beta*dw + dy[M,N]^T @ x[M,K];  db [N] = beta*db + column sums of dy."""
+    M, N, ldy = _row_major_2d(dy, "dy")
+    M2, K, ldx = _row_major_2d(x, "x")
+    assert M == M2 and dw.is_contiguous() and dw.numel() == N * K
+    split = max(1, min(64, M // 256))
+    gemm_ex(dy, x, N, K, M, ldy, ldx, dw, K, trans_a=True, beta=beta, split_k=split)
+    if db is not None:
+        assert ldy == N, "bias gradient needs a dense dy"
+        reduce_channels(dy, db, 1, M, N, 1, beta)
+
+
+def reduce_channels(x: torch.Tensor, out: torch.Tensor, groups: int, outer: int, C: int, inner: int, beta: float = 0.0):
+    _chk(x, torch.float32, "x"); _chk(out, torch.float32, "out")
+    assert x.is_contiguous() and out.is_contiguous() and x.numel() == groups * outer * C * inner and out.numel() == groups * C
+    _call("ocv_reduce_channels_f32", x.data_ptr(), out.data_ptr(), groups, outer, C, inner, float(beta), _stream())
+    return out
+
+
+def act_bwd(dy: torch.Tensor, out: torch.Tensor, act: int) -> torch.Tensor:
+    _chk(dy, torch.float32, "dy"); _chk(out, torch.float32, "out")
+    assert dy.is_contiguous() and out.is_contiguous() and dy.shape == out.shape
+    dx = torch.empty_like(dy)
+    _call("ocv_act_bwd_f32", dy.data_ptr(), out.data_ptr(), dx.data_ptr(), dy.numel(), act, _stream())
+    return dx
+
+
+def layernorm_bwd(dy: torch.Tensor, z: torch.Tensor, gamma: torch.Tensor, dgamma=None, dbeta=None, beta: float = 1.0):
+    _chk(dy, torch.float32, "dy"); _chk(z, torch.float32, "z")
+    assert dy.is_contiguous() and z.is_contiguous() and dy.shape == z.shape
+    E = z.shape[-1]
+    rows = z.numel() // E
+    dz = torch.empty_like(z)
+    ws = _workspace(rows * 8, z.device, "ln_bwd")
+    _call("ocv_layernorm_bwd_f32", dy.data_ptr(), z.data_ptr(), gamma.data_ptr(), dz.data_ptr(), _ptr(dgamma), _ptr(dbeta), rows, E,
+          float(beta), ws.data_ptr(), _stream(), launches=2)
+    return dz
+
+
+def mha_core_bwd(q, k, v, out, dout, key_padding_mask=None, heads: int = 4):
+    """Backward of :func:`mha_core`: returns (dq, dk, dv) dense [B,S,E]."""
+    for t, n in ((q, "q"), (k, "k"), (v, "v"), (out, "out"), (dout, "dout")):
+        _chk(t, torch.float32, n)
+        assert t.dim() == 3 and t.stride(2) == 1
+    B, Sq, E = q.shape
+    Sk = k.shape[1]
+    assert out.stride() == dout.stride()
+    dq = torch.empty(B, Sq, E, device=q.device, dtype=torch.float32)
+    dk = torch.empty(B, Sk, E, device=q.device, dtype=torch.float32)
+    dv = torch.empty(B, Sk, E, device=q.device, dtype=torch.float32)
+    ws = _workspace(B * heads * Sq * 12, q.device, "mha_bwd")
+    _call("ocv_mha_core_bwd_f32", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), dout.data_ptr(), _ptr(key_padding_mask),
+          dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), B, Sq, Sk, heads, E // heads, q.stride(0), q.stride(1), k.stride(0),
+          k.stride(1), v.stride(0), v.stride(1), out.stride(0), out.stride(1), dq.stride(0), dq.stride(1), dk.stride(0),
+          dk.stride(1), dv.stride(0), dv.stride(1), ws.data_ptr(), _stream(), launches=2)
+    return dq, dk, dv
+
+
+def tail_bwd(logits: torch.Tensor, centres: torch.Tensor, grad_depth: torch.Tensor):
+    """logits [B,K,P] (overwritten by dl) -> (dl, pg)."""
+    _chk(logits, torch.float32, "logits")
+    assert logits.is_contiguous() and centres.is_contiguous() and grad_depth.is_contiguous()
+    B, K, P = logits.shape
+    pg = torch.empty_like(logits)
+    _call("ocv_tail_bwd_f32", logits.data_ptr(), pg.data_ptr(), centres.data_ptr(), grad_depth.data_ptr(), B, K, P, _stream())
+    return logits, pg
+
+
+def bins_bwd(y_raw: torch.Tensor, grad_edges, grad_centres, min_depth: float, max_depth: float) -> torch.Tensor:
+    _chk(y_raw, torch.float32, "y_raw")
+    assert y_raw.is_contiguous()
+    B, K = y_raw.shape
+    dy = torch.empty_like(y_raw)
+    _call("ocv_bins_bwd_f32", y_raw.data_ptr(), _ptr(grad_edges), _ptr(grad_centres), dy.data_ptr(), B, K, float(min_depth),
+          float(max_depth), _stream())
+    return dy
