@@ -247,10 +247,15 @@ int ocv_mha_core_bwd_f32(const float* q, const float* k, const float* v, const f
                          long long q_bstride, int q_rstride, long long k_bstride, int k_rstride, long long v_bstride, int v_rstride,
                          long long o_bstride, int o_rstride, long long dq_bstride, int dq_rstride, long long dk_bstride,
                          int dk_rstride, long long dv_bstride, int dv_rstride, void* workspace, void* stream);
-/* Backward of depth = sum_k softmax_k(l) c_k per pixel: logits l [B,K,P] are overwritten by dl = g p (c - depth);
- * pg [B,K,P] = g p (its sum over pixels is d loss / d centres).   g = grad_depth [B,P]. */
-int ocv_tail_bwd_f32(float* logits_inout, float* pg_out, const float* centres, const float* grad_depth, int B, int K, long long P,
-                     void* stream);
+/* Backward of depth = sum_k softmax_k(l + bias) c_k per pixel: logits l [B,K,P] are overwritten by dl = g p (c - depth);
+ * pg [B,K,P] = g p (its sum over pixels is d loss / d centres).   g = grad_depth [B,P];  logit_bias [K] or NULL (the conv_out
+ * bias, so that the logits operand can be the bare GEMM Wout @ ram). */
+int ocv_tail_bwd_f32(float* logits_inout, float* pg_out, const float* centres, const float* grad_depth, const float* logit_bias,
+                     int B, int K, long long P, void* stream);
+/* Adjoint of ocv_pad_objects_f32: dsrc[offsets[b]+j, :] = beta * dsrc + dpadded[b, left+j, :] for j < n_b (left = L-Nmax when
+ * left_pad else 0); pad rows carry no gradient. */
+int ocv_unpad_objects_f32(const float* dpadded, const int32_t* offsets, float* dsrc, int B, int L, int Nmax, int E, int left_pad,
+                          float beta, void* stream);
 /* Backward of ocv_bins_f32 (norm 'linear'): grad_edges [B,K+1] and/or grad_centres [B,K] -> grad_y [B,K] (regressor output). */
 int ocv_bins_bwd_f32(const float* y_raw, const float* grad_edges, const float* grad_centres, float* grad_y, int B, int K,
                      float min_depth, float max_depth, void* stream);
@@ -274,6 +279,18 @@ int ocv_silog_backward(const float* depth_pred, const float* depth_gt, const uin
 long long ocv_bins_chamfer_workspace(int B, int K);
 int ocv_bins_chamfer(const float* bin_edges, const float* depth_gt, const uint8_t* depth_mask, int B, int K, long long HW,
                      float grad_scale, float* loss, float* grad_edges, void* workspace, void* stream);
+
+/* ---- optimizer step on flat buffers (config 5) ---------------------------------------------------------------------------
+ * out[0] = scale^2 * sum x^2 (fixed-order two-stage reduction; deterministic).  workspace: ocv_sumsq_workspace() bytes.
+ * ocv_adamw_step_f32: torch.optim.AdamW semantics on flat param / grad / exp_avg / exp_avg_sq buffers (16-byte aligned):
+ *   g = grad * grad_scale * clip, clip = grad_sumsq ? min(1, max_norm / (sqrt(grad_sumsq[0]) + 1e-6)) : 1   (grad_sumsq: DEVICE scalar,
+ *   so that no host synchronisation sits between the all-reduce, the clipping and the update);  step >= 1 (bias correction).
+ * replaces: clip_grad_norm_ (gradient_clip_val, main.py:35-38,64) + torch.optim.AdamW.step (modules/GraphBinsLM.py:467). */
+long long ocv_sumsq_workspace(long long n);
+int ocv_sumsq_f32(const float* x, long long n, float scale, float* out, void* workspace, void* stream);
+int ocv_adamw_step_f32(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, long long n, float lr, float beta1,
+                       float beta2, float eps, float weight_decay, int step, float grad_scale, const float* grad_sumsq,
+                       float max_norm, void* stream);
 
 /* ---- whole head, one call (native host-side sequencing) -------------------------------------------------
  * An ocv_head is a HOST-side plan: the head's configuration, the device pointers of its parameters keyed by the

@@ -59,7 +59,11 @@ PROTOTYPES = {
     "ocv_layernorm_bwd_f32": (i32, [p, p, p, p, p, p, i32, i32, f32, p, p]),
     "ocv_mha_core_bwd_f32": (i32, [p, p, p, p, p, p, p, p, p, i32, i32, i32, i32, i32, i64, i32, i64, i32, i64, i32, i64, i32,
                                    i64, i32, i64, i32, i64, i32, p, p]),
-    "ocv_tail_bwd_f32": (i32, [p, p, p, p, i32, i32, i64, p]),
+    "ocv_tail_bwd_f32": (i32, [p, p, p, p, p, i32, i32, i64, p]),
+    "ocv_unpad_objects_f32": (i32, [p, p, p, i32, i32, i32, i32, i32, f32, p]),
+    "ocv_sumsq_workspace": (i64, [i64]),
+    "ocv_sumsq_f32": (i32, [p, i64, f32, p, p, p]),
+    "ocv_adamw_step_f32": (i32, [p, p, p, p, i64, f32, f32, f32, f32, f32, i32, f32, p, f32, p]),
     "ocv_bins_bwd_f32": (i32, [p, p, p, p, i32, i32, f32, f32, p]),
     "ocv_silog_workspace": (i64, [i32, i32, i32]),
     "ocv_silog_forward": (i32, [p, p, p, i32, i32, i32, i32, i32, f32, f32, p, p, p]),

@@ -187,26 +187,30 @@ __global__ void mha_bwd_kv_kernel(const float* __restrict__ q, const float* __re
 // ---- head tail backward: depth = sum_k softmax_k(l) c_k -------------------------------------------------------------------
 // thread = pixel; logits [B,K,P] are overwritten by dl = gd * p * (c - depth); pg [B,K,P] = gd * p (its pixel sum is dcentres)
 __global__ void tail_bwd_kernel(float* __restrict__ logits, float* __restrict__ pg, const float* __restrict__ centres,
-                                const float* __restrict__ gdepth, int K, long long P) {
-  extern __shared__ float cs[];  // [K]
+                                const float* __restrict__ gdepth, const float* __restrict__ bias, int K, long long P) {
+  extern __shared__ float cs[];  // [K] centres, [K] logit bias
+  float* bs = cs + K;
   const int b = blockIdx.y;
-  for (int k = threadIdx.x; k < K; k += blockDim.x) cs[k] = centres[(long long)b * K + k];
+  for (int k = threadIdx.x; k < K; k += blockDim.x) {
+    cs[k] = centres[(long long)b * K + k];
+    bs[k] = bias ? bias[k] : 0.f;
+  }
   __syncthreads();
   const long long px = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (px >= P) return;
   float* l = logits + (long long)b * K * P + px;
   float* g = pg + (long long)b * K * P + px;
   float m = -INFINITY;
-  for (int k = 0; k < K; ++k) m = fmaxf(m, l[(long long)k * P]);
+  for (int k = 0; k < K; ++k) m = fmaxf(m, l[(long long)k * P] + bs[k]);
   float s = 0.f, a = 0.f;
   for (int k = 0; k < K; ++k) {
-    const float e = __expf(l[(long long)k * P] - m);
+    const float e = __expf(l[(long long)k * P] + bs[k] - m);
     s += e;
     a = fmaf(e, cs[k], a);
   }
   const float inv = 1.f / s, d = a * inv, gd = gdepth[(long long)b * P + px];
   for (int k = 0; k < K; ++k) {
-    const float p = __expf(l[(long long)k * P] - m) * inv;
+    const float p = __expf(l[(long long)k * P] + bs[k] - m) * inv;
     g[(long long)k * P] = gd * p;
     l[(long long)k * P] = gd * p * (cs[k] - d);
   }
@@ -245,7 +249,28 @@ __global__ void bins_bwd_kernel(const float* __restrict__ y_raw, const float* __
     dy[(long long)b * K + k] = y[k] > 0.f ? (dw[k] - dot) / S : 0.f;
 }
 
+// ---- adjoint of ocv_pad_objects_f32: dsrc[offsets[b] + j] = beta * dsrc + dpadded[b, left + j]  (pad rows receive no gradient)
+__global__ void unpad_objects_kernel(const float* __restrict__ dpadded, const int32_t* __restrict__ offsets, float* __restrict__ dsrc,
+                                     int L, int Nmax, int E, int left_pad, float beta) {
+  const int b = blockIdx.y, j = blockIdx.x;
+  const int beg = offsets[b], n = offsets[b + 1] - beg;
+  if (j >= n) return;
+  const int left = left_pad ? (L - Nmax) : 0;
+  const float* s = dpadded + ((long long)b * L + left + j) * E;
+  float* d = dsrc + (long long)(beg + j) * E;
+  for (int e = threadIdx.x; e < E; e += blockDim.x) d[e] = beta != 0.f ? beta * d[e] + s[e] : s[e];
+}
+
 }  // namespace
+
+extern "C" int ocv_unpad_objects_f32(const float* dpadded, const int32_t* offsets, float* dsrc, int B, int L, int Nmax, int E,
+                                     int left_pad, float beta, void* stream) {
+  OCV_CHECK_ARG(dpadded && offsets && dsrc && B > 0 && L > 0 && E > 0);
+  OCV_CHECK_SHAPE(Nmax > 0 && Nmax <= L && B <= 65535);
+  if (int s = ocv_require_sm100()) return s;
+  unpad_objects_kernel<<<dim3(Nmax, B), 128, 0, ocv_stream(stream)>>>(dpadded, offsets, dsrc, L, Nmax, E, left_pad, beta);
+  return ocv_launch_status();
+}
 
 extern "C" int ocv_reduce_channels_f32(const float* x, float* out, int groups, int outer, int C, long long inner, float beta,
                                        void* stream) {
@@ -299,13 +324,13 @@ extern "C" int ocv_mha_core_bwd_f32(const float* q, const float* k, const float*
   return ocv_launch_status();
 }
 
-extern "C" int ocv_tail_bwd_f32(float* logits_inout, float* pg_out, const float* centres, const float* grad_depth, int B, int K,
-                                long long P, void* stream) {
+extern "C" int ocv_tail_bwd_f32(float* logits_inout, float* pg_out, const float* centres, const float* grad_depth,
+                                const float* logit_bias, int B, int K, long long P, void* stream) {
   OCV_CHECK_ARG(logits_inout && pg_out && centres && grad_depth && B > 0 && P > 0);
   OCV_CHECK_SHAPE(K > 0 && K <= 4096 && B <= 65535);
   if (int s = ocv_require_sm100()) return s;
-  tail_bwd_kernel<<<dim3((unsigned)ceil_div<long long>(P, 128), B), 128, K * sizeof(float), ocv_stream(stream)>>>(
-      logits_inout, pg_out, centres, grad_depth, K, P);
+  tail_bwd_kernel<<<dim3((unsigned)ceil_div<long long>(P, 128), B), 128, 2 * K * sizeof(float), ocv_stream(stream)>>>(
+      logits_inout, pg_out, centres, grad_depth, logit_bias, K, P);
   return ocv_launch_status();
 }
 

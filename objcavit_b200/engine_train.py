@@ -1,0 +1,346 @@
+"""Training-mode sequencing of the head: forward with saved activations + explicit backward.
+
+The reference trains the head through torch autograd over ATen ops (``modules/GraphBinsLM.py:121-139``); here every stage of the
+forward AND of the backward is a C-ABI kernel of ``libobjcavit_b200.so`` (fp32 SIMT parity path), sequenced by this file:
+
+    tape = forward(P, cfg, x, objects...)          -> depth_pred [B,1,h,w], bin_edges [B,K+1]  (+ saved activations)
+    backward(P, G, tape, d_depth, d_edges)         -> accumulates d loss / d parameter into G[key] (same keys as P)
+
+``G`` maps a ``state_dict`` key to a zero-initialised (or already holding earlier micro-batches) fp32 buffer of the parameter's
+shape — normally views of ONE flat gradient buffer (``grad_sync.FlatGradBuffer``), so the data-parallel step is a single
+all-reduce.  Parameters the reference leaves without gradient simply keep their zeros.
+
+Grad-mode semantics of the reference are reproduced: ``nn.TransformerEncoder`` takes the slow path under autograd, so padded
+object rows are NOT zeroed (F7), the left-pad / right-mask quirk (F5) is kept, and dropout is the identity (``dropout=0`` —
+gradient parity is defined with dropout disabled).  The decoder features are constants of the step
+(frozen extractor): no gradient w.r.t. ``x`` is produced.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional
+
+import torch
+
+from . import ops
+from .engine import E, HEADS, ObjectBatch, marshal_objects
+
+Params = Dict[str, torch.Tensor]
+RELU, LEAKY, NONE = ops.ACT_RELU, ops.ACT_LEAKY_RELU, ops.ACT_NONE
+
+
+def _split(M: int, N: int, batch: int, K: int, target_blocks: int = 592) -> int:
+    """split-K factor that fills the 148 SMs ~4x with 64x64 tiles without cutting K below 256 per split."""
+    tiles = ((M + 63) // 64) * ((N + 63) // 64) * batch
+    s = max(1, (target_blocks + tiles - 1) // tiles)
+    s = min(s, max(1, K // 256), max(1, 65535 // max(batch, 1)), 64)
+    return s
+
+
+class Touched(dict):
+    """Gradient map that records which keys the backward pass wrote: parameters it never touches have NO gradient (``.grad is
+    None`` in the reference) and the optimizer must leave them alone (no weight decay either)."""
+
+    def __init__(self, *a, **kw):
+        super().__init__(*a, **kw)
+        self.touched = set()
+
+    def __getitem__(self, k):
+        self.touched.add(k)
+        return super().__getitem__(k)
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# MLP chains (positional encoder, regressor)
+# ----------------------------------------------------------------------------------------------------------------------
+
+def mlp_fwd(P: Params, pre: str, x: torch.Tensor, idxs):
+    saved = []
+    for j, i in enumerate(idxs):
+        act = LEAKY if j < len(idxs) - 1 else NONE
+        y = ops.linear(x, P[f"{pre}{i}.weight"], P[f"{pre}{i}.bias"], act=act)
+        saved.append((x, y))
+        x = y
+    return x, saved
+
+
+def mlp_bwd(P: Params, G: Params, pre: str, idxs, saved, dy: torch.Tensor, dx_out: Optional[torch.Tensor] = None):
+    """dy: gradient of the chain output (dense 2-D).  ``dx_out``: where the gradient w.r.t. the chain input goes (a 2-D view,
+    overwritten); ``None`` = the input is a constant of the step (boxes / patch coordinates)."""
+    for j in range(len(idxs) - 1, -1, -1):
+        i = idxs[j]
+        x, y = saved[j]
+        if j < len(idxs) - 1:
+            dy = ops.act_bwd(dy, y, LEAKY)
+        ops.linear_wgrad(dy, x, G[f"{pre}{i}.weight"], G[f"{pre}{i}.bias"], beta=1.0)
+        if j > 0:
+            dy = ops.linear_dgrad(dy, P[f"{pre}{i}.weight"])
+        elif dx_out is not None:
+            ops.linear_dgrad(dy, P[f"{pre}{i}.weight"], out=dx_out)
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# nn.TransformerEncoderLayer (post-norm) / nn.TransformerEncoder
+# ----------------------------------------------------------------------------------------------------------------------
+
+def encoder_layer_fwd(P: Params, pre: str, x: torch.Tensor, mask):
+    B, S, _ = x.shape
+    x2 = x.view(B * S, E)
+    qkv = ops.linear(x2, P[pre + "self_attn.in_proj_weight"], P[pre + "self_attn.in_proj_bias"]).view(B, S, 3 * E)
+    att = ops.mha_core(qkv[:, :, 0:E], qkv[:, :, E:2 * E], qkv[:, :, 2 * E:], mask, HEADS)
+    y = ops.linear(att.view(B * S, E), P[pre + "self_attn.out_proj.weight"], P[pre + "self_attn.out_proj.bias"], residual=x2)
+    x1 = ops.add_layernorm(y, None, P[pre + "norm1.weight"], P[pre + "norm1.bias"])
+    h = ops.linear(x1, P[pre + "linear1.weight"], P[pre + "linear1.bias"], act=RELU)
+    y2 = ops.linear(h, P[pre + "linear2.weight"], P[pre + "linear2.bias"], residual=x1)
+    out = ops.add_layernorm(y2, None, P[pre + "norm2.weight"], P[pre + "norm2.bias"])
+    return out.view(B, S, E), (x2, qkv, att, y, x1, h, y2, mask)
+
+
+def encoder_layer_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor) -> torch.Tensor:
+    x2, qkv, att, y, x1, h, y2, mask = saved
+    B, S, _ = qkv.shape
+    d = dout.reshape(B * S, E)
+    dy2 = ops.layernorm_bwd(d, y2, P[pre + "norm2.weight"], G[pre + "norm2.weight"], G[pre + "norm2.bias"], beta=1.0)
+    ops.linear_wgrad(dy2, h, G[pre + "linear2.weight"], G[pre + "linear2.bias"], beta=1.0)
+    dh = ops.act_bwd(ops.linear_dgrad(dy2, P[pre + "linear2.weight"]), h, RELU)
+    ops.linear_wgrad(dh, x1, G[pre + "linear1.weight"], G[pre + "linear1.bias"], beta=1.0)
+    ops.linear_dgrad(dh, P[pre + "linear1.weight"], out=dy2, beta=1.0)           # dy2 <- d loss / d x1 (residual + FFN)
+    dy = ops.layernorm_bwd(dy2, y, P[pre + "norm1.weight"], G[pre + "norm1.weight"], G[pre + "norm1.bias"], beta=1.0)
+    ops.linear_wgrad(dy, att.view(B * S, E), G[pre + "self_attn.out_proj.weight"], G[pre + "self_attn.out_proj.bias"], beta=1.0)
+    datt = ops.linear_dgrad(dy, P[pre + "self_attn.out_proj.weight"]).view(B, S, E)
+    dqkv = ops.mha_core_bwd(qkv[:, :, 0:E], qkv[:, :, E:2 * E], qkv[:, :, 2 * E:], att, datt, mask, HEADS, packed=True)[3]
+    dqkv = dqkv.view(B * S, 3 * E)
+    ops.linear_wgrad(dqkv, x2, G[pre + "self_attn.in_proj_weight"], G[pre + "self_attn.in_proj_bias"], beta=1.0)
+    ops.linear_dgrad(dqkv, P[pre + "self_attn.in_proj_weight"], out=dy, beta=1.0)  # dy <- d loss / d x (residual + attention)
+    return dy.view(B, S, E)
+
+
+def encoder_fwd(P: Params, pre: str, x: torch.Tensor, mask=None, num_layers: int = 4):
+    saved = []
+    for i in range(num_layers):
+        x, sv = encoder_layer_fwd(P, f"{pre}layers.{i}.", x, mask)
+        saved.append(sv)
+    return x, saved
+
+
+def encoder_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor) -> torch.Tensor:
+    for i in range(len(saved) - 1, -1, -1):
+        dout = encoder_layer_bwd(P, G, f"{pre}layers.{i}.", saved[i], dout)
+    return dout
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# nn.MultiheadAttention used as cross attention
+# ----------------------------------------------------------------------------------------------------------------------
+
+def cross_fwd(P: Params, pre: str, q_in, k_in, v_in, mask):
+    w, b = P[pre + "in_proj_weight"], P[pre + "in_proj_bias"]
+    B, Sq, _ = q_in.shape
+    Sk = k_in.shape[1]
+    q = ops.linear(q_in.reshape(B * Sq, E), w[0:E], b[0:E]).view(B, Sq, E)
+    k = ops.linear(k_in.reshape(B * Sk, E), w[E:2 * E], b[E:2 * E]).view(B, Sk, E)
+    v = ops.linear(v_in.reshape(B * Sk, E), w[2 * E:], b[2 * E:]).view(B, Sk, E)
+    att = ops.mha_core(q, k, v, mask, HEADS)
+    out = ops.linear(att.view(B * Sq, E), P[pre + "out_proj.weight"], P[pre + "out_proj.bias"]).view(B, Sq, E)
+    return out, (q_in, k_in, v_in, q, k, v, att, mask)
+
+
+def cross_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor, acc_q, acc_k, acc_v):
+    """``acc_*`` = (tensor [B,S,E] contiguous, beta): where the gradient w.r.t. the query / key / value INPUT is written
+    (beta 0) or accumulated (beta 1) — the same tensor may be named twice when one input plays two roles."""
+    q_in, k_in, v_in, q, k, v, att, mask = saved
+    B, Sq, _ = q.shape
+    Sk = k.shape[1]
+    w = P[pre + "in_proj_weight"]
+    gw, gb = G[pre + "in_proj_weight"], G[pre + "in_proj_bias"]
+    d = dout.reshape(B * Sq, E)
+    ops.linear_wgrad(d, att.view(B * Sq, E), G[pre + "out_proj.weight"], G[pre + "out_proj.bias"], beta=1.0)
+    datt = ops.linear_dgrad(d, P[pre + "out_proj.weight"]).view(B, Sq, E)
+    dq, dk, dv = ops.mha_core_bwd(q, k, v, att, datt, mask, HEADS)
+    for dz, z_in, lo, acc, rows in ((dq, q_in, 0, acc_q, B * Sq), (dk, k_in, E, acc_k, B * Sk), (dv, v_in, 2 * E, acc_v, B * Sk)):
+        dz2 = dz.view(rows, E)
+        ops.linear_wgrad(dz2, z_in.reshape(rows, E), gw[lo:lo + E], gb[lo:lo + E], beta=1.0)
+        if acc is not None:
+            ops.linear_dgrad(dz2, w[lo:lo + E], out=acc[0].view(rows, E), beta=acc[1])
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# SelfAttnCrossAttn (modules/ObjCAViT.py:167-213)
+# ----------------------------------------------------------------------------------------------------------------------
+
+def saca_fwd(P: Params, pre: str, img_tok: torch.Tensor, objs, no_obj_sa: bool, need_object_output: bool):
+    B, S, _ = img_tok.shape
+    att_img, sv_img = encoder_fwd(P, pre + "image_transformer_encoder.", img_tok)
+    sv_obj = None
+    if isinstance(objs, ObjectBatch):
+        n_max = objs.n_max
+        if n_max > S:
+            raise ValueError("more objects than image tokens: the reference's F.pad would crop; unsupported")
+        padded, mask = ops.pad_objects(objs.rows, objs.offsets, B, n_max, n_max, 0.0001, False)            # :180-183
+        att_obj = padded
+        if not no_obj_sa:
+            att_obj, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", padded, mask)              # :188 (slow path)
+        uni = objs.uniform_offsets(n_max)
+        att_obj_s, kpm = ops.pad_objects(att_obj.reshape(B * n_max, E), uni, B, S, n_max, 0.0001, True,
+                                         mask_offsets=objs.offsets)                                         # :192-194 (F5)
+        geom = ("ragged", objs, uni, n_max)
+    else:
+        assert objs.shape == (B, S, E)
+        att_obj_s = objs.contiguous()
+        if not no_obj_sa:
+            att_obj_s, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", att_obj_s)
+        kpm = None
+        geom = ("dense",)
+    final_img, sv_c1 = cross_fwd(P, pre + "cross_attn_obj_im.", att_img, att_obj_s, att_img, kpm)          # :195-201
+    final_obj, sv_c2 = None, None
+    if need_object_output:
+        final_obj, sv_c2 = cross_fwd(P, pre + "cross_attn_im_obj.", att_obj_s, att_img, att_obj_s, None)   # :202-207
+    return final_img, final_obj, (sv_img, sv_obj, sv_c1, sv_c2, geom, (B, S))
+
+
+def saca_bwd(P: Params, G: Params, pre: str, saved, d_final_img: torch.Tensor, d_final_obj: Optional[torch.Tensor]):
+    """-> (d image tokens [B,S,E], d objects: ragged rows [total,E] (block 1) or dense [B,S,E] (block 2))."""
+    sv_img, sv_obj, sv_c1, sv_c2, geom, (B, S) = saved
+    dev = d_final_img.device
+    d_att_img = torch.empty(B, S, E, device=dev, dtype=torch.float32)
+    d_att_obj_s = torch.empty(B, S, E, device=dev, dtype=torch.float32)
+    cross_bwd(P, G, pre + "cross_attn_obj_im.", sv_c1, d_final_img, (d_att_img, 0.0), (d_att_obj_s, 0.0), (d_att_img, 1.0))
+    if sv_c2 is not None and d_final_obj is not None:
+        cross_bwd(P, G, pre + "cross_attn_im_obj.", sv_c2, d_final_obj, (d_att_obj_s, 1.0), (d_att_img, 1.0), (d_att_obj_s, 1.0))
+    d_img_tok = encoder_bwd(P, G, pre + "image_transformer_encoder.", sv_img, d_att_img)
+    if geom[0] == "ragged":
+        _, objs, uni, n_max = geom
+        d_att_obj = ops.unpad_objects(d_att_obj_s, uni, B * n_max, n_max, True).view(B, n_max, E)
+        if sv_obj is not None:
+            d_att_obj = encoder_bwd(P, G, pre + "obj_transformer_encoder.", sv_obj, d_att_obj)
+        d_objs = ops.unpad_objects(d_att_obj.contiguous(), objs.offsets, objs.offsets_host[-1], n_max, False)
+    else:
+        d_objs = d_att_obj_s
+        if sv_obj is not None:
+            d_objs = encoder_bwd(P, G, pre + "obj_transformer_encoder.", sv_obj, d_att_obj_s)
+    return d_img_tok, d_objs
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# whole head
+# ----------------------------------------------------------------------------------------------------------------------
+
+class Tape:
+    """Saved activations of one training forward (plain attributes; freed when the object dies)."""
+
+
+def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_xywh_list=None, mutate_inputs: bool = True,
+            patch_size: int = 16, n_query: int = 128):
+    """-> (depth_pred [B,1,h,w], bin_edges [B,K+1], tape).  ``cfg``: kind ('adabins' | 'graphbins'), strategy, no_obj_sa,
+    use_2_saca, min_depth, max_depth."""
+    t = Tape()
+    t.cfg, t.x = cfg, x
+    B, C, h, w = x.shape
+    t.shape = (B, C, h, w)
+    if cfg["kind"] == "adabins":
+        pre = "adaptive_bins_layer."
+        pt = pre + "patch_transformer."
+        tok0 = ops.patch_embed(x, P[pt + "embedding_convPxP.weight"], P[pt + "embedding_convPxP.bias"],
+                               P[pt + "positional_encodings"], patch_size)
+        tok, t.sv_enc = encoder_fwd(P, pt + "transformer_encoder.", tok0)
+    else:
+        pre = "objcavit."
+        strategy = cfg["strategy"]
+        if strategy not in ("learned", "learned_bbox_wh"):
+            raise NotImplementedError("objcavit_b200 training: gradient of the grid_random positional table is not built; "
+                                      "the training path supports the 'learned' / 'learned_bbox_wh' strategies (config 5)")
+        nin = 4 if strategy == "learned_bbox_wh" else 2
+        feats, boxes, counts = marshal_objects(object_features, object_xywh_list, x.device)
+        coords = ops.patch_coords(h // patch_size, w // patch_size, patch_size, x.device)
+        pe = pre + "positional_encoder."
+        obj_pos, t.sv_mlp_obj = mlp_fwd(P, pe, boxes[:, 0:nin], (0, 2, 4, 6, 8))
+        img_pos, t.sv_mlp_img = mlp_fwd(P, pe, coords[:, 0:nin], (0, 2, 4, 6, 8))
+        obj_tok = ops.linear(feats, P[pre + "obj_embedding_layer.weight"], P[pre + "obj_embedding_layer.bias"], residual=obj_pos)
+        t.feats = feats
+        batch = ObjectBatch(obj_tok, counts)
+        if mutate_inputs:                                                            # F11
+            for i in range(B):
+                object_features[i] = obj_tok[batch.offsets_host[i]:batch.offsets_host[i + 1]]
+        tok0 = ops.patch_embed(x, P[pre + "image_embedding_convPxP.weight"], P[pre + "image_embedding_convPxP.bias"], img_pos,
+                               patch_size)
+        two = bool(cfg.get("use_2_saca"))
+        tok, obj_out, t.sv_saca1 = saca_fwd(P, pre + "saca_1.", tok0, batch, bool(cfg.get("no_obj_sa")), two)
+        if two:
+            tok, _, t.sv_saca2 = saca_fwd(P, pre + "saca_2.", tok, obj_out, bool(cfg.get("no_obj_sa")), False)
+    t.pre = pre
+    S = tok.shape[1]
+    t.tok = tok
+    Q = min(n_query, S - 1)
+    t.x3 = ops.conv3x3(x, P[pre + "conv3x3.weight"], P[pre + "conv3x3.bias"])
+    t.ram = ops.batched_matmul_nn(tok[:, 1:Q + 1, :], t.x3.view(B, C, h * w)).view(B, Q, h, w)
+    t.y_raw, t.sv_reg = mlp_fwd(P, pre + "regressor.", tok[:, 0, :], (0, 2, 4))
+    _, edges, t.centres = ops.bins(t.y_raw, "linear", cfg["min_depth"], cfg["max_depth"])
+    depth = ops.tail(t.ram, P["conv_out.0.weight"], P["conv_out.0.bias"], t.centres)
+    return depth, edges, t
+
+
+def backward(P: Params, G: Params, t: Tape, d_depth: torch.Tensor, d_edges: Optional[torch.Tensor]) -> None:
+    """Accumulate parameter gradients into ``G`` for upstream gradients ``d_depth`` [B,1,h,w] and ``d_edges`` [B,K+1]|None."""
+    cfg, pre, x = t.cfg, t.pre, t.x
+    B, C, h, w = t.shape
+    Pn = h * w
+    dev = x.device
+    tok = t.tok
+    S = tok.shape[1]
+    Q = t.ram.shape[1]
+    Wout = P["conv_out.0.weight"].view(-1, Q)
+    K = Wout.shape[0]
+    ram = t.ram.view(B, Q, Pn)
+    gd = d_depth.contiguous().view(B, Pn)
+    # ---- tail: depth = sum_k softmax_k(Wout ram + bout) c_k ----------------------------------------------------------
+    logits = torch.empty(B, K, Pn, device=dev, dtype=torch.float32)
+    ops.gemm_ex(Wout, ram, K, Pn, Q, Q, Pn, logits, Pn, batch=B, stride_a=0, stride_b=Q * Pn, stride_c=K * Pn)
+    dl, pg = ops.tail_bwd(logits, t.centres, gd, bias=P["conv_out.0.bias"])
+    dcent = torch.empty(B, K, device=dev, dtype=torch.float32)
+    ops.reduce_channels(pg, dcent, B, 1, K, Pn)
+    del pg
+    ops.reduce_channels(dl, G["conv_out.0.bias"], 1, B, K, Pn, beta=1.0)
+    ops.gemm_ex(dl, ram, K, Q, Pn, Pn, Pn, G["conv_out.0.weight"], Q, op_b=1, beta=1.0, batch=B, stride_a=K * Pn, stride_b=Q * Pn,
+                reduce_batch=True, split_k=_split(K, Q, B, Pn))
+    dram = torch.empty(B, Q, Pn, device=dev, dtype=torch.float32)
+    ops.gemm_ex(Wout, dl, Q, Pn, K, Q, Pn, dram, Pn, trans_a=True, batch=B, stride_a=0, stride_b=K * Pn, stride_c=Q * Pn)
+    del dl, logits
+    # ---- bins + regressor -------------------------------------------------------------------------------------------
+    dy_raw = ops.bins_bwd(t.y_raw, d_edges.contiguous() if d_edges is not None else None, dcent, cfg["min_depth"], cfg["max_depth"])
+    dtok = torch.zeros(B, S, E, device=dev, dtype=torch.float32)
+    mlp_bwd(P, G, pre + "regressor.", (0, 2, 4), t.sv_reg, dy_raw, dx_out=dtok[:, 0, :])
+    # ---- range attention: ram[b] = queries[b] @ x3[b] ------------------------------------------------------------------
+    x3 = t.x3.view(B, C, Pn)
+    queries = tok[:, 1:Q + 1, :]
+    ops.gemm_ex(dram, x3, Q, E, Pn, Pn, Pn, dtok[:, 1:Q + 1, :], E, op_b=1, batch=B, stride_a=Q * Pn, stride_b=C * Pn,
+                stride_c=S * E, split_k=_split(Q, E, B, Pn))
+    dx3 = torch.empty(B, C, Pn, device=dev, dtype=torch.float32)
+    ops.gemm_ex(queries, dram, E, Pn, Q, E, Pn, dx3, Pn, trans_a=True, batch=B, stride_a=S * E, stride_b=Q * Pn, stride_c=C * Pn)
+    del dram
+    ops.gemm_ex(dx3, x, C, C * 9, Pn, Pn, 0, G[pre + "conv3x3.weight"], C * 9, op_b=3, beta=1.0, batch=B, stride_a=C * Pn,
+                stride_b=C * Pn, reduce_batch=True, split_k=_split(C, C * 9, B, Pn), geom=(C, h, w, 0))
+    ops.reduce_channels(dx3, G[pre + "conv3x3.bias"], 1, B, C, Pn, beta=1.0)
+    del dx3
+    # ---- tokens -------------------------------------------------------------------------------------------------------
+    if cfg["kind"] == "adabins":
+        pt = pre + "patch_transformer."
+        dtok0 = encoder_bwd(P, G, pt + "transformer_encoder.", t.sv_enc, dtok)
+        wkey, bkey = pt + "embedding_convPxP.weight", pt + "embedding_convPxP.bias"
+        d_pos_rows = G[pt + "positional_encodings"][0:S]
+        ops.reduce_channels(dtok0.contiguous(), d_pos_rows, 1, B, S * E, 1, beta=1.0)
+    else:
+        d_obj = None
+        if cfg.get("use_2_saca"):
+            dtok, d_obj = saca_bwd(P, G, pre + "saca_2.", t.sv_saca2, dtok, None)
+        dtok0, d_obj_tok = saca_bwd(P, G, pre + "saca_1.", t.sv_saca1, dtok, d_obj)
+        wkey, bkey = pre + "image_embedding_convPxP.weight", pre + "image_embedding_convPxP.bias"
+        d_img_pos = torch.empty(S, E, device=dev, dtype=torch.float32)
+        ops.reduce_channels(dtok0.contiguous(), d_img_pos, 1, B, S * E, 1)
+        pe = pre + "positional_encoder."
+        mlp_bwd(P, G, pe, (0, 2, 4, 6, 8), t.sv_mlp_img, d_img_pos)
+        ops.linear_wgrad(d_obj_tok, t.feats, G[pre + "obj_embedding_layer.weight"], G[pre + "obj_embedding_layer.bias"], beta=1.0)
+        mlp_bwd(P, G, pe, (0, 2, 4, 6, 8), t.sv_mlp_obj, d_obj_tok)
+    dt2 = dtok0.contiguous().view(B * S, E)
+    Pp = 16
+    ops.gemm_ex(dt2, x, E, C * Pp * Pp, B * S, E, 0, G[wkey], C * Pp * Pp, trans_a=True, op_b=2, beta=1.0,
+                split_k=_split(E, C * Pp * Pp, 1, B * S), geom=(C, h, w, Pp))
+    ops.reduce_channels(dt2, G[bkey], 1, B * S, E, 1, beta=1.0)

@@ -19,8 +19,53 @@ from .miniViT import mViT
 from .ObjCAViT import ObjCAViT
 
 
+class _HeadTrainFn(torch.autograd.Function):
+    """Autograd node of the whole head in grad mode (config 5): forward = ``engine_train.forward`` (fp32 kernels, activations
+    kept on a tape), backward = ``engine_train.backward`` into ONE zero-filled flat buffer whose slices are returned as the
+    parameter gradients (autograd then accumulates them into ``.grad``, e.g. the views of a ``FlatGradBuffer``)."""
+
+    @staticmethod
+    def forward(ctx, head, cfg, x, object_features, object_xywh_list, keys, *params):
+        from .. import engine_train
+        P = {k: p.detach() for k, p in zip(keys, params)}
+        depth, edges, tape = engine_train.forward(P, cfg, x.detach().contiguous().float(), object_features, object_xywh_list)
+        ctx.tape, ctx.P, ctx.keys = tape, P, keys
+        ctx.needs = [p.requires_grad for p in params]
+        return depth, edges
+
+    @staticmethod
+    def backward(ctx, d_depth, d_edges):
+        from .. import engine_train
+        P, keys = ctx.P, ctx.keys
+        sizes = [(P[k].numel() + 63) // 64 * 64 for k in keys]
+        flat = torch.zeros(sum(sizes), device=P[keys[0]].device, dtype=torch.float32)
+        G, off = engine_train.Touched(), 0
+        for k, n in zip(keys, sizes):
+            G[k] = flat[off:off + P[k].numel()].view_as(P[k])
+            off += n
+        if d_depth is None:
+            d_depth = torch.zeros_like(ctx.tape.x[:, :1])
+        engine_train.backward(P, G, ctx.tape, d_depth.contiguous().float(), d_edges)
+        ctx.tape = None
+        touched = set(G.touched)     # parameters the backward never wrote have no gradient at all (None, as in the reference: F10)
+        return (None,) * 6 + tuple(dict.__getitem__(G, k) if (need and k in touched) else None for k, need in zip(keys, ctx.needs))
+
+
 class _HeadBase(KernelModule):
     precision = "fp32"   # "fp32": parity path (SIMT fp32).  "bf16": tensor-core path (tcgen05).
+
+    def _wants_grad(self, x):
+        return torch.is_grad_enabled() and (any(p.requires_grad for p in self.parameters()) or
+                                            (torch.is_tensor(x) and x.requires_grad))
+
+    def _train_forward(self, cfg, x, object_features, object_xywh_list):
+        """Grad-mode forward (the reference's training step): fp32 kernels + explicit backward, for either ``precision``."""
+        if torch.is_tensor(x) and x.requires_grad:
+            raise NotImplementedError("objcavit_b200: gradients w.r.t. the decoder features are not produced (the extractor is "
+                                      "frozen in config 5); pass features.detach()")
+        named = list(self.named_parameters())
+        keys = tuple(k for k, _ in named)
+        return _HeadTrainFn.apply(self, cfg, x, object_features, object_xywh_list, keys, *[p for _, p in named])
 
     def _depth_range(self):
         ds = self.args[self.args.basic.dataset]
@@ -51,8 +96,10 @@ class AdaBinsHead(_HeadBase):
 
     def forward(self, unet_out):
         """``unet_out``: decoder features ``[B,128,h,w]`` -> ``ReturnType(depth_pred [B,1,h,w], bin_edges [B,K+1])``."""
-        self._guard_inference(unet_out)
         lo, hi = self._depth_range()
+        if self._wants_grad(unet_out):
+            depth, edges = self._train_forward(dict(kind="adabins", min_depth=lo, max_depth=hi), unet_out, None, None)
+            return self.ReturnType(depth_pred=depth, bin_edges=edges)
         P = self._params()
         if self.precision == "bf16":
             from .. import engine_bf16
@@ -80,10 +127,14 @@ class GraphBinsHead(_HeadBase):
 
     def forward(self, dense_features, object_features, object_xywh_list, detections=None):
         """-> ``ReturnType(depth_pred, bin_edges, detections)`` (``GraphBins.py:105-121``)."""
-        self._guard_inference(dense_features)
         lo, hi = self._depth_range()
-        P = self._params()
         oc = self.objcavit
+        if self._wants_grad(dense_features):
+            cfg = dict(kind="graphbins", strategy=oc.strategy, no_obj_sa=oc.no_obj_sa, use_2_saca=oc.use_2_saca, min_depth=lo,
+                       max_depth=hi)
+            depth, edges = self._train_forward(cfg, dense_features, object_features, object_xywh_list)
+            return self.ReturnType(depth_pred=depth, bin_edges=edges, detections=detections)
+        P = self._params()
         if self.precision == "bf16":
             from .. import engine_bf16
             depth, edges = engine_bf16.head_forward(self, P, "objcavit.", dense_features, object_features,

@@ -582,13 +582,17 @@ def gemm_ex(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, lda: int, 
     return out
 
 
-def linear_dgrad(dy: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
-    """dx [M,K] = dy [M,N] @ w [N,K]."""
+def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, out=None, beta: float = 0.0) -> torch.Tensor:
+    """dx [M,K] = beta*dx + dy [M,N] @ w [N,K]  (``out``: a 2-D view with unit inner stride, e.g. one token row per image)."""
     M, N, ldy = _row_major_2d(dy, "dy")
     N2, K, ldw = _row_major_2d(w, "w")
     assert N == N2
-    dx = torch.empty(M, K, device=dy.device, dtype=torch.float32)
-    return gemm_ex(dy, w, M, K, N, ldy, ldw, dx, K)
+    if out is None:
+        out = torch.empty(M, K, device=dy.device, dtype=torch.float32)
+        beta = 0.0
+    M2, K2, ldo = _row_major_2d(out, "out")
+    assert (M2, K2) == (M, K)
+    return gemm_ex(dy, w, M, K, N, ldy, ldw, out, ldo, beta=beta)
 
 
 def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, db=None, beta: float = 1.0):
@@ -630,32 +634,39 @@ def layernorm_bwd(dy: torch.Tensor, z: torch.Tensor, gamma: torch.Tensor, dgamma
     return dz
 
 
-def mha_core_bwd(q, k, v, out, dout, key_padding_mask=None, heads: int = 4):
-    """Backward of :func:`mha_core`: returns (dq, dk, dv) dense [B,S,E]."""
+def mha_core_bwd(q, k, v, out, dout, key_padding_mask=None, heads: int = 4, packed: bool = False):
+    """Backward of :func:`mha_core`: returns (dq, dk, dv) dense [B,S,E]; ``packed`` (self-attention, Sq == Sk): the three are
+    views of one [B,S,3E] buffer laid out like the packed QKV projection output."""
     for t, n in ((q, "q"), (k, "k"), (v, "v"), (out, "out"), (dout, "dout")):
         _chk(t, torch.float32, n)
         assert t.dim() == 3 and t.stride(2) == 1
     B, Sq, E = q.shape
     Sk = k.shape[1]
     assert out.stride() == dout.stride()
-    dq = torch.empty(B, Sq, E, device=q.device, dtype=torch.float32)
-    dk = torch.empty(B, Sk, E, device=q.device, dtype=torch.float32)
-    dv = torch.empty(B, Sk, E, device=q.device, dtype=torch.float32)
+    if packed:
+        assert Sq == Sk
+        dqkv = torch.empty(B, Sq, 3 * E, device=q.device, dtype=torch.float32)
+        dq, dk, dv = dqkv[:, :, 0:E], dqkv[:, :, E:2 * E], dqkv[:, :, 2 * E:]
+    else:
+        dq = torch.empty(B, Sq, E, device=q.device, dtype=torch.float32)
+        dk = torch.empty(B, Sk, E, device=q.device, dtype=torch.float32)
+        dv = torch.empty(B, Sk, E, device=q.device, dtype=torch.float32)
     ws = _workspace(B * heads * Sq * 12, q.device, "mha_bwd")
     _call("ocv_mha_core_bwd_f32", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), dout.data_ptr(), _ptr(key_padding_mask),
           dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), B, Sq, Sk, heads, E // heads, q.stride(0), q.stride(1), k.stride(0),
           k.stride(1), v.stride(0), v.stride(1), out.stride(0), out.stride(1), dq.stride(0), dq.stride(1), dk.stride(0),
           dk.stride(1), dv.stride(0), dv.stride(1), ws.data_ptr(), _stream(), launches=2)
-    return dq, dk, dv
+    return (dq, dk, dv, dqkv) if packed else (dq, dk, dv)
 
 
-def tail_bwd(logits: torch.Tensor, centres: torch.Tensor, grad_depth: torch.Tensor):
-    """logits [B,K,P] (overwritten by dl) -> (dl, pg)."""
+def tail_bwd(logits: torch.Tensor, centres: torch.Tensor, grad_depth: torch.Tensor, bias=None):
+    """logits [B,K,P] (overwritten by dl) -> (dl, pg).  ``bias`` [K]: added to the logits before the softmax."""
     _chk(logits, torch.float32, "logits")
     assert logits.is_contiguous() and centres.is_contiguous() and grad_depth.is_contiguous()
     B, K, P = logits.shape
     pg = torch.empty_like(logits)
-    _call("ocv_tail_bwd_f32", logits.data_ptr(), pg.data_ptr(), centres.data_ptr(), grad_depth.data_ptr(), B, K, P, _stream())
+    _call("ocv_tail_bwd_f32", logits.data_ptr(), pg.data_ptr(), centres.data_ptr(), grad_depth.data_ptr(), _ptr(bias), B, K, P,
+          _stream())
     return logits, pg
 
 
@@ -667,3 +678,39 @@ def bins_bwd(y_raw: torch.Tensor, grad_edges, grad_centres, min_depth: float, ma
     _call("ocv_bins_bwd_f32", y_raw.data_ptr(), _ptr(grad_edges), _ptr(grad_centres), dy.data_ptr(), B, K, float(min_depth),
           float(max_depth), _stream())
     return dy
+
+
+def unpad_objects(dpadded: torch.Tensor, offsets: torch.Tensor, total: int, n_max: int, left_pad: bool, out=None, beta: float = 0.0):
+    """Adjoint of :func:`pad_objects`: dpadded [B,L,E] -> gradient of the ragged rows [total,E]."""
+    _chk(dpadded, torch.float32, "dpadded")
+    assert dpadded.is_contiguous() and dpadded.dim() == 3
+    B, L, E = dpadded.shape
+    if out is None:
+        out = torch.empty(total, E, device=dpadded.device, dtype=torch.float32)
+        beta = 0.0
+    _call("ocv_unpad_objects_f32", dpadded.data_ptr(), offsets.data_ptr(), out.data_ptr(), B, L, n_max, E, int(left_pad), float(beta),
+          _stream())
+    return out
+
+
+def sumsq(x: torch.Tensor, scale: float = 1.0, out=None) -> torch.Tensor:
+    """out[0] = scale^2 * sum(x^2) (deterministic); stays on the device."""
+    _chk(x, torch.float32, "x")
+    assert x.is_contiguous()
+    if out is None:
+        out = torch.empty(1, device=x.device, dtype=torch.float32)
+    ws = _workspace(_lib.lib().ocv_sumsq_workspace(x.numel()), x.device, "sumsq")
+    _call("ocv_sumsq_f32", x.data_ptr(), x.numel(), float(scale), out.data_ptr(), ws.data_ptr(), _stream(), launches=2)
+    return out
+
+
+def adamw_step(param: torch.Tensor, grad: torch.Tensor, exp_avg: torch.Tensor, exp_avg_sq: torch.Tensor, lr: float, beta1: float,
+               beta2: float, eps: float, weight_decay: float, step: int, grad_scale: float = 1.0, grad_sumsq=None,
+               max_norm: float = 0.0):
+    """In-place AdamW update of a flat parameter buffer (``torch.optim.AdamW`` semantics, optional fused norm clipping)."""
+    for t, n in ((param, "param"), (grad, "grad"), (exp_avg, "exp_avg"), (exp_avg_sq, "exp_avg_sq")):
+        _chk(t, torch.float32, n)
+        assert t.is_contiguous() and t.numel() == param.numel()
+    _call("ocv_adamw_step_f32", param.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(), param.numel(), float(lr),
+          float(beta1), float(beta2), float(eps), float(weight_decay), int(step), float(grad_scale), _ptr(grad_sumsq), float(max_norm),
+          _stream())

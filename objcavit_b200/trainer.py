@@ -1,0 +1,143 @@
+"""The data-parallel training step of the head (BASELINE.json config 5) without torch autograd or torch
+optimizers on the path:
+
+    zero flat grads -> engine_train.forward -> SILog / chamfer kernels (loss + d depth, d edges) -> engine_train.backward
+    (accumulates straight into the flat gradient buffer) -> ONE all-reduce of that buffer (NCCL over NVLink; skipped at world 1)
+    -> deterministic sum-of-squares -> fused clip + AdamW over the flat parameter buffer (2 launches for the whole head).
+
+replaces: ``GraphBinsLM.training_step`` (``modules/GraphBinsLM.py:121-139``: model forward + LossWrapper), Lightning's backward,
+DDP's bucketed gradient all-reduce with unused-parameter search (``main.py:66``), ``gradient_clip_val`` (``main.py:35-38``),
+``torch.optim.AdamW`` + ``OneCycleLR(cycle_momentum)`` (``modules/GraphBinsLM.py:455-480``).
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from . import engine_train, ops
+from .grad_sync import FlatGradBuffer
+
+
+class OneCycle:
+    """``torch.optim.lr_scheduler.OneCycleLR`` (cos annealing, two phases, ``cycle_momentum=True``) as a pure host function of
+    the step index: returns (lr, beta1) for optimizer step ``i`` (0-based)."""
+
+    def __init__(self, max_lr: float, total_steps: int, div_factor: float = 25.0, final_div_factor: float = 100.0,
+                 pct_start: float = 0.3, base_momentum: float = 0.85, max_momentum: float = 0.95):
+        self.total = total_steps
+        self.initial_lr = max_lr / div_factor
+        self.max_lr = max_lr
+        self.min_lr = self.initial_lr / final_div_factor
+        self.base_m, self.max_m = base_momentum, max_momentum
+        self.end1 = float(pct_start * total_steps) - 1.0
+        self.end2 = float(total_steps) - 1.0
+
+    @staticmethod
+    def _cos(start, end, pct):
+        return end + (start - end) / 2.0 * (math.cos(math.pi * pct) + 1.0)
+
+    def at(self, i: int):
+        i = min(i, self.total - 1)
+        if i <= self.end1 or self.end1 <= 0:
+            pct = i / self.end1 if self.end1 > 0 else 1.0
+            return self._cos(self.initial_lr, self.max_lr, pct), self._cos(self.max_m, self.base_m, pct)
+        pct = (i - self.end1) / (self.end2 - self.end1)
+        return self._cos(self.max_lr, self.min_lr, pct), self._cos(self.base_m, self.max_m, pct)
+
+
+class HeadTrainer:
+    """Owns the flat parameter / gradient / AdamW-moment buffers of one head replica and runs whole training steps.
+
+    The head's ``nn.Parameter``s are re-pointed at slices of ONE flat fp32 buffer (their values are preserved; ``state_dict``
+    and checkpoints are unchanged), so the optimizer step is a single kernel over [param | grad | exp_avg | exp_avg_sq].
+    """
+
+    def __init__(self, head, lr: float = 0.000357, weight_decay: float = 0.1, betas=(0.9, 0.999), eps: float = 1e-8,
+                 clip_grad_norm: float = 0.1, loss_coeffs=(1.0, 0.1), schedule: Optional[OneCycle] = None, group=None):
+        self.head = head
+        self.group = group
+        self.lr, self.wd, self.betas, self.eps, self.clip = lr, weight_decay, betas, eps, clip_grad_norm
+        self.coeffs = loss_coeffs
+        self.schedule = schedule
+        self.grads = FlatGradBuffer(head.parameters())
+        flat = torch.empty_like(self.grads.flat)
+        flat.zero_()
+        for p, off in zip(self.grads.params, self.grads.offsets):      # parameters become views of one buffer
+            view = flat[off:off + p.numel()].view_as(p)
+            view.copy_(p.data)
+            p.data = view
+        self.flat_params = flat
+        self.exp_avg = torch.zeros_like(flat)
+        self.exp_avg_sq = torch.zeros_like(flat)
+        self.sumsq = torch.zeros(1, device=flat.device, dtype=torch.float32)
+        self.step_index = 0
+        self.ranges = None
+        self.keys = [k for k, p in head.named_parameters() if p.requires_grad]
+        head.__dict__.pop("_ocv_param_cache", None)
+        oc = getattr(head, "objcavit", None)
+        lo, hi = head._depth_range()
+        if oc is None:
+            self.cfg = dict(kind="adabins", min_depth=lo, max_depth=hi)
+        else:
+            self.cfg = dict(kind="graphbins", strategy=oc.strategy, no_obj_sa=oc.no_obj_sa, use_2_saca=oc.use_2_saca,
+                            min_depth=lo, max_depth=hi)
+
+    def world(self) -> int:
+        return dist.get_world_size(self.group) if dist.is_available() and dist.is_initialized() else 1
+
+    def _maps(self):
+        named = dict(self.head.named_parameters())
+        P = {k: named[k].data for k in self.keys}
+        G = engine_train.Touched({k: named[k].grad for k in self.keys})
+        return P, G
+
+    def forward_backward(self, features, object_features, object_xywh_list, depth_gt, depth_mask):
+        """Local forward + loss + backward; gradients accumulate into the flat buffer.  Returns the loss (device scalar)."""
+        P, G = self._maps()
+        x = features.contiguous().float()
+        depth, edges, tape = engine_train.forward(P, self.cfg, x, object_features, object_xywh_list)
+        gt = depth_gt.contiguous().float()
+        l1, d_depth = ops.silog(depth, gt, depth_mask, want_grad=True, grad_scale=self.coeffs[0])
+        l2, d_edges = ops.bins_chamfer(edges, gt, depth_mask, want_grad=True, grad_scale=self.coeffs[1])
+        engine_train.backward(P, G, tape, d_depth, d_edges)
+        if self.ranges is None:                      # static per configuration: merge the touched parameters into flat ranges
+            named = dict(self.head.named_parameters())
+            spans = sorted((off, off + (p.numel() + 63) // 64 * 64) for (p, off) in zip(self.grads.params, self.grads.offsets)
+                           if any(named[k] is p for k in G.touched))
+            merged = []
+            for lo, hi in spans:
+                if merged and merged[-1][1] == lo:
+                    merged[-1][1] = hi
+                else:
+                    merged.append([lo, hi])
+            self.ranges = [(lo, min(hi, self.flat_params.numel())) for lo, hi in merged]
+        self.last_outputs = (depth, edges)
+        return l1, l2
+
+    def step(self, features, object_features, object_xywh_list, depth_gt, depth_mask):
+        """One optimizer step on this rank's shard of the batch.  No host synchronisation anywhere in the step."""
+        self.grads.zero()
+        l1, l2 = self.forward_backward(features, object_features, object_xywh_list, depth_gt, depth_mask)
+        world = self.world()
+        if world > 1:
+            dist.all_reduce(self.grads.flat, op=dist.ReduceOp.SUM, group=self.group)   # the ONE collective of the step
+        scale = 1.0 / world
+        lr, beta1 = (self.lr, self.betas[0]) if self.schedule is None else self.schedule.at(self.step_index)
+        self.step_index += 1
+        clip = self.clip and self.clip > 0
+        if clip:
+            ops.sumsq(self.grads.flat, scale, out=self.sumsq)
+        for lo, hi in self.ranges:                   # 1-3 ranges: everything except the parameters that never get a gradient
+            ops.adamw_step(self.flat_params[lo:hi], self.grads.flat[lo:hi], self.exp_avg[lo:hi], self.exp_avg_sq[lo:hi], lr, beta1,
+                           self.betas[1], self.eps, self.wd, self.step_index, grad_scale=scale,
+                           grad_sumsq=self.sumsq if clip else None, max_norm=float(self.clip or 0.0))
+        for m in self.head.modules():              # the kernel wrote the parameters behind torch's version counters:
+            m.__dict__.pop("_ocv_packed", None)    # drop the derived bf16 / packed inference operands
+            m.__dict__.pop("_ocv_native", None)
+        return l1, l2
+
+    def loss_value(self, l1, l2) -> float:
+        return float(self.coeffs[0] * l1.item() + self.coeffs[1] * l2.item())

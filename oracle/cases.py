@@ -21,6 +21,25 @@ CASES = {
                                   seed=7),
 }
 
+# training-step cases (config 5 semantics: grad mode, dropout disabled, SILog + 0.1 chamfer): gradients w.r.t. every parameter
+TRAIN_CASES = {
+    "train_learned_bbox_wh_small": dict(args="nyu_ocv_learned_bbox_wh", B=2, h=176, w=192, n_obj=6, ragged=True, none_at=1,
+                                        seed=8),
+    "train_2saca_small": dict(args="nyu_ocv_learned_bbox_wh_2saca", B=2, h=176, w=192, n_obj=7, ragged=True, seed=9),
+    "train_no_obj_sa_small": dict(args="nyu_ocv_learned_bbox_wh_no_obj_sa", B=2, h=176, w=192, n_obj=4, ragged=True, seed=10),
+    "train_adabins_small": dict(args="nyu_adabins", B=2, h=176, w=192, seed=11),
+}
+
+
+def grad_probe_indices(numel: int, n: int = 8):
+    """Fixed flat positions at which a parameter's gradient is stored in the training fixtures."""
+    return sorted({(i * 2654435761 + 12345) % numel for i in range(n)})
+
+
+def case_gt(case, args):
+    ds = args[args.basic.dataset]
+    return synth.make_gt(case["B"], case["h"], case["w"], ds.max_depth, ds.min_depth, seed=1234 + case["seed"])
+
 
 def case_inputs(case):
     feats = synth.make_features(case["B"], case["h"], case["w"], seed=1234 + case["seed"])

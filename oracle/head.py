@@ -62,12 +62,14 @@ def encoder_layer(sd: SD, pre: str, x, num_heads: int = 4, key_padding_mask=None
     return F.layer_norm(x + h, (x.shape[-1],), sd[pre + "norm2.weight"], sd[pre + "norm2.bias"], 1e-5)
 
 
-def transformer_encoder(sd: SD, pre: str, x, num_layers: int = 4, num_heads: int = 4, key_padding_mask=None):
+def transformer_encoder(sd: SD, pre: str, x, num_layers: int = 4, num_heads: int = 4, key_padding_mask=None,
+                        fast_path: bool = True):
     """``nn.TransformerEncoder(layer, num_layers=4)`` (no final norm).  With a padding mask the
-    inference fast path returns zeros at the padded rows (F7)."""
+    inference fast path returns zeros at the padded rows (F7); under autograd (``fast_path=False``,
+    the training step of config 5) PyTorch takes the slow path and the padded rows keep their values."""
     for i in range(num_layers):
         x = encoder_layer(sd, f"{pre}layers.{i}.", x, num_heads, key_padding_mask)
-    if key_padding_mask is not None:
+    if key_padding_mask is not None and fast_path:
         x = x.masked_fill(key_padding_mask[:, :, None], 0.0)
     return x
 
@@ -310,14 +312,15 @@ def pad_objects(object_features, S: Optional[int] = None):
     return F.pad(padded, (0, 0, amt, 0), value=0.0001), F.pad(mask, (0, amt), value=True)
 
 
-def saca_forward(sd: SD, pre: str, image_tokens, object_features, no_obj_sa: bool = False):
+def saca_forward(sd: SD, pre: str, image_tokens, object_features, no_obj_sa: bool = False, fast_path: bool = True):
     """``SelfAttnCrossAttn.forward`` (``ObjCAViT.py:167-213``)."""
     att_img = transformer_encoder(sd, pre + "image_transformer_encoder.", image_tokens)        # :169
     obj, mask = pad_objects(object_features)                                                   # :180-183
     if no_obj_sa:
         att_obj = obj                                                                          # :186
     else:
-        att_obj = transformer_encoder(sd, pre + "obj_transformer_encoder.", obj, key_padding_mask=mask)  # :188
+        att_obj = transformer_encoder(sd, pre + "obj_transformer_encoder.", obj, key_padding_mask=mask,
+                                      fast_path=fast_path)                                     # :188
     S = att_img.shape[1]
     amt = S - att_obj.shape[1]                                                                 # :192
     kpm = F.pad(mask, (0, amt), value=True)                                                    # :193 (right pad)
@@ -346,7 +349,7 @@ def patch_coords(B: int, gh: int, gw: int, patch_size: int = 16):
 def objcavit_forward(sd: SD, image_features, object_features: List[torch.Tensor],
                      object_xywh_list: List[Optional[torch.Tensor]], strategy: str,
                      pre: str = "", no_obj_sa: bool = False, use_2_saca: bool = False,
-                     n_query_channels: int = 128, norm: str = "linear", patch_size: int = 16):
+                     n_query_channels: int = 128, norm: str = "linear", patch_size: int = 16, fast_path: bool = True):
     """``ObjCAViT.forward`` (``ObjCAViT.py:306-390``) -> ``(bin_widths_normed, ram)``.
     Does NOT mutate the caller's list (the reference does, F11; the product wrapper mimics that)."""
     B, _, h, w = image_features.shape
@@ -384,9 +387,9 @@ def objcavit_forward(sd: SD, image_features, object_features: List[torch.Tensor]
         ipos = _pos_mlp(sd, pre + "positional_encoder.", pc[..., 0:2])
     tok = pe.flatten(2).permute(0, 2, 1) + ipos                                    # :362-364
 
-    tok, obj_out = saca_forward(sd, pre + "saca_1.", tok, objs, no_obj_sa)         # :366
+    tok, obj_out = saca_forward(sd, pre + "saca_1.", tok, objs, no_obj_sa, fast_path)         # :366
     if use_2_saca:
-        tok, obj_out = saca_forward(sd, pre + "saca_2.", tok, obj_out, no_obj_sa)  # :368
+        tok, obj_out = saca_forward(sd, pre + "saca_2.", tok, obj_out, no_obj_sa, fast_path)  # :368
 
     regression_head, queries = tok[:, 0, :], tok[:, 1:n_query_channels + 1, :]     # :373
     xc = F.conv2d(image_features, sd[pre + "conv3x3.weight"], sd[pre + "conv3x3.bias"], padding=1)  # :374
@@ -403,7 +406,7 @@ def head_forward(sd: SD, cfg: dict, features, object_features=None, object_xywh_
     else:
         y, ram = objcavit_forward(sd, features, object_features, object_xywh_list, cfg["strategy"],
                                   pre="objcavit.", no_obj_sa=cfg.get("no_obj_sa", False),
-                                  use_2_saca=cfg.get("use_2_saca", False))
+                                  use_2_saca=cfg.get("use_2_saca", False), fast_path=not cfg.get("train", False))
     depth, edges = head_tail(sd, ram, y, cfg["min_depth"], cfg["max_depth"])
     return depth, edges, y, ram
 

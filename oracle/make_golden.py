@@ -24,7 +24,7 @@ sys.path.insert(0, ROOT)
 from objcavit_b200.config import builtin_args  # noqa: E402  (args loader only; no kernels involved)
 from oracle import head as oh  # noqa: E402
 from oracle import synth  # noqa: E402
-from oracle.cases import CASES, case_cfg, case_inputs  # noqa: E402
+from oracle.cases import CASES, TRAIN_CASES, case_cfg, case_gt, case_inputs, grad_probe_indices  # noqa: E402
 from oracle.ref_shim import ReferenceHead, import_reference  # noqa: E402
 
 GOLD = os.path.join(ROOT, "tests", "golden")
@@ -117,6 +117,70 @@ def pin_losses():
     torch.save(dict(depth=depth, silog=want, edges=edges, chamfer=b), os.path.join(GOLD, "losses.pt"))
 
 
+GRAD_FLOOR = 1e-3   # per-parameter gradient error is relative to max(|g|_max, GRAD_FLOOR * largest |g| of the head)
+
+
+def training_loss(depth, edges, gt, mask):
+    """config 5: 1 * SILog + 0.1 * BinsChamfer (``params/*.yaml`` loss.names / loss.coeffs)."""
+    return oh.silog_loss(depth, gt, mask) + 0.1 * oh.bins_chamfer_loss(edges, gt, mask)
+
+
+def run_train_case(name: str):
+    """Gradients of the training loss w.r.t. every head parameter from the UNMODIFIED reference modules in train() mode with
+    dropout disabled ("parity of grads checked with dropout disabled"), pinned against autograd through
+    the restatement (``train=True``: slow-path semantics), stored as a compact fixture: per-parameter L2 norm, sum and 8 probes."""
+    case = TRAIN_CASES[name]
+    args = builtin_args(case["args"])
+    torch.manual_seed(0)
+    ref = ReferenceHead(args).train()
+    for m in ref.modules():
+        if isinstance(m, torch.nn.Dropout):
+            m.p = 0.0
+        if isinstance(m, torch.nn.MultiheadAttention):
+            m.dropout = 0.0
+    with open(os.path.join(GOLD, f"manifest_{case['args']}.json")) as f:
+        manifest = json.load(f)
+    sd = synth.make_state_dict(manifest, seed=case["seed"])
+    ref.load_state_dict(sd, strict=True)
+    feats, objs, boxes = case_inputs(case)
+    gt, mask = case_gt(case, args)
+    if objs is None:
+        depth, edges, _, _ = ref(feats)
+    else:
+        depth, edges, _, _ = ref(feats, [o.clone() for o in objs], copy.deepcopy(boxes))
+    silog_ref = import_reference().SILogLoss(None)(depth, gt, mask)
+    loss = silog_ref + 0.1 * oh.bins_chamfer_loss(edges, gt, mask)          # chamfer: restatement (pytorch3d unavailable)
+    loss.backward()
+    ref_grads = {k: p.grad for k, p in ref.named_parameters()}
+    # restatement under autograd
+    sd_g = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    cfg = dict(case_cfg(case, args), train=True)
+    o_depth, o_edges, _, _ = oh.head_forward(sd_g, cfg, feats, objs, boxes)
+    o_loss = training_loss(o_depth, o_edges, gt, mask)
+    o_loss.backward()
+    worst = 0.0
+    gmax = max(float(g.abs().max()) for g in ref_grads.values() if g is not None)
+    fixture = {}
+    for k, g in ref_grads.items():
+        og = sd_g[k].grad
+        if g is None:
+            assert og is None or float(og.abs().max()) == 0.0, f"{name}: {k} has no reference gradient but the oracle gives one"
+            fixture[k] = None
+            continue
+        assert og is not None, f"{name}: oracle gives no gradient for {k}"
+        # parameters whose true gradient is a rounding-noise cancellation (e.g. the block-2 object path: |g| ~ 1e-9 of the
+        # largest gradient) are compared on the global scale
+        err = float((og - g).abs().max()) / max(float(g.abs().max()), GRAD_FLOOR * gmax)
+        worst = max(worst, err)
+        idx = torch.tensor(grad_probe_indices(g.numel()))
+        fixture[k] = dict(norm=g.double().norm().float(), sum=g.double().sum().float(), probes=g.flatten()[idx].clone())
+    print(f"[pin] {name}: largest |grad| {gmax:.3e}; loss ref {float(loss):.6f} oracle {float(o_loss):.6f}; worst per-parameter grad rel err {worst:.2e}; "
+          f"{sum(v is None for v in fixture.values())} parameters without gradient")
+    assert abs(float(loss) - float(o_loss)) < 1e-5 * abs(float(loss)) and worst < 2e-3, f"{name}: restatement gradients differ"
+    torch.save(dict(loss=loss.detach(), gmax=torch.tensor(gmax), depth=depth.detach()[:, :, ::4, ::4].contiguous(), bin_edges=edges.detach(), grads=fixture),
+               os.path.join(GOLD, f"{name}.pt"))
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(max(1, os.cpu_count() or 1))
@@ -124,6 +188,8 @@ def main():
     pin_losses()
     for name in CASES:
         run_case(name)
+    for name in TRAIN_CASES:
+        run_train_case(name)
     print("golden fixtures written to", GOLD)
 
 

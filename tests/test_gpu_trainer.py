@@ -1,0 +1,94 @@
+"""GPU: the native training step (objcavit_b200/trainer.py) against torch: flat-buffer gradients equal the autograd-boundary
+gradients, and clip + AdamW (+ OneCycle momentum cycling) equals ``clip_grad_norm_`` + ``torch.optim.AdamW`` + ``OneCycleLR``."""
+import json
+import os
+
+import pytest
+import torch
+
+from helpers import GOLD, rel_err
+from objcavit_b200 import ops
+from objcavit_b200.config import builtin_args
+from objcavit_b200.modules import build_head
+from objcavit_b200.trainer import HeadTrainer, OneCycle
+from oracle import synth
+from oracle.cases import TRAIN_CASES, case_gt, case_inputs
+
+pytestmark = pytest.mark.gpu
+
+
+def test_onecycle_matches_torch():
+    p = torch.nn.Parameter(torch.zeros(1))
+    opt = torch.optim.AdamW([p], lr=0.000357)
+    sch = torch.optim.lr_scheduler.OneCycleLR(opt, max_lr=0.000357, total_steps=50, cycle_momentum=True, base_momentum=0.85,
+                                              max_momentum=0.95, div_factor=25, final_div_factor=100)
+    mine = OneCycle(0.000357, 50, 25, 100)
+    for i in range(50):
+        lr, b1 = mine.at(i)
+        assert abs(lr - opt.param_groups[0]["lr"]) < 1e-12 and abs(b1 - opt.param_groups[0]["betas"][0]) < 1e-12
+        opt.step()
+        sch.step()
+
+
+def test_sumsq_and_adamw_against_torch(cuda):
+    g = torch.Generator().manual_seed(0)
+    n = 100003 * 4
+    p0 = torch.randn(n, generator=g)
+    ref = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.AdamW([ref], lr=3.57e-4, weight_decay=0.1)
+    sch = torch.optim.lr_scheduler.OneCycleLR(opt, max_lr=3.57e-4, total_steps=10, cycle_momentum=True, base_momentum=0.85,
+                                              max_momentum=0.95, div_factor=25, final_div_factor=100)
+    mine = OneCycle(3.57e-4, 10, 25, 100)
+    p = p0.clone().to(cuda)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    for step in range(1, 6):
+        grad = torch.randn(n, generator=g) * (0.01 if step % 2 else 10.0)      # below / above the clipping threshold
+        ref.grad = grad.clone()
+        norm = torch.nn.utils.clip_grad_norm_([ref], 0.1 if step > 1 else 1e9)
+        opt.step(); sch.step()
+        gd = (grad * 2.0).to(cuda)                                              # "sum over 2 ranks", scaled back by 0.5
+        ss = ops.sumsq(gd, 0.5)
+        assert rel_err(ss.sqrt(), norm.view(1)) < 1e-5
+        lr, b1 = mine.at(step - 1)
+        ops.adamw_step(p, gd, m, v, lr, b1, 0.999, 1e-8, 0.1, step, grad_scale=0.5, grad_sumsq=ss if step > 1 else None,
+                       max_norm=0.1)
+        assert rel_err(p, ref.data) < 2e-6, step
+    assert torch.equal(ops.sumsq(gd, 0.5), ops.sumsq(gd, 0.5))                  # deterministic
+
+
+def test_trainer_step_equals_autograd_boundary_plus_torch_adamw(cuda):
+    name = "train_learned_bbox_wh_small"
+    case = TRAIN_CASES[name]
+    args = builtin_args(case["args"])
+    with open(os.path.join(GOLD, f"manifest_{case['args']}.json")) as f:
+        sd = synth.make_state_dict(json.load(f), seed=case["seed"])
+    feats, objs, boxes = case_inputs(case)
+    gt, mask = case_gt(case, args)
+    dev = lambda lst: [None if t is None else t.to(cuda) for t in lst]
+    # torch side: the autograd boundary + torch's clip + AdamW
+    from objcavit_b200.config import AttrDict
+    from objcavit_b200.losses import LossWrapper
+    a = build_head(args).to(cuda).train(); a.load_state_dict(sd)
+    opt = torch.optim.AdamW(a.parameters(), lr=3.57e-4, weight_decay=0.1)
+    out = a(feats.to(cuda), dev(objs), dev(boxes))
+    loss = LossWrapper(AttrDict({"loss": {"names": ["silog", "bins_chamfer"], "coeffs": [1, 0.1]}}))(
+        out.depth_pred, gt.to(cuda), mask.to(cuda), out)
+    loss.backward()
+    torch.nn.utils.clip_grad_norm_([p for p in a.parameters() if p.grad is not None], 0.1)
+    opt.step()
+    # native step
+    b = build_head(args).to(cuda).train(); b.load_state_dict(sd)
+    tr = HeadTrainer(b, lr=3.57e-4, weight_decay=0.1, clip_grad_norm=0.1)
+    l1, l2 = tr.step(feats.to(cuda), dev(objs), dev(boxes), gt.to(cuda), mask.to(cuda))
+    torch.cuda.synchronize()
+    assert abs(tr.loss_value(l1, l2) - float(loss)) < 1e-5 * abs(float(loss))
+    pa = dict(a.named_parameters())
+    for k, p in b.named_parameters():
+        if pa[k].grad is None:       # torch skips parameters without gradient entirely (no weight decay either): F10
+            assert torch.equal(p.data.cpu(), sd[k]), f"{k}: a parameter without gradient was modified"
+            continue
+        assert rel_err(p.data, pa[k].data) < 1e-5, k
+    assert set(b.state_dict()) == set(sd)                                       # checkpoint surface unchanged by the flat buffers
+    with torch.no_grad():                                                       # and inference still runs on the updated weights
+        o2 = b.eval()(feats.to(cuda), dev(objs), dev(boxes))
+    assert torch.isfinite(o2.depth_pred).all()

@@ -48,10 +48,14 @@ def test_no_cpu_fallback():
         head(torch.randn(1, 128, 176, 192))
 
 
-def test_training_mode_is_refused_not_silently_wrong():
+def test_training_mode_has_no_cpu_path_either():
+    """Grad mode routes the head through the training kernels (engine_train): on CPU tensors that must raise, never fall
+    back to torch ops; gradients w.r.t. the (frozen-extractor) features are refused explicitly."""
     head = AdaBinsHead(builtin_args("nyu_adabins"))
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(_lib.OcvError):
         head(torch.randn(1, 128, 176, 192))
+    with pytest.raises(NotImplementedError):
+        head(torch.randn(1, 128, 176, 192, requires_grad=True))
 
 
 def test_attrdict_access_styles():
