@@ -143,6 +143,127 @@ def run_reference(a):
     }))
 
 
+# ---- config 5: the training step ----------------------------------------------------------------------------------
+TRAIN_H, TRAIN_W = 208, 272          # NYU-train features of a 416x544 crop
+GF_TRAIN = 56.5                      # algorithmic GFLOP / image / step (fwd 25.02 + bwd 31.5)
+
+
+def run_train(a):
+    """--workload train: BASELINE.json configs[4] — frozen features + ObjCAViT head fwd/bwd, SILog + 0.1 chamfer, one all-reduce
+    of the flat head-gradient buffer, clip 0.1, AdamW + OneCycle; batch 8 per GPU (weak scaling)."""
+    from objcavit_b200 import ops
+    from objcavit_b200.config import builtin_args
+    from objcavit_b200.modules import build_head
+    from objcavit_b200.trainer import HeadTrainer, OneCycle
+    from oracle import synth
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback)"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+    B = a.batch if a.batch != 16 else 8
+    W_, K = max(a.warmup, 3), a.steps
+    head = build_head(builtin_args(CFG_NAME), precision="fp32").to(dev).train()
+    head.load_state_dict(load_weights(CFG_NAME), strict=True)
+    trainer = HeadTrainer(head, lr=0.000357, weight_decay=0.1, clip_grad_norm=0.1,
+                          schedule=OneCycle(0.000357, max(W_ + 3 * K + 16, 100), 25, 100))
+    feats = synth.make_features(B, TRAIN_H, TRAIN_W, seed=1234 + rank)
+    objs, boxes = synth.make_objects(B, TRAIN_H, TRAIN_W, NOBJ, seed=1234 + rank)
+    gt, mask = synth.make_gt(B, TRAIN_H, TRAIN_W, 10.0, seed=1234 + rank)
+    host = dict(x=feats.pin_memory(), gt=gt.pin_memory(), mask=mask.pin_memory(), objs=[o.pin_memory() for o in objs],
+                boxes=[b.pin_memory() for b in boxes])
+    x_dev, gt_dev, mask_dev = host["x"].to(dev), host["gt"].to(dev), host["mask"].to(dev)
+    objs_dev, boxes_dev = [o.to(dev) for o in host["objs"]], [b.to(dev) for b in host["boxes"]]
+
+    def step():
+        return trainer.step(x_dev, list(objs_dev), boxes_dev, gt_dev, mask_dev)
+
+    def e2e_step():
+        x = host["x"].to(dev, non_blocking=True)
+        g = host["gt"].to(dev, non_blocking=True)
+        m = host["mask"].to(dev, non_blocking=True)
+        ob = [o.to(dev, non_blocking=True) for o in host["objs"]]
+        bx = [b.to(dev, non_blocking=True) for b in host["boxes"]]
+        l1, l2 = trainer.step(x, ob, bx, g, m)
+        return trainer.loss_value(l1, l2)            # D2H read of the step's result (the loss)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = e0.elapsed_time(e1)
+        if dist is not None:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        return ms
+
+    for _ in range(W_):
+        step()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ops.launch_count
+    ms = timed(step, K)
+    launches = ops.launch_count - l0
+    clocks = sampler.stop() if rank == 0 else None
+    value = world * B * K / (ms * 1e-3)
+    # per-entry-point breakdown of one step (CUDA events around every C-ABI call on the launching stream)
+    ops.profile_events = []
+    step()
+    torch.cuda.synchronize()
+    agg = {}
+    for name, e0, e1 in ops.profile_events:
+        agg[name] = agg.get(name, 0.0) + e0.elapsed_time(e1)
+    ops.profile_events = None
+    top = sorted(agg.items(), key=lambda kv: -kv[1])
+    dom, dom_ms = top[0]
+    pk = peaks()
+    step_tf = GF_TRAIN * B * K / ms                  # GFLOP/ms == TFLOP/s, whole step on the algorithmic FLOPs
+    roofline = {"bound": "tensor", "kernel": f"{dom} (fp32 SIMT; all calls of one step)", "achieved": step_tf,
+                "peak": pk["tf_sust"], "unit": "TFLOP/s", "frac": step_tf / pk["tf_sust"], "traffic": None,
+                "peak_source": pk["src"] + " (bf16 sustained); achieved = 56.5 GF/image x images/s of the WHOLE step",
+                "kernel_ms": dom_ms, "kernel_share_of_step": dom_ms / max(sum(agg.values()), 1e-9),
+                "breakdown_ms": {k: round(v, 3) for k, v in top[:10]}}
+    for _ in range(3):
+        e2e_step()
+    ms_e2e = timed(e2e_step, K)
+    h2d = sum(t.numel() * t.element_size() for t in (host["x"], host["gt"], host["mask"])) + \
+        sum(t.numel() * 4 for t in host["objs"] + host["boxes"])
+    out = {
+        "metric": "ObjCAViT head training images/sec (config 5: fwd+bwd, SILog+BinsChamfer, grad all-reduce, AdamW)",
+        "value": value, "unit": "images/s", "n_gpus": world, "steps": K, "warmup": W_, "ms_per_step": ms / K,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": f"{CFG_NAME} head training step, {NOBJ} boxes/img, frozen features 128x{TRAIN_H}x{TRAIN_W} fp32, "
+                               f"GT {2 * TRAIN_H}x{2 * TRAIN_W}, batch {B}/GPU, dropout disabled",
+                   "batch_per_gpu": B, "parallelism": f"dp{world} (batch sharded, one all-reduce of "
+                                                      f"{trainer.grads.flat.numel() * 4 / 1e6:.1f} MB head gradients per step)",
+                   "l2": f"activations {B * 256 * TRAIN_H * TRAIN_W * 4 / 1e6:.0f} MB logits per step > 126 MB L2, no explicit flush"},
+        "gpu_launches": launches, "roofline": roofline, "clocks": clocks,
+        "e2e": {"value": world * B * K / (ms_e2e * 1e-3), "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
+                "ms_per_step": ms_e2e / K},
+    }
+    if rank == 0:
+        print(json.dumps(out))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -152,9 +273,13 @@ def main():
     ap.add_argument("--precision", default=None, choices=[None, "bf16", "fp32"])
     ap.add_argument("--batch", type=int, default=16, help="images per GPU per step")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="infer", choices=["infer", "train"],
+                    help="infer = BASELINE.json configs[1] (the headline line); train = configs[4] (the training step)")
     a = ap.parse_args()
     if a.impl == "reference":
         return run_reference(a)
+    if a.workload == "train":
+        return run_train(a)
 
     from objcavit_b200 import ops
     from objcavit_b200.config import builtin_args
