@@ -334,6 +334,19 @@ long long ocv_head_workspace_bytes(const ocv_head* head, int B, int h, int w, in
 int ocv_head_forward(ocv_head* head, const void* X_nhwc_bf16, const float* obj_feat, const float* obj_xywh,
                      const int32_t* obj_offsets, int total_obj, int n_max, int B, int h, int w, float* depth,
                      float* bin_edges, float* obj_tokens_out, void* workspace, void* stream);
+/* Pipelined serving mode (opt-in; lanes = 0 restores the classic mode where everything runs on the caller's stream).
+ * With lanes = L in 1..4, call i of ocv_head_forward runs its token path on lane i % L (the head's own streams, ordered after
+ * the caller's stream at call time) and its fused pixel kernel on ONE shared pixel stream with at most pixel_ctas CTAs
+ * (0 = one per SM), so the latency-bound token chains of the next calls overlap the tensor-bound pixel kernel of this one.
+ * `workspace` must then hold L x ocv_head_workspace_bytes' single-lane size (ocv_head_workspace_bytes already reports the
+ * multiplied size once the mode is set).  The call returns WITHOUT ordering the caller's stream after the work:
+ *   - outputs (depth, bin_edges, obj_tokens_out) are valid on `stream` only after ocv_head_join(head, stream);
+ *   - X and the object inputs must stay untouched until then; set_param / pack require a join first.
+ * ocv_head_stream: the head's internal streams (which: 0 token lane, 1 side lane, 2 pixel stream) so that a caching
+ * allocator can be told about them (torch: Tensor.record_stream). */
+int ocv_head_set_pipeline(ocv_head* head, int lanes, int pixel_ctas);
+int ocv_head_join(ocv_head* head, void* stream);
+void* ocv_head_stream(const ocv_head* head, int which, int lane);
 /* number of kernel launches the last ocv_head_forward issued */
 int ocv_head_last_launches(const ocv_head* head);
 /* Measurement aid (bench.py): when enabled, ocv_head_forward brackets the fused pixel kernel with CUDA events on the

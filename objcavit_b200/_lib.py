@@ -79,6 +79,9 @@ PROTOTYPES = {
     "ocv_head_workspace_bytes": (i64, [p, i32, i32, i32, i32, i32]),
     "ocv_head_forward": (i32, [p, p, p, p, p, i32, i32, i32, i32, i32, p, p, p, p, p]),
     "ocv_head_last_launches": (i32, [p]),
+    "ocv_head_set_pipeline": (i32, [p, i32, i32]),
+    "ocv_head_join": (i32, [p, p]),
+    "ocv_head_stream": (p, [p, i32, i32]),
     "ocv_head_enable_timing": (i32, [p, i32]),
     "ocv_head_pixel_ms": (f32, [p]),
 }

@@ -205,6 +205,9 @@ def head_forward(head, P, pre, x, object_features, object_xywh_list, lo, hi, mut
             nh = ops.NativeHead(1, oc.strategy, oc.no_obj_sa, oc.use_2_saca, head.args.graphbins.n_bins,
                                 oc.obj_embedding_layer.in_features, lo, hi)
         head.__dict__["_ocv_native"] = nh
+        pipe = head.__dict__.get("_ocv_pipeline")
+        if pipe:
+            nh.set_pipeline(*pipe)
     nh.bind(P)
     if object_features is None:
         return nh.forward(x_nhwc, None, None, None, 0, 0)

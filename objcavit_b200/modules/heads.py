@@ -54,6 +54,22 @@ class _HeadTrainFn(torch.autograd.Function):
 class _HeadBase(KernelModule):
     precision = "fp32"   # "fp32": parity path (SIMT fp32).  "bf16": tensor-core path (tcgen05).
 
+    def enable_pipeline(self, lanes: int = 2, pixel_ctas: int = 0):
+        """Pipelined serving mode of the bf16 path (``ocv_head_set_pipeline``): consecutive ``forward`` calls overlap — the
+        latency-bound token path of call i+1 runs next to the tensor-bound fused pixel kernel of call i.  Calls return
+        immediately; outputs are valid on the current stream only after :meth:`join`, and the inputs of a call must stay
+        untouched until then.  ``lanes=0`` switches back."""
+        assert self.precision == "bf16", "the pipelined mode drives the bf16 throughput path"
+        self.__dict__["_ocv_pipeline"] = (int(lanes), int(pixel_ctas)) if lanes else None
+        nh = self.__dict__.get("_ocv_native")
+        if nh is not None:
+            nh.set_pipeline(int(lanes), int(pixel_ctas))
+
+    def join(self):
+        nh = self.__dict__.get("_ocv_native")
+        if nh is not None:
+            nh.join()
+
     def _wants_grad(self, x):
         return torch.is_grad_enabled() and (any(p.requires_grad for p in self.parameters()) or
                                             (torch.is_tensor(x) and x.requires_grad))

@@ -433,6 +433,39 @@ class NativeHead:
         self.packed = None
         self.sig = None
         self.ws = None
+        self.lanes = 0
+        self._lane_streams = []
+
+    def set_pipeline(self, lanes: int, pixel_ctas: int = 0):
+        """Opt into the pipelined serving mode of ``ocv_head_set_pipeline`` (``lanes`` = 0: back to the classic mode)."""
+        L = _lib.lib()
+        if self.lanes:
+            self.join()
+        self._check(L.ocv_head_set_pipeline(self._h, int(lanes), int(pixel_ctas)), "ocv_head_set_pipeline")
+        self.lanes = int(lanes)
+        self.ws = None
+        self._lane_streams = []
+        self._calls = 0
+        if lanes:
+            self._pix_stream = torch.cuda.ExternalStream(int(L.ocv_head_stream(self._h, 2, 0)))
+            self._lane_streams = [torch.cuda.ExternalStream(int(L.ocv_head_stream(self._h, 0, i))) for i in range(lanes)]
+
+    def join(self):
+        """Order the current stream after every outstanding pipelined call (outputs become valid on it)."""
+        if self.lanes:
+            self._check(_lib.lib().ocv_head_join(self._h, _stream()), "ocv_head_join")
+
+    def _hold(self, x_nhwc, depth, small):
+        # tensors allocated on the caller's stream but used on the head's internal streams: tell the caching allocator.
+        # The small object inputs / outputs only meet the lane's token stream (they are staged through lane-static buffers).
+        tok = self._lane_streams[self._calls % self.lanes]
+        self._calls += 1
+        x_nhwc.record_stream(tok)
+        x_nhwc.record_stream(self._pix_stream)
+        depth.record_stream(self._pix_stream)
+        for t in small:
+            if t is not None:
+                t.record_stream(tok)
 
     def __del__(self):
         try:
@@ -455,6 +488,9 @@ class NativeHead:
         if sig == self.sig:
             return
         L = _lib.lib()
+        if self.lanes:          # lanes may still read the old derived copies
+            self.join()
+            torch.cuda.current_stream().synchronize()
         for k, v in P.items():
             _chk(v, torch.float32, k)
             assert v.is_contiguous()
@@ -477,6 +513,9 @@ class NativeHead:
         if need < 0:
             _lib.check(int(need), "ocv_head_workspace_bytes")
         if self.ws is None or self.ws.numel() < need or self.ws.device != x_nhwc.device:
+            if self.lanes and self.ws is not None:      # outstanding lanes still use the old workspace
+                self.join()
+                torch.cuda.current_stream().synchronize()
             self.ws = torch.empty(need, device=x_nhwc.device, dtype=torch.uint8)
         depth = torch.empty(B, 1, h, w, device=x_nhwc.device, dtype=torch.float32)
         edges = torch.empty(B, self.n_bins + 1, device=x_nhwc.device, dtype=torch.float32)
@@ -495,6 +534,8 @@ class NativeHead:
             e1.record()
             timed_events.append((e0, e1))
         launch_count += L.ocv_head_last_launches(self._h)
+        if self.lanes:
+            self._hold(x_nhwc, depth, (feats, boxes, offsets, obj_tokens_out, edges))
         return depth, edges
 
 
