@@ -280,6 +280,35 @@ long long ocv_bins_chamfer_workspace(int B, int K);
 int ocv_bins_chamfer(const float* bin_edges, const float* depth_gt, const uint8_t* depth_mask, int B, int K, long long HW,
                      float grad_scale, float* loss, float* grad_edges, void* workspace, void* stream);
 
+/* ---- rows either side of the head -------------------------------------------------------------------
+ * Test-time-augmentation merge: out = 0.5 * (clamp(depth, lo, hi) + clamp(flip_w(depth_mirror), lo, hi)); NaN stays NaN like
+ *   torch.clamp; depth_mirror NULL -> out = clamp(depth).  All [B,1,h,w].
+ * replaces: modules/GraphBinsLM.py:159-183 (clamp x2, flip, average). */
+int ocv_tta_merge_f32(const float* depth, const float* depth_mirror, float* out, int B, int h, int w, float min_depth,
+                      float max_depth, void* stream);
+/* Evaluation metrics in one pass over the ground truth: depth_pred [B,1,h,w] is up-sampled bilinearly (align_corners=True) to
+ *   [B,1,H,W], nan -> min_depth, +-inf -> max_depth, mask = gt > min_depth && gt <= max_depth && inside crop_host = {y0,y1,x0,x1}
+ *   (NULL = no crop; the Garg / Eigen rectangles are the caller's), then the NINE fp64 sums
+ *   {sum |gt-p|/gt, sum (gt-p)^2/gt, sum (gt-p)^2, sum (ln gt - ln p)^2, sum |log10 gt - log10 p|, #(thr<1.25), #(thr<1.25^2),
+ *    #(thr<1.25^3), #valid}  with thr = max(gt/p, p/gt)
+ *   are written to sums[9] (this call, optional) and ADDED to acc[9] (running state over batches, optional; sum-reduce it
+ *   across ranks).  upsampled_out [B,1,H,W] optional.  Deterministic (two-stage fixed-order reduction).
+ *   workspace: ocv_depth_metrics_workspace() bytes.
+ * replaces: metrics/MetricsPreprocess.py:17-45 + the update() of metrics/{AbsRel,SqRel,RMSE,RMSELog,Log10,AccThresh}.py
+ *   (modules/GraphBinsLM.py:198-222). */
+long long ocv_depth_metrics_workspace(void);
+int ocv_depth_metrics_f32(const float* depth_pred, const float* depth_gt, int B, int h, int w, int H, int W, float min_depth,
+                          float max_depth, const int* crop_host, float* upsampled_out, double* sums, double* acc, void* workspace,
+                          void* stream);
+/* Object front-end glue: detections of image b are rows [offsets[b], offsets[b+1]) of xyxy [total,4] (corner boxes); written in
+ *   REVERSED order per image when `reverse` (the reference's reversed(det)), as centre/size boxes xywh [total,4]; size_bucket
+ *   [total] int32 (optional) = index into the relative-size scale (n_scale entries, 7 in the reference) comparing each object's
+ *   box area with the NEXT object's: clip(round((ln(a_i/a_next)+1)/2*(n_scale-3))+1, 0, n_scale-1); -1 for a lone object;
+ *   INT_MIN where the reference would raise (non-positive / NaN area ratio).  Bit-exact index work.
+ * replaces: modules/Yolov7Wrapper.py:118-123 (reversed + xyxy2xywh) and modules/ObjectLanguageStrategy.py:61-81. */
+int ocv_object_glue_f32(const float* xyxy, const int32_t* offsets, float* xywh, int32_t* size_bucket, int B, int n_max, int reverse,
+                        int n_scale, void* stream);
+
 /* ---- optimizer step on flat buffers (config 5) ---------------------------------------------------------------------------
  * out[0] = scale^2 * sum x^2 (fixed-order two-stage reduction; deterministic).  workspace: ocv_sumsq_workspace() bytes.
  * ocv_adamw_step_f32: torch.optim.AdamW semantics on flat param / grad / exp_avg / exp_avg_sq buffers (16-byte aligned):

@@ -61,6 +61,10 @@ PROTOTYPES = {
                                    i64, i32, i64, i32, i64, i32, p, p]),
     "ocv_tail_bwd_f32": (i32, [p, p, p, p, p, i32, i32, i64, p]),
     "ocv_unpad_objects_f32": (i32, [p, p, p, i32, i32, i32, i32, i32, f32, p]),
+    "ocv_tta_merge_f32": (i32, [p, p, p, i32, i32, i32, f32, f32, p]),
+    "ocv_depth_metrics_workspace": (i64, []),
+    "ocv_depth_metrics_f32": (i32, [p, p, i32, i32, i32, i32, i32, f32, f32, p, p, p, p, p, p]),
+    "ocv_object_glue_f32": (i32, [p, p, p, p, i32, i32, i32, i32, p]),
     "ocv_sumsq_workspace": (i64, [i64]),
     "ocv_sumsq_f32": (i32, [p, i64, f32, p, p, p]),
     "ocv_adamw_step_f32": (i32, [p, p, p, p, i64, f32, f32, f32, f32, f32, i32, f32, p, f32, p]),

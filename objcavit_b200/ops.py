@@ -764,3 +764,48 @@ def adamw_step(param: torch.Tensor, grad: torch.Tensor, exp_avg: torch.Tensor, e
     _call("ocv_adamw_step_f32", param.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(), param.numel(), float(lr),
           float(beta1), float(beta2), float(eps), float(weight_decay), int(step), float(grad_scale), _ptr(grad_sumsq), float(max_norm),
           _stream())
+
+
+# ---- rows either side of the head -------------------------------------------------
+
+def tta_merge(depth: torch.Tensor, depth_mirror, min_depth: float, max_depth: float) -> torch.Tensor:
+    """0.5 * (clamp(depth) + clamp(flip_w(depth_mirror))) (``GraphBinsLM.py:159-183``); ``depth_mirror`` None -> clamp only."""
+    _chk(depth, torch.float32, "depth")
+    assert depth.is_contiguous() and (depth_mirror is None or (depth_mirror.is_contiguous() and depth_mirror.shape == depth.shape))
+    B, _, h, w = depth.shape
+    out = torch.empty_like(depth)
+    _call("ocv_tta_merge_f32", depth.data_ptr(), _ptr(depth_mirror), out.data_ptr(), B, h, w, float(min_depth), float(max_depth),
+          _stream())
+    return out
+
+
+def depth_metrics(depth_pred: torch.Tensor, depth_gt: torch.Tensor, min_depth: float, max_depth: float, crop=None, acc=None,
+                  want_upsampled: bool = False):
+    """-> (sums [9] float64 of this call, up-sampled prediction | None); ``acc`` [9] float64 is incremented in place."""
+    import ctypes as C
+    _chk(depth_pred, torch.float32, "depth_pred"); _chk(depth_gt, torch.float32, "depth_gt")
+    assert depth_pred.is_contiguous() and depth_gt.is_contiguous()
+    B, _, h, w = depth_pred.shape
+    _, _, H, W = depth_gt.shape
+    sums = torch.empty(9, device=depth_pred.device, dtype=torch.float64)
+    up = torch.empty_like(depth_gt) if want_upsampled else None
+    if acc is not None:
+        assert acc.dtype == torch.float64 and acc.is_cuda and acc.numel() == 9 and acc.is_contiguous()
+    ws = _workspace(_lib.lib().ocv_depth_metrics_workspace(), depth_pred.device, "metrics")
+    c = (C.c_int * 4)(*[int(v) for v in crop]) if crop is not None else None
+    _call("ocv_depth_metrics_f32", depth_pred.data_ptr(), depth_gt.data_ptr(), B, h, w, H, W, float(min_depth), float(max_depth), c,
+          _ptr(up), sums.data_ptr(), _ptr(acc), ws.data_ptr(), _stream(), launches=2)
+    return sums, up
+
+
+def object_glue(xyxy: torch.Tensor, offsets: torch.Tensor, n_max: int, reverse: bool = True, n_scale: int = 7,
+                want_bucket: bool = True):
+    """corner boxes (CSR per image) -> (centre/size boxes [total,4], relative-size bucket [total] int32 | None)."""
+    _chk(xyxy, torch.float32, "xyxy"); _chk(offsets, torch.int32, "offsets")
+    assert xyxy.is_contiguous() and xyxy.shape[1] == 4
+    B = offsets.numel() - 1
+    xywh = torch.empty_like(xyxy)
+    bucket = torch.empty(xyxy.shape[0], device=xyxy.device, dtype=torch.int32) if want_bucket else None
+    _call("ocv_object_glue_f32", xyxy.data_ptr(), offsets.data_ptr(), xywh.data_ptr(), _ptr(bucket), B, int(n_max), int(reverse),
+          int(n_scale), _stream())
+    return xywh, bucket

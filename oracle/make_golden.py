@@ -117,6 +117,95 @@ def pin_losses():
     torch.save(dict(depth=depth, silog=want, edges=edges, chamfer=b), os.path.join(GOLD, "losses.pt"))
 
 
+def pin_eval():
+    """Rows N2-N4: the restatement in ``oracle/eval.py`` against the reference's own code, imported unmodified:
+    ``metrics/MetricsPreprocess.py`` (torch only), the six metric classes of ``metrics/*.py`` through a minimal ``torchmetrics``
+    stub (``Metric`` = nn.Module whose ``add_state`` sets an attribute, call = ``update``), and
+    ``ObjectLanguageStrategy.get_single_relative_size_clause`` through an ``nltk`` stub with a duck-typed ``self``."""
+    import types
+
+    import torch.nn as nn
+
+    from oracle import eval as oe
+    from oracle.ref_shim import REFERENCE_ROOT
+
+    class Metric(nn.Module):
+        def add_state(self, name, default, dist_reduce_fx=None):
+            setattr(self, name, default.clone())
+
+        def forward(self, *a, **kw):
+            return self.update(*a, **kw)
+
+    tm = types.ModuleType("torchmetrics")
+    tm.Metric = Metric
+    sys.modules.setdefault("torchmetrics", tm)
+    nl, nc = types.ModuleType("nltk"), types.ModuleType("nltk.corpus")
+    nc.wordnet = None
+    nl.corpus = nc
+    sys.modules.setdefault("nltk", nl)
+    sys.modules.setdefault("nltk.corpus", nc)
+    if REFERENCE_ROOT not in sys.path:
+        sys.path.insert(0, REFERENCE_ROOT)
+    import_reference()
+    from metrics.AbsRel import AbsRel  # type: ignore
+    from metrics.AccThresh import AccThresh  # type: ignore
+    from metrics.Log10 import Log10  # type: ignore
+    from metrics.MetricsPreprocess import MetricsPreprocess  # type: ignore
+    from metrics.RMSE import RMSE  # type: ignore
+    from metrics.RMSELog import RMSELog  # type: ignore
+    from metrics.SqRel import SqRel  # type: ignore
+    from modules.ObjectLanguageStrategy import ObjectLanguageStrategy  # type: ignore
+    from objcavit_b200.config import AttrDict
+
+    out = {}
+    for tag, c in oe.EVAL_CASES.items():
+        dataset, lo, hi, garg, eigen = c["dataset"], c["lo"], c["hi"], c["garg"], c["eigen"]
+        args = AttrDict({"basic": {"dataset": dataset},
+                         dataset: {"min_depth": lo, "max_depth": hi, "garg_crop": garg, "eigen_crop": eigen}})
+        a, b, gt = oe.eval_case_inputs(tag)
+        H, W = gt.shape[-2:]
+        # reference: validation_step lines 159-183 verbatim on the two passes
+        p1 = torch.clamp(a, min=lo, max=hi)
+        p2 = torch.clamp(b.flip(dims=[3]), min=lo, max=hi)
+        final = 0.5 * (p1 + p2)
+        pm, mask = MetricsPreprocess(args)(depth_pred=final.clone(), depth_gt=gt.clone())
+        pm_m, gt_m = pm[mask], gt[mask]
+        ms = [AbsRel(args), SqRel(args), RMSE(args), RMSELog(args), Log10(args), AccThresh(args, 1.25), AccThresh(args, 1.25 ** 2),
+              AccThresh(args, 1.25 ** 3)]
+        for m in ms:
+            m(depth_pred=pm_m.clone(), depth_gt=gt_m.clone())
+        ref_vals = torch.tensor([float(m.compute()) for m in ms])
+        # restatement
+        crop = oe.crop_rect(dataset, garg, eigen, H, W)
+        o_final = oe.tta_merge(a, b, lo, hi)
+        assert torch.equal(torch.isnan(o_final), torch.isnan(final)) and torch.equal(o_final.nan_to_num(), final.nan_to_num())
+        o_pm, o_mask = oe.metrics_preprocess(o_final, gt, lo, hi, crop)
+        assert torch.equal(o_mask, mask) and torch.equal(o_pm, pm)
+        sums = oe.metric_sums(o_pm[o_mask], gt[o_mask])
+        mv = oe.metrics_from_sums(sums)
+        got = torch.tensor([mv[k] for k in ("abs_rel", "sq_rel", "rmse", "rmse_log", "log10", "acc_1", "acc_2", "acc_3")])
+        err = float(((got - ref_vals).abs() / ref_vals.abs().clamp_min(1e-12)).max())
+        print(f"[pin] eval {tag}: metrics vs reference classes rel err {err:.2e}; valid {int(sums[8])} px")
+        assert err < 2e-5, (got, ref_vals)
+        out[tag] = dict(crop=crop, final=final[:, :, ::3, ::3].contiguous(), upsampled=pm[:, :, ::5, ::5].contiguous(), sums=sums,
+                        metrics=ref_vals)
+    # object glue
+    xyxy = oe.glue_case_inputs()
+    o_xywh, o_bucket = oe.object_glue(xyxy)
+    fake = types.SimpleNamespace(rel_size_scale=list(oe.REL_SIZE_SCALE), synset_to_name=lambda s: s)
+    names = [[f"obj{j}" for j in range(len(x))] for x in o_xywh]
+    clauses = ObjectLanguageStrategy.get_single_relative_size_clause(fake, o_xywh, None, None, None, names)
+    for cl, bl in zip(clauses, o_bucket):
+        for c, bi in zip(cl, bl):
+            if bi < 0:
+                assert c == ""
+            else:
+                assert f" appears {oe.REL_SIZE_SCALE[bi]} the " in c, (c, bi)
+    print(f"[pin] object glue: {sum(len(b) for b in o_bucket)} relative-size buckets match the reference clauses")
+    out["glue"] = dict(xywh=o_xywh, bucket=o_bucket)
+    torch.save(out, os.path.join(GOLD, "eval_rows.pt"))
+
+
 GRAD_FLOOR = 1e-3   # per-parameter gradient error is relative to max(|g|_max, GRAD_FLOOR * largest |g| of the head)
 
 
@@ -186,6 +275,7 @@ def main():
     torch.set_num_threads(max(1, os.cpu_count() or 1))
     pin_grid_ops()
     pin_losses()
+    pin_eval()
     for name in CASES:
         run_case(name)
     for name in TRAIN_CASES:
