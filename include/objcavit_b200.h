@@ -213,6 +213,14 @@ int ocv_fold_queries_bf16(const float* Wout /*[K,Q]*/, const float* bout /*[K]*/
 int ocv_pixel_fused_bf16(const void* X, const void* W3p, const void* Mb, const float* blog, const float* centres,
                          float* depth, int B, int h, int w, int max_ctas, void* stream);
 
+/* The conv3x3 stage of the same kernel on its own (CONV_ONLY instantiation): Y [B,h,w,128] bf16 NHWC = conv3x3(X, pad 1) + bias,
+ * fp32 accumulation in TMEM.  X, W3p as above; bias [128] fp32; Y 16-byte aligned.
+ * replaces: the decoder's final convolution `DenseFeatureExtractor.conv3` (3x3, 128 -> 128, no activation;
+ *   modules/DenseFeatureExtractor.py:97,116) so that the feature map is born in the layout / dtype the head consumes
+ *   (no fp32 NCHW round trip between decoder and head). */
+int ocv_conv3x3_nhwc_bf16(const void* X, const void* W3p, const float* bias, void* Y, int B, int h, int w, int max_ctas,
+                          void* stream);
+
 /* Same kernel, additionally writing the bin with the largest logit per pixel (uint8 [B,h*w], first maximum): used by the
  * parity tests for the north star's "identical bin argmax" criterion; not on the throughput path. */
 int ocv_pixel_fused_bf16_argmax(const void* X, const void* W3p, const void* Mb, const float* blog, const float* centres,

@@ -51,6 +51,7 @@ PROTOTYPES = {
     "ocv_pack_conv3x3_bf16": (i32, [p, p, p]),
     "ocv_fold_queries_bf16": (i32, [p, p, p, i64, i32, p, f32, p, p, i32, i32, i32, i32, p]),
     "ocv_pixel_fused_bf16": (i32, [p, p, p, p, p, p, i32, i32, i32, i32, p]),
+    "ocv_conv3x3_nhwc_bf16": (i32, [p, p, p, p, i32, i32, i32, i32, p]),
     "ocv_pixel_fused_bf16_argmax": (i32, [p, p, p, p, p, p, p, i32, i32, i32, p]),
     "ocv_gemm_f32_ex_workspace": (i64, [i32, i32, i32, i32]),
     "ocv_gemm_f32_ex": (i32, [i32, i32, p, p, p, i32, i32, i32, i32, i32, i32, f32, i32, i64, i64, i64, i32, i32, p, p, p]),

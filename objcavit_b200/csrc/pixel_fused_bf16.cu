@@ -55,6 +55,8 @@ struct PixParams {
   const float* centres;  // [B,256]
   float* depth;          // [B,h*w]
   uint8_t* argmax;       // [B,h*w] bin with the largest logit (ARGMAX instantiation only: the parity tests' bin-agreement check)
+  __nv_bfloat16* conv_out;  // CONV_ONLY instantiation: [B,h,w,128] bf16 NHWC = conv3x3(X) + conv_bias (the kernel stops there)
+  const float* conv_bias;   // [128]
   int B, h, w, tiles_x, tiles_y, n_tiles;   // tiles = 16x16 pair blocks
 };
 
@@ -125,7 +127,10 @@ __device__ __forceinline__ TileCoord tile_coord(const PixParams& p, int t) {
   return {b, ty * TH, (r - ty * p.tiles_x) * PW};
 }
 
-template <bool ARGMAX>
+// MODE 0: the fused head tail; 1: + per-pixel bin argmax (parity tests); 2: CONV_ONLY — the same implicit-GEMM conv3x3 pipeline
+// with a bias + bf16 NHWC store epilogue and no logits / softmax stage (ocv_conv3x3_nhwc_bf16: the decoder's final conv emitting
+// the head's input layout).
+template <int MODE>
 __global__ void __launch_bounds__(THREADS, 1)
 pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                    const __grid_constant__ CUtensorMap tmMb, PixParams p) {
@@ -149,6 +154,7 @@ pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
   uint64_t* log_empty = log_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(log_empty + 1);
 
+  constexpr bool ARGMAX = MODE == 1, CONV_ONLY = MODE == 2;
   pdl_launch();
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   // contiguous chunk of pair blocks per CTA (neighbours share halo rows in L2 and the per-image operands)
@@ -213,18 +219,19 @@ pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
         for (int nh = 0; nh < 2; ++nh)
           for (int kh = 0; kh < 2; ++kh) load_slab(&tmMb, kh * 64, b * NB + nh * 128);
       };
+      if (CONV_ONLY) pdl_wait();  // here X is typically the previous kernel's output (layout conversion of the decoder features)
       load_plane(0, 0);
       for (int it = 0; it < n_my; ++it) {
         for (int tap = 0; tap < 5; ++tap) load_slab(&tmW, 0, tap * C);
         load_plane(it, 1);
         for (int tap = 5; tap < 9; ++tap) load_slab(&tmW, 0, tap * C);
-        if (it > 0) load_logit_slabs(it - 1);            // logits B(it-1)
+        if (!CONV_ONLY && it > 0) load_logit_slabs(it - 1);            // logits B(it-1)
         for (int tap = 0; tap < 5; ++tap) load_slab(&tmW, 64, tap * C);
         if (it + 1 < n_my) load_plane(it + 1, 0);
         for (int tap = 5; tap < 9; ++tap) load_slab(&tmW, 64, tap * C);
-        load_logit_slabs(it);                            // logits A(it)
+        if (!CONV_ONLY) load_logit_slabs(it);                          // logits A(it)
       }
-      load_logit_slabs(n_my - 1);                        // logits B(n_my-1)
+      if (!CONV_ONLY) load_logit_slabs(n_my - 1);                      // logits B(n_my-1)
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
@@ -282,12 +289,12 @@ pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
         mbar_wait(conv_empty, (it & 1) ^ 1);   // both conv accumulators drained by the epilogue (pair it-1)
         tc_fence_after();
         conv_half(it, 0);
-        if (it > 0) logits_mma(it - 1, 1);
+        if (!CONV_ONLY && it > 0) logits_mma(it - 1, 1);
         conv_half(it, 1);
         umma_commit(conv_full);
-        logits_mma(it, 0);
+        if (!CONV_ONLY) logits_mma(it, 0);
       }
-      logits_mma(n_my - 1, 1);
+      if (!CONV_ONLY) logits_mma(n_my - 1, 1);
     }
   } else if (warp >= 4) {
     // ================= convert + softmax epilogue =================
@@ -324,6 +331,29 @@ pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
       }
       fence_proxy_async_smem();
       mbar_arrive(&stg_full[tile]);
+    };
+    // CONV_ONLY: conv accumulator + bias -> bf16 -> 128 contiguous bytes of the NHWC output per thread
+    auto convert_store = [&](int it, int tile) {
+      const TileCoord tc_ = tile_coord(p, t_begin + it);
+      const uint32_t src = tmem + lane_base + (tile ? TM_CONVB : TM_CONVA) + half * 64;
+      uint32_t r0[32], r1[32];
+      tmem_ld32(src, r0);
+      tmem_ld32(src + 32, r1);
+      tmem_ld_wait();
+      const int y = tc_.y0 + ty, x = tc_.x0 + tile * TW + tx;
+      if (y < p.h && x < p.w) {
+        const float4* b4 = reinterpret_cast<const float4*>(p.conv_bias + half * 64);
+        uint4* dst = reinterpret_cast<uint4*>(p.conv_out + (((long long)tc_.b * p.h + y) * p.w + x) * C + half * 64);
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) {
+          const uint32_t* r = ch < 4 ? r0 + ch * 8 : r1 + (ch - 4) * 8;
+          const float4 ba = __ldg(b4 + 2 * ch), bb = __ldg(b4 + 2 * ch + 1);
+          dst[ch] = make_uint4(pack_bf16(__uint_as_float(r[0]) + ba.x, __uint_as_float(r[1]) + ba.y),
+                               pack_bf16(__uint_as_float(r[2]) + ba.z, __uint_as_float(r[3]) + ba.w),
+                               pack_bf16(__uint_as_float(r[4]) + bb.x, __uint_as_float(r[5]) + bb.y),
+                               pack_bf16(__uint_as_float(r[6]) + bb.z, __uint_as_float(r[7]) + bb.w));
+        }
+      }
     };
     auto softmax_store = [&](int it, int tile) {
       const TileCoord tc_ = tile_coord(p, t_begin + it);
@@ -422,6 +452,13 @@ pixel_fused_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constan
     for (int it = 0; it < n_my; ++it) {
       mbar_wait(conv_full, it & 1);
       tc_fence_after();
+      if (CONV_ONLY) {
+        convert_store(it, 0);
+        convert_store(it, 1);
+        tc_fence_before();
+        mbar_arrive(conv_empty);
+        continue;
+      }
       convert(it, 0);
       convert(it, 1);
       tc_fence_before();
@@ -452,26 +489,37 @@ int make_tmap_features(CUtensorMap* out, const void* X, int B, int h, int w) {
 }  // namespace
 
 static int pixel_launch(const void* X, const void* W3p, const void* Mb, const float* blog, const float* centres, float* depth,
-                        uint8_t* argmax, int B, int h, int w, int max_ctas, void* stream) {
-  OCV_CHECK_ARG(X && W3p && Mb && blog && centres && depth && B > 0 && h > 0 && w > 0);
-  OCV_CHECK_ALIGN(((reinterpret_cast<uintptr_t>(blog) | reinterpret_cast<uintptr_t>(centres)) & 15) == 0);
+                        uint8_t* argmax, int B, int h, int w, int max_ctas, void* stream, void* conv_out = nullptr,
+                        const float* conv_bias = nullptr) {
+  const bool conv_only = conv_out != nullptr;
+  OCV_CHECK_ARG(X && W3p && B > 0 && h > 0 && w > 0);
+  if (conv_only) {
+    OCV_CHECK_ARG(conv_bias);
+    OCV_CHECK_ALIGN(((reinterpret_cast<uintptr_t>(conv_out) | reinterpret_cast<uintptr_t>(conv_bias)) & 15) == 0);
+  } else {
+    OCV_CHECK_ARG(Mb && blog && centres && depth);
+    OCV_CHECK_ALIGN(((reinterpret_cast<uintptr_t>(blog) | reinterpret_cast<uintptr_t>(centres)) & 15) == 0);
+  }
   if (int s = ocv_require_sm100()) return s;
   CUtensorMap tmX, tmW, tmMb;
   if (int s = make_tmap_features(&tmX, X, B, h, w)) return s;
   if (int s = tc::make_tmap_2d_bf16(&tmW, W3p, 9 * C, C, C, 128, 64, CU_TENSOR_MAP_SWIZZLE_128B)) return s;
-  if (int s = tc::make_tmap_2d_bf16(&tmMb, Mb, (uint64_t)B * NB, C, C, 128, 64, CU_TENSOR_MAP_SWIZZLE_128B)) return s;
+  if (conv_only) tmMb = tmW;  // unused by that instantiation
+  else if (int s = tc::make_tmap_2d_bf16(&tmMb, Mb, (uint64_t)B * NB, C, C, 128, 64, CU_TENSOR_MAP_SWIZZLE_128B)) return s;
   static int n_sm = 0;
   if (n_sm == 0) {
     int dev = 0;
     cudaGetDevice(&dev);
     cudaError_t e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
     if (e != cudaSuccess) return (int)e;
-    e = cudaFuncSetAttribute(pixel_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(pixel_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    e = cudaFuncSetAttribute(pixel_fused_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(pixel_fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(pixel_fused_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES);
     if (e != cudaSuccess) { n_sm = 0; return (int)e; }
   }
   PixParams p{};
   p.blog = blog; p.centres = centres; p.depth = depth; p.argmax = argmax;
+  p.conv_out = static_cast<__nv_bfloat16*>(conv_out); p.conv_bias = conv_bias;
   p.B = B; p.h = h; p.w = w;
   p.tiles_x = ceil_div(w, PW);
   p.tiles_y = ceil_div(h, TH);
@@ -481,8 +529,9 @@ static int pixel_launch(const void* X, const void* W3p, const void* Mb, const fl
   int grid = n_sm;
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (grid > p.n_tiles) grid = p.n_tiles;
-  if (argmax) return ocv_launch_pdl(pixel_fused_kernel<true>, dim3(grid), dim3(THREADS), SMEM_BYTES, stream, tmX, tmW, tmMb, p);
-  return ocv_launch_pdl(pixel_fused_kernel<false>, dim3(grid), dim3(THREADS), SMEM_BYTES, stream, tmX, tmW, tmMb, p);
+  if (conv_only) return ocv_launch_pdl(pixel_fused_kernel<2>, dim3(grid), dim3(THREADS), SMEM_BYTES, stream, tmX, tmW, tmMb, p);
+  if (argmax) return ocv_launch_pdl(pixel_fused_kernel<1>, dim3(grid), dim3(THREADS), SMEM_BYTES, stream, tmX, tmW, tmMb, p);
+  return ocv_launch_pdl(pixel_fused_kernel<0>, dim3(grid), dim3(THREADS), SMEM_BYTES, stream, tmX, tmW, tmMb, p);
 }
 
 extern "C" int ocv_pixel_fused_bf16(const void* X, const void* W3p, const void* Mb, const float* blog,
@@ -496,4 +545,10 @@ extern "C" int ocv_pixel_fused_bf16_argmax(const void* X, const void* W3p, const
                                            void* stream) {
   OCV_CHECK_ARG(argmax_bin);
   return pixel_launch(X, W3p, Mb, blog, centres, depth, argmax_bin, B, h, w, 0, stream);
+}
+
+extern "C" int ocv_conv3x3_nhwc_bf16(const void* X, const void* W3p, const float* bias, void* Y, int B, int h, int w, int max_ctas,
+                                     void* stream) {
+  OCV_CHECK_ARG(Y && bias);
+  return pixel_launch(X, W3p, nullptr, nullptr, nullptr, nullptr, nullptr, B, h, w, max_ctas, stream, Y, bias);
 }

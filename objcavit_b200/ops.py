@@ -809,3 +809,13 @@ def object_glue(xyxy: torch.Tensor, offsets: torch.Tensor, n_max: int, reverse: 
     _call("ocv_object_glue_f32", xyxy.data_ptr(), offsets.data_ptr(), xywh.data_ptr(), _ptr(bucket), B, int(n_max), int(reverse),
           int(n_scale), _stream())
     return xywh, bucket
+
+
+def conv3x3_nhwc_bf16(x_nhwc: torch.Tensor, w3p: torch.Tensor, bias: torch.Tensor, max_ctas: int = 0) -> torch.Tensor:
+    """[B,h,w,128] bf16 NHWC -> conv3x3 (pad 1) + bias -> [B,h,w,128] bf16 NHWC on the tcgen05 implicit-GEMM pipeline."""
+    _chk(x_nhwc, torch.bfloat16, "x_nhwc"); _chk(w3p, torch.bfloat16, "w3p"); _chk(bias, torch.float32, "bias")
+    assert x_nhwc.is_contiguous() and x_nhwc.shape[3] == 128 and bias.numel() == 128
+    B, h, w, _ = x_nhwc.shape
+    y = torch.empty_like(x_nhwc)
+    _call("ocv_conv3x3_nhwc_bf16", x_nhwc.data_ptr(), w3p.data_ptr(), bias.data_ptr(), y.data_ptr(), B, h, w, int(max_ctas), _stream())
+    return y
