@@ -48,6 +48,7 @@ PROTOTYPES = {
     "ocv_mlp_rows_f32_workspace": (i64, [i32, i32, p]),
     "ocv_mlp_rows_f32": (i32, [p, i64, i32, i32, p, p, p, p, p, p]),
     "ocv_gemm_bf16_ex": (i32, [p, p, p, p, i32, p, p, p, p, i32, p, i32, i32, i32, i32, i32, i32, i32, p]),
+    "ocv_ffn_fused_bf16": (i32, [p, i32, p, p, p, p, p, i32, p, p, p, p, i32, p, i32, i32, i32, p]),
     "ocv_pack_conv3x3_bf16": (i32, [p, p, p]),
     "ocv_fold_queries_bf16": (i32, [p, p, p, i64, i32, p, f32, p, p, i32, i32, i32, i32, p]),
     "ocv_pixel_fused_bf16": (i32, [p, p, p, p, p, p, i32, i32, i32, i32, p]),
