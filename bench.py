@@ -148,6 +148,51 @@ TRAIN_H, TRAIN_W = 208, 272          # NYU-train features of a 416x544 crop (SUR
 GF_TRAIN = 56.5                      # algorithmic GFLOP / image / step (fwd 25.02 + bwd 31.5)
 
 
+def cpu_train_rate(sample_images, threads, repeats=2):
+    """The reference's training step of the head on the host cores (oracle port under torch autograd: forward, SILog + 0.1
+    chamfer, backward; no optimizer) on a bounded sample of the config-5 workload."""
+    from oracle import head as oh
+    from oracle import synth
+    torch.set_num_threads(threads)
+    sd = {k: v.clone().requires_grad_(True) for k, v in load_weights(CFG_NAME).items()}
+    feats = synth.make_features(sample_images, TRAIN_H, TRAIN_W, seed=1234)
+    objs, boxes = synth.make_objects(sample_images, TRAIN_H, TRAIN_W, NOBJ, seed=1234)
+    gt, mask = synth.make_gt(sample_images, TRAIN_H, TRAIN_W, 10.0, seed=1234)
+    cfg = dict(kind="graphbins", strategy="learned_bbox_wh", min_depth=0.001, max_depth=10.0, train=True)
+    best = float("inf")
+    for i in range(repeats + 1):
+        t0 = time.perf_counter()
+        depth, edges, _, _ = oh.head_forward(sd, cfg, feats, objs, boxes)
+        (oh.silog_loss(depth, gt, mask) + 0.1 * oh.bins_chamfer_loss(edges, gt, mask)).backward()
+        if i > 0:
+            best = min(best, time.perf_counter() - t0)
+        for v in sd.values():
+            v.grad = None
+    return sample_images / best, best
+
+
+def run_reference_train(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    sample = 2
+    v, secs = cpu_train_rate(sample, threads, repeats=max(1, min(a.steps, 3)))
+    print(json.dumps({
+        "impl": "reference", "metric": TRAIN_METRIC, "value": v, "unit": "images/s", "n_gpus": a.gpus, "steps": max(1, min(a.steps, 3)),
+        "warmup": 1, "ms_per_step": secs * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": f"{CFG_NAME} head training step (fwd + SILog/chamfer + bwd), {NOBJ} boxes/img, features "
+                               f"128x{TRAIN_H}x{TRAIN_W}, bounded sample of {sample} images per step"},
+        "cpu_baseline": {"value": v, "unit": "images/s", "cores": threads, "kind": "port",
+                         "sample": f"{sample} images per step, best of {max(1, min(a.steps, 3))}, torch autograd over oracle/head.py"},
+        "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+TRAIN_METRIC = "ObjCAViT head training images/sec (config 5: fwd+bwd, SILog+BinsChamfer, grad all-reduce, AdamW)"
+
+
 def run_train(a):
     """--workload train: BASELINE.json configs[4] — frozen features + ObjCAViT head fwd/bwd, SILog + 0.1 chamfer, one all-reduce
     of the flat head-gradient buffer, clip 0.1, AdamW + OneCycle; batch 8 per GPU (weak scaling)."""
@@ -246,7 +291,7 @@ def run_train(a):
     h2d = sum(t.numel() * t.element_size() for t in (host["x"], host["gt"], host["mask"])) + \
         sum(t.numel() * 4 for t in host["objs"] + host["boxes"])
     out = {
-        "metric": "ObjCAViT head training images/sec (config 5: fwd+bwd, SILog+BinsChamfer, grad all-reduce, AdamW)",
+        "metric": TRAIN_METRIC,
         "value": value, "unit": "images/s", "n_gpus": world, "steps": K, "warmup": W_, "ms_per_step": ms / K,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"{CFG_NAME} head training step, {NOBJ} boxes/img, frozen features 128x{TRAIN_H}x{TRAIN_W} fp32, "
@@ -258,6 +303,12 @@ def run_train(a):
         "e2e": {"value": world * B * K / (ms_e2e * 1e-3), "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
                 "ms_per_step": ms_e2e / K},
     }
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        v, secs = cpu_train_rate(2, threads)
+        out["cpu_baseline"] = {"value": v, "unit": "images/s", "cores": threads, "kind": "port",
+                               "sample": f"2 images of the same workload, best of 2 ({secs:.2f} s per pass: forward + losses + backward, "
+                                         "no optimizer), torch autograd over oracle/head.py"}
     if rank == 0:
         print(json.dumps(out))
     if dist is not None:
@@ -279,7 +330,7 @@ def main():
                     help="infer = BASELINE.json configs[1] (the headline line); train = configs[4] (the training step)")
     a = ap.parse_args()
     if a.impl == "reference":
-        return run_reference(a)
+        return run_reference_train(a) if a.workload == "train" else run_reference(a)
     if a.workload == "train":
         return run_train(a)
 

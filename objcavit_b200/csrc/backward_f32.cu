@@ -20,21 +20,56 @@ __device__ __forceinline__ float block_sum_f(float v, float* sh) {  // result on
 }
 
 // x viewed [G, outer, C, inner] -> out[g, c] = beta * out[g, c] + sum_{o, i} x[g, o, c, i];  one block per (c, g)
-__global__ void reduce_channels_kernel(const float* __restrict__ x, float* __restrict__ out, int outer, int C, long long inner,
-                                       float beta) {
+__global__ void __launch_bounds__(512) reduce_channels_kernel(const float* __restrict__ x, float* __restrict__ out, int outer, int C,
+                                                              long long inner, float beta) {
   __shared__ float sh[32];
   const int c = blockIdx.x, g = blockIdx.y;
   const float* xg = x + (long long)g * outer * C * inner;
-  float acc = 0.f;
-  const long long n = (long long)outer * inner;
-  for (long long t = threadIdx.x; t < n; t += blockDim.x) {
-    const long long o = t / inner, i = t - o * inner;
-    acc += xg[(o * C + c) * inner + i];
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  for (int o = 0; o < outer; ++o) {  // contiguous runs of `inner` floats: no per-element index arithmetic, 128-bit loads when aligned
+    const float* run = xg + ((long long)o * C + c) * inner;
+    if ((inner & 3) == 0 && (reinterpret_cast<uintptr_t>(run) & 15) == 0) {
+      const float4* r4 = reinterpret_cast<const float4*>(run);
+      for (long long i = threadIdx.x; i < inner / 4; i += blockDim.x) {
+        const float4 v = r4[i];
+        a0 += v.x; a1 += v.y; a2 += v.z; a3 += v.w;
+      }
+    } else {
+      for (long long i = threadIdx.x; i < inner; i += blockDim.x) a0 += run[i];
+    }
   }
-  const float s = block_sum_f(acc, sh);
+  const float s = block_sum_f((a0 + a1) + (a2 + a3), sh);
   if (threadIdx.x == 0) {
     float* o = out + (long long)g * C + c;
     *o = beta != 0.f ? beta * (*o) + s : s;
+  }
+}
+
+// inner == 1 (column sums of a [G, rows, C] matrix: Linear bias gradients, positional-row gradients): threads along C so that every
+// load is coalesced; 32 row lanes per block combined through shared memory in a fixed order
+__global__ void __launch_bounds__(1024) reduce_columns_kernel(const float* __restrict__ x, float* __restrict__ out, int rows, int C,
+                                                              float beta) {
+  __shared__ float sh[32][33];
+  const int c = blockIdx.x * 32 + threadIdx.x, g = blockIdx.y, ry = threadIdx.y;
+  const float* xg = x + (long long)g * rows * C;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  if (c < C) {
+    int r = ry;
+    for (; r + 96 < rows; r += 128) {
+      a0 += xg[(long long)r * C + c];
+      a1 += xg[(long long)(r + 32) * C + c];
+      a2 += xg[(long long)(r + 64) * C + c];
+      a3 += xg[(long long)(r + 96) * C + c];
+    }
+    for (; r < rows; r += 32) a0 += xg[(long long)r * C + c];
+  }
+  sh[ry][threadIdx.x] = (a0 + a1) + (a2 + a3);
+  __syncthreads();
+  if (ry == 0 && c < C) {
+    float t = 0.f;
+    for (int i = 0; i < 32; ++i) t += sh[i][threadIdx.x];
+    float* o = out + (long long)g * C + c;
+    *o = beta != 0.f ? beta * (*o) + t : t;
   }
 }
 
@@ -277,7 +312,8 @@ extern "C" int ocv_reduce_channels_f32(const float* x, float* out, int groups, i
   OCV_CHECK_ARG(x && out && groups > 0 && outer > 0 && C > 0 && inner > 0);
   OCV_CHECK_SHAPE(groups <= 65535);
   if (int s = ocv_require_sm100()) return s;
-  reduce_channels_kernel<<<dim3(C, groups), 256, 0, ocv_stream(stream)>>>(x, out, outer, C, inner, beta);
+  if (inner == 1) reduce_columns_kernel<<<dim3(ceil_div(C, 32), groups), dim3(32, 32), 0, ocv_stream(stream)>>>(x, out, outer, C, beta);
+  else reduce_channels_kernel<<<dim3(C, groups), inner >= 4096 ? 512 : 128, 0, ocv_stream(stream)>>>(x, out, outer, C, inner, beta);
   return ocv_launch_status();
 }
 
