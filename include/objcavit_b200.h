@@ -271,6 +271,24 @@ int ocv_mha_core_bwd_f32(const float* q, const float* k, const float* v, const f
  * bias, so that the logits operand can be the bare GEMM Wout @ ram). */
 int ocv_tail_bwd_f32(float* logits_inout, float* pg_out, const float* centres, const float* grad_depth, const float* logit_bias,
                      int B, int K, long long P, void* stream);
+/* Dropout of training mode (nn.TransformerEncoderLayer: dropout 0.1 on the attention probabilities, after out_proj, after the
+ * FFN activation and after linear2).  Counter-based masks: element idx of site `seed` is kept iff
+ * hash(seed, idx) >= p 2^32 (csrc/common.cuh), kept values are scaled by 1/(1-p).  Same statistics as torch's Bernoulli masks, a
+ * different random stream (torch's Philox offsets cannot be reproduced); the backward pass regenerates the forward mask.
+ *   ocv_dropout_f32: out = residual + dropout(x) (residual optional, in place allowed); applied to a gradient it is its own backward.
+ *   ocv_mha_core_dropout_f32 / ocv_mha_core_bwd_dropout_f32: the attention core with dropout on the probabilities, mask index =
+ *   flat index into [B, heads, Sq, Sk] (so ocv_dropout_f32 on a tensor of ones of that shape reproduces the mask: tests). */
+int ocv_dropout_f32(const float* x, const float* residual, float* out, long long n, float p, unsigned long long seed, void* stream);
+int ocv_mha_core_dropout_f32(const float* q, const float* k, const float* v, float* out, const uint8_t* key_padding_mask,
+                             int B, int Sq, int Sk, int heads, int d, long long q_bstride, int q_rstride, long long k_bstride,
+                             int k_rstride, long long v_bstride, int v_rstride, long long o_bstride, int o_rstride, float drop_p,
+                             unsigned long long drop_seed, void* stream);
+int ocv_mha_core_bwd_dropout_f32(const float* q, const float* k, const float* v, const float* out, const float* dout,
+                                 const uint8_t* key_padding_mask, float* dq, float* dk, float* dv, int B, int Sq, int Sk, int heads,
+                                 int d, long long q_bstride, int q_rstride, long long k_bstride, int k_rstride, long long v_bstride,
+                                 int v_rstride, long long o_bstride, int o_rstride, long long dq_bstride, int dq_rstride,
+                                 long long dk_bstride, int dk_rstride, long long dv_bstride, int dv_rstride, float drop_p,
+                                 unsigned long long drop_seed, void* workspace, void* stream);
 /* Adjoint of ocv_pad_objects_f32: dsrc[offsets[b]+j, :] = beta * dsrc + dpadded[b, left+j, :] for j < n_b (left = L-Nmax when
  * left_pad else 0); pad rows carry no gradient. */
 int ocv_unpad_objects_f32(const float* dpadded, const int32_t* offsets, float* dsrc, int B, int L, int Nmax, int E, int left_pad,

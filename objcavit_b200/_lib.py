@@ -62,6 +62,11 @@ PROTOTYPES = {
     "ocv_mha_core_bwd_f32": (i32, [p, p, p, p, p, p, p, p, p, i32, i32, i32, i32, i32, i64, i32, i64, i32, i64, i32, i64, i32,
                                    i64, i32, i64, i32, i64, i32, p, p]),
     "ocv_tail_bwd_f32": (i32, [p, p, p, p, p, i32, i32, i64, p]),
+    "ocv_dropout_f32": (i32, [p, p, p, i64, f32, C.c_ulonglong, p]),
+    "ocv_mha_core_dropout_f32": (i32, [p, p, p, p, p, i32, i32, i32, i32, i32, i64, i32, i64, i32, i64, i32, i64, i32, f32,
+                                       C.c_ulonglong, p]),
+    "ocv_mha_core_bwd_dropout_f32": (i32, [p, p, p, p, p, p, p, p, p, i32, i32, i32, i32, i32, i64, i32, i64, i32, i64, i32, i64, i32,
+                                           i64, i32, i64, i32, i64, i32, f32, C.c_ulonglong, p, p]),
     "ocv_unpad_objects_f32": (i32, [p, p, p, i32, i32, i32, i32, i32, f32, p]),
     "ocv_tta_merge_f32": (i32, [p, p, p, i32, i32, i32, f32, f32, p]),
     "ocv_depth_metrics_workspace": (i64, []),

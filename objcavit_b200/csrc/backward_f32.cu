@@ -153,11 +153,14 @@ __global__ void mha_bwd_q_kernel(const float* __restrict__ q, const float* __res
                                  const float* __restrict__ o, const float* __restrict__ dout, const uint8_t* __restrict__ mask,
                                  float* __restrict__ dq, float* __restrict__ stats, int Sq, int Sk, int heads, long long q_bs,
                                  int q_rs, long long k_bs, int k_rs, long long v_bs, int v_rs, long long o_bs, int o_rs,
-                                 long long dq_bs, int dq_rs) {
+                                 long long dq_bs, int dq_rs, float drop_p, unsigned long long drop_seed) {
   const int b = blockIdx.z, hd = blockIdx.y;
   const int i = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32, lane = threadIdx.x % 32;
   if (i >= Sq) return;
   const float scale = rsqrtf(32.f);
+  const uint32_t drop_thr = ocv_drop_threshold(drop_p);
+  const float drop_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  const unsigned long long drop_row = (((unsigned long long)b * heads + hd) * Sq + i) * Sk;
   const float qi = q[b * q_bs + (long long)i * q_rs + hd * 32 + lane];
   const float doi = dout[b * o_bs + (long long)i * o_rs + hd * 32 + lane];
   const float oi = o[b * o_bs + (long long)i * o_rs + hd * 32 + lane];
@@ -179,7 +182,8 @@ __global__ void mha_bwd_q_kernel(const float* __restrict__ q, const float* __res
     const float kj = kb[(long long)j * k_rs];
     const float s = warp_sum(qi * kj) * scale;
     const float p = __expf(s - m) / l;
-    const float dP = warp_sum(doi * vb[(long long)j * v_rs]);
+    float dP = warp_sum(doi * vb[(long long)j * v_rs]);
+    if (drop_p > 0.f) dP = ocv_drop_keep(drop_seed, drop_row + j, drop_thr) ? dP * drop_scale : 0.f;
     acc = fmaf(p * (dP - D), kj, acc);
   }
   dq[b * dq_bs + (long long)i * dq_rs + hd * 32 + lane] = acc * scale;
@@ -194,11 +198,14 @@ __global__ void mha_bwd_kv_kernel(const float* __restrict__ q, const float* __re
                                   const float* __restrict__ dout, const uint8_t* __restrict__ mask, const float* __restrict__ stats,
                                   float* __restrict__ dk, float* __restrict__ dv, int Sq, int Sk, int heads, long long q_bs,
                                   int q_rs, long long k_bs, int k_rs, long long v_bs, int v_rs, long long o_bs, int o_rs,
-                                  long long dk_bs, int dk_rs, long long dv_bs, int dv_rs) {
+                                  long long dk_bs, int dk_rs, long long dv_bs, int dv_rs, float drop_p, unsigned long long drop_seed) {
   const int b = blockIdx.z, hd = blockIdx.y;
   const int j = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32, lane = threadIdx.x % 32;
   if (j >= Sk) return;
   const float scale = rsqrtf(32.f);
+  const uint32_t drop_thr = ocv_drop_threshold(drop_p);
+  const float drop_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  const unsigned long long drop_base = ((unsigned long long)b * heads + hd) * Sq;
   float ak = 0.f, av = 0.f;
   if (!(mask && mask[(long long)b * Sk + j])) {
     const float kj = k[b * k_bs + (long long)j * k_rs + hd * 32 + lane];
@@ -210,8 +217,14 @@ __global__ void mha_bwd_kv_kernel(const float* __restrict__ q, const float* __re
       const float qi = qb[(long long)i * q_rs], doi = db[(long long)i * o_rs];
       const float s = warp_sum(qi * kj) * scale;
       const float p = __expf(s - st[3 * i]) / st[3 * i + 1];
-      const float dP = warp_sum(doi * vj);
-      av = fmaf(p, doi, av);
+      float dP = warp_sum(doi * vj);
+      float pd = p;
+      if (drop_p > 0.f) {
+        const float ms = ocv_drop_keep(drop_seed, (drop_base + i) * Sk + j, drop_thr) ? drop_scale : 0.f;
+        dP *= ms;
+        pd *= ms;
+      }
+      av = fmaf(pd, doi, av);
       ak = fmaf(p * (dP - st[3 * i + 2]), qi, ak);
     }
   }
@@ -284,6 +297,15 @@ __global__ void bins_bwd_kernel(const float* __restrict__ y_raw, const float* __
     dy[(long long)b * K + k] = y[k] > 0.f ? (dw[k] - dot) / S : 0.f;
 }
 
+// ---- elementwise dropout (+ optional residual): out = residual + (keep ? x / (1-p) : 0); the same call on a gradient is its backward
+__global__ void dropout_kernel(const float* __restrict__ x, const float* __restrict__ residual, float* __restrict__ out, long long n,
+                               uint32_t thr, float scale, unsigned long long seed) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float v = ocv_drop_keep(seed, (unsigned long long)i, thr) ? x[i] * scale : 0.f;
+  out[i] = residual ? residual[i] + v : v;
+}
+
 // ---- adjoint of ocv_pad_objects_f32: dsrc[offsets[b] + j] = beta * dsrc + dpadded[b, left + j]  (pad rows receive no gradient)
 __global__ void unpad_objects_kernel(const float* __restrict__ dpadded, const int32_t* __restrict__ offsets, float* __restrict__ dsrc,
                                      int L, int Nmax, int E, int left_pad, float beta) {
@@ -297,6 +319,15 @@ __global__ void unpad_objects_kernel(const float* __restrict__ dpadded, const in
 }
 
 }  // namespace
+
+extern "C" int ocv_dropout_f32(const float* x, const float* residual, float* out, long long n, float p, unsigned long long seed,
+                               void* stream) {
+  OCV_CHECK_ARG(x && out && n > 0 && p >= 0.f && p < 1.f);
+  if (int s = ocv_require_sm100()) return s;
+  dropout_kernel<<<(unsigned)ceil_div<long long>(n, 256), 256, 0, ocv_stream(stream)>>>(x, residual, out, n, ocv_drop_threshold(p),
+                                                                                       1.f / (1.f - p), seed);
+  return ocv_launch_status();
+}
 
 extern "C" int ocv_unpad_objects_f32(const float* dpadded, const int32_t* offsets, float* dsrc, int B, int L, int Nmax, int E,
                                      int left_pad, float beta, void* stream) {
@@ -346,17 +377,30 @@ extern "C" int ocv_mha_core_bwd_f32(const float* q, const float* k, const float*
                                     long long v_bstride, int v_rstride, long long o_bstride, int o_rstride, long long dq_bstride,
                                     int dq_rstride, long long dk_bstride, int dk_rstride, long long dv_bstride, int dv_rstride,
                                     void* workspace /* B*heads*Sq*3 floats */, void* stream) {
+  return ocv_mha_core_bwd_dropout_f32(q, k, v, out, dout, key_padding_mask, dq, dk, dv, B, Sq, Sk, heads, d, q_bstride, q_rstride,
+                                      k_bstride, k_rstride, v_bstride, v_rstride, o_bstride, o_rstride, dq_bstride, dq_rstride,
+                                      dk_bstride, dk_rstride, dv_bstride, dv_rstride, 0.f, 0ull, workspace, stream);
+}
+
+extern "C" int ocv_mha_core_bwd_dropout_f32(const float* q, const float* k, const float* v, const float* out, const float* dout,
+                                            const uint8_t* key_padding_mask, float* dq, float* dk, float* dv, int B, int Sq, int Sk,
+                                            int heads, int d, long long q_bstride, int q_rstride, long long k_bstride, int k_rstride,
+                                            long long v_bstride, int v_rstride, long long o_bstride, int o_rstride,
+                                            long long dq_bstride, int dq_rstride, long long dk_bstride, int dk_rstride,
+                                            long long dv_bstride, int dv_rstride, float drop_p, unsigned long long drop_seed,
+                                            void* workspace /* B*heads*Sq*3 floats */, void* stream) {
   OCV_CHECK_ARG(q && k && v && out && dout && dq && dk && dv && workspace && B > 0 && Sq > 0 && Sk > 0 && heads > 0);
+  OCV_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f);
   OCV_CHECK_SHAPE(d == 32 && B <= 65535 && heads <= 65535);
   if (int s = ocv_require_sm100()) return s;
   float* stats = static_cast<float*>(workspace);
   mha_bwd_q_kernel<<<dim3(ceil_div(Sq, 8), heads, B), 256, 0, ocv_stream(stream)>>>(
       q, k, v, out, dout, key_padding_mask, dq, stats, Sq, Sk, heads, q_bstride, q_rstride, k_bstride, k_rstride, v_bstride,
-      v_rstride, o_bstride, o_rstride, dq_bstride, dq_rstride);
+      v_rstride, o_bstride, o_rstride, dq_bstride, dq_rstride, drop_p, drop_seed);
   if (int s = ocv_launch_status()) return s;
   mha_bwd_kv_kernel<<<dim3(ceil_div(Sk, 8), heads, B), 256, 0, ocv_stream(stream)>>>(
       q, k, v, dout, key_padding_mask, stats, dk, dv, Sq, Sk, heads, q_bstride, q_rstride, k_bstride, k_rstride, v_bstride,
-      v_rstride, o_bstride, o_rstride, dk_bstride, dk_rstride, dv_bstride, dv_rstride);
+      v_rstride, o_bstride, o_rstride, dk_bstride, dk_rstride, dv_bstride, dv_rstride, drop_p, drop_seed);
   return ocv_launch_status();
 }
 

@@ -38,6 +38,22 @@ __device__ __forceinline__ float warp_max(float v) {
 template <typename T>
 static inline T ceil_div(T a, T b) { return (a + b - 1) / b; }
 
+// ---- dropout (training mode) ---------------------------------------------------------------------------------------
+// Counter-based: element `idx` of dropout site `seed` is kept iff the upper 32 bits of a splitmix64 hash of (seed, idx) are
+// >= p * 2^32.  Stateless, so the backward pass regenerates exactly the forward mask from (seed, idx); the statistics match
+// torch's Bernoulli(1-p) masks, the random stream itself is (necessarily) a different one.
+__host__ __device__ __forceinline__ uint32_t ocv_drop_threshold(float p) {
+  const double t = (double)p * 4294967296.0;
+  return t >= 4294967295.0 ? 4294967295u : (uint32_t)t;
+}
+__device__ __forceinline__ bool ocv_drop_keep(unsigned long long seed, unsigned long long idx, uint32_t thresh) {
+  unsigned long long z = seed + idx * 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (uint32_t)(z >> 32) >= thresh;
+}
+
 // ---- programmatic dependent launch (PDL) ---------------------------------------------------------------------------
 // The head is a chain of ~50 short dependent kernels: launch latency and each kernel's prologue (barrier init, TMEM
 // allocation, tensor-map fetch, weight tiles, bias vectors) would otherwise sit on the critical path.  Every kernel of

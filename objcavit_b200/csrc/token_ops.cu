@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(ATT_WARPS * 32)
 mha_core_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
                 float* __restrict__ out, const uint8_t* __restrict__ mask, int Sq, int Sk,
                 long long q_bs, int q_rs, long long k_bs, int k_rs, long long v_bs, int v_rs, long long o_bs,
-                int o_rs) {
+                int o_rs, float drop_p, unsigned long long drop_seed) {
   __shared__ float Ks[ATT_KT][33];
   __shared__ float Vs[ATT_KT][32];
   __shared__ float Msk[ATT_KT];
@@ -62,6 +62,10 @@ mha_core_kernel(const float* __restrict__ q, const float* __restrict__ k, const 
   // every lane keeps the whole (scaled) query vector: broadcast through shuffles of the lane-owned element
   float qown = active ? q[b * q_bs + (long long)qi * q_rs + hd * 32 + lane] * scale : 0.f;
   float m = -INFINITY, l = 0.f, acc = 0.f;
+  // attention-probability dropout (training): mask index = flat index into [B, heads, Sq, Sk]
+  const uint32_t drop_thr = ocv_drop_threshold(drop_p);
+  const float drop_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  const unsigned long long drop_row = (((unsigned long long)b * gridDim.y + hd) * Sq + (active ? qi : 0)) * Sk;
   for (int k0 = 0; k0 < Sk; k0 += ATT_KT) {
     __syncthreads();
     for (int i = threadIdx.x; i < ATT_KT * 32; i += blockDim.x) {
@@ -90,6 +94,7 @@ mha_core_kernel(const float* __restrict__ q, const float* __restrict__ k, const 
     }
     l = l * corr + warp_sum(p);
     acc *= corr;
+    if (drop_p > 0.f) p = ocv_drop_keep(drop_seed, drop_row + k0 + lane, drop_thr) ? p * drop_scale : 0.f;  // after the normaliser
 #pragma unroll
     for (int j = 0; j < 32; ++j) acc = fmaf(__shfl_sync(0xffffffffu, p, j), Vs[j][lane], acc);
     m = m_new;
@@ -331,13 +336,22 @@ extern "C" int ocv_mha_core_f32(const float* q, const float* k, const float* v, 
                                 long long q_bstride, int q_rstride, long long k_bstride, int k_rstride,
                                 long long v_bstride, int v_rstride, long long o_bstride, int o_rstride,
                                 void* stream) {
-  OCV_CHECK_ARG(q && k && v && out && B > 0 && Sq > 0 && Sk > 0 && heads > 0);
+  return ocv_mha_core_dropout_f32(q, k, v, out, key_padding_mask, B, Sq, Sk, heads, d, q_bstride, q_rstride, k_bstride, k_rstride,
+                                  v_bstride, v_rstride, o_bstride, o_rstride, 0.f, 0ull, stream);
+}
+
+extern "C" int ocv_mha_core_dropout_f32(const float* q, const float* k, const float* v, float* out,
+                                        const uint8_t* key_padding_mask, int B, int Sq, int Sk, int heads, int d,
+                                        long long q_bstride, int q_rstride, long long k_bstride, int k_rstride,
+                                        long long v_bstride, int v_rstride, long long o_bstride, int o_rstride,
+                                        float drop_p, unsigned long long drop_seed, void* stream) {
+  OCV_CHECK_ARG(q && k && v && out && B > 0 && Sq > 0 && Sk > 0 && heads > 0 && drop_p >= 0.f && drop_p < 1.f);
   OCV_CHECK_SHAPE(d == 32 && B <= 65535 && heads <= 65535);
   if (int s = ocv_require_sm100()) return s;
   dim3 grid(ceil_div(Sq, ATT_WARPS), heads, B);
   mha_core_kernel<<<grid, ATT_WARPS * 32, 0, ocv_stream(stream)>>>(q, k, v, out, key_padding_mask, Sq, Sk, q_bstride,
                                                                   q_rstride, k_bstride, k_rstride, v_bstride,
-                                                                  v_rstride, o_bstride, o_rstride);
+                                                                  v_rstride, o_bstride, o_rstride, drop_p, drop_seed);
   return ocv_launch_status();
 }
 

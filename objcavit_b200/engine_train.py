@@ -11,8 +11,9 @@ shape — normally views of ONE flat gradient buffer (``grad_sync.FlatGradBuffer
 all-reduce.  Parameters the reference leaves without gradient simply keep their zeros.
 
 Grad-mode semantics of the reference are reproduced: ``nn.TransformerEncoder`` takes the slow path under autograd, so padded
-object rows are NOT zeroed (F7), the left-pad / right-mask quirk (F5) is kept, and dropout is the identity (``dropout=0`` —
-gradient parity is defined with dropout disabled).  The decoder features are constants of the step
+object rows are NOT zeroed (F7), the left-pad / right-mask quirk (F5) is kept.  Dropout (``DropCtx``): p = 0 is the identity (the
+configuration gradient parity is defined on); p > 0 applies counter-based masks at the four sites of every
+encoder layer and the backward regenerates them — torch's random stream cannot be reproduced, the masks are statistically the same.  The decoder features are constants of the step
 (frozen extractor): no gradient w.r.t. ``x`` is produced.
 """
 from __future__ import annotations
@@ -49,6 +50,25 @@ class Touched(dict):
         return super().__getitem__(k)
 
 
+class DropCtx:
+    """Dropout state of one training forward: probability ``p`` (0 = identity: no dropout kernels are launched) and a base seed;
+    every dropout site of the forward draws its own 64-bit site seed with :meth:`site`, recorded on the tape for the backward.
+    Sites per encoder layer, in this order (nn.TransformerEncoderLayer): attention probabilities, after out_proj
+    (dropout1), after the FFN activation (dropout), after linear2 (dropout2).  The cross-attention MHAs have dropout 0."""
+
+    def __init__(self, p: float = 0.0, seed: int = 0):
+        self.p = float(p)
+        self.seed = int(seed) & 0xFFFFFFFFFFFF
+        self.count = 0
+
+    def site(self) -> int:
+        self.count += 1
+        return ((self.seed * 0x9E3779B1 + self.count * 0x632BE5AB) ^ (self.count << 48)) & 0xFFFFFFFFFFFFFFFF
+
+
+NO_DROP = DropCtx(0.0, 0)
+
+
 # ----------------------------------------------------------------------------------------------------------------------
 # MLP chains (positional encoder, regressor)
 # ----------------------------------------------------------------------------------------------------------------------
@@ -82,42 +102,61 @@ def mlp_bwd(P: Params, G: Params, pre: str, idxs, saved, dy: torch.Tensor, dx_ou
 # nn.TransformerEncoderLayer (post-norm) / nn.TransformerEncoder
 # ----------------------------------------------------------------------------------------------------------------------
 
-def encoder_layer_fwd(P: Params, pre: str, x: torch.Tensor, mask):
+def encoder_layer_fwd(P: Params, pre: str, x: torch.Tensor, mask, drop: DropCtx = NO_DROP):
     B, S, _ = x.shape
     x2 = x.view(B * S, E)
+    p = drop.p
     qkv = ops.linear(x2, P[pre + "self_attn.in_proj_weight"], P[pre + "self_attn.in_proj_bias"]).view(B, S, 3 * E)
-    att = ops.mha_core(qkv[:, :, 0:E], qkv[:, :, E:2 * E], qkv[:, :, 2 * E:], mask, HEADS)
-    y = ops.linear(att.view(B * S, E), P[pre + "self_attn.out_proj.weight"], P[pre + "self_attn.out_proj.bias"], residual=x2)
-    x1 = ops.add_layernorm(y, None, P[pre + "norm1.weight"], P[pre + "norm1.bias"])
-    h = ops.linear(x1, P[pre + "linear1.weight"], P[pre + "linear1.bias"], act=RELU)
-    y2 = ops.linear(h, P[pre + "linear2.weight"], P[pre + "linear2.bias"], residual=x1)
+    if p > 0:
+        sites = (drop.site(), drop.site(), drop.site(), drop.site())
+        att = ops.mha_core(qkv[:, :, 0:E], qkv[:, :, E:2 * E], qkv[:, :, 2 * E:], mask, HEADS, drop=(p, sites[0]))
+        sa = ops.linear(att.view(B * S, E), P[pre + "self_attn.out_proj.weight"], P[pre + "self_attn.out_proj.bias"])
+        y = ops.dropout(sa, p, sites[1], residual=x2, out=sa)                       # x + dropout1(self-attention)
+        x1 = ops.add_layernorm(y, None, P[pre + "norm1.weight"], P[pre + "norm1.bias"])
+        h = ops.linear(x1, P[pre + "linear1.weight"], P[pre + "linear1.bias"], act=RELU)
+        h = ops.dropout(h, p, sites[2], out=h)                                      # dropout(relu(linear1)): what linear2 sees
+        f = ops.linear(h, P[pre + "linear2.weight"], P[pre + "linear2.bias"])
+        y2 = ops.dropout(f, p, sites[3], residual=x1, out=f)                        # x1 + dropout2(linear2)
+    else:
+        sites = None
+        att = ops.mha_core(qkv[:, :, 0:E], qkv[:, :, E:2 * E], qkv[:, :, 2 * E:], mask, HEADS)
+        y = ops.linear(att.view(B * S, E), P[pre + "self_attn.out_proj.weight"], P[pre + "self_attn.out_proj.bias"], residual=x2)
+        x1 = ops.add_layernorm(y, None, P[pre + "norm1.weight"], P[pre + "norm1.bias"])
+        h = ops.linear(x1, P[pre + "linear1.weight"], P[pre + "linear1.bias"], act=RELU)
+        y2 = ops.linear(h, P[pre + "linear2.weight"], P[pre + "linear2.bias"], residual=x1)
     out = ops.add_layernorm(y2, None, P[pre + "norm2.weight"], P[pre + "norm2.bias"])
-    return out.view(B, S, E), (x2, qkv, att, y, x1, h, y2, mask)
+    return out.view(B, S, E), (x2, qkv, att, y, x1, h, y2, mask, (p, sites))
 
 
 def encoder_layer_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor) -> torch.Tensor:
-    x2, qkv, att, y, x1, h, y2, mask = saved
+    x2, qkv, att, y, x1, h, y2, mask, (p, sites) = saved
     B, S, _ = qkv.shape
     d = dout.reshape(B * S, E)
     dy2 = ops.layernorm_bwd(d, y2, P[pre + "norm2.weight"], G[pre + "norm2.weight"], G[pre + "norm2.bias"], beta=1.0)
-    ops.linear_wgrad(dy2, h, G[pre + "linear2.weight"], G[pre + "linear2.bias"], beta=1.0)
-    dh = ops.act_bwd(ops.linear_dgrad(dy2, P[pre + "linear2.weight"]), h, RELU)
+    df = ops.dropout(dy2, p, sites[3]) if p > 0 else dy2                         # gradient of linear2's output
+    ops.linear_wgrad(df, h, G[pre + "linear2.weight"], G[pre + "linear2.bias"], beta=1.0)
+    dh = ops.linear_dgrad(df, P[pre + "linear2.weight"])
+    if p > 0:
+        ops.dropout(dh, p, sites[2], out=dh)                                     # h is the post-dropout activation: h > 0 <=> kept & positive
+    dh = ops.act_bwd(dh, h, RELU)
     ops.linear_wgrad(dh, x1, G[pre + "linear1.weight"], G[pre + "linear1.bias"], beta=1.0)
     ops.linear_dgrad(dh, P[pre + "linear1.weight"], out=dy2, beta=1.0)           # dy2 <- d loss / d x1 (residual + FFN)
     dy = ops.layernorm_bwd(dy2, y, P[pre + "norm1.weight"], G[pre + "norm1.weight"], G[pre + "norm1.bias"], beta=1.0)
-    ops.linear_wgrad(dy, att.view(B * S, E), G[pre + "self_attn.out_proj.weight"], G[pre + "self_attn.out_proj.bias"], beta=1.0)
-    datt = ops.linear_dgrad(dy, P[pre + "self_attn.out_proj.weight"]).view(B, S, E)
-    dqkv = ops.mha_core_bwd(qkv[:, :, 0:E], qkv[:, :, E:2 * E], qkv[:, :, 2 * E:], att, datt, mask, HEADS, packed=True)[3]
+    dsa = ops.dropout(dy, p, sites[1]) if p > 0 else dy                          # gradient of out_proj's output
+    ops.linear_wgrad(dsa, att.view(B * S, E), G[pre + "self_attn.out_proj.weight"], G[pre + "self_attn.out_proj.bias"], beta=1.0)
+    datt = ops.linear_dgrad(dsa, P[pre + "self_attn.out_proj.weight"]).view(B, S, E)
+    dqkv = ops.mha_core_bwd(qkv[:, :, 0:E], qkv[:, :, E:2 * E], qkv[:, :, 2 * E:], att, datt, mask, HEADS, packed=True,
+                            drop=(p, sites[0]) if p > 0 else None)[3]
     dqkv = dqkv.view(B * S, 3 * E)
     ops.linear_wgrad(dqkv, x2, G[pre + "self_attn.in_proj_weight"], G[pre + "self_attn.in_proj_bias"], beta=1.0)
     ops.linear_dgrad(dqkv, P[pre + "self_attn.in_proj_weight"], out=dy, beta=1.0)  # dy <- d loss / d x (residual + attention)
     return dy.view(B, S, E)
 
 
-def encoder_fwd(P: Params, pre: str, x: torch.Tensor, mask=None, num_layers: int = 4):
+def encoder_fwd(P: Params, pre: str, x: torch.Tensor, mask=None, num_layers: int = 4, drop: DropCtx = NO_DROP):
     saved = []
     for i in range(num_layers):
-        x, sv = encoder_layer_fwd(P, f"{pre}layers.{i}.", x, mask)
+        x, sv = encoder_layer_fwd(P, f"{pre}layers.{i}.", x, mask, drop)
         saved.append(sv)
     return x, saved
 
@@ -167,9 +206,9 @@ def cross_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor, acc_q, 
 # SelfAttnCrossAttn (modules/ObjCAViT.py:167-213)
 # ----------------------------------------------------------------------------------------------------------------------
 
-def saca_fwd(P: Params, pre: str, img_tok: torch.Tensor, objs, no_obj_sa: bool, need_object_output: bool):
+def saca_fwd(P: Params, pre: str, img_tok: torch.Tensor, objs, no_obj_sa: bool, need_object_output: bool, drop: DropCtx = NO_DROP):
     B, S, _ = img_tok.shape
-    att_img, sv_img = encoder_fwd(P, pre + "image_transformer_encoder.", img_tok)
+    att_img, sv_img = encoder_fwd(P, pre + "image_transformer_encoder.", img_tok, drop=drop)
     sv_obj = None
     if isinstance(objs, ObjectBatch):
         n_max = objs.n_max
@@ -178,7 +217,7 @@ def saca_fwd(P: Params, pre: str, img_tok: torch.Tensor, objs, no_obj_sa: bool, 
         padded, mask = ops.pad_objects(objs.rows, objs.offsets, B, n_max, n_max, 0.0001, False)            # :180-183
         att_obj = padded
         if not no_obj_sa:
-            att_obj, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", padded, mask)              # :188 (slow path)
+            att_obj, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", padded, mask, drop=drop)   # :188 (slow path)
         uni = objs.uniform_offsets(n_max)
         att_obj_s, kpm = ops.pad_objects(att_obj.reshape(B * n_max, E), uni, B, S, n_max, 0.0001, True,
                                          mask_offsets=objs.offsets)                                         # :192-194 (F5)
@@ -187,7 +226,7 @@ def saca_fwd(P: Params, pre: str, img_tok: torch.Tensor, objs, no_obj_sa: bool, 
         assert objs.shape == (B, S, E)
         att_obj_s = objs.contiguous()
         if not no_obj_sa:
-            att_obj_s, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", att_obj_s)
+            att_obj_s, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", att_obj_s, drop=drop)
         kpm = None
         geom = ("dense",)
     final_img, sv_c1 = cross_fwd(P, pre + "cross_attn_obj_im.", att_img, att_obj_s, att_img, kpm)          # :195-201
@@ -229,7 +268,7 @@ class Tape:
 
 
 def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_xywh_list=None, mutate_inputs: bool = True,
-            patch_size: int = 16, n_query: int = 128):
+            patch_size: int = 16, n_query: int = 128, drop: DropCtx = NO_DROP):
     """-> (depth_pred [B,1,h,w], bin_edges [B,K+1], tape).  ``cfg``: kind ('adabins' | 'graphbins'), strategy, no_obj_sa,
     use_2_saca, min_depth, max_depth."""
     t = Tape()
@@ -241,7 +280,7 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
         pt = pre + "patch_transformer."
         tok0 = ops.patch_embed(x, P[pt + "embedding_convPxP.weight"], P[pt + "embedding_convPxP.bias"],
                                P[pt + "positional_encodings"], patch_size)
-        tok, t.sv_enc = encoder_fwd(P, pt + "transformer_encoder.", tok0)
+        tok, t.sv_enc = encoder_fwd(P, pt + "transformer_encoder.", tok0, drop=drop)
     else:
         pre = "objcavit."
         strategy = cfg["strategy"]
@@ -263,9 +302,9 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
         tok0 = ops.patch_embed(x, P[pre + "image_embedding_convPxP.weight"], P[pre + "image_embedding_convPxP.bias"], img_pos,
                                patch_size)
         two = bool(cfg.get("use_2_saca"))
-        tok, obj_out, t.sv_saca1 = saca_fwd(P, pre + "saca_1.", tok0, batch, bool(cfg.get("no_obj_sa")), two)
+        tok, obj_out, t.sv_saca1 = saca_fwd(P, pre + "saca_1.", tok0, batch, bool(cfg.get("no_obj_sa")), two, drop)
         if two:
-            tok, _, t.sv_saca2 = saca_fwd(P, pre + "saca_2.", tok, obj_out, bool(cfg.get("no_obj_sa")), False)
+            tok, _, t.sv_saca2 = saca_fwd(P, pre + "saca_2.", tok, obj_out, bool(cfg.get("no_obj_sa")), False, drop)
     t.pre = pre
     S = tok.shape[1]
     t.tok = tok

@@ -28,7 +28,9 @@ class _HeadTrainFn(torch.autograd.Function):
     def forward(ctx, head, cfg, x, object_features, object_xywh_list, keys, *params):
         from .. import engine_train
         P = {k: p.detach() for k, p in zip(keys, params)}
-        depth, edges, tape = engine_train.forward(P, cfg, x.detach().contiguous().float(), object_features, object_xywh_list)
+        drop = engine_train.DropCtx(cfg.get("dropout", 0.0), cfg.get("dropout_seed", 0))
+        depth, edges, tape = engine_train.forward(P, cfg, x.detach().contiguous().float(), object_features, object_xywh_list,
+                                                  drop=drop)
         ctx.tape, ctx.P, ctx.keys = tape, P, keys
         ctx.needs = [p.requires_grad for p in params]
         return depth, edges
@@ -51,8 +53,18 @@ class _HeadTrainFn(torch.autograd.Function):
         return (None,) * 6 + tuple(dict.__getitem__(G, k) if (need and k in touched) else None for k, need in zip(keys, ctx.needs))
 
 
+def draw_dropout_seed() -> int:
+    """Base seed of one training forward's dropout masks, drawn from torch's CPU generator: reproducible under
+    ``torch.manual_seed`` like the reference's masks, without a device synchronisation."""
+    return int(torch.randint(0, 2 ** 47, (1,)).item())
+
+
 class _HeadBase(KernelModule):
     precision = "fp32"   # "fp32": parity path (SIMT fp32).  "bf16": tensor-core path (tcgen05).
+    # Dropout probability of the encoder layers while ``self.training`` (nn.TransformerEncoderLayer's default, which the
+    # reference never overrides: modules/layers.py:8, modules/ObjCAViT.py:155-161).  The reference's modules are switched off
+    # with ``m.p = 0`` / ``mha.dropout = 0``; here it is this one attribute.  ``eval()`` or 0.0 = no dropout kernels at all.
+    dropout = 0.1
 
     def enable_pipeline(self, lanes: int = 2, pixel_ctas: int = 0):
         """Pipelined serving mode of the bf16 path (``ocv_head_set_pipeline``): consecutive ``forward`` calls overlap — the
@@ -81,6 +93,8 @@ class _HeadBase(KernelModule):
                                       "frozen in config 5); pass features.detach()")
         named = list(self.named_parameters())
         keys = tuple(k for k, _ in named)
+        if self.training and self.dropout > 0:
+            cfg = dict(cfg, dropout=float(self.dropout), dropout_seed=draw_dropout_seed())
         return _HeadTrainFn.apply(self, cfg, x, object_features, object_xywh_list, keys, *[p for _, p in named])
 
     def _depth_range(self):

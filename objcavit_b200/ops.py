@@ -127,8 +127,9 @@ def add_layernorm(x: torch.Tensor, r, gamma, beta, zero_rows=None, out=None):
     return out
 
 
-def mha_core(q, k, v, key_padding_mask=None, heads: int = 4):
-    """q [B,Sq,E], k/v [B,Sk,E] views with unit channel stride -> [B,Sq,E]."""
+def mha_core(q, k, v, key_padding_mask=None, heads: int = 4, drop=None):
+    """q [B,Sq,E], k/v [B,Sk,E] views with unit channel stride -> [B,Sq,E].  ``drop`` = (p, seed): dropout on the attention
+    probabilities (training mode)."""
     for t, n in ((q, "q"), (k, "k"), (v, "v")):
         _chk(t, torch.float32, n)
         assert t.dim() == 3 and t.stride(2) == 1
@@ -138,6 +139,11 @@ def mha_core(q, k, v, key_padding_mask=None, heads: int = 4):
     if key_padding_mask is not None:
         _chk(key_padding_mask, torch.uint8, "key_padding_mask")
         assert key_padding_mask.is_contiguous() and key_padding_mask.shape == (B, Sk)
+    if drop is not None and drop[0] > 0:
+        _call("ocv_mha_core_dropout_f32", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), _ptr(key_padding_mask),
+              B, Sq, Sk, heads, E // heads, q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0),
+              v.stride(1), out.stride(0), out.stride(1), float(drop[0]), int(drop[1]), _stream())
+        return out
     _call("ocv_mha_core_f32", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), _ptr(key_padding_mask),
           B, Sq, Sk, heads, E // heads, q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0),
           v.stride(1), out.stride(0), out.stride(1), _stream())
@@ -684,7 +690,7 @@ def layernorm_bwd(dy: torch.Tensor, z: torch.Tensor, gamma: torch.Tensor, dgamma
     return dz
 
 
-def mha_core_bwd(q, k, v, out, dout, key_padding_mask=None, heads: int = 4, packed: bool = False):
+def mha_core_bwd(q, k, v, out, dout, key_padding_mask=None, heads: int = 4, packed: bool = False, drop=None):
     """Backward of :func:`mha_core`: returns (dq, dk, dv) dense [B,S,E]; ``packed`` (self-attention, Sq == Sk): the three are
     views of one [B,S,3E] buffer laid out like the packed QKV projection output."""
     for t, n in ((q, "q"), (k, "k"), (v, "v"), (out, "out"), (dout, "dout")):
@@ -702,10 +708,11 @@ def mha_core_bwd(q, k, v, out, dout, key_padding_mask=None, heads: int = 4, pack
         dk = torch.empty(B, Sk, E, device=q.device, dtype=torch.float32)
         dv = torch.empty(B, Sk, E, device=q.device, dtype=torch.float32)
     ws = _workspace(B * heads * Sq * 12, q.device, "mha_bwd")
-    _call("ocv_mha_core_bwd_f32", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), dout.data_ptr(), _ptr(key_padding_mask),
-          dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), B, Sq, Sk, heads, E // heads, q.stride(0), q.stride(1), k.stride(0),
-          k.stride(1), v.stride(0), v.stride(1), out.stride(0), out.stride(1), dq.stride(0), dq.stride(1), dk.stride(0),
-          dk.stride(1), dv.stride(0), dv.stride(1), ws.data_ptr(), _stream(), launches=2)
+    dp, dseed = (float(drop[0]), int(drop[1])) if drop is not None else (0.0, 0)
+    _call("ocv_mha_core_bwd_dropout_f32", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), dout.data_ptr(),
+          _ptr(key_padding_mask), dq.data_ptr(), dk.data_ptr(), dv.data_ptr(), B, Sq, Sk, heads, E // heads, q.stride(0), q.stride(1),
+          k.stride(0), k.stride(1), v.stride(0), v.stride(1), out.stride(0), out.stride(1), dq.stride(0), dq.stride(1), dk.stride(0),
+          dk.stride(1), dv.stride(0), dv.stride(1), dp, dseed, ws.data_ptr(), _stream(), launches=2)
     return (dq, dk, dv, dqkv) if packed else (dq, dk, dv)
 
 
@@ -833,3 +840,13 @@ def ffn_fused_bf16(x16: torch.Tensor, x32: torch.Tensor, w1: torch.Tensor, b1, w
     _call("ocv_ffn_fused_bf16", x16.data_ptr(), 128, w1.data_ptr(), b1.data_ptr(), w2.data_ptr(), b2.data_ptr(), x32.data_ptr(), 128,
           gamma.data_ptr(), beta.data_ptr(), _ptr(zero_rows), o32.data_ptr(), 128, o16.data_ptr(), 128, M, F_, _stream())
     return o32, o16
+
+
+def dropout(x: torch.Tensor, p: float, seed: int, residual=None, out=None) -> torch.Tensor:
+    """out = residual + dropout(x) with the counter-based mask of site ``seed`` (``ocv_dropout_f32``); on a gradient: its backward."""
+    _chk(x, torch.float32, "x")
+    assert x.is_contiguous() and (residual is None or (residual.is_contiguous() and residual.shape == x.shape))
+    if out is None:
+        out = torch.empty_like(x)
+    _call("ocv_dropout_f32", x.data_ptr(), _ptr(residual), out.data_ptr(), x.numel(), float(p), int(seed), _stream())
+    return out

@@ -19,6 +19,7 @@ import torch.distributed as dist
 
 from . import engine_train, ops
 from .grad_sync import FlatGradBuffer
+from .modules.heads import draw_dropout_seed
 
 
 class OneCycle:
@@ -98,7 +99,9 @@ class HeadTrainer:
         """Local forward + loss + backward; gradients accumulate into the flat buffer.  Returns the loss (device scalar)."""
         P, G = self._maps()
         x = features.contiguous().float()
-        depth, edges, tape = engine_train.forward(P, self.cfg, x, object_features, object_xywh_list)
+        p_drop = float(self.head.dropout) if self.head.training else 0.0      # encoder-layer dropout, as the reference in train()
+        drop = engine_train.DropCtx(p_drop, draw_dropout_seed() if p_drop > 0 else 0)
+        depth, edges, tape = engine_train.forward(P, self.cfg, x, object_features, object_xywh_list, drop=drop)
         gt = depth_gt.contiguous().float()
         l1, d_depth = ops.silog(depth, gt, depth_mask, want_grad=True, grad_scale=self.coeffs[0])
         l2, d_edges = ops.bins_chamfer(edges, gt, depth_mask, want_grad=True, grad_scale=self.coeffs[1])

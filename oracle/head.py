@@ -26,7 +26,17 @@ SD = Dict[str, torch.Tensor]
 # ----------------------------------------------------------------------------------------------
 
 
-def mha(sd: SD, pre: str, query, key, value, num_heads: int = 4, key_padding_mask=None):
+# Tests only: a callable(tensor) -> tensor that applies the NEXT dropout site's mask (train() mode of the reference: dropout 0.1 at
+# four sites per nn.TransformerEncoderLayer, in call order: attention probabilities, dropout1, dropout, dropout2).  None = no
+# dropout (eval(), or the "dropout disabled" configuration gradient parity is pinned on).
+DROPOUT_HOOK = None
+
+
+def _drop(t):
+    return t if DROPOUT_HOOK is None else DROPOUT_HOOK(t)
+
+
+def mha(sd: SD, pre: str, query, key, value, num_heads: int = 4, key_padding_mask=None, attn_dropout: bool = False):
     """``nn.MultiheadAttention`` forward, batch-first ``[B,S,E]`` operands, ``need_weights=False``.
 
     Call sites: ``modules/ObjCAViT.py:195-207`` (cross attention) and inside every
@@ -49,16 +59,18 @@ def mha(sd: SD, pre: str, query, key, value, num_heads: int = 4, key_padding_mas
     if key_padding_mask is not None:
         scores = scores.masked_fill(key_padding_mask[:, None, None, :], float("-inf"))
     attn = torch.softmax(scores, dim=-1)
+    if attn_dropout:                      # self-attention of an encoder layer; the cross-attention MHAs are built with dropout 0
+        attn = _drop(attn)
     out = (attn @ v).transpose(1, 2).reshape(B, Sq, E)
     return out @ sd[pre + "out_proj.weight"].T + sd[pre + "out_proj.bias"]
 
 
 def encoder_layer(sd: SD, pre: str, x, num_heads: int = 4, key_padding_mask=None):
     """``nn.TransformerEncoderLayer`` (post-norm, ReLU, eps 1e-5), batch-first ``[B,S,E]``."""
-    a = mha(sd, pre + "self_attn.", x, x, x, num_heads, key_padding_mask)
-    x = F.layer_norm(x + a, (x.shape[-1],), sd[pre + "norm1.weight"], sd[pre + "norm1.bias"], 1e-5)
-    h = torch.relu(x @ sd[pre + "linear1.weight"].T + sd[pre + "linear1.bias"])
-    h = h @ sd[pre + "linear2.weight"].T + sd[pre + "linear2.bias"]
+    a = mha(sd, pre + "self_attn.", x, x, x, num_heads, key_padding_mask, attn_dropout=True)
+    x = F.layer_norm(x + _drop(a), (x.shape[-1],), sd[pre + "norm1.weight"], sd[pre + "norm1.bias"], 1e-5)
+    h = _drop(torch.relu(x @ sd[pre + "linear1.weight"].T + sd[pre + "linear1.bias"]))
+    h = _drop(h @ sd[pre + "linear2.weight"].T + sd[pre + "linear2.bias"])
     return F.layer_norm(x + h, (x.shape[-1],), sd[pre + "norm2.weight"], sd[pre + "norm2.bias"], 1e-5)
 
 
@@ -301,7 +313,7 @@ def pad_objects(object_features, S: Optional[int] = None):
     B = len(seqs)
     n_max = max(int(o.shape[0]) for o in seqs)
     E = seqs[0].shape[1]
-    padded = torch.full((B, n_max, E), 0.0001, dtype=torch.float32)
+    padded = torch.full((B, n_max, E), 0.0001, dtype=seqs[0].dtype)     # float32 in the reference
     mask = torch.ones(B, n_max, dtype=torch.bool)
     for b, o in enumerate(seqs):
         padded[b, : o.shape[0]] = o
@@ -353,11 +365,12 @@ def objcavit_forward(sd: SD, image_features, object_features: List[torch.Tensor]
     """``ObjCAViT.forward`` (``ObjCAViT.py:306-390``) -> ``(bin_widths_normed, ram)``.
     Does NOT mutate the caller's list (the reference does, F11; the product wrapper mimics that)."""
     B, _, h, w = image_features.shape
+    dt = image_features.dtype       # float32 as the reference's .float(); the tests' fp64 runs of the oracle follow the features
     objs = []
     for i, xywhs in enumerate(object_xywh_list):                                   # :311-330
         if xywhs is None:
             xywhs = torch.zeros((1, 4)) - 1                                        # :313
-        xywhs = xywhs.float()
+        xywhs = xywhs.to(dt)
         if strategy == "grid_random":
             pos = grid_random_pos(sd[pre + "positional_encoder.positional_encodings"], "centre",
                                   xywhs[:, 0:2], h, w, "obj", patch_size)
@@ -368,13 +381,13 @@ def objcavit_forward(sd: SD, image_features, object_features: List[torch.Tensor]
             pos = _pos_mlp(sd, pre + "positional_encoder.", xywhs[:, 0:4])
         else:
             pos = _pos_mlp(sd, pre + "positional_encoder.", xywhs[:, 0:2])
-        emb = object_features[i].float() @ sd[pre + "obj_embedding_layer.weight"].T + sd[pre + "obj_embedding_layer.bias"]
+        emb = object_features[i].to(dt) @ sd[pre + "obj_embedding_layer.weight"].T + sd[pre + "obj_embedding_layer.bias"]
         objs.append(emb + pos)                                                     # :330
 
     pe = F.conv2d(image_features, sd[pre + "image_embedding_convPxP.weight"],
                   sd[pre + "image_embedding_convPxP.bias"], stride=patch_size)     # :333
     gh, gw = pe.shape[2], pe.shape[3]
-    pc = patch_coords(B, gh, gw, patch_size)                                       # :336-347
+    pc = patch_coords(B, gh, gw, patch_size).to(dt)                                # :336-347
     if strategy == "grid_random":
         ipos = grid_random_pos(sd[pre + "positional_encoder.positional_encodings"], "centre",
                                pc[..., 0:2], h, w, "img", patch_size)

@@ -40,6 +40,7 @@ def _load(name):
 
 def _run_cuda(args, sd, feats, objs, boxes, gt, mask, cuda):
     head = build_head(args, precision="fp32").to(cuda).train()
+    head.dropout = 0.0          # the fixtures were generated with the reference's dropout modules switched off (p = 0)
     head.load_state_dict(sd, strict=True)
     largs = AttrDict({"loss": {"names": ["silog", "bins_chamfer"], "coeffs": [1, 0.1]}})
     crit = LossWrapper(largs)
@@ -95,6 +96,7 @@ def test_training_forward_equals_inference_forward_without_padding(cuda):
     """AdaBins head: no padded rows exist, so the grad-mode forward must equal the no_grad forward bit for bit (same kernels)."""
     case, args, sd, feats, objs, boxes, gt, mask, gold = _load("train_adabins_small")
     head = build_head(args, precision="fp32").to(cuda)
+    head.dropout = 0.0
     head.load_state_dict(sd, strict=True)
     a = head(feats.to(cuda))
     with torch.no_grad():

@@ -68,7 +68,7 @@ def test_trainer_step_equals_autograd_boundary_plus_torch_adamw(cuda):
     # torch side: the autograd boundary + torch's clip + AdamW
     from objcavit_b200.config import AttrDict
     from objcavit_b200.losses import LossWrapper
-    a = build_head(args).to(cuda).train(); a.load_state_dict(sd)
+    a = build_head(args).to(cuda).train(); a.load_state_dict(sd); a.dropout = 0.0   # the two arms must see the same (no) masks
     opt = torch.optim.AdamW(a.parameters(), lr=3.57e-4, weight_decay=0.1)
     out = a(feats.to(cuda), dev(objs), dev(boxes))
     loss = LossWrapper(AttrDict({"loss": {"names": ["silog", "bins_chamfer"], "coeffs": [1, 0.1]}}))(
@@ -77,7 +77,7 @@ def test_trainer_step_equals_autograd_boundary_plus_torch_adamw(cuda):
     torch.nn.utils.clip_grad_norm_([p for p in a.parameters() if p.grad is not None], 0.1)
     opt.step()
     # native step
-    b = build_head(args).to(cuda).train(); b.load_state_dict(sd)
+    b = build_head(args).to(cuda).train(); b.load_state_dict(sd); b.dropout = 0.0
     tr = HeadTrainer(b, lr=3.57e-4, weight_decay=0.1, clip_grad_norm=0.1)
     l1, l2 = tr.step(feats.to(cuda), dev(objs), dev(boxes), gt.to(cuda), mask.to(cuda))
     torch.cuda.synchronize()
