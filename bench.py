@@ -218,7 +218,8 @@ def run_train(a):
         dist.init_process_group("nccl", device_id=dev)
     B = a.batch if a.batch != 16 else 8
     W_, K = max(a.warmup, 3), a.steps
-    head = build_head(builtin_args(CFG_NAME), precision="fp32").to(dev).train()
+    tprec = a.precision or "fp32"     # "bf16": pixel path of the step on tcgen05 (bf16 operands); token path fp32 either way
+    head = build_head(builtin_args(CFG_NAME), precision=tprec).to(dev).train()
     head.load_state_dict(load_weights(CFG_NAME), strict=True)
     trainer = HeadTrainer(head, lr=0.000357, weight_decay=0.1, clip_grad_norm=0.1,
                           schedule=OneCycle(0.000357, max(W_ + 3 * K + 16, 100), 25, 100))
@@ -284,7 +285,7 @@ def run_train(a):
     dom, dom_ms = top[0]
     pk = peaks()
     step_tf = GF_TRAIN * B * K / ms                  # GFLOP/ms == TFLOP/s, whole step on the algorithmic FLOPs
-    roofline = {"bound": "tensor", "kernel": f"{dom} (fp32 SIMT; all calls of one step)", "achieved": step_tf,
+    roofline = {"bound": "tensor", "kernel": f"{dom} ({'pixel path tcgen05 bf16, token path fp32 SIMT' if tprec == 'bf16' else 'fp32 SIMT'}; all calls of one step)", "achieved": step_tf,
                 "peak": pk["tf_sust"], "unit": "TFLOP/s", "frac": step_tf / pk["tf_sust"], "traffic": None,
                 "peak_source": pk["src"] + " (bf16 sustained); achieved = 56.5 GF/image x images/s of the WHOLE step",
                 "kernel_ms": dom_ms, "kernel_share_of_step": dom_ms / max(sum(agg.values()), 1e-9),
@@ -297,7 +298,7 @@ def run_train(a):
     out = {
         "metric": TRAIN_METRIC,
         "value": value, "unit": "images/s", "n_gpus": world, "steps": K, "warmup": W_, "ms_per_step": ms / K,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if tprec == "bf16" else "f32", "data": "synthetic",
         "config": {"workload": f"{CFG_NAME} head training step, {NOBJ} boxes/img, frozen features 128x{TRAIN_H}x{TRAIN_W} fp32, "
                                f"GT {2 * TRAIN_H}x{2 * TRAIN_W}, batch {B}/GPU, encoder dropout {head.dropout} (train() mode, as the reference)",
                    "batch_per_gpu": B, "parallelism": f"dp{world} (batch sharded, one all-reduce of "

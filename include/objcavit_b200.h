@@ -289,6 +289,26 @@ int ocv_mha_core_bwd_dropout_f32(const float* q, const float* k, const float* v,
                                  int v_rstride, long long o_bstride, int o_rstride, long long dq_bstride, int dq_rstride,
                                  long long dk_bstride, int dk_rstride, long long dv_bstride, int dv_rstride, float drop_p,
                                  unsigned long long drop_seed, void* workspace, void* stream);
+
+/* ---- training step, tensor-core pixel path (precision "bf16"; objcavit_b200/csrc/train_pixel_bf16.cu) ----------------------
+ * The pixel path of the training step as tcgen05 GEMMs (ocv_conv3x3_nhwc_bf16, ocv_gemm_bf16) joined by HBM-bound helpers:
+ *   ocv_tail_logits_f32: depth [B,P] = sum_k softmax_k(logits[b,k,p] + bias[k]) centres[b,k] on channel-major fp32 logits
+ *     [B,K,P] (one pass, online softmax).  replaces conv_out's Softmax + torch.sum(out*centers) (modules/AdaBins.py:77,87).
+ *   ocv_tail_logits_bwd_bf16: its backward — dlT [B,K,P] bf16 = g p (c - depth); grad_centres [B,K] = sum_p g p;
+ *     grad_bias [K] = bias_beta*grad_bias + sum_{b,p} dl  (fixed-order block partials in `workspace`: deterministic).
+ *   ocv_transpose_bf16: dst[z][c][r] = src[z][r][c], bf16, R % 64 == 0, C % 64 == 0 (strides in elements, even).
+ *   ocv_im2col3x3_bf16: col [C*9+8, B*P] bf16 from the planar map x [B,C,h,w] bf16: row c*9+ky*3+kx = the map shifted by
+ *     (ky-1, kx-1) with zero padding, row C*9 = 1 (its GEMM column is the conv bias gradient), 7 zero rows.  (h*w) % 8 == 0.
+ * (backward of) self.conv3x3 (modules/miniViT.py:25; modules/ObjCAViT.py:374) as ONE GEMM dW[o, :] = dx3T[o, B*P] @ col^T. */
+int ocv_tail_logits_f32(const float* logits, const float* logit_bias, const float* centres, float* depth, int B, int K,
+                        long long P, void* stream);
+long long ocv_tail_logits_bwd_workspace(int B, int K, long long P);
+int ocv_tail_logits_bwd_bf16(const float* logits, const float* logit_bias, const float* centres, const float* grad_depth,
+                             void* dlT_bf16, float* grad_centres, float* grad_bias, float bias_beta, int B, int K, long long P,
+                             void* workspace, void* stream);
+int ocv_transpose_bf16(const void* src, void* dst, int batch, int R, int C, long long src_bstride, long long src_ld,
+                       long long dst_bstride, long long dst_ld, void* stream);
+int ocv_im2col3x3_bf16(const void* x_planar_bf16, void* col_bf16, int B, int C, int h, int w, void* stream);
 /* Adjoint of ocv_pad_objects_f32: dsrc[offsets[b]+j, :] = beta * dsrc + dpadded[b, left+j, :] for j < n_b (left = L-Nmax when
  * left_pad else 0); pad rows carry no gradient. */
 int ocv_unpad_objects_f32(const float* dpadded, const int32_t* offsets, float* dsrc, int B, int L, int Nmax, int E, int left_pad,

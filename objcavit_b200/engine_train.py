@@ -309,12 +309,89 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
     S = tok.shape[1]
     t.tok = tok
     Q = min(n_query, S - 1)
-    t.x3 = ops.conv3x3(x, P[pre + "conv3x3.weight"], P[pre + "conv3x3.bias"])
-    t.ram = ops.batched_matmul_nn(tok[:, 1:Q + 1, :], t.x3.view(B, C, h * w)).view(B, Q, h, w)
     t.y_raw, t.sv_reg = mlp_fwd(P, pre + "regressor.", tok[:, 0, :], (0, 2, 4))
     _, edges, t.centres = ops.bins(t.y_raw, "linear", cfg["min_depth"], cfg["max_depth"])
-    depth = ops.tail(t.ram, P["conv_out.0.weight"], P["conv_out.0.bias"], t.centres)
+    t.pixel = cfg.get("pixel", "fp32")
+    t.Q = Q
+    if t.pixel == "bf16":
+        depth = _pixel_fwd_bf16(P, pre, t, x, tok, Q)
+    else:
+        t.x3 = ops.conv3x3(x, P[pre + "conv3x3.weight"], P[pre + "conv3x3.bias"])
+        t.ram = ops.batched_matmul_nn(tok[:, 1:Q + 1, :], t.x3.view(B, C, h * w)).view(B, Q, h, w)
+        depth = ops.tail(t.ram, P["conv_out.0.weight"], P["conv_out.0.bias"], t.centres)
     return depth, edges, t
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# Pixel path on tensor cores (cfg["pixel"] == "bf16"): conv3x3, logits and every pixel-sized gradient GEMM are tcgen05 kernels on
+# bf16 operands (fp32 accumulation), joined by the HBM-bound helpers of csrc/train_pixel_bf16.cu.  The 128 range-attention
+# channels are folded away as in the inference kernel: logits[b] = Mb[b] x3[b] + bout with Mb[b] = Wout @ queries[b]  (K x C),
+# so neither ram nor d ram is ever formed.  Every GEMM sees its contraction dimension contiguous (K-major operands):
+#   logits[b] [K,P]   = Mb[b] [K,C]     @ x3[b] [P,C]^T            (x3 NHWC, as the conv kernel writes it)
+#   dx3T[:, b] [C,P]  = Mb[b]^T [C,K]   @ dl[b] [P,K]^T            (dl pixel-major: transposed copy of dlT)
+#   dMb[b] [K,C]      = dlT[b] [K,P]    @ x3T[b] [C,P]^T           (split-K over pixels)
+#   dW3 [C, 9C]       = dx3T [C, B P]   @ col [9C, B P]^T          (ONE split-K GEMM for the batch; col = im2col of the planar map)
+# Gradient precision is bf16 (operands rounded to 8 mantissa bits); the fp32 path stays the parity reference.
+# ----------------------------------------------------------------------------------------------------------------------
+
+def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, Q: int) -> torch.Tensor:
+    B, C, h, w = x.shape
+    Pn, S = h * w, tok.shape[1]
+    Wout = P["conv_out.0.weight"].view(-1, Q)
+    K = Wout.shape[0]
+    xh = ops.nchw_to_nhwc_bf16(x)
+    t.x3h = ops.conv3x3_nhwc_bf16(xh, ops.pack_conv3x3_bf16(P[pre + "conv3x3.weight"]), P[pre + "conv3x3.bias"])
+    del xh
+    Mb = torch.empty(B, K, E, device=x.device, dtype=torch.float32)
+    ops.gemm_ex(Wout, tok[:, 1:Q + 1, :], K, E, Q, Q, E, Mb, E, batch=B, stride_a=0, stride_b=S * E, stride_c=K * E)
+    t.Mb16 = ops.cast_bf16(Mb)
+    t.logits = torch.empty(B, K, Pn, device=x.device, dtype=torch.float32)
+    x3 = t.x3h.view(B, Pn, C)
+    for b in range(B):
+        ops.gemm_bf16(t.Mb16[b], x3[b], out=t.logits[b])
+    return ops.tail_logits(t.logits, P["conv_out.0.bias"], t.centres).view(B, 1, h, w)
+
+
+def _pixel_bwd_bf16_tail(P: Params, G: Params, t, gd: torch.Tensor):
+    """-> (dlT [B,K,P] bf16, d loss / d centres [B,K]); accumulates the conv_out bias gradient."""
+    dlT, dcent = ops.tail_logits_bwd(t.logits, P["conv_out.0.bias"], t.centres, gd, grad_bias=G["conv_out.0.bias"], beta=1.0)
+    t.logits = None
+    return dlT, dcent
+
+
+def _pixel_bwd_bf16_rest(P: Params, G: Params, t, dlT: torch.Tensor, dtok: torch.Tensor) -> None:
+    """conv_out weight, query (into ``dtok[:, 1:Q+1]``), conv3x3 weight and bias gradients from dlT."""
+    pre, x, tok, Q = t.pre, t.x, t.tok, t.Q
+    B, C, h, w = t.shape
+    Pn, S = h * w, tok.shape[1]
+    dev = x.device
+    Wout = P["conv_out.0.weight"].view(-1, Q)
+    K = Wout.shape[0]
+    # d x3 (channel-major over the whole batch: the A operand of the weight-gradient GEMM)
+    dl = ops.transpose_bf16(dlT)                                              # [B,P,K]
+    MbT16 = ops.transpose_bf16(t.Mb16)                                        # [B,C,K]
+    dx3T = torch.empty(C, B * Pn, device=dev, dtype=torch.bfloat16)
+    for b in range(B):
+        ops.gemm_bf16(MbT16[b], dl[b], out=dx3T[:, b * Pn:(b + 1) * Pn])
+    del dl
+    # d Mb -> conv_out weight and queries
+    x3T = ops.transpose_bf16(t.x3h.view(B, Pn, C))                            # [B,C,P]
+    dMb = torch.empty(B, K, E, device=dev, dtype=torch.float32)
+    sk = max(1, min(64, Pn // 1024))
+    for b in range(B):
+        ops.gemm_bf16(dlT[b], x3T[b], out=dMb[b], split_k=sk)
+    del x3T, dlT
+    queries = tok[:, 1:Q + 1, :]
+    ops.gemm_ex(dMb, queries, K, Q, E, E, E, G["conv_out.0.weight"], Q, op_b=1, beta=1.0, batch=B, stride_a=K * E, stride_b=S * E,
+                reduce_batch=True)
+    ops.gemm_ex(Wout, dMb, Q, E, K, Q, E, dtok[:, 1:Q + 1, :], E, trans_a=True, batch=B, stride_a=0, stride_b=K * E, stride_c=S * E)
+    # conv3x3 weight + bias: one GEMM over all pixels of the batch
+    col = ops.im2col3x3_bf16(ops.cast_bf16(x))
+    gw = G[pre + "conv3x3.weight"].view(C, C * 9)
+    skw = max(1, min(32, (B * Pn) // 8192))
+    ops.gemm_bf16(dx3T, col[:C * 9], residual=gw, out=gw, split_k=skw)
+    db = ops.gemm_bf16(dx3T, col[C * 9:], split_k=skw)                        # [C,8]: column 0 = sum over pixels, the rest 0
+    ops.reduce_channels(db, G[pre + "conv3x3.bias"], 1, 1, C, 8, beta=1.0)
 
 
 def backward(P: Params, G: Params, t: Tape, d_depth: torch.Tensor, d_edges: Optional[torch.Tensor]) -> None:
@@ -325,11 +402,19 @@ def backward(P: Params, G: Params, t: Tape, d_depth: torch.Tensor, d_edges: Opti
     dev = x.device
     tok = t.tok
     S = tok.shape[1]
-    Q = t.ram.shape[1]
+    Q = t.Q
     Wout = P["conv_out.0.weight"].view(-1, Q)
     K = Wout.shape[0]
-    ram = t.ram.view(B, Q, Pn)
     gd = d_depth.contiguous().view(B, Pn)
+    if t.pixel == "bf16":
+        dlT, dcent = _pixel_bwd_bf16_tail(P, G, t, gd)
+        dy_raw = ops.bins_bwd(t.y_raw, d_edges.contiguous() if d_edges is not None else None, dcent, cfg["min_depth"], cfg["max_depth"])
+        dtok = torch.zeros(B, S, E, device=dev, dtype=torch.float32)
+        mlp_bwd(P, G, pre + "regressor.", (0, 2, 4), t.sv_reg, dy_raw, dx_out=dtok[:, 0, :])
+        _pixel_bwd_bf16_rest(P, G, t, dlT, dtok)
+        del dlT
+        return _token_bwd(P, G, t, dtok)
+    ram = t.ram.view(B, Q, Pn)
     # ---- tail: depth = sum_k softmax_k(Wout ram + bout) c_k ----------------------------------------------------------
     logits = torch.empty(B, K, Pn, device=dev, dtype=torch.float32)
     ops.gemm_ex(Wout, ram, K, Pn, Q, Q, Pn, logits, Pn, batch=B, stride_a=0, stride_b=Q * Pn, stride_c=K * Pn)
@@ -359,7 +444,15 @@ def backward(P: Params, G: Params, t: Tape, d_depth: torch.Tensor, d_edges: Opti
                 stride_b=C * Pn, reduce_batch=True, split_k=_split(C, C * 9, B, Pn), geom=(C, h, w, 0))
     ops.reduce_channels(dx3, G[pre + "conv3x3.bias"], 1, B, C, Pn, beta=1.0)
     del dx3
-    # ---- tokens -------------------------------------------------------------------------------------------------------
+    _token_bwd(P, G, t, dtok)
+
+
+def _token_bwd(P: Params, G: Params, t: Tape, dtok: torch.Tensor) -> None:
+    """Backward of everything that produced the tokens, from d loss / d tokens [B,S,E]."""
+    cfg, pre, x = t.cfg, t.pre, t.x
+    B, C, h, w = t.shape
+    dev = x.device
+    S = t.tok.shape[1]
     if cfg["kind"] == "adabins":
         pt = pre + "patch_transformer."
         dtok0 = encoder_bwd(P, G, pt + "transformer_encoder.", t.sv_enc, dtok)

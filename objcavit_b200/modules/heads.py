@@ -87,7 +87,9 @@ class _HeadBase(KernelModule):
                                             (torch.is_tensor(x) and x.requires_grad))
 
     def _train_forward(self, cfg, x, object_features, object_xywh_list):
-        """Grad-mode forward (the reference's training step): fp32 kernels + explicit backward, for either ``precision``."""
+        """Grad-mode forward (the reference's training step): explicit forward + backward kernels.  ``precision="fp32"``: every
+        kernel fp32 SIMT (the parity path); ``"bf16"``: the pixel path (conv3x3, logits and their gradients: 90 % of the FLOPs)
+        on tcgen05 with bf16 operands, the token path still fp32."""
         if torch.is_tensor(x) and x.requires_grad:
             raise NotImplementedError("objcavit_b200: gradients w.r.t. the decoder features are not produced (the extractor is "
                                       "frozen in config 5); pass features.detach()")
@@ -95,6 +97,8 @@ class _HeadBase(KernelModule):
         keys = tuple(k for k, _ in named)
         if self.training and self.dropout > 0:
             cfg = dict(cfg, dropout=float(self.dropout), dropout_seed=draw_dropout_seed())
+        if self.precision == "bf16":      # pixel path of the step on tensor cores (bf16 operands, fp32 accumulation)
+            cfg = dict(cfg, pixel="bf16")
         return _HeadTrainFn.apply(self, cfg, x, object_features, object_xywh_list, keys, *[p for _, p in named])
 
     def _depth_range(self):

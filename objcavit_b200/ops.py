@@ -850,3 +850,51 @@ def dropout(x: torch.Tensor, p: float, seed: int, residual=None, out=None) -> to
         out = torch.empty_like(x)
     _call("ocv_dropout_f32", x.data_ptr(), _ptr(residual), out.data_ptr(), x.numel(), float(p), int(seed), _stream())
     return out
+
+
+# ---- training step, tensor-core pixel path (csrc/train_pixel_bf16.cu) -------------------------------------------------
+
+def tail_logits(logits: torch.Tensor, bias, centres: torch.Tensor) -> torch.Tensor:
+    """depth [B,P] = sum_k softmax_k(logits[b,k,p] + bias[k]) centres[b,k]; logits channel-major fp32 [B,K,P]."""
+    _chk(logits, torch.float32, "logits"); _chk(centres, torch.float32, "centres")
+    assert logits.is_contiguous() and centres.is_contiguous()
+    B, K, Pn = logits.shape
+    depth = torch.empty(B, Pn, device=logits.device, dtype=torch.float32)
+    _call("ocv_tail_logits_f32", logits.data_ptr(), _ptr(bias), centres.data_ptr(), depth.data_ptr(), B, K, Pn, _stream())
+    return depth
+
+
+def tail_logits_bwd(logits: torch.Tensor, bias, centres: torch.Tensor, grad_depth: torch.Tensor, grad_bias=None, beta: float = 1.0):
+    """-> (dlT [B,K,P] bf16, grad_centres [B,K]); ``grad_bias`` [K] is beta-accumulated in place when given."""
+    _chk(logits, torch.float32, "logits"); _chk(grad_depth, torch.float32, "grad_depth")
+    assert logits.is_contiguous() and centres.is_contiguous() and grad_depth.is_contiguous()
+    B, K, Pn = logits.shape
+    dlT = torch.empty(B, K, Pn, device=logits.device, dtype=torch.bfloat16)
+    dcent = torch.empty(B, K, device=logits.device, dtype=torch.float32)
+    ws = _workspace(_lib.lib().ocv_tail_logits_bwd_workspace(B, K, Pn), logits.device, "tail_logits_bwd")
+    _call("ocv_tail_logits_bwd_bf16", logits.data_ptr(), _ptr(bias), centres.data_ptr(), grad_depth.data_ptr(), dlT.data_ptr(),
+          dcent.data_ptr(), _ptr(grad_bias), float(beta), B, K, Pn, ws.data_ptr(), _stream(), launches=2)
+    return dlT, dcent
+
+
+def transpose_bf16(src: torch.Tensor, out=None) -> torch.Tensor:
+    """[Z,R,C] bf16 (unit inner stride) -> [Z,C,R]; ``out``: any [Z,C,R] view with unit inner stride (e.g. a slice of [C, Z*R])."""
+    _chk(src, torch.bfloat16, "src")
+    Z, R, Cc = src.shape
+    assert src.stride(2) == 1
+    if out is None:
+        out = torch.empty(Z, Cc, R, device=src.device, dtype=torch.bfloat16)
+    assert tuple(out.shape) == (Z, Cc, R) and out.stride(2) == 1
+    _call("ocv_transpose_bf16", src.data_ptr(), out.data_ptr(), Z, R, Cc, src.stride(0), src.stride(1), out.stride(0), out.stride(1),
+          _stream())
+    return out
+
+
+def im2col3x3_bf16(x_planar: torch.Tensor) -> torch.Tensor:
+    """[B,C,h,w] bf16 -> col [C*9+8, B*h*w] bf16 (9 shifted copies per channel, a row of ones, 7 zero rows)."""
+    _chk(x_planar, torch.bfloat16, "x_planar")
+    assert x_planar.is_contiguous()
+    B, Cc, h, wd = x_planar.shape
+    col = torch.empty(Cc * 9 + 8, B * h * wd, device=x_planar.device, dtype=torch.bfloat16)
+    _call("ocv_im2col3x3_bf16", x_planar.data_ptr(), col.data_ptr(), B, Cc, h, wd, _stream())
+    return col

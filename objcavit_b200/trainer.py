@@ -85,6 +85,8 @@ class HeadTrainer:
         else:
             self.cfg = dict(kind="graphbins", strategy=oc.strategy, no_obj_sa=oc.no_obj_sa, use_2_saca=oc.use_2_saca,
                             min_depth=lo, max_depth=hi)
+        if getattr(head, "precision", "fp32") == "bf16":     # pixel path of the step on tensor cores (engine_train._pixel_*_bf16)
+            self.cfg["pixel"] = "bf16"
 
     def world(self) -> int:
         return dist.get_world_size(self.group) if dist.is_available() and dist.is_initialized() else 1

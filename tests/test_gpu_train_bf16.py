@@ -1,0 +1,100 @@
+"""GPU: the tensor-core pixel path of the training step (``precision="bf16"``: conv3x3, logits and all pixel-sized gradient GEMMs
+on tcgen05 with bf16 operands) against the fp32 parity path on the same inputs, plus its HBM-bound helper kernels against torch.
+
+Tolerance: north_star gives 2e-2 relative for the bf16 path; gradients: per parameter max |g - g32| <= 3e-2 * max(|g32|_max,
+1e-2 * largest |g| of the head) (bf16 operands carry 8 mantissa bits; typical measured errors are a few 1e-3).
+"""
+import json
+import os
+
+import pytest
+import torch
+
+from helpers import GOLD, rel_err
+from objcavit_b200 import ops
+from objcavit_b200.config import AttrDict, builtin_args
+from objcavit_b200.losses import LossWrapper
+from objcavit_b200.modules import build_head
+from oracle import synth
+from oracle.cases import TRAIN_CASES, case_gt, case_inputs
+
+pytestmark = pytest.mark.gpu
+
+
+def test_tail_logits_forward_backward(cuda):
+    torch.manual_seed(0)
+    B, K, Pn = 2, 256, 1000                                           # ragged last block
+    logits = torch.randn(B, K, Pn, device=cuda) * 3
+    bias = torch.randn(K, device=cuda)
+    centres = torch.rand(B, K, device=cuda).cumsum(1)
+    g = torch.randn(B, Pn, device=cuda)
+    l64 = logits.double().requires_grad_(True)
+    b64 = bias.double().requires_grad_(True)
+    c64 = centres.double().requires_grad_(True)
+    d64 = (torch.softmax(l64 + b64[None, :, None], 1) * c64[:, :, None]).sum(1)
+    depth = ops.tail_logits(logits, bias, centres)
+    assert rel_err(depth, d64.detach().float()) < 1e-5
+    (d64 * g.double()).sum().backward()
+    gb = torch.ones(K, device=cuda)
+    dlT, dcent = ops.tail_logits_bwd(logits, bias, centres, g, grad_bias=gb, beta=1.0)
+    assert rel_err(dlT.float(), l64.grad.float()) < 1e-2              # bf16 storage
+    assert rel_err(dcent, c64.grad.float()) < 1e-5
+    assert rel_err(gb - 1.0, b64.grad.float()) < 1e-4
+    dlT2, dcent2 = ops.tail_logits_bwd(logits, bias, centres, g)
+    assert torch.equal(dlT, dlT2) and torch.equal(dcent, dcent2)      # deterministic
+
+
+def test_transpose_and_im2col(cuda):
+    torch.manual_seed(1)
+    a = torch.randn(3, 128, 320, device=cuda).bfloat16()
+    assert torch.equal(ops.transpose_bf16(a), a.transpose(1, 2).contiguous())
+    big = torch.zeros(320, 3 * 128, device=cuda, dtype=torch.bfloat16)   # [C, Z*R] destination: slices as [Z,C,R] views
+    ops.transpose_bf16(a, out=big.view(320, 3, 128).permute(1, 0, 2))
+    assert torch.equal(big.view(320, 3, 128).permute(1, 2, 0), a)
+    x = torch.randn(2, 4, 6, 8, device=cuda).bfloat16()
+    col = ops.im2col3x3_bf16(x)
+    ref = torch.nn.functional.unfold(x.float(), 3, padding=1)             # [B, C*9, P]
+    assert torch.equal(col[:36].float(), ref.permute(1, 0, 2).reshape(36, -1))
+    assert torch.equal(col[36].float(), torch.ones(2 * 48, device=cuda)) and float(col[37:].float().abs().max()) == 0.0
+
+
+def _run(name, precision, cuda):
+    case = TRAIN_CASES[name]
+    args = builtin_args(case["args"])
+    with open(os.path.join(GOLD, f"manifest_{case['args']}.json")) as f:
+        sd = synth.make_state_dict(json.load(f), seed=case["seed"])
+    feats, objs, boxes = case_inputs(case)
+    gt, mask = case_gt(case, args)
+    head = build_head(args, precision=precision).to(cuda).train()
+    head.dropout = 0.0
+    head.load_state_dict(sd, strict=True)
+    dev = lambda lst: [None if t is None else t.to(cuda) for t in lst]
+    out = head(feats.to(cuda)) if objs is None else head(feats.to(cuda), dev(objs), dev(boxes))
+    crit = LossWrapper(AttrDict({"loss": {"names": ["silog", "bins_chamfer"], "coeffs": [1, 0.1]}}))
+    loss = crit(out.depth_pred, gt.to(cuda), mask.to(cuda), out)
+    loss.backward()
+    torch.cuda.synchronize()
+    return head, out, float(loss.detach())
+
+
+@pytest.mark.parametrize("name", ["train_adabins_small", "train_learned_bbox_wh_small"])
+def test_bf16_pixel_path_training_matches_fp32_path(cuda, name):
+    h32, o32, l32 = _run(name, "fp32", cuda)
+    h16, o16, l16 = _run(name, "bf16", cuda)
+    assert rel_err(o16.depth_pred.detach(), o32.depth_pred.detach()) < 2e-2
+    assert rel_err(o16.bin_edges.detach(), o32.bin_edges.detach()) < 1e-5      # token path is fp32 in both
+    assert abs(l16 - l32) < 2e-2 * abs(l32)
+    g32 = {k: p.grad for k, p in h32.named_parameters()}
+    gmax = max(float(g.abs().max()) for g in g32.values() if g is not None)
+    worst, bad = 0.0, []
+    for k, p in h16.named_parameters():
+        if g32[k] is None:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, k
+            continue
+        assert p.grad is not None, k
+        err = float((p.grad - g32[k]).abs().max()) / max(float(g32[k].abs().max()), 1e-2 * gmax)
+        worst = max(worst, err)
+        if err >= 3e-2:
+            bad.append(f"{k}: {err:.2e}")
+    print(f"{name}: bf16 pixel path, worst per-parameter gradient error vs fp32 path {worst:.2e}")
+    assert not bad, "; ".join(bad)
