@@ -309,6 +309,13 @@ int ocv_tail_logits_bwd_bf16(const float* logits, const float* logit_bias, const
 int ocv_transpose_bf16(const void* src, void* dst, int batch, int R, int C, long long src_bstride, long long src_ld,
                        long long dst_bstride, long long dst_ld, void* stream);
 int ocv_im2col3x3_bf16(const void* x_planar_bf16, void* col_bf16, int B, int C, int h, int w, void* stream);
+/* Operands of the patch-embedding weight gradient as a K-major GEMM  dW [E, C P P] = dtokT [E, B S] @ unfold [C P P, B S]^T
+ * (backward of embedding_convPxP, modules/layers.py:11-12,17; image_embedding_convPxP, modules/ObjCAViT.py:243,333):
+ *   ocv_patch_unfold_bf16: out[(c*P*P + py*P + px), b*S + sy*gw + sx] = x[b,c,sy*P+py,sx*P+px]; x fp32 NCHW, out bf16 with row
+ *     pitch ld (elements) >= B*S; columns >= B*S are left untouched (zero them once when ld is padded).
+ *   ocv_transpose_cast_f32_bf16: dst[c][r] = bf16(src[r][c]) for any R, C (pitches in elements). */
+int ocv_patch_unfold_bf16(const float* x, void* out_bf16, int B, int C, int h, int w, int P, long long ld, void* stream);
+int ocv_transpose_cast_f32_bf16(const float* src, void* dst_bf16, int R, int C, long long src_ld, long long dst_ld, void* stream);
 /* Adjoint of ocv_pad_objects_f32: dsrc[offsets[b]+j, :] = beta * dsrc + dpadded[b, left+j, :] for j < n_b (left = L-Nmax when
  * left_pad else 0); pad rows carry no gradient. */
 int ocv_unpad_objects_f32(const float* dpadded, const int32_t* offsets, float* dsrc, int B, int L, int Nmax, int E, int left_pad,

@@ -147,89 +147,196 @@ __global__ void layernorm_bwd_params_kernel(const float* __restrict__ dy, const 
   }
 }
 
-// ---- attention core backward (d = 32: lane = channel) --------------------------------------------------------------------
-// pass 1, warp per query row: softmax statistics (m, l), D = dO . O, and dq
-__global__ void mha_bwd_q_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
-                                 const float* __restrict__ o, const float* __restrict__ dout, const uint8_t* __restrict__ mask,
-                                 float* __restrict__ dq, float* __restrict__ stats, int Sq, int Sk, int heads, long long q_bs,
-                                 int q_rs, long long k_bs, int k_rs, long long v_bs, int v_rs, long long o_bs, int o_rs,
-                                 long long dq_bs, int dq_rs, float drop_p, unsigned long long drop_seed) {
-  const int b = blockIdx.z, hd = blockIdx.y;
-  const int i = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32, lane = threadIdx.x % 32;
-  if (i >= Sq) return;
-  const float scale = rsqrtf(32.f);
-  const uint32_t drop_thr = ocv_drop_threshold(drop_p);
-  const float drop_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
-  const unsigned long long drop_row = (((unsigned long long)b * heads + hd) * Sq + i) * Sk;
-  const float qi = q[b * q_bs + (long long)i * q_rs + hd * 32 + lane];
-  const float doi = dout[b * o_bs + (long long)i * o_rs + hd * 32 + lane];
-  const float oi = o[b * o_bs + (long long)i * o_rs + hd * 32 + lane];
-  const float D = warp_sum(doi * oi);
-  const float* kb = k + b * k_bs + hd * 32 + lane;
-  const float* vb = v + b * v_bs + hd * 32 + lane;
-  const uint8_t* mb = mask ? mask + (long long)b * Sk : nullptr;
-  float m = -INFINITY, l = 0.f;
-  for (int j = 0; j < Sk; ++j) {
-    if (mb && mb[j]) continue;
-    const float s = warp_sum(qi * kb[(long long)j * k_rs]) * scale;
-    const float mn = fmaxf(m, s);
-    l = l * __expf(m - mn) + __expf(s - mn);
-    m = mn;
-  }
-  float acc = 0.f;
-  for (int j = 0; j < Sk; ++j) {
-    if (mb && mb[j]) continue;
-    const float kj = kb[(long long)j * k_rs];
-    const float s = warp_sum(qi * kj) * scale;
-    const float p = __expf(s - m) / l;
-    float dP = warp_sum(doi * vb[(long long)j * v_rs]);
-    if (drop_p > 0.f) dP = ocv_drop_keep(drop_seed, drop_row + j, drop_thr) ? dP * drop_scale : 0.f;
-    acc = fmaf(p * (dP - D), kj, acc);
-  }
-  dq[b * dq_bs + (long long)i * dq_rs + hd * 32 + lane] = acc * scale;
-  if (lane == 0) {
-    float* st = stats + (((long long)b * heads + hd) * Sq + i) * 3;
-    st[0] = m; st[1] = l; st[2] = D;
+// ---- attention core backward (head dim 32) ------------------------------------------------------------------------------
+// Thread-per-row kernels: a thread owns one query (key) row in registers and walks the key (query) rows staged in shared memory,
+// so the 32-wide dot products are register FMAs instead of warp reductions.  Four threads share a row (each takes every fourth
+// staged row) and are combined by two shuffles; blocks of 32 rows x 4 slices.  Staged rows are padded to 33 floats: the four
+// slices of a row read four different banks, the eight rows of a warp read the same address (broadcast).
+constexpr int AR = 32, ASL = 4, AJ = 64, APAD = 33;
+
+__device__ __forceinline__ void stage_rows(float (*dst)[APAD], const float* __restrict__ src, long long row_stride, int row0, int rows_total) {
+  for (int idx = threadIdx.x; idx < AJ * 32; idx += AR * ASL) {
+    const int r = idx >> 5, c = idx & 31;
+    dst[r][c] = row0 + r < rows_total ? src[(long long)(row0 + r) * row_stride + c] : 0.f;
   }
 }
 
-// pass 2, warp per key row: dk, dv
-__global__ void mha_bwd_kv_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
-                                  const float* __restrict__ dout, const uint8_t* __restrict__ mask, const float* __restrict__ stats,
-                                  float* __restrict__ dk, float* __restrict__ dv, int Sq, int Sk, int heads, long long q_bs,
-                                  int q_rs, long long k_bs, int k_rs, long long v_bs, int v_rs, long long o_bs, int o_rs,
-                                  long long dk_bs, int dk_rs, long long dv_bs, int dv_rs, float drop_p, unsigned long long drop_seed) {
+// pass 1: softmax statistics (m, l), D = dO . O, and dq
+__global__ void __launch_bounds__(AR * ASL)
+mha_bwd_q_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v, const float* __restrict__ o,
+                 const float* __restrict__ dout, const uint8_t* __restrict__ mask, float* __restrict__ dq, float* __restrict__ stats,
+                 int Sq, int Sk, int heads, long long q_bs, int q_rs, long long k_bs, int k_rs, long long v_bs, int v_rs,
+                 long long o_bs, int o_rs, long long dq_bs, int dq_rs, float drop_p, unsigned long long drop_seed) {
+  __shared__ float Ks[AJ][APAD], Vs[AJ][APAD];
+  __shared__ uint8_t Ms[AJ];
   const int b = blockIdx.z, hd = blockIdx.y;
-  const int j = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32, lane = threadIdx.x % 32;
-  if (j >= Sk) return;
+  const int r = threadIdx.x / ASL, t = threadIdx.x % ASL;
+  const int i = blockIdx.x * AR + r;
+  const bool live = i < Sq;
+  const float scale = rsqrtf(32.f);
+  const uint32_t drop_thr = ocv_drop_threshold(drop_p);
+  const float drop_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  const unsigned long long drop_row = (((unsigned long long)b * heads + hd) * Sq + (live ? i : 0)) * Sk;
+  float qi[32], doi[32];
+  float D = 0.f;
+  {
+    const float* qp = q + b * q_bs + (long long)(live ? i : 0) * q_rs + hd * 32;
+    const float* dp = dout + b * o_bs + (long long)(live ? i : 0) * o_rs + hd * 32;
+    const float* op = o + b * o_bs + (long long)(live ? i : 0) * o_rs + hd * 32;
+#pragma unroll
+    for (int c = 0; c < 32; ++c) {
+      qi[c] = qp[c] * scale;
+      doi[c] = dp[c];
+      D = fmaf(doi[c], op[c], D);
+    }
+  }
+  const float* kb = k + b * k_bs + hd * 32;
+  const float* vb = v + b * v_bs + hd * 32;
+  const uint8_t* mb = mask ? mask + (long long)b * Sk : nullptr;
+  float m = -INFINITY, l = 0.f;
+  for (int j0 = 0; j0 < Sk; j0 += AJ) {
+    __syncthreads();
+    stage_rows(Ks, kb, k_rs, j0, Sk);
+    if (threadIdx.x < AJ) Ms[threadIdx.x] = (j0 + threadIdx.x >= Sk) || (mb && mb[j0 + threadIdx.x]);
+    __syncthreads();
+    for (int jj = t; jj < AJ; jj += ASL) {
+      if (Ms[jj]) continue;
+      float s = 0.f;
+#pragma unroll
+      for (int c = 0; c < 32; ++c) s = fmaf(qi[c], Ks[jj][c], s);
+      const float mn = fmaxf(m, s);
+      l = l * __expf(m - mn) + __expf(s - mn);
+      m = mn;
+    }
+  }
+#pragma unroll
+  for (int off = 1; off < ASL; off <<= 1) {  // combine the four slices of a row
+    const float m2 = __shfl_xor_sync(0xffffffffu, m, off), l2 = __shfl_xor_sync(0xffffffffu, l, off);
+    const float mn = fmaxf(m, m2);
+    l = (m > -INFINITY ? l * __expf(m - mn) : 0.f) + (m2 > -INFINITY ? l2 * __expf(m2 - mn) : 0.f);
+    m = mn;
+  }
+  const float inv_l = l > 0.f ? 1.f / l : 0.f;
+  float acc[32];
+#pragma unroll
+  for (int c = 0; c < 32; ++c) acc[c] = 0.f;
+  for (int j0 = 0; j0 < Sk; j0 += AJ) {
+    __syncthreads();
+    stage_rows(Ks, kb, k_rs, j0, Sk);
+    stage_rows(Vs, vb, v_rs, j0, Sk);
+    if (threadIdx.x < AJ) Ms[threadIdx.x] = (j0 + threadIdx.x >= Sk) || (mb && mb[j0 + threadIdx.x]);
+    __syncthreads();
+    for (int jj = t; jj < AJ; jj += ASL) {
+      if (Ms[jj]) continue;
+      float s = 0.f, dP = 0.f;
+#pragma unroll
+      for (int c = 0; c < 32; ++c) {
+        s = fmaf(qi[c], Ks[jj][c], s);
+        dP = fmaf(doi[c], Vs[jj][c], dP);
+      }
+      const float p = __expf(s - m) * inv_l;
+      if (drop_p > 0.f) dP = ocv_drop_keep(drop_seed, drop_row + j0 + jj, drop_thr) ? dP * drop_scale : 0.f;
+      const float wgt = p * (dP - D);
+#pragma unroll
+      for (int c = 0; c < 32; ++c) acc[c] = fmaf(wgt, Ks[jj][c], acc[c]);
+    }
+  }
+#pragma unroll
+  for (int c = 0; c < 32; ++c) {
+    acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 1);
+    acc[c] += __shfl_xor_sync(0xffffffffu, acc[c], 2);
+  }
+  if (live) {
+    float* dst = dq + b * dq_bs + (long long)i * dq_rs + hd * 32;
+#pragma unroll
+    for (int c = 0; c < 32; ++c)
+      if ((c & 3) == t) dst[c] = acc[c] * scale;
+    if (t == 0) {
+      float* st = stats + (((long long)b * heads + hd) * Sq + i) * 3;
+      st[0] = m; st[1] = inv_l; st[2] = D;
+    }
+  }
+}
+
+// pass 2: dk, dv (a thread owns a key row; query rows, dO rows and their statistics are staged)
+__global__ void __launch_bounds__(AR * ASL)
+mha_bwd_kv_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
+                  const float* __restrict__ dout, const uint8_t* __restrict__ mask, const float* __restrict__ stats,
+                  float* __restrict__ dk, float* __restrict__ dv, int Sq, int Sk, int heads, long long q_bs, int q_rs,
+                  long long k_bs, int k_rs, long long v_bs, int v_rs, long long o_bs, int o_rs, long long dk_bs, int dk_rs,
+                  long long dv_bs, int dv_rs, float drop_p, unsigned long long drop_seed) {
+  __shared__ float Qs[AJ][APAD], Ds[AJ][APAD];
+  __shared__ float St[AJ][3];
+  const int b = blockIdx.z, hd = blockIdx.y;
+  const int r = threadIdx.x / ASL, t = threadIdx.x % ASL;
+  const int j = blockIdx.x * AR + r;
+  const bool live = j < Sk && !(mask && mask[(long long)b * Sk + j]);
   const float scale = rsqrtf(32.f);
   const uint32_t drop_thr = ocv_drop_threshold(drop_p);
   const float drop_scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
   const unsigned long long drop_base = ((unsigned long long)b * heads + hd) * Sq;
-  float ak = 0.f, av = 0.f;
-  if (!(mask && mask[(long long)b * Sk + j])) {
-    const float kj = k[b * k_bs + (long long)j * k_rs + hd * 32 + lane];
-    const float vj = v[b * v_bs + (long long)j * v_rs + hd * 32 + lane];
-    const float* qb = q + b * q_bs + hd * 32 + lane;
-    const float* db = dout + b * o_bs + hd * 32 + lane;
-    const float* st = stats + ((long long)b * heads + hd) * Sq * 3;
-    for (int i = 0; i < Sq; ++i) {
-      const float qi = qb[(long long)i * q_rs], doi = db[(long long)i * o_rs];
-      const float s = warp_sum(qi * kj) * scale;
-      const float p = __expf(s - st[3 * i]) / st[3 * i + 1];
-      float dP = warp_sum(doi * vj);
+  float kj[32], vj[32], ak[32], av[32];
+  {
+    const float* kp = k + b * k_bs + (long long)(j < Sk ? j : 0) * k_rs + hd * 32;
+    const float* vp = v + b * v_bs + (long long)(j < Sk ? j : 0) * v_rs + hd * 32;
+#pragma unroll
+    for (int c = 0; c < 32; ++c) {
+      kj[c] = kp[c] * scale;
+      vj[c] = vp[c];
+      ak[c] = 0.f;
+      av[c] = 0.f;
+    }
+  }
+  const float* qb = q + b * q_bs + hd * 32;
+  const float* db = dout + b * o_bs + hd * 32;
+  const float* stb = stats + ((long long)b * heads + hd) * Sq * 3;
+  for (int i0 = 0; i0 < Sq; i0 += AJ) {
+    __syncthreads();
+    stage_rows(Qs, qb, q_rs, i0, Sq);
+    stage_rows(Ds, db, o_rs, i0, Sq);
+    for (int idx = threadIdx.x; idx < AJ * 3; idx += AR * ASL) St[idx / 3][idx % 3] = i0 + idx / 3 < Sq ? stb[(long long)i0 * 3 + idx] : 0.f;
+    __syncthreads();
+    if (!live) continue;
+    const int n = min(AJ, Sq - i0);
+    for (int ii = t; ii < n; ii += ASL) {
+      float s = 0.f, dP = 0.f;
+#pragma unroll
+      for (int c = 0; c < 32; ++c) {
+        s = fmaf(Qs[ii][c], kj[c], s);
+        dP = fmaf(Ds[ii][c], vj[c], dP);
+      }
+      const float p = __expf(s - St[ii][0]) * St[ii][1];
       float pd = p;
       if (drop_p > 0.f) {
-        const float ms = ocv_drop_keep(drop_seed, (drop_base + i) * Sk + j, drop_thr) ? drop_scale : 0.f;
+        const float ms = ocv_drop_keep(drop_seed, (drop_base + i0 + ii) * Sk + j, drop_thr) ? drop_scale : 0.f;
         dP *= ms;
         pd *= ms;
       }
-      av = fmaf(pd, doi, av);
-      ak = fmaf(p * (dP - st[3 * i + 2]), qi, ak);
+      const float wgt = p * (dP - St[ii][2]);
+#pragma unroll
+      for (int c = 0; c < 32; ++c) {
+        av[c] = fmaf(pd, Ds[ii][c], av[c]);
+        ak[c] = fmaf(wgt, Qs[ii][c], ak[c]);
+      }
     }
   }
-  dk[b * dk_bs + (long long)j * dk_rs + hd * 32 + lane] = ak * scale;
-  dv[b * dv_bs + (long long)j * dv_rs + hd * 32 + lane] = av;
+#pragma unroll
+  for (int c = 0; c < 32; ++c) {
+    ak[c] += __shfl_xor_sync(0xffffffffu, ak[c], 1);
+    ak[c] += __shfl_xor_sync(0xffffffffu, ak[c], 2);
+    av[c] += __shfl_xor_sync(0xffffffffu, av[c], 1);
+    av[c] += __shfl_xor_sync(0xffffffffu, av[c], 2);
+  }
+  if (j < Sk) {
+    float* dkp = dk + b * dk_bs + (long long)j * dk_rs + hd * 32;
+    float* dvp = dv + b * dv_bs + (long long)j * dv_rs + hd * 32;
+#pragma unroll
+    for (int c = 0; c < 32; ++c)
+      if ((c & 3) == t) {
+        dkp[c] = ak[c] * scale;
+        dvp[c] = av[c];
+      }
+  }
 }
 
 // ---- head tail backward: depth = sum_k softmax_k(l) c_k -------------------------------------------------------------------
@@ -394,11 +501,11 @@ extern "C" int ocv_mha_core_bwd_dropout_f32(const float* q, const float* k, cons
   OCV_CHECK_SHAPE(d == 32 && B <= 65535 && heads <= 65535);
   if (int s = ocv_require_sm100()) return s;
   float* stats = static_cast<float*>(workspace);
-  mha_bwd_q_kernel<<<dim3(ceil_div(Sq, 8), heads, B), 256, 0, ocv_stream(stream)>>>(
+  mha_bwd_q_kernel<<<dim3(ceil_div(Sq, AR), heads, B), AR * ASL, 0, ocv_stream(stream)>>>(
       q, k, v, out, dout, key_padding_mask, dq, stats, Sq, Sk, heads, q_bstride, q_rstride, k_bstride, k_rstride, v_bstride,
       v_rstride, o_bstride, o_rstride, dq_bstride, dq_rstride, drop_p, drop_seed);
   if (int s = ocv_launch_status()) return s;
-  mha_bwd_kv_kernel<<<dim3(ceil_div(Sk, 8), heads, B), 256, 0, ocv_stream(stream)>>>(
+  mha_bwd_kv_kernel<<<dim3(ceil_div(Sk, AR), heads, B), AR * ASL, 0, ocv_stream(stream)>>>(
       q, k, v, dout, key_padding_mask, stats, dk, dv, Sq, Sk, heads, q_bstride, q_rstride, k_bstride, k_rstride, v_bstride,
       v_rstride, o_bstride, o_rstride, dk_bstride, dk_rstride, dv_bstride, dv_rstride, drop_p, drop_seed);
   return ocv_launch_status();

@@ -51,15 +51,16 @@ tail_logits_kernel(const float* __restrict__ logits, const float* __restrict__ b
   depth[(long long)b * P + px] = a / s;
 }
 
-// dlT[b,k,p] (bf16) = g p (c - depth);   part[b][blk][0][k] = sum over the block's pixels of g p,  part[..][1][k] = of dl
+// dlT[b,k,p] (bf16) = g p (c - depth);   part[b][blk][0][k] = sum over the block's pixels of g p,  part[..][1][k] = of dl.
+// Three passes over the block's [K x 128] logits (max; sum; outputs): the loads of a pass are independent (deep memory-level
+// parallelism), passes 2-3 hit L2 (all resident blocks together hold < 126 MB).  The per-bin pixel sums are warp-reduced by
+// shuffles, kept in registers (lane j owns bins j, j+32, ...), and the four warps are added in fixed order.  K % 32 == 0, K <= 512.
+template <int KK>  // K / 32
 __global__ void __launch_bounds__(TPB)
 tail_logits_bwd_kernel(const float* __restrict__ logits, const float* __restrict__ bias, const float* __restrict__ centres,
-                       const float* __restrict__ gdepth, __nv_bfloat16* __restrict__ dlT, float* __restrict__ part, int K,
-                       long long P) {
-  extern __shared__ float sm[];  // [K] centres, [K] bias, [TPB/32][2][K] per-warp sums
-  float* cs = sm;
-  float* bs = sm + K;
-  float* ws = sm + 2 * K;
+                       const float* __restrict__ gdepth, __nv_bfloat16* __restrict__ dlT, float* __restrict__ part, long long P) {
+  constexpr int K = KK * 32;
+  __shared__ float cs[K], bs[K], acc[2 * K];
   const int b = blockIdx.y, warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   for (int k = threadIdx.x; k < K; k += TPB) {
     cs[k] = centres[(long long)b * K + k];
@@ -69,69 +70,90 @@ tail_logits_bwd_kernel(const float* __restrict__ logits, const float* __restrict
   const long long px = (long long)blockIdx.x * TPB + threadIdx.x;
   const bool live = px < P;
   const float* l = logits + (long long)b * K * P + (live ? px : 0);
-  float m = -INFINITY, s = 0.f, a = 0.f;
-  if (live) {
-#pragma unroll 4
-    for (int k = 0; k < K; ++k) {
-      const float v = l[(long long)k * P] + bs[k];
-      if (v > m) {
-        const float r = __expf(m - v);
-        s *= r;
-        a *= r;
-        m = v;
-      }
-      const float e = __expf(v - m);
-      s += e;
-      a = fmaf(e, cs[k], a);
-    }
-  }
-  const float inv = live ? 1.f / s : 0.f, d = a * inv, gd = live ? gdepth[(long long)b * P + px] : 0.f;
-  __nv_bfloat16* o = dlT + (long long)b * K * P + (live ? px : 0);
-  float* wsum = ws + warp * 2 * K;
+  float m = -INFINITY;
+#pragma unroll 8
+  for (int k = 0; k < K; ++k) m = fmaxf(m, l[(long long)k * P] + bs[k]);
+  float s = 0.f, a = 0.f;
+#pragma unroll 8
   for (int k = 0; k < K; ++k) {
-    float pg = 0.f, dl = 0.f;
-    if (live) {
-      pg = gd * __expf(l[(long long)k * P] + bs[k] - m) * inv;
-      dl = pg * (cs[k] - d);
-      o[(long long)k * P] = __float2bfloat16(dl);
-    }
+    const float e = __expf(l[(long long)k * P] + bs[k] - m);
+    s += e;
+    a = fmaf(e, cs[k], a);
+  }
+  const float inv = 1.f / s, d = a * inv, gd = live ? gdepth[(long long)b * P + px] : 0.f;
+  __nv_bfloat16* o = dlT + (long long)b * K * P + (live ? px : 0);
+  float rpg[KK], rdl[KK];
 #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) {
-      pg += __shfl_xor_sync(0xffffffffu, pg, off);
-      dl += __shfl_xor_sync(0xffffffffu, dl, off);
-    }
-    if (lane == 0) {
-      wsum[k] = pg;
-      wsum[K + k] = dl;
+  for (int kk = 0; kk < KK; ++kk) {
+#pragma unroll 8
+    for (int j = 0; j < 32; ++j) {
+      const int k = kk * 32 + j;
+      float pg = gd * __expf(l[(long long)k * P] + bs[k] - m) * inv;
+      float dl = pg * (cs[k] - d);
+      if (live) o[(long long)k * P] = __float2bfloat16(dl);
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1) {
+        pg += __shfl_xor_sync(0xffffffffu, pg, off);
+        dl += __shfl_xor_sync(0xffffffffu, dl, off);
+      }
+      if (lane == j) {
+        rpg[kk] = pg;
+        rdl[kk] = dl;
+      }
     }
   }
-  __syncthreads();
-  float* dst = part + ((long long)b * gridDim.x + blockIdx.x) * 2 * K;
-  for (int i = threadIdx.x; i < 2 * K; i += TPB) {
-    float t = 0.f;
+  for (int w = 0; w < TPB / 32; ++w) {  // fixed order over the warps
+    if (warp == w) {
 #pragma unroll
-    for (int w = 0; w < TPB / 32; ++w) t += ws[w * 2 * K + i];
-    dst[i] = t;
+      for (int kk = 0; kk < KK; ++kk) {
+        const int k = kk * 32 + lane;
+        acc[k] = (w ? acc[k] : 0.f) + rpg[kk];
+        acc[K + k] = (w ? acc[K + k] : 0.f) + rdl[kk];
+      }
+    }
+    __syncthreads();
+  }
+  float* dst = part + ((long long)b * gridDim.x + blockIdx.x) * 2 * K;
+  for (int i = threadIdx.x; i < 2 * K; i += TPB) dst[i] = acc[i];
+}
+
+// dcentres[b,k] = sum_blk part[b][blk][0][k];  pb[b][k] = sum_blk part[b][blk][1][k].   Block = (32 bins, 8 slices of the block
+// list), slices added in fixed order: deterministic, and parallel enough that the 2 K nblk B floats stream at L2 speed.
+__global__ void __launch_bounds__(256)
+tail_logits_bwd_final_kernel(const float* __restrict__ part, float* __restrict__ dcentres, float* __restrict__ pb, int nblk, int K) {
+  __shared__ float sc[8][32], sd[8][32];
+  const int b = blockIdx.y, k = blockIdx.x * 32 + threadIdx.x, sl = threadIdx.y;
+  float tc = 0.f, td = 0.f;
+  if (k < K) {
+    const float* p = part + (long long)b * nblk * 2 * K + k;
+#pragma unroll 4
+    for (int i = sl; i < nblk; i += 8) {
+      tc += p[(long long)i * 2 * K];
+      td += p[(long long)i * 2 * K + K];
+    }
+  }
+  sc[sl][threadIdx.x] = tc;
+  sd[sl][threadIdx.x] = td;
+  __syncthreads();
+  if (sl == 0 && k < K) {
+    float a = 0.f, c = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      a += sc[i][threadIdx.x];
+      c += sd[i][threadIdx.x];
+    }
+    dcentres[(long long)b * K + k] = a;
+    pb[(long long)b * K + k] = c;
   }
 }
 
-// dcentres[b,k] = sum_blk part[b][blk][0][k];   dbias[k] = beta*dbias[k] + sum_b sum_blk part[b][blk][1][k]   (fixed order)
-__global__ void tail_logits_bwd_final_kernel(const float* __restrict__ part, float* __restrict__ dcentres, float* __restrict__ dbias,
-                                             int B, int nblk, int K, float beta) {
+// dbias[k] = beta*dbias[k] + sum_b pb[b][k]
+__global__ void tail_logits_bwd_bias_kernel(const float* __restrict__ pb, float* __restrict__ dbias, int B, int K, float beta) {
   const int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= K) return;
-  float tb = 0.f;
-  for (int b = 0; b < B; ++b) {
-    float tc = 0.f, td = 0.f;
-    const float* p = part + (long long)b * nblk * 2 * K;
-    for (int i = 0; i < nblk; ++i) {
-      tc += p[(long long)i * 2 * K + k];
-      td += p[(long long)i * 2 * K + K + k];
-    }
-    dcentres[(long long)b * K + k] = tc;
-    tb += td;
-  }
-  if (dbias) dbias[k] = (beta != 0.f ? beta * dbias[k] : 0.f) + tb;
+  float t = 0.f;
+  for (int b = 0; b < B; ++b) t += pb[(long long)b * K + k];
+  dbias[k] = (beta != 0.f ? beta * dbias[k] : 0.f) + t;
 }
 
 // dst[z][c][r] = src[z][r][c]   (bf16; R % 64 == 0, C % 64 == 0; 64 x 64 tiles, 32-bit accesses on both sides)
@@ -184,6 +206,44 @@ im2col3x3_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __rest
   *reinterpret_cast<uint4*>(col + (long long)row * total + g) = *reinterpret_cast<const uint4*>(v);
 }
 
+// Patch unfold for the patch-embedding weight gradient: out[(c*Pp*Pp + py*Pp + px), b*S + sy*gw + sx] = x[b,c,sy*Pp+py,sx*Pp+px]
+// (bf16; the rows are the weight's (c,py,px) order, the columns the token order): dW [E, C Pp Pp] = dtok^T [E, B S] @ out^T is then a
+// K-major GEMM.  One block per (strip group, c, b): `R` patch rows of the plane are staged in shared memory (coalesced reads),
+// then every (py,px) row gets its R*gw consecutive columns from one warp (coalesced writes).
+__global__ void __launch_bounds__(256)
+patch_unfold_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int C, int h, int w, int Pp, int R, long long ld) {
+  extern __shared__ __nv_bfloat16 strip[];  // [R*Pp][w]
+  const int b = blockIdx.z, c = blockIdx.y, sy0 = blockIdx.x * R;
+  const int gh = h / Pp, gw = w / Pp, S = gh * gw;
+  const int rows = min(R, gh - sy0);
+  const float* src = x + (((long long)b * C + c) * h + (long long)sy0 * Pp) * w;
+  const int n = rows * Pp * w;
+  for (int i = threadIdx.x; i < n; i += 256) strip[i] = __float2bfloat16(src[i]);
+  __syncthreads();
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int run = rows * gw;
+  for (int pr = warp; pr < Pp * Pp; pr += 8) {
+    const int py = pr / Pp, px = pr - py * Pp;
+    __nv_bfloat16* dst = out + ((long long)c * Pp * Pp + pr) * ld + (long long)b * S + (long long)sy0 * gw;
+    for (int e = lane; e < run; e += 32) {
+      const int sy = e / gw, sx = e - sy * gw;
+      dst[e] = strip[(sy * Pp + py) * w + sx * Pp + px];
+    }
+  }
+}
+
+// dst[c][r] (bf16, row pitch dst_ld) = src[r][c] (fp32, row pitch src_ld): any R, C (32 x 32 tiles with bounds checks)
+__global__ void transpose_cast_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int R, int C, long long src_ld,
+                                      long long dst_ld) {
+  __shared__ float tile[32][33];
+  const int r0 = blockIdx.y * 32, c0 = blockIdx.x * 32;
+  for (int rr = threadIdx.y; rr < 32; rr += 8)
+    tile[rr][threadIdx.x] = (r0 + rr < R && c0 + threadIdx.x < C) ? src[(long long)(r0 + rr) * src_ld + c0 + threadIdx.x] : 0.f;
+  __syncthreads();
+  for (int cc = threadIdx.y; cc < 32; cc += 8)
+    if (c0 + cc < C && r0 + threadIdx.x < R) dst[(long long)(c0 + cc) * dst_ld + r0 + threadIdx.x] = __float2bfloat16(tile[threadIdx.x][cc]);
+}
+
 }  // namespace
 
 extern "C" int ocv_tail_logits_f32(const float* logits, const float* logit_bias, const float* centres, float* depth, int B, int K,
@@ -198,27 +258,36 @@ extern "C" int ocv_tail_logits_f32(const float* logits, const float* logit_bias,
 
 extern "C" long long ocv_tail_logits_bwd_workspace(int B, int K, long long P) {
   if (B <= 0 || K <= 0 || P <= 0) return 0;
-  return (long long)B * ceil_div<long long>(P, TPB) * 2 * K * (long long)sizeof(float);
+  return ((long long)B * ceil_div<long long>(P, TPB) * 2 * K + (long long)B * K) * (long long)sizeof(float);
 }
 
 extern "C" int ocv_tail_logits_bwd_bf16(const float* logits, const float* logit_bias, const float* centres, const float* grad_depth,
                                         void* dlT_bf16, float* grad_centres, float* grad_bias, float bias_beta, int B, int K,
                                         long long P, void* workspace, void* stream) {
   OCV_CHECK_ARG(logits && centres && grad_depth && dlT_bf16 && grad_centres && workspace && B > 0 && P > 0);
-  OCV_CHECK_SHAPE(K > 0 && K <= 2048 && B <= 65535);
+  OCV_CHECK_SHAPE(K > 0 && K % 32 == 0 && K <= 512 && B <= 65535);
   if (int s = ocv_require_sm100()) return s;
   const int nblk = (int)ceil_div<long long>(P, TPB);
-  const size_t smem = (size_t)(2 * K + (TPB / 32) * 2 * K) * sizeof(float);
-  if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(tail_logits_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return (int)e;
-  }
   float* part = static_cast<float*>(workspace);
-  tail_logits_bwd_kernel<<<dim3(nblk, B), TPB, smem, ocv_stream(stream)>>>(logits, logit_bias, centres, grad_depth,
-                                                                         static_cast<__nv_bfloat16*>(dlT_bf16), part, K, P);
+  __nv_bfloat16* o = static_cast<__nv_bfloat16*>(dlT_bf16);
+  const dim3 grid(nblk, B);
+  cudaStream_t st = ocv_stream(stream);
+  switch (K / 32) {
+    case 2: tail_logits_bwd_kernel<2><<<grid, TPB, 0, st>>>(logits, logit_bias, centres, grad_depth, o, part, P); break;
+    case 4: tail_logits_bwd_kernel<4><<<grid, TPB, 0, st>>>(logits, logit_bias, centres, grad_depth, o, part, P); break;
+    case 8: tail_logits_bwd_kernel<8><<<grid, TPB, 0, st>>>(logits, logit_bias, centres, grad_depth, o, part, P); break;
+    case 16: tail_logits_bwd_kernel<16><<<grid, TPB, 0, st>>>(logits, logit_bias, centres, grad_depth, o, part, P); break;
+    default: return OCV_E_SHAPE;  // n_bins of the reference's params files: 256 (64 / 128 / 512 also built)
+  }
   if (int s = ocv_launch_status()) return s;
-  tail_logits_bwd_final_kernel<<<ceil_div(K, 128), 128, 0, ocv_stream(stream)>>>(part, grad_centres, grad_bias, B, nblk, K, bias_beta);
-  return ocv_launch_status();
+  float* pb = part + (long long)B * nblk * 2 * K;
+  tail_logits_bwd_final_kernel<<<dim3(K / 32, B), dim3(32, 8), 0, st>>>(part, grad_centres, pb, nblk, K);
+  if (int s = ocv_launch_status()) return s;
+  if (grad_bias) {
+    tail_logits_bwd_bias_kernel<<<ceil_div(K, 128), 128, 0, st>>>(pb, grad_bias, B, K, bias_beta);
+    return ocv_launch_status();
+  }
+  return OCV_OK;
 }
 
 extern "C" int ocv_transpose_bf16(const void* src, void* dst, int batch, int R, int C, long long src_bstride, long long src_ld,
@@ -241,5 +310,34 @@ extern "C" int ocv_im2col3x3_bf16(const void* x_planar_bf16, void* col_bf16, int
   const long long groups = (long long)B * h * w / 8;
   im2col3x3_bf16_kernel<<<dim3((unsigned)ceil_div<long long>(groups, 256), C * 9 + 8), 256, 0, ocv_stream(stream)>>>(
       static_cast<const __nv_bfloat16*>(x_planar_bf16), static_cast<__nv_bfloat16*>(col_bf16), B, C, h, w);
+  return ocv_launch_status();
+}
+
+extern "C" int ocv_patch_unfold_bf16(const float* x, void* out_bf16, int B, int C, int h, int w, int P, long long ld, void* stream) {
+  OCV_CHECK_ARG(x && out_bf16 && B > 0 && C > 0 && h > 0 && w > 0 && P > 0);
+  OCV_CHECK_SHAPE(h % P == 0 && w % P == 0 && ld >= (long long)B * (h / P) * (w / P) && B <= 65535 && C <= 65535);
+  if (int s = ocv_require_sm100()) return s;
+  const int gh = h / P;
+  const size_t strip = (size_t)P * w * sizeof(__nv_bfloat16);
+  OCV_CHECK_SHAPE(strip <= 200 * 1024);
+  int R = (int)((96 * 1024) / strip);
+  R = R < 1 ? 1 : (R > gh ? gh : R);
+  const size_t smem = strip * R;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(patch_unfold_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+  }
+  patch_unfold_bf16_kernel<<<dim3(ceil_div(gh, R), C, B), 256, smem, ocv_stream(stream)>>>(x, static_cast<__nv_bfloat16*>(out_bf16), C, h, w,
+                                                                                      P, R, ld);
+  return ocv_launch_status();
+}
+
+extern "C" int ocv_transpose_cast_f32_bf16(const float* src, void* dst_bf16, int R, int C, long long src_ld, long long dst_ld,
+                                           void* stream) {
+  OCV_CHECK_ARG(src && dst_bf16 && R > 0 && C > 0 && src_ld >= C && dst_ld >= R);
+  OCV_CHECK_SHAPE(ceil_div(R, 32) <= 65535);
+  if (int s = ocv_require_sm100()) return s;
+  transpose_cast_kernel<<<dim3(ceil_div(C, 32), ceil_div(R, 32)), dim3(32, 8), 0, ocv_stream(stream)>>>(
+      src, static_cast<__nv_bfloat16*>(dst_bf16), R, C, src_ld, dst_ld);
   return ocv_launch_status();
 }

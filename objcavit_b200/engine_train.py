@@ -278,8 +278,8 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
     if cfg["kind"] == "adabins":
         pre = "adaptive_bins_layer."
         pt = pre + "patch_transformer."
-        tok0 = ops.patch_embed(x, P[pt + "embedding_convPxP.weight"], P[pt + "embedding_convPxP.bias"],
-                               P[pt + "positional_encodings"], patch_size)
+        tok0 = _patch_embed(t, x, P[pt + "embedding_convPxP.weight"], P[pt + "embedding_convPxP.bias"],
+                            P[pt + "positional_encodings"], patch_size)
         tok, t.sv_enc = encoder_fwd(P, pt + "transformer_encoder.", tok0, drop=drop)
     else:
         pre = "objcavit."
@@ -299,8 +299,8 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
         if mutate_inputs:                                                            # F11
             for i in range(B):
                 object_features[i] = obj_tok[batch.offsets_host[i]:batch.offsets_host[i + 1]]
-        tok0 = ops.patch_embed(x, P[pre + "image_embedding_convPxP.weight"], P[pre + "image_embedding_convPxP.bias"], img_pos,
-                               patch_size)
+        tok0 = _patch_embed(t, x, P[pre + "image_embedding_convPxP.weight"], P[pre + "image_embedding_convPxP.bias"],
+                            img_pos.contiguous(), patch_size)
         two = bool(cfg.get("use_2_saca"))
         tok, obj_out, t.sv_saca1 = saca_fwd(P, pre + "saca_1.", tok0, batch, bool(cfg.get("no_obj_sa")), two, drop)
         if two:
@@ -334,14 +334,22 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
 # Gradient precision is bf16 (operands rounded to 8 mantissa bits); the fp32 path stays the parity reference.
 # ----------------------------------------------------------------------------------------------------------------------
 
+def _patch_embed(t, x: torch.Tensor, w: torch.Tensor, bias, pos, patch_size: int) -> torch.Tensor:
+    """Patch-embedding conv + bias + positional rows -> tokens [B,S,E] fp32.  Tensor-core pixel mode: the tcgen05 patch-embed
+    kernel on the NHWC bf16 copy of the features (kept on the tape for the conv3x3 kernel)."""
+    if t.cfg.get("pixel") == "bf16":
+        t.xh = ops.nchw_to_nhwc_bf16(x)
+        return ops.patch_embed_bf16(t.xh, ops.pack_patch_weights_bf16(w), bias, pos, patch_size, want32=True, want16=False)[0]
+    return ops.patch_embed(x, w, bias, pos, patch_size)
+
+
 def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, Q: int) -> torch.Tensor:
     B, C, h, w = x.shape
     Pn, S = h * w, tok.shape[1]
     Wout = P["conv_out.0.weight"].view(-1, Q)
     K = Wout.shape[0]
-    xh = ops.nchw_to_nhwc_bf16(x)
-    t.x3h = ops.conv3x3_nhwc_bf16(xh, ops.pack_conv3x3_bf16(P[pre + "conv3x3.weight"]), P[pre + "conv3x3.bias"])
-    del xh
+    t.x3h = ops.conv3x3_nhwc_bf16(t.xh, ops.pack_conv3x3_bf16(P[pre + "conv3x3.weight"]), P[pre + "conv3x3.bias"])
+    t.xh = None
     Mb = torch.empty(B, K, E, device=x.device, dtype=torch.float32)
     ops.gemm_ex(Wout, tok[:, 1:Q + 1, :], K, E, Q, Q, E, Mb, E, batch=B, stride_a=0, stride_b=S * E, stride_c=K * E)
     t.Mb16 = ops.cast_bf16(Mb)
@@ -473,6 +481,9 @@ def _token_bwd(P: Params, G: Params, t: Tape, dtok: torch.Tensor) -> None:
         mlp_bwd(P, G, pe, (0, 2, 4, 6, 8), t.sv_mlp_obj, d_obj_tok)
     dt2 = dtok0.contiguous().view(B * S, E)
     Pp = 16
-    ops.gemm_ex(dt2, x, E, C * Pp * Pp, B * S, E, 0, G[wkey], C * Pp * Pp, trans_a=True, op_b=2, beta=1.0,
-                split_k=_split(E, C * Pp * Pp, 1, B * S), geom=(C, h, w, Pp))
+    if t.pixel == "bf16":
+        ops.patch_embed_wgrad_bf16(dt2, x, G[wkey], Pp)
+    else:
+        ops.gemm_ex(dt2, x, E, C * Pp * Pp, B * S, E, 0, G[wkey], C * Pp * Pp, trans_a=True, op_b=2, beta=1.0,
+                    split_k=_split(E, C * Pp * Pp, 1, B * S), geom=(C, h, w, Pp))
     ops.reduce_channels(dt2, G[bkey], 1, B * S, E, 1, beta=1.0)

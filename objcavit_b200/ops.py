@@ -42,6 +42,9 @@ timed_events = []
 profile_events = None
 
 
+profile_tag = ""          # optional suffix of the next profiled entries (bench / probes: shapes of the generic GEMM calls)
+
+
 def _call(name: str, *args, launches: int = 1):
     global launch_count
     launch_count += launches
@@ -50,7 +53,7 @@ def _call(name: str, *args, launches: int = 1):
         e0.record()
         _lib.check(getattr(_lib.lib(), name)(*args), name)
         e1.record()
-        profile_events.append((name, e0, e1))
+        profile_events.append((name + profile_tag if profile_tag else name, e0, e1))
         return
     if timed_kernel == name:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -873,7 +876,7 @@ def tail_logits_bwd(logits: torch.Tensor, bias, centres: torch.Tensor, grad_dept
     dcent = torch.empty(B, K, device=logits.device, dtype=torch.float32)
     ws = _workspace(_lib.lib().ocv_tail_logits_bwd_workspace(B, K, Pn), logits.device, "tail_logits_bwd")
     _call("ocv_tail_logits_bwd_bf16", logits.data_ptr(), _ptr(bias), centres.data_ptr(), grad_depth.data_ptr(), dlT.data_ptr(),
-          dcent.data_ptr(), _ptr(grad_bias), float(beta), B, K, Pn, ws.data_ptr(), _stream(), launches=2)
+          dcent.data_ptr(), _ptr(grad_bias), float(beta), B, K, Pn, ws.data_ptr(), _stream(), launches=3)
     return dlT, dcent
 
 
@@ -898,3 +901,20 @@ def im2col3x3_bf16(x_planar: torch.Tensor) -> torch.Tensor:
     col = torch.empty(Cc * 9 + 8, B * h * wd, device=x_planar.device, dtype=torch.bfloat16)
     _call("ocv_im2col3x3_bf16", x_planar.data_ptr(), col.data_ptr(), B, Cc, h, wd, _stream())
     return col
+
+
+def patch_embed_wgrad_bf16(dtok: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, P: int = 16):
+    """dw [E, C, P, P] += dtok [B*S, E]^T @ unfold(x): the patch-embedding weight gradient as ONE tcgen05 GEMM (bf16 operands)."""
+    _chk(dtok, torch.float32, "dtok"); _chk(x, torch.float32, "x"); _chk(dw, torch.float32, "dw")
+    assert dtok.is_contiguous() and x.is_contiguous() and dw.is_contiguous()
+    B, Cc, h, wd = x.shape
+    BS, E = dtok.shape
+    assert BS == B * (h // P) * (wd // P) and dw.numel() == E * Cc * P * P
+    ld = (BS + 7) // 8 * 8
+    alloc = torch.empty if ld == BS else torch.zeros
+    unf = alloc(Cc * P * P, ld, device=x.device, dtype=torch.bfloat16)
+    _call("ocv_patch_unfold_bf16", x.data_ptr(), unf.data_ptr(), B, Cc, h, wd, P, ld, _stream())
+    dT = alloc(E, ld, device=x.device, dtype=torch.bfloat16)
+    _call("ocv_transpose_cast_f32_bf16", dtok.data_ptr(), dT.data_ptr(), BS, E, E, ld, _stream())
+    g = dw.view(E, Cc * P * P)
+    gemm_bf16(dT, unf, residual=g, out=g)

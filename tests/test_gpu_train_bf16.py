@@ -2,7 +2,8 @@
 on tcgen05 with bf16 operands) against the fp32 parity path on the same inputs, plus its HBM-bound helper kernels against torch.
 
 Tolerance: north_star gives 2e-2 relative for the bf16 path; gradients: per parameter max |g - g32| <= 3e-2 * max(|g32|_max,
-1e-2 * largest |g| of the head) (bf16 operands carry 8 mantissa bits; typical measured errors are a few 1e-3).
+1e-2 * largest |g| of the head) (bf16 operands carry 8 mantissa bits; typical measured errors are a few 1e-3), except the
+linear1 parameters of the encoder layers (ReLU gates flip under the bf16 patch embedding): cosine >= 0.98, norm within 10 %.
 """
 import json
 import os
@@ -82,19 +83,45 @@ def test_bf16_pixel_path_training_matches_fp32_path(cuda, name):
     h32, o32, l32 = _run(name, "fp32", cuda)
     h16, o16, l16 = _run(name, "bf16", cuda)
     assert rel_err(o16.depth_pred.detach(), o32.depth_pred.detach()) < 2e-2
-    assert rel_err(o16.bin_edges.detach(), o32.bin_edges.detach()) < 1e-5      # token path is fp32 in both
+    assert rel_err(o16.bin_edges.detach(), o32.bin_edges.detach()) < 2e-2      # fp32 token path fed by the bf16 patch embedding
     assert abs(l16 - l32) < 2e-2 * abs(l32)
     g32 = {k: p.grad for k, p in h32.named_parameters()}
     gmax = max(float(g.abs().max()) for g in g32.values() if g is not None)
-    worst, bad = 0.0, []
+    worst, worst_cos, bad = 0.0, 1.0, []
     for k, p in h16.named_parameters():
         if g32[k] is None:
             assert p.grad is None or float(p.grad.abs().max()) == 0.0, k
             continue
         assert p.grad is not None, k
-        err = float((p.grad - g32[k]).abs().max()) / max(float(g32[k].abs().max()), 1e-2 * gmax)
+        a, r = p.grad.double().flatten(), g32[k].double().flatten()
+        if float(r.abs().max()) == 0.0:                      # e.g. the object encoder of a 1-SACA head
+            assert float(a.abs().max()) == 0.0, k
+            continue
+        if ".linear1." in k:
+            # behind a ReLU gate of the token path: the bf16 patch embedding moves pre-activations by ~4e-3 relative, a few
+            # hundred gates near zero flip, and each flip is a finite jump of the gradient (no smooth bound exists): direction
+            # and size of the gradient are checked instead of the element-wise maximum
+            cos = float((a @ r) / (a.norm() * r.norm()).clamp_min(1e-300))
+            worst_cos = min(worst_cos, cos)
+            if cos < 0.98 or abs(float(a.norm() / r.norm()) - 1.0) > 0.1:
+                bad.append(f"{k}: cosine {cos:.4f}, norm ratio {float(a.norm() / r.norm()):.3f}")
+            continue
+        err = float((a - r).abs().max()) / max(float(r.abs().max()), 1e-2 * gmax)
         worst = max(worst, err)
         if err >= 3e-2:
             bad.append(f"{k}: {err:.2e}")
-    print(f"{name}: bf16 pixel path, worst per-parameter gradient error vs fp32 path {worst:.2e}")
+    print(f"{name}: bf16 pixel path vs fp32 path: worst per-parameter gradient error {worst:.2e}, worst linear1 cosine {worst_cos:.4f}")
     assert not bad, "; ".join(bad)
+
+
+def test_patch_embed_wgrad_bf16(cuda):
+    torch.manual_seed(2)
+    B, C, h, w, P, E = 2, 8, 48, 80, 16, 128                      # B*S = 30: not a multiple of 8 -> padded pitch
+    x = torch.randn(B, C, h, w, device=cuda)
+    S = (h // P) * (w // P)
+    dtok = torch.randn(B * S, E, device=cuda)
+    dw = torch.ones(E, C, P, P, device=cuda)
+    ops.patch_embed_wgrad_bf16(dtok, x, dw, P)
+    patches = torch.nn.functional.unfold(x, P, stride=P)           # [B, C*P*P, S]
+    ref = torch.einsum("bse,bks->ek", dtok.view(B, S, E), patches).view(E, C, P, P) + 1.0
+    assert rel_err(dw, ref) < 1e-2
