@@ -56,42 +56,54 @@ sgemm_ex_kernel(const float* __restrict__ A, const float* __restrict__ Bm, float
   const int ldo = to_partials ? N : ldc;
   const int ty = tid / 16, tx = tid % 16;
   float acc[4][4] = {};
-  for (int k0 = k_begin; k0 < k_end; k0 += BK) {
+  // Register double buffering: the global loads of tile t+1 are issued before the FMAs of tile t, so a CTA that is alone on
+  // its SM (token-sized problems: fewer tiles than SMs) still overlaps memory latency with compute.
+  const int r4 = tid / 4, k4 = (tid % 4) * 4;     // "k fastest" operand: (row, 4 consecutive k)
+  const int k16 = tid / 16, c16 = (tid % 16) * 4;  // "row fastest" operand: (k, 4 consecutive rows)
+  float ra[4], rb[4];
+  auto fetch = [&](int k0) {
     if (TA == 0) {  // A[m][k], k contiguous
-      const int r = tid / 4, kk = (tid % 4) * 4;
-      const int m = m0 + r;
+      const int m = m0 + r4;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const int k = k0 + kk + j;
-        As[kk + j][r] = (m < M && k < k_end) ? A[(long long)m * lda + k] : 0.f;
+        const int k = k0 + k4 + j;
+        ra[j] = (m < M && k < k_end) ? A[(long long)m * lda + k] : 0.f;
       }
     } else {  // A^T: element (m, k) at A[k*lda + m], m contiguous
-      const int kk = tid / 16, mm = (tid % 16) * 4;
-      const int k = k0 + kk;
+      const int k = k0 + k16;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const int m = m0 + mm + j;
-        As[kk][mm + j] = (m < M && k < k_end) ? A[(long long)k * lda + m] : 0.f;
+        const int m = m0 + c16 + j;
+        ra[j] = (m < M && k < k_end) ? A[(long long)k * lda + m] : 0.f;
       }
     }
     if (BMODE == B_T || BMODE == B_IM2COL) {  // k (pixel) fastest
-      const int r = tid / 4, kk = (tid % 4) * 4;
-      const int n = n0 + r;
+      const int n = n0 + r4;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const int k = k0 + kk + j;
-        Bs[kk + j][r] = (n < N && k < k_end) ? load_b(BMODE, Bm, k, n, ldb, g) : 0.f;
+        const int k = k0 + k4 + j;
+        rb[j] = (n < N && k < k_end) ? load_b(BMODE, Bm, k, n, ldb, g) : 0.f;
       }
     } else {  // n fastest
-      const int kk = tid / 16, nn = (tid % 16) * 4;
-      const int k = k0 + kk;
+      const int k = k0 + k16;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const int n = n0 + nn + j;
-        Bs[kk][nn + j] = (n < N && k < k_end) ? load_b(BMODE, Bm, k, n, ldb, g) : 0.f;
+        const int n = n0 + c16 + j;
+        rb[j] = (n < N && k < k_end) ? load_b(BMODE, Bm, k, n, ldb, g) : 0.f;
       }
     }
+  };
+  fetch(k_begin);
+  for (int k0 = k_begin; k0 < k_end; k0 += BK) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (TA == 0) As[k4 + j][r4] = ra[j];
+      else As[k16][c16 + j] = ra[j];
+      if (BMODE == B_T || BMODE == B_IM2COL) Bs[k4 + j][r4] = rb[j];
+      else Bs[k16][c16 + j] = rb[j];
+    }
     __syncthreads();
+    if (k0 + BK < k_end) fetch(k0 + BK);
 #pragma unroll
     for (int k = 0; k < BK; ++k) {
       const float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);

@@ -45,35 +45,44 @@ sgemm_kernel(const float* __restrict__ A, const float* __restrict__ Bm, const fl
   }
   const int ty = tid / 16, tx = tid % 16;
   float acc[4][4] = {};
-  for (int k0 = k_begin; k0 < k_end; k0 += BK) {
-    // A tile: 64 rows x 16 k, thread -> (row = tid/4, k = (tid%4)*4 .. +3)
-    {
-      const int r = tid / 4, kk = (tid % 4) * 4;
-      const int m = m0 + r;
+  // Register double buffering: the global loads of tile t+1 are issued before the FMAs of tile t (token-sized problems have
+  // fewer tiles than SMs, so no other CTA hides the latency).
+  const int r4 = tid / 4, k4 = (tid % 4) * 4;      // (row, 4 consecutive k) of a K-contiguous operand
+  const int k16 = tid / 16, c16 = (tid % 16) * 4;  // (k, 4 consecutive n) of Bm [K,N]
+  float ra[4], rb[4];
+  auto fetch = [&](int k0) {
+    const int m = m0 + r4;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int k = k0 + kk + j;
-        As[kk + j][r] = (m < M && k < k_end) ? load_a<A_MODE>(A, m, k, lda, g) : 0.f;
-      }
+    for (int j = 0; j < 4; ++j) {
+      const int k = k0 + k4 + j;
+      ra[j] = (m < M && k < k_end) ? load_a<A_MODE>(A, m, k, lda, g) : 0.f;
     }
     if (TRANSB) {  // Bm [N,K]
-      const int r = tid / 4, kk = (tid % 4) * 4;
-      const int n = n0 + r;
+      const int n = n0 + r4;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const int k = k0 + kk + j;
-        Bs[kk + j][r] = (n < N && k < k_end) ? Bm[(long long)n * ldb + k] : 0.f;
+        const int k = k0 + k4 + j;
+        rb[j] = (n < N && k < k_end) ? Bm[(long long)n * ldb + k] : 0.f;
       }
     } else {  // Bm [K,N]
-      const int kk = tid / 16, nn = (tid % 16) * 4;
-      const int k = k0 + kk;
+      const int k = k0 + k16;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const int n = n0 + nn + j;
-        Bs[kk][nn + j] = (n < N && k < k_end) ? Bm[(long long)k * ldb + n] : 0.f;
+        const int n = n0 + c16 + j;
+        rb[j] = (n < N && k < k_end) ? Bm[(long long)k * ldb + n] : 0.f;
       }
     }
+  };
+  fetch(k_begin);
+  for (int k0 = k_begin; k0 < k_end; k0 += BK) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      As[k4 + j][r4] = ra[j];
+      if (TRANSB) Bs[k4 + j][r4] = rb[j];
+      else Bs[k16][c16 + j] = rb[j];
+    }
     __syncthreads();
+    if (k0 + BK < k_end) fetch(k0 + BK);
 #pragma unroll
     for (int k = 0; k < BK; ++k) {
       const float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);

@@ -641,6 +641,12 @@ def gemm_ex(a: torch.Tensor, b: torch.Tensor, M: int, N: int, K: int, lda: int, 
     return out
 
 
+def _auto_split(M: int, N: int, K: int) -> int:
+    """split-K factor of a token-sized SIMT GEMM: enough 64x64 tiles x splits to cover the 148 SMs, at least 64 of K per split."""
+    tiles = ((M + 63) // 64) * ((N + 63) // 64)
+    return max(1, min((192 + tiles - 1) // tiles, K // 64, 64))
+
+
 def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, out=None, beta: float = 0.0) -> torch.Tensor:
     """dx [M,K] = beta*dx + dy [M,N] @ w [N,K]  (``out``: a 2-D view with unit inner stride, e.g. one token row per image)."""
     M, N, ldy = _row_major_2d(dy, "dy")
@@ -651,7 +657,7 @@ def linear_dgrad(dy: torch.Tensor, w: torch.Tensor, out=None, beta: float = 0.0)
         beta = 0.0
     M2, K2, ldo = _row_major_2d(out, "out")
     assert (M2, K2) == (M, K)
-    return gemm_ex(dy, w, M, K, N, ldy, ldw, out, ldo, beta=beta)
+    return gemm_ex(dy, w, M, K, N, ldy, ldw, out, ldo, beta=beta, split_k=_auto_split(M, K, N))
 
 
 def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, db=None, beta: float = 1.0):
@@ -659,8 +665,7 @@ def linear_wgrad(dy: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, db=None, b
     M, N, ldy = _row_major_2d(dy, "dy")
     M2, K, ldx = _row_major_2d(x, "x")
     assert M == M2 and dw.is_contiguous() and dw.numel() == N * K
-    split = max(1, min(64, M // 256))
-    gemm_ex(dy, x, N, K, M, ldy, ldx, dw, K, trans_a=True, beta=beta, split_k=split)
+    gemm_ex(dy, x, N, K, M, ldy, ldx, dw, K, trans_a=True, beta=beta, split_k=_auto_split(N, K, M))
     if db is not None:
         assert ldy == N, "bias gradient needs a dense dy"
         reduce_channels(dy, db, 1, M, N, 1, beta)
