@@ -218,7 +218,7 @@ def run_train(a):
         dist.init_process_group("nccl", device_id=dev)
     B = a.batch if a.batch != 16 else 8
     W_, K = max(a.warmup, 3), a.steps
-    tprec = a.precision or "fp32"     # "bf16": pixel path of the step on tcgen05 (bf16 operands); token path fp32 either way
+    tprec = a.precision or "bf16"     # "bf16" (default): pixel path of the step on tcgen05; "fp32": the all-SIMT parity path
     head = build_head(builtin_args(CFG_NAME), precision=tprec).to(dev).train()
     head.load_state_dict(load_weights(CFG_NAME), strict=True)
     trainer = HeadTrainer(head, lr=0.000357, weight_decay=0.1, clip_grad_norm=0.1,
@@ -234,14 +234,21 @@ def run_train(a):
     def step():
         return trainer.step(x_dev, list(objs_dev), boxes_dev, gt_dev, mask_dev)
 
+    # end to end: every step's inputs come from pinned host memory and every step's loss goes back to the host; the copy of
+    # step i+1 runs on the prefetcher's stream while step i computes, the loss is read one step late (objcavit_b200/prefetch.py)
+    from objcavit_b200.prefetch import DevicePrefetcher, LaggedScalars
+
+    def host_batches():
+        while True:
+            yield (host["x"], host["objs"], host["boxes"], host["gt"], host["mask"])
+
+    feed = DevicePrefetcher(host_batches(), dev)
+    losses = LaggedScalars(2, lag=1)
+
     def e2e_step():
-        x = host["x"].to(dev, non_blocking=True)
-        g = host["gt"].to(dev, non_blocking=True)
-        m = host["mask"].to(dev, non_blocking=True)
-        ob = [o.to(dev, non_blocking=True) for o in host["objs"]]
-        bx = [b.to(dev, non_blocking=True) for b in host["boxes"]]
-        l1, l2 = trainer.step(x, ob, bx, g, m)
-        return trainer.loss_value(l1, l2)            # D2H read of the step's result (the loss)
+        x, ob, bx, g, m = next(feed)
+        l1, l2 = trainer.step(x, list(ob), list(bx), g, m)
+        return losses.push(l1, l2)                    # D2H of this step's loss; returns the previous step's values
 
     def barrier():
         if dist is not None:
