@@ -257,7 +257,7 @@ int ocv_reduce_channels_f32(const float* x, float* out, int groups, int outer, i
 /* dx = dy * act'(.) from the activation OUTPUT (ReLU / LeakyReLU 0.01 keep the sign) */
 int ocv_act_bwd_f32(const float* dy, const float* out, float* dx, long long n, int act, void* stream);
 /* LayerNorm backward: z = pre-norm input [rows,E]; dz [rows,E]; dgamma/dbeta [E] (optional pair, beta-accumulated);
- * workspace rows*2 floats. */
+ * workspace rows*2 + 32*E floats (row statistics + fixed-order partials of the parameter sums). */
 int ocv_layernorm_bwd_f32(const float* dy, const float* z, const float* gamma, float* dz, float* dgamma, float* dbeta, int rows,
                           int E, float beta, void* workspace, void* stream);
 /* Backward of ocv_mha_core_f32 (same view conventions; `out` = its forward result): dq, dk, dv.  workspace B*heads*Sq*3 floats. */

@@ -121,14 +121,17 @@ __global__ void layernorm_bwd_rows_kernel(const float* __restrict__ dy, const fl
   }
 }
 
-// dgamma[e] = beta*dgamma[e] + sum_rows dy * xhat,  dbeta[e] likewise;  block = 32 channels x 8 row lanes
+// dgamma[e] = beta*dgamma[e] + sum_rows dy * xhat,  dbeta[e] likewise.  Two fixed-order stages: LNG row groups x (32 channels x
+// 8 row lanes) blocks write partials, a second kernel adds the LNG partials (4 blocks alone needed 50 us for 1768 rows).
+constexpr int LNG = 16;
 __global__ void layernorm_bwd_params_kernel(const float* __restrict__ dy, const float* __restrict__ z, const float* __restrict__ stats,
-                                            float* __restrict__ dgamma, float* __restrict__ dbeta, int rows, int E, float beta) {
+                                            float* __restrict__ part /* [LNG][2][E] */, int rows, int E) {
   __shared__ float sg[8][33], sb[8][33];
   const int e = blockIdx.x * 32 + threadIdx.x, ry = threadIdx.y;
+  const int per = (rows + LNG - 1) / LNG, r0 = blockIdx.y * per, r1 = min(rows, r0 + per);
   float ag = 0.f, ab = 0.f;
   if (e < E)
-    for (int r = ry; r < rows; r += 8) {
+    for (int r = r0 + ry; r < r1; r += 8) {
       const float d = dy[(long long)r * E + e];
       ag += d * (z[(long long)r * E + e] - stats[2 * r]) * stats[2 * r + 1];
       ab += d;
@@ -142,9 +145,23 @@ __global__ void layernorm_bwd_params_kernel(const float* __restrict__ dy, const 
       tg += sg[i][threadIdx.x];
       tb += sb[i][threadIdx.x];
     }
-    dgamma[e] = beta != 0.f ? beta * dgamma[e] + tg : tg;
-    dbeta[e] = beta != 0.f ? beta * dbeta[e] + tb : tb;
+    part[((long long)blockIdx.y * 2) * E + e] = tg;
+    part[((long long)blockIdx.y * 2 + 1) * E + e] = tb;
   }
+}
+
+__global__ void layernorm_bwd_params_final_kernel(const float* __restrict__ part, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                  int E, float beta) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= E) return;
+  float tg = 0.f, tb = 0.f;
+#pragma unroll
+  for (int i = 0; i < LNG; ++i) {
+    tg += part[((long long)i * 2) * E + e];
+    tb += part[((long long)i * 2 + 1) * E + e];
+  }
+  dgamma[e] = beta != 0.f ? beta * dgamma[e] + tg : tg;
+  dbeta[e] = beta != 0.f ? beta * dbeta[e] + tb : tb;
 }
 
 // ---- attention core backward (head dim 32) ------------------------------------------------------------------------------
@@ -463,7 +480,7 @@ extern "C" int ocv_act_bwd_f32(const float* dy, const float* out, float* dx, lon
 }
 
 extern "C" int ocv_layernorm_bwd_f32(const float* dy, const float* z, const float* gamma, float* dz, float* dgamma, float* dbeta,
-                                     int rows, int E, float beta, void* workspace /* rows*2 floats */, void* stream) {
+                                     int rows, int E, float beta, void* workspace /* rows*2 + 32*E floats */, void* stream) {
   OCV_CHECK_ARG(dy && z && gamma && dz && workspace && rows > 0);
   OCV_CHECK_SHAPE(E > 0 && E % 32 == 0 && E <= 512);
   OCV_CHECK_ARG((dgamma == nullptr) == (dbeta == nullptr));
@@ -472,7 +489,10 @@ extern "C" int ocv_layernorm_bwd_f32(const float* dy, const float* z, const floa
   layernorm_bwd_rows_kernel<<<ceil_div(rows, 8), 256, 0, ocv_stream(stream)>>>(dy, z, gamma, dz, stats, rows, E);
   if (int s = ocv_launch_status()) return s;
   if (dgamma) {
-    layernorm_bwd_params_kernel<<<ceil_div(E, 32), dim3(32, 8), 0, ocv_stream(stream)>>>(dy, z, stats, dgamma, dbeta, rows, E, beta);
+    float* part = stats + 2 * (long long)rows;
+    layernorm_bwd_params_kernel<<<dim3(ceil_div(E, 32), LNG), dim3(32, 8), 0, ocv_stream(stream)>>>(dy, z, stats, part, rows, E);
+    if (int s = ocv_launch_status()) return s;
+    layernorm_bwd_params_final_kernel<<<ceil_div(E, 128), 128, 0, ocv_stream(stream)>>>(part, dgamma, dbeta, E, beta);
     return ocv_launch_status();
   }
   return OCV_OK;

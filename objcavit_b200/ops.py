@@ -692,9 +692,9 @@ def layernorm_bwd(dy: torch.Tensor, z: torch.Tensor, gamma: torch.Tensor, dgamma
     E = z.shape[-1]
     rows = z.numel() // E
     dz = torch.empty_like(z)
-    ws = _workspace(rows * 8, z.device, "ln_bwd")
+    ws = _workspace(rows * 8 + 32 * E * 4, z.device, "ln_bwd")
     _call("ocv_layernorm_bwd_f32", dy.data_ptr(), z.data_ptr(), gamma.data_ptr(), dz.data_ptr(), _ptr(dgamma), _ptr(dbeta), rows, E,
-          float(beta), ws.data_ptr(), _stream(), launches=2)
+          float(beta), ws.data_ptr(), _stream(), launches=3 if dgamma is not None else 1)
     return dz
 
 
