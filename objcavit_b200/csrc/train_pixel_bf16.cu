@@ -19,6 +19,36 @@ namespace {
 
 constexpr int TPB = 128;   // pixels per block (thread = pixel)
 
+// Online softmax statistics of one pixel's K logits (stride P apart): m = max, s = sum exp(l - m), a = sum exp(l - m) c.
+// Four independent chains (k mod 4) keep four loads and four exp's in flight; merged in fixed order.  K % 4 == 0.
+__device__ __forceinline__ void softmax_stats(const float* __restrict__ l, long long P, const float* __restrict__ bs,
+                                              const float* __restrict__ cs, int K, float& m, float& s, float& a) {
+  float mm[4], ss[4], aa[4];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) { mm[c] = -INFINITY; ss[c] = 0.f; aa[c] = 0.f; }
+#pragma unroll 2
+  for (int k = 0; k < K; k += 4) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const float v = l[(long long)(k + c) * P] + bs[k + c];
+      const float mn = fmaxf(mm[c], v);
+      const float r = __expf(mm[c] - mn), e = __expf(v - mn);
+      ss[c] = fmaf(ss[c], r, e);
+      aa[c] = fmaf(aa[c], r, e * cs[k + c]);
+      mm[c] = mn;
+    }
+  }
+  m = fmaxf(fmaxf(mm[0], mm[1]), fmaxf(mm[2], mm[3]));
+  s = 0.f;
+  a = 0.f;
+#pragma unroll
+  for (int c = 0; c < 4; ++c) {
+    const float r = __expf(mm[c] - m);
+    s = fmaf(ss[c], r, s);
+    a = fmaf(aa[c], r, a);
+  }
+}
+
 // depth[b,p] = sum_k softmax_k(l[b,k,p] + bias[k]) c[b,k]  — one pass, online softmax
 __global__ void __launch_bounds__(TPB)
 tail_logits_kernel(const float* __restrict__ logits, const float* __restrict__ bias, const float* __restrict__ centres,
@@ -34,26 +64,14 @@ tail_logits_kernel(const float* __restrict__ logits, const float* __restrict__ b
   const long long px = (long long)blockIdx.x * TPB + threadIdx.x;
   if (px >= P) return;
   const float* l = logits + (long long)b * K * P + px;
-  float m = -INFINITY, s = 0.f, a = 0.f;
-#pragma unroll 4
-  for (int k = 0; k < K; ++k) {
-    const float v = l[(long long)k * P] + bs[k];
-    if (v > m) {
-      const float r = __expf(m - v);
-      s *= r;
-      a *= r;
-      m = v;
-    }
-    const float e = __expf(v - m);
-    s += e;
-    a = fmaf(e, cs[k], a);
-  }
+  float m, s, a;
+  softmax_stats(l, P, bs, cs, K, m, s, a);
   depth[(long long)b * P + px] = a / s;
 }
 
 // dlT[b,k,p] (bf16) = g p (c - depth);   part[b][blk][0][k] = sum over the block's pixels of g p,  part[..][1][k] = of dl.
-// Three passes over the block's [K x 128] logits (max; sum; outputs): the loads of a pass are independent (deep memory-level
-// parallelism), passes 2-3 hit L2 (all resident blocks together hold < 126 MB).  The per-bin pixel sums are warp-reduced by
+// Two passes over the block's [K x 128] logits (online-softmax statistics on four independent chains; outputs): the loads of a
+// pass are independent (deep memory-level parallelism).  The per-bin pixel sums are warp-reduced by
 // shuffles, kept in registers (lane j owns bins j, j+32, ...), and the four warps are added in fixed order.  K % 32 == 0, K <= 512.
 template <int KK>  // K / 32
 __global__ void __launch_bounds__(TPB)
@@ -70,16 +88,8 @@ tail_logits_bwd_kernel(const float* __restrict__ logits, const float* __restrict
   const long long px = (long long)blockIdx.x * TPB + threadIdx.x;
   const bool live = px < P;
   const float* l = logits + (long long)b * K * P + (live ? px : 0);
-  float m = -INFINITY;
-#pragma unroll 8
-  for (int k = 0; k < K; ++k) m = fmaxf(m, l[(long long)k * P] + bs[k]);
-  float s = 0.f, a = 0.f;
-#pragma unroll 8
-  for (int k = 0; k < K; ++k) {
-    const float e = __expf(l[(long long)k * P] + bs[k] - m);
-    s += e;
-    a = fmaf(e, cs[k], a);
-  }
+  float m, s, a;
+  softmax_stats(l, P, bs, cs, K, m, s, a);
   const float inv = 1.f / s, d = a * inv, gd = live ? gdepth[(long long)b * P + px] : 0.f;
   __nv_bfloat16* o = dlT + (long long)b * K * P + (live ? px : 0);
   float rpg[KK], rdl[KK];
@@ -179,8 +189,8 @@ transpose_bf16_kernel(const uint32_t* __restrict__ src, uint32_t* __restrict__ d
 
 // col[row, b*P + p], row = c*9 + ky*3 + kx < C*9: x[b,c,y+ky-1,x+kx-1] (0 outside);  row C*9: 1;  rows above: 0.   8 pixels per thread.
 __global__ void __launch_bounds__(256)
-im2col3x3_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, int B, int C, int h, int w) {
-  const int row = blockIdx.y;
+im2col3x3_bf16_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, int B, int C, int h, int w, int row0) {
+  const int row = row0 + blockIdx.y;
   const long long P = (long long)h * w, total = P * B;
   const long long g = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8;
   if (g >= total) return;
@@ -244,12 +254,45 @@ __global__ void transpose_cast_kernel(const float* __restrict__ src, __nv_bfloat
     if (c0 + cc < C && r0 + threadIdx.x < R) dst[(long long)(c0 + cc) * dst_ld + r0 + threadIdx.x] = __float2bfloat16(tile[threadIdx.x][cc]);
 }
 
+// Vector path of the same (w % 8 == 0): a thread takes 8 consecutive pixels of one (c, ky) and writes the three kx rows from ONE
+// aligned 16-byte load of the source row plus its two neighbours (3 loads and 3 stores instead of 24 + 3).
+__global__ void __launch_bounds__(256)
+im2col3x3_vec_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ col, int B, int C, int h, int w) {
+  const int c = blockIdx.y / 3, ky = blockIdx.y - c * 3;
+  const long long P = (long long)h * w, total = P * B;
+  const long long g = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (g >= total) return;
+  const int b = (int)(g / P);
+  const long long p = g - (long long)b * P;
+  const int y = (int)(p / w), xx = (int)(p - (long long)y * w), sy = y + ky - 1;
+  __align__(16) unsigned short v[10];  // source pixels xx-1 .. xx+8 of row sy (zeros outside)
+#pragma unroll
+  for (int i = 0; i < 10; ++i) v[i] = 0;
+  if (sy >= 0 && sy < h) {
+    const unsigned short* src = reinterpret_cast<const unsigned short*>(x) + ((long long)b * C + c) * P + (long long)sy * w + xx;
+    const uint4 mid = *reinterpret_cast<const uint4*>(src);
+    const unsigned short* mv = reinterpret_cast<const unsigned short*>(&mid);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) v[1 + i] = mv[i];
+    if (xx > 0) v[0] = src[-1];
+    if (xx + 8 < w) v[9] = src[8];
+  }
+  unsigned short* dst = reinterpret_cast<unsigned short*>(col) + ((long long)(c * 9 + ky * 3)) * total + g;
+#pragma unroll
+  for (int kx = 0; kx < 3; ++kx) {
+    __align__(16) unsigned short o[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i] = v[i + kx];
+    *reinterpret_cast<uint4*>(dst + (long long)kx * total) = *reinterpret_cast<const uint4*>(o);
+  }
+}
+
 }  // namespace
 
 extern "C" int ocv_tail_logits_f32(const float* logits, const float* logit_bias, const float* centres, float* depth, int B, int K,
                                    long long P, void* stream) {
   OCV_CHECK_ARG(logits && centres && depth && B > 0 && P > 0);
-  OCV_CHECK_SHAPE(K > 0 && K <= 4096 && B <= 65535);
+  OCV_CHECK_SHAPE(K > 0 && K % 4 == 0 && K <= 4096 && B <= 65535);
   if (int s = ocv_require_sm100()) return s;
   tail_logits_kernel<<<dim3((unsigned)ceil_div<long long>(P, TPB), B), TPB, 2 * K * sizeof(float), ocv_stream(stream)>>>(
       logits, logit_bias, centres, depth, K, P);
@@ -308,8 +351,16 @@ extern "C" int ocv_im2col3x3_bf16(const void* x_planar_bf16, void* col_bf16, int
   OCV_CHECK_ALIGN((reinterpret_cast<uintptr_t>(col_bf16) & 15) == 0);
   if (int s = ocv_require_sm100()) return s;
   const long long groups = (long long)B * h * w / 8;
-  im2col3x3_bf16_kernel<<<dim3((unsigned)ceil_div<long long>(groups, 256), C * 9 + 8), 256, 0, ocv_stream(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x_planar_bf16), static_cast<__nv_bfloat16*>(col_bf16), B, C, h, w);
+  const unsigned gx = (unsigned)ceil_div<long long>(groups, 256);
+  const __nv_bfloat16* xs = static_cast<const __nv_bfloat16*>(x_planar_bf16);
+  __nv_bfloat16* cd = static_cast<__nv_bfloat16*>(col_bf16);
+  if (w % 8 == 0 && (reinterpret_cast<uintptr_t>(x_planar_bf16) & 15) == 0) {
+    im2col3x3_vec_kernel<<<dim3(gx, C * 3), 256, 0, ocv_stream(stream)>>>(xs, cd, B, C, h, w);
+    if (int s = ocv_launch_status()) return s;
+    im2col3x3_bf16_kernel<<<dim3(gx, 8), 256, 0, ocv_stream(stream)>>>(xs, cd, B, C, h, w, C * 9);   // ones row + zero rows
+  } else {
+    im2col3x3_bf16_kernel<<<dim3(gx, C * 9 + 8), 256, 0, ocv_stream(stream)>>>(xs, cd, B, C, h, w, 0);
+  }
   return ocv_launch_status();
 }
 
