@@ -248,6 +248,10 @@ int ocv_pixel_fused_bf16_argmax(const void* X, const void* W3p, const void* Mb, 
  *            (conv3x3 weight gradient);  gather_geom_host = {C, h, w, P} for opB >= 2.
  *   split_k > 1 / reduce_batch / beta != 0 go through `workspace` (ocv_gemm_f32_ex_workspace bytes), added in a fixed order.
  * replaces: the autograd of nn.Linear / nn.Conv2d / torch.matmul on the path. */
+/* nn.Linear forward C[M,N] = A[M,K] @ W[N,K]^T + bias with split-K (fixed-order reduction): for long-K / few-tile problems
+ * (linear2 of nn.TransformerEncoderLayer in the training forward).  workspace: split_k * M * N floats. */
+int ocv_linear_splitk_f32(const float* A, const float* W, const float* bias, float* C, int M, int N, int K, int lda, int ldb,
+                          int ldc, int split_k, void* workspace, void* stream);
 long long ocv_gemm_f32_ex_workspace(int M, int N, int batch, int split_k);
 int ocv_gemm_f32_ex(int transA, int opB, const float* A, const float* Bm, float* C, int M, int N, int K, int lda, int ldb, int ldc,
                     float beta, int batch, long long strideA, long long strideB, long long strideC, int reduce_batch, int split_k,

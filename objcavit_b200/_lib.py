@@ -54,6 +54,7 @@ PROTOTYPES = {
     "ocv_pixel_fused_bf16": (i32, [p, p, p, p, p, p, i32, i32, i32, i32, p]),
     "ocv_conv3x3_nhwc_bf16": (i32, [p, p, p, p, i32, i32, i32, i32, p]),
     "ocv_pixel_fused_bf16_argmax": (i32, [p, p, p, p, p, p, p, i32, i32, i32, p]),
+    "ocv_linear_splitk_f32": (i32, [p, p, p, p, i32, i32, i32, i32, i32, i32, i32, p, p]),
     "ocv_gemm_f32_ex_workspace": (i64, [i32, i32, i32, i32]),
     "ocv_gemm_f32_ex": (i32, [i32, i32, p, p, p, i32, i32, i32, i32, i32, i32, f32, i32, i64, i64, i64, i32, i32, p, p, p]),
     "ocv_reduce_channels_f32": (i32, [p, p, i32, i32, i32, i64, f32, p]),

@@ -143,6 +143,18 @@ __global__ void gemm_ex_reduce_kernel(const float* __restrict__ part, float* __r
   *c = beta != 0.f ? beta * (*c) + v : v;
 }
 
+// C[m][n] = sum_z part[z][m][n] + bias[n]   (fixed order)
+__global__ void linear_splitk_reduce_kernel(const float* __restrict__ part, const float* __restrict__ bias, float* __restrict__ C,
+                                            int M, int N, int ldc, int splits) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long mn = (long long)M * N;
+  if (i >= mn) return;
+  const int m = (int)(i / N), n = (int)(i - (long long)m * N);
+  float v = bias ? bias[n] : 0.f;
+  for (int z = 0; z < splits; ++z) v += part[(long long)z * mn + i];
+  C[(long long)m * ldc + n] = v;
+}
+
 template <int TA>
 int launch_ex(int opB, dim3 grid, void* stream, const float* A, const float* Bm, float* C, int M, int N, int K, int lda, int ldb,
               int ldc, long long sA, long long sB, long long sC, int splits, int kps, int to_part, Gather g) {
@@ -196,5 +208,24 @@ extern "C" int ocv_gemm_f32_ex(int transA, int opB, const float* A, const float*
   const long long n = (long long)M * N * groups;
   gemm_ex_reduce_kernel<<<(unsigned)ceil_div<long long>(n, 256), 256, 0, ocv_stream(stream)>>>(
       static_cast<const float*>(workspace), C, M, N, ldc, strideC, groups, per_group, beta);
+  return ocv_launch_status();
+}
+
+// nn.Linear forward for problems with a long K and few output tiles (linear2 of the encoder layers: K = 1024, N = 128):
+// split-K partials + fixed-order reduction with the bias, so that 8-56 tiles become 100+ CTAs.  workspace: split_k*M*N floats.
+extern "C" int ocv_linear_splitk_f32(const float* A, const float* W, const float* bias, float* C, int M, int N, int K, int lda,
+                                     int ldb, int ldc, int split_k, void* workspace, void* stream) {
+  OCV_CHECK_ARG(A && W && C && workspace && M > 0 && N > 0 && K > 0 && split_k >= 1 && split_k <= 65535);
+  if (int s = ocv_require_sm100()) return s;
+  const int kps = ceil_div(ceil_div(K, split_k), BK) * BK;
+  const int splits = ceil_div(K, kps);
+  dim3 grid(ceil_div(N, BN), ceil_div(M, BM), splits);
+  Gather g{};
+  sgemm_ex_kernel<0, B_T><<<grid, NT, 0, ocv_stream(stream)>>>(A, W, static_cast<float*>(workspace), M, N, K, lda, ldb, ldc, 0, 0, 0,
+                                                              splits, kps, 1, g);
+  if (int s = ocv_launch_status()) return s;
+  const long long n = (long long)M * N;
+  linear_splitk_reduce_kernel<<<(unsigned)ceil_div<long long>(n, 256), 256, 0, ocv_stream(stream)>>>(
+      static_cast<const float*>(workspace), bias, C, M, N, ldc, splits);
   return ocv_launch_status();
 }

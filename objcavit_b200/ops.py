@@ -83,6 +83,12 @@ def linear(a: torch.Tensor, w: torch.Tensor, bias=None, act: int = ACT_NONE, res
     _, _, ldc = _row_major_2d(out, "out")
     if residual is not None:
         assert residual.shape == out.shape and residual.stride() == out.stride()
+    if residual is None and act == ACT_NONE and K >= 512 and ((M + 63) // 64) * ((N + 63) // 64) <= 64:
+        split = max(2, min(K // 128, (192 * 64 * 64) // max(M * N, 1), 32))      # long K, few tiles: split-K
+        ws = _workspace(split * M * N * 4, a.device, "linear_splitk")
+        _call("ocv_linear_splitk_f32", a.data_ptr(), w.data_ptr(), _ptr(bias), out.data_ptr(), M, N, K, lda, ldb, ldc, split,
+              ws.data_ptr(), _stream(), launches=2)
+        return out
     _call("ocv_linear_f32", a.data_ptr(), w.data_ptr(), _ptr(bias), _ptr(residual), out.data_ptr(),
           M, N, K, lda, ldb, ldc, 1, act, 1, 0, 0, 0, _stream())
     return out

@@ -25,6 +25,14 @@ def tagged(a, b, M, N, K, *args, **kw):
     finally:
         ops.profile_tag = ""
 ops.gemm_ex = tagged
+orig_lin = ops.linear
+def tagged_lin(a, w, *args, **kw):
+    ops.profile_tag = f"[{a.shape[0]}x{w.shape[0]}x{a.shape[1]}]"
+    try:
+        return orig_lin(a, w, *args, **kw)
+    finally:
+        ops.profile_tag = ""
+ops.linear = tagged_lin
 import objcavit_b200.engine_train as et
 for _ in range(3):
     tr.step(x, list(objs), list(boxes), gt, mask)

@@ -125,3 +125,17 @@ def test_patch_embed_wgrad_bf16(cuda):
     patches = torch.nn.functional.unfold(x, P, stride=P)           # [B, C*P*P, S]
     ref = torch.einsum("bse,bks->ek", dtok.view(B, S, E), patches).view(E, C, P, P) + 1.0
     assert rel_err(dw, ref) < 1e-2
+
+
+def test_prefetcher_and_lagged_scalars(cuda):
+    from objcavit_b200.prefetch import DevicePrefetcher, LaggedScalars
+    host = [(torch.full((4, 3), float(i)).pin_memory(), [torch.full((2,), float(10 * i)).pin_memory(), None], {"k": i}) for i in range(5)]
+    seen = []
+    for a, lst, meta in DevicePrefetcher(host, cuda):
+        assert a.is_cuda and lst[0].is_cuda and lst[1] is None
+        seen.append((float(a[0, 0]), float(lst[0][0]), meta["k"]))
+    assert seen == [(float(i), float(10 * i), i) for i in range(5)]
+    lag = LaggedScalars(2, lag=1)
+    outs = [lag.push(torch.tensor(float(i), device=cuda), torch.tensor(float(-i), device=cuda)) for i in range(4)]
+    assert outs[0] is None and outs[1:] == [[0.0, -0.0], [1.0, -1.0], [2.0, -2.0]]
+    assert lag.flush() == [[3.0, -3.0]]
