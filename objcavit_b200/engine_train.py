@@ -50,6 +50,46 @@ class Touched(dict):
         return super().__getitem__(k)
 
 
+# ----------------------------------------------------------------------------------------------------------------------
+# Weight-gradient stream.  In the backward of a layer only the DATA gradients are on the critical path; the weight / bias gradient
+# GEMMs (half of the token-path GEMM time, each far too small to fill 148 SMs) run on a second stream next to them.  The side
+# stream waits for everything issued so far on the main stream before each GEMM; tensors it reads are pinned to it with
+# record_stream; `join_side` makes the main stream wait (end of the backward, and before any in-place update of a tensor the side
+# stream may still read).  Gradient buffers are written by one stream only per parameter, so the result is bit-identical.
+# ----------------------------------------------------------------------------------------------------------------------
+ASYNC_WGRAD = True
+_side_streams = {}
+
+
+def _side(device) -> "torch.cuda.Stream":
+    key = torch.device(device).index or 0
+    if key not in _side_streams:
+        _side_streams[key] = torch.cuda.Stream(device)
+    return _side_streams[key]
+
+
+def on_side(fn, *tensors):
+    """Run ``fn()`` (kernel launches only) on the weight-gradient stream after everything issued so far; ``tensors`` = what it reads."""
+    if not ASYNC_WGRAD:
+        return fn()
+    dev = tensors[0].device
+    side = _side(dev)
+    side.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(side):
+        fn()
+    for t in tensors:
+        t.record_stream(side)
+
+
+def join_side(device) -> None:
+    if ASYNC_WGRAD and (torch.device(device).index or 0) in _side_streams:
+        torch.cuda.current_stream(device).wait_stream(_side(device))
+
+
+def _wgrad(dy, x, gw, gb) -> None:
+    on_side(lambda: ops.linear_wgrad(dy, x, gw, gb, beta=1.0), dy, x)
+
+
 class DropCtx:
     """Dropout state of one training forward: probability ``p`` (0 = identity: no dropout kernels are launched) and a base seed;
     every dropout site of the forward draws its own 64-bit site seed with :meth:`site`, recorded on the tape for the backward.
@@ -134,21 +174,25 @@ def encoder_layer_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor)
     d = dout.reshape(B * S, E)
     dy2 = ops.layernorm_bwd(d, y2, P[pre + "norm2.weight"], G[pre + "norm2.weight"], G[pre + "norm2.bias"], beta=1.0)
     df = ops.dropout(dy2, p, sites[3]) if p > 0 else dy2                         # gradient of linear2's output
-    ops.linear_wgrad(df, h, G[pre + "linear2.weight"], G[pre + "linear2.bias"], beta=1.0)
+    _wgrad(df, h, G[pre + "linear2.weight"], G[pre + "linear2.bias"])
     dh = ops.linear_dgrad(df, P[pre + "linear2.weight"])
     if p > 0:
         ops.dropout(dh, p, sites[2], out=dh)                                     # h is the post-dropout activation: h > 0 <=> kept & positive
     dh = ops.act_bwd(dh, h, RELU)
-    ops.linear_wgrad(dh, x1, G[pre + "linear1.weight"], G[pre + "linear1.bias"], beta=1.0)
+    _wgrad(dh, x1, G[pre + "linear1.weight"], G[pre + "linear1.bias"])
+    if p == 0:
+        join_side(d.device)                                                      # df aliases dy2, which is updated in place next
     ops.linear_dgrad(dh, P[pre + "linear1.weight"], out=dy2, beta=1.0)           # dy2 <- d loss / d x1 (residual + FFN)
     dy = ops.layernorm_bwd(dy2, y, P[pre + "norm1.weight"], G[pre + "norm1.weight"], G[pre + "norm1.bias"], beta=1.0)
     dsa = ops.dropout(dy, p, sites[1]) if p > 0 else dy                          # gradient of out_proj's output
-    ops.linear_wgrad(dsa, att.view(B * S, E), G[pre + "self_attn.out_proj.weight"], G[pre + "self_attn.out_proj.bias"], beta=1.0)
+    _wgrad(dsa, att.view(B * S, E), G[pre + "self_attn.out_proj.weight"], G[pre + "self_attn.out_proj.bias"])
     datt = ops.linear_dgrad(dsa, P[pre + "self_attn.out_proj.weight"]).view(B, S, E)
     dqkv = ops.mha_core_bwd(qkv[:, :, 0:E], qkv[:, :, E:2 * E], qkv[:, :, 2 * E:], att, datt, mask, HEADS, packed=True,
                             drop=(p, sites[0]) if p > 0 else None)[3]
     dqkv = dqkv.view(B * S, 3 * E)
-    ops.linear_wgrad(dqkv, x2, G[pre + "self_attn.in_proj_weight"], G[pre + "self_attn.in_proj_bias"], beta=1.0)
+    _wgrad(dqkv, x2, G[pre + "self_attn.in_proj_weight"], G[pre + "self_attn.in_proj_bias"])
+    if p == 0:
+        join_side(d.device)                                                      # dsa aliases dy, which is updated in place next
     ops.linear_dgrad(dqkv, P[pre + "self_attn.in_proj_weight"], out=dy, beta=1.0)  # dy <- d loss / d x (residual + attention)
     return dy.view(B, S, E)
 
@@ -393,13 +437,18 @@ def _pixel_bwd_bf16_rest(P: Params, G: Params, t, dlT: torch.Tensor, dtok: torch
     ops.gemm_ex(dMb, queries, K, Q, E, E, E, G["conv_out.0.weight"], Q, op_b=1, beta=1.0, batch=B, stride_a=K * E, stride_b=S * E,
                 reduce_batch=True)
     ops.gemm_ex(Wout, dMb, Q, E, K, Q, E, dtok[:, 1:Q + 1, :], E, trans_a=True, batch=B, stride_a=0, stride_b=K * E, stride_c=S * E)
-    # conv3x3 weight + bias: one GEMM over all pixels of the batch
-    col = ops.im2col3x3_bf16(ops.cast_bf16(x))
-    gw = G[pre + "conv3x3.weight"].view(C, C * 9)
-    skw = max(1, min(32, (B * Pn) // 8192))
-    ops.gemm_bf16(dx3T, col[:C * 9], residual=gw, out=gw, split_k=skw)
-    db = ops.gemm_bf16(dx3T, col[C * 9:], split_k=skw)                        # [C,8]: column 0 = sum over pixels, the rest 0
-    ops.reduce_channels(db, G[pre + "conv3x3.bias"], 1, 1, C, 8, beta=1.0)
+    # conv3x3 weight + bias: one GEMM over all pixels of the batch — nothing downstream needs it, so it runs on the
+    # weight-gradient stream next to the token-path backward
+    gw, gb = G[pre + "conv3x3.weight"].view(C, C * 9), G[pre + "conv3x3.bias"]
+
+    def conv_wgrad():
+        col = ops.im2col3x3_bf16(ops.cast_bf16(x))
+        skw = max(1, min(32, (B * Pn) // 8192))
+        ops.gemm_bf16(dx3T, col[:C * 9], residual=gw, out=gw, split_k=skw)
+        db = ops.gemm_bf16(dx3T, col[C * 9:], split_k=skw)                    # [C,8]: column 0 = sum over pixels, the rest 0
+        ops.reduce_channels(db, gb, 1, 1, C, 8, beta=1.0)
+
+    on_side(conv_wgrad, dx3T, x)
 
 
 def backward(P: Params, G: Params, t: Tape, d_depth: torch.Tensor, d_edges: Optional[torch.Tensor]) -> None:
@@ -487,3 +536,4 @@ def _token_bwd(P: Params, G: Params, t: Tape, dtok: torch.Tensor) -> None:
         ops.gemm_ex(dt2, x, E, C * Pp * Pp, B * S, E, 0, G[wkey], C * Pp * Pp, trans_a=True, op_b=2, beta=1.0,
                     split_k=_split(E, C * Pp * Pp, 1, B * S), geom=(C, h, w, Pp))
     ops.reduce_channels(dt2, G[bkey], 1, B * S, E, 1, beta=1.0)
+    join_side(dev)

@@ -92,7 +92,10 @@ class HeadTrainer:
         return dist.get_world_size(self.group) if dist.is_available() and dist.is_initialized() else 1
 
     def _maps(self):
-        named = dict(self.head.named_parameters())
+        named = self.__dict__.get("_named")
+        if named is None:                                   # the walk over the module tree is host time on every step otherwise
+            named = self._named = dict(self.head.named_parameters())
+            self._modules = list(self.head.modules())
         P = {k: named[k].data for k in self.keys}
         G = engine_train.Touched({k: named[k].grad for k in self.keys})
         return P, G
@@ -109,7 +112,7 @@ class HeadTrainer:
         l2, d_edges = ops.bins_chamfer(edges, gt, depth_mask, want_grad=True, grad_scale=self.coeffs[1])
         engine_train.backward(P, G, tape, d_depth, d_edges)
         if self.ranges is None:                      # static per configuration: merge the touched parameters into flat ranges
-            named = dict(self.head.named_parameters())
+            named = self._named
             spans = sorted((off, off + (p.numel() + 63) // 64 * 64) for (p, off) in zip(self.grads.params, self.grads.offsets)
                            if any(named[k] is p for k in G.touched))
             merged = []
@@ -139,7 +142,7 @@ class HeadTrainer:
             ops.adamw_step(self.flat_params[lo:hi], self.grads.flat[lo:hi], self.exp_avg[lo:hi], self.exp_avg_sq[lo:hi], lr, beta1,
                            self.betas[1], self.eps, self.wd, self.step_index, grad_scale=scale,
                            grad_sumsq=self.sumsq if clip else None, max_norm=float(self.clip or 0.0))
-        for m in self.head.modules():              # the kernel wrote the parameters behind torch's version counters:
+        for m in self._modules:                    # the kernel wrote the parameters behind torch's version counters:
             m.__dict__.pop("_ocv_packed", None)    # drop the derived bf16 / packed inference operands
             m.__dict__.pop("_ocv_native", None)
         return l1, l2
