@@ -109,14 +109,19 @@ metrics_partial_kernel(const float* __restrict__ pred, const float* __restrict__
   }
 }
 
-// sums[k] (this call) and acc[k] += sums[k] (running state across calls), fixed order
-__global__ void metrics_final_kernel(const double* __restrict__ part, int nblk, double* __restrict__ sums, double* __restrict__ acc) {
-  const int k = threadIdx.x;
-  if (k >= NACC) return;
+// sums[k] (this call) and acc[k] += sums[k] (running state across calls).  One warp per accumulator: lane l adds the partials of
+// blocks l, l+32, ... in order, then a fixed shuffle tree — deterministic, and 32 independent load streams instead of one thread
+// walking 1184 blocks (which cost 60 us).
+__global__ void __launch_bounds__(NACC * 32)
+metrics_final_kernel(const double* __restrict__ part, int nblk, double* __restrict__ sums, double* __restrict__ acc) {
+  const int k = threadIdx.x / 32, lane = threadIdx.x % 32;
   double t = 0.0;
-  for (int i = 0; i < nblk; ++i) t += part[(long long)i * NACC + k];
-  if (sums) sums[k] = t;
-  if (acc) acc[k] += t;
+  for (int i = lane; i < nblk; i += 32) t += part[(long long)i * NACC + k];
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  if (lane == 0) {
+    if (sums) sums[k] = t;
+    if (acc) acc[k] += t;
+  }
 }
 
 // one thread per object: reversed order inside the image, xyxy -> (cx, cy, w, h), relative-size bucket vs the next object
@@ -188,7 +193,7 @@ extern "C" int ocv_depth_metrics_f32(const float* depth_pred, const float* depth
   double* part = static_cast<double*>(workspace);
   metrics_partial_kernel<<<nblk, NT, 0, ocv_stream(stream)>>>(depth_pred, depth_gt, upsampled_out, a, part);
   if (int s = ocv_launch_status()) return s;
-  metrics_final_kernel<<<1, 32, 0, ocv_stream(stream)>>>(part, nblk, sums, acc);
+  metrics_final_kernel<<<1, NACC * 32, 0, ocv_stream(stream)>>>(part, nblk, sums, acc);
   return ocv_launch_status();
 }
 
