@@ -71,14 +71,14 @@ tail_logits_kernel(const float* __restrict__ logits, const float* __restrict__ b
 
 // dlT[b,k,p] (bf16) = g p (c - depth);   part[b][blk][0][k] = sum over the block's pixels of g p,  part[..][1][k] = of dl.
 // Two passes over the block's [K x 128] logits (online-softmax statistics on four independent chains; outputs): the loads of a
-// pass are independent (deep memory-level parallelism).  The per-bin pixel sums are warp-reduced by
-// shuffles, kept in registers (lane j owns bins j, j+32, ...), and the four warps are added in fixed order.  K % 32 == 0, K <= 512.
+// pass are independent (deep memory-level parallelism).  The per-bin pixel sums are warp-reduced by a transposed
+// butterfly, kept in registers (lane j owns bins j, j+32, ...), and the four warps are added in fixed order.  K % 32 == 0, K <= 512.
 template <int KK>  // K / 32
-__global__ void __launch_bounds__(TPB)
+__global__ void __launch_bounds__(TPB, 4)
 tail_logits_bwd_kernel(const float* __restrict__ logits, const float* __restrict__ bias, const float* __restrict__ centres,
                        const float* __restrict__ gdepth, __nv_bfloat16* __restrict__ dlT, float* __restrict__ part, long long P) {
   constexpr int K = KK * 32;
-  __shared__ float cs[K], bs[K], acc[2 * K];
+  __shared__ float cs[K], bs[K], wacc[TPB / 32][2 * K];
   const int b = blockIdx.y, warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   for (int k = threadIdx.x; k < K; k += TPB) {
     cs[k] = centres[(long long)b * K + k];
@@ -92,39 +92,40 @@ tail_logits_bwd_kernel(const float* __restrict__ logits, const float* __restrict
   softmax_stats(l, P, bs, cs, K, m, s, a);
   const float inv = 1.f / s, d = a * inv, gd = live ? gdepth[(long long)b * P + px] : 0.f;
   __nv_bfloat16* o = dlT + (long long)b * K * P + (live ? px : 0);
-  float rpg[KK], rdl[KK];
-#pragma unroll
+#pragma unroll 1
   for (int kk = 0; kk < KK; ++kk) {
-#pragma unroll 8
+    float pg[32], dl[32];
+#pragma unroll
     for (int j = 0; j < 32; ++j) {
       const int k = kk * 32 + j;
-      float pg = gd * __expf(l[(long long)k * P] + bs[k] - m) * inv;
-      float dl = pg * (cs[k] - d);
-      if (live) o[(long long)k * P] = __float2bfloat16(dl);
+      pg[j] = gd * __expf(l[(long long)k * P] + bs[k] - m) * inv;
+      dl[j] = pg[j] * (cs[k] - d);
+      if (live) o[(long long)k * P] = __float2bfloat16(dl[j]);
+    }
+    // transposed butterfly: 31 shuffles per array leave the sum over the 32 pixels of bin kk*32 + lane in element 0 of lane
+    // `lane` (a plain butterfly per bin would be 160); fixed order -> deterministic
 #pragma unroll
-      for (int off = 16; off > 0; off >>= 1) {
-        pg += __shfl_xor_sync(0xffffffffu, pg, off);
-        dl += __shfl_xor_sync(0xffffffffu, dl, off);
-      }
-      if (lane == j) {
-        rpg[kk] = pg;
-        rdl[kk] = dl;
+    for (int off = 16; off >= 1; off >>= 1) {
+      const bool upper = (lane & off) != 0;
+#pragma unroll
+      for (int i = 0; i < off; ++i) {
+        const float sp = upper ? pg[i] : pg[i + off], kp = upper ? pg[i + off] : pg[i];
+        pg[i] = kp + __shfl_xor_sync(0xffffffffu, sp, off);
+        const float sd = upper ? dl[i] : dl[i + off], kd = upper ? dl[i + off] : dl[i];
+        dl[i] = kd + __shfl_xor_sync(0xffffffffu, sd, off);
       }
     }
+    wacc[warp][kk * 32 + lane] = pg[0];
+    wacc[warp][K + kk * 32 + lane] = dl[0];
   }
-  for (int w = 0; w < TPB / 32; ++w) {  // fixed order over the warps
-    if (warp == w) {
-#pragma unroll
-      for (int kk = 0; kk < KK; ++kk) {
-        const int k = kk * 32 + lane;
-        acc[k] = (w ? acc[k] : 0.f) + rpg[kk];
-        acc[K + k] = (w ? acc[K + k] : 0.f) + rdl[kk];
-      }
-    }
-    __syncthreads();
-  }
+  __syncthreads();
   float* dst = part + ((long long)b * gridDim.x + blockIdx.x) * 2 * K;
-  for (int i = threadIdx.x; i < 2 * K; i += TPB) dst[i] = acc[i];
+  for (int i = threadIdx.x; i < 2 * K; i += TPB) {  // fixed order over the warps
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < TPB / 32; ++w) t += wacc[w][i];
+    dst[i] = t;
+  }
 }
 
 // dcentres[b,k] = sum_blk part[b][blk][0][k];  pb[b][k] = sum_blk part[b][blk][1][k].   Block = (32 bins, 8 slices of the block

@@ -92,3 +92,57 @@ def test_trainer_step_equals_autograd_boundary_plus_torch_adamw(cuda):
     with torch.no_grad():                                                       # and inference still runs on the updated weights
         o2 = b.eval()(feats.to(cuda), dev(objs), dev(boxes))
     assert torch.isfinite(o2.depth_pred).all()
+
+
+def _fullsize_inputs(cuda, seed=3):
+    """BASELINE.json config 5 at its full size: batch 8, features 128x208x272, GT 416x544, 32 boxes per image."""
+    B, H, W, NOBJ = 8, 208, 272, 32
+    x = synth.make_features(B, H, W, seed=seed).to(cuda)
+    objs, boxes = synth.make_objects(B, H, W, NOBJ, seed=seed)
+    gt, mask = synth.make_gt(B, H, W, 10.0, seed=seed)
+    return x, [o.to(cuda) for o in objs], [b.to(cuda) for b in boxes], gt.to(cuda), mask.to(cuda)
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_fullsize_training_steps_are_deterministic_and_reduce_the_loss(cuda, precision):
+    """Size-independent properties at the full config-5 size: two runs from the same seed give bit-identical parameters (every
+    reduction is fixed-order, the weight-gradient stream writes disjoint buffers, dropout masks are counter-based), all values
+    stay finite, and six optimizer steps on one batch lower the loss."""
+    args = builtin_args("nyu_ocv_learned_bbox_wh")
+    with open(os.path.join(GOLD, "manifest_nyu_ocv_learned_bbox_wh.json")) as f:
+        sd = synth.make_state_dict(json.load(f), seed=5)
+    x, objs, boxes, gt, mask = _fullsize_inputs(cuda)
+    runs = []
+    for rep in range(2):
+        head = build_head(args, precision=precision).to(cuda).train()
+        head.load_state_dict(sd)
+        tr = HeadTrainer(head, lr=3.57e-4, weight_decay=0.1, clip_grad_norm=0.1)
+        torch.manual_seed(123)
+        losses = []
+        for _ in range(6):
+            l1, l2 = tr.step(x, list(objs), list(boxes), gt, mask)
+            losses.append(tr.loss_value(l1, l2))
+        runs.append((losses, tr.flat_params.clone()))
+    assert runs[0][0] == runs[1][0] and torch.equal(runs[0][1], runs[1][1])
+    assert all(l == l and abs(l) < 1e6 for l in runs[0][0]) and bool(torch.isfinite(runs[0][1]).all())
+    assert runs[0][0][-1] < runs[0][0][0], runs[0][0]
+
+
+def test_fullsize_bf16_pixel_path_loss_matches_fp32_path(cuda):
+    args = builtin_args("nyu_ocv_learned_bbox_wh")
+    with open(os.path.join(GOLD, "manifest_nyu_ocv_learned_bbox_wh.json")) as f:
+        sd = synth.make_state_dict(json.load(f), seed=5)
+    x, objs, boxes, gt, mask = _fullsize_inputs(cuda)
+    vals = {}
+    for precision in ("fp32", "bf16"):
+        head = build_head(args, precision=precision).to(cuda).train()
+        head.dropout = 0.0
+        head.load_state_dict(sd)
+        tr = HeadTrainer(head, lr=3.57e-4, weight_decay=0.1, clip_grad_norm=0.1)
+        l1, l2 = tr.forward_backward(x, list(objs), list(boxes), gt, mask)
+        torch.cuda.synchronize()
+        vals[precision] = (float(l1), float(l2), tr.last_outputs[0].clone(), float(tr.grads.flat.double().norm()))
+    a, b = vals["fp32"], vals["bf16"]
+    assert abs(a[0] - b[0]) < 2e-2 * abs(a[0]) and abs(a[1] - b[1]) < 2e-2 * abs(a[1])
+    assert rel_err(b[2], a[2]) < 2e-2                                   # north_star: bf16 path within 2e-2 relative
+    assert abs(a[3] - b[3]) < 5e-2 * a[3]                               # size of the whole gradient
