@@ -294,6 +294,17 @@ int ocv_mha_core_bwd_dropout_f32(const float* q, const float* k, const float* v,
                                  long long dk_bstride, int dk_rstride, long long dv_bstride, int dv_rstride, float drop_p,
                                  unsigned long long drop_seed, void* workspace, void* stream);
 
+/* Backward of ocv_grid_sample_pos_f32 / ocv_ps_roi_align_pos_f32 w.r.t. the positional table (training with the grid_random /
+ * grid_random_roi_align strategies; what autograd does through F.grid_sample / torchvision.ops.ps_roi_align in
+ * modules/ObjCAViT.py:99,109,128,144).  Same argument meaning as the forward; dout [N,E].  The kernels scatter into
+ * table_grad_fix [gh*gw, E] int64 (fixed point, 2^40 per unit; zero it first; integer atomics -> deterministic);
+ * ocv_table_grad_commit_f32 then does table_grad[i] = beta*table_grad[i] + fix[i] / 2^40. */
+int ocv_grid_sample_pos_bwd_f32(const float* dout, const float* pts, long long* table_grad_fix, int N, int gh, int gw, int E,
+                                int norm_mode, float div0, float div1, void* stream);
+int ocv_ps_roi_align_pos_bwd_f32(const float* dout, const float* boxes, long long* table_grad_fix, int N, int gh, int gw, int E,
+                                 float spatial_scale, int boxes_are_xywh, void* stream);
+int ocv_table_grad_commit_f32(const long long* table_grad_fix, float* table_grad, long long n, float beta, void* stream);
+
 /* ---- training step, tensor-core pixel path (precision "bf16"; objcavit_b200/csrc/train_pixel_bf16.cu) ----------------------
  * The pixel path of the training step as tcgen05 GEMMs (ocv_conv3x3_nhwc_bf16, ocv_gemm_bf16) joined by HBM-bound helpers:
  *   ocv_tail_logits_f32: depth [B,P] = sum_k softmax_k(logits[b,k,p] + bias[k]) centres[b,k] on channel-major fp32 logits

@@ -249,6 +249,101 @@ __global__ void ps_roi_align_pos_kernel(const float* __restrict__ table, const f
 }
 
 // ------------------------------------------------------------------------------------------------
+// Backward of the two table lookups w.r.t. the positional table (training with the grid_random* strategies): the same index /
+// weight arithmetic as the forward kernels, scattering  w * dout[n,e]  into the table cells.  The scatter target is a 64-bit
+// FIXED-POINT accumulator (2^40 per unit): integer atomics commute, so the result does not depend on the order in which warps
+// arrive (deterministic), and its resolution (1e-12) is far below fp32.  ocv_table_grad_commit_f32 converts and accumulates it
+// into the fp32 gradient.  Coordinates / boxes are inputs of the head: they receive no gradient (as in the reference).
+// ------------------------------------------------------------------------------------------------
+constexpr double TG_FIX = 1099511627776.0;  // 2^40
+
+__device__ __forceinline__ void table_scatter(long long* __restrict__ fix, int cell, int e, int E, float v) {
+  atomicAdd(reinterpret_cast<unsigned long long*>(fix + (long long)cell * E + e), (unsigned long long)__double2ll_rn((double)v * TG_FIX));
+}
+
+__global__ void grid_sample_pos_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ pts, long long* __restrict__ fix,
+                                           int N, int gh, int gw, int E, int norm_mode, float div0, float div1) {
+  const int n = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+  const int lane = threadIdx.x % 32;
+  if (n >= N) return;
+  float x = pts[2 * n], y = pts[2 * n + 1];
+  if (norm_mode == 1) {
+    x = __fsub_rn(__fmul_rn(__fdiv_rn(x, div0), 2.f), 1.f);
+    y = __fsub_rn(__fmul_rn(__fdiv_rn(y, div1), 2.f), 1.f);
+  } else if (norm_mode == 2 && n < 2) {
+    const float d = n == 0 ? div0 : div1;
+    x = __fsub_rn(__fmul_rn(__fdiv_rn(x, d), 2.f), 1.f);
+    y = __fsub_rn(__fmul_rn(__fdiv_rn(y, d), 2.f), 1.f);
+  }
+  const float ix = __fsub_rn(__fmul_rn(__fadd_rn(x, 1.f), (float)gw / 2.f), 0.5f);
+  const float iy = __fsub_rn(__fmul_rn(__fadd_rn(y, 1.f), (float)gh / 2.f), 0.5f);
+  const float x0 = floorf(ix), y0 = floorf(iy);
+  const float x1 = x0 + 1.f, y1 = y0 + 1.f;
+  const float wts[4] = {__fmul_rn(__fsub_rn(x1, ix), __fsub_rn(y1, iy)), __fmul_rn(__fsub_rn(ix, x0), __fsub_rn(y1, iy)),
+                        __fmul_rn(__fsub_rn(x1, ix), __fsub_rn(iy, y0)), __fmul_rn(__fsub_rn(ix, x0), __fsub_rn(iy, y0))};
+  const float cx[4] = {x0, x1, x0, x1}, cy[4] = {y0, y0, y1, y1};
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const bool ok = (cx[j] >= 0.f) && (cx[j] < (float)gw) && (cy[j] >= 0.f) && (cy[j] < (float)gh);
+    if (!ok) continue;
+    const int cell = (int)cy[j] * gw + (int)cx[j];
+    for (int e = lane; e < E; e += 32) table_scatter(fix, cell, e, E, wts[j] * dout[(long long)n * E + e]);
+  }
+}
+
+__global__ void ps_roi_align_pos_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ boxes, long long* __restrict__ fix,
+                                            int N, int gh, int gw, int E, float scale, int is_xywh) {
+  const int n = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+  const int lane = threadIdx.x % 32;
+  if (n >= N) return;
+  float bx1 = boxes[4 * n + 0], by1 = boxes[4 * n + 1], bx2 = boxes[4 * n + 2], by2 = boxes[4 * n + 3];
+  if (is_xywh) {
+    const float hw = __fdiv_rn(bx2, 2.f), hh = __fdiv_rn(by2, 2.f);
+    const float cx = bx1, cy = by1;
+    bx1 = fmaxf(__fsub_rn(cx, hw), 0.f);
+    by1 = fmaxf(__fsub_rn(cy, hh), 0.f);
+    bx2 = fmaxf(__fadd_rn(cx, hw), 0.f);
+    by2 = fmaxf(__fadd_rn(cy, hh), 0.f);
+  }
+  const float rsw = __fsub_rn(__fmul_rn(bx1, scale), 0.5f);
+  const float rsh = __fsub_rn(__fmul_rn(by1, scale), 0.5f);
+  const float rew = __fsub_rn(__fmul_rn(bx2, scale), 0.5f);
+  const float reh = __fsub_rn(__fmul_rn(by2, scale), 0.5f);
+  const float rw = __fsub_rn(rew, rsw), rh = __fsub_rn(reh, rsh);
+  const int grid_h = (int)ceilf(rh), grid_w = (int)ceilf(rw);
+  if (grid_h <= 0 || grid_w <= 0) return;  // forward value is 0/0 = NaN there: nothing meaningful to propagate
+  const float inv_count = 1.f / (float)(grid_h * grid_w);
+  const float H = (float)gh, W = (float)gw;
+  for (int iy = 0; iy < grid_h; ++iy) {
+    const float y = __fadd_rn(rsh, __fdiv_rn(__fmul_rn((float)iy + 0.5f, rh), (float)grid_h));
+    for (int ix = 0; ix < grid_w; ++ix) {
+      const float x = __fadd_rn(rsw, __fdiv_rn(__fmul_rn((float)ix + 0.5f, rw), (float)grid_w));
+      if (y < -1.f || y > H || x < -1.f || x > W) continue;
+      float yy = y <= 0.f ? 0.f : y, xx = x <= 0.f ? 0.f : x;
+      int y_low = (int)yy, x_low = (int)xx, y_high, x_high;
+      if (y_low >= gh - 1) { y_high = y_low = gh - 1; yy = (float)y_low; } else y_high = y_low + 1;
+      if (x_low >= gw - 1) { x_high = x_low = gw - 1; xx = (float)x_low; } else x_high = x_low + 1;
+      const float ly = __fsub_rn(yy, (float)y_low), lx = __fsub_rn(xx, (float)x_low);
+      const float hy = __fsub_rn(1.f, ly), hx = __fsub_rn(1.f, lx);
+      const float w4[4] = {__fmul_rn(hy, hx), __fmul_rn(hy, lx), __fmul_rn(ly, hx), __fmul_rn(ly, lx)};
+      const int cell[4] = {y_low * gw + x_low, y_low * gw + x_high, y_high * gw + x_low, y_high * gw + x_high};
+      for (int e = lane; e < E; e += 32) {
+        const float g = dout[(long long)n * E + e] * inv_count;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) table_scatter(fix, cell[j], e, E, w4[j] * g);
+      }
+    }
+  }
+}
+
+__global__ void table_grad_commit_kernel(const long long* __restrict__ fix, float* __restrict__ dtable, long long n, float beta) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float v = (float)((double)fix[i] / TG_FIX);
+  dtable[i] = beta != 0.f ? beta * dtable[i] + v : v;
+}
+
+// ------------------------------------------------------------------------------------------------
 // bins: one block per image
 // ------------------------------------------------------------------------------------------------
 __global__ void bins_kernel(const float* __restrict__ y_raw, float* __restrict__ widths, float* __restrict__ edges,
@@ -406,4 +501,29 @@ extern "C" int ocv_bins_f32(const float* y_raw, float* widths_normed, float* edg
   if (int s = ocv_require_sm100()) return s;
   return ocv_launch_pdl(bins_kernel, dim3(B), dim3(256), 0, stream, y_raw, widths_normed, edges, centres, K, norm,
                         min_depth, max_depth);
+}
+
+extern "C" int ocv_grid_sample_pos_bwd_f32(const float* dout, const float* pts, long long* table_grad_fix, int N, int gh, int gw, int E,
+                                           int norm_mode, float div0, float div1, void* stream) {
+  OCV_CHECK_ARG(dout && pts && table_grad_fix && N > 0 && gh > 0 && gw > 0 && E > 0 && norm_mode >= 0 && norm_mode <= 2);
+  if (int s = ocv_require_sm100()) return s;
+  grid_sample_pos_bwd_kernel<<<ceil_div(N, 4), 128, 0, ocv_stream(stream)>>>(dout, pts, table_grad_fix, N, gh, gw, E, norm_mode, div0,
+                                                                            div1);
+  return ocv_launch_status();
+}
+
+extern "C" int ocv_ps_roi_align_pos_bwd_f32(const float* dout, const float* boxes, long long* table_grad_fix, int N, int gh, int gw,
+                                            int E, float spatial_scale, int boxes_are_xywh, void* stream) {
+  OCV_CHECK_ARG(dout && boxes && table_grad_fix && N > 0 && gh > 0 && gw > 0 && E > 0);
+  if (int s = ocv_require_sm100()) return s;
+  ps_roi_align_pos_bwd_kernel<<<ceil_div(N, 4), 128, 0, ocv_stream(stream)>>>(dout, boxes, table_grad_fix, N, gh, gw, E,
+                                                                             spatial_scale, boxes_are_xywh);
+  return ocv_launch_status();
+}
+
+extern "C" int ocv_table_grad_commit_f32(const long long* table_grad_fix, float* table_grad, long long n, float beta, void* stream) {
+  OCV_CHECK_ARG(table_grad_fix && table_grad && n > 0);
+  if (int s = ocv_require_sm100()) return s;
+  table_grad_commit_kernel<<<(unsigned)ceil_div<long long>(n, 256), 256, 0, ocv_stream(stream)>>>(table_grad_fix, table_grad, n, beta);
+  return ocv_launch_status();
 }

@@ -23,7 +23,8 @@ from typing import Dict, List, Optional
 import torch
 
 from . import ops
-from .engine import E, HEADS, ObjectBatch, marshal_objects
+from .engine import E, HEADS, ObjectBatch, grid_geometry, marshal_objects
+from .engine import positional_embeddings as engine_positional_embeddings
 
 Params = Dict[str, torch.Tensor]
 RELU, LEAKY, NONE = ops.ACT_RELU, ops.ACT_LEAKY_RELU, ops.ACT_NONE
@@ -328,15 +329,16 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
     else:
         pre = "objcavit."
         strategy = cfg["strategy"]
-        if strategy not in ("learned", "learned_bbox_wh"):
-            raise NotImplementedError("objcavit_b200 training: gradient of the grid_random positional table is not built; "
-                                      "the training path supports the 'learned' / 'learned_bbox_wh' strategies (config 5)")
-        nin = 4 if strategy == "learned_bbox_wh" else 2
         feats, boxes, counts = marshal_objects(object_features, object_xywh_list, x.device)
         coords = ops.patch_coords(h // patch_size, w // patch_size, patch_size, x.device)
         pe = pre + "positional_encoder."
-        obj_pos, t.sv_mlp_obj = mlp_fwd(P, pe, boxes[:, 0:nin], (0, 2, 4, 6, 8))
-        img_pos, t.sv_mlp_img = mlp_fwd(P, pe, coords[:, 0:nin], (0, 2, 4, 6, 8))
+        if strategy in ("learned", "learned_bbox_wh"):
+            nin = 4 if strategy == "learned_bbox_wh" else 2
+            obj_pos, t.sv_mlp_obj = mlp_fwd(P, pe, boxes[:, 0:nin], (0, 2, 4, 6, 8))
+            img_pos, t.sv_mlp_img = mlp_fwd(P, pe, coords[:, 0:nin], (0, 2, 4, 6, 8))
+        else:                                # table look-ups (GridRandomPositionalEmbeddings): the inference kernels, boxes kept
+            obj_pos, img_pos = engine_positional_embeddings(P, pe, strategy, boxes, h, w, patch_size)
+            t.pos_inputs = (boxes, coords, patch_size)
         obj_tok = ops.linear(feats, P[pre + "obj_embedding_layer.weight"], P[pre + "obj_embedding_layer.bias"], residual=obj_pos)
         t.feats = feats
         batch = ObjectBatch(obj_tok, counts)
@@ -504,6 +506,23 @@ def backward(P: Params, G: Params, t: Tape, d_depth: torch.Tensor, d_edges: Opti
     _token_bwd(P, G, t, dtok)
 
 
+def _table_bwd(g_table: torch.Tensor, strategy: str, pos_inputs, d_obj: torch.Tensor, d_img: torch.Tensor, h: int, w: int,
+               factor: float = 2.0) -> None:
+    """Gradient of the positional table of the grid_random* strategies (``GridRandomPositionalEmbeddings``,
+    ``modules/ObjCAViT.py:50-147``): the adjoint of ``engine.positional_embeddings`` — same geometry, same quirks (F13) — for the
+    object rows ``d_obj`` [total,E] and the batch-summed image rows ``d_img`` [S,E]."""
+    boxes, coords, patch_size = pos_inputs
+    gh, gw = grid_geometry(h, w, patch_size)
+    fix = ops.table_grad_buffer(gh, gw, E, d_obj.device)
+    if strategy == "grid_random":
+        ops.grid_sample_pos_bwd(d_obj, boxes[:, 0:2].contiguous(), fix, gh, gw, 1, h * factor, w * factor)
+        ops.grid_sample_pos_bwd(d_img, coords[:, 0:2].contiguous(), fix, gh, gw, 2, float(gh), float(gw))
+    else:
+        ops.ps_roi_align_pos_bwd(d_obj, boxes, fix, gh, gw, 1.0 / (patch_size * factor), True)
+        ops.ps_roi_align_pos_bwd(d_img, coords, fix, gh, gw, 1.0 / patch_size, True)
+    ops.table_grad_commit(fix, g_table[0:gh * gw], beta=1.0)
+
+
 def _token_bwd(P: Params, G: Params, t: Tape, dtok: torch.Tensor) -> None:
     """Backward of everything that produced the tokens, from d loss / d tokens [B,S,E]."""
     cfg, pre, x = t.cfg, t.pre, t.x
@@ -525,9 +544,12 @@ def _token_bwd(P: Params, G: Params, t: Tape, dtok: torch.Tensor) -> None:
         d_img_pos = torch.empty(S, E, device=dev, dtype=torch.float32)
         ops.reduce_channels(dtok0.contiguous(), d_img_pos, 1, B, S * E, 1)
         pe = pre + "positional_encoder."
-        mlp_bwd(P, G, pe, (0, 2, 4, 6, 8), t.sv_mlp_img, d_img_pos)
         ops.linear_wgrad(d_obj_tok, t.feats, G[pre + "obj_embedding_layer.weight"], G[pre + "obj_embedding_layer.bias"], beta=1.0)
-        mlp_bwd(P, G, pe, (0, 2, 4, 6, 8), t.sv_mlp_obj, d_obj_tok)
+        if cfg["strategy"] in ("learned", "learned_bbox_wh"):
+            mlp_bwd(P, G, pe, (0, 2, 4, 6, 8), t.sv_mlp_img, d_img_pos)
+            mlp_bwd(P, G, pe, (0, 2, 4, 6, 8), t.sv_mlp_obj, d_obj_tok)
+        else:
+            _table_bwd(G[pe + "positional_encodings"], cfg["strategy"], t.pos_inputs, d_obj_tok.contiguous(), d_img_pos, h, w)
     dt2 = dtok0.contiguous().view(B * S, E)
     Pp = 16
     if t.pixel == "bf16":

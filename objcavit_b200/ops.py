@@ -942,3 +942,37 @@ def patch_embed_wgrad_bf16(dtok: torch.Tensor, x: torch.Tensor, dw: torch.Tensor
     _call("ocv_transpose_cast_f32_bf16", dtok.data_ptr(), dT.data_ptr(), BS, E, E, ld, _stream())
     g = dw.view(E, Cc * P * P)
     gemm_bf16(dT, unf, residual=g, out=g)
+
+
+# ---- positional-table gradients (grid_random / grid_random_roi_align training) ------------------------------------------
+
+def table_grad_buffer(gh: int, gw: int, E: int, device) -> torch.Tensor:
+    """Zeroed fixed-point accumulator [gh*gw, E] int64 for the two scatter kernels below."""
+    return torch.zeros(gh * gw, E, device=device, dtype=torch.int64)
+
+
+def grid_sample_pos_bwd(dout: torch.Tensor, pts: torch.Tensor, fix: torch.Tensor, gh: int, gw: int, norm_mode: int = 0,
+                        div0: float = 1.0, div1: float = 1.0) -> None:
+    _chk(dout, torch.float32, "dout"); _chk(pts, torch.float32, "pts"); _chk(fix, torch.int64, "fix")
+    assert dout.is_contiguous() and pts.is_contiguous() and fix.is_contiguous() and pts.shape == (dout.shape[0], 2)
+    N, E = dout.shape
+    assert fix.shape == (gh * gw, E)
+    _call("ocv_grid_sample_pos_bwd_f32", dout.data_ptr(), pts.data_ptr(), fix.data_ptr(), N, gh, gw, E, norm_mode, float(div0),
+          float(div1), _stream())
+
+
+def ps_roi_align_pos_bwd(dout: torch.Tensor, boxes: torch.Tensor, fix: torch.Tensor, gh: int, gw: int, spatial_scale: float,
+                         boxes_are_xywh: bool) -> None:
+    _chk(dout, torch.float32, "dout"); _chk(boxes, torch.float32, "boxes"); _chk(fix, torch.int64, "fix")
+    assert dout.is_contiguous() and boxes.is_contiguous() and fix.is_contiguous() and boxes.shape == (dout.shape[0], 4)
+    N, E = dout.shape
+    assert fix.shape == (gh * gw, E)
+    _call("ocv_ps_roi_align_pos_bwd_f32", dout.data_ptr(), boxes.data_ptr(), fix.data_ptr(), N, gh, gw, E, float(spatial_scale),
+          int(boxes_are_xywh), _stream())
+
+
+def table_grad_commit(fix: torch.Tensor, dtable: torch.Tensor, beta: float = 1.0) -> None:
+    """dtable[:gh*gw] = beta * dtable[:gh*gw] + fix / 2^40  (``dtable``: the leading rows of the table's gradient)."""
+    _chk(fix, torch.int64, "fix"); _chk(dtable, torch.float32, "dtable")
+    assert fix.is_contiguous() and dtable.is_contiguous() and dtable.numel() == fix.numel()
+    _call("ocv_table_grad_commit_f32", fix.data_ptr(), dtable.data_ptr(), fix.numel(), float(beta), _stream())

@@ -191,7 +191,7 @@ def grid_sample_points(grid_hwE, xs: Sequence[float], ys: Sequence[float]):
     N = xs.numel()
     idx = torch.full((N, 4), -1, dtype=torch.int64)
     wts = torch.stack([w_nw, w_ne, w_sw, w_se], dim=1)
-    out = torch.zeros(N, E, dtype=f32)
+    out = torch.zeros(N, E, dtype=grid_hwE.dtype)          # float32 in the reference; follows the table in the tests' fp64 runs
     flat = grid_hwE.reshape(H * W, E)
     for n in range(N):
         for j, (xx, yy) in enumerate(((x0[n], y0[n]), (x1[n], y0[n]), (x0[n], y1[n]), (x1[n], y1[n]))):
@@ -213,7 +213,7 @@ def ps_roi_align_1x1(grid_hwE, xyxy, spatial_scale: float):
     f32 = torch.float32
     xyxy = torch.as_tensor(xyxy, dtype=f32)
     N = xyxy.shape[0]
-    out = torch.zeros(N, E, dtype=f32)
+    out = torch.zeros(N, E, dtype=grid_hwE.dtype)
     plans = []
     sc = torch.tensor(spatial_scale, dtype=f32)
     half = torch.tensor(0.5, dtype=f32)
@@ -227,7 +227,7 @@ def ps_roi_align_1x1(grid_hwE, xyxy, spatial_scale: float):
         gh = int(math.ceil(float(rh)))
         gw = int(math.ceil(float(rw)))
         count = gh * gw
-        acc = torch.zeros(E, dtype=f32)
+        acc = torch.zeros(E, dtype=grid_hwE.dtype)
         samples = []
         for iy in range(gh):
             y = rsh + torch.tensor(iy + 0.5, dtype=f32) * bin_h / torch.tensor(float(gh), dtype=f32)

@@ -119,3 +119,48 @@ def test_gradient_accumulation_and_flat_buffer(cuda):
         assert p.grad.data_ptr() == buf.flat[off:].data_ptr(), f"{k}: .grad no longer a view of the flat buffer"
         if k in once:
             assert rel_err(p.grad, 2 * once[k]) < 1e-5 or float(once[k].abs().max()) < 1e-7
+
+
+GRID_CASES = {
+    "grid_random": dict(args="nyu_ocv_grid_random", B=2, h=176, w=192, n_obj=6, ragged=True, none_at=1, seed=21),
+    "grid_random_roi_align": dict(args="kitti_ocv_grid_random_roi_align", B=2, h=128, w=320, n_obj=7, ragged=True, seed=22),
+}
+
+
+@pytest.mark.parametrize("name", sorted(GRID_CASES))
+def test_positional_table_gradients_of_the_grid_strategies(cuda, name):
+    """Training with the grid_random / grid_random_roi_align strategies: every parameter gradient, including the positional
+    TABLE (adjoint of F.grid_sample / ps_roi_align incl. the quirks F13), against autograd through the fp64 oracle."""
+    case = GRID_CASES[name]
+    args = builtin_args(case["args"])
+    with open(os.path.join(GOLD, f"manifest_{case['args']}.json")) as f:
+        sd = synth.make_state_dict(json.load(f), seed=case["seed"])
+    feats, objs, boxes = case_inputs(case)
+    gt, mask = case_gt(case, args)
+    head, out, loss = _run_cuda(args, sd, feats, objs, boxes, gt, mask, cuda)
+    sd_g = {k: v.double().requires_grad_(True) for k, v in sd.items()}
+    f64 = lambda lst: [None if t is None else t.double() for t in lst]
+    o_depth, o_edges, _, _ = oh.head_forward(sd_g, dict(case_cfg(case, args), train=True), feats.double(), f64(objs), f64(boxes))
+    o_loss = oh.silog_loss(o_depth, gt.double(), mask) + 0.1 * oh.bins_chamfer_loss(o_edges, gt.double(), mask)
+    o_loss.backward()
+    assert abs(float(loss.detach()) - float(o_loss.detach())) < 2e-5 * abs(float(o_loss.detach()))
+    grads = {k: p.grad for k, p in head.named_parameters()}
+    gmax = max(float(v.grad.abs().max()) for v in sd_g.values() if v.grad is not None)
+    tkey = "objcavit.positional_encoder.positional_encodings"
+    assert sd_g[tkey].grad is not None and float(sd_g[tkey].grad.abs().max()) > 0 and grads[tkey] is not None
+    worst, bad = 0.0, []
+    for k, g in grads.items():
+        og = sd_g[k].grad
+        if og is None:
+            assert g is None or float(g.abs().max()) == 0.0, k
+            continue
+        assert g is not None, k
+        err = float((g.cpu().double() - og).abs().max()) / max(float(og.abs().max()), GRAD_FLOOR * gmax)
+        worst = max(worst, err)
+        if err >= GRAD_TOL:
+            bad.append(f"{k}: {err:.2e}")
+    print(f"{name}: worst per-parameter gradient error {worst:.2e}; table gradient max {float(grads[tkey].abs().max()):.3e}")
+    assert not bad, "; ".join(bad)
+    # deterministic scatter (integer fixed-point atomics)
+    head2, _, _ = _run_cuda(args, sd, feats, objs, boxes, gt, mask, cuda)
+    assert torch.equal(dict(head2.named_parameters())[tkey].grad, grads[tkey])
