@@ -294,6 +294,26 @@ int ocv_mha_core_bwd_dropout_f32(const float* q, const float* k, const float* v,
                                  long long dk_bstride, int dk_rstride, long long dv_bstride, int dv_rstride, float drop_p,
                                  unsigned long long drop_seed, void* workspace, void* stream);
 
+/* ---- native sequencer of one encoder layer of the training step (objcavit_b200/csrc/train_layer.cu) ----------------------
+ * One call = the forward (or the explicit backward) of one nn.TransformerEncoderLayer (post-norm, ReLU, E = 128, 4 heads, FFN
+ * width F; modules/layers.py:8, modules/ObjCAViT.py:155-161) in train() mode, built from the entry points above in the order
+ * autograd would run them.  W / G: HOST arrays of 12 DEVICE pointers (parameters / their gradient buffers, accumulated) in the
+ * order in_proj_weight, in_proj_bias, out_proj.weight, out_proj.bias, linear1.weight, linear1.bias, linear2.weight,
+ * linear2.bias, norm1.weight, norm1.bias, norm2.weight, norm2.bias.  x [B*S,128]; mask uint8 [B,S] or NULL; drop_p + seeds (HOST
+ * array of 4 site seeds: attention probabilities, dropout1, dropout, dropout2; ignored when drop_p == 0).
+ * Forward outputs = what the backward reads: qkv [B*S,384], att, y (pre-norm1 sum), x1, h [B*S,F] (post ReLU / dropout), y2
+ * (pre-norm2 sum), out.  Backward: dout [B*S,128] -> dx [B*S,128]; weight / bias gradients run on side_stream (NULL = same
+ * stream), ordered with events; the caller makes its stream wait for side_stream before it reads G. */
+long long ocv_encoder_layer_fwd_train_workspace(int B, int S, int F);
+int ocv_encoder_layer_fwd_train_f32(const float* const* W, const float* x, const uint8_t* mask, int B, int S, int F, float drop_p,
+                                    const unsigned long long* seeds, float* qkv, float* att, float* y, float* x1, float* h, float* y2,
+                                    float* out, void* workspace, void* stream);
+long long ocv_encoder_layer_bwd_train_workspace(int B, int S, int F);
+int ocv_encoder_layer_bwd_train_f32(const float* const* W, float* const* G, const float* x, const float* qkv, const float* att,
+                                    const float* y, const float* x1, const float* h, const float* y2, const uint8_t* mask,
+                                    const float* dout, float* dx, int B, int S, int F, float drop_p, const unsigned long long* seeds,
+                                    void* workspace, void* stream, void* side_stream);
+
 /* Backward of ocv_grid_sample_pos_f32 / ocv_ps_roi_align_pos_f32 w.r.t. the positional table (training with the grid_random /
  * grid_random_roi_align strategies; what autograd does through F.grid_sample / torchvision.ops.ps_roi_align in
  * modules/ObjCAViT.py:99,109,128,144).  Same argument meaning as the forward; dout [N,E].  The kernels scatter into

@@ -143,8 +143,17 @@ def mlp_bwd(P: Params, G: Params, pre: str, idxs, saved, dy: torch.Tensor, dx_ou
 # nn.TransformerEncoderLayer (post-norm) / nn.TransformerEncoder
 # ----------------------------------------------------------------------------------------------------------------------
 
+NATIVE_LAYER = True      # one C call per encoder layer and direction (csrc/train_layer.cu) instead of ~30 Python-sequenced ones
+
+
 def encoder_layer_fwd(P: Params, pre: str, x: torch.Tensor, mask, drop: DropCtx = NO_DROP):
     B, S, _ = x.shape
+    if NATIVE_LAYER:
+        p = drop.p
+        sites = (drop.site(), drop.site(), drop.site(), drop.site()) if p > 0 else None
+        xc = x.contiguous()
+        out, (qkv, att, y, x1, h, y2) = ops.encoder_layer_fwd_train([P[pre + k] for k in ops.LAYER_KEYS], xc, mask, p, sites)
+        return out, (xc.view(B * S, E), qkv, att, y, x1, h, y2, mask, (p, sites))
     x2 = x.view(B * S, E)
     p = drop.p
     qkv = ops.linear(x2, P[pre + "self_attn.in_proj_weight"], P[pre + "self_attn.in_proj_bias"]).view(B, S, 3 * E)
@@ -172,6 +181,10 @@ def encoder_layer_fwd(P: Params, pre: str, x: torch.Tensor, mask, drop: DropCtx 
 def encoder_layer_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor) -> torch.Tensor:
     x2, qkv, att, y, x1, h, y2, mask, (p, sites) = saved
     B, S, _ = qkv.shape
+    if NATIVE_LAYER:
+        side = _side(dout.device) if ASYNC_WGRAD else None
+        return ops.encoder_layer_bwd_train([P[pre + k] for k in ops.LAYER_KEYS], [G[pre + k] for k in ops.LAYER_KEYS], x2, qkv, att,
+                                           y, x1, h, y2, mask, dout, p, sites, side)
     d = dout.reshape(B * S, E)
     dy2 = ops.layernorm_bwd(d, y2, P[pre + "norm2.weight"], G[pre + "norm2.weight"], G[pre + "norm2.bias"], beta=1.0)
     df = ops.dropout(dy2, p, sites[3]) if p > 0 else dy2                         # gradient of linear2's output

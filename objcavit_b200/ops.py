@@ -976,3 +976,58 @@ def table_grad_commit(fix: torch.Tensor, dtable: torch.Tensor, beta: float = 1.0
     _chk(fix, torch.int64, "fix"); _chk(dtable, torch.float32, "dtable")
     assert fix.is_contiguous() and dtable.is_contiguous() and dtable.numel() == fix.numel()
     _call("ocv_table_grad_commit_f32", fix.data_ptr(), dtable.data_ptr(), fix.numel(), float(beta), _stream())
+
+
+# ---- native sequencer of one encoder layer of the training step (csrc/train_layer.cu) ---------------------------------------
+
+LAYER_KEYS = ("self_attn.in_proj_weight", "self_attn.in_proj_bias", "self_attn.out_proj.weight", "self_attn.out_proj.bias",
+              "linear1.weight", "linear1.bias", "linear2.weight", "linear2.bias", "norm1.weight", "norm1.bias", "norm2.weight",
+              "norm2.bias")
+
+
+def _ptr_array(tensors):
+    import ctypes as C
+    return (C.c_void_p * len(tensors))(*[t.data_ptr() for t in tensors])
+
+
+def encoder_layer_fwd_train(W, x: torch.Tensor, mask, drop_p: float, seeds):
+    """One nn.TransformerEncoderLayer forward in train() mode, one C call.  W: the 12 parameter tensors in ``LAYER_KEYS`` order;
+    x [B,S,128] contiguous.  -> (out [B,S,128], (qkv, att, y, x1, h, y2)) — the activations the backward reads."""
+    import ctypes as C
+    _chk(x, torch.float32, "x")
+    assert x.is_contiguous() and x.dim() == 3 and x.shape[2] == 128 and len(W) == 12
+    B, S, E = x.shape
+    F_ = W[4].shape[0]
+    M, dev = B * S, x.device
+    qkv = torch.empty(B, S, 3 * E, device=dev, dtype=torch.float32)
+    att, y, x1, y2, out = (torch.empty(M, E, device=dev, dtype=torch.float32) for _ in range(5))
+    h = torch.empty(M, F_, device=dev, dtype=torch.float32)
+    ws = _workspace(_lib.lib().ocv_encoder_layer_fwd_train_workspace(B, S, F_), dev, "layer_fwd")
+    sd = (C.c_ulonglong * 4)(*[int(v) for v in seeds]) if drop_p > 0 else None
+    _call("ocv_encoder_layer_fwd_train_f32", _ptr_array(W), x.data_ptr(), _ptr(mask), B, S, F_, float(drop_p), sd, qkv.data_ptr(),
+          att.data_ptr(), y.data_ptr(), x1.data_ptr(), h.data_ptr(), y2.data_ptr(), out.data_ptr(), ws.data_ptr(), _stream(),
+          launches=13 if drop_p > 0 else 9)
+    return out.view(B, S, E), (qkv, att.view(B, S, E), y, x1, h, y2)
+
+
+def encoder_layer_bwd_train(W, G, x, qkv, att, y, x1, h, y2, mask, dout: torch.Tensor, drop_p: float, seeds, side_stream=None):
+    """Explicit backward of the same layer, one C call: -> dx [B,S,128]; parameter gradients are ACCUMULATED into the 12 tensors
+    of ``G``, the weight / bias gradient GEMMs on ``side_stream`` (a torch stream; the caller joins it before reading G)."""
+    import ctypes as C
+    _chk(dout, torch.float32, "dout")
+    B, S, E3 = qkv.shape
+    E = E3 // 3
+    F_ = W[4].shape[0]
+    dev = dout.device
+    d = dout.reshape(B * S, E)
+    assert d.is_contiguous() and x.is_contiguous()
+    dx = torch.empty(B * S, E, device=dev, dtype=torch.float32)
+    ws = torch.empty(_lib.lib().ocv_encoder_layer_bwd_train_workspace(B, S, F_), device=dev, dtype=torch.uint8)
+    sd = (C.c_ulonglong * 4)(*[int(v) for v in seeds]) if drop_p > 0 else None
+    _call("ocv_encoder_layer_bwd_train_f32", _ptr_array(W), _ptr_array(G), x.data_ptr(), qkv.data_ptr(), att.data_ptr(), y.data_ptr(),
+          x1.data_ptr(), h.data_ptr(), y2.data_ptr(), _ptr(mask), d.data_ptr(), dx.data_ptr(), B, S, F_, float(drop_p), sd,
+          ws.data_ptr(), _stream(), None if side_stream is None else side_stream.cuda_stream, launches=32 if drop_p > 0 else 29)
+    if side_stream is not None:
+        for t in (ws, x, att, x1, h):
+            t.record_stream(side_stream)
+    return dx.view(B, S, E)
