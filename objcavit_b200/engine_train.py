@@ -63,7 +63,10 @@ _side_streams = {}
 
 
 def _side(device) -> "torch.cuda.Stream":
-    key = torch.device(device).index or 0
+    """The weight-gradient stream that belongs to the CURRENT launching stream (the object branch below has its own, so the two
+    branches do not serialise on one queue)."""
+    idx = torch.device(device).index or 0
+    key = (idx, torch._C._cuda_getCurrentRawStream(idx))
     if key not in _side_streams:
         _side_streams[key] = torch.cuda.Stream(device)
     return _side_streams[key]
@@ -83,8 +86,78 @@ def on_side(fn, *tensors):
 
 
 def join_side(device) -> None:
-    if ASYNC_WGRAD and (torch.device(device).index or 0) in _side_streams:
-        torch.cuda.current_stream(device).wait_stream(_side(device))
+    """The current stream waits for every weight-gradient stream of the device."""
+    if not ASYNC_WGRAD:
+        return
+    idx = torch.device(device).index or 0
+    cur = torch.cuda.current_stream(device)
+    for (i, _), s in _side_streams.items():
+        if i == idx:
+            cur.wait_stream(s)
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# Object-branch stream.  Inside SelfAttnCrossAttn the object encoder (B x N_max rows: a few CTAs per kernel) and the image encoder
+# (B x S rows) are independent until the cross attention, and both are chains of latency-bound launches; the object chain runs on
+# its own stream next to the image chain, forward and backward.  `fork_branch` marks the point the branch starts from,
+# `on_branch` runs a region there, `join_branch` orders the launching stream after it.  No kernel changes: bit-identical.
+# ----------------------------------------------------------------------------------------------------------------------
+import os as _os
+BRANCH_OBJECTS = int(_os.environ.get("OCV_BRANCH", "3"))   # bit 0: forward, bit 1: backward
+_branch_streams = {}
+
+
+def _branch(device) -> "torch.cuda.Stream":
+    idx = torch.device(device).index or 0
+    if idx not in _branch_streams:
+        _branch_streams[idx] = torch.cuda.Stream(device)
+    return _branch_streams[idx]
+
+
+def fork_branch(device, bit: int = 1):
+    """-> token marking "everything issued so far on the current stream" (None when branching is off)."""
+    if not (BRANCH_OBJECTS & bit):
+        return None
+    ev = torch.cuda.Event()
+    ev.record(torch.cuda.current_stream(device))
+    return ev
+
+
+class on_branch:
+    """``with on_branch(dev, fork, *inputs):`` — launches inside go to the object-branch stream, ordered after ``fork``;
+    ``inputs`` are the tensors of other streams the region reads."""
+
+    def __init__(self, device, fork, *inputs):
+        self.device, self.fork, self.inputs, self.ctx = device, fork, inputs, None
+
+    def __enter__(self):
+        if self.fork is None:
+            return self
+        br = _branch(self.device)
+        br.wait_event(self.fork)
+        self.ctx = torch.cuda.stream(br)
+        self.ctx.__enter__()
+        return self
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
+            br = _branch(self.device)
+            for t in self.inputs:
+                if t is not None:
+                    t.record_stream(br)
+        return False
+
+
+def join_branch(device, fork, *outputs) -> None:
+    """The current stream waits for the branch; ``outputs`` = tensors made there that the current stream reads from now on."""
+    if fork is None:
+        return
+    cur = torch.cuda.current_stream(device)
+    cur.wait_stream(_branch(device))
+    for t in outputs:
+        if t is not None:
+            t.record_stream(cur)
 
 
 def _wgrad(dy, x, gw, gb) -> None:
@@ -266,27 +339,33 @@ def cross_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor, acc_q, 
 
 def saca_fwd(P: Params, pre: str, img_tok: torch.Tensor, objs, no_obj_sa: bool, need_object_output: bool, drop: DropCtx = NO_DROP):
     B, S, _ = img_tok.shape
-    att_img, sv_img = encoder_fwd(P, pre + "image_transformer_encoder.", img_tok, drop=drop)
-    sv_obj = None
+    dev = img_tok.device
     if isinstance(objs, ObjectBatch):
         n_max = objs.n_max
         if n_max > S:
             raise ValueError("more objects than image tokens: the reference's F.pad would crop; unsupported")
-        padded, mask = ops.pad_objects(objs.rows, objs.offsets, B, n_max, n_max, 0.0001, False)            # :180-183
-        att_obj = padded
-        if not no_obj_sa:
-            att_obj, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", padded, mask, drop=drop)   # :188 (slow path)
-        uni = objs.uniform_offsets(n_max)
-        att_obj_s, kpm = ops.pad_objects(att_obj.reshape(B * n_max, E), uni, B, S, n_max, 0.0001, True,
-                                         mask_offsets=objs.offsets)                                         # :192-194 (F5)
+        uni = objs.uniform_offsets(n_max)            # made on the launching stream BEFORE the fork: the branch reads it
+    fork = fork_branch(dev)
+    att_img, sv_img = encoder_fwd(P, pre + "image_transformer_encoder.", img_tok, drop=drop)
+    sv_obj = None
+    if isinstance(objs, ObjectBatch):
+        with on_branch(dev, fork, objs.rows, objs.offsets, uni):
+            padded, mask = ops.pad_objects(objs.rows, objs.offsets, B, n_max, n_max, 0.0001, False)        # :180-183
+            att_obj = padded
+            if not no_obj_sa:
+                att_obj, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", padded, mask, drop=drop)   # :188 (slow path)
+            att_obj_s, kpm = ops.pad_objects(att_obj.reshape(B * n_max, E), uni, B, S, n_max, 0.0001, True,
+                                             mask_offsets=objs.offsets)                                     # :192-194 (F5)
         geom = ("ragged", objs, uni, n_max)
     else:
         assert objs.shape == (B, S, E)
-        att_obj_s = objs.contiguous()
-        if not no_obj_sa:
-            att_obj_s, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", att_obj_s, drop=drop)
+        with on_branch(dev, fork, objs):
+            att_obj_s = objs.contiguous()
+            if not no_obj_sa:
+                att_obj_s, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", att_obj_s, drop=drop)
         kpm = None
         geom = ("dense",)
+    join_branch(dev, fork, att_obj_s, kpm)
     final_img, sv_c1 = cross_fwd(P, pre + "cross_attn_obj_im.", att_img, att_obj_s, att_img, kpm)          # :195-201
     final_obj, sv_c2 = None, None
     if need_object_output:
@@ -303,17 +382,20 @@ def saca_bwd(P: Params, G: Params, pre: str, saved, d_final_img: torch.Tensor, d
     cross_bwd(P, G, pre + "cross_attn_obj_im.", sv_c1, d_final_img, (d_att_img, 0.0), (d_att_obj_s, 0.0), (d_att_img, 1.0))
     if sv_c2 is not None and d_final_obj is not None:
         cross_bwd(P, G, pre + "cross_attn_im_obj.", sv_c2, d_final_obj, (d_att_obj_s, 1.0), (d_att_img, 1.0), (d_att_obj_s, 1.0))
+    fork = fork_branch(dev, 2)
     d_img_tok = encoder_bwd(P, G, pre + "image_transformer_encoder.", sv_img, d_att_img)
-    if geom[0] == "ragged":
-        _, objs, uni, n_max = geom
-        d_att_obj = ops.unpad_objects(d_att_obj_s, uni, B * n_max, n_max, True).view(B, n_max, E)
-        if sv_obj is not None:
-            d_att_obj = encoder_bwd(P, G, pre + "obj_transformer_encoder.", sv_obj, d_att_obj)
-        d_objs = ops.unpad_objects(d_att_obj.contiguous(), objs.offsets, objs.offsets_host[-1], n_max, False)
-    else:
-        d_objs = d_att_obj_s
-        if sv_obj is not None:
-            d_objs = encoder_bwd(P, G, pre + "obj_transformer_encoder.", sv_obj, d_att_obj_s)
+    with on_branch(dev, fork, d_att_obj_s):
+        if geom[0] == "ragged":
+            _, objs, uni, n_max = geom
+            d_att_obj = ops.unpad_objects(d_att_obj_s, uni, B * n_max, n_max, True).view(B, n_max, E)
+            if sv_obj is not None:
+                d_att_obj = encoder_bwd(P, G, pre + "obj_transformer_encoder.", sv_obj, d_att_obj)
+            d_objs = ops.unpad_objects(d_att_obj.contiguous(), objs.offsets, objs.offsets_host[-1], n_max, False)
+        else:
+            d_objs = d_att_obj_s
+            if sv_obj is not None:
+                d_objs = encoder_bwd(P, G, pre + "obj_transformer_encoder.", sv_obj, d_att_obj_s)
+    join_branch(dev, fork, d_objs)
     return d_img_tok, d_objs
 
 
