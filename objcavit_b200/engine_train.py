@@ -62,22 +62,22 @@ ASYNC_WGRAD = True
 _side_streams = {}
 
 
-def _side(device) -> "torch.cuda.Stream":
+def _side(device, name: str = "") -> "torch.cuda.Stream":
     """The weight-gradient stream that belongs to the CURRENT launching stream (the object branch below has its own, so the two
-    branches do not serialise on one queue)."""
+    branches do not serialise on one queue); ``name`` selects a further queue of the same launching stream."""
     idx = torch.device(device).index or 0
-    key = (idx, torch._C._cuda_getCurrentRawStream(idx))
+    key = (idx, torch._C._cuda_getCurrentRawStream(idx), name)
     if key not in _side_streams:
         _side_streams[key] = torch.cuda.Stream(device)
     return _side_streams[key]
 
 
-def on_side(fn, *tensors):
+def on_side(fn, *tensors, name: str = ""):
     """Run ``fn()`` (kernel launches only) on the weight-gradient stream after everything issued so far; ``tensors`` = what it reads."""
     if not ASYNC_WGRAD:
         return fn()
     dev = tensors[0].device
-    side = _side(dev)
+    side = _side(dev, name)
     side.wait_stream(torch.cuda.current_stream(dev))
     with torch.cuda.stream(side):
         fn()
@@ -91,7 +91,7 @@ def join_side(device) -> None:
         return
     idx = torch.device(device).index or 0
     cur = torch.cuda.current_stream(device)
-    for (i, _), s in _side_streams.items():
+    for (i, _, _), s in _side_streams.items():
         if i == idx:
             cur.wait_stream(s)
 
@@ -103,15 +103,15 @@ def join_side(device) -> None:
 # `on_branch` runs a region there, `join_branch` orders the launching stream after it.  No kernel changes: bit-identical.
 # ----------------------------------------------------------------------------------------------------------------------
 import os as _os
-BRANCH_OBJECTS = int(_os.environ.get("OCV_BRANCH", "3"))   # bit 0: forward, bit 1: backward
+BRANCH_OBJECTS = int(_os.environ.get("OCV_BRANCH", "7"))   # bit 0: object branch forward, bit 1: backward, bit 2: conv3x3 forward
 _branch_streams = {}
 
 
-def _branch(device) -> "torch.cuda.Stream":
-    idx = torch.device(device).index or 0
-    if idx not in _branch_streams:
-        _branch_streams[idx] = torch.cuda.Stream(device)
-    return _branch_streams[idx]
+def _branch(device, name: str = "objects") -> "torch.cuda.Stream":
+    key = (torch.device(device).index or 0, name)
+    if key not in _branch_streams:
+        _branch_streams[key] = torch.cuda.Stream(device)
+    return _branch_streams[key]
 
 
 def fork_branch(device, bit: int = 1):
@@ -127,13 +127,13 @@ class on_branch:
     """``with on_branch(dev, fork, *inputs):`` — launches inside go to the object-branch stream, ordered after ``fork``;
     ``inputs`` are the tensors of other streams the region reads."""
 
-    def __init__(self, device, fork, *inputs):
-        self.device, self.fork, self.inputs, self.ctx = device, fork, inputs, None
+    def __init__(self, device, fork, *inputs, name: str = "objects"):
+        self.device, self.fork, self.inputs, self.ctx, self.name = device, fork, inputs, None, name
 
     def __enter__(self):
         if self.fork is None:
             return self
-        br = _branch(self.device)
+        br = _branch(self.device, self.name)
         br.wait_event(self.fork)
         self.ctx = torch.cuda.stream(br)
         self.ctx.__enter__()
@@ -142,19 +142,19 @@ class on_branch:
     def __exit__(self, *exc):
         if self.ctx is not None:
             self.ctx.__exit__(*exc)
-            br = _branch(self.device)
+            br = _branch(self.device, self.name)
             for t in self.inputs:
                 if t is not None:
                     t.record_stream(br)
         return False
 
 
-def join_branch(device, fork, *outputs) -> None:
+def join_branch(device, fork, *outputs, name: str = "objects") -> None:
     """The current stream waits for the branch; ``outputs`` = tensors made there that the current stream reads from now on."""
     if fork is None:
         return
     cur = torch.cuda.current_stream(device)
-    cur.wait_stream(_branch(device))
+    cur.wait_stream(_branch(device, name))
     for t in outputs:
         if t is not None:
             t.record_stream(cur)
@@ -420,6 +420,7 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
         pt = pre + "patch_transformer."
         tok0 = _patch_embed(t, x, P[pt + "embedding_convPxP.weight"], P[pt + "embedding_convPxP.bias"],
                             P[pt + "positional_encodings"], patch_size)
+        _conv3x3_branch(P, pre, t)
         tok, t.sv_enc = encoder_fwd(P, pt + "transformer_encoder.", tok0, drop=drop)
     else:
         pre = "objcavit."
@@ -442,6 +443,7 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
                 object_features[i] = obj_tok[batch.offsets_host[i]:batch.offsets_host[i + 1]]
         tok0 = _patch_embed(t, x, P[pre + "image_embedding_convPxP.weight"], P[pre + "image_embedding_convPxP.bias"],
                             img_pos.contiguous(), patch_size)
+        _conv3x3_branch(P, pre, t)
         two = bool(cfg.get("use_2_saca"))
         tok, obj_out, t.sv_saca1 = saca_fwd(P, pre + "saca_1.", tok0, batch, bool(cfg.get("no_obj_sa")), two, drop)
         if two:
@@ -480,8 +482,20 @@ def _patch_embed(t, x: torch.Tensor, w: torch.Tensor, bias, pos, patch_size: int
     kernel on the NHWC bf16 copy of the features (kept on the tape for the conv3x3 kernel)."""
     if t.cfg.get("pixel") == "bf16":
         t.xh = ops.nchw_to_nhwc_bf16(x)
+        t.conv_fork = fork_branch(x.device, 4)       # the conv3x3 of the pixel path needs only x: next to the whole token path
         return ops.patch_embed_bf16(t.xh, ops.pack_patch_weights_bf16(w), bias, pos, patch_size, want32=True, want16=False)[0]
     return ops.patch_embed(x, w, bias, pos, patch_size)
+
+
+def _conv3x3_branch(P: Params, pre: str, t) -> None:
+    """conv3x3 of the tensor-core pixel path -> ``t.x3h`` (NHWC bf16), launched on the "pixel" branch stream from the fork taken in
+    ``_patch_embed``; ``_pixel_fwd_bf16`` joins it.  (Branching off: same launches on the current stream.)"""
+    if t.cfg.get("pixel") != "bf16":
+        return
+    dev = t.xh.device
+    with on_branch(dev, t.conv_fork, t.xh, name="pixel"):
+        t.x3h = ops.conv3x3_nhwc_bf16(t.xh, ops.pack_conv3x3_bf16(P[pre + "conv3x3.weight"]), P[pre + "conv3x3.bias"])
+    t.xh = None
 
 
 def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, Q: int) -> torch.Tensor:
@@ -489,8 +503,7 @@ def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, 
     Pn, S = h * w, tok.shape[1]
     Wout = P["conv_out.0.weight"].view(-1, Q)
     K = Wout.shape[0]
-    t.x3h = ops.conv3x3_nhwc_bf16(t.xh, ops.pack_conv3x3_bf16(P[pre + "conv3x3.weight"]), P[pre + "conv3x3.bias"])
-    t.xh = None
+    join_branch(x.device, t.conv_fork, t.x3h, name="pixel")
     Mb = torch.empty(B, K, E, device=x.device, dtype=torch.float32)
     ops.gemm_ex(Wout, tok[:, 1:Q + 1, :], K, E, Q, Q, E, Mb, E, batch=B, stride_a=0, stride_b=S * E, stride_c=K * E)
     t.Mb16 = ops.cast_bf16(Mb)
@@ -516,36 +529,37 @@ def _pixel_bwd_bf16_rest(P: Params, G: Params, t, dlT: torch.Tensor, dtok: torch
     dev = x.device
     Wout = P["conv_out.0.weight"].view(-1, Q)
     K = Wout.shape[0]
-    # d x3 (channel-major over the whole batch: the A operand of the weight-gradient GEMM)
-    dl = ops.transpose_bf16(dlT)                                              # [B,P,K]
-    MbT16 = ops.transpose_bf16(t.Mb16)                                        # [B,C,K]
-    dx3T = torch.empty(C, B * Pn, device=dev, dtype=torch.bfloat16)
-    for b in range(B):
-        ops.gemm_bf16(MbT16[b], dl[b], out=dx3T[:, b * Pn:(b + 1) * Pn])
-    del dl
-    # d Mb -> conv_out weight and queries
+    # d Mb -> conv_out weight and queries: the only part the token-path backward waits for
     x3T = ops.transpose_bf16(t.x3h.view(B, Pn, C))                            # [B,C,P]
     dMb = torch.empty(B, K, E, device=dev, dtype=torch.float32)
     sk = max(1, min(64, Pn // 1024))
     for b in range(B):
         ops.gemm_bf16(dlT[b], x3T[b], out=dMb[b], split_k=sk)
-    del x3T, dlT
+    del x3T
     queries = tok[:, 1:Q + 1, :]
     ops.gemm_ex(dMb, queries, K, Q, E, E, E, G["conv_out.0.weight"], Q, op_b=1, beta=1.0, batch=B, stride_a=K * E, stride_b=S * E,
                 reduce_batch=True)
     ops.gemm_ex(Wout, dMb, Q, E, K, Q, E, dtok[:, 1:Q + 1, :], E, trans_a=True, batch=B, stride_a=0, stride_b=K * E, stride_c=S * E)
-    # conv3x3 weight + bias: one GEMM over all pixels of the batch — nothing downstream needs it, so it runs on the
-    # weight-gradient stream next to the token-path backward
+    # d x3 (channel-major over the whole batch: the A operand of the weight-gradient GEMM), then conv3x3 weight + bias as one
+    # GEMM over all pixels of the batch — nothing downstream needs either, so the whole chain runs on the weight-gradient
+    # stream next to the token-path backward
     gw, gb = G[pre + "conv3x3.weight"].view(C, C * 9), G[pre + "conv3x3.bias"]
+    Mb16 = t.Mb16
 
     def conv_wgrad():
+        dl = ops.transpose_bf16(dlT)                                          # [B,P,K]
+        MbT16 = ops.transpose_bf16(Mb16)                                      # [B,C,K]
+        dx3T = torch.empty(C, B * Pn, device=dev, dtype=torch.bfloat16)
+        for b in range(B):
+            ops.gemm_bf16(MbT16[b], dl[b], out=dx3T[:, b * Pn:(b + 1) * Pn])
+        del dl
         col = ops.im2col3x3_bf16(ops.cast_bf16(x))
         skw = max(1, min(32, (B * Pn) // 8192))
         ops.gemm_bf16(dx3T, col[:C * 9], residual=gw, out=gw, split_k=skw)
         db = ops.gemm_bf16(dx3T, col[C * 9:], split_k=skw)                    # [C,8]: column 0 = sum over pixels, the rest 0
         ops.reduce_channels(db, gb, 1, 1, C, 8, beta=1.0)
 
-    on_side(conv_wgrad, dx3T, x)
+    on_side(conv_wgrad, dlT, Mb16, x, name="conv3x3")       # its own queue: ~1 ms of HBM-bound work the layer wgrads must not wait behind
 
 
 def backward(P: Params, G: Params, t: Tape, d_depth: torch.Tensor, d_edges: Optional[torch.Tensor]) -> None:
