@@ -222,7 +222,7 @@ def run_train(a):
     head = build_head(builtin_args(CFG_NAME), precision=tprec).to(dev).train()
     head.load_state_dict(load_weights(CFG_NAME), strict=True)
     trainer = HeadTrainer(head, lr=0.000357, weight_decay=0.1, clip_grad_norm=0.1,
-                          schedule=OneCycle(0.000357, max(W_ + 3 * K + 16, 100), 25, 100))
+                          schedule=OneCycle(0.000357, max(W_ + 3 * K + 16, 100), 25, 100), graph=bool(a.graph))
     feats = synth.make_features(B, TRAIN_H, TRAIN_W, seed=1234 + rank)
     objs, boxes = synth.make_objects(B, TRAIN_H, TRAIN_W, NOBJ, seed=1234 + rank)
     gt, mask = synth.make_gt(B, TRAIN_H, TRAIN_W, 10.0, seed=1234 + rank)
@@ -282,7 +282,9 @@ def run_train(a):
     value = world * B * K / (ms * 1e-3)
     # per-entry-point breakdown of one step (CUDA events around every C-ABI call on the launching stream)
     ops.profile_events = []
+    trainer.graph = False                            # the breakdown needs the individual calls: one eager step
     step()
+    trainer.graph = bool(a.graph)
     torch.cuda.synchronize()
     agg = {}
     for name, e0, e1 in ops.profile_events:
@@ -308,7 +310,10 @@ def run_train(a):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16" if tprec == "bf16" else "f32", "data": "synthetic",
         "config": {"workload": f"{CFG_NAME} head training step, {NOBJ} boxes/img, frozen features 128x{TRAIN_H}x{TRAIN_W} fp32, "
                                f"GT {2 * TRAIN_H}x{2 * TRAIN_W}, batch {B}/GPU, encoder dropout {head.dropout} (train() mode, as the reference)",
-                   "batch_per_gpu": B, "parallelism": f"dp{world} (batch sharded, one all-reduce of "
+                   "batch_per_gpu": B, "launch": ("zero-grads + forward + losses + backward replayed from ONE CUDA graph per step (same kernels, "
+                                                  "streams and order as the eager step; inputs copied into static buffers inside the timed region), "
+                                                  "all-reduce + clip + AdamW eager") if a.graph else "eager launches",
+                   "parallelism": f"dp{world} (batch sharded, one all-reduce of "
                                                       f"{trainer.grads.flat.numel() * 4 / 1e6:.1f} MB head gradients per step)",
                    "l2": f"activations {B * 256 * TRAIN_H * TRAIN_W * 4 / 1e6:.0f} MB logits per step > 126 MB L2, no explicit flush"},
         "gpu_launches": launches, "roofline": roofline, "clocks": clocks,
@@ -338,6 +343,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--lanes", type=int, default=2, help="pipelined serving mode of the bf16 head (0 = classic calls)")
     ap.add_argument("--pixel-ctas", type=int, default=0, help="grid cap of the fused pixel kernel in pipelined mode (0 = 148)")
+    ap.add_argument("--graph", type=int, default=1, help="--workload train: replay zero-grads + forward + losses + backward from a CUDA graph (0 = eager launches)")
     ap.add_argument("--workload", default="infer", choices=["infer", "train"],
                     help="infer = BASELINE.json configs[1] (the headline line); train = configs[4] (the training step)")
     a = ap.parse_args()

@@ -283,6 +283,10 @@ int ocv_tail_bwd_f32(float* logits_inout, float* pg_out, const float* centres, c
  *   ocv_mha_core_dropout_f32 / ocv_mha_core_bwd_dropout_f32: the attention core with dropout on the probabilities, mask index =
  *   flat index into [B, heads, Sq, Sk] (so ocv_dropout_f32 on a tensor of ones of that shape reproduces the mask: tests). */
 int ocv_dropout_f32(const float* x, const float* residual, float* out, long long n, float p, unsigned long long seed, void* stream);
+/* Per-step salt of every dropout mask: `device_salt` points at ONE 64-bit word in device memory (or NULL = none, the default);
+ * each dropout kernel uses seed ^ *device_salt.  It exists for CUDA-graph replay of the training step, where the site seeds are
+ * frozen kernel arguments: the caller changes the word between replays.  Process-wide (one process per GPU). */
+int ocv_set_dropout_salt(const unsigned long long* device_salt);
 int ocv_mha_core_dropout_f32(const float* q, const float* k, const float* v, float* out, const uint8_t* key_padding_mask,
                              int B, int Sq, int Sk, int heads, int d, long long q_bstride, int q_rstride, long long k_bstride,
                              int k_rstride, long long v_bstride, int v_rstride, long long o_bstride, int o_rstride, float drop_p,

@@ -24,6 +24,13 @@ bool ocv_pdl_enabled() {
   return cached == 1;
 }
 
+static const unsigned long long* g_dropout_salt = nullptr;
+const unsigned long long* ocv_dropout_salt() { return g_dropout_salt; }
+extern "C" int ocv_set_dropout_salt(const unsigned long long* device_salt) {
+  g_dropout_salt = device_salt;
+  return OCV_OK;
+}
+
 extern "C" int ocv_abi_version(void) { return 1; }
 
 extern "C" int ocv_device_check(int device) {

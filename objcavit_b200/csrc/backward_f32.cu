@@ -183,7 +183,9 @@ __global__ void __launch_bounds__(AR * ASL)
 mha_bwd_q_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v, const float* __restrict__ o,
                  const float* __restrict__ dout, const uint8_t* __restrict__ mask, float* __restrict__ dq, float* __restrict__ stats,
                  int Sq, int Sk, int heads, long long q_bs, int q_rs, long long k_bs, int k_rs, long long v_bs, int v_rs,
-                 long long o_bs, int o_rs, long long dq_bs, int dq_rs, float drop_p, unsigned long long drop_seed) {
+                 long long o_bs, int o_rs, long long dq_bs, int dq_rs, float drop_p, unsigned long long drop_seed_in,
+                 const unsigned long long* drop_salt) {
+  const unsigned long long drop_seed = ocv_salted(drop_seed_in, drop_salt);
   __shared__ float Ks[AJ][APAD], Vs[AJ][APAD];
   __shared__ uint8_t Ms[AJ];
   const int b = blockIdx.z, hd = blockIdx.y;
@@ -281,7 +283,9 @@ mha_bwd_kv_kernel(const float* __restrict__ q, const float* __restrict__ k, cons
                   const float* __restrict__ dout, const uint8_t* __restrict__ mask, const float* __restrict__ stats,
                   float* __restrict__ dk, float* __restrict__ dv, int Sq, int Sk, int heads, long long q_bs, int q_rs,
                   long long k_bs, int k_rs, long long v_bs, int v_rs, long long o_bs, int o_rs, long long dk_bs, int dk_rs,
-                  long long dv_bs, int dv_rs, float drop_p, unsigned long long drop_seed) {
+                  long long dv_bs, int dv_rs, float drop_p, unsigned long long drop_seed_in,
+                  const unsigned long long* drop_salt) {
+  const unsigned long long drop_seed = ocv_salted(drop_seed_in, drop_salt);
   __shared__ float Qs[AJ][APAD], Ds[AJ][APAD];
   __shared__ float St[AJ][3];
   const int b = blockIdx.z, hd = blockIdx.y;
@@ -423,7 +427,8 @@ __global__ void bins_bwd_kernel(const float* __restrict__ y_raw, const float* __
 
 // ---- elementwise dropout (+ optional residual): out = residual + (keep ? x / (1-p) : 0); the same call on a gradient is its backward
 __global__ void dropout_kernel(const float* __restrict__ x, const float* __restrict__ residual, float* __restrict__ out, long long n,
-                               uint32_t thr, float scale, unsigned long long seed) {
+                               uint32_t thr, float scale, unsigned long long seed_in, const unsigned long long* salt) {
+  const unsigned long long seed = ocv_salted(seed_in, salt);
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const float v = ocv_drop_keep(seed, (unsigned long long)i, thr) ? x[i] * scale : 0.f;
@@ -449,7 +454,7 @@ extern "C" int ocv_dropout_f32(const float* x, const float* residual, float* out
   OCV_CHECK_ARG(x && out && n > 0 && p >= 0.f && p < 1.f);
   if (int s = ocv_require_sm100()) return s;
   dropout_kernel<<<(unsigned)ceil_div<long long>(n, 256), 256, 0, ocv_stream(stream)>>>(x, residual, out, n, ocv_drop_threshold(p),
-                                                                                       1.f / (1.f - p), seed);
+                                                                                       1.f / (1.f - p), seed, ocv_dropout_salt());
   return ocv_launch_status();
 }
 
@@ -523,11 +528,11 @@ extern "C" int ocv_mha_core_bwd_dropout_f32(const float* q, const float* k, cons
   float* stats = static_cast<float*>(workspace);
   mha_bwd_q_kernel<<<dim3(ceil_div(Sq, AR), heads, B), AR * ASL, 0, ocv_stream(stream)>>>(
       q, k, v, out, dout, key_padding_mask, dq, stats, Sq, Sk, heads, q_bstride, q_rstride, k_bstride, k_rstride, v_bstride,
-      v_rstride, o_bstride, o_rstride, dq_bstride, dq_rstride, drop_p, drop_seed);
+      v_rstride, o_bstride, o_rstride, dq_bstride, dq_rstride, drop_p, drop_seed, ocv_dropout_salt());
   if (int s = ocv_launch_status()) return s;
   mha_bwd_kv_kernel<<<dim3(ceil_div(Sk, AR), heads, B), AR * ASL, 0, ocv_stream(stream)>>>(
       q, k, v, dout, key_padding_mask, stats, dk, dv, Sq, Sk, heads, q_bstride, q_rstride, k_bstride, k_rstride, v_bstride,
-      v_rstride, o_bstride, o_rstride, dk_bstride, dk_rstride, dv_bstride, dv_rstride, drop_p, drop_seed);
+      v_rstride, o_bstride, o_rstride, dk_bstride, dk_rstride, dv_bstride, dv_rstride, drop_p, drop_seed, ocv_dropout_salt());
   return ocv_launch_status();
 }
 

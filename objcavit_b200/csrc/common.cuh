@@ -54,6 +54,14 @@ __device__ __forceinline__ bool ocv_drop_keep(unsigned long long seed, unsigned 
   return (uint32_t)(z >> 32) >= thresh;
 }
 
+// Per-step salt of the dropout masks, read from DEVICE memory by every dropout kernel (nullptr = none: seeds are used as passed).
+// A CUDA-graph replay of the training step freezes the seeds (kernel arguments); the salt is what changes between replays.
+// Set with ocv_set_dropout_salt (csrc/api.cu); the effective seed is seed ^ *salt.
+const unsigned long long* ocv_dropout_salt();
+__device__ __forceinline__ unsigned long long ocv_salted(unsigned long long seed, const unsigned long long* salt) {
+  return salt ? (seed ^ __ldg(salt)) : seed;
+}
+
 // ---- programmatic dependent launch (PDL) ---------------------------------------------------------------------------
 // The head is a chain of ~50 short dependent kernels: launch latency and each kernel's prologue (barrier init, TMEM
 // allocation, tensor-map fetch, weight tiles, bias vectors) would otherwise sit on the critical path.  Every kernel of

@@ -50,7 +50,8 @@ __global__ void __launch_bounds__(ATT_WARPS * 32)
 mha_core_kernel(const float* __restrict__ q, const float* __restrict__ k, const float* __restrict__ v,
                 float* __restrict__ out, const uint8_t* __restrict__ mask, int Sq, int Sk,
                 long long q_bs, int q_rs, long long k_bs, int k_rs, long long v_bs, int v_rs, long long o_bs,
-                int o_rs, float drop_p, unsigned long long drop_seed) {
+                int o_rs, float drop_p, unsigned long long drop_seed_in, const unsigned long long* drop_salt) {
+  const unsigned long long drop_seed = ocv_salted(drop_seed_in, drop_salt);
   __shared__ float Ks[ATT_KT][33];
   __shared__ float Vs[ATT_KT][32];
   __shared__ float Msk[ATT_KT];
@@ -446,7 +447,7 @@ extern "C" int ocv_mha_core_dropout_f32(const float* q, const float* k, const fl
   dim3 grid(ceil_div(Sq, ATT_WARPS), heads, B);
   mha_core_kernel<<<grid, ATT_WARPS * 32, 0, ocv_stream(stream)>>>(q, k, v, out, key_padding_mask, Sq, Sk, q_bstride,
                                                                   q_rstride, k_bstride, k_rstride, v_bstride,
-                                                                  v_rstride, o_bstride, o_rstride, drop_p, drop_seed);
+                                                                  v_rstride, o_bstride, o_rstride, drop_p, drop_seed, ocv_dropout_salt());
   return ocv_launch_status();
 }
 

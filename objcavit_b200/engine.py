@@ -108,6 +108,9 @@ def mvit_forward(P: Params, pre: str, x: torch.Tensor, n_query: int = 128, norm:
 # a4-a6: ObjCAViT
 # ----------------------------------------------------------------------------------------------------
 
+_OFFSETS_CACHE = {}
+
+
 class ObjectBatch:
     """Ragged per-image object rows in CSR form (device offsets) — replaces the reference's python lists."""
 
@@ -123,8 +126,29 @@ class ObjectBatch:
         self.offsets = self._to_device(offs)
 
     def _to_device(self, values):
-        t = torch.tensor(values, dtype=torch.int32)
-        return t.pin_memory().to(self.rows.device, non_blocking=True) if self.rows.is_cuda else t
+        """int32 device copy of a small host list.  Cached per (device, values): batches with the same object counts reuse the
+        tensor (never written by any kernel), so a steady-state step issues no host->device copy here — which is also what lets
+        the training step be captured into a CUDA graph (a copy out of a transient pinned buffer must not be replayed)."""
+        if not self.rows.is_cuda:
+            return torch.tensor(values, dtype=torch.int32)
+        dev = self.rows.device
+        key = (dev.index, tuple(values))
+        hit = _OFFSETS_CACHE.get(key)
+        if hit is not None:
+            t, ev = hit
+            if ev is not None:
+                if ev.query():
+                    _OFFSETS_CACHE[key] = (t, None)
+                else:
+                    torch.cuda.current_stream(dev).wait_event(ev)
+            return t
+        if len(_OFFSETS_CACHE) >= 512:
+            _OFFSETS_CACHE.clear()
+        t = torch.tensor(values, dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record(torch.cuda.current_stream(dev))
+        _OFFSETS_CACHE[key] = (t, ev)
+        return t
 
     def uniform_offsets(self, n_max: int) -> torch.Tensor:
         """CSR offsets of the dense [B, n_max] padded layout (every image n_max rows)."""

@@ -60,6 +60,8 @@ class Touched(dict):
 # ----------------------------------------------------------------------------------------------------------------------
 ASYNC_WGRAD = True
 _side_streams = {}
+_side_dirty = set()      # keys with work issued since the last join (join_side waits for these only: under CUDA-graph capture a
+                         # wait on a stream that is not part of the capture is illegal)
 
 
 def _side(device, name: str = "") -> "torch.cuda.Stream":
@@ -69,6 +71,7 @@ def _side(device, name: str = "") -> "torch.cuda.Stream":
     key = (idx, torch._C._cuda_getCurrentRawStream(idx), name)
     if key not in _side_streams:
         _side_streams[key] = torch.cuda.Stream(device)
+    _side_dirty.add(key)
     return _side_streams[key]
 
 
@@ -91,9 +94,9 @@ def join_side(device) -> None:
         return
     idx = torch.device(device).index or 0
     cur = torch.cuda.current_stream(device)
-    for (i, _, _), s in _side_streams.items():
-        if i == idx:
-            cur.wait_stream(s)
+    for key in [k for k in _side_dirty if k[0] == idx]:
+        cur.wait_stream(_side_streams[key])
+        _side_dirty.discard(key)
 
 
 # ----------------------------------------------------------------------------------------------------------------------

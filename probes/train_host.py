@@ -30,6 +30,17 @@ t1 = time.perf_counter()
 torch.cuda.synchronize()
 t2 = time.perf_counter()
 print(f"{prec} async_wgrad={et.ASYNC_WGRAD}: host issue {1e3 * (t1 - t0) / K:.2f} ms/step, total {1e3 * (t2 - t0) / K:.2f} ms/step")
+# host issue time of ONE step with the GPU held busy by a spin kernel (the host never waits for a full launch queue: one step is
+# ~560 launches), i.e. the time below which the step cannot go however fast the kernels are
+ts = []
+for _ in range(10):
+    torch.cuda._sleep(int(40e-3 * 1.9e9))
+    t0 = time.perf_counter()
+    tr.step(x, list(objs), list(boxes), gt, mask)
+    ts.append(time.perf_counter() - t0)
+    torch.cuda.synchronize()
+ts.sort()
+print(f"host issue of one step behind a busy GPU: median {1e3 * ts[len(ts) // 2]:.2f} ms, min {1e3 * ts[0]:.2f} ms")
 import cProfile, pstats
 pr = cProfile.Profile(); pr.enable()
 for _ in range(5):

@@ -146,3 +146,58 @@ def test_fullsize_bf16_pixel_path_loss_matches_fp32_path(cuda):
     assert abs(a[0] - b[0]) < 2e-2 * abs(a[0]) and abs(a[1] - b[1]) < 2e-2 * abs(a[1])
     assert rel_err(b[2], a[2]) < 2e-2                                   # north_star: bf16 path within 2e-2 relative
     assert abs(a[3] - b[3]) < 5e-2 * a[3]                               # size of the whole gradient
+
+
+@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+def test_graph_replay_of_the_step_is_bit_identical_to_eager_steps(cuda, precision):
+    """``HeadTrainer(graph=True)`` captures zero-grads + forward + losses + backward into a CUDA graph after two eager steps and
+    replays it: same kernels in the same order on the same streams, so with dropout off the parameters after six steps (two
+    eager, four replayed, fresh inputs copied into the static buffers each step) equal the eager trainer's bit for bit."""
+    args = builtin_args("nyu_ocv_learned_bbox_wh")
+    with open(os.path.join(GOLD, "manifest_nyu_ocv_learned_bbox_wh.json")) as f:
+        sd = synth.make_state_dict(json.load(f), seed=5)
+    batches = [_fullsize_inputs(cuda, seed=3), _fullsize_inputs(cuda, seed=4)]
+    runs = []
+    for graph in (False, True):
+        head = build_head(args, precision=precision).to(cuda).train()
+        head.dropout = 0.0
+        head.load_state_dict(sd)
+        tr = HeadTrainer(head, lr=3.57e-4, weight_decay=0.1, clip_grad_norm=0.1, graph=graph)
+        losses = []
+        for i in range(6):
+            x, objs, boxes, gt, mask = batches[i % 2]
+            l1, l2 = tr.step(x, list(objs), list(boxes), gt, mask)
+            losses.append(tr.loss_value(l1, l2))
+        runs.append((losses, tr.flat_params.clone(), tr.last_outputs[0].clone()))
+        if graph:
+            assert len(tr._graphs) == 1
+            tr.enable_graph(False)
+    assert runs[0][0] == runs[1][0], (runs[0][0], runs[1][0])
+    assert torch.equal(runs[0][1], runs[1][1]) and torch.equal(runs[0][2], runs[1][2])
+
+
+def test_graph_replay_draws_new_dropout_masks_every_step_and_is_reproducible(cuda):
+    """Dropout on: the site seeds are frozen into the graph, the device-side salt is what changes — replaying the SAME batch with
+    the learning rate at 0 must give different losses from step to step (new masks), two runs from the same torch seed must agree
+    bit for bit, and the loss must stay close to the eager trainer's (same distribution of masks)."""
+    args = builtin_args("nyu_ocv_learned_bbox_wh")
+    with open(os.path.join(GOLD, "manifest_nyu_ocv_learned_bbox_wh.json")) as f:
+        sd = synth.make_state_dict(json.load(f), seed=5)
+    x, objs, boxes, gt, mask = _fullsize_inputs(cuda)
+    runs = []
+    for graph in (True, True, False):
+        head = build_head(args, precision="bf16").to(cuda).train()
+        head.load_state_dict(sd)
+        torch.manual_seed(77)
+        tr = HeadTrainer(head, lr=0.0, weight_decay=0.0, clip_grad_norm=0.1, graph=graph)
+        losses = []
+        for _ in range(6):
+            l1, l2 = tr.step(x, list(objs), list(boxes), gt, mask)
+            losses.append(tr.loss_value(l1, l2))
+        runs.append(losses)
+        if graph:
+            tr.enable_graph(False)
+    assert runs[0] == runs[1]                                             # reproducible
+    assert len(set(runs[0][2:])) == 4, runs[0]                            # replays: a new mask stream every step
+    mean = lambda v: sum(v) / len(v)
+    assert abs(mean(runs[0]) - mean(runs[2])) < 0.05 * abs(mean(runs[2])), (runs[0], runs[2])
