@@ -347,6 +347,9 @@ def main():
     ap.add_argument("--workload", default="infer", choices=["infer", "train"],
                     help="infer = BASELINE.json configs[1] (the headline line); train = configs[4] (the training step)")
     a = ap.parse_args()
+    if a.impl != "reference" and int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        from objcavit_b200.sharding import bind_host_to_gpu
+        bind_host_to_gpu(int(os.environ.get("LOCAL_RANK", "0")))     # NUMA-local pinned buffers for the e2e (host-buffer) legs
     if a.impl == "reference":
         return run_reference_train(a) if a.workload == "train" else run_reference(a)
     if a.workload == "train":

@@ -88,13 +88,13 @@ def on_side(fn, *tensors, name: str = ""):
         t.record_stream(side)
 
 
-def join_side(device) -> None:
-    """The current stream waits for every weight-gradient stream of the device."""
+def join_side(device, name: Optional[str] = None) -> None:
+    """The current stream waits for every weight-gradient stream of the device (``name``: only the queues of that name)."""
     if not ASYNC_WGRAD:
         return
     idx = torch.device(device).index or 0
     cur = torch.cuda.current_stream(device)
-    for key in [k for k in _side_dirty if k[0] == idx]:
+    for key in [k for k in _side_dirty if k[0] == idx and (name is None or k[2] == name)]:
         cur.wait_stream(_side_streams[key])
         _side_dirty.discard(key)
 
@@ -106,6 +106,7 @@ def join_side(device) -> None:
 # `on_branch` runs a region there, `join_branch` orders the launching stream after it.  No kernel changes: bit-identical.
 # ----------------------------------------------------------------------------------------------------------------------
 import os as _os
+UNFOLD_IN_FORWARD = _os.environ.get("OCV_UNFOLD_FWD", "1") == "1"
 BRANCH_OBJECTS = int(_os.environ.get("OCV_BRANCH", "7"))   # bit 0: object branch forward, bit 1: backward, bit 2: conv3x3 forward
 _branch_streams = {}
 
@@ -418,15 +419,15 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
     t.cfg, t.x = cfg, x
     B, C, h, w = x.shape
     t.shape = (B, C, h, w)
+    pre = "adaptive_bins_layer." if cfg["kind"] == "adabins" else "objcavit."
+    if cfg.get("pixel") == "bf16":
+        _pixel_prologue(P, pre, t, x)
     if cfg["kind"] == "adabins":
-        pre = "adaptive_bins_layer."
         pt = pre + "patch_transformer."
         tok0 = _patch_embed(t, x, P[pt + "embedding_convPxP.weight"], P[pt + "embedding_convPxP.bias"],
                             P[pt + "positional_encodings"], patch_size)
-        _conv3x3_branch(P, pre, t)
         tok, t.sv_enc = encoder_fwd(P, pt + "transformer_encoder.", tok0, drop=drop)
     else:
-        pre = "objcavit."
         strategy = cfg["strategy"]
         feats, boxes, counts = marshal_objects(object_features, object_xywh_list, x.device)
         coords = ops.patch_coords(h // patch_size, w // patch_size, patch_size, x.device)
@@ -446,7 +447,6 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
                 object_features[i] = obj_tok[batch.offsets_host[i]:batch.offsets_host[i + 1]]
         tok0 = _patch_embed(t, x, P[pre + "image_embedding_convPxP.weight"], P[pre + "image_embedding_convPxP.bias"],
                             img_pos.contiguous(), patch_size)
-        _conv3x3_branch(P, pre, t)
         two = bool(cfg.get("use_2_saca"))
         tok, obj_out, t.sv_saca1 = saca_fwd(P, pre + "saca_1.", tok0, batch, bool(cfg.get("no_obj_sa")), two, drop)
         if two:
@@ -484,21 +484,33 @@ def _patch_embed(t, x: torch.Tensor, w: torch.Tensor, bias, pos, patch_size: int
     """Patch-embedding conv + bias + positional rows -> tokens [B,S,E] fp32.  Tensor-core pixel mode: the tcgen05 patch-embed
     kernel on the NHWC bf16 copy of the features (kept on the tape for the conv3x3 kernel)."""
     if t.cfg.get("pixel") == "bf16":
-        t.xh = ops.nchw_to_nhwc_bf16(x)
-        t.conv_fork = fork_branch(x.device, 4)       # the conv3x3 of the pixel path needs only x: next to the whole token path
-        return ops.patch_embed_bf16(t.xh, ops.pack_patch_weights_bf16(w), bias, pos, patch_size, want32=True, want16=False)[0]
+        cur = torch.cuda.current_stream(x.device)
+        if t.xh_ready is not None:                   # t.xh was made on the pixel branch (_pixel_prologue)
+            cur.wait_event(t.xh_ready)
+            t.xh.record_stream(cur)
+        tok = ops.patch_embed_bf16(t.xh, ops.pack_patch_weights_bf16(w), bias, pos, patch_size, want32=True, want16=False)[0]
+        t.xh = None
+        return tok
     return ops.patch_embed(x, w, bias, pos, patch_size)
 
 
-def _conv3x3_branch(P: Params, pre: str, t) -> None:
-    """conv3x3 of the tensor-core pixel path -> ``t.x3h`` (NHWC bf16), launched on the "pixel" branch stream from the fork taken in
-    ``_patch_embed``; ``_pixel_fwd_bf16`` joins it.  (Branching off: same launches on the current stream.)"""
-    if t.cfg.get("pixel") != "bf16":
-        return
-    dev = t.xh.device
-    with on_branch(dev, t.conv_fork, t.xh, name="pixel"):
-        t.x3h = ops.conv3x3_nhwc_bf16(t.xh, ops.pack_conv3x3_bf16(P[pre + "conv3x3.weight"]), P[pre + "conv3x3.bias"])
-    t.xh = None
+def _pixel_prologue(P: Params, pre: str, t, x: torch.Tensor) -> None:
+    """Everything of the tensor-core pixel path that needs only the features, launched on the "pixel" branch stream at the very
+    start of the forward, next to the positional MLPs and the whole token path: NCHW fp32 -> NHWC bf16 (``t.xh``, which the
+    patch embedding on the launching stream waits for through ``t.xh_ready``), then conv3x3 -> ``t.x3h``; ``_pixel_fwd_bf16`` joins
+    the branch.  (Branching off: the same launches on the current stream.)"""
+    dev = x.device
+    t.conv_fork = fork_branch(dev, 4)
+    t.xh_ready = None
+    with on_branch(dev, t.conv_fork, x, name="pixel"):
+        t.xh = xh = ops.nchw_to_nhwc_bf16(x)
+        if t.conv_fork is not None:
+            t.xh_ready = torch.cuda.Event()
+            t.xh_ready.record(torch.cuda.current_stream(dev))
+        t.x3h = ops.conv3x3_nhwc_bf16(xh, ops.pack_conv3x3_bf16(P[pre + "conv3x3.weight"]), P[pre + "conv3x3.bias"])
+        # B operand of the patch-embedding weight gradient (backward): needs only x; 0.23 ms of HBM-bound work that fits under the
+        # latency-bound encoder chain here, while anywhere in the backward it competes with the HBM-bound tail kernels
+        t.unf = ops.patch_unfold_bf16(x, 16) if UNFOLD_IN_FORWARD else None
 
 
 def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, Q: int) -> torch.Tensor:
@@ -665,7 +677,10 @@ def _token_bwd(P: Params, G: Params, t: Tape, dtok: torch.Tensor) -> None:
     dt2 = dtok0.contiguous().view(B * S, E)
     Pp = 16
     if t.pixel == "bf16":
-        ops.patch_embed_wgrad_bf16(dt2, x, G[wkey], Pp)
+        unf = getattr(t, "unf", None)        # made on the pixel branch in the forward (joined there by _pixel_fwd_bf16)
+        if unf is not None:
+            unf.record_stream(torch.cuda.current_stream(dev))
+        ops.patch_embed_wgrad_bf16(dt2, x, G[wkey], Pp, unf=unf)
     else:
         ops.gemm_ex(dt2, x, E, C * Pp * Pp, B * S, E, 0, G[wkey], C * Pp * Pp, trans_a=True, op_b=2, beta=1.0,
                     split_k=_split(E, C * Pp * Pp, 1, B * S), geom=(C, h, w, Pp))

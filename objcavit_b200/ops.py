@@ -927,8 +927,23 @@ def im2col3x3_bf16(x_planar: torch.Tensor) -> torch.Tensor:
     return col
 
 
-def patch_embed_wgrad_bf16(dtok: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, P: int = 16):
-    """dw [E, C, P, P] += dtok [B*S, E]^T @ unfold(x): the patch-embedding weight gradient as ONE tcgen05 GEMM (bf16 operands)."""
+def patch_unfold_bf16(x: torch.Tensor, P: int = 16) -> torch.Tensor:
+    """unfold(x) [C*P*P, ld] bf16 (ld = B*S rounded up to 8): the K-major B operand of the patch-embedding weight-gradient GEMM.
+    Depends on the features only, so the training step launches it off the critical path."""
+    _chk(x, torch.float32, "x")
+    assert x.is_contiguous()
+    B, Cc, h, wd = x.shape
+    BS = B * (h // P) * (wd // P)
+    ld = (BS + 7) // 8 * 8
+    alloc = torch.empty if ld == BS else torch.zeros
+    unf = alloc(Cc * P * P, ld, device=x.device, dtype=torch.bfloat16)
+    _call("ocv_patch_unfold_bf16", x.data_ptr(), unf.data_ptr(), B, Cc, h, wd, P, ld, _stream())
+    return unf
+
+
+def patch_embed_wgrad_bf16(dtok: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, P: int = 16, unf: Optional[torch.Tensor] = None):
+    """dw [E, C, P, P] += dtok [B*S, E]^T @ unfold(x): the patch-embedding weight gradient as ONE tcgen05 GEMM (bf16 operands).
+    ``unf``: a precomputed ``patch_unfold_bf16(x, P)``."""
     _chk(dtok, torch.float32, "dtok"); _chk(x, torch.float32, "x"); _chk(dw, torch.float32, "dw")
     assert dtok.is_contiguous() and x.is_contiguous() and dw.is_contiguous()
     B, Cc, h, wd = x.shape
@@ -936,8 +951,9 @@ def patch_embed_wgrad_bf16(dtok: torch.Tensor, x: torch.Tensor, dw: torch.Tensor
     assert BS == B * (h // P) * (wd // P) and dw.numel() == E * Cc * P * P
     ld = (BS + 7) // 8 * 8
     alloc = torch.empty if ld == BS else torch.zeros
-    unf = alloc(Cc * P * P, ld, device=x.device, dtype=torch.bfloat16)
-    _call("ocv_patch_unfold_bf16", x.data_ptr(), unf.data_ptr(), B, Cc, h, wd, P, ld, _stream())
+    if unf is None:
+        unf = patch_unfold_bf16(x, P)
+    assert unf.shape == (Cc * P * P, ld)
     dT = alloc(E, ld, device=x.device, dtype=torch.bfloat16)
     _call("ocv_transpose_cast_f32_bf16", dtok.data_ptr(), dT.data_ptr(), BS, E, E, ld, _stream())
     g = dw.view(E, Cc * P * P)

@@ -61,3 +61,26 @@ def gather_depth(depth: torch.Tensor, batch: int, group=None) -> Optional[torch.
     if rank != 0:
         return None
     return torch.cat([b[:hi - lo] for b, (lo, hi) in zip(bufs, sizes)], 0)
+
+
+def bind_host_to_gpu(local_rank: int) -> Optional[list]:
+    """Pin this process to the CPU cores NVML reports as local to GPU ``local_rank`` (same NUMA node / PCIe root), intersected with
+    the cores the process may use.  With one process per GPU the pinned host buffers of the host->device pipeline are then
+    first-touched on the GPU's own NUMA node, so 8 ranks do not pull their 50 GB/s each through one socket's memory controllers
+    and the inter-socket link.  Returns the core list, or None when nothing was changed (no NVML, empty intersection)."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        handle = pynvml.nvmlDeviceGetHandleByIndex(int(local_rank))
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(handle, words)
+        cores = [64 * w + b for w, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1]
+        allowed = os.sched_getaffinity(0)
+        cores = sorted(set(cores) & set(allowed))
+        if not cores or len(cores) == len(allowed):
+            return None
+        os.sched_setaffinity(0, cores)
+        return cores
+    except Exception:
+        return None
