@@ -25,6 +25,25 @@ if ROOT not in sys.path:
 
 import torch  # noqa: E402
 
+_REAL_STDOUT = None
+
+
+def capture_stdout() -> None:
+    """From here on everything libraries write to fd 1 (NCCL prints its version banner there under torchrun) goes to stderr; the
+    ONE JSON line of the contract is written to the real stdout by ``emit``."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj) -> None:
+    line = (json.dumps(obj) + "\n").encode()
+    sys.stdout.flush()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, line)
+
+
 METRIC = "ObjCAViT head depth-maps/sec @480x640"
 UNIT = "depth-maps/s"
 CFG_NAME = "nyu_ocv_learned_bbox_wh"
@@ -132,7 +151,7 @@ def run_reference(a):
             oh.head_forward(sd, cfg, feats, objs, boxes)
         dt = (time.perf_counter() - t0) / steps
     v = sample / dt
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": a.gpus, "steps": steps,
         "warmup": min(a.warmup, 2), "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -182,7 +201,7 @@ def run_reference_train(a):
     threads = os.cpu_count() or 1
     sample = 2
     v, secs = cpu_train_rate(sample, threads, repeats=max(1, min(a.steps, 3)))
-    print(json.dumps({
+    emit(({
         "impl": "reference", "metric": TRAIN_METRIC, "value": v, "unit": "images/s", "n_gpus": a.gpus, "steps": max(1, min(a.steps, 3)),
         "warmup": 1, "ms_per_step": secs * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
@@ -327,7 +346,7 @@ def run_train(a):
                                "sample": f"2 images of the same workload, best of 2 ({secs:.2f} s per pass: forward with dropout 0.1 + losses + "
                                          "backward, no optimizer), torch autograd over oracle/head.py"}
     if rank == 0:
-        print(json.dumps(out))
+        emit(out)
     if dist is not None:
         dist.destroy_process_group()
 
@@ -347,6 +366,7 @@ def main():
     ap.add_argument("--workload", default="infer", choices=["infer", "train"],
                     help="infer = BASELINE.json configs[1] (the headline line); train = configs[4] (the training step)")
     a = ap.parse_args()
+    capture_stdout()
     if a.impl != "reference" and int(os.environ.get("WORLD_SIZE", "1")) > 1:
         from objcavit_b200.sharding import bind_host_to_gpu
         bind_host_to_gpu(int(os.environ.get("LOCAL_RANK", "0")))     # NUMA-local pinned buffers for the e2e (host-buffer) legs
@@ -526,7 +546,7 @@ def main():
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                "sample": f"2 images of the same workload, best of 3 ({secs:.2f} s per pass), oracle/head.py fp32 on torch CPU"}
     if rank == 0:
-        print(json.dumps(out))
+        emit(out)
     if dist is not None:
         dist.destroy_process_group()
 

@@ -209,7 +209,7 @@ def mlp_bwd(P: Params, G: Params, pre: str, idxs, saved, dy: torch.Tensor, dx_ou
         x, y = saved[j]
         if j < len(idxs) - 1:
             dy = ops.act_bwd(dy, y, LEAKY)
-        ops.linear_wgrad(dy, x, G[f"{pre}{i}.weight"], G[f"{pre}{i}.bias"], beta=1.0)
+        _wgrad(dy, x, G[f"{pre}{i}.weight"], G[f"{pre}{i}.bias"])      # weight-gradient stream: only dgrad is on the chain
         if j > 0:
             dy = ops.linear_dgrad(dy, P[f"{pre}{i}.weight"])
         elif dx_out is not None:
@@ -327,12 +327,12 @@ def cross_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor, acc_q, 
     w = P[pre + "in_proj_weight"]
     gw, gb = G[pre + "in_proj_weight"], G[pre + "in_proj_bias"]
     d = dout.reshape(B * Sq, E)
-    ops.linear_wgrad(d, att.view(B * Sq, E), G[pre + "out_proj.weight"], G[pre + "out_proj.bias"], beta=1.0)
+    _wgrad(d, att.view(B * Sq, E), G[pre + "out_proj.weight"], G[pre + "out_proj.bias"])
     datt = ops.linear_dgrad(d, P[pre + "out_proj.weight"]).view(B, Sq, E)
     dq, dk, dv = ops.mha_core_bwd(q, k, v, att, datt, mask, HEADS)
     for dz, z_in, lo, acc, rows in ((dq, q_in, 0, acc_q, B * Sq), (dk, k_in, E, acc_k, B * Sk), (dv, v_in, 2 * E, acc_v, B * Sk)):
         dz2 = dz.view(rows, E)
-        ops.linear_wgrad(dz2, z_in.reshape(rows, E), gw[lo:lo + E], gb[lo:lo + E], beta=1.0)
+        _wgrad(dz2, z_in.reshape(rows, E), gw[lo:lo + E], gb[lo:lo + E])
         if acc is not None:
             ops.linear_dgrad(dz2, w[lo:lo + E], out=acc[0].view(rows, E), beta=acc[1])
 
@@ -434,8 +434,10 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
         pe = pre + "positional_encoder."
         if strategy in ("learned", "learned_bbox_wh"):
             nin = 4 if strategy == "learned_bbox_wh" else 2
-            obj_pos, t.sv_mlp_obj = mlp_fwd(P, pe, boxes[:, 0:nin], (0, 2, 4, 6, 8))
-            img_pos, t.sv_mlp_img = mlp_fwd(P, pe, coords[:, 0:nin], (0, 2, 4, 6, 8))
+            # ONE chain for the object rows and the patch rows (the same MLP): half the launches of two chains, forward and backward
+            t.n_obj_rows = boxes.shape[0]
+            pos, t.sv_mlp_pos = mlp_fwd(P, pe, torch.cat([boxes[:, 0:nin], coords[:, 0:nin]], 0), (0, 2, 4, 6, 8))
+            obj_pos, img_pos = pos[:t.n_obj_rows], pos[t.n_obj_rows:]
         else:                                # table look-ups (GridRandomPositionalEmbeddings): the inference kernels, boxes kept
             obj_pos, img_pos = engine_positional_embeddings(P, pe, strategy, boxes, h, w, patch_size)
             t.pos_inputs = (boxes, coords, patch_size)
@@ -665,13 +667,16 @@ def _token_bwd(P: Params, G: Params, t: Tape, dtok: torch.Tensor) -> None:
             dtok, d_obj = saca_bwd(P, G, pre + "saca_2.", t.sv_saca2, dtok, None)
         dtok0, d_obj_tok = saca_bwd(P, G, pre + "saca_1.", t.sv_saca1, dtok, d_obj)
         wkey, bkey = pre + "image_embedding_convPxP.weight", pre + "image_embedding_convPxP.bias"
-        d_img_pos = torch.empty(S, E, device=dev, dtype=torch.float32)
-        ops.reduce_channels(dtok0.contiguous(), d_img_pos, 1, B, S * E, 1)
         pe = pre + "positional_encoder."
-        ops.linear_wgrad(d_obj_tok, t.feats, G[pre + "obj_embedding_layer.weight"], G[pre + "obj_embedding_layer.bias"], beta=1.0)
-        if cfg["strategy"] in ("learned", "learned_bbox_wh"):
-            mlp_bwd(P, G, pe, (0, 2, 4, 6, 8), t.sv_mlp_img, d_img_pos)
-            mlp_bwd(P, G, pe, (0, 2, 4, 6, 8), t.sv_mlp_obj, d_obj_tok)
+        learned = cfg["strategy"] in ("learned", "learned_bbox_wh")
+        n_obj = t.n_obj_rows if learned else 0
+        d_pos = torch.empty(n_obj + S, E, device=dev, dtype=torch.float32)       # [object rows | patch rows], as the forward chain
+        d_img_pos = d_pos[n_obj:]
+        ops.reduce_channels(dtok0.contiguous(), d_img_pos, 1, B, S * E, 1)
+        _wgrad(d_obj_tok, t.feats, G[pre + "obj_embedding_layer.weight"], G[pre + "obj_embedding_layer.bias"])
+        if learned:
+            d_pos[:n_obj].copy_(d_obj_tok.reshape(n_obj, E))
+            mlp_bwd(P, G, pe, (0, 2, 4, 6, 8), t.sv_mlp_pos, d_pos)
         else:
             _table_bwd(G[pe + "positional_encodings"], cfg["strategy"], t.pos_inputs, d_obj_tok.contiguous(), d_img_pos, h, w)
     dt2 = dtok0.contiguous().view(B * S, E)
