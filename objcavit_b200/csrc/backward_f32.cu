@@ -169,10 +169,16 @@ __global__ void layernorm_bwd_params_final_kernel(const float* __restrict__ part
 // so the 32-wide dot products are register FMAs instead of warp reductions.  Four threads share a row (each takes every fourth
 // staged row) and are combined by two shuffles; blocks of 32 rows x 4 slices.  Staged rows are padded to 33 floats: the four
 // slices of a row read four different banks, the eight rows of a warp read the same address (broadcast).
-constexpr int AR = 32, ASL = 4, AJ = 64, APAD = 33;
+// (Measured and rejected: 128-bit shared loads — same time, the kernels are bound by the latency of the per-thread FMA
+// chains at 6 warps per SM; 8 rows x 16 slices per block — 4x the CTAs each staging the whole key set, 30 % slower.)
+// The staged tile is `aj` rows (dynamic shared memory, up to AJ_MAX = 256): at S = 221 the whole key / query set is ONE tile, so
+// each CTA pays the global-load latency of staging once instead of eight times (ncu: a third of the stall samples of the
+// 64-row-tile version sat on the staging stores), and the second pass of the dq kernel re-uses the resident keys.
+constexpr int AR = 32, ASL = 4, AJ_MAX = 256, APAD = 33;
 
-__device__ __forceinline__ void stage_rows(float (*dst)[APAD], const float* __restrict__ src, long long row_stride, int row0, int rows_total) {
-  for (int idx = threadIdx.x; idx < AJ * 32; idx += AR * ASL) {
+__device__ __forceinline__ void stage_rows(float (*dst)[APAD], const float* __restrict__ src, long long row_stride, int row0, int rows_total,
+                                           int aj) {
+  for (int idx = threadIdx.x; idx < aj * 32; idx += AR * ASL) {
     const int r = idx >> 5, c = idx & 31;
     dst[r][c] = row0 + r < rows_total ? src[(long long)(row0 + r) * row_stride + c] : 0.f;
   }
@@ -184,10 +190,13 @@ mha_bwd_q_kernel(const float* __restrict__ q, const float* __restrict__ k, const
                  const float* __restrict__ dout, const uint8_t* __restrict__ mask, float* __restrict__ dq, float* __restrict__ stats,
                  int Sq, int Sk, int heads, long long q_bs, int q_rs, long long k_bs, int k_rs, long long v_bs, int v_rs,
                  long long o_bs, int o_rs, long long dq_bs, int dq_rs, float drop_p, unsigned long long drop_seed_in,
-                 const unsigned long long* drop_salt) {
+                 const unsigned long long* drop_salt, int aj) {
   const unsigned long long drop_seed = ocv_salted(drop_seed_in, drop_salt);
-  __shared__ float Ks[AJ][APAD], Vs[AJ][APAD];
-  __shared__ uint8_t Ms[AJ];
+  extern __shared__ __align__(16) unsigned char att_smem[];
+  float (*Ks)[APAD] = reinterpret_cast<float (*)[APAD]>(att_smem);
+  float (*Vs)[APAD] = Ks + aj;
+  uint8_t* Ms = reinterpret_cast<uint8_t*>(Vs + aj);
+  const bool resident = Sk <= aj;       // one tile: K, V and the mask are staged once for both passes
   const int b = blockIdx.z, hd = blockIdx.y;
   const int r = threadIdx.x / ASL, t = threadIdx.x % ASL;
   const int i = blockIdx.x * AR + r;
@@ -213,12 +222,13 @@ mha_bwd_q_kernel(const float* __restrict__ q, const float* __restrict__ k, const
   const float* vb = v + b * v_bs + hd * 32;
   const uint8_t* mb = mask ? mask + (long long)b * Sk : nullptr;
   float m = -INFINITY, l = 0.f;
-  for (int j0 = 0; j0 < Sk; j0 += AJ) {
+  for (int j0 = 0; j0 < Sk; j0 += aj) {
     __syncthreads();
-    stage_rows(Ks, kb, k_rs, j0, Sk);
-    if (threadIdx.x < AJ) Ms[threadIdx.x] = (j0 + threadIdx.x >= Sk) || (mb && mb[j0 + threadIdx.x]);
+    stage_rows(Ks, kb, k_rs, j0, Sk, aj);
+    if (resident) stage_rows(Vs, vb, v_rs, j0, Sk, aj);
+    for (int x = threadIdx.x; x < aj; x += AR * ASL) Ms[x] = (j0 + x >= Sk) || (mb && mb[j0 + x]);
     __syncthreads();
-    for (int jj = t; jj < AJ; jj += ASL) {
+    for (int jj = t; jj < aj; jj += ASL) {
       if (Ms[jj]) continue;
       float s = 0.f;
 #pragma unroll
@@ -239,13 +249,15 @@ mha_bwd_q_kernel(const float* __restrict__ q, const float* __restrict__ k, const
   float acc[32];
 #pragma unroll
   for (int c = 0; c < 32; ++c) acc[c] = 0.f;
-  for (int j0 = 0; j0 < Sk; j0 += AJ) {
-    __syncthreads();
-    stage_rows(Ks, kb, k_rs, j0, Sk);
-    stage_rows(Vs, vb, v_rs, j0, Sk);
-    if (threadIdx.x < AJ) Ms[threadIdx.x] = (j0 + threadIdx.x >= Sk) || (mb && mb[j0 + threadIdx.x]);
-    __syncthreads();
-    for (int jj = t; jj < AJ; jj += ASL) {
+  for (int j0 = 0; j0 < Sk; j0 += aj) {
+    if (!resident) {
+      __syncthreads();
+      stage_rows(Ks, kb, k_rs, j0, Sk, aj);
+      stage_rows(Vs, vb, v_rs, j0, Sk, aj);
+      for (int x = threadIdx.x; x < aj; x += AR * ASL) Ms[x] = (j0 + x >= Sk) || (mb && mb[j0 + x]);
+      __syncthreads();
+    }
+    for (int jj = t; jj < aj; jj += ASL) {
       if (Ms[jj]) continue;
       float s = 0.f, dP = 0.f;
 #pragma unroll
@@ -284,10 +296,12 @@ mha_bwd_kv_kernel(const float* __restrict__ q, const float* __restrict__ k, cons
                   float* __restrict__ dk, float* __restrict__ dv, int Sq, int Sk, int heads, long long q_bs, int q_rs,
                   long long k_bs, int k_rs, long long v_bs, int v_rs, long long o_bs, int o_rs, long long dk_bs, int dk_rs,
                   long long dv_bs, int dv_rs, float drop_p, unsigned long long drop_seed_in,
-                  const unsigned long long* drop_salt) {
+                  const unsigned long long* drop_salt, int aj) {
   const unsigned long long drop_seed = ocv_salted(drop_seed_in, drop_salt);
-  __shared__ float Qs[AJ][APAD], Ds[AJ][APAD];
-  __shared__ float St[AJ][3];
+  extern __shared__ __align__(16) unsigned char att_smem[];
+  float (*Qs)[APAD] = reinterpret_cast<float (*)[APAD]>(att_smem);
+  float (*Ds)[APAD] = Qs + aj;
+  float (*St)[3] = reinterpret_cast<float (*)[3]>(Ds + aj);
   const int b = blockIdx.z, hd = blockIdx.y;
   const int r = threadIdx.x / ASL, t = threadIdx.x % ASL;
   const int j = blockIdx.x * AR + r;
@@ -311,14 +325,14 @@ mha_bwd_kv_kernel(const float* __restrict__ q, const float* __restrict__ k, cons
   const float* qb = q + b * q_bs + hd * 32;
   const float* db = dout + b * o_bs + hd * 32;
   const float* stb = stats + ((long long)b * heads + hd) * Sq * 3;
-  for (int i0 = 0; i0 < Sq; i0 += AJ) {
+  for (int i0 = 0; i0 < Sq; i0 += aj) {
     __syncthreads();
-    stage_rows(Qs, qb, q_rs, i0, Sq);
-    stage_rows(Ds, db, o_rs, i0, Sq);
-    for (int idx = threadIdx.x; idx < AJ * 3; idx += AR * ASL) St[idx / 3][idx % 3] = i0 + idx / 3 < Sq ? stb[(long long)i0 * 3 + idx] : 0.f;
+    stage_rows(Qs, qb, q_rs, i0, Sq, aj);
+    stage_rows(Ds, db, o_rs, i0, Sq, aj);
+    for (int idx = threadIdx.x; idx < aj * 3; idx += AR * ASL) St[idx / 3][idx % 3] = i0 + idx / 3 < Sq ? stb[(long long)i0 * 3 + idx] : 0.f;
     __syncthreads();
     if (!live) continue;
-    const int n = min(AJ, Sq - i0);
+    const int n = min(aj, Sq - i0);
     for (int ii = t; ii < n; ii += ASL) {
       float s = 0.f, dP = 0.f;
 #pragma unroll
@@ -526,13 +540,22 @@ extern "C" int ocv_mha_core_bwd_dropout_f32(const float* q, const float* k, cons
   OCV_CHECK_SHAPE(d == 32 && B <= 65535 && heads <= 65535);
   if (int s = ocv_require_sm100()) return s;
   float* stats = static_cast<float*>(workspace);
-  mha_bwd_q_kernel<<<dim3(ceil_div(Sq, AR), heads, B), AR * ASL, 0, ocv_stream(stream)>>>(
+  static bool smem_opt_in = false;       // tiles of up to AJ_MAX rows need more than the 48 KB default
+  constexpr int SMEM_MAX = 2 * AJ_MAX * APAD * 4 + AJ_MAX * 12;
+  if (!smem_opt_in) {
+    if (cudaError_t e = cudaFuncSetAttribute(mha_bwd_q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX)) return (int)e;
+    if (cudaError_t e = cudaFuncSetAttribute(mha_bwd_kv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_MAX)) return (int)e;
+    smem_opt_in = true;
+  }
+  auto tile = [](int rows) { return rows >= AJ_MAX ? AJ_MAX : (rows + ASL - 1) / ASL * ASL; };
+  const int ajk = tile(Sk), ajq = tile(Sq);
+  mha_bwd_q_kernel<<<dim3(ceil_div(Sq, AR), heads, B), AR * ASL, 2 * ajk * APAD * 4 + ajk, ocv_stream(stream)>>>(
       q, k, v, out, dout, key_padding_mask, dq, stats, Sq, Sk, heads, q_bstride, q_rstride, k_bstride, k_rstride, v_bstride,
-      v_rstride, o_bstride, o_rstride, dq_bstride, dq_rstride, drop_p, drop_seed, ocv_dropout_salt());
+      v_rstride, o_bstride, o_rstride, dq_bstride, dq_rstride, drop_p, drop_seed, ocv_dropout_salt(), ajk);
   if (int s = ocv_launch_status()) return s;
-  mha_bwd_kv_kernel<<<dim3(ceil_div(Sk, AR), heads, B), AR * ASL, 0, ocv_stream(stream)>>>(
+  mha_bwd_kv_kernel<<<dim3(ceil_div(Sk, AR), heads, B), AR * ASL, 2 * ajq * APAD * 4 + ajq * 12, ocv_stream(stream)>>>(
       q, k, v, dout, key_padding_mask, stats, dk, dv, Sq, Sk, heads, q_bstride, q_rstride, k_bstride, k_rstride, v_bstride,
-      v_rstride, o_bstride, o_rstride, dk_bstride, dk_rstride, dv_bstride, dv_rstride, drop_p, drop_seed, ocv_dropout_salt());
+      v_rstride, o_bstride, o_rstride, dk_bstride, dk_rstride, dv_bstride, dv_rstride, drop_p, drop_seed, ocv_dropout_salt(), ajq);
   return ocv_launch_status();
 }
 
