@@ -107,7 +107,7 @@ def join_side(device, name: Optional[str] = None) -> None:
 # ----------------------------------------------------------------------------------------------------------------------
 import os as _os
 UNFOLD_IN_FORWARD = _os.environ.get("OCV_UNFOLD_FWD", "1") == "1"
-BRANCH_OBJECTS = int(_os.environ.get("OCV_BRANCH", "7"))   # bit 0: object branch forward, bit 1: backward, bit 2: conv3x3 forward
+BRANCH_OBJECTS = int(_os.environ.get("OCV_BRANCH", "15"))  # bit 0: object branch forward, bit 1: backward, bit 2: pixel prologue, bit 3: chamfer loss
 _branch_streams = {}
 
 
@@ -459,6 +459,8 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
     Q = min(n_query, S - 1)
     t.y_raw, t.sv_reg = mlp_fwd(P, pre + "regressor.", tok[:, 0, :], (0, 2, 4))
     _, edges, t.centres = ops.bins(t.y_raw, "linear", cfg["min_depth"], cfg["max_depth"])
+    t.edges_ready = fork_branch(x.device, 8)       # the bin edges exist before the pixel path starts: the trainer runs the chamfer
+                                                   # loss from here on a branch, under the pixel forward (trainer.forward_backward)
     t.pixel = cfg.get("pixel", "fp32")
     t.Q = Q
     if t.pixel == "bf16":

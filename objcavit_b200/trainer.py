@@ -111,10 +111,15 @@ class HeadTrainer:
         x = features.contiguous().float()
         p_drop = float(self.head.dropout) if self.head.training else 0.0      # encoder-layer dropout, as the reference in train()
         drop = engine_train.DropCtx(p_drop, draw_dropout_seed() if p_drop > 0 else 0)
+        gt = depth_gt.contiguous().float()                # before the forward: the chamfer branch below forks inside it
         depth, edges, tape = engine_train.forward(P, self.cfg, x, object_features, object_xywh_list, drop=drop)
-        gt = depth_gt.contiguous().float()
+        # the chamfer loss needs only the bin edges (ready before the pixel path of the forward) and the ground truth: it runs on a
+        # branch stream from that point, next to the pixel forward; SILog (needs the depth map) stays on the launching stream
+        dev, fork = depth.device, getattr(tape, "edges_ready", None)
+        with engine_train.on_branch(dev, fork, edges, gt, depth_mask, name="loss"):
+            l2, d_edges = ops.bins_chamfer(edges, gt, depth_mask, want_grad=True, grad_scale=self.coeffs[1])
         l1, d_depth = ops.silog(depth, gt, depth_mask, want_grad=True, grad_scale=self.coeffs[0])
-        l2, d_edges = ops.bins_chamfer(edges, gt, depth_mask, want_grad=True, grad_scale=self.coeffs[1])
+        engine_train.join_branch(dev, fork, l2, d_edges, name="loss")
         engine_train.backward(P, G, tape, d_depth, d_edges)
         if self.ranges is None:                      # static per configuration: merge the touched parameters into flat ranges
             named = self._named
