@@ -107,7 +107,7 @@ def join_side(device, name: Optional[str] = None) -> None:
 # ----------------------------------------------------------------------------------------------------------------------
 import os as _os
 UNFOLD_IN_FORWARD = _os.environ.get("OCV_UNFOLD_FWD", "1") == "1"
-BRANCH_OBJECTS = int(_os.environ.get("OCV_BRANCH", "15"))  # bit 0: object branch forward, bit 1: backward, bit 2: pixel prologue, bit 3: chamfer loss
+BRANCH_OBJECTS = int(_os.environ.get("OCV_BRANCH", "31"))  # bit 0: object branch forward, bit 1: backward, bit 2: pixel prologue, bit 3: chamfer loss, bit 4: regressor
 _branch_streams = {}
 
 
@@ -457,14 +457,19 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
     S = tok.shape[1]
     t.tok = tok
     Q = min(n_query, S - 1)
-    t.y_raw, t.sv_reg = mlp_fwd(P, pre + "regressor.", tok[:, 0, :], (0, 2, 4))
-    _, edges, t.centres = ops.bins(t.y_raw, "linear", cfg["min_depth"], cfg["max_depth"])
-    t.edges_ready = fork_branch(x.device, 8)       # the bin edges exist before the pixel path starts: the trainer runs the chamfer
-                                                   # loss from here on a branch, under the pixel forward (trainer.forward_backward)
     t.pixel = cfg.get("pixel", "fp32")
+    # regressor + bins: only the LAST kernel of the pixel path (the tail) needs the bin centres, so in the tensor-core mode the chain
+    # runs on a branch next to the logits GEMMs
+    reg_fork = fork_branch(x.device, 16) if t.pixel == "bf16" else None
+    with on_branch(x.device, reg_fork, tok, name="regressor"):
+        t.y_raw, t.sv_reg = mlp_fwd(P, pre + "regressor.", tok[:, 0, :], (0, 2, 4))
+        _, edges, t.centres = ops.bins(t.y_raw, "linear", cfg["min_depth"], cfg["max_depth"])
+        t.edges_ready = fork_branch(x.device, 8)   # the bin edges exist before the pixel path ends: the trainer runs the chamfer
+                                                   # loss from here on a branch, under the pixel forward (trainer.forward_backward)
+    t.reg_fork = reg_fork
     t.Q = Q
     if t.pixel == "bf16":
-        depth = _pixel_fwd_bf16(P, pre, t, x, tok, Q)
+        depth = _pixel_fwd_bf16(P, pre, t, x, tok, Q, edges)
     else:
         t.x3 = ops.conv3x3(x, P[pre + "conv3x3.weight"], P[pre + "conv3x3.bias"])
         t.ram = ops.batched_matmul_nn(tok[:, 1:Q + 1, :], t.x3.view(B, C, h * w)).view(B, Q, h, w)
@@ -517,7 +522,7 @@ def _pixel_prologue(P: Params, pre: str, t, x: torch.Tensor) -> None:
         t.unf = ops.patch_unfold_bf16(x, 16) if UNFOLD_IN_FORWARD else None
 
 
-def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, Q: int) -> torch.Tensor:
+def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, Q: int, edges=None) -> torch.Tensor:
     B, C, h, w = x.shape
     Pn, S = h * w, tok.shape[1]
     Wout = P["conv_out.0.weight"].view(-1, Q)
@@ -530,6 +535,7 @@ def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, 
     x3 = t.x3h.view(B, Pn, C)
     for b in range(B):
         ops.gemm_bf16(t.Mb16[b], x3[b], out=t.logits[b])
+    join_branch(x.device, t.reg_fork, t.centres, t.y_raw, edges, name="regressor")      # the tail needs the bin centres
     return ops.tail_logits(t.logits, P["conv_out.0.bias"], t.centres).view(B, 1, h, w)
 
 
@@ -595,10 +601,14 @@ def backward(P: Params, G: Params, t: Tape, d_depth: torch.Tensor, d_edges: Opti
     gd = d_depth.contiguous().view(B, Pn)
     if t.pixel == "bf16":
         dlT, dcent = _pixel_bwd_bf16_tail(P, G, t, gd)
-        dy_raw = ops.bins_bwd(t.y_raw, d_edges.contiguous() if d_edges is not None else None, dcent, cfg["min_depth"], cfg["max_depth"])
         dtok = torch.zeros(B, S, E, device=dev, dtype=torch.float32)
-        mlp_bwd(P, G, pre + "regressor.", (0, 2, 4), t.sv_reg, dy_raw, dx_out=dtok[:, 0, :])
+        de = d_edges.contiguous() if d_edges is not None else None
+        fork = fork_branch(dev, 16)      # bins + regressor backward (-> dtok[:, 0]) next to the dMb chain (-> dtok[:, 1:Q+1])
+        with on_branch(dev, fork, dcent, de, dtok, name="regressor"):
+            dy_raw = ops.bins_bwd(t.y_raw, de, dcent, cfg["min_depth"], cfg["max_depth"])
+            mlp_bwd(P, G, pre + "regressor.", (0, 2, 4), t.sv_reg, dy_raw, dx_out=dtok[:, 0, :])
         _pixel_bwd_bf16_rest(P, G, t, dlT, dtok)
+        join_branch(dev, fork, name="regressor")
         del dlT
         return _token_bwd(P, G, t, dtok)
     ram = t.ram.view(B, Q, Pn)
