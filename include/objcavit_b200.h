@@ -283,6 +283,15 @@ int ocv_tail_bwd_f32(float* logits_inout, float* pg_out, const float* centres, c
  *   ocv_mha_core_dropout_f32 / ocv_mha_core_bwd_dropout_f32: the attention core with dropout on the probabilities, mask index =
  *   flat index into [B, heads, Sq, Sk] (so ocv_dropout_f32 on a tensor of ones of that shape reproduces the mask: tests). */
 int ocv_dropout_f32(const float* x, const float* residual, float* out, long long n, float p, unsigned long long seed, void* stream);
+/* Fused forms used by the native encoder-layer sequencer (bit-identical to the two-call sequences they replace):
+ *   ocv_dropout_add_layernorm_f32: sum = residual + dropout(x) over the flat [rows,E] index, y = LayerNorm(sum) * gamma + beta
+ *     (`sum` is kept: the LayerNorm backward reads it);  replaces dropout1 + norm1 / dropout2 + norm2 of
+ *     nn.TransformerEncoderLayer in train() mode.
+ *   ocv_dropout_act_bwd_f32: dx = act'(out) * dropout(dy)  (the FFN dropout site folded into the activation backward). */
+int ocv_dropout_add_layernorm_f32(const float* x, const float* residual, const float* gamma, const float* beta, float* sum, float* y,
+                                  int rows, int E, float p, unsigned long long seed, void* stream);
+int ocv_dropout_act_bwd_f32(const float* dy, const float* out, float* dx, long long n, int act, float p, unsigned long long seed,
+                            void* stream);
 /* Per-step salt of every dropout mask: `device_salt` points at ONE 64-bit word in device memory (or NULL = none, the default);
  * each dropout kernel uses seed ^ *device_salt.  It exists for CUDA-graph replay of the training step, where the site seeds are
  * frozen kernel arguments: the caller changes the word between replays.  Process-wide (one process per GPU). */

@@ -65,6 +65,8 @@ PROTOTYPES = {
                                    i64, i32, i64, i32, i64, i32, p, p]),
     "ocv_tail_bwd_f32": (i32, [p, p, p, p, p, i32, i32, i64, p]),
     "ocv_dropout_f32": (i32, [p, p, p, i64, f32, C.c_ulonglong, p]),
+    "ocv_dropout_add_layernorm_f32": (i32, [p, p, p, p, p, p, i32, i32, f32, C.c_ulonglong, p]),
+    "ocv_dropout_act_bwd_f32": (i32, [p, p, p, i64, i32, f32, C.c_ulonglong, p]),
     "ocv_encoder_layer_fwd_train_workspace": (i64, [i32, i32, i32]),
     "ocv_encoder_layer_fwd_train_f32": (i32, [p, p, p, i32, i32, i32, f32, p, p, p, p, p, p, p, p, p, p]),
     "ocv_encoder_layer_bwd_train_workspace": (i64, [i32, i32, i32]),

@@ -82,6 +82,19 @@ __global__ void act_bwd_kernel(const float* __restrict__ dy, const float* __rest
   dx[i] = act == OCV_ACT_RELU ? (o > 0.f ? g : 0.f) : (act == OCV_ACT_LEAKY_RELU ? (o > 0.f ? g : 0.01f * g) : g);
 }
 
+// dx = act'(out) * dropout(dy): the FFN dropout site and the ReLU backward of a training-mode encoder layer in one pass (same
+// arithmetic as ocv_dropout_f32 followed by ocv_act_bwd_f32: bit-identical)
+__global__ void dropout_act_bwd_kernel(const float* __restrict__ dy, const float* __restrict__ out, float* __restrict__ dx, long long n,
+                                       int act, uint32_t thr, float scale, unsigned long long seed_in,
+                                       const unsigned long long* salt) {
+  const unsigned long long seed = ocv_salted(seed_in, salt);
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float o = out[i];
+  const float g = ocv_drop_keep(seed, (unsigned long long)i, thr) ? dy[i] * scale : 0.f;
+  dx[i] = act == OCV_ACT_RELU ? (o > 0.f ? g : 0.f) : (act == OCV_ACT_LEAKY_RELU ? (o > 0.f ? g : 0.01f * g) : g);
+}
+
 // LayerNorm backward, one warp per row (E <= 512, E % 32 == 0): z = pre-norm input, y = (z - mean) rstd gamma + beta
 //   dz = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma;  also stores (mean, rstd) per row for the parameter pass
 __global__ void layernorm_bwd_rows_kernel(const float* __restrict__ dy, const float* __restrict__ z, const float* __restrict__ gamma,
@@ -495,6 +508,15 @@ extern "C" int ocv_act_bwd_f32(const float* dy, const float* out, float* dx, lon
   OCV_CHECK_ARG(dy && out && dx && n > 0);
   if (int s = ocv_require_sm100()) return s;
   act_bwd_kernel<<<(unsigned)ceil_div<long long>(n, 256), 256, 0, ocv_stream(stream)>>>(dy, out, dx, n, act);
+  return ocv_launch_status();
+}
+
+extern "C" int ocv_dropout_act_bwd_f32(const float* dy, const float* out, float* dx, long long n, int act, float p,
+                                       unsigned long long seed, void* stream) {
+  OCV_CHECK_ARG(dy && out && dx && n > 0 && p >= 0.f && p < 1.f);
+  if (int s = ocv_require_sm100()) return s;
+  dropout_act_bwd_kernel<<<(unsigned)ceil_div<long long>(n, 256), 256, 0, ocv_stream(stream)>>>(
+      dy, out, dx, n, act, ocv_drop_threshold(p), 1.f / (1.f - p), seed, ocv_dropout_salt());
   return ocv_launch_status();
 }
 

@@ -39,6 +39,41 @@ __global__ void add_layernorm_kernel(const float* __restrict__ x, const float* _
   }
 }
 
+// sum = r + dropout(x) (counter-based mask over the flat [rows, E] index, as ocv_dropout_f32), y = LN(sum): the two dropout +
+// residual sites of a training-mode encoder layer fused into the LayerNorm that follows them (same arithmetic, same order:
+// bit-identical to ocv_dropout_f32 followed by ocv_add_layernorm_f32); `sum` is kept for the backward.
+__global__ void dropout_add_layernorm_kernel(const float* x /* may alias sum */, const float* __restrict__ r, const float* __restrict__ gamma,
+                                             const float* __restrict__ beta, float* sum, float* __restrict__ y, int rows,
+                                             int E, uint32_t thr, float scale, unsigned long long seed_in,
+                                             const unsigned long long* salt) {
+  const unsigned long long seed = ocv_salted(seed_in, salt);
+  const int row = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
+  const int lane = threadIdx.x % 32;
+  if (row >= rows) return;
+  const int per = E / 32;
+  float v[16];
+  const long long base = (long long)row * E;
+  float s = 0.f;
+  for (int i = 0; i < per; ++i) {
+    const int e = i * 32 + lane;
+    const float d = ocv_drop_keep(seed, (unsigned long long)(base + e), thr) ? x[base + e] * scale : 0.f;
+    v[i] = r[base + e] + d;
+    sum[base + e] = v[i];
+    s += v[i];
+  }
+  const float mean = warp_sum(s) / E;
+  float q = 0.f;
+  for (int i = 0; i < per; ++i) {
+    const float d = v[i] - mean;
+    q += d * d;
+  }
+  const float rstd = rsqrtf(warp_sum(q) / E + 1e-5f);
+  for (int i = 0; i < per; ++i) {
+    const int e = i * 32 + lane;
+    y[base + e] = (v[i] - mean) * rstd * gamma[e] + beta[e];
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // attention core, d = 32: one warp per query row, keys in tiles of 32 (lane = key for the scores,
 // lane = channel for P@V), online softmax in fp32
@@ -424,6 +459,17 @@ extern "C" int ocv_add_layernorm_f32(const float* x, const float* r, const float
   const int wpb = 8;
   add_layernorm_kernel<<<ceil_div(rows, wpb), wpb * 32, 0, ocv_stream(stream)>>>(x, r, gamma, beta, y, rows, E,
                                                                                 zero_rows);
+  return ocv_launch_status();
+}
+
+extern "C" int ocv_dropout_add_layernorm_f32(const float* x, const float* residual, const float* gamma, const float* beta, float* sum,
+                                             float* y, int rows, int E, float p, unsigned long long seed, void* stream) {
+  OCV_CHECK_ARG(x && residual && gamma && beta && sum && y && rows > 0 && p >= 0.f && p < 1.f);
+  OCV_CHECK_SHAPE(E > 0 && E % 32 == 0 && E <= 512);
+  if (int s = ocv_require_sm100()) return s;
+  const int wpb = 8;
+  dropout_add_layernorm_kernel<<<ceil_div(rows, wpb), wpb * 32, 0, ocv_stream(stream)>>>(
+      x, residual, gamma, beta, sum, y, rows, E, ocv_drop_threshold(p), 1.f / (1.f - p), seed, ocv_dropout_salt());
   return ocv_launch_status();
 }
 

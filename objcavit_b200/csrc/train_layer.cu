@@ -103,23 +103,22 @@ extern "C" int ocv_encoder_layer_fwd_train_f32(const float* const* W, const floa
   TRY(ocv_mha_core_dropout_f32(qkv, qkv + LE, qkv + 2 * LE, att, mask, B, S, S, LH, LD, (long long)S * 3 * LE, 3 * LE,
                                (long long)S * 3 * LE, 3 * LE, (long long)S * 3 * LE, 3 * LE, (long long)S * LE, LE,
                                drop ? drop_p : 0.f, drop ? seeds[0] : 0ull, stream));
-  if (drop) {
+  if (drop) {                                                                         // y = x + dropout1(self-attention), x1 = LN(y)
     TRY(linear(att, W[W_OUT], W[B_OUT], nullptr, y, M, LE, LE, OCV_ACT_NONE, stream));
-    TRY(ocv_dropout_f32(y, x, y, ME, drop_p, seeds[1], stream));                      // x + dropout1(self-attention)
+    TRY(ocv_dropout_add_layernorm_f32(y, x, W[G_1], W[BE_1], y, x1, M, LE, drop_p, seeds[1], stream));
   } else {
     TRY(linear(att, W[W_OUT], W[B_OUT], x, y, M, LE, LE, OCV_ACT_NONE, stream));
+    TRY(ocv_add_layernorm_f32(y, nullptr, W[G_1], W[BE_1], x1, M, LE, nullptr, stream));
   }
-  TRY(ocv_add_layernorm_f32(y, nullptr, W[G_1], W[BE_1], x1, M, LE, nullptr, stream));
   TRY(linear(x1, W[W_1], W[B_1], nullptr, h, M, F, LE, OCV_ACT_RELU, stream));
   if (drop) {
     TRY(ocv_dropout_f32(h, nullptr, h, (long long)M * F, drop_p, seeds[2], stream));   // dropout(relu(linear1)): what linear2 sees
     const int sp = linear_split(M, LE, F);
     if (sp > 0) TRY(ocv_linear_splitk_f32(h, W[W_2], W[B_2], y2, M, LE, F, F, F, LE, sp, workspace, stream));
     else TRY(linear(h, W[W_2], W[B_2], nullptr, y2, M, LE, F, OCV_ACT_NONE, stream));
-    TRY(ocv_dropout_f32(y2, x1, y2, ME, drop_p, seeds[3], stream));                    // x1 + dropout2(linear2)
-  } else {
-    TRY(linear(h, W[W_2], W[B_2], x1, y2, M, LE, F, OCV_ACT_NONE, stream));
+    return ocv_dropout_add_layernorm_f32(y2, x1, W[G_2], W[BE_2], y2, out, M, LE, drop_p, seeds[3], stream);   // x1 + dropout2(linear2), LN
   }
+  TRY(linear(h, W[W_2], W[B_2], x1, y2, M, LE, F, OCV_ACT_NONE, stream));
   return ocv_add_layernorm_f32(y2, nullptr, W[G_2], W[BE_2], out, M, LE, nullptr, stream);
 }
 
@@ -173,8 +172,8 @@ extern "C" int ocv_encoder_layer_bwd_train_f32(const float* const* W, float* con
   TRY(order_after(sd, st));
   TRY(wgrad(df, h, G[W_2], G[B_2], M, LE, F, ws_side, sd));
   TRY(dgrad(df, W[W_2], dh, M, LE, F, 0.f, ws_main, st));
-  if (drop) TRY(ocv_dropout_f32(dh, nullptr, dh, MF, drop_p, seeds[2], st));       // h is post-dropout: h > 0 <=> kept & positive
-  TRY(ocv_act_bwd_f32(dh, h, dh2, MF, OCV_ACT_RELU, st));
+  if (drop) TRY(ocv_dropout_act_bwd_f32(dh, h, dh2, MF, OCV_ACT_RELU, drop_p, seeds[2], st));   // h is post-dropout: h > 0 <=> kept & positive
+  else TRY(ocv_act_bwd_f32(dh, h, dh2, MF, OCV_ACT_RELU, st));
   TRY(order_after(sd, st));
   TRY(wgrad(dh2, x1, G[W_1], G[B_1], M, F, LE, ws_side, sd));
   if (!drop) TRY(order_after(st, sd));                                             // df aliases dy2, updated in place next

@@ -879,6 +879,26 @@ def dropout(x: torch.Tensor, p: float, seed: int, residual=None, out=None) -> to
     return out
 
 
+def dropout_add_layernorm(x: torch.Tensor, residual: torch.Tensor, gamma, beta, p: float, seed: int):
+    """-> (sum = residual + dropout(x), LayerNorm(sum)) in one kernel; bit-identical to ``dropout`` + ``add_layernorm``."""
+    _chk(x, torch.float32, "x"); _chk(residual, torch.float32, "residual")
+    assert x.is_contiguous() and residual.is_contiguous() and residual.shape == x.shape
+    E = x.shape[-1]
+    total, y = torch.empty_like(x), torch.empty_like(x)
+    _call("ocv_dropout_add_layernorm_f32", x.data_ptr(), residual.data_ptr(), gamma.data_ptr(), beta.data_ptr(), total.data_ptr(),
+          y.data_ptr(), x.numel() // E, E, float(p), int(seed), _stream())
+    return total, y
+
+
+def dropout_act_bwd(dy: torch.Tensor, out: torch.Tensor, act: int, p: float, seed: int) -> torch.Tensor:
+    """dx = act'(out) * dropout(dy) in one kernel; bit-identical to ``dropout`` + ``act_bwd``."""
+    _chk(dy, torch.float32, "dy"); _chk(out, torch.float32, "out")
+    assert dy.is_contiguous() and out.is_contiguous() and dy.shape == out.shape
+    dx = torch.empty_like(dy)
+    _call("ocv_dropout_act_bwd_f32", dy.data_ptr(), out.data_ptr(), dx.data_ptr(), dy.numel(), act, float(p), int(seed), _stream())
+    return dx
+
+
 # ---- training step, tensor-core pixel path (csrc/train_pixel_bf16.cu) -------------------------------------------------
 
 def tail_logits(logits: torch.Tensor, bias, centres: torch.Tensor) -> torch.Tensor:
@@ -1022,7 +1042,7 @@ def encoder_layer_fwd_train(W, x: torch.Tensor, mask, drop_p: float, seeds):
     sd = (C.c_ulonglong * 4)(*[int(v) for v in seeds]) if drop_p > 0 else None
     _call("ocv_encoder_layer_fwd_train_f32", _ptr_array(W), x.data_ptr(), _ptr(mask), B, S, F_, float(drop_p), sd, qkv.data_ptr(),
           att.data_ptr(), y.data_ptr(), x1.data_ptr(), h.data_ptr(), y2.data_ptr(), out.data_ptr(), ws.data_ptr(), _stream(),
-          launches=13 if drop_p > 0 else 9)
+          launches=11 if drop_p > 0 else 9)
     return out.view(B, S, E), (qkv, att.view(B, S, E), y, x1, h, y2)
 
 
@@ -1042,7 +1062,7 @@ def encoder_layer_bwd_train(W, G, x, qkv, att, y, x1, h, y2, mask, dout: torch.T
     sd = (C.c_ulonglong * 4)(*[int(v) for v in seeds]) if drop_p > 0 else None
     _call("ocv_encoder_layer_bwd_train_f32", _ptr_array(W), _ptr_array(G), x.data_ptr(), qkv.data_ptr(), att.data_ptr(), y.data_ptr(),
           x1.data_ptr(), h.data_ptr(), y2.data_ptr(), _ptr(mask), d.data_ptr(), dx.data_ptr(), B, S, F_, float(drop_p), sd,
-          ws.data_ptr(), _stream(), None if side_stream is None else side_stream.cuda_stream, launches=32 if drop_p > 0 else 29)
+          ws.data_ptr(), _stream(), None if side_stream is None else side_stream.cuda_stream, launches=31 if drop_p > 0 else 29)
     if side_stream is not None:
         for t in (ws, x, att, x1, h):
             t.record_stream(side_stream)

@@ -197,3 +197,23 @@ def test_trainer_step_with_dropout_is_reproducible(cuda):
     tr0 = HeadTrainer(h0, lr=3.57e-4, weight_decay=0.1, clip_grad_norm=0.1)
     l1, l2 = tr0.step(feats.to(cuda), dev(objs), dev(boxes), gt.to(cuda), mask.to(cuda))
     assert tr0.loss_value(l1, l2) != res[0][0]
+
+
+def test_fused_dropout_kernels_of_the_layer_sequencer_equal_the_two_call_sequences(cuda):
+    """``ocv_dropout_add_layernorm_f32`` == ``ocv_dropout_f32`` (+ residual) then ``ocv_add_layernorm_f32``, and
+    ``ocv_dropout_act_bwd_f32`` == ``ocv_dropout_f32`` then ``ocv_act_bwd_f32``: same mask, same arithmetic, bit for bit."""
+    from objcavit_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    rows, E, F = 8 * 221, 128, 1024
+    x = torch.randn(rows, E, generator=g).to(cuda)
+    r = torch.randn(rows, E, generator=g).to(cuda)
+    gamma, beta = torch.randn(E, generator=g).to(cuda), torch.randn(E, generator=g).to(cuda)
+    for p, seed in ((0.1, 0x1234567890ABCDEF), (0.5, 7)):
+        want_sum = ops.dropout(x, p, seed, residual=r)
+        want_y = ops.add_layernorm(want_sum, None, gamma, beta)
+        got_sum, got_y = ops.dropout_add_layernorm(x, r, gamma, beta, p, seed)
+        assert torch.equal(got_sum, want_sum) and torch.equal(got_y, want_y)
+        dy = torch.randn(rows, F, generator=g).to(cuda)
+        h = torch.relu(torch.randn(rows, F, generator=g)).to(cuda)
+        want = ops.act_bwd(ops.dropout(dy, p, seed), h, 1)
+        assert torch.equal(ops.dropout_act_bwd(dy, h, 1, p, seed), want)
