@@ -106,8 +106,9 @@ def join_side(device, name: Optional[str] = None) -> None:
 # `on_branch` runs a region there, `join_branch` orders the launching stream after it.  No kernel changes: bit-identical.
 # ----------------------------------------------------------------------------------------------------------------------
 import os as _os
+PIXEL_QUEUES = max(1, int(_os.environ.get("OCV_PIXEL_QUEUES", "2")))   # the per-image pixel GEMMs alternate over this many queues
 UNFOLD_IN_FORWARD = _os.environ.get("OCV_UNFOLD_FWD", "1") == "1"
-BRANCH_OBJECTS = int(_os.environ.get("OCV_BRANCH", "31"))  # bit 0: object branch forward, bit 1: backward, bit 2: pixel prologue, bit 3: chamfer loss, bit 4: regressor
+BRANCH_OBJECTS = int(_os.environ.get("OCV_BRANCH", "63"))  # bit 0: object branch forward, bit 1: backward, bit 2: pixel prologue, bit 3: chamfer loss, bit 4: regressor, bit 5: per-image pixel GEMMs over two queues
 _branch_streams = {}
 
 
@@ -533,8 +534,13 @@ def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, 
     t.Mb16 = ops.cast_bf16(Mb)
     t.logits = torch.empty(B, K, Pn, device=x.device, dtype=torch.float32)
     x3 = t.x3h.view(B, Pn, C)
+    # one GEMM per image, each bound by its 58 MB output write: alternate images over PIXEL_QUEUES queues so that several of them are in flight
+    fork = fork_branch(x.device, 32)
     for b in range(B):
-        ops.gemm_bf16(t.Mb16[b], x3[b], out=t.logits[b])
+        with on_branch(x.device, fork if b % PIXEL_QUEUES else None, t.Mb16, t.x3h, t.logits, name=f"pixel_q{b % PIXEL_QUEUES}"):
+            ops.gemm_bf16(t.Mb16[b], x3[b], out=t.logits[b])
+    for qi in range(1, min(PIXEL_QUEUES, B)):
+        join_branch(x.device, fork, name=f"pixel_q{qi}")
     join_branch(x.device, t.reg_fork, t.centres, t.y_raw, edges, name="regressor")      # the tail needs the bin centres
     return ops.tail_logits(t.logits, P["conv_out.0.bias"], t.centres).view(B, 1, h, w)
 
@@ -558,8 +564,12 @@ def _pixel_bwd_bf16_rest(P: Params, G: Params, t, dlT: torch.Tensor, dtok: torch
     x3T = ops.transpose_bf16(t.x3h.view(B, Pn, C))                            # [B,C,P]
     dMb = torch.empty(B, K, E, device=dev, dtype=torch.float32)
     sk = max(1, min(64, Pn // 1024))
+    fork = fork_branch(dev, 32)
     for b in range(B):
-        ops.gemm_bf16(dlT[b], x3T[b], out=dMb[b], split_k=sk)
+        with on_branch(dev, fork if b % PIXEL_QUEUES else None, dlT, x3T, dMb, name=f"pixel_q{b % PIXEL_QUEUES}"):
+            ops.gemm_bf16(dlT[b], x3T[b], out=dMb[b], split_k=sk)
+    for qi in range(1, min(PIXEL_QUEUES, B)):
+        join_branch(dev, fork, name=f"pixel_q{qi}")
     del x3T
     queries = tok[:, 1:Q + 1, :]
     ops.gemm_ex(dMb, queries, K, Q, E, E, E, G["conv_out.0.weight"], Q, op_b=1, beta=1.0, batch=B, stride_a=K * E, stride_b=S * E,
