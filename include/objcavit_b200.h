@@ -264,6 +264,15 @@ int ocv_act_bwd_f32(const float* dy, const float* out, float* dx, long long n, i
  * workspace rows*2 + 32*E floats (row statistics + fixed-order partials of the parameter sums). */
 int ocv_layernorm_bwd_f32(const float* dy, const float* z, const float* gamma, float* dz, float* dgamma, float* dbeta, int rows,
                           int E, float beta, void* workspace, void* stream);
+/* Data half of the LayerNorm backward fused with the dropout site behind it (backward of a train()-mode encoder layer):
+ * dz as ocv_layernorm_bwd_f32, dz_dropped = dropout(dz) — bit-identical to ocv_dropout_f32(dz); row statistics into `workspace`
+ * (rows*2 + 32*E floats) for a following ocv_layernorm_bwd_params_f32. */
+int ocv_layernorm_bwd_dropout_f32(const float* dy, const float* z, const float* gamma, float* dz, float* dz_dropped, int rows, int E,
+                                  float p, unsigned long long seed, void* workspace, void* stream);
+/* The parameter half of ocv_layernorm_bwd_f32 alone: call ocv_layernorm_bwd_f32 with dgamma = dbeta = NULL first (data gradient +
+ * row statistics into `workspace`), then this on the same dy / z / workspace — possibly on another stream, ordered after it. */
+int ocv_layernorm_bwd_params_f32(const float* dy, const float* z, float* dgamma, float* dbeta, int rows, int E, float beta,
+                                 void* workspace, void* stream);
 /* Backward of ocv_mha_core_f32 (same view conventions; `out` = its forward result): dq, dk, dv.  workspace B*heads*Sq*3 floats. */
 int ocv_mha_core_bwd_f32(const float* q, const float* k, const float* v, const float* out, const float* dout,
                          const uint8_t* key_padding_mask, float* dq, float* dk, float* dv, int B, int Sq, int Sk, int heads, int d,

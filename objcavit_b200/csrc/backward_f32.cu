@@ -98,7 +98,11 @@ __global__ void dropout_act_bwd_kernel(const float* __restrict__ dy, const float
 // LayerNorm backward, one warp per row (E <= 512, E % 32 == 0): z = pre-norm input, y = (z - mean) rstd gamma + beta
 //   dz = rstd * (g - mean(g) - xhat * mean(g * xhat)),  g = dy * gamma;  also stores (mean, rstd) per row for the parameter pass
 __global__ void layernorm_bwd_rows_kernel(const float* __restrict__ dy, const float* __restrict__ z, const float* __restrict__ gamma,
-                                          float* __restrict__ dz, float* __restrict__ stats, int rows, int E) {
+                                          float* __restrict__ dz, float* __restrict__ stats, int rows, int E,
+                                          float* __restrict__ dz_dropped, uint32_t thr, float scale, unsigned long long seed_in,
+                                          const unsigned long long* salt) {
+  // dz_dropped (optional) = dropout(dz) over the flat [rows, E] index, as ocv_dropout_f32 would compute it from dz
+  const unsigned long long seed = ocv_salted(seed_in, salt);
   const int row = blockIdx.x * (blockDim.x / 32) + threadIdx.x / 32;
   const int lane = threadIdx.x % 32;
   if (row >= rows) return;
@@ -127,7 +131,12 @@ __global__ void layernorm_bwd_rows_kernel(const float* __restrict__ dy, const fl
   }
   const float mg = warp_sum(sg) / E, mgx = warp_sum(sgx) / E;
   float* o = dz + (long long)row * E;
-  for (int i = 0; i < per; ++i) o[i * 32 + lane] = rstd * (g[i] - mg - v[i] * mgx);
+  float* od = dz_dropped ? dz_dropped + (long long)row * E : nullptr;
+  for (int i = 0; i < per; ++i) {
+    const float d = rstd * (g[i] - mg - v[i] * mgx);
+    o[i * 32 + lane] = d;
+    if (od) od[i * 32 + lane] = ocv_drop_keep(seed, (unsigned long long)((long long)row * E + i * 32 + lane), thr) ? d * scale : 0.f;
+  }
   if (lane == 0) {
     stats[2 * row] = mean;
     stats[2 * row + 1] = rstd;
@@ -527,7 +536,8 @@ extern "C" int ocv_layernorm_bwd_f32(const float* dy, const float* z, const floa
   OCV_CHECK_ARG((dgamma == nullptr) == (dbeta == nullptr));
   if (int s = ocv_require_sm100()) return s;
   float* stats = static_cast<float*>(workspace);
-  layernorm_bwd_rows_kernel<<<ceil_div(rows, 8), 256, 0, ocv_stream(stream)>>>(dy, z, gamma, dz, stats, rows, E);
+  layernorm_bwd_rows_kernel<<<ceil_div(rows, 8), 256, 0, ocv_stream(stream)>>>(dy, z, gamma, dz, stats, rows, E, nullptr, 0u, 1.f, 0ull,
+                                                                               nullptr);
   if (int s = ocv_launch_status()) return s;
   if (dgamma) {
     float* part = stats + 2 * (long long)rows;
@@ -537,6 +547,34 @@ extern "C" int ocv_layernorm_bwd_f32(const float* dy, const float* z, const floa
     return ocv_launch_status();
   }
   return OCV_OK;
+}
+
+// Data half of the LayerNorm backward with the dropout site that follows it in the backward of a training-mode encoder layer:
+// dz as ocv_layernorm_bwd_f32, dz_dropped = dropout(dz) (bit-identical to ocv_dropout_f32 on dz); row statistics into `workspace`.
+extern "C" int ocv_layernorm_bwd_dropout_f32(const float* dy, const float* z, const float* gamma, float* dz, float* dz_dropped, int rows,
+                                             int E, float p, unsigned long long seed, void* workspace, void* stream) {
+  OCV_CHECK_ARG(dy && z && gamma && dz && dz_dropped && workspace && rows > 0 && p >= 0.f && p < 1.f);
+  OCV_CHECK_SHAPE(E > 0 && E % 32 == 0 && E <= 512);
+  if (int s = ocv_require_sm100()) return s;
+  layernorm_bwd_rows_kernel<<<ceil_div(rows, 8), 256, 0, ocv_stream(stream)>>>(dy, z, gamma, dz, static_cast<float*>(workspace), rows, E,
+                                                                               dz_dropped, ocv_drop_threshold(p), 1.f / (1.f - p), seed,
+                                                                               ocv_dropout_salt());
+  return ocv_launch_status();
+}
+
+// The parameter half of ocv_layernorm_bwd_f32 on its own: `workspace` is the one a preceding ocv_layernorm_bwd_f32(dgamma = dbeta =
+// NULL) call on the same (dy, z) filled with the row statistics.  Lets a sequencer keep only the data gradient on its chain.
+extern "C" int ocv_layernorm_bwd_params_f32(const float* dy, const float* z, float* dgamma, float* dbeta, int rows, int E, float beta,
+                                            void* workspace /* rows*2 + 32*E floats */, void* stream) {
+  OCV_CHECK_ARG(dy && z && dgamma && dbeta && workspace && rows > 0);
+  OCV_CHECK_SHAPE(E > 0 && E % 32 == 0 && E <= 512);
+  if (int s = ocv_require_sm100()) return s;
+  float* stats = static_cast<float*>(workspace);
+  float* part = stats + 2 * (long long)rows;
+  layernorm_bwd_params_kernel<<<dim3(ceil_div(E, 32), LNG), dim3(32, 8), 0, ocv_stream(stream)>>>(dy, z, stats, part, rows, E);
+  if (int s = ocv_launch_status()) return s;
+  layernorm_bwd_params_final_kernel<<<ceil_div(E, 128), 128, 0, ocv_stream(stream)>>>(part, dgamma, dbeta, E, beta);
+  return ocv_launch_status();
 }
 
 extern "C" int ocv_mha_core_bwd_f32(const float* q, const float* k, const float* v, const float* out, const float* dout,

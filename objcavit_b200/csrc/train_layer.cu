@@ -130,7 +130,7 @@ extern "C" long long ocv_encoder_layer_bwd_train_workspace(int B, int S, int F) 
   bytes += 2 * al((size_t)M * F * 4);             // dh, dh2
   bytes += al((size_t)M * 3 * LE * 4);            // dqkv
   bytes += al((size_t)B * LH * S * 3 * 4);        // attention statistics
-  bytes += al((size_t)(M * 2 + 32 * LE) * 4);     // LayerNorm row statistics + parameter partials
+  bytes += 2 * al((size_t)(M * 2 + 32 * LE) * 4); // LayerNorm row statistics + parameter partials, one set per LayerNorm
   bytes += 2 * al((size_t)gemm_ws_floats((int)M, F) * 4);   // GEMM partials: main stream, weight-gradient stream
   return (long long)bytes;
 }
@@ -157,19 +157,22 @@ extern "C" int ocv_encoder_layer_bwd_train_f32(const float* const* W, float* con
   float* dh2 = static_cast<float*>(take(MF * 4));
   float* dqkv = static_cast<float*>(take(ME * 3 * 4));
   void* stats = take((size_t)B * LH * S * 3 * 4);
-  void* lnws = take((size_t)((long long)M * 2 + 32 * LE) * 4);
+  void* lnws2 = take((size_t)((long long)M * 2 + 32 * LE) * 4);   // norm2 / norm1: their parameter reductions run on the
+  void* lnws1 = take((size_t)((long long)M * 2 + 32 * LE) * 4);   // weight-gradient stream while the chain goes on
   const size_t gws = (size_t)gemm_ws_floats(M, F) * 4;
   void* ws_main = take(gws);
   void* ws_side = take(gws);
   float* dy = dx;  // d loss / d (x + attention branch), becomes d loss / d x after the last accumulation
 
-  TRY(ocv_layernorm_bwd_f32(dout, y2, W[G_2], dy2, G[G_2], G[BE_2], M, LE, 1.f, lnws, st));
   const float* df = dy2;                                                           // gradient of linear2's output
   if (drop) {
-    TRY(ocv_dropout_f32(dy2, nullptr, dfb, ME, drop_p, seeds[3], st));
+    TRY(ocv_layernorm_bwd_dropout_f32(dout, y2, W[G_2], dy2, dfb, M, LE, drop_p, seeds[3], lnws2, st));
     df = dfb;
+  } else {
+    TRY(ocv_layernorm_bwd_f32(dout, y2, W[G_2], dy2, nullptr, nullptr, M, LE, 1.f, lnws2, st));
   }
   TRY(order_after(sd, st));
+  TRY(ocv_layernorm_bwd_params_f32(dout, y2, G[G_2], G[BE_2], M, LE, 1.f, lnws2, sd));
   TRY(wgrad(df, h, G[W_2], G[B_2], M, LE, F, ws_side, sd));
   TRY(dgrad(df, W[W_2], dh, M, LE, F, 0.f, ws_main, st));
   if (drop) TRY(ocv_dropout_act_bwd_f32(dh, h, dh2, MF, OCV_ACT_RELU, drop_p, seeds[2], st));   // h is post-dropout: h > 0 <=> kept & positive
@@ -178,13 +181,15 @@ extern "C" int ocv_encoder_layer_bwd_train_f32(const float* const* W, float* con
   TRY(wgrad(dh2, x1, G[W_1], G[B_1], M, F, LE, ws_side, sd));
   if (!drop) TRY(order_after(st, sd));                                             // df aliases dy2, updated in place next
   TRY(dgrad(dh2, W[W_1], dy2, M, F, LE, 1.f, ws_main, st));                        // dy2 <- d loss / d x1 (residual + FFN)
-  TRY(ocv_layernorm_bwd_f32(dy2, y, W[G_1], dy, G[G_1], G[BE_1], M, LE, 1.f, lnws, st));
   const float* dsa = dy;                                                           // gradient of out_proj's output
   if (drop) {
-    TRY(ocv_dropout_f32(dy, nullptr, dsab, ME, drop_p, seeds[1], st));
+    TRY(ocv_layernorm_bwd_dropout_f32(dy2, y, W[G_1], dy, dsab, M, LE, drop_p, seeds[1], lnws1, st));
     dsa = dsab;
+  } else {
+    TRY(ocv_layernorm_bwd_f32(dy2, y, W[G_1], dy, nullptr, nullptr, M, LE, 1.f, lnws1, st));
   }
   TRY(order_after(sd, st));
+  TRY(ocv_layernorm_bwd_params_f32(dy2, y, G[G_1], G[BE_1], M, LE, 1.f, lnws1, sd));
   TRY(wgrad(dsa, att, G[W_OUT], G[B_OUT], M, LE, LE, ws_side, sd));
   TRY(dgrad(dsa, W[W_OUT], datt, M, LE, LE, 0.f, ws_main, st));
   const long long qs = (long long)S * 3 * LE;

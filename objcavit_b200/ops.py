@@ -717,6 +717,24 @@ def layernorm_bwd(dy: torch.Tensor, z: torch.Tensor, gamma: torch.Tensor, dgamma
     return dz
 
 
+def layernorm_bwd_dropout(dy: torch.Tensor, z: torch.Tensor, gamma: torch.Tensor, p: float, seed: int, dgamma, dbeta,
+                          beta: float = 1.0):
+    """-> (dz, dropout(dz)): the data half of the LayerNorm backward fused with the dropout site behind it, then the parameter
+    half as its own call (``ocv_layernorm_bwd_dropout_f32`` + ``ocv_layernorm_bwd_params_f32``: what the layer sequencer issues on
+    two streams).  Bit-identical to ``layernorm_bwd`` + ``dropout``."""
+    _chk(dy, torch.float32, "dy"); _chk(z, torch.float32, "z")
+    assert dy.is_contiguous() and z.is_contiguous() and dy.shape == z.shape
+    E = z.shape[-1]
+    rows = z.numel() // E
+    dz, dzd = torch.empty_like(z), torch.empty_like(z)
+    ws = _workspace(rows * 8 + 32 * E * 4, z.device, "ln_bwd")
+    _call("ocv_layernorm_bwd_dropout_f32", dy.data_ptr(), z.data_ptr(), gamma.data_ptr(), dz.data_ptr(), dzd.data_ptr(), rows, E,
+          float(p), int(seed), ws.data_ptr(), _stream())
+    _call("ocv_layernorm_bwd_params_f32", dy.data_ptr(), z.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), rows, E, float(beta),
+          ws.data_ptr(), _stream(), launches=2)
+    return dz, dzd
+
+
 def mha_core_bwd(q, k, v, out, dout, key_padding_mask=None, heads: int = 4, packed: bool = False, drop=None):
     """Backward of :func:`mha_core`: returns (dq, dk, dv) dense [B,S,E]; ``packed`` (self-attention, Sq == Sk): the three are
     views of one [B,S,3E] buffer laid out like the packed QKV projection output."""
@@ -1062,7 +1080,7 @@ def encoder_layer_bwd_train(W, G, x, qkv, att, y, x1, h, y2, mask, dout: torch.T
     sd = (C.c_ulonglong * 4)(*[int(v) for v in seeds]) if drop_p > 0 else None
     _call("ocv_encoder_layer_bwd_train_f32", _ptr_array(W), _ptr_array(G), x.data_ptr(), qkv.data_ptr(), att.data_ptr(), y.data_ptr(),
           x1.data_ptr(), h.data_ptr(), y2.data_ptr(), _ptr(mask), d.data_ptr(), dx.data_ptr(), B, S, F_, float(drop_p), sd,
-          ws.data_ptr(), _stream(), None if side_stream is None else side_stream.cuda_stream, launches=31 if drop_p > 0 else 29)
+          ws.data_ptr(), _stream(), None if side_stream is None else side_stream.cuda_stream, launches=29)
     if side_stream is not None:
         for t in (ws, x, att, x1, h):
             t.record_stream(side_stream)

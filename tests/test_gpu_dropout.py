@@ -217,3 +217,10 @@ def test_fused_dropout_kernels_of_the_layer_sequencer_equal_the_two_call_sequenc
         h = torch.relu(torch.randn(rows, F, generator=g)).to(cuda)
         want = ops.act_bwd(ops.dropout(dy, p, seed), h, 1)
         assert torch.equal(ops.dropout_act_bwd(dy, h, 1, p, seed), want)
+        # LayerNorm backward: data half + dropout in one kernel, parameter half as its own call
+        dg0, db0 = torch.randn(E, generator=g).to(cuda), torch.randn(E, generator=g).to(cuda)
+        dg1, db1 = dg0.clone(), db0.clone()
+        want_dz = ops.layernorm_bwd(x, r, gamma, dg0, db0, beta=1.0)
+        got_dz, got_dzd = ops.layernorm_bwd_dropout(x, r, gamma, p, seed, dg1, db1, beta=1.0)
+        assert torch.equal(got_dz, want_dz) and torch.equal(got_dzd, ops.dropout(want_dz, p, seed))
+        assert torch.equal(dg1, dg0) and torch.equal(db1, db0)
