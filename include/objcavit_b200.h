@@ -359,6 +359,13 @@ int ocv_table_grad_commit_f32(const long long* table_grad_fix, float* table_grad
  * (backward of) self.conv3x3 (modules/miniViT.py:25; modules/ObjCAViT.py:374) as ONE GEMM dW[o, :] = dx3T[o, B*P] @ col^T. */
 int ocv_tail_logits_f32(const float* logits, const float* logit_bias, const float* centres, float* depth, int B, int K,
                         long long P, void* stream);
+/* ..._stats_...: the forward also saves the per-pixel softmax statistics (max, sum, centre-weighted sum; stats [B,3,P] fp32), the
+ * backward reads them instead of recomputing them in a first pass over the 4K-byte-per-pixel logits (same values, bit for bit). */
+int ocv_tail_logits_stats_f32(const float* logits, const float* logit_bias, const float* centres, float* depth, float* stats, int B,
+                              int K, long long P, void* stream);
+int ocv_tail_logits_bwd_stats_bf16(const float* logits, const float* logit_bias, const float* centres, const float* stats,
+                                   const float* grad_depth, void* dlT_bf16, float* grad_centres, float* grad_bias, float bias_beta,
+                                   int B, int K, long long P, void* workspace, void* stream);
 long long ocv_tail_logits_bwd_workspace(int B, int K, long long P);
 int ocv_tail_logits_bwd_bf16(const float* logits, const float* logit_bias, const float* centres, const float* grad_depth,
                              void* dlT_bf16, float* grad_centres, float* grad_bias, float bias_beta, int B, int K, long long P,

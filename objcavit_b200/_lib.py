@@ -78,6 +78,8 @@ PROTOTYPES = {
     "ocv_table_grad_commit_f32": (i32, [p, p, i64, f32, p]),
     "ocv_tail_logits_f32": (i32, [p, p, p, p, i32, i32, i64, p]),
     "ocv_tail_logits_bwd_workspace": (i64, [i32, i32, i64]),
+    "ocv_tail_logits_stats_f32": (i32, [p, p, p, p, p, i32, i32, i64, p]),
+    "ocv_tail_logits_bwd_stats_bf16": (i32, [p, p, p, p, p, p, p, p, f32, i32, i32, i64, p, p]),
     "ocv_tail_logits_bwd_bf16": (i32, [p, p, p, p, p, p, p, f32, i32, i32, i64, p, p]),
     "ocv_transpose_bf16": (i32, [p, p, i32, i32, i32, i64, i64, i64, i64, p]),
     "ocv_im2col3x3_bf16": (i32, [p, p, i32, i32, i32, i32, p]),

@@ -52,7 +52,7 @@ __device__ __forceinline__ void softmax_stats(const float* __restrict__ l, long 
 // depth[b,p] = sum_k softmax_k(l[b,k,p] + bias[k]) c[b,k]  — one pass, online softmax
 __global__ void __launch_bounds__(TPB)
 tail_logits_kernel(const float* __restrict__ logits, const float* __restrict__ bias, const float* __restrict__ centres,
-                   float* __restrict__ depth, int K, long long P) {
+                   float* __restrict__ depth, int K, long long P, float* __restrict__ stats /* [B,3,P] (m, s, a) or NULL */) {
   extern __shared__ float cs[];  // [K] centres, [K] bias
   float* bs = cs + K;
   const int b = blockIdx.y;
@@ -67,6 +67,12 @@ tail_logits_kernel(const float* __restrict__ logits, const float* __restrict__ b
   float m, s, a;
   softmax_stats(l, P, bs, cs, K, m, s, a);
   depth[(long long)b * P + px] = a / s;
+  if (stats) {                       // what the backward's first pass would recompute from the same logits: saved, bit for bit
+    float* st = stats + (long long)b * 3 * P + px;
+    st[0] = m;
+    st[P] = s;
+    st[2 * P] = a;
+  }
 }
 
 // dlT[b,k,p] (bf16) = g p (c - depth);   part[b][blk][0][k] = sum over the block's pixels of g p,  part[..][1][k] = of dl.
@@ -76,7 +82,8 @@ tail_logits_kernel(const float* __restrict__ logits, const float* __restrict__ b
 template <int KK>  // K / 32
 __global__ void __launch_bounds__(TPB, 4)
 tail_logits_bwd_kernel(const float* __restrict__ logits, const float* __restrict__ bias, const float* __restrict__ centres,
-                       const float* __restrict__ gdepth, __nv_bfloat16* __restrict__ dlT, float* __restrict__ part, long long P) {
+                       const float* __restrict__ gdepth, __nv_bfloat16* __restrict__ dlT, float* __restrict__ part, long long P,
+                       const float* __restrict__ stats /* [B,3,P] from the forward, or NULL: recompute */) {
   constexpr int K = KK * 32;
   __shared__ float cs[K], bs[K], wacc[TPB / 32][2 * K];
   const int b = blockIdx.y, warp = threadIdx.x / 32, lane = threadIdx.x % 32;
@@ -89,7 +96,14 @@ tail_logits_bwd_kernel(const float* __restrict__ logits, const float* __restrict
   const bool live = px < P;
   const float* l = logits + (long long)b * K * P + (live ? px : 0);
   float m, s, a;
-  softmax_stats(l, P, bs, cs, K, m, s, a);
+  if (stats) {                       // one pass over the logits instead of two
+    const float* st = stats + (long long)b * 3 * P + (live ? px : 0);
+    m = st[0];
+    s = st[P];
+    a = st[2 * P];
+  } else {
+    softmax_stats(l, P, bs, cs, K, m, s, a);
+  }
   const float inv = 1.f / s, d = a * inv, gd = live ? gdepth[(long long)b * P + px] : 0.f;
   __nv_bfloat16* o = dlT + (long long)b * K * P + (live ? px : 0);
 #pragma unroll 1
@@ -296,7 +310,18 @@ extern "C" int ocv_tail_logits_f32(const float* logits, const float* logit_bias,
   OCV_CHECK_SHAPE(K > 0 && K % 4 == 0 && K <= 4096 && B <= 65535);
   if (int s = ocv_require_sm100()) return s;
   tail_logits_kernel<<<dim3((unsigned)ceil_div<long long>(P, TPB), B), TPB, 2 * K * sizeof(float), ocv_stream(stream)>>>(
-      logits, logit_bias, centres, depth, K, P);
+      logits, logit_bias, centres, depth, K, P, nullptr);
+  return ocv_launch_status();
+}
+
+// Same, and the per-pixel softmax statistics (max, sum, centre-weighted sum) into stats [B,3,P] for ocv_tail_logits_bwd_stats_bf16.
+extern "C" int ocv_tail_logits_stats_f32(const float* logits, const float* logit_bias, const float* centres, float* depth, float* stats,
+                                         int B, int K, long long P, void* stream) {
+  OCV_CHECK_ARG(logits && centres && depth && stats && B > 0 && P > 0);
+  OCV_CHECK_SHAPE(K > 0 && K % 4 == 0 && K <= 4096 && B <= 65535);
+  if (int s = ocv_require_sm100()) return s;
+  tail_logits_kernel<<<dim3((unsigned)ceil_div<long long>(P, TPB), B), TPB, 2 * K * sizeof(float), ocv_stream(stream)>>>(
+      logits, logit_bias, centres, depth, K, P, stats);
   return ocv_launch_status();
 }
 
@@ -305,9 +330,21 @@ extern "C" long long ocv_tail_logits_bwd_workspace(int B, int K, long long P) {
   return ((long long)B * ceil_div<long long>(P, TPB) * 2 * K + (long long)B * K) * (long long)sizeof(float);
 }
 
+extern "C" int ocv_tail_logits_bwd_stats_bf16(const float* logits, const float* logit_bias, const float* centres, const float* stats,
+                                              const float* grad_depth, void* dlT_bf16, float* grad_centres, float* grad_bias,
+                                              float bias_beta, int B, int K, long long P, void* workspace, void* stream);
+
 extern "C" int ocv_tail_logits_bwd_bf16(const float* logits, const float* logit_bias, const float* centres, const float* grad_depth,
                                         void* dlT_bf16, float* grad_centres, float* grad_bias, float bias_beta, int B, int K,
                                         long long P, void* workspace, void* stream) {
+  return ocv_tail_logits_bwd_stats_bf16(logits, logit_bias, centres, nullptr, grad_depth, dlT_bf16, grad_centres, grad_bias, bias_beta, B,
+                                        K, P, workspace, stream);
+}
+
+// `stats` = what ocv_tail_logits_stats_f32 saved in the forward (NULL: recomputed in a first pass over the logits)
+extern "C" int ocv_tail_logits_bwd_stats_bf16(const float* logits, const float* logit_bias, const float* centres, const float* stats,
+                                              const float* grad_depth, void* dlT_bf16, float* grad_centres, float* grad_bias,
+                                              float bias_beta, int B, int K, long long P, void* workspace, void* stream) {
   OCV_CHECK_ARG(logits && centres && grad_depth && dlT_bf16 && grad_centres && workspace && B > 0 && P > 0);
   OCV_CHECK_SHAPE(K > 0 && K % 32 == 0 && K <= 512 && B <= 65535);
   if (int s = ocv_require_sm100()) return s;
@@ -317,10 +354,10 @@ extern "C" int ocv_tail_logits_bwd_bf16(const float* logits, const float* logit_
   const dim3 grid(nblk, B);
   cudaStream_t st = ocv_stream(stream);
   switch (K / 32) {
-    case 2: tail_logits_bwd_kernel<2><<<grid, TPB, 0, st>>>(logits, logit_bias, centres, grad_depth, o, part, P); break;
-    case 4: tail_logits_bwd_kernel<4><<<grid, TPB, 0, st>>>(logits, logit_bias, centres, grad_depth, o, part, P); break;
-    case 8: tail_logits_bwd_kernel<8><<<grid, TPB, 0, st>>>(logits, logit_bias, centres, grad_depth, o, part, P); break;
-    case 16: tail_logits_bwd_kernel<16><<<grid, TPB, 0, st>>>(logits, logit_bias, centres, grad_depth, o, part, P); break;
+    case 2: tail_logits_bwd_kernel<2><<<grid, TPB, 0, st>>>(logits, logit_bias, centres, grad_depth, o, part, P, stats); break;
+    case 4: tail_logits_bwd_kernel<4><<<grid, TPB, 0, st>>>(logits, logit_bias, centres, grad_depth, o, part, P, stats); break;
+    case 8: tail_logits_bwd_kernel<8><<<grid, TPB, 0, st>>>(logits, logit_bias, centres, grad_depth, o, part, P, stats); break;
+    case 16: tail_logits_bwd_kernel<16><<<grid, TPB, 0, st>>>(logits, logit_bias, centres, grad_depth, o, part, P, stats); break;
     default: return OCV_E_SHAPE;  // n_bins of the reference's params files: 256 (64 / 128 / 512 also built)
   }
   if (int s = ocv_launch_status()) return s;

@@ -542,13 +542,15 @@ def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, 
     for qi in range(1, min(PIXEL_QUEUES, B)):
         join_branch(x.device, fork, name=f"pixel_q{qi}")
     join_branch(x.device, t.reg_fork, t.centres, t.y_raw, edges, name="regressor")      # the tail needs the bin centres
-    return ops.tail_logits(t.logits, P["conv_out.0.bias"], t.centres).view(B, 1, h, w)
+    depth, t.tail_stats = ops.tail_logits(t.logits, P["conv_out.0.bias"], t.centres, want_stats=True)
+    return depth.view(B, 1, h, w)
 
 
 def _pixel_bwd_bf16_tail(P: Params, G: Params, t, gd: torch.Tensor):
     """-> (dlT [B,K,P] bf16, d loss / d centres [B,K]); accumulates the conv_out bias gradient."""
-    dlT, dcent = ops.tail_logits_bwd(t.logits, P["conv_out.0.bias"], t.centres, gd, grad_bias=G["conv_out.0.bias"], beta=1.0)
-    t.logits = None
+    dlT, dcent = ops.tail_logits_bwd(t.logits, P["conv_out.0.bias"], t.centres, gd, grad_bias=G["conv_out.0.bias"], beta=1.0,
+                                     stats=getattr(t, "tail_stats", None))
+    t.logits = t.tail_stats = None
     return dlT, dcent
 
 

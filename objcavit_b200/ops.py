@@ -919,26 +919,35 @@ def dropout_act_bwd(dy: torch.Tensor, out: torch.Tensor, act: int, p: float, see
 
 # ---- training step, tensor-core pixel path (csrc/train_pixel_bf16.cu) -------------------------------------------------
 
-def tail_logits(logits: torch.Tensor, bias, centres: torch.Tensor) -> torch.Tensor:
-    """depth [B,P] = sum_k softmax_k(logits[b,k,p] + bias[k]) centres[b,k]; logits channel-major fp32 [B,K,P]."""
+def tail_logits(logits: torch.Tensor, bias, centres: torch.Tensor, want_stats: bool = False):
+    """depth [B,P] = sum_k softmax_k(logits[b,k,p] + bias[k]) centres[b,k]; logits channel-major fp32 [B,K,P].
+    ``want_stats``: -> (depth, stats [B,3,P]) — the softmax statistics ``tail_logits_bwd`` would otherwise recompute."""
     _chk(logits, torch.float32, "logits"); _chk(centres, torch.float32, "centres")
     assert logits.is_contiguous() and centres.is_contiguous()
     B, K, Pn = logits.shape
     depth = torch.empty(B, Pn, device=logits.device, dtype=torch.float32)
+    if want_stats:
+        stats = torch.empty(B, 3, Pn, device=logits.device, dtype=torch.float32)
+        _call("ocv_tail_logits_stats_f32", logits.data_ptr(), _ptr(bias), centres.data_ptr(), depth.data_ptr(), stats.data_ptr(), B, K,
+              Pn, _stream())
+        return depth, stats
     _call("ocv_tail_logits_f32", logits.data_ptr(), _ptr(bias), centres.data_ptr(), depth.data_ptr(), B, K, Pn, _stream())
     return depth
 
 
-def tail_logits_bwd(logits: torch.Tensor, bias, centres: torch.Tensor, grad_depth: torch.Tensor, grad_bias=None, beta: float = 1.0):
-    """-> (dlT [B,K,P] bf16, grad_centres [B,K]); ``grad_bias`` [K] is beta-accumulated in place when given."""
+def tail_logits_bwd(logits: torch.Tensor, bias, centres: torch.Tensor, grad_depth: torch.Tensor, grad_bias=None, beta: float = 1.0,
+                    stats=None):
+    """-> (dlT [B,K,P] bf16, grad_centres [B,K]); ``grad_bias`` [K] is beta-accumulated in place when given.  ``stats``: from
+    ``tail_logits(..., want_stats=True)`` on the same logits (one pass over the logits instead of two; same result bit for bit)."""
     _chk(logits, torch.float32, "logits"); _chk(grad_depth, torch.float32, "grad_depth")
     assert logits.is_contiguous() and centres.is_contiguous() and grad_depth.is_contiguous()
     B, K, Pn = logits.shape
     dlT = torch.empty(B, K, Pn, device=logits.device, dtype=torch.bfloat16)
     dcent = torch.empty(B, K, device=logits.device, dtype=torch.float32)
     ws = _workspace(_lib.lib().ocv_tail_logits_bwd_workspace(B, K, Pn), logits.device, "tail_logits_bwd")
-    _call("ocv_tail_logits_bwd_bf16", logits.data_ptr(), _ptr(bias), centres.data_ptr(), grad_depth.data_ptr(), dlT.data_ptr(),
-          dcent.data_ptr(), _ptr(grad_bias), float(beta), B, K, Pn, ws.data_ptr(), _stream(), launches=3)
+    assert stats is None or (stats.is_contiguous() and tuple(stats.shape) == (B, 3, Pn) and stats.dtype == torch.float32)
+    _call("ocv_tail_logits_bwd_stats_bf16", logits.data_ptr(), _ptr(bias), centres.data_ptr(), _ptr(stats), grad_depth.data_ptr(),
+          dlT.data_ptr(), dcent.data_ptr(), _ptr(grad_bias), float(beta), B, K, Pn, ws.data_ptr(), _stream(), launches=3)
     return dlT, dcent
 
 

@@ -43,6 +43,9 @@ def test_tail_logits_forward_backward(cuda):
     assert rel_err(gb - 1.0, b64.grad.float()) < 1e-4
     dlT2, dcent2 = ops.tail_logits_bwd(logits, bias, centres, g)
     assert torch.equal(dlT, dlT2) and torch.equal(dcent, dcent2)      # deterministic
+    depth3, stats = ops.tail_logits(logits, bias, centres, want_stats=True)   # statistics saved by the forward: one-pass backward
+    dlT3, dcent3 = ops.tail_logits_bwd(logits, bias, centres, g, stats=stats)
+    assert torch.equal(depth3, depth) and torch.equal(dlT3, dlT) and torch.equal(dcent3, dcent)
 
 
 def test_transpose_and_im2col(cuda):
