@@ -521,6 +521,9 @@ def _pixel_prologue(P: Params, pre: str, t, x: torch.Tensor) -> None:
         # B operand of the patch-embedding weight gradient (backward): needs only x; 0.23 ms of HBM-bound work that fits under the
         # latency-bound encoder chain here, while anywhere in the backward it competes with the HBM-bound tail kernels
         t.unf = ops.patch_unfold_bf16(x, 16) if UNFOLD_IN_FORWARD else None
+        # channel-major copy of the conv output (B operand of the dMb GEMMs of the backward): also a function of x only
+        Bq, hq, wq, Cq = t.x3h.shape
+        t.x3T = ops.transpose_bf16(t.x3h.view(Bq, hq * wq, Cq)) if UNFOLD_IN_FORWARD else None
 
 
 def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, Q: int, edges=None) -> torch.Tensor:
@@ -563,7 +566,12 @@ def _pixel_bwd_bf16_rest(P: Params, G: Params, t, dlT: torch.Tensor, dtok: torch
     Wout = P["conv_out.0.weight"].view(-1, Q)
     K = Wout.shape[0]
     # d Mb -> conv_out weight and queries: the only part the token-path backward waits for
-    x3T = ops.transpose_bf16(t.x3h.view(B, Pn, C))                            # [B,C,P]
+    x3T = getattr(t, "x3T", None)                                             # [B,C,P]: made in the forward on the pixel branch
+    if x3T is None:
+        x3T = ops.transpose_bf16(t.x3h.view(B, Pn, C))
+    else:
+        x3T.record_stream(torch.cuda.current_stream(dev))
+        t.x3T = None
     dMb = torch.empty(B, K, E, device=dev, dtype=torch.float32)
     sk = max(1, min(64, Pn // 1024))
     fork = fork_branch(dev, 32)
