@@ -201,3 +201,29 @@ def test_graph_replay_draws_new_dropout_masks_every_step_and_is_reproducible(cud
     assert len(set(runs[0][2:])) == 4, runs[0]                            # replays: a new mask stream every step
     mean = lambda v: sum(v) / len(v)
     assert abs(mean(runs[0]) - mean(runs[2])) < 0.05 * abs(mean(runs[2])), (runs[0], runs[2])
+
+
+def test_branch_streams_do_not_change_a_single_bit_of_the_step(cuda):
+    """Every scheduling change of the step (object / pixel / loss / regressor branches, the per-image GEMM queues, the forward
+    hoists) moves launches between streams without touching a kernel: three optimizer steps with dropout on, from the same
+    torch seed, must leave exactly the parameters of the single-stream step (``BRANCH_OBJECTS = 0``)."""
+    import objcavit_b200.engine_train as et
+    args = builtin_args("nyu_ocv_learned_bbox_wh")
+    with open(os.path.join(GOLD, "manifest_nyu_ocv_learned_bbox_wh.json")) as f:
+        sd = synth.make_state_dict(json.load(f), seed=5)
+    x, objs, boxes, gt, mask = _fullsize_inputs(cuda)
+    saved = (et.BRANCH_OBJECTS, et.UNFOLD_IN_FORWARD, et.PIXEL_QUEUES)
+    runs = []
+    try:
+        for branches, hoist, queues in ((0, False, 1), saved):
+            et.BRANCH_OBJECTS, et.UNFOLD_IN_FORWARD, et.PIXEL_QUEUES = branches, hoist, queues
+            head = build_head(args, precision="bf16").to(cuda).train()
+            head.load_state_dict(sd)
+            torch.manual_seed(11)
+            tr = HeadTrainer(head, lr=3.57e-4, weight_decay=0.1, clip_grad_norm=0.1)
+            losses = [tr.loss_value(*tr.step(x, list(objs), list(boxes), gt, mask)) for _ in range(3)]
+            runs.append((losses, tr.flat_params.clone()))
+    finally:
+        et.BRANCH_OBJECTS, et.UNFOLD_IN_FORWARD, et.PIXEL_QUEUES = saved
+    assert saved[0] != 0, "the default configuration is the branched one"
+    assert runs[0][0] == runs[1][0] and torch.equal(runs[0][1], runs[1][1])
