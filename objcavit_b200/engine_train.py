@@ -106,6 +106,8 @@ def join_side(device, name: Optional[str] = None) -> None:
 # `on_branch` runs a region there, `join_branch` orders the launching stream after it.  No kernel changes: bit-identical.
 # ----------------------------------------------------------------------------------------------------------------------
 import os as _os
+PIXEL_LATE = _os.environ.get("OCV_PIXEL_LATE", "1") == "1"   # conv3x3 / unfold / transpose of the pixel branch start after the patch embedding
+CHAIN_PRIORITY = _os.environ.get("OCV_CHAIN_PRIORITY", "1") == "1"
 PIXEL_QUEUES = max(1, int(_os.environ.get("OCV_PIXEL_QUEUES", "2")))   # the per-image pixel GEMMs alternate over this many queues
 UNFOLD_IN_FORWARD = _os.environ.get("OCV_UNFOLD_FWD", "1") == "1"
 BRANCH_OBJECTS = int(_os.environ.get("OCV_BRANCH", "63"))  # bit 0: object branch forward, bit 1: backward, bit 2: pixel prologue, bit 3: chamfer loss, bit 4: regressor, bit 5: per-image pixel GEMMs over two queues
@@ -115,7 +117,12 @@ _branch_streams = {}
 def _branch(device, name: str = "objects") -> "torch.cuda.Stream":
     key = (torch.device(device).index or 0, name)
     if key not in _branch_streams:
-        _branch_streams[key] = torch.cuda.Stream(device)
+        # Branches that carry pieces of the dependency chain (object encoder, regressor, loss) get a high-priority stream, the
+        # "pixel" queues (whole-GPU HBM-bound work hoisted off the chain) stay at the default = lowest priority: when SM slots
+        # free up, the block scheduler serves the chain first.  (HeadTrainer captures the step on a high-priority stream too; stream
+        # priorities are recorded into the kernel nodes of the graph.)
+        prio = 0 if (name.startswith("pixel") or not CHAIN_PRIORITY) else -1
+        _branch_streams[key] = torch.cuda.Stream(device, priority=prio)
     return _branch_streams[key]
 
 
@@ -422,6 +429,7 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
     t.shape = (B, C, h, w)
     pre = "adaptive_bins_layer." if cfg["kind"] == "adabins" else "objcavit."
     if cfg.get("pixel") == "bf16":
+        t.late_P, t.late_pre = P, pre
         _pixel_prologue(P, pre, t, x)
     if cfg["kind"] == "adabins":
         pt = pre + "patch_transformer."
@@ -499,6 +507,12 @@ def _patch_embed(t, x: torch.Tensor, w: torch.Tensor, bias, pos, patch_size: int
             cur.wait_event(t.xh_ready)
             t.xh.record_stream(cur)
         tok = ops.patch_embed_bf16(t.xh, ops.pack_patch_weights_bf16(w), bias, pos, patch_size, want32=True, want16=False)[0]
+        if getattr(t, "pixel_rest_pending", False):      # the rest of the pixel branch, ordered after the patch embedding
+            t.pixel_rest_pending = False
+            t.xh_keep = t.xh
+            late = fork_branch(x.device, 4)
+            with on_branch(x.device, late, x, t.xh, name="pixel"):
+                _pixel_prologue_rest(t.late_P, t.late_pre, t, x)
         t.xh = None
         return tok
     return ops.patch_embed(x, w, bias, pos, patch_size)
@@ -517,13 +531,24 @@ def _pixel_prologue(P: Params, pre: str, t, x: torch.Tensor) -> None:
         if t.conv_fork is not None:
             t.xh_ready = torch.cuda.Event()
             t.xh_ready.record(torch.cuda.current_stream(dev))
-        t.x3h = ops.conv3x3_nhwc_bf16(xh, ops.pack_conv3x3_bf16(P[pre + "conv3x3.weight"]), P[pre + "conv3x3.bias"])
-        # B operand of the patch-embedding weight gradient (backward): needs only x; 0.23 ms of HBM-bound work that fits under the
-        # latency-bound encoder chain here, while anywhere in the backward it competes with the HBM-bound tail kernels
-        t.unf = ops.patch_unfold_bf16(x, 16) if UNFOLD_IN_FORWARD else None
-        # channel-major copy of the conv output (B operand of the dMb GEMMs of the backward): also a function of x only
-        Bq, hq, wq, Cq = t.x3h.shape
-        t.x3T = ops.transpose_bf16(t.x3h.view(Bq, hq * wq, Cq)) if UNFOLD_IN_FORWARD else None
+        t.pixel_rest_pending = PIXEL_LATE and t.conv_fork is not None
+        if not t.pixel_rest_pending:
+            _pixel_prologue_rest(P, pre, t, x)
+
+
+def _pixel_prologue_rest(P: Params, pre: str, t, x: torch.Tensor) -> None:
+    """conv3x3 and the two x-only operands of the backward; called inside the "pixel" branch.  With ``PIXEL_LATE`` the forward calls
+    it after the patch embedding has been issued (ordered after it), so that these whole-GPU kernels (a persistent 148-CTA conv,
+    0.5 ms of HBM-bound copies) run under the encoder chain instead of delaying the positional MLPs and the patch embedding."""
+    t.x3h = ops.conv3x3_nhwc_bf16(t.xh_keep if getattr(t, "xh_keep", None) is not None else t.xh,
+                                  ops.pack_conv3x3_bf16(P[pre + "conv3x3.weight"]), P[pre + "conv3x3.bias"])
+    # B operand of the patch-embedding weight gradient (backward): needs only x; 0.23 ms of HBM-bound work that fits under the
+    # latency-bound encoder chain here, while anywhere in the backward it competes with the HBM-bound tail kernels
+    t.unf = ops.patch_unfold_bf16(x, 16) if UNFOLD_IN_FORWARD else None
+    # channel-major copy of the conv output (B operand of the dMb GEMMs of the backward): also a function of x only
+    Bq, hq, wq, Cq = t.x3h.shape
+    t.x3T = ops.transpose_bf16(t.x3h.view(Bq, hq * wq, Cq)) if UNFOLD_IN_FORWARD else None
+    t.xh_keep = None
 
 
 def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, Q: int, edges=None) -> torch.Tensor:

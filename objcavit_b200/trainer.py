@@ -62,6 +62,7 @@ class HeadTrainer:
         self.head = head
         self.graph = False
         self._graphs, self._graph_seen, self._graph_pool, self._salt = {}, {}, None, None
+        self._capture_stream = None
         self.group = group
         self.lr, self.wd, self.betas, self.eps, self.clip = lr, weight_decay, betas, eps, clip_grad_norm
         self.coeffs = loss_coeffs
@@ -192,7 +193,9 @@ class HeadTrainer:
             torch.cuda.synchronize(dev)
             g = torch.cuda.CUDAGraph()
             l0 = ops.launch_count
-            with torch.cuda.graph(g, pool=self._graph_pool):
+            if self._capture_stream is None:      # the launching stream of the captured step: high priority (engine_train._branch)
+                self._capture_stream = torch.cuda.Stream(dev, priority=-1 if engine_train.CHAIN_PRIORITY else 0)
+            with torch.cuda.graph(g, pool=self._graph_pool, stream=self._capture_stream):
                 self._salt.add_(-7046029254386353131)       # 0x9E3779B97F4A7C15 as int64: a new mask stream per replay
                 self.grads.zero()
                 l1, l2 = self.forward_backward(st["x"], None if object_features is None else list(st["obj_views"]),
