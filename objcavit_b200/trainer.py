@@ -195,7 +195,9 @@ class HeadTrainer:
             l0 = ops.launch_count
             if self._capture_stream is None:      # the launching stream of the captured step: high priority (engine_train._branch)
                 self._capture_stream = torch.cuda.Stream(dev, priority=-1 if engine_train.CHAIN_PRIORITY else 0)
-            with torch.cuda.graph(g, pool=self._graph_pool, stream=self._capture_stream):
+            # thread_local: other threads of the process (the NCCL watchdog polling its events, the input prefetcher) may make
+            # CUDA calls while this thread captures
+            with torch.cuda.graph(g, pool=self._graph_pool, stream=self._capture_stream, capture_error_mode="thread_local"):
                 self._salt.add_(-7046029254386353131)       # 0x9E3779B97F4A7C15 as int64: a new mask stream per replay
                 self.grads.zero()
                 l1, l2 = self.forward_backward(st["x"], None if object_features is None else list(st["obj_views"]),
