@@ -270,6 +270,60 @@ def run_train_case(name: str):
                os.path.join(GOLD, f"{name}.pt"))
 
 
+def head_args_subset(args):
+    """The keys of a params file the head reads (SURVEY.md §8b "args keys consumed by the head")."""
+    model = args["model"]["name"]
+    dataset = args["basic"]["dataset"]
+    out = {"model": {"name": model}, "basic": {"dataset": dataset}}
+    m = {k: args[model][k] for k in ("n_bins", "do_final_upscale") if k in args[model]}
+    if "objcavit" in args[model]:
+        m["objcavit"] = dict(args[model]["objcavit"])
+    out[model] = m
+    if model != "graphbins" and "graphbins" in args and "objcavit" in args["graphbins"]:
+        out["graphbins"] = {"objcavit": dict(args["graphbins"]["objcavit"])}
+    out[dataset] = {k: args[dataset][k] for k in ("min_depth", "max_depth", "dimensions_train", "dimensions_test") if k in args[dataset]}
+    return out
+
+
+def dump_params_sweep():
+    """Every ``params/*.yaml`` of the reference ("all must construct through the new modules"): build the
+    UNMODIFIED reference head for it, record its ``state_dict`` {key: shape} (deduplicated by content hash) and the head-relevant
+    subset of the file.  ``tests/test_modules_cpu.py::test_params_sweep`` builds the product head from that subset (and, in the
+    build container, from the real file) and compares the surfaces."""
+    import glob
+    import hashlib
+
+    import yaml
+
+    from objcavit_b200.config import AttrDict
+    from oracle.ref_shim import REFERENCE_ROOT
+
+    files, manifests, skipped = {}, {}, {}
+    for path in sorted(glob.glob(os.path.join(REFERENCE_ROOT, "params", "*.yaml"))):
+        name = os.path.basename(path)
+        try:
+            with open(path) as f:
+                raw = yaml.safe_load(f)
+        except yaml.YAMLError as e:           # SURVEY.md F14: one shipped file is not valid YAML
+            skipped[name] = "not valid YAML: " + str(e).splitlines()[0]
+            continue
+        if not isinstance(raw, dict) or "model" not in raw:
+            skipped[name] = "no model section (basicParams.yaml: validation-time overrides only)"
+            continue
+        args = AttrDict(raw)
+        torch.manual_seed(0)
+        ref = ReferenceHead(args)
+        man = {k: list(v.shape) for k, v in ref.state_dict().items()}
+        blob = json.dumps(man, sort_keys=True)
+        h = hashlib.sha1(blob.encode()).hexdigest()[:12]
+        manifests[h] = man
+        files[name] = {"args": head_args_subset(raw), "manifest": h, "n_keys": len(man),
+                       "n_params": int(sum(p.numel() for p in ref.parameters()))}
+    with open(os.path.join(GOLD, "params_sweep.json"), "w") as f:
+        json.dump({"files": files, "manifests": manifests, "skipped": skipped}, f, indent=0, sort_keys=True)
+    print(f"[pin] params sweep: {len(files)} files -> {len(manifests)} distinct state_dict surfaces; skipped {skipped}")
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     torch.set_num_threads(max(1, os.cpu_count() or 1))
@@ -280,8 +334,12 @@ def main():
         run_case(name)
     for name in TRAIN_CASES:
         run_train_case(name)
+    dump_params_sweep()
     print("golden fixtures written to", GOLD)
 
 
 if __name__ == "__main__":
-    main()
+    if "--params-sweep" in sys.argv:       # only the params sweep (leaves the other fixtures untouched)
+        dump_params_sweep()
+    else:
+        main()

@@ -61,3 +61,30 @@ def test_training_mode_has_no_cpu_path_either():
 def test_attrdict_access_styles():
     a = AttrDict({"graphbins": {"objcavit": {"x": 1}}, "model": {"name": "graphbins"}})
     assert a[a.model.name].objcavit.x == 1 and a.graphbins.objcavit.get("no_obj_sa") is None
+
+
+# ---- every params file of the reference ("all must construct through the new modules") -----------------
+with open(os.path.join(GOLD, "params_sweep.json")) as _f:
+    SWEEP = json.load(_f)          # oracle/make_golden.py:dump_params_sweep — state_dict surfaces of the UNMODIFIED reference heads
+
+
+@pytest.mark.parametrize("fname", sorted(SWEEP["files"]), ids=[n[:-5] for n in sorted(SWEEP["files"])])
+def test_params_sweep(fname):
+    """The product head built from each reference params file has exactly the reference head's ``state_dict`` keys and shapes
+    (checkpoint drop-in, F9).  The committed fixture carries the head-relevant keys of each file; in the build container the
+    real file is loaded through ``load_params`` as well."""
+    entry = SWEEP["files"][fname]
+    want = SWEEP["manifests"][entry["manifest"]]
+    head = build_head(AttrDict(entry["args"]))
+    got = {k: list(v.shape) for k, v in head.state_dict().items()}
+    assert got == want
+    assert len(got) == entry["n_keys"] and sum(p.numel() for p in head.parameters()) == entry["n_params"]
+    real = os.path.join(os.environ.get("OBJCAVIT_REFERENCE_ROOT", "/root/reference"), "params", fname)
+    if os.path.isfile(real):
+        from objcavit_b200.config import load_params
+        head2 = build_head(load_params(real))
+        assert {k: list(v.shape) for k, v in head2.state_dict().items()} == want
+
+
+def test_params_sweep_covers_the_reference_tree():
+    assert len(SWEEP["files"]) == 56 and len(SWEEP["skipped"]) == 1      # 57 shipped files, one is not valid YAML (F14)
