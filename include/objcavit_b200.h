@@ -305,6 +305,8 @@ int ocv_dropout_act_bwd_f32(const float* dy, const float* out, float* dx, long l
  * each dropout kernel uses seed ^ *device_salt.  It exists for CUDA-graph replay of the training step, where the site seeds are
  * frozen kernel arguments: the caller changes the word between replays.  Process-wide (one process per GPU). */
 int ocv_set_dropout_salt(const unsigned long long* device_salt);
+/* Clear the salt only if `owner` is the pointer currently installed (a trainer going away must not disarm another one's). */
+int ocv_release_dropout_salt(const unsigned long long* owner);
 int ocv_mha_core_dropout_f32(const float* q, const float* k, const float* v, float* out, const uint8_t* key_padding_mask,
                              int B, int Sq, int Sk, int heads, int d, long long q_bstride, int q_rstride, long long k_bstride,
                              int k_rstride, long long v_bstride, int v_rstride, long long o_bstride, int o_rstride, float drop_p,

@@ -24,6 +24,7 @@ PROTOTYPES = {
     "ocv_abi_version": (i32, []),
     "ocv_device_check": (i32, [i32]),
     "ocv_set_dropout_salt": (i32, [p]),
+    "ocv_release_dropout_salt": (i32, [p]),
     "ocv_status_string": (C.c_char_p, [i32]),
     "ocv_linear_f32": (i32, [p, p, p, p, p, i32, i32, i32, i32, i32, i32, i32, i32, i32, i64, i64, i64, p]),
     "ocv_patch_embed_f32_workspace": (i64, [i32, i32, i32, i32, i32, i32]),

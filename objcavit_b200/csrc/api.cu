@@ -30,6 +30,11 @@ extern "C" int ocv_set_dropout_salt(const unsigned long long* device_salt) {
   g_dropout_salt = device_salt;
   return OCV_OK;
 }
+// Clears the process-wide salt only when `owner` still owns it (several trainers may be alive in one process).
+extern "C" int ocv_release_dropout_salt(const unsigned long long* owner) {
+  if (g_dropout_salt == owner) g_dropout_salt = nullptr;
+  return OCV_OK;
+}
 
 extern "C" int ocv_abi_version(void) { return 1; }
 

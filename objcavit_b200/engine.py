@@ -108,7 +108,10 @@ def mvit_forward(P: Params, pre: str, x: torch.Tensor, n_query: int = 128, norm:
 # a4-a6: ObjCAViT
 # ----------------------------------------------------------------------------------------------------
 
-_OFFSETS_CACHE = {}
+_OFFSETS_CACHE = {}        # young generation: (device index, values) -> (int32 device tensor, upload event | None)
+_OFFSETS_OLD = {}          # previous generation: entries not hit since the last rotation
+_OFFSETS_GENERATION = 512  # rotation period (insertions)
+offsets_capture_refs = None    # a list while a caller (HeadTrainer graph capture) wants to own every offsets tensor handed out
 
 
 class ObjectBatch:
@@ -128,12 +131,23 @@ class ObjectBatch:
     def _to_device(self, values):
         """int32 device copy of a small host list.  Cached per (device, values): batches with the same object counts reuse the
         tensor (never written by any kernel), so a steady-state step issues no host->device copy here — which is also what lets
-        the training step be captured into a CUDA graph (a copy out of a transient pinned buffer must not be replayed)."""
+        the training step be captured into a CUDA graph (a copy out of a transient pinned buffer must not be replayed).
+
+        Lifetime: a two-generation cache.  Every ``_OFFSETS_GENERATION`` insertions the young generation becomes the old one
+        and the previous old one is dropped; a hit in the old generation promotes the entry.  A tensor is therefore freed only
+        after it has gone unused for at least one whole generation (hundreds of steps), long after any kernel on any branch
+        stream that read it has finished — no per-stream ``record_stream`` bookkeeping is needed.  Captured CUDA graphs bake the
+        addresses into kernel arguments and may be replayed arbitrarily later: while ``offsets_capture_refs`` is a list (set by
+        ``HeadTrainer`` around a capture) every tensor handed out is appended to it, and the graph entry keeps that list."""
         if not self.rows.is_cuda:
             return torch.tensor(values, dtype=torch.int32)
         dev = self.rows.device
         key = (dev.index, tuple(values))
         hit = _OFFSETS_CACHE.get(key)
+        if hit is None:
+            hit = _OFFSETS_OLD.pop(key, None)
+            if hit is not None:
+                _OFFSETS_CACHE[key] = hit
         if hit is not None:
             t, ev = hit
             if ev is not None:
@@ -141,13 +155,17 @@ class ObjectBatch:
                     _OFFSETS_CACHE[key] = (t, None)
                 else:
                     torch.cuda.current_stream(dev).wait_event(ev)
-            return t
-        if len(_OFFSETS_CACHE) >= 512:
-            _OFFSETS_CACHE.clear()
-        t = torch.tensor(values, dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
-        ev = torch.cuda.Event()
-        ev.record(torch.cuda.current_stream(dev))
-        _OFFSETS_CACHE[key] = (t, ev)
+        else:
+            if len(_OFFSETS_CACHE) >= _OFFSETS_GENERATION:
+                _OFFSETS_OLD.clear()
+                _OFFSETS_OLD.update(_OFFSETS_CACHE)
+                _OFFSETS_CACHE.clear()
+            t = torch.tensor(values, dtype=torch.int32).pin_memory().to(dev, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(torch.cuda.current_stream(dev))
+            _OFFSETS_CACHE[key] = (t, ev)
+        if offsets_capture_refs is not None:
+            offsets_capture_refs.append(t)
         return t
 
     def uniform_offsets(self, n_max: int) -> torch.Tensor:

@@ -92,10 +92,10 @@ class DepthMetrics:
 def object_frontend(xyxy_list: List[Optional[torch.Tensor]], reverse: bool = True):
     """Detections per image as corner boxes (``None`` / empty = no detection) -> (list of centre/size boxes or None, list of
     relative-size bucket tensors (index into ``REL_SIZE_SCALE``; -1 = lone object) or None)."""
-    dev = next(t.device for t in xyxy_list if t is not None)
     counts = [0 if t is None else int(t.shape[0]) for t in xyxy_list]
-    if sum(counts) == 0:
+    if sum(counts) == 0:        # no detection in the whole batch (all None: what Yolov7Wrapper returns, common at batch size 1)
         return [None] * len(xyxy_list), [None] * len(xyxy_list)
+    dev = next(t.device for t in xyxy_list if t is not None and t.shape[0] > 0)
     rows = torch.cat([t.to(device=dev, dtype=torch.float32) for t in xyxy_list if t is not None and t.shape[0] > 0], 0).contiguous()
     offs = [0]
     for c in counts:

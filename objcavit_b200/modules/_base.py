@@ -17,7 +17,19 @@ class KernelModule(nn.Module):
         if cache is None:
             cache = {k: v for k, v in self.named_parameters()}
             self.__dict__["_ocv_param_cache"] = cache
-        return {k: v.data for k, v in cache.items()}
+        # detach() (not .data): the view shares the parameter's version counter, so load_state_dict, an optimizer step or any
+        # other in-place update shows up in ``_version`` and invalidates the derived bf16 / packed copies (ops.NativeHead.bind,
+        # engine_bf16.Packed.signature).  Writes through ``p.data`` bypass torch's version counters by design: callers doing
+        # that must call :meth:`invalidate_caches`.
+        return {k: v.detach() for k, v in cache.items()}
+
+    def invalidate_caches(self):
+        """Drop every derived copy of the parameters (bf16 GEMM weights, packed conv weights, native plan).  Needed only after
+        writes torch cannot see (``p.data.copy_``, a kernel writing into parameter storage); everything else is detected."""
+        for m in self.modules():
+            m.__dict__.pop("_ocv_param_cache", None)
+            m.__dict__.pop("_ocv_packed", None)
+            m.__dict__.pop("_ocv_native", None)
 
     def _apply(self, fn, *a, **kw):  # .to() / .cuda() / .half(): drop derived caches
         self.__dict__.pop("_ocv_param_cache", None)
@@ -31,8 +43,8 @@ class KernelModule(nn.Module):
         if torch.is_grad_enabled() and (any(torch.is_tensor(t) and t.requires_grad for t in tensors)
                                         or any(p.requires_grad for p in self.parameters())):
             raise NotImplementedError(
-                "objcavit_b200: the kernel path implements inference (eval + no_grad); the training step "
-                "(backward kernels, SURVEY.md config 5) is not built yet — wrap the call in torch.no_grad().")
+                "objcavit_b200: gradients w.r.t. these inputs are not produced (the decoder is frozen in config 5, SURVEY.md "
+                "§8d); pass features.detach(), or wrap the call in torch.no_grad() for inference.")
 
     @property
     def device(self):  # the reference modules are LightningModules and use self.device

@@ -195,8 +195,12 @@ class HostPipeline:
         self.done = [None, None]
 
     @torch.no_grad()
-    def __call__(self, feats_nhwc_host, object_features=None, object_xywh_list=None, depth_out=None, edges_out=None):
-        """feats_nhwc_host: pinned [B,h,w,128] bf16.  Returns (depth [B,1,h,w] fp32, bin_edges [B,K+1]) in pinned host memory."""
+    def __call__(self, feats_nhwc_host, object_features=None, object_xywh_list=None, depth_out=None, edges_out=None,
+                 sync: bool = True):
+        """feats_nhwc_host: pinned [B,h,w,128] bf16.  Returns (depth [B,1,h,w] fp32, bin_edges [B,K+1]) in pinned host memory.
+        The results live in HOST memory, so the call waits (``sync=True``, the default) until the last device->host copy has
+        landed before it returns; with ``sync=False`` it returns at once and the caller must ``pipe.done_event.synchronize()``
+        before reading the outputs on the CPU."""
         head = self.head
         dev = head.device
         B, h, w, C = feats_nhwc_host.shape
@@ -215,6 +219,8 @@ class HostPipeline:
                 if self.done[slot] is not None:
                     self.h2d.wait_event(self.done[slot])      # the chunk that used this buffer two steps ago has been consumed
                 if self.xbuf[slot] is None or self.xbuf[slot].shape[0] < hi - lo or self.xbuf[slot].shape[1:] != (h, w, C):
+                    if self.xbuf[slot] is not None:
+                        self.xbuf[slot].record_stream(cur)    # the compute stream may still read the buffer being replaced
                     self.xbuf[slot] = torch.empty(max(hi - lo, (B + n - 1) // n), h, w, C, device=dev, dtype=torch.bfloat16)
                 x = self.xbuf[slot][:hi - lo]
                 x.copy_(feats_nhwc_host[lo:hi], non_blocking=True)
@@ -239,6 +245,10 @@ class HostPipeline:
             results.append(out)                                # keep device tensors alive until the copies are done
         cur.wait_stream(self.d2h)
         self._keep = results
+        self.done_event = torch.cuda.Event()
+        self.done_event.record(self.d2h)                       # after the last device->host copy
+        if sync:
+            self.done_event.synchronize()                      # stream order is not host order: the outputs are host memory
         return depth_out, edges_out
 
 

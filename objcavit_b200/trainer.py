@@ -52,9 +52,13 @@ class OneCycle:
 class HeadTrainer:
     """Owns the flat parameter / gradient / AdamW-moment buffers of one head replica and runs whole training steps.
 
+    ``MAX_GRAPHS``: captured step graphs kept alive (LRU over input signatures); the seen-signature counter is bounded too.
+
     The head's ``nn.Parameter``s are re-pointed at slices of ONE flat fp32 buffer (their values are preserved; ``state_dict``
     and checkpoints are unchanged), so the optimizer step is a single kernel over [param | grad | exp_avg | exp_avg_sq].
     """
+
+    MAX_GRAPHS = 8
 
     def __init__(self, head, lr: float = 0.000357, weight_decay: float = 0.1, betas=(0.9, 0.999), eps: float = 1e-8,
                  clip_grad_norm: float = 0.1, loss_coeffs=(1.0, 0.1), schedule: Optional[OneCycle] = None, group=None,
@@ -150,15 +154,25 @@ class HeadTrainer:
         if on and self._salt is None:
             self._salt = torch.zeros(1, device=self.flat_params.device, dtype=torch.int64) + int(torch.randint(0, 2 ** 62, (1,)).item())
             self._graph_pool = torch.cuda.graph_pool_handle()
-        _lib.check(_lib.lib().ocv_set_dropout_salt(self._salt.data_ptr() if on else None), "ocv_set_dropout_salt")
-        if not on:
+        if on:
+            self._arm_salt()
+        else:
+            if self._salt is not None:      # only if the process-wide pointer is still ours (another live trainer may own it)
+                _lib.check(_lib.lib().ocv_release_dropout_salt(self._salt.data_ptr()), "ocv_release_dropout_salt")
             self._graphs.clear()
+
+    def _arm_salt(self) -> None:
+        """Install THIS trainer's salt word as the process-wide dropout salt (a host pointer write).  Done before every step of
+        a graph-mode trainer, so a second trainer in the process (or one that was deleted) cannot leave a capture with a NULL or
+        foreign salt — which would freeze the dropout masks of every replay."""
+        from . import _lib
+        _lib.check(_lib.lib().ocv_set_dropout_salt(self._salt.data_ptr()), "ocv_set_dropout_salt")
 
     def __del__(self):
         try:
-            if self._salt is not None and self.graph:
+            if self._salt is not None:
                 from . import _lib
-                _lib.lib().ocv_set_dropout_salt(None)
+                _lib.lib().ocv_release_dropout_salt(self._salt.data_ptr())
         except Exception:
             pass
 
@@ -197,13 +211,22 @@ class HeadTrainer:
                 self._capture_stream = torch.cuda.Stream(dev, priority=-1 if engine_train.CHAIN_PRIORITY else 0)
             # thread_local: other threads of the process (the NCCL watchdog polling its events, the input prefetcher) may make
             # CUDA calls while this thread captures
-            with torch.cuda.graph(g, pool=self._graph_pool, stream=self._capture_stream, capture_error_mode="thread_local"):
-                self._salt.add_(-7046029254386353131)       # 0x9E3779B97F4A7C15 as int64: a new mask stream per replay
-                self.grads.zero()
-                l1, l2 = self.forward_backward(st["x"], None if object_features is None else list(st["obj_views"]),
-                                               None if object_features is None else list(st["box_views"]), st["gt"], st["mask"])
+            from . import engine
+            refs = engine.offsets_capture_refs = []      # the graph bakes in the addresses of the CSR offset tensors: own them
+            try:
+                with torch.cuda.graph(g, pool=self._graph_pool, stream=self._capture_stream, capture_error_mode="thread_local"):
+                    self._salt.add_(-7046029254386353131)       # 0x9E3779B97F4A7C15 as int64: a new mask stream per replay
+                    self.grads.zero()
+                    l1, l2 = self.forward_backward(st["x"], None if object_features is None else list(st["obj_views"]),
+                                                   None if object_features is None else list(st["box_views"]), st["gt"], st["mask"])
+            finally:
+                engine.offsets_capture_refs = None
+            st["_offset_refs"] = refs
+            while len(self._graphs) >= self.MAX_GRAPHS:       # each entry pins its static buffers and pool memory: evict the
+                self._graphs.pop(next(iter(self._graphs)))    # least recently used signature
             entry = self._graphs[sig] = (g, st, l1, l2, self.last_outputs, ops.launch_count - l0)
         else:
+            self._graphs[sig] = self._graphs.pop(sig)         # most recently used last
             self._load_static(entry[1], features, object_features, object_xywh_list, depth_gt, depth_mask)
         g, st, l1, l2, outs, launches = entry
         g.replay()
@@ -223,11 +246,14 @@ class HeadTrainer:
 
     def _local_step(self, features, object_features, object_xywh_list, depth_gt, depth_mask):
         if self.graph:
+            self._arm_salt()
             sig = self._signature(features, object_features, object_xywh_list, depth_gt, depth_mask)
             if sig is not None:
                 seen = self._graph_seen.get(sig, 0)
                 if seen >= 2:                                 # two eager steps first: allocations, caches, parameter ranges
                     return self._graph_step(sig, features, object_features, object_xywh_list, depth_gt, depth_mask)
+                if len(self._graph_seen) >= 4096:             # signatures that never repeat (ragged object counts of real data)
+                    self._graph_seen.clear()
                 self._graph_seen[sig] = seen + 1
         self.grads.zero()
         return self.forward_backward(features, object_features, object_xywh_list, depth_gt, depth_mask)

@@ -121,8 +121,12 @@ def test_host_pipeline_matches_device_call(cuda):
     pipe = HostPipeline(head, chunks=3)
     for _ in range(2):   # second call reuses the ring buffers
         depth, edges = pipe(x_host, [o.cpu().pin_memory() for o in objs], [b.cpu().pin_memory() for b in boxes])
-        torch.cuda.synchronize()
+        # no torch.cuda.synchronize() here: the call itself waits for its last device->host copy (the outputs are HOST memory)
         assert rel_err(depth, want.depth_pred) < 1e-2 and rel_err(edges, want.bin_edges) < 1e-2
+    depth.zero_()
+    depth, edges = pipe(x_host, [o.cpu().pin_memory() for o in objs], [b.cpu().pin_memory() for b in boxes], depth_out=depth, sync=False)
+    pipe.done_event.synchronize()                      # the documented contract of sync=False
+    assert rel_err(depth, want.depth_pred) < 1e-2
 
 
 @pytest.mark.parametrize("name,B,h,w,n_obj,lanes,ctas", [

@@ -33,3 +33,28 @@ def test_join_side_waits_only_for_queues_used_since_the_last_join():
     et._side_dirty.clear()
     et.join_side(torch.device("cpu")) if not et.ASYNC_WGRAD else None      # nothing dirty: nothing to wait for, no CUDA call
     assert not et._side_dirty
+
+
+def test_param_views_share_the_version_counter():
+    """the kernels' parameter views must move their ``_version`` with in-place updates of the Parameter."""
+    import torch
+    from objcavit_b200.config import builtin_args
+    from objcavit_b200.modules import build_head
+    head = build_head(builtin_args("nyu_adabins"))
+    k = "conv_out.0.bias"
+    v0 = head._params()[k]._version
+    with torch.no_grad():
+        head.conv_out[0].bias.add_(1.0)
+    assert head._params()[k]._version > v0
+    sd = {n: t.clone() for n, t in head.state_dict().items()}
+    v1 = head._params()[k]._version
+    head.load_state_dict(sd)
+    assert head._params()[k]._version > v1
+
+
+def test_object_frontend_all_none_batch():
+    """Yolov7Wrapper returns None for an image without detections; a whole batch of them (batch size 1 at validation) must give
+    the placeholders, not raise."""
+    from objcavit_b200.evaluation import object_frontend
+    assert object_frontend([None, None]) == ([None, None], [None, None])
+    assert object_frontend([None]) == ([None], [None])
