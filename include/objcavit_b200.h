@@ -389,6 +389,10 @@ int ocv_unpad_objects_f32(const float* dpadded, const int32_t* offsets, float* d
 /* Backward of ocv_bins_f32 (norm 'linear'): grad_edges [B,K+1] and/or grad_centres [B,K] -> grad_y [B,K] (regressor output). */
 int ocv_bins_bwd_f32(const float* y_raw, const float* grad_edges, const float* grad_centres, float* grad_y, int B, int K,
                      float min_depth, float max_depth, void* stream);
+/* Same with an additional gradient given directly on the normalised widths (grad_widths [B,K] or NULL): the backward of the
+ * `bin_widths_normed` output of mViT.forward / ObjCAViT.forward (miniViT.py:34-42, ObjCAViT.py:379-388) at the module surface. */
+int ocv_bins_bwd_ex_f32(const float* y_raw, const float* grad_edges, const float* grad_centres, const float* grad_widths,
+                        float* grad_y, int B, int K, float min_depth, float max_depth, void* stream);
 
 /* ---- training losses (config 5), forward + gradients w.r.t. the head outputs ---------------------------------------
  * SILog: depth_pred [B,1,h,w] is up-sampled bilinearly (align_corners=True) to the GT size [B,1,H,W]; mask uint8 (1 = valid)

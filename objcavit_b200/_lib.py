@@ -99,6 +99,7 @@ PROTOTYPES = {
     "ocv_sumsq_f32": (i32, [p, i64, f32, p, p, p]),
     "ocv_adamw_step_f32": (i32, [p, p, p, p, i64, f32, f32, f32, f32, f32, i32, f32, p, f32, p]),
     "ocv_bins_bwd_f32": (i32, [p, p, p, p, i32, i32, f32, f32, p]),
+    "ocv_bins_bwd_ex_f32": (i32, [p, p, p, p, p, i32, i32, f32, f32, p]),
     "ocv_silog_workspace": (i64, [i32, i32, i32]),
     "ocv_silog_forward": (i32, [p, p, p, i32, i32, i32, i32, i32, f32, f32, p, p, p]),
     "ocv_silog_backward": (i32, [p, p, p, i32, i32, i32, i32, i32, f32, f32, f32, p, p, p]),

@@ -431,7 +431,7 @@ __global__ void tail_bwd_kernel(float* __restrict__ logits, float* __restrict__ 
 // ---- bin-width normalisation backward ('linear': w = (relu(y)+0.1)/sum; edges = min + (max-min) cumsum(w); centres = mid-points)
 // one block per image, K <= 1024 threads-strided
 __global__ void bins_bwd_kernel(const float* __restrict__ y_raw, const float* __restrict__ dedges, const float* __restrict__ dcentres,
-                                float* __restrict__ dy, int K, float range) {
+                                const float* __restrict__ dwidths, float* __restrict__ dy, int K, float range) {
   __shared__ float de[1025], dw[1024], sh[32];
   const int b = blockIdx.x;
   const float* y = y_raw + (long long)b * K;
@@ -445,7 +445,7 @@ __global__ void bins_bwd_kernel(const float* __restrict__ y_raw, const float* __
     float run = 0.f;
     for (int k = K - 1; k >= 0; --k) {
       run += de[k + 1];
-      dw[k] = range * run;
+      dw[k] = range * run + (dwidths ? dwidths[(long long)b * K + k] : 0.f);   // + a gradient given on the normalised widths themselves
     }
   }
   __syncthreads();
@@ -629,11 +629,16 @@ extern "C" int ocv_tail_bwd_f32(float* logits_inout, float* pg_out, const float*
   return ocv_launch_status();
 }
 
-extern "C" int ocv_bins_bwd_f32(const float* y_raw, const float* grad_edges, const float* grad_centres, float* grad_y, int B, int K,
-                                float min_depth, float max_depth, void* stream) {
-  OCV_CHECK_ARG(y_raw && grad_y && (grad_edges || grad_centres) && B > 0);
+extern "C" int ocv_bins_bwd_ex_f32(const float* y_raw, const float* grad_edges, const float* grad_centres, const float* grad_widths,
+                                   float* grad_y, int B, int K, float min_depth, float max_depth, void* stream) {
+  OCV_CHECK_ARG(y_raw && grad_y && (grad_edges || grad_centres || grad_widths) && B > 0);
   OCV_CHECK_SHAPE(K > 0 && K <= 1024);
   if (int s = ocv_require_sm100()) return s;
-  bins_bwd_kernel<<<B, 256, 0, ocv_stream(stream)>>>(y_raw, grad_edges, grad_centres, grad_y, K, max_depth - min_depth);
+  bins_bwd_kernel<<<B, 256, 0, ocv_stream(stream)>>>(y_raw, grad_edges, grad_centres, grad_widths, grad_y, K, max_depth - min_depth);
   return ocv_launch_status();
+}
+
+extern "C" int ocv_bins_bwd_f32(const float* y_raw, const float* grad_edges, const float* grad_centres, float* grad_y, int B, int K,
+                                float min_depth, float max_depth, void* stream) {
+  return ocv_bins_bwd_ex_f32(y_raw, grad_edges, grad_centres, nullptr, grad_y, B, K, min_depth, max_depth, stream);
 }

@@ -427,7 +427,8 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
     t.cfg, t.x = cfg, x
     B, C, h, w = x.shape
     t.shape = (B, C, h, w)
-    pre = "adaptive_bins_layer." if cfg["kind"] == "adabins" else "objcavit."
+    # ``cfg["prefix"]``: key prefix of the mViT / ObjCAViT parameters ("" when the inner module itself is the boundary)
+    pre = cfg.get("prefix", "adaptive_bins_layer." if cfg["kind"] == "adabins" else "objcavit.")
     if cfg.get("pixel") == "bf16":
         t.late_P, t.late_pre = P, pre
         _pixel_prologue(P, pre, t, x)
@@ -467,6 +468,15 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
     t.tok = tok
     Q = min(n_query, S - 1)
     t.pixel = cfg.get("pixel", "fp32")
+    if cfg.get("surface") == "module":
+        # mViT.forward / ObjCAViT.forward surface (miniViT.py:22-44, ObjCAViT.py:373-390): (bin_widths_normed, range_attention_maps)
+        # are the outputs, the tail belongs to the caller (AdaBins.py:77-87) — fp32 kernels, ram materialised because it IS the output
+        t.y_raw, t.sv_reg = mlp_fwd(P, pre + "regressor.", tok[:, 0, :], (0, 2, 4))
+        widths, _, _ = ops.bins(t.y_raw, "linear")
+        t.Q = Q
+        t.x3 = ops.conv3x3(x, P[pre + "conv3x3.weight"], P[pre + "conv3x3.bias"])
+        ram = ops.batched_matmul_nn(tok[:, 1:Q + 1, :], t.x3.view(B, C, h * w)).view(B, Q, h, w)
+        return widths, ram, t
     # regressor + bins: only the LAST kernel of the pixel path (the tail) needs the bin centres, so in the tensor-core mode the chain
     # runs on a branch next to the logits GEMMs
     reg_fork = fork_branch(x.device, 16) if t.pixel == "bf16" else None
@@ -670,8 +680,17 @@ def backward(P: Params, G: Params, t: Tape, d_depth: torch.Tensor, d_edges: Opti
     dram = torch.empty(B, Q, Pn, device=dev, dtype=torch.float32)
     ops.gemm_ex(Wout, dl, Q, Pn, K, Q, Pn, dram, Pn, trans_a=True, batch=B, stride_a=0, stride_b=K * Pn, stride_c=Q * Pn)
     del dl, logits
-    # ---- bins + regressor -------------------------------------------------------------------------------------------
+    # ---- bins + regressor, range attention, conv3x3, tokens --------------------------------------------------------------
     dy_raw = ops.bins_bwd(t.y_raw, d_edges.contiguous() if d_edges is not None else None, dcent, cfg["min_depth"], cfg["max_depth"])
+    _ram_bwd(P, G, t, dram, dy_raw)
+
+
+def _ram_bwd(P: Params, G: Params, t: Tape, dram: torch.Tensor, dy_raw: torch.Tensor) -> None:
+    """fp32 path from (d loss / d range_attention_maps [B,Q,P], d loss / d regressor output [B,K]) down to every parameter."""
+    pre, x, tok, Q = t.pre, t.x, t.tok, t.Q
+    B, C, h, w = t.shape
+    Pn, S = h * w, tok.shape[1]
+    dev = x.device
     dtok = torch.zeros(B, S, E, device=dev, dtype=torch.float32)
     mlp_bwd(P, G, pre + "regressor.", (0, 2, 4), t.sv_reg, dy_raw, dx_out=dtok[:, 0, :])
     # ---- range attention: ram[b] = queries[b] @ x3[b] ------------------------------------------------------------------
@@ -687,6 +706,19 @@ def backward(P: Params, G: Params, t: Tape, d_depth: torch.Tensor, d_edges: Opti
     ops.reduce_channels(dx3, G[pre + "conv3x3.bias"], 1, B, C, Pn, beta=1.0)
     del dx3
     _token_bwd(P, G, t, dtok)
+
+
+def backward_module(P: Params, G: Params, t: Tape, d_widths: Optional[torch.Tensor], d_ram: Optional[torch.Tensor]) -> None:
+    """Backward of the ``surface="module"`` forward: upstream gradients of ``bin_widths_normed`` [B,K] and of
+    ``range_attention_maps`` [B,Q,h,w] (either may be None)."""
+    B, C, h, w = t.shape
+    dev = t.x.device
+    K = t.y_raw.shape[1]
+    dw = d_widths.contiguous().float() if d_widths is not None else torch.zeros(B, K, device=dev, dtype=torch.float32)
+    dy_raw = ops.bins_bwd(t.y_raw, None, None, 0.0, 1.0, grad_widths=dw)
+    dram = (d_ram.contiguous().float() if d_ram is not None
+            else torch.zeros(B, t.Q, h, w, device=dev, dtype=torch.float32)).view(B, t.Q, h * w)
+    _ram_bwd(P, G, t, dram, dy_raw)
 
 
 def _table_bwd(g_table: torch.Tensor, strategy: str, pos_inputs, d_obj: torch.Tensor, d_img: torch.Tensor, h: int, w: int,

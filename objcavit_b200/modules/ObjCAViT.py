@@ -149,7 +149,14 @@ class ObjCAViT(KernelModule):
     def forward(self, image_features, object_features, object_xywh_list):
         """-> ``(bin_widths_normed, range_attention_maps)``; overwrites ``object_features[i]`` with the
         embedded object tokens like the reference does (``ObjCAViT.py:330``, F11)."""
-        self._guard_inference(image_features)
+        if self._wants_grad(image_features):     # training through ``self.objcavit(...)`` (GraphBins.py:107)
+            if self.norm != 'linear':
+                raise NotImplementedError("objcavit_b200: the training kernels implement norm='linear', the only value the "
+                                          "reference's callers pass (AdaBins.py:46, GraphBins.py:54)")
+            from ._autograd import train_forward
+            cfg = dict(kind="graphbins", prefix="", surface="module", strategy=self.strategy, no_obj_sa=self.no_obj_sa,
+                       use_2_saca=self.use_2_saca)
+            return train_forward(self, cfg, image_features, object_features, object_xywh_list)
         return engine.objcavit_forward(self._params(), "", image_features.contiguous().float(), object_features,
                                        object_xywh_list, self.strategy, self.no_obj_sa, self.use_2_saca,
                                        self.n_query_channels, self.norm)

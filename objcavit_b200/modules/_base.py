@@ -12,6 +12,15 @@ class KernelModule(nn.Module):
     reference layout); ``_params()`` hands the kernels a ``{state_dict key: tensor}`` view of them.
     """
 
+    # Dropout probability of the encoder layers while ``self.training`` (nn.TransformerEncoderLayer's default, which the
+    # reference never overrides: modules/layers.py:8, modules/ObjCAViT.py:155-161).  The reference's modules are switched off
+    # with ``m.p = 0`` / ``mha.dropout = 0``; here it is this one attribute.  ``eval()`` or 0.0 = no dropout kernels at all.
+    dropout = 0.1
+
+    def _wants_grad(self, *tensors):
+        return torch.is_grad_enabled() and (any(p.requires_grad for p in self.parameters()) or
+                                            any(torch.is_tensor(t) and t.requires_grad for t in tensors))
+
     def _params(self):
         cache = self.__dict__.get("_ocv_param_cache")
         if cache is None:
@@ -43,8 +52,8 @@ class KernelModule(nn.Module):
         if torch.is_grad_enabled() and (any(torch.is_tensor(t) and t.requires_grad for t in tensors)
                                         or any(p.requires_grad for p in self.parameters())):
             raise NotImplementedError(
-                "objcavit_b200: gradients w.r.t. these inputs are not produced (the decoder is frozen in config 5, SURVEY.md "
-                "§8d); pass features.detach(), or wrap the call in torch.no_grad() for inference.")
+                f"objcavit_b200: {type(self).__name__} on its own runs inference only (wrap the call in torch.no_grad()); training "
+                "goes through mViT / ObjCAViT or the head classes, whose forward is an autograd node over the training kernels.")
 
     @property
     def device(self):  # the reference modules are LightningModules and use self.device

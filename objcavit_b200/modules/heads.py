@@ -19,52 +19,11 @@ from .miniViT import mViT
 from .ObjCAViT import ObjCAViT
 
 
-class _HeadTrainFn(torch.autograd.Function):
-    """Autograd node of the whole head in grad mode (config 5): forward = ``engine_train.forward`` (fp32 kernels, activations
-    kept on a tape), backward = ``engine_train.backward`` into ONE zero-filled flat buffer whose slices are returned as the
-    parameter gradients (autograd then accumulates them into ``.grad``, e.g. the views of a ``FlatGradBuffer``)."""
-
-    @staticmethod
-    def forward(ctx, head, cfg, x, object_features, object_xywh_list, keys, *params):
-        from .. import engine_train
-        P = {k: p.detach() for k, p in zip(keys, params)}
-        drop = engine_train.DropCtx(cfg.get("dropout", 0.0), cfg.get("dropout_seed", 0))
-        depth, edges, tape = engine_train.forward(P, cfg, x.detach().contiguous().float(), object_features, object_xywh_list,
-                                                  drop=drop)
-        ctx.tape, ctx.P, ctx.keys = tape, P, keys
-        ctx.needs = [p.requires_grad for p in params]
-        return depth, edges
-
-    @staticmethod
-    def backward(ctx, d_depth, d_edges):
-        from .. import engine_train
-        P, keys = ctx.P, ctx.keys
-        sizes = [(P[k].numel() + 63) // 64 * 64 for k in keys]
-        flat = torch.zeros(sum(sizes), device=P[keys[0]].device, dtype=torch.float32)
-        G, off = engine_train.Touched(), 0
-        for k, n in zip(keys, sizes):
-            G[k] = flat[off:off + P[k].numel()].view_as(P[k])
-            off += n
-        if d_depth is None:
-            d_depth = torch.zeros_like(ctx.tape.x[:, :1])
-        engine_train.backward(P, G, ctx.tape, d_depth.contiguous().float(), d_edges)
-        ctx.tape = None
-        touched = set(G.touched)     # parameters the backward never wrote have no gradient at all (None, as in the reference: F10)
-        return (None,) * 6 + tuple(dict.__getitem__(G, k) if (need and k in touched) else None for k, need in zip(keys, ctx.needs))
-
-
-def draw_dropout_seed() -> int:
-    """Base seed of one training forward's dropout masks, drawn from torch's CPU generator: reproducible under
-    ``torch.manual_seed`` like the reference's masks, without a device synchronisation."""
-    return int(torch.randint(0, 2 ** 47, (1,)).item())
+from ._autograd import draw_dropout_seed, train_forward  # noqa: E402,F401  (draw_dropout_seed is re-exported for trainer.py)
 
 
 class _HeadBase(KernelModule):
     precision = "fp32"   # "fp32": parity path (SIMT fp32).  "bf16": tensor-core path (tcgen05).
-    # Dropout probability of the encoder layers while ``self.training`` (nn.TransformerEncoderLayer's default, which the
-    # reference never overrides: modules/layers.py:8, modules/ObjCAViT.py:155-161).  The reference's modules are switched off
-    # with ``m.p = 0`` / ``mha.dropout = 0``; here it is this one attribute.  ``eval()`` or 0.0 = no dropout kernels at all.
-    dropout = 0.1
 
     def enable_pipeline(self, lanes: int = 2, pixel_ctas: int = 0):
         """Pipelined serving mode of the bf16 path (``ocv_head_set_pipeline``): consecutive ``forward`` calls overlap — the
@@ -82,24 +41,13 @@ class _HeadBase(KernelModule):
         if nh is not None:
             nh.join()
 
-    def _wants_grad(self, x):
-        return torch.is_grad_enabled() and (any(p.requires_grad for p in self.parameters()) or
-                                            (torch.is_tensor(x) and x.requires_grad))
-
     def _train_forward(self, cfg, x, object_features, object_xywh_list):
         """Grad-mode forward (the reference's training step): explicit forward + backward kernels.  ``precision="fp32"``: every
         kernel fp32 SIMT (the parity path); ``"bf16"``: the pixel path (conv3x3, logits and their gradients: 90 % of the FLOPs)
-        on tcgen05 with bf16 operands, the token path still fp32."""
-        if torch.is_tensor(x) and x.requires_grad:
-            raise NotImplementedError("objcavit_b200: gradients w.r.t. the decoder features are not produced (the extractor is "
-                                      "frozen in config 5); pass features.detach()")
-        named = list(self.named_parameters())
-        keys = tuple(k for k, _ in named)
-        if self.training and self.dropout > 0:
-            cfg = dict(cfg, dropout=float(self.dropout), dropout_seed=draw_dropout_seed())
-        if self.precision == "bf16":      # pixel path of the step on tensor cores (bf16 operands, fp32 accumulation)
+        and the encoder GEMMs on tcgen05 with bf16 operands."""
+        if self.precision == "bf16":
             cfg = dict(cfg, pixel="bf16")
-        return _HeadTrainFn.apply(self, cfg, x, object_features, object_xywh_list, keys, *[p for _, p in named])
+        return train_forward(self, cfg, x, object_features, object_xywh_list)
 
     def _depth_range(self):
         ds = self.args[self.args.basic.dataset]

@@ -26,5 +26,10 @@ class mViT(KernelModule):
 
     def forward(self, x):
         """-> ``(bin_widths_normed [N,dim_out], range_attention_maps [N,n_query_channels,h,w])``."""
-        self._guard_inference(x)
+        if self._wants_grad(x):        # training through ``self.adaptive_bins_layer(unet_out)`` (AdaBins.py:76)
+            if self.norm != 'linear':
+                raise NotImplementedError("objcavit_b200: the training kernels implement norm='linear', the only value the "
+                                          "reference's callers pass (AdaBins.py:46, GraphBins.py:54)")
+            from ._autograd import train_forward
+            return train_forward(self, dict(kind="adabins", prefix="", surface="module"), x, None, None)
         return engine.mvit_forward(self._params(), "", x.contiguous().float(), self.n_query_channels, self.norm)

@@ -772,13 +772,16 @@ def tail_bwd(logits: torch.Tensor, centres: torch.Tensor, grad_depth: torch.Tens
     return logits, pg
 
 
-def bins_bwd(y_raw: torch.Tensor, grad_edges, grad_centres, min_depth: float, max_depth: float) -> torch.Tensor:
+def bins_bwd(y_raw: torch.Tensor, grad_edges, grad_centres, min_depth: float, max_depth: float, grad_widths=None) -> torch.Tensor:
     _chk(y_raw, torch.float32, "y_raw")
     assert y_raw.is_contiguous()
     B, K = y_raw.shape
     dy = torch.empty_like(y_raw)
-    _call("ocv_bins_bwd_f32", y_raw.data_ptr(), _ptr(grad_edges), _ptr(grad_centres), dy.data_ptr(), B, K, float(min_depth),
-          float(max_depth), _stream())
+    if grad_widths is not None:
+        _chk(grad_widths, torch.float32, "grad_widths")
+        assert grad_widths.is_contiguous() and grad_widths.shape == y_raw.shape
+    _call("ocv_bins_bwd_ex_f32", y_raw.data_ptr(), _ptr(grad_edges), _ptr(grad_centres), _ptr(grad_widths), dy.data_ptr(), B, K,
+          float(min_depth), float(max_depth), _stream())
     return dy
 
 

@@ -1,6 +1,7 @@
 """TEST INFRASTRUCTURE ONLY. Import the UNMODIFIED reference head modules from /root/reference.
 
-Only usable in the build container (``/root/reference`` does not exist on the GPU box).  Follows
+In the build container the files come from ``/root/reference``; on the GPU box from ``oracle/_ref`` (unmodified copies made by
+``oracle/vendor_ref.py``, git-ignored).  Follows
 SURVEY.md Appendix A: the reference's ``modules/ObjCAViT.py:10`` imports ``pytorch_lightning`` only
 for the ``pl.LightningModule`` base class (``ObjCAViT.py:150,216``), so a stub whose
 ``LightningModule`` is ``nn.Module`` (+ a ``device`` property) lets the file import as it is.
@@ -14,7 +15,18 @@ import types
 import torch
 import torch.nn as nn
 
-REFERENCE_ROOT = os.environ.get("OBJCAVIT_REFERENCE_ROOT", "/root/reference")
+def _find_root() -> str:
+    """``$OBJCAVIT_REFERENCE_ROOT`` > ``/root/reference`` (build container) > ``oracle/_ref`` (the byte-identical copies made by
+    ``oracle/vendor_ref.py``; what the GPU box has)."""
+    env = os.environ.get("OBJCAVIT_REFERENCE_ROOT")
+    if env:
+        return env
+    if os.path.isfile("/root/reference/modules/ObjCAViT.py"):
+        return "/root/reference"
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+REFERENCE_ROOT = _find_root()
 
 
 def reference_available() -> bool:

@@ -175,8 +175,8 @@ def test_bin_argmax_against_the_oracle_logits(cuda, label, name, B, h, w, n_obj)
 # Overall agreement floors: the values measured on the B200 (profiles/parity_fullsize_r02.json) minus a margin for
 # box-to-box differences; a regression of the bf16 pixel path shows up here before it shows in the depth tolerance.
 ARGMAX_OVERALL_FLOOR = {
-    "config1_adabins": 0.90,
-    "config2_nyu_learned_bbox_wh": 0.90,
-    "config3_kitti_roi_align": 0.90,
-    "config4_nyu_2saca": 0.90,
+    "config1_adabins": 0.985,                  # measured 0.9931
+    "config2_nyu_learned_bbox_wh": 0.975,      # measured 0.9874
+    "config3_kitti_roi_align": 0.975,          # measured 0.9875
+    "config4_nyu_2saca": 0.975,                # measured 0.9859
 }
