@@ -143,15 +143,28 @@ class HostPipeline:
         self.done = [None, None]
 
     @torch.no_grad()
-    def __call__(self, feats_nhwc_host, object_features=None, object_xywh_list=None, depth_out=None, edges_out=None,
+    def __call__(self, feats_host, object_features=None, object_xywh_list=None, depth_out=None, edges_out=None,
                  sync: bool = True):
-        """feats_nhwc_host: pinned [B,h,w,128] bf16.  Returns (depth [B,1,h,w] fp32, bin_edges [B,K+1]) in pinned host memory.
-        The results live in HOST memory, so the call waits (``sync=True``, the default) until the last device->host copy has
-        landed before it returns; with ``sync=False`` it returns at once and the caller must ``pipe.done_event.synchronize()``
-        before reading the outputs on the CPU."""
+        """``feats_host`` (pinned host memory), either layout:
+
+        * ``[B,h,w,128]`` bf16 NHWC — the decoder hand-off format (``modules/decoder_handoff.py``): copied and consumed in place;
+        * ``[B,128,h,w]`` fp32 NCHW — what the reference's caller holds (``modules/GraphBins.py:107``): each chunk crosses PCIe
+          as fp32 (twice the bytes) and is converted on the device by ``ocv_nchw_to_nhwc_bf16`` before the head runs.
+
+        Returns (depth [B,1,h,w] fp32, bin_edges [B,K+1]) in pinned host memory.  The results live in HOST memory, so the call
+        waits (``sync=True``, the default) until the last device->host copy has landed before it returns; with ``sync=False``
+        it returns at once and the caller must ``pipe.done_event.synchronize()`` before reading the outputs on the CPU."""
+        from .. import ops
         head = self.head
         dev = head.device
-        B, h, w, C = feats_nhwc_host.shape
+        nchw32 = feats_host.dtype == torch.float32
+        if nchw32:
+            B, C, h, w = feats_host.shape
+            chunk_shape = lambda n: (n, C, h, w)
+        else:
+            assert feats_host.dtype == torch.bfloat16, "host features: bf16 NHWC or fp32 NCHW"
+            B, h, w, C = feats_host.shape
+            chunk_shape = lambda n: (n, h, w, C)
         n = min(self.chunks, B)
         bounds = [(B * i // n, B * (i + 1) // n) for i in range(n)]
         if depth_out is None:
@@ -166,12 +179,13 @@ class HostPipeline:
             with torch.cuda.stream(self.h2d):
                 if self.done[slot] is not None:
                     self.h2d.wait_event(self.done[slot])      # the chunk that used this buffer two steps ago has been consumed
-                if self.xbuf[slot] is None or self.xbuf[slot].shape[0] < hi - lo or self.xbuf[slot].shape[1:] != (h, w, C):
-                    if self.xbuf[slot] is not None:
-                        self.xbuf[slot].record_stream(cur)    # the compute stream may still read the buffer being replaced
-                    self.xbuf[slot] = torch.empty(max(hi - lo, (B + n - 1) // n), h, w, C, device=dev, dtype=torch.bfloat16)
+                buf = self.xbuf[slot]
+                if buf is None or buf.shape[0] < hi - lo or buf.shape[1:] != chunk_shape(1)[1:] or buf.dtype != feats_host.dtype:
+                    if buf is not None:
+                        buf.record_stream(cur)                # the compute stream may still read the buffer being replaced
+                    self.xbuf[slot] = torch.empty(chunk_shape(max(hi - lo, (B + n - 1) // n)), device=dev, dtype=feats_host.dtype)
                 x = self.xbuf[slot][:hi - lo]
-                x.copy_(feats_nhwc_host[lo:hi], non_blocking=True)
+                x.copy_(feats_host[lo:hi], non_blocking=True)
                 objs = boxes = None
                 if object_features is not None:
                     objs = [o.to(dev, non_blocking=True) for o in object_features[lo:hi]]
@@ -181,7 +195,10 @@ class HostPipeline:
                 ready = torch.cuda.Event()
                 ready.record(self.h2d)
             cur.wait_event(ready)
-            xv = x.permute(0, 3, 1, 2)                         # logical NCHW view of NHWC memory: consumed in place
+            if nchw32:
+                xv = ops.nchw_to_nhwc_bf16(x).permute(0, 3, 1, 2)   # layout + precision change on the device, then as below
+            else:
+                xv = x.permute(0, 3, 1, 2)                     # logical NCHW view of NHWC memory: consumed in place
             out = head(xv) if objs is None else head(xv, objs, boxes)
             ev = torch.cuda.Event()
             ev.record(cur)

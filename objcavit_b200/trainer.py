@@ -65,6 +65,7 @@ class HeadTrainer:
                  graph: bool = False):
         self.head = head
         self.graph = False
+        self.allreduce_events = None     # a list while the caller wants the exposed all-reduce time of every step (bench.py)
         self._graphs, self._graph_seen, self._graph_pool, self._salt = {}, {}, None, None
         self._capture_stream = None
         self.group = group
@@ -263,7 +264,13 @@ class HeadTrainer:
         l1, l2 = self._local_step(features, object_features, object_xywh_list, depth_gt, depth_mask)
         world = self.world()
         if world > 1:
+            if self.allreduce_events is not None:      # bench: CUDA events on the launching stream around the collective
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
             dist.all_reduce(self.grads.flat, op=dist.ReduceOp.SUM, group=self.group)   # the ONE collective of the step
+            if self.allreduce_events is not None:
+                e1.record()
+                self.allreduce_events.append((e0, e1))
         scale = 1.0 / world
         lr, beta1 = (self.lr, self.betas[0]) if self.schedule is None else self.schedule.at(self.step_index)
         self.step_index += 1
