@@ -359,6 +359,21 @@ int ocv_table_grad_commit_f32(const long long* table_grad_fix, float* table_grad
  *   ocv_im2col3x3_bf16: col [C*9+8, B*P] bf16 from the planar map x [B,C,h,w] bf16: row c*9+ky*3+kx = the map shifted by
  *     (ky-1, kx-1) with zero padding, row C*9 = 1 (its GEMM column is the conv bias gradient), 7 zero rows.  (h*w) % 8 == 0.
  * (backward of) self.conv3x3 (modules/miniViT.py:25; modules/ObjCAViT.py:374) as ONE GEMM dW[o, :] = dx3T[o, B*P] @ col^T. */
+/* Pixel path of the training step WITHOUT materialised logits (csrc/train_tail_fused_bf16.cu); P % 128 == 0.
+ *   x3 [B*P,128] bf16 NHWC = conv3x3(features) + bias (ocv_conv3x3_nhwc_bf16); Mb2 [B,256,128] bf16 = log2e * Wout @ Q[b] and
+ *   blog2 [B,256] = log2e * conv_out bias (ocv_fold_queries_bf16 with b3 = NULL, logit_scale = log2e); centres [B,256].
+ * fwd: depth [B*P], stat_max / stat_sum [B*P] (max and sum of 2^(l - max) over the 256 log2-domain logits of a pixel).
+ *      replaces self.conv_out + softmax + sum(out * centers) (modules/GraphBins.py:109-119) on top of PixelWiseDotProduct.
+ * bwd: from grad_depth [B*P]: dx3T [128, ld_dx3T] bf16 (channel-major d loss / d x3), dMb [B,256,128] fp32 (natural-logit units:
+ *      d loss / d (Wout @ Q[b])), grad_centres [B,256], grad_bias [256] = bias_beta * grad_bias + sum over pixels of d logits
+ *      (conv_out bias; may be NULL).  Deterministic (fixed-order reduction of per-CTA partial accumulators in `workspace`). */
+int ocv_tail_fused_fwd_bf16(const void* x3_nhwc_bf16, const void* Mb2_bf16, const float* blog2, const float* centres, float* depth,
+                            float* stat_max, float* stat_sum, int B, long long P, void* stream);
+long long ocv_tail_fused_bwd_workspace(int B, long long P);
+int ocv_tail_fused_bwd_bf16(const void* x3_nhwc_bf16, const void* Mb2_bf16, const float* blog2, const float* centres,
+                            const float* depth, const float* stat_max, const float* stat_sum, const float* grad_depth,
+                            void* dx3T_bf16, long long ld_dx3T, float* dMb, float* grad_centres, float* grad_bias, float bias_beta,
+                            int B, long long P, void* workspace, void* stream);
 int ocv_tail_logits_f32(const float* logits, const float* logit_bias, const float* centres, float* depth, int B, int K,
                         long long P, void* stream);
 /* ..._stats_...: the forward also saves the per-pixel softmax statistics (max, sum, centre-weighted sum; stats [B,3,P] fp32), the

@@ -77,6 +77,9 @@ PROTOTYPES = {
     "ocv_grid_sample_pos_bwd_f32": (i32, [p, p, p, i32, i32, i32, i32, i32, f32, f32, p]),
     "ocv_ps_roi_align_pos_bwd_f32": (i32, [p, p, p, i32, i32, i32, i32, f32, i32, p]),
     "ocv_table_grad_commit_f32": (i32, [p, p, i64, f32, p]),
+    "ocv_tail_fused_fwd_bf16": (i32, [p, p, p, p, p, p, p, i32, i64, p]),
+    "ocv_tail_fused_bwd_workspace": (i64, [i32, i64]),
+    "ocv_tail_fused_bwd_bf16": (i32, [p, p, p, p, p, p, p, p, p, i64, p, p, p, f32, i32, i64, p, p]),
     "ocv_tail_logits_f32": (i32, [p, p, p, p, i32, i32, i64, p]),
     "ocv_tail_logits_bwd_workspace": (i64, [i32, i32, i64]),
     "ocv_tail_logits_stats_f32": (i32, [p, p, p, p, p, i32, i32, i64, p]),

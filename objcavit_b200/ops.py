@@ -922,6 +922,43 @@ def dropout_act_bwd(dy: torch.Tensor, out: torch.Tensor, act: int, p: float, see
 
 # ---- training step, tensor-core pixel path (csrc/train_pixel_bf16.cu) -------------------------------------------------
 
+def tail_fused_fwd_bf16(x3_nhwc: torch.Tensor, Mb2: torch.Tensor, blog2: torch.Tensor, centres: torch.Tensor):
+    """-> (depth [B,P], stat_max [B,P], stat_sum [B,P]) from x3 [B,h,w,128] / [B,P,128] bf16 without materialising the logits:
+    logits (log2 domain) = x3 @ Mb2[b]^T + blog2[b], softmax over the 256 bins in registers, depth = sum_k p_k centres[b,k]."""
+    _chk(x3_nhwc, torch.bfloat16, "x3"); _chk(Mb2, torch.bfloat16, "Mb2"); _chk(blog2, torch.float32, "blog2")
+    _chk(centres, torch.float32, "centres")
+    assert x3_nhwc.is_contiguous() and Mb2.is_contiguous() and blog2.is_contiguous() and centres.is_contiguous()
+    B = Mb2.shape[0]
+    Pn = x3_nhwc.numel() // (B * 128)
+    assert tuple(Mb2.shape) == (B, 256, 128) and tuple(blog2.shape) == (B, 256) and tuple(centres.shape) == (B, 256)
+    out = torch.empty(3, B, Pn, device=x3_nhwc.device, dtype=torch.float32)
+    _call("ocv_tail_fused_fwd_bf16", x3_nhwc.data_ptr(), Mb2.data_ptr(), blog2.data_ptr(), centres.data_ptr(), out[0].data_ptr(),
+          out[1].data_ptr(), out[2].data_ptr(), B, Pn, _stream())
+    return out[0], out[1], out[2]
+
+
+def tail_fused_bwd_bf16(x3_nhwc: torch.Tensor, Mb2: torch.Tensor, blog2: torch.Tensor, centres: torch.Tensor, depth: torch.Tensor,
+                        stat_max: torch.Tensor, stat_sum: torch.Tensor, grad_depth: torch.Tensor, grad_bias=None, beta: float = 1.0):
+    """-> (dx3T [128, B*P] bf16, dMb [B,256,128] fp32, grad_centres [B,256]); ``grad_bias`` [256] beta-accumulated in place.  The
+    logits are recomputed tile by tile on the tensor cores; nothing of size [B,256,P] touches HBM."""
+    _chk(x3_nhwc, torch.bfloat16, "x3"); _chk(Mb2, torch.bfloat16, "Mb2"); _chk(grad_depth, torch.float32, "grad_depth")
+    for t in (depth, stat_max, stat_sum):
+        _chk(t, torch.float32, "stats")
+        assert t.is_contiguous()
+    assert x3_nhwc.is_contiguous() and Mb2.is_contiguous() and grad_depth.is_contiguous()
+    B = Mb2.shape[0]
+    Pn = x3_nhwc.numel() // (B * 128)
+    dev = x3_nhwc.device
+    dx3T = torch.empty(128, B * Pn, device=dev, dtype=torch.bfloat16)
+    dMb = torch.empty(B, 256, 128, device=dev, dtype=torch.float32)
+    dcent = torch.empty(B, 256, device=dev, dtype=torch.float32)
+    ws = _workspace(_lib.lib().ocv_tail_fused_bwd_workspace(B, Pn), dev, "tail_fused_bwd")
+    _call("ocv_tail_fused_bwd_bf16", x3_nhwc.data_ptr(), Mb2.data_ptr(), blog2.data_ptr(), centres.data_ptr(), depth.data_ptr(),
+          stat_max.data_ptr(), stat_sum.data_ptr(), grad_depth.data_ptr(), dx3T.data_ptr(), B * Pn, dMb.data_ptr(), dcent.data_ptr(),
+          _ptr(grad_bias), float(beta), B, Pn, ws.data_ptr(), _stream(), launches=3)
+    return dx3T, dMb, dcent
+
+
 def tail_logits(logits: torch.Tensor, bias, centres: torch.Tensor, want_stats: bool = False):
     """depth [B,P] = sum_k softmax_k(logits[b,k,p] + bias[k]) centres[b,k]; logits channel-major fp32 [B,K,P].
     ``want_stats``: -> (depth, stats [B,3,P]) — the softmax statistics ``tail_logits_bwd`` would otherwise recompute."""
