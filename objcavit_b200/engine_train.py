@@ -557,8 +557,16 @@ def _pixel_prologue_rest(P: Params, pre: str, t, x: torch.Tensor) -> None:
     t.unf = ops.patch_unfold_bf16(x, 16) if UNFOLD_IN_FORWARD else None
     # channel-major copy of the conv output (B operand of the dMb GEMMs of the backward): also a function of x only
     Bq, hq, wq, Cq = t.x3h.shape
-    t.x3T = ops.transpose_bf16(t.x3h.view(Bq, hq * wq, Cq)) if UNFOLD_IN_FORWARD else None
+    t.x3T = ops.transpose_bf16(t.x3h.view(Bq, hq * wq, Cq)) if (UNFOLD_IN_FORWARD and not _fused_tail(hq * wq)) else None
     t.xh_keep = None
+
+
+FUSED_TAIL = _os.environ.get("OCV_FUSED_TAIL", "1") == "1"   # 0: the round-1 path with materialised logits (kept as the general fallback)
+
+
+def _fused_tail(Pn: int) -> bool:
+    """The logits-free kernels (csrc/train_tail_fused_bf16.cu) walk flat 128-pixel tiles that must not straddle images."""
+    return FUSED_TAIL and Pn % 128 == 0
 
 
 def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, Q: int, edges=None) -> torch.Tensor:
@@ -567,6 +575,14 @@ def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, 
     Wout = P["conv_out.0.weight"].view(-1, Q)
     K = Wout.shape[0]
     join_branch(x.device, t.conv_fork, t.x3h, name="pixel")
+    t.fused_tail = _fused_tail(Pn) and K == 256 and Q == 128
+    if t.fused_tail:
+        # logits never reach HBM: Mb2 = log2e * Wout @ queries[b] (bf16) and blog2 = log2e * bout from one small kernel, then ONE
+        # tcgen05 kernel over 128-pixel tiles of x3: logits in TMEM -> softmax in registers -> depth + (max, sum) per pixel
+        t.Mb2, t.blog2 = ops.fold_queries_bf16(P["conv_out.0.weight"], P["conv_out.0.bias"], tok[:, 1:Q + 1, :], None)
+        join_branch(x.device, t.reg_fork, t.centres, t.y_raw, edges, name="regressor")      # the kernel needs the bin centres
+        t.depth, t.smax, t.ssum = ops.tail_fused_fwd_bf16(t.x3h, t.Mb2, t.blog2, t.centres)
+        return t.depth.view(B, 1, h, w)
     Mb = torch.empty(B, K, E, device=x.device, dtype=torch.float32)
     ops.gemm_ex(Wout, tok[:, 1:Q + 1, :], K, E, Q, Q, E, Mb, E, batch=B, stride_a=0, stride_b=S * E, stride_c=K * E)
     t.Mb16 = ops.cast_bf16(Mb)
@@ -592,30 +608,32 @@ def _pixel_bwd_bf16_tail(P: Params, G: Params, t, gd: torch.Tensor):
     return dlT, dcent
 
 
-def _pixel_bwd_bf16_rest(P: Params, G: Params, t, dlT: torch.Tensor, dtok: torch.Tensor) -> None:
-    """conv_out weight, query (into ``dtok[:, 1:Q+1]``), conv3x3 weight and bias gradients from dlT."""
+def _pixel_bwd_bf16_rest(P: Params, G: Params, t, dlT, dtok: torch.Tensor, dMb=None, dx3T=None) -> None:
+    """conv_out weight, query (into ``dtok[:, 1:Q+1]``), conv3x3 weight and bias gradients — from dlT (materialised-logits path) or
+    from the (dMb, dx3T) the logits-free backward kernel has already produced."""
     pre, x, tok, Q = t.pre, t.x, t.tok, t.Q
     B, C, h, w = t.shape
     Pn, S = h * w, tok.shape[1]
     dev = x.device
     Wout = P["conv_out.0.weight"].view(-1, Q)
     K = Wout.shape[0]
-    # d Mb -> conv_out weight and queries: the only part the token-path backward waits for
-    x3T = getattr(t, "x3T", None)                                             # [B,C,P]: made in the forward on the pixel branch
-    if x3T is None:
-        x3T = ops.transpose_bf16(t.x3h.view(B, Pn, C))
-    else:
-        x3T.record_stream(torch.cuda.current_stream(dev))
-        t.x3T = None
-    dMb = torch.empty(B, K, E, device=dev, dtype=torch.float32)
-    sk = max(1, min(64, Pn // 1024))
-    fork = fork_branch(dev, 32)
-    for b in range(B):
-        with on_branch(dev, fork if b % PIXEL_QUEUES else None, dlT, x3T, dMb, name=f"pixel_q{b % PIXEL_QUEUES}"):
-            ops.gemm_bf16(dlT[b], x3T[b], out=dMb[b], split_k=sk)
-    for qi in range(1, min(PIXEL_QUEUES, B)):
-        join_branch(dev, fork, name=f"pixel_q{qi}")
-    del x3T
+    if dMb is None:
+        # d Mb -> conv_out weight and queries: the only part the token-path backward waits for
+        x3T = getattr(t, "x3T", None)                                             # [B,C,P]: made in the forward on the pixel branch
+        if x3T is None:
+            x3T = ops.transpose_bf16(t.x3h.view(B, Pn, C))
+        else:
+            x3T.record_stream(torch.cuda.current_stream(dev))
+            t.x3T = None
+        dMb = torch.empty(B, K, E, device=dev, dtype=torch.float32)
+        sk = max(1, min(64, Pn // 1024))
+        fork = fork_branch(dev, 32)
+        for b in range(B):
+            with on_branch(dev, fork if b % PIXEL_QUEUES else None, dlT, x3T, dMb, name=f"pixel_q{b % PIXEL_QUEUES}"):
+                ops.gemm_bf16(dlT[b], x3T[b], out=dMb[b], split_k=sk)
+        for qi in range(1, min(PIXEL_QUEUES, B)):
+            join_branch(dev, fork, name=f"pixel_q{qi}")
+        del x3T
     queries = tok[:, 1:Q + 1, :]
     ops.gemm_ex(dMb, queries, K, Q, E, E, E, G["conv_out.0.weight"], Q, op_b=1, beta=1.0, batch=B, stride_a=K * E, stride_b=S * E,
                 reduce_batch=True)
@@ -624,22 +642,25 @@ def _pixel_bwd_bf16_rest(P: Params, G: Params, t, dlT: torch.Tensor, dtok: torch
     # GEMM over all pixels of the batch — nothing downstream needs either, so the whole chain runs on the weight-gradient
     # stream next to the token-path backward
     gw, gb = G[pre + "conv3x3.weight"].view(C, C * 9), G[pre + "conv3x3.bias"]
-    Mb16 = t.Mb16
+    Mb16 = getattr(t, "Mb16", None)
 
     def conv_wgrad():
-        dl = ops.transpose_bf16(dlT)                                          # [B,P,K]
-        MbT16 = ops.transpose_bf16(Mb16)                                      # [B,C,K]
-        dx3T = torch.empty(C, B * Pn, device=dev, dtype=torch.bfloat16)
-        for b in range(B):
-            ops.gemm_bf16(MbT16[b], dl[b], out=dx3T[:, b * Pn:(b + 1) * Pn])
-        del dl
+        dx = dx3T
+        if dx is None:
+            dl = ops.transpose_bf16(dlT)                                          # [B,P,K]
+            MbT16 = ops.transpose_bf16(Mb16)                                      # [B,C,K]
+            dx = torch.empty(C, B * Pn, device=dev, dtype=torch.bfloat16)
+            for b in range(B):
+                ops.gemm_bf16(MbT16[b], dl[b], out=dx[:, b * Pn:(b + 1) * Pn])
+            del dl
         col = ops.im2col3x3_bf16(ops.cast_bf16(x))
         skw = max(1, min(32, (B * Pn) // 8192))
-        ops.gemm_bf16(dx3T, col[:C * 9], residual=gw, out=gw, split_k=skw)
-        db = ops.gemm_bf16(dx3T, col[C * 9:], split_k=skw)                    # [C,8]: column 0 = sum over pixels, the rest 0
+        ops.gemm_bf16(dx, col[:C * 9], residual=gw, out=gw, split_k=skw)
+        db = ops.gemm_bf16(dx, col[C * 9:], split_k=skw)                      # [C,8]: column 0 = sum over pixels, the rest 0
         ops.reduce_channels(db, gb, 1, 1, C, 8, beta=1.0)
 
-    on_side(conv_wgrad, dlT, Mb16, x, name="conv3x3")       # its own queue: ~1 ms of HBM-bound work the layer wgrads must not wait behind
+    reads = [r for r in (dlT, Mb16, dx3T, x) if r is not None]
+    on_side(conv_wgrad, *reads, name="conv3x3")       # its own queue: HBM-bound work the layer wgrads must not wait behind
 
 
 def backward(P: Params, G: Params, t: Tape, d_depth: torch.Tensor, d_edges: Optional[torch.Tensor]) -> None:
@@ -655,16 +676,22 @@ def backward(P: Params, G: Params, t: Tape, d_depth: torch.Tensor, d_edges: Opti
     K = Wout.shape[0]
     gd = d_depth.contiguous().view(B, Pn)
     if t.pixel == "bf16":
-        dlT, dcent = _pixel_bwd_bf16_tail(P, G, t, gd)
+        dMb = dx3T = dlT = None
+        if getattr(t, "fused_tail", False):
+            # flash-style: the logits tile is recomputed on the tensor cores, d logits goes straight into the dMb / dx3^T MMAs
+            dx3T, dMb, dcent = ops.tail_fused_bwd_bf16(t.x3h, t.Mb2, t.blog2, t.centres, t.depth, t.smax, t.ssum, gd,
+                                                       grad_bias=G["conv_out.0.bias"], beta=1.0)
+        else:
+            dlT, dcent = _pixel_bwd_bf16_tail(P, G, t, gd)
         dtok = torch.zeros(B, S, E, device=dev, dtype=torch.float32)
         de = d_edges.contiguous() if d_edges is not None else None
         fork = fork_branch(dev, 16)      # bins + regressor backward (-> dtok[:, 0]) next to the dMb chain (-> dtok[:, 1:Q+1])
         with on_branch(dev, fork, dcent, de, dtok, name="regressor"):
             dy_raw = ops.bins_bwd(t.y_raw, de, dcent, cfg["min_depth"], cfg["max_depth"])
             mlp_bwd(P, G, pre + "regressor.", (0, 2, 4), t.sv_reg, dy_raw, dx_out=dtok[:, 0, :])
-        _pixel_bwd_bf16_rest(P, G, t, dlT, dtok)
+        _pixel_bwd_bf16_rest(P, G, t, dlT, dtok, dMb=dMb, dx3T=dx3T)
         join_branch(dev, fork, name="regressor")
-        del dlT
+        del dlT, dx3T
         return _token_bwd(P, G, t, dtok)
     ram = t.ram.view(B, Q, Pn)
     # ---- tail: depth = sum_k softmax_k(Wout ram + bout) c_k ----------------------------------------------------------
