@@ -186,6 +186,16 @@ int ocv_mlp_rows_f32(const float* x, long long x_ld, int R, int n_layers, const 
                      const float* const* biases_host, const int* dims_host, float* out32, void* workspace, void* stream);
 int ocv_cast_f32_to_bf16(const float* src, void* dst_bf16, long long n, void* stream);
 
+/* Training-step form of the tcgen05 GEMM (csrc/tc_gemm.cu): C = [LayerNorm]( dropout(act(op(A) op(B)^T + bias)) + residual ).
+ *   a_mn_major = 0: A is [M,K] row-major (lda);  1: A is stored [K,M] row-major (the contraction index is the ROW) and is read as
+ *   an MN-major shared-memory operand — no transposed copy.  Same for B: 0 = [N,K] (nn.Linear weight layout), 1 = [K,N].
+ *   So dX = dY W is (A = dY, B = W [N_out rows = contraction, K_in cols], b_mn_major = 1) and dW = dY^T X is (A = dY, a_mn_major = 1,
+ *   B = X, b_mn_major = 1).  drop_p > 0: keep mask of element m*N+n from (drop_seed ^ salt), as ocv_dropout_f32.
+ *   Cpre (with ln_gamma): the pre-normalisation sum, a third output.  split_k > 1: fp32 output only, fixed-order reduction. */
+int ocv_gemm_bf16_v2(const void* A, const void* Bt, int a_mn_major, int b_mn_major, const float* bias, const float* residual, int ldr,
+                     const float* ln_gamma, const float* ln_beta, float* Cpre, int ldpre, float* C32, int ldc32, void* C16, int ldc16,
+                     int M, int N, int K, int lda, int ldb, int act, float drop_p, unsigned long long drop_seed, int split_k,
+                     void* workspace, void* stream);
 /* Extended epilogue of the same kernel (the bf16 token path):
  *   y = act(A @ Wt^T + bias) + residual (fp32, row pitch ldr);  if ln_gamma: y = LayerNorm_128(y)*gamma+beta (eps 1e-5,
  *   requires N == 128, act none), rows flagged in zero_rows (uint8 [M]) are written as 0.
@@ -337,6 +347,21 @@ int ocv_encoder_layer_bwd_train_f32(const float* const* W, float* const* G, cons
                                     const float* y, const float* x1, const float* h, const float* y2, const uint8_t* mask,
                                     const float* dout, float* dx, int B, int S, int F, float drop_p, const unsigned long long* seeds,
                                     void* workspace, void* stream, void* side_stream);
+/* Tensor-core form of the two calls above (training step, precision "bf16"; csrc/train_layer.cu): all GEMMs of the layer — forward,
+ * data gradients, weight gradients — through ocv_gemm_bf16_v2, the dropout / residual / LayerNorm sites in its epilogue.
+ * W16[4]: bf16 copies of in_proj_weight, out_proj.weight, linear1.weight, linear2.weight (nn.Linear layout).  x16 / att16 / x1_16 /
+ * h16 / out16: bf16 copies of the corresponding activations ([B*S, 128 | F]) — outputs of the forward, inputs of the backward. */
+int ocv_encoder_layer_fwd_train_bf16(const float* const* W, const void* const* W16, const float* x, const void* x16,
+                                     const uint8_t* mask, int B, int S, int F, float drop_p, const unsigned long long* seeds,
+                                     float* qkv, float* att, void* att16, float* y, float* x1, void* x1_16, float* h, void* h16,
+                                     float* y2, float* out, void* out16, void* stream);
+long long ocv_encoder_layer_bwd_train_bf16_workspace(int B, int S, int F);
+int ocv_encoder_layer_bwd_train_bf16(const float* const* W, const void* const* W16, float* const* G, const void* x16, const float* qkv,
+                                     const float* att, const void* att16, const float* y, const void* x1_16, const float* h,
+                                     const void* h16, const float* y2, const uint8_t* mask, const float* dout, float* dx, int B, int S,
+                                     int F, float drop_p, const unsigned long long* seeds, void* workspace, void* stream,
+                                     void* side_stream);
+
 
 /* Backward of ocv_grid_sample_pos_f32 / ocv_ps_roi_align_pos_f32 w.r.t. the positional table (training with the grid_random /
  * grid_random_roi_align strategies; what autograd does through F.grid_sample / torchvision.ops.ps_roi_align in

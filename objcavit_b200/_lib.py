@@ -49,6 +49,8 @@ PROTOTYPES = {
     "ocv_cast_f32_to_bf16": (i32, [p, p, i64, p]),
     "ocv_mlp_rows_f32_workspace": (i64, [i32, i32, p]),
     "ocv_mlp_rows_f32": (i32, [p, i64, i32, i32, p, p, p, p, p, p]),
+    "ocv_gemm_bf16_v2": (i32, [p, p, i32, i32, p, p, i32, p, p, p, i32, p, i32, p, i32, i32, i32, i32, i32, i32, i32, f32, C.c_ulonglong,
+                                i32, p, p]),
     "ocv_gemm_bf16_ex": (i32, [p, p, p, p, i32, p, p, p, p, i32, p, i32, i32, i32, i32, i32, i32, i32, p]),
     "ocv_ffn_fused_bf16": (i32, [p, i32, p, p, p, p, p, i32, p, p, p, p, i32, p, i32, i32, i32, p]),
     "ocv_pack_conv3x3_bf16": (i32, [p, p, p]),
@@ -73,6 +75,9 @@ PROTOTYPES = {
     "ocv_encoder_layer_fwd_train_workspace": (i64, [i32, i32, i32]),
     "ocv_encoder_layer_fwd_train_f32": (i32, [p, p, p, i32, i32, i32, f32, p, p, p, p, p, p, p, p, p, p]),
     "ocv_encoder_layer_bwd_train_workspace": (i64, [i32, i32, i32]),
+    "ocv_encoder_layer_fwd_train_bf16": (i32, [p, p, p, p, p, i32, i32, i32, f32, p, p, p, p, p, p, p, p, p, p, p, p, p]),
+    "ocv_encoder_layer_bwd_train_bf16_workspace": (i64, [i32, i32, i32]),
+    "ocv_encoder_layer_bwd_train_bf16": (i32, [p, p, p, p, p, p, p, p, p, p, p, p, p, p, p, i32, i32, i32, f32, p, p, p, p]),
     "ocv_encoder_layer_bwd_train_f32": (i32, [p, p, p, p, p, p, p, p, p, p, p, p, i32, i32, i32, f32, p, p, p, p]),
     "ocv_grid_sample_pos_bwd_f32": (i32, [p, p, p, i32, i32, i32, i32, i32, f32, f32, p]),
     "ocv_ps_roi_align_pos_bwd_f32": (i32, [p, p, p, i32, i32, i32, i32, f32, i32, p]),

@@ -60,6 +60,14 @@ struct GemmParams {
   const uint8_t* zero_rows;
   __nv_bfloat16* C16;
   int ldc16, ldr;
+  // v2 (training): operand majorness, dropout in the epilogue, pre-LayerNorm sum as a third output
+  int a_mn, b_mn;                  // 1: the operand is stored [K rows, M|N cols] (contraction index = row) and read MN-major
+  uint32_t drop_thr;               // 0 = no dropout; else keep iff hash(seed, m*N+n) >= thr, kept values scaled by drop_scale
+  float drop_scale;
+  unsigned long long drop_seed;
+  const unsigned long long* drop_salt;
+  float* Cpre;                     // with LayerNorm: act(A W^T + b) [dropout] + residual BEFORE the normalisation (what its backward reads)
+  int ldpre;
 };
 
 __global__ void __launch_bounds__(512, 1)
@@ -143,37 +151,61 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   }
   if (warp == 0) {
     if (elect_one()) {
+      // K-major operand: one box [128 rows x 64 k]; MN-major operand (stored [K rows, cols]): two boxes [64 k rows x 64 cols]
+      // (= the two 64-element MN blocks of the canonical MN-major SW128 layout, 8 KB apart)
+      auto load_a = [&](int it, int s) {
+        uint8_t* dst = smem + s * STAGE_BYTES;
+        const int k = k_begin + it * GK;
+        if (p.a_mn) {
+          tma_load_2d(dst, &tmA, &full[s], m0, k);
+          tma_load_2d(dst + A_BYTES / 2, &tmA, &full[s], m0 + 64, k);
+        } else {
+          tma_load_2d(dst, &tmA, &full[s], k, m0);
+        }
+      };
+      auto load_b = [&](int it, int s) {
+        uint8_t* dst = smem + s * STAGE_BYTES + A_BYTES;
+        const int k = k_begin + it * GK;
+        if (p.b_mn) {
+          tma_load_2d(dst, &tmB, &full[s], n0, k);
+          tma_load_2d(dst + B_BYTES / 2, &tmB, &full[s], n0 + 64, k);
+        } else {
+          tma_load_2d(dst, &tmB, &full[s], k, n0);
+        }
+      };
       // weight tiles of the first stages before the grid dependency resolves, activations after it
       const int n_pre = n_k < STAGES ? n_k : STAGES;
       for (int it = 0; it < n_pre; ++it) {
         mbar_arrive_expect_tx(&full[it], STAGE_BYTES);
-        tma_load_2d(smem + it * STAGE_BYTES + A_BYTES, &tmB, &full[it], k_begin + it * GK, n0);
+        load_b(it, it);
       }
       pdl_wait();
-      for (int it = 0; it < n_pre; ++it) tma_load_2d(smem + it * STAGE_BYTES, &tmA, &full[it], k_begin + it * GK, m0);
+      for (int it = 0; it < n_pre; ++it) load_a(it, it);
       for (int it = n_pre; it < n_k; ++it) {
         const int s = it % STAGES;
         const uint32_t ph = (it / STAGES) & 1;
         mbar_wait(&empty[s], ph ^ 1);
         mbar_arrive_expect_tx(&full[s], STAGE_BYTES);
-        uint8_t* a = smem + s * STAGE_BYTES;
-        tma_load_2d(a, &tmA, &full[s], k_begin + it * GK, m0);
-        tma_load_2d(a + A_BYTES, &tmB, &full[s], k_begin + it * GK, n0);
+        load_a(it, s);
+        load_b(it, s);
       }
     }
   } else if (warp == 1) {
     if (elect_one()) {
-      constexpr uint32_t idesc = make_idesc_bf16(GM, GN);
+      const uint32_t idesc = make_idesc_bf16(GM, GN, p.a_mn, p.b_mn);
       for (int it = 0; it < n_k; ++it) {
         const int s = it % STAGES;
         const uint32_t ph = (it / STAGES) & 1;
         mbar_wait(&full[s], ph);
         tc_fence_after();
         const uint32_t a = smem_u32(smem + s * STAGE_BYTES);
-        const uint64_t da = desc_kmajor_sw128(a), db = desc_kmajor_sw128(a + A_BYTES);
+        // K-major: 16 k = +32 B on the start address; MN-major: 16 k rows = +2048 B, MN blocks A_BYTES/2 apart, 8-row groups 1 KB
+        const uint64_t da = p.a_mn ? make_smem_desc(a, A_BYTES / 2, 1024, LAYOUT_SW128) : desc_kmajor_sw128(a);
+        const uint64_t db = p.b_mn ? make_smem_desc(a + A_BYTES, B_BYTES / 2, 1024, LAYOUT_SW128) : desc_kmajor_sw128(a + A_BYTES);
+        const uint64_t sa = p.a_mn ? 128 : 2, sb = p.b_mn ? 128 : 2;   // descriptor start-address units of 16 B
 #pragma unroll
         for (int kk = 0; kk < GK / 16; ++kk)
-          umma_bf16(tmem_d, da + (uint64_t)(kk * 2), db + (uint64_t)(kk * 2), idesc, (it | kk) != 0);
+          umma_bf16(tmem_d, da + (uint64_t)kk * sa, db + (uint64_t)kk * sb, idesc, (it | kk) != 0);
         umma_commit(&empty[s]);
       }
       umma_commit(tmem_full);
@@ -225,11 +257,34 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
           for (int t = 0; t < 4; ++t) v[4 * j + t] = v[4 * j + t] > 0.f ? v[4 * j + t] : 0.01f * v[4 * j + t];
         }
+        if (p.drop_thr) {   // training: dropout of act(A W^T + b), element index m * N + n (the convention of ocv_dropout_f32)
+          const unsigned long long seed = ocv_salted(p.drop_seed, p.drop_salt);
+          const unsigned long long e0 = (unsigned long long)m * (unsigned long long)p.N + (unsigned long long)n;
+#pragma unroll
+          for (int t = 0; t < 4; ++t) v[4 * j + t] = ocv_drop_keep(seed, e0 + t, p.drop_thr) ? v[4 * j + t] * p.drop_scale : 0.f;
+        }
         if (p.residual) {
           const float4 rr = *reinterpret_cast<const float4*>(trow + 4 * j);
           v[4 * j] += rr.x; v[4 * j + 1] += rr.y; v[4 * j + 2] += rr.z; v[4 * j + 3] += rr.w;
         }
       }
+    }
+    if (p.gamma && p.Cpre) {  // the pre-normalisation sum is an output of its own (saved for the LayerNorm backward)
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<float4*>(trow + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      __syncthreads();
+      const bool vp = (p.ldpre & 3) == 0 && (reinterpret_cast<uintptr_t>(p.Cpre) & 15) == 0;
+      for (int i = threadIdx.x; i < GM * 32; i += 512) {
+        const int rr = i >> 5, c = (i & 31) * 4;
+        const int mm = m0 + rr, n = n0 + c;
+        if (mm >= p.M || n >= p.N) continue;
+        const float4 o = *reinterpret_cast<const float4*>(tile + rr * TP + c);
+        float* d = p.Cpre + (long long)mm * p.ldpre + n;
+        if (vp) *reinterpret_cast<float4*>(d) = o;
+        else { d[0] = o.x; d[1] = o.y; d[2] = o.z; d[3] = o.w; }
+      }
+      __syncthreads();
     }
     if (p.gamma) {  // LayerNorm over the N == 128 row (post-norm encoder layer: LN(residual + A W^T + b))
       float sum = 0.f;
@@ -362,6 +417,45 @@ extern "C" int ocv_gemm_bf16_ex(const void* A, const void* Wt, const float* bias
   return gemm_launch(A, Wt, M, N, K, lda, ldb, p, 1, nullptr, nullptr, 0, 0, stream);
 }
 
+extern "C" int ocv_gemm_bf16_v2(const void* A, const void* Bt, int a_mn_major, int b_mn_major, const float* bias,
+                                const float* residual, int ldr, const float* ln_gamma, const float* ln_beta, float* Cpre, int ldpre,
+                                float* C32, int ldc32, void* C16, int ldc16, int M, int N, int K, int lda, int ldb, int act,
+                                float drop_p, unsigned long long drop_seed, int split_k, void* workspace, void* stream) {
+  OCV_CHECK_ARG(A && Bt && (C32 || C16) && M > 0 && N > 0 && K > 0 && drop_p >= 0.f && drop_p < 1.f);
+  OCV_CHECK_ARG((ln_gamma == nullptr) == (ln_beta == nullptr) && (!Cpre || ln_gamma));
+  OCV_CHECK_SHAPE(lda % 8 == 0 && ldb % 8 == 0 && N % 4 == 0 && (a_mn_major ? M % 8 == 0 : K % 8 == 0));
+  OCV_CHECK_ALIGN((reinterpret_cast<uintptr_t>(bias) & 15) == 0);
+  if (split_k < 1) split_k = 1;
+  if (split_k > 1) OCV_CHECK_ARG(workspace && C32 && !C16 && !ln_gamma && drop_p == 0.f && (!residual || ldr == ldc32));
+  if (ln_gamma) {
+    OCV_CHECK_SHAPE(N == GN && act == OCV_ACT_NONE);
+    OCV_CHECK_ALIGN((!C32 || ldc32 % 4 == 0) && (!C16 || ldc16 % 4 == 0) && (!residual || ldr % 4 == 0));
+    OCV_CHECK_ALIGN(((reinterpret_cast<uintptr_t>(bias) | reinterpret_cast<uintptr_t>(residual) |
+                      reinterpret_cast<uintptr_t>(ln_gamma) | reinterpret_cast<uintptr_t>(ln_beta) |
+                      reinterpret_cast<uintptr_t>(C32)) & 15) == 0 && (reinterpret_cast<uintptr_t>(C16) & 7) == 0);
+  }
+  GemmParams p{};
+  p.bias = bias; p.residual = residual; p.ldr = ldr; p.gamma = ln_gamma; p.beta = ln_beta;
+  p.M = M; p.N = N; p.K = K; p.act = act;
+  p.a_mn = a_mn_major ? 1 : 0; p.b_mn = b_mn_major ? 1 : 0;
+  p.Cpre = Cpre; p.ldpre = ldpre;
+  if (drop_p > 0.f) {
+    p.drop_thr = ocv_drop_threshold(drop_p);
+    p.drop_scale = 1.f / (1.f - drop_p);
+    p.drop_seed = drop_seed;
+    p.drop_salt = ocv_dropout_salt();
+  }
+  if (C32) {
+    p.C = C32; p.ldc = ldc32; p.c_is_bf16 = 0;
+    p.C16 = static_cast<__nv_bfloat16*>(C16); p.ldc16 = ldc16;
+  } else if (ln_gamma) {
+    p.C = nullptr; p.C16 = static_cast<__nv_bfloat16*>(C16); p.ldc16 = ldc16;
+  } else {
+    p.C = C16; p.ldc = ldc16; p.c_is_bf16 = 1;
+  }
+  return gemm_launch(A, Bt, M, N, K, lda, ldb, p, split_k, workspace, C32, ldc32, 0, stream);
+}
+
 extern "C" int ocv_gemm_bf16(const void* A, const void* Wt, const float* bias, const float* residual, void* C, int M,
                              int N, int K, int lda, int ldb, int ldc, int act, int c_is_bf16, int split_k,
                              void* workspace, void* stream) {
@@ -383,8 +477,11 @@ static int gemm_launch(const void* A, const void* Wt, int M, int N, int K, int l
                        void* workspace, void* C_final, int ldc_final, int c_final_bf16, void* stream) {
   if (int s = ocv_require_sm100()) return s;
   CUtensorMap tmA, tmB;
-  if (int s = tc::make_tmap_2d_bf16(&tmA, A, M, K, lda, GM, GK, CU_TENSOR_MAP_SWIZZLE_128B)) return s;
-  if (int s = tc::make_tmap_2d_bf16(&tmB, Wt, N, K, ldb, GN, GK, CU_TENSOR_MAP_SWIZZLE_128B)) return s;
+  // K-major operand: tensor [rows = M|N, cols = K], box 128 x 64.  MN-major operand: tensor [rows = K, cols = M|N], box 64 x 64.
+  if (p.a_mn) { if (int s = tc::make_tmap_2d_bf16(&tmA, A, K, M, lda, GK, 64, CU_TENSOR_MAP_SWIZZLE_128B)) return s; }
+  else if (int s = tc::make_tmap_2d_bf16(&tmA, A, M, K, lda, GM, GK, CU_TENSOR_MAP_SWIZZLE_128B)) return s;
+  if (p.b_mn) { if (int s = tc::make_tmap_2d_bf16(&tmB, Wt, K, N, ldb, GK, 64, CU_TENSOR_MAP_SWIZZLE_128B)) return s; }
+  else if (int s = tc::make_tmap_2d_bf16(&tmB, Wt, N, K, ldb, GN, GK, CU_TENSOR_MAP_SWIZZLE_128B)) return s;
   static bool attr_set = false;
   if (!attr_set) {
     cudaError_t e = cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, GEMM_SMEM);

@@ -201,3 +201,162 @@ extern "C" int ocv_encoder_layer_bwd_train_f32(const float* const* W, float* con
   if (!drop) TRY(order_after(st, sd));                                             // dsa aliases dy, updated in place next
   return dgrad(dqkv, W[W_IN], dy, M, 3 * LE, LE, 1.f, ws_main, st);                // dy <- d loss / d x (residual + attention)
 }
+
+// ======================================================================================================================
+// Tensor-core form of the same layer (training step, precision "bf16"): every GEMM of the forward and of the backward —
+// data gradients AND weight gradients — runs on tcgen05 (ocv_gemm_bf16_v2: bf16 operands, fp32 accumulation in TMEM);
+// bias + ReLU + the dropout sites + residual + LayerNorm are the GEMM's epilogue, the transposed contractions of the backward
+// (dX = dY W, dW = dY^T X) read the SAME row-major tensors as MN-major operands, so no transposed copies exist.  The attention core
+// and the LayerNorm / activation backward stay the fp32 kernels (softmax statistics, row reductions); their outputs get one bf16
+// copy each (ocv_cast_f32_to_bf16) as the next GEMM's A operand.  fp32 master weights; W16 = bf16 copies in nn.Linear layout.
+// ======================================================================================================================
+namespace {
+
+enum { W16_IN = 0, W16_OUT, W16_1, W16_2, N_LAYER_W16 };
+
+int gemm16(const void* A, const void* B, int a_mn, int b_mn, const float* bias, const float* res, const float* g, const float* be,
+           float* pre, float* c32, void* c16, int M, int N, int K, int lda, int ldb, int act, float drop_p, unsigned long long seed,
+           int split, void* ws, void* st) {
+  return ocv_gemm_bf16_v2(A, B, a_mn, b_mn, bias, res, N, g, be, pre, N, c32, N, c16, N, M, N, K, lda, ldb, act, drop_p, seed, split, ws, st);
+}
+
+inline int wsplit(int Mtok) {  // split-K of the weight-gradient GEMMs (K = token rows, 1-8 output tiles): off the critical path
+  int s = Mtok / 512;
+  return s < 1 ? 1 : (s > 8 ? 8 : s);
+}
+
+// dW [N,K] += dY^T X (both operands MN-major), dB [N] += column sums of dY (fp32)
+int wgrad16(const void* dy16, const float* dy32, const void* x16, float* dw, float* db, int Mtok, int N, int K, void* ws, void* st) {
+  const int sp = wsplit(Mtok);
+  TRY(ocv_gemm_bf16_v2(dy16, x16, 1, 1, nullptr, dw, K, nullptr, nullptr, nullptr, 0, dw, K, nullptr, 0, N, K, Mtok, N, K, OCV_ACT_NONE,
+                       0.f, 0ull, sp, ws, st));
+  return ocv_reduce_channels_f32(dy32, db, 1, Mtok, N, 1, 1.f, st);
+}
+
+}  // namespace
+
+extern "C" long long ocv_encoder_layer_bwd_train_bf16_workspace(int B, int S, int F) {
+  if (B <= 0 || S <= 0 || F <= 0) return 0;
+  const long long M = (long long)B * S;
+  size_t bytes = 0;
+  bytes += 4 * al((size_t)M * LE * 4);            // dy2, df, dsa, datt
+  bytes += 2 * al((size_t)M * F * 4);             // dh, dh2
+  bytes += al((size_t)M * 3 * LE * 4);            // dqkv
+  bytes += 2 * al((size_t)M * LE * 2) + al((size_t)M * F * 2) + al((size_t)M * 3 * LE * 2);   // bf16 copies: df, dsa, dh2, dqkv
+  bytes += al((size_t)B * LH * S * 3 * 4);        // attention statistics
+  bytes += 2 * al((size_t)(M * 2 + 32 * LE) * 4); // LayerNorm row statistics + parameter partials
+  bytes += 2 * al((size_t)8 * F * 3 * LE * 4);    // split-K partials of the weight-gradient GEMMs (side stream), generous
+  return (long long)bytes;
+}
+
+extern "C" int ocv_encoder_layer_fwd_train_bf16(const float* const* W, const void* const* W16, const float* x, const void* x16,
+                                                const uint8_t* mask, int B, int S, int F, float drop_p,
+                                                const unsigned long long* seeds, float* qkv, float* att, void* att16, float* y,
+                                                float* x1, void* x1_16, float* h, void* h16, float* y2, float* out, void* out16,
+                                                void* stream) {
+  OCV_CHECK_ARG(W && W16 && x && x16 && qkv && att && att16 && y && x1 && x1_16 && h && h16 && y2 && out && out16 && B > 0 && S > 0 && F > 0);
+  OCV_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f && (drop_p == 0.f || seeds));
+  for (int i = 0; i < N_LAYER_TENSORS; ++i) OCV_CHECK_ARG(W[i] != nullptr);
+  for (int i = 0; i < N_LAYER_W16; ++i) OCV_CHECK_ARG(W16[i] != nullptr);
+  const int M = B * S;
+  const bool drop = drop_p > 0.f;
+  const float p = drop ? drop_p : 0.f;
+  // qkv = x W_in^T + b  (fp32 out: the attention core and its backward read it)
+  TRY(gemm16(x16, W16[W16_IN], 0, 0, W[B_IN], nullptr, nullptr, nullptr, nullptr, qkv, nullptr, M, 3 * LE, LE, LE, LE, OCV_ACT_NONE,
+             0.f, 0ull, 1, nullptr, stream));
+  TRY(ocv_mha_core_dropout_f32(qkv, qkv + LE, qkv + 2 * LE, att, mask, B, S, S, LH, LD, (long long)S * 3 * LE, 3 * LE,
+                               (long long)S * 3 * LE, 3 * LE, (long long)S * 3 * LE, 3 * LE, (long long)S * LE, LE, p,
+                               drop ? seeds[0] : 0ull, stream));
+  TRY(ocv_cast_f32_to_bf16(att, att16, (long long)M * LE, stream));
+  // y = x + dropout1(att W_out^T + b); x1 = LN1(y)      — one GEMM, three outputs (y, x1, bf16 x1)
+  TRY(gemm16(att16, W16[W16_OUT], 0, 0, W[B_OUT], x, W[G_1], W[BE_1], y, x1, x1_16, M, LE, LE, LE, LE, OCV_ACT_NONE, p,
+             drop ? seeds[1] : 0ull, 1, nullptr, stream));
+  // h = dropout(relu(x1 W_1^T + b))                      — fp32 (activation backward) and bf16 (next GEMM, weight gradient)
+  TRY(gemm16(x1_16, W16[W16_1], 0, 0, W[B_1], nullptr, nullptr, nullptr, nullptr, h, h16, M, F, LE, LE, LE, OCV_ACT_RELU, p,
+             drop ? seeds[2] : 0ull, 1, nullptr, stream));
+  // y2 = x1 + dropout2(h W_2^T + b); out = LN2(y2)
+  return gemm16(h16, W16[W16_2], 0, 0, W[B_2], x1, W[G_2], W[BE_2], y2, out, out16, M, LE, F, F, F, OCV_ACT_NONE, p,
+                drop ? seeds[3] : 0ull, 1, nullptr, stream);
+}
+
+extern "C" int ocv_encoder_layer_bwd_train_bf16(const float* const* W, const void* const* W16, float* const* G, const void* x16,
+                                                const float* qkv, const float* att, const void* att16, const float* y,
+                                                const void* x1_16, const float* h, const void* h16, const float* y2,
+                                                const uint8_t* mask, const float* dout, float* dx, int B, int S, int F, float drop_p,
+                                                const unsigned long long* seeds, void* workspace, void* stream, void* side_stream) {
+  OCV_CHECK_ARG(W && W16 && G && x16 && qkv && att && att16 && y && x1_16 && h && h16 && y2 && dout && dx && workspace && B > 0 && S > 0 && F > 0);
+  OCV_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f && (drop_p == 0.f || seeds));
+  OCV_CHECK_ALIGN((reinterpret_cast<uintptr_t>(workspace) & 255) == 0);
+  for (int i = 0; i < N_LAYER_TENSORS; ++i) OCV_CHECK_ARG(W[i] != nullptr && G[i] != nullptr);
+  for (int i = 0; i < N_LAYER_W16; ++i) OCV_CHECK_ARG(W16[i] != nullptr);
+  const int M = B * S;
+  const long long ME = (long long)M * LE, MF = (long long)M * F;
+  const bool drop = drop_p > 0.f;
+  cudaStream_t st = ocv_stream(stream), sd = side_stream ? ocv_stream(side_stream) : st;
+  uint8_t* p = static_cast<uint8_t*>(workspace);
+  auto take = [&](size_t bytes) { void* r = p; p += al(bytes); return r; };
+  float* dy2 = static_cast<float*>(take(ME * 4));
+  float* dfb = static_cast<float*>(take(ME * 4));
+  float* dsab = static_cast<float*>(take(ME * 4));
+  float* datt = static_cast<float*>(take(ME * 4));
+  float* dh = static_cast<float*>(take(MF * 4));
+  float* dh2 = static_cast<float*>(take(MF * 4));
+  float* dqkv = static_cast<float*>(take(ME * 3 * 4));
+  void* df16 = take(ME * 2);
+  void* dsa16 = take(ME * 2);
+  void* dh2_16 = take(MF * 2);
+  void* dqkv16 = take(ME * 3 * 2);
+  void* stats = take((size_t)B * LH * S * 3 * 4);
+  void* lnws2 = take((size_t)((long long)M * 2 + 32 * LE) * 4);
+  void* lnws1 = take((size_t)((long long)M * 2 + 32 * LE) * 4);
+  void* ws_side = take((size_t)8 * F * 3 * LE * 4);
+  float* dy = dx;  // d loss / d (x + attention branch), becomes d loss / d x after the last accumulation
+
+  const float* df = dy2;                                                           // gradient of linear2's output
+  if (drop) {
+    TRY(ocv_layernorm_bwd_dropout_f32(dout, y2, W[G_2], dy2, dfb, M, LE, drop_p, seeds[3], lnws2, st));
+    df = dfb;
+  } else {
+    TRY(ocv_layernorm_bwd_f32(dout, y2, W[G_2], dy2, nullptr, nullptr, M, LE, 1.f, lnws2, st));
+  }
+  TRY(ocv_cast_f32_to_bf16(df, df16, ME, st));
+  TRY(order_after(sd, st));
+  TRY(ocv_layernorm_bwd_params_f32(dout, y2, G[G_2], G[BE_2], M, LE, 1.f, lnws2, sd));
+  TRY(wgrad16(df16, df, h16, G[W_2], G[B_2], M, LE, F, ws_side, sd));                                   // dW2 [128,F] += df^T h
+  // dh [M,F] = df [M,128] W_2 [128,F]   (B = W_2 as stored: contraction index = row -> MN-major)
+  TRY(gemm16(df16, W16[W16_2], 0, 1, nullptr, nullptr, nullptr, nullptr, nullptr, dh, nullptr, M, F, LE, LE, F, OCV_ACT_NONE, 0.f, 0ull,
+             1, nullptr, st));
+  if (drop) TRY(ocv_dropout_act_bwd_f32(dh, h, dh2, MF, OCV_ACT_RELU, drop_p, seeds[2], st));   // h is post-dropout: h > 0 <=> kept & positive
+  else TRY(ocv_act_bwd_f32(dh, h, dh2, MF, OCV_ACT_RELU, st));
+  TRY(ocv_cast_f32_to_bf16(dh2, dh2_16, MF, st));
+  TRY(order_after(sd, st));
+  TRY(wgrad16(dh2_16, dh2, x1_16, G[W_1], G[B_1], M, F, LE, ws_side, sd));                             // dW1 [F,128] += dh2^T x1
+  if (!drop) TRY(order_after(st, sd));     // the side stream's bias-gradient sums read df = dy2, which is updated in place next
+  // dy2 += dh2 [M,F] W_1 [F,128]        (residual + FFN branch; in place: the tile is read before it is written)
+  TRY(gemm16(dh2_16, W16[W16_1], 0, 1, nullptr, dy2, nullptr, nullptr, nullptr, dy2, nullptr, M, LE, F, F, LE, OCV_ACT_NONE, 0.f, 0ull,
+             1, nullptr, st));
+  const float* dsa = dy;                                                           // gradient of out_proj's output
+  if (drop) {
+    TRY(ocv_layernorm_bwd_dropout_f32(dy2, y, W[G_1], dy, dsab, M, LE, drop_p, seeds[1], lnws1, st));
+    dsa = dsab;
+  } else {
+    TRY(ocv_layernorm_bwd_f32(dy2, y, W[G_1], dy, nullptr, nullptr, M, LE, 1.f, lnws1, st));
+  }
+  TRY(ocv_cast_f32_to_bf16(dsa, dsa16, ME, st));
+  TRY(order_after(sd, st));
+  TRY(ocv_layernorm_bwd_params_f32(dy2, y, G[G_1], G[BE_1], M, LE, 1.f, lnws1, sd));
+  TRY(wgrad16(dsa16, dsa, att16, G[W_OUT], G[B_OUT], M, LE, LE, ws_side, sd));                         // dWout += dsa^T att
+  TRY(gemm16(dsa16, W16[W16_OUT], 0, 1, nullptr, nullptr, nullptr, nullptr, nullptr, datt, nullptr, M, LE, LE, LE, LE, OCV_ACT_NONE,
+             0.f, 0ull, 1, nullptr, st));                                                              // datt = dsa W_out
+  const long long qs = (long long)S * 3 * LE;
+  TRY(ocv_mha_core_bwd_dropout_f32(qkv, qkv + LE, qkv + 2 * LE, att, datt, mask, dqkv, dqkv + LE, dqkv + 2 * LE, B, S, S, LH, LD, qs,
+                                   3 * LE, qs, 3 * LE, qs, 3 * LE, (long long)S * LE, LE, qs, 3 * LE, qs, 3 * LE, qs, 3 * LE,
+                                   drop ? drop_p : 0.f, drop ? seeds[0] : 0ull, stats, st));
+  TRY(ocv_cast_f32_to_bf16(dqkv, dqkv16, ME * 3, st));
+  TRY(order_after(sd, st));
+  TRY(wgrad16(dqkv16, dqkv, x16, G[W_IN], G[B_IN], M, 3 * LE, LE, ws_side, sd));                       // dWin [384,128] += dqkv^T x
+  if (!drop) TRY(order_after(st, sd));                                             // dsa aliases dy, updated in place next
+  // dy += dqkv [M,384] W_in [384,128]   (residual + attention branch)
+  return gemm16(dqkv16, W16[W16_IN], 0, 1, nullptr, dy, nullptr, nullptr, nullptr, dy, nullptr, M, LE, 3 * LE, 3 * LE, LE, OCV_ACT_NONE,
+                0.f, 0ull, 1, nullptr, st);
+}

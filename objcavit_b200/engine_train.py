@@ -229,10 +229,36 @@ def mlp_bwd(P: Params, G: Params, pre: str, idxs, saved, dy: torch.Tensor, dx_ou
 # ----------------------------------------------------------------------------------------------------------------------
 
 NATIVE_LAYER = True      # one C call per encoder layer and direction (csrc/train_layer.cu) instead of ~30 Python-sequenced ones
+TOKEN_BF16 = _os.environ.get("OCV_TOKEN_BF16", "1") == "1"   # precision "bf16": the encoder layers' GEMMs on tcgen05 as well
 
 
-def encoder_layer_fwd(P: Params, pre: str, x: torch.Tensor, mask, drop: DropCtx = NO_DROP):
+class LazyBf16(dict):
+    """bf16 copies of fp32 parameters, cast on first use (one forward + backward); ``HeadTrainer`` passes a mapping of views into ONE
+    bf16 mirror of its flat parameter buffer instead (a single cast kernel per step)."""
+
+    def __init__(self, P):
+        super().__init__()
+        self.P = P
+
+    def __missing__(self, key):
+        t = ops.cast_bf16(self.P[key].contiguous())
+        self[key] = t
+        return t
+
+
+
+def encoder_layer_fwd(P: Params, pre: str, x: torch.Tensor, mask, drop: DropCtx = NO_DROP, P16=None, x16=None):
+    """-> (out [B,S,E], saved) — with ``P16`` (bf16 weight copies) the tensor-core layer: returns (out, saved, out16)."""
     B, S, _ = x.shape
+    if P16 is not None:
+        p = drop.p
+        sites = (drop.site(), drop.site(), drop.site(), drop.site()) if p > 0 else None
+        xc = x.contiguous()
+        if x16 is None:
+            x16 = ops.cast_bf16(xc)
+        out, out16, sv = ops.encoder_layer_fwd_train_bf16([P[pre + k] for k in ops.LAYER_KEYS], [P16[pre + k] for k in ops.LAYER_W16_KEYS],
+                                                         xc, x16, mask, p, sites)
+        return out, ("bf16", sv, mask, (p, sites)), out16
     if NATIVE_LAYER:
         p = drop.p
         sites = (drop.site(), drop.site(), drop.site(), drop.site()) if p > 0 else None
@@ -263,7 +289,12 @@ def encoder_layer_fwd(P: Params, pre: str, x: torch.Tensor, mask, drop: DropCtx 
     return out.view(B, S, E), (x2, qkv, att, y, x1, h, y2, mask, (p, sites))
 
 
-def encoder_layer_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor) -> torch.Tensor:
+def encoder_layer_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor, P16=None) -> torch.Tensor:
+    if saved[0] == "bf16":
+        _, sv, mask, (p, sites) = saved
+        side = _side(dout.device) if ASYNC_WGRAD else None
+        return ops.encoder_layer_bwd_train_bf16([P[pre + k] for k in ops.LAYER_KEYS], [P16[pre + k] for k in ops.LAYER_W16_KEYS],
+                                                [G[pre + k] for k in ops.LAYER_KEYS], sv, mask, dout, p, sites, side)
     x2, qkv, att, y, x1, h, y2, mask, (p, sites) = saved
     B, S, _ = qkv.shape
     if NATIVE_LAYER:
@@ -296,17 +327,21 @@ def encoder_layer_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor)
     return dy.view(B, S, E)
 
 
-def encoder_fwd(P: Params, pre: str, x: torch.Tensor, mask=None, num_layers: int = 4, drop: DropCtx = NO_DROP):
+def encoder_fwd(P: Params, pre: str, x: torch.Tensor, mask=None, num_layers: int = 4, drop: DropCtx = NO_DROP, P16=None):
     saved = []
+    x16 = None
     for i in range(num_layers):
-        x, sv = encoder_layer_fwd(P, f"{pre}layers.{i}.", x, mask, drop)
+        if P16 is not None:
+            x, sv, x16 = encoder_layer_fwd(P, f"{pre}layers.{i}.", x, mask, drop, P16, x16)
+        else:
+            x, sv = encoder_layer_fwd(P, f"{pre}layers.{i}.", x, mask, drop)
         saved.append(sv)
     return x, saved
 
 
-def encoder_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor) -> torch.Tensor:
+def encoder_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor, P16=None) -> torch.Tensor:
     for i in range(len(saved) - 1, -1, -1):
-        dout = encoder_layer_bwd(P, G, f"{pre}layers.{i}.", saved[i], dout)
+        dout = encoder_layer_bwd(P, G, f"{pre}layers.{i}.", saved[i], dout, P16)
     return dout
 
 
@@ -349,7 +384,8 @@ def cross_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor, acc_q, 
 # SelfAttnCrossAttn (modules/ObjCAViT.py:167-213)
 # ----------------------------------------------------------------------------------------------------------------------
 
-def saca_fwd(P: Params, pre: str, img_tok: torch.Tensor, objs, no_obj_sa: bool, need_object_output: bool, drop: DropCtx = NO_DROP):
+def saca_fwd(P: Params, pre: str, img_tok: torch.Tensor, objs, no_obj_sa: bool, need_object_output: bool, drop: DropCtx = NO_DROP,
+             P16=None):
     B, S, _ = img_tok.shape
     dev = img_tok.device
     if isinstance(objs, ObjectBatch):
@@ -358,14 +394,14 @@ def saca_fwd(P: Params, pre: str, img_tok: torch.Tensor, objs, no_obj_sa: bool, 
             raise ValueError("more objects than image tokens: the reference's F.pad would crop; unsupported")
         uni = objs.uniform_offsets(n_max)            # made on the launching stream BEFORE the fork: the branch reads it
     fork = fork_branch(dev)
-    att_img, sv_img = encoder_fwd(P, pre + "image_transformer_encoder.", img_tok, drop=drop)
+    att_img, sv_img = encoder_fwd(P, pre + "image_transformer_encoder.", img_tok, drop=drop, P16=P16)
     sv_obj = None
     if isinstance(objs, ObjectBatch):
         with on_branch(dev, fork, objs.rows, objs.offsets, uni):
             padded, mask = ops.pad_objects(objs.rows, objs.offsets, B, n_max, n_max, 0.0001, False)        # :180-183
             att_obj = padded
             if not no_obj_sa:
-                att_obj, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", padded, mask, drop=drop)   # :188 (slow path)
+                att_obj, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", padded, mask, drop=drop, P16=P16)   # :188 (slow path)
             att_obj_s, kpm = ops.pad_objects(att_obj.reshape(B * n_max, E), uni, B, S, n_max, 0.0001, True,
                                              mask_offsets=objs.offsets)                                     # :192-194 (F5)
         geom = ("ragged", objs, uni, n_max)
@@ -374,7 +410,7 @@ def saca_fwd(P: Params, pre: str, img_tok: torch.Tensor, objs, no_obj_sa: bool, 
         with on_branch(dev, fork, objs):
             att_obj_s = objs.contiguous()
             if not no_obj_sa:
-                att_obj_s, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", att_obj_s, drop=drop)
+                att_obj_s, sv_obj = encoder_fwd(P, pre + "obj_transformer_encoder.", att_obj_s, drop=drop, P16=P16)
         kpm = None
         geom = ("dense",)
     join_branch(dev, fork, att_obj_s, kpm)
@@ -385,7 +421,7 @@ def saca_fwd(P: Params, pre: str, img_tok: torch.Tensor, objs, no_obj_sa: bool, 
     return final_img, final_obj, (sv_img, sv_obj, sv_c1, sv_c2, geom, (B, S))
 
 
-def saca_bwd(P: Params, G: Params, pre: str, saved, d_final_img: torch.Tensor, d_final_obj: Optional[torch.Tensor]):
+def saca_bwd(P: Params, G: Params, pre: str, saved, d_final_img: torch.Tensor, d_final_obj: Optional[torch.Tensor], P16=None):
     """-> (d image tokens [B,S,E], d objects: ragged rows [total,E] (block 1) or dense [B,S,E] (block 2))."""
     sv_img, sv_obj, sv_c1, sv_c2, geom, (B, S) = saved
     dev = d_final_img.device
@@ -395,18 +431,18 @@ def saca_bwd(P: Params, G: Params, pre: str, saved, d_final_img: torch.Tensor, d
     if sv_c2 is not None and d_final_obj is not None:
         cross_bwd(P, G, pre + "cross_attn_im_obj.", sv_c2, d_final_obj, (d_att_obj_s, 1.0), (d_att_img, 1.0), (d_att_obj_s, 1.0))
     fork = fork_branch(dev, 2)
-    d_img_tok = encoder_bwd(P, G, pre + "image_transformer_encoder.", sv_img, d_att_img)
+    d_img_tok = encoder_bwd(P, G, pre + "image_transformer_encoder.", sv_img, d_att_img, P16)
     with on_branch(dev, fork, d_att_obj_s):
         if geom[0] == "ragged":
             _, objs, uni, n_max = geom
             d_att_obj = ops.unpad_objects(d_att_obj_s, uni, B * n_max, n_max, True).view(B, n_max, E)
             if sv_obj is not None:
-                d_att_obj = encoder_bwd(P, G, pre + "obj_transformer_encoder.", sv_obj, d_att_obj)
+                d_att_obj = encoder_bwd(P, G, pre + "obj_transformer_encoder.", sv_obj, d_att_obj, P16)
             d_objs = ops.unpad_objects(d_att_obj.contiguous(), objs.offsets, objs.offsets_host[-1], n_max, False)
         else:
             d_objs = d_att_obj_s
             if sv_obj is not None:
-                d_objs = encoder_bwd(P, G, pre + "obj_transformer_encoder.", sv_obj, d_att_obj_s)
+                d_objs = encoder_bwd(P, G, pre + "obj_transformer_encoder.", sv_obj, d_att_obj_s, P16)
     join_branch(dev, fork, d_objs)
     return d_img_tok, d_objs
 
@@ -420,11 +456,18 @@ class Tape:
 
 
 def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_xywh_list=None, mutate_inputs: bool = True,
-            patch_size: int = 16, n_query: int = 128, drop: DropCtx = NO_DROP):
+            patch_size: int = 16, n_query: int = 128, drop: DropCtx = NO_DROP, P16=None):
     """-> (depth_pred [B,1,h,w], bin_edges [B,K+1], tape).  ``cfg``: kind ('adabins' | 'graphbins'), strategy, no_obj_sa,
     use_2_saca, min_depth, max_depth."""
     t = Tape()
     t.cfg, t.x = cfg, x
+    # precision "bf16": the encoder layers' GEMMs run on tcgen05 with bf16 copies of the weights (P16: given by the trainer as views
+    # of one bf16 mirror of its flat parameter buffer, else cast lazily here)
+    if cfg.get("pixel") == "bf16" and TOKEN_BF16 and NATIVE_LAYER:
+        P16 = P16 if P16 is not None else LazyBf16(P)
+    else:
+        P16 = None
+    t.P16 = P16
     B, C, h, w = x.shape
     t.shape = (B, C, h, w)
     # ``cfg["prefix"]``: key prefix of the mViT / ObjCAViT parameters ("" when the inner module itself is the boundary)
@@ -436,7 +479,7 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
         pt = pre + "patch_transformer."
         tok0 = _patch_embed(t, x, P[pt + "embedding_convPxP.weight"], P[pt + "embedding_convPxP.bias"],
                             P[pt + "positional_encodings"], patch_size)
-        tok, t.sv_enc = encoder_fwd(P, pt + "transformer_encoder.", tok0, drop=drop)
+        tok, t.sv_enc = encoder_fwd(P, pt + "transformer_encoder.", tok0, drop=drop, P16=P16)
     else:
         strategy = cfg["strategy"]
         feats, boxes, counts = marshal_objects(object_features, object_xywh_list, x.device)
@@ -460,9 +503,9 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
         tok0 = _patch_embed(t, x, P[pre + "image_embedding_convPxP.weight"], P[pre + "image_embedding_convPxP.bias"],
                             img_pos.contiguous(), patch_size)
         two = bool(cfg.get("use_2_saca"))
-        tok, obj_out, t.sv_saca1 = saca_fwd(P, pre + "saca_1.", tok0, batch, bool(cfg.get("no_obj_sa")), two, drop)
+        tok, obj_out, t.sv_saca1 = saca_fwd(P, pre + "saca_1.", tok0, batch, bool(cfg.get("no_obj_sa")), two, drop, P16)
         if two:
-            tok, _, t.sv_saca2 = saca_fwd(P, pre + "saca_2.", tok, obj_out, bool(cfg.get("no_obj_sa")), False, drop)
+            tok, _, t.sv_saca2 = saca_fwd(P, pre + "saca_2.", tok, obj_out, bool(cfg.get("no_obj_sa")), False, drop, P16)
     t.pre = pre
     S = tok.shape[1]
     t.tok = tok
@@ -773,15 +816,15 @@ def _token_bwd(P: Params, G: Params, t: Tape, dtok: torch.Tensor) -> None:
     S = t.tok.shape[1]
     if cfg["kind"] == "adabins":
         pt = pre + "patch_transformer."
-        dtok0 = encoder_bwd(P, G, pt + "transformer_encoder.", t.sv_enc, dtok)
+        dtok0 = encoder_bwd(P, G, pt + "transformer_encoder.", t.sv_enc, dtok, t.P16)
         wkey, bkey = pt + "embedding_convPxP.weight", pt + "embedding_convPxP.bias"
         d_pos_rows = G[pt + "positional_encodings"][0:S]
         ops.reduce_channels(dtok0.contiguous(), d_pos_rows, 1, B, S * E, 1, beta=1.0)
     else:
         d_obj = None
         if cfg.get("use_2_saca"):
-            dtok, d_obj = saca_bwd(P, G, pre + "saca_2.", t.sv_saca2, dtok, None)
-        dtok0, d_obj_tok = saca_bwd(P, G, pre + "saca_1.", t.sv_saca1, dtok, d_obj)
+            dtok, d_obj = saca_bwd(P, G, pre + "saca_2.", t.sv_saca2, dtok, None, t.P16)
+        dtok0, d_obj_tok = saca_bwd(P, G, pre + "saca_1.", t.sv_saca1, dtok, d_obj, t.P16)
         wkey, bkey = pre + "image_embedding_convPxP.weight", pre + "image_embedding_convPxP.bias"
         pe = pre + "positional_encoder."
         learned = cfg["strategy"] in ("learned", "learned_bbox_wh")

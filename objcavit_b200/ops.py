@@ -348,10 +348,14 @@ def pixel_fused_bf16(x_nhwc: torch.Tensor, w3p: torch.Tensor, Mb: torch.Tensor, 
 
 # ---- bf16 token path --------------------------------------------------------------------------------
 
-def cast_bf16(x: torch.Tensor) -> torch.Tensor:
+def cast_bf16(x: torch.Tensor, out=None) -> torch.Tensor:
     _chk(x, torch.float32, "x")
     assert x.is_contiguous()
-    out = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16)
+    if out is None:
+        out = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16)
+    else:
+        _chk(out, torch.bfloat16, "out")
+        assert out.is_contiguous() and out.numel() == x.numel()
     _call("ocv_cast_f32_to_bf16", x.data_ptr(), out.data_ptr(), x.numel(), _stream())
     return out
 
@@ -1132,5 +1136,83 @@ def encoder_layer_bwd_train(W, G, x, qkv, att, y, x1, h, y2, mask, dout: torch.T
           ws.data_ptr(), _stream(), None if side_stream is None else side_stream.cuda_stream, launches=29)
     if side_stream is not None:
         for t in (ws, x, att, x1, h):
+            t.record_stream(side_stream)
+    return dx.view(B, S, E)
+
+
+LAYER_W16_KEYS = ("self_attn.in_proj_weight", "self_attn.out_proj.weight", "linear1.weight", "linear2.weight")
+
+
+def gemm_bf16_v2(a: torch.Tensor, b: torch.Tensor, a_mn: bool = False, b_mn: bool = False, bias=None, act: int = ACT_NONE,
+                 residual=None, ln=None, want_pre: bool = False, want32: bool = True, want16: bool = False, drop=None,
+                 split_k: int = 1, out32=None):
+    """Training-step GEMM on tcgen05 (``ocv_gemm_bf16_v2``): ``[LN](dropout(act(op(a) op(b)^T + bias)) + residual)``.
+    ``a``: [M,K] (or [K,M] with ``a_mn``), ``b``: [N,K] (or [K,N] with ``b_mn``), bf16 row-major; ``drop`` = (p, seed).
+    -> (pre | None, out32 | None, out16 | None)."""
+    _chk(a, torch.bfloat16, "a"); _chk(b, torch.bfloat16, "b")
+    r0, c0, lda = _row_major_2d(a, "a")
+    r1, c1, ldb = _row_major_2d(b, "b")
+    M, K = (c0, r0) if a_mn else (r0, c0)
+    N, K2 = (c1, r1) if b_mn else (r1, c1)
+    assert K == K2, (a.shape, b.shape, a_mn, b_mn)
+    dev = a.device
+    o32 = out32 if out32 is not None else (torch.empty(M, N, device=dev, dtype=torch.float32) if want32 else None)
+    o16 = torch.empty(M, N, device=dev, dtype=torch.bfloat16) if want16 else None
+    pre = torch.empty(M, N, device=dev, dtype=torch.float32) if want_pre else None
+    ldr = 0
+    if residual is not None:
+        _chk(residual, torch.float32, "residual")
+        _, _, ldr = _row_major_2d(residual, "residual")
+    ws = None
+    if split_k > 1:
+        ws = _workspace(_lib.lib().ocv_gemm_bf16_workspace(M, N, K, split_k), dev, "gemm_bf16")
+    p_drop, seed = drop if drop is not None else (0.0, 0)
+    _call("ocv_gemm_bf16_v2", a.data_ptr(), b.data_ptr(), int(a_mn), int(b_mn), _ptr(bias), _ptr(residual), ldr,
+          _ptr(ln[0]) if ln else None, _ptr(ln[1]) if ln else None, _ptr(pre), N, _ptr(o32), o32.stride(0) if o32 is not None else 0,
+          _ptr(o16), N, M, N, K, lda, ldb, int(act), float(p_drop), int(seed), int(split_k), _ptr(ws), _stream(),
+          launches=2 if split_k > 1 else 1)
+    return pre, o32, o16
+
+
+def encoder_layer_fwd_train_bf16(W, W16, x: torch.Tensor, x16: torch.Tensor, mask, drop_p: float, seeds):
+    """Tensor-core form of :func:`encoder_layer_fwd_train`.  W16: the 4 bf16 weight copies in ``LAYER_W16_KEYS`` order; x16: bf16
+    copy of x.  -> (out fp32 [B,S,128], out bf16, saved) with saved = (x16, qkv, att, att16, y, x1_16, h, h16, y2)."""
+    import ctypes as C
+    _chk(x, torch.float32, "x"); _chk(x16, torch.bfloat16, "x16")
+    assert x.is_contiguous() and x16.is_contiguous() and x.dim() == 3 and x.shape[2] == 128 and len(W) == 12 and len(W16) == 4
+    B, S, E = x.shape
+    F_ = W[4].shape[0]
+    M, dev = B * S, x.device
+    f32 = lambda *s: torch.empty(*s, device=dev, dtype=torch.float32)
+    b16 = lambda *s: torch.empty(*s, device=dev, dtype=torch.bfloat16)
+    qkv, att, y, x1, y2, out, h = f32(B, S, 3 * E), f32(M, E), f32(M, E), f32(M, E), f32(M, E), f32(M, E), f32(M, F_)
+    att16, x1_16, out16, h16 = b16(M, E), b16(M, E), b16(M, E), b16(M, F_)
+    sd = (C.c_ulonglong * 4)(*[int(v) for v in seeds]) if drop_p > 0 else None
+    _call("ocv_encoder_layer_fwd_train_bf16", _ptr_array(W), _ptr_array(W16), x.data_ptr(), x16.data_ptr(), _ptr(mask), B, S, F_,
+          float(drop_p), sd, qkv.data_ptr(), att.data_ptr(), att16.data_ptr(), y.data_ptr(), x1.data_ptr(), x1_16.data_ptr(),
+          h.data_ptr(), h16.data_ptr(), y2.data_ptr(), out.data_ptr(), out16.data_ptr(), _stream(), launches=7)
+    return out.view(B, S, E), out16.view(B, S, E), (x16, qkv, att.view(B, S, E), att16, y, x1_16, h, h16, y2)
+
+
+def encoder_layer_bwd_train_bf16(W, W16, G, saved, mask, dout: torch.Tensor, drop_p: float, seeds, side_stream=None):
+    """Explicit backward of the layer on the tensor cores: -> dx [B,S,128]; parameter gradients ACCUMULATED into ``G``."""
+    import ctypes as C
+    x16, qkv, att, att16, y, x1_16, h, h16, y2 = saved
+    _chk(dout, torch.float32, "dout")
+    B, S, E3 = qkv.shape
+    E = E3 // 3
+    F_ = W[4].shape[0]
+    dev = dout.device
+    d = dout.reshape(B * S, E)
+    assert d.is_contiguous()
+    dx = torch.empty(B * S, E, device=dev, dtype=torch.float32)
+    ws = torch.empty(_lib.lib().ocv_encoder_layer_bwd_train_bf16_workspace(B, S, F_), device=dev, dtype=torch.uint8)
+    sd = (C.c_ulonglong * 4)(*[int(v) for v in seeds]) if drop_p > 0 else None
+    _call("ocv_encoder_layer_bwd_train_bf16", _ptr_array(W), _ptr_array(W16), _ptr_array(G), x16.data_ptr(), qkv.data_ptr(),
+          att.data_ptr(), att16.data_ptr(), y.data_ptr(), x1_16.data_ptr(), h.data_ptr(), h16.data_ptr(), y2.data_ptr(), _ptr(mask),
+          d.data_ptr(), dx.data_ptr(), B, S, F_, float(drop_p), sd, ws.data_ptr(), _stream(),
+          None if side_stream is None else side_stream.cuda_stream, launches=33)
+    if side_stream is not None:
+        for t in (ws, x16, att16, x1_16, h16):
             t.record_stream(side_stream)
     return dx.view(B, S, E)

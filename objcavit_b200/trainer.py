@@ -66,6 +66,7 @@ class HeadTrainer:
         self.head = head
         self.graph = False
         self.allreduce_events = None     # a list while the caller wants the exposed all-reduce time of every step (bench.py)
+        self.flat16, self._P16 = None, None
         self._graphs, self._graph_seen, self._graph_pool, self._salt = {}, {}, None, None
         self._capture_stream = None
         self.group = group
@@ -109,16 +110,27 @@ class HeadTrainer:
             self._modules = list(self.head.modules())
         P = {k: named[k].data for k in self.keys}
         G = engine_train.Touched({k: named[k].grad for k in self.keys})
-        return P, G
+        if self.cfg.get("pixel") == "bf16" and engine_train.TOKEN_BF16:
+            # bf16 operands of the encoder GEMMs: views (same offsets) of ONE bf16 mirror of the flat parameter buffer, refreshed by a
+            # single cast kernel at the start of every step (forward_backward)
+            if self.flat16 is None:
+                self.flat16 = torch.empty(self.flat_params.numel(), device=self.flat_params.device, dtype=torch.bfloat16)
+                offs = {id(p): off for p, off in zip(self.grads.params, self.grads.offsets)}
+                self._P16 = {k: self.flat16[offs[id(named[k])]:offs[id(named[k])] + named[k].numel()].view_as(named[k])
+                             for k in self.keys if named[k].dim() == 2 and id(named[k]) in offs}
+            return P, G, self._P16
+        return P, G, None
 
     def forward_backward(self, features, object_features, object_xywh_list, depth_gt, depth_mask):
         """Local forward + loss + backward; gradients accumulate into the flat buffer.  Returns the loss (device scalar)."""
-        P, G = self._maps()
+        P, G, P16 = self._maps()
+        if P16 is not None:
+            ops.cast_bf16(self.flat_params, out=self.flat16)
         x = features.contiguous().float()
         p_drop = float(self.head.dropout) if self.head.training else 0.0      # encoder-layer dropout, as the reference in train()
         drop = engine_train.DropCtx(p_drop, draw_dropout_seed() if p_drop > 0 else 0)
         gt = depth_gt.contiguous().float()                # before the forward: the chamfer branch below forks inside it
-        depth, edges, tape = engine_train.forward(P, self.cfg, x, object_features, object_xywh_list, drop=drop)
+        depth, edges, tape = engine_train.forward(P, self.cfg, x, object_features, object_xywh_list, drop=drop, P16=P16)
         # the chamfer loss needs only the bin edges (ready before the pixel path of the forward) and the ground truth: it runs on a
         # branch stream from that point, next to the pixel forward; SILog (needs the depth map) stays on the launching stream
         dev, fork = depth.device, getattr(tape, "edges_ready", None)

@@ -1,9 +1,16 @@
-"""GPU: the tensor-core pixel path of the training step (``precision="bf16"``: conv3x3, logits and all pixel-sized gradient GEMMs
-on tcgen05 with bf16 operands) against the fp32 parity path on the same inputs, plus its HBM-bound helper kernels against torch.
+"""GPU: the tensor-core training step (``precision="bf16"``: conv3x3, logits and all pixel-sized gradient GEMMs, and the encoder
+layers' GEMMs on tcgen05 with bf16 operands) against the fp32 parity path on the same inputs, plus its HBM-bound helper kernels
+against torch.
 
-Tolerance: north_star gives 2e-2 relative for the bf16 path; gradients: per parameter max |g - g32| <= 3e-2 * max(|g32|_max,
-1e-2 * largest |g| of the head) (bf16 operands carry 8 mantissa bits; typical measured errors are a few 1e-3), except the
-linear1 parameters of the encoder layers (ReLU gates flip under the bf16 patch embedding): cosine >= 0.98, norm within 10 %.
+Tolerance: north_star gives 2e-2 relative for the bf16 path (depth, bin edges, loss).  Gradients:
+* pixel path alone on tensor cores (``OCV_TOKEN_BF16=0``: fp32 token path): per parameter max |g - g32| <= 3e-2 * max(|g32|_max,
+  1e-2 * largest |g| of the head) (typical measured errors are a few 1e-3), except the linear1 parameters (ReLU gates flip under the
+  bf16 patch embedding): cosine >= 0.98, norm within 10 %;
+* token path on tensor cores as well (the default): the tokens carry ~1e-2 relative error, the 256-bin softmax behind them is sharp
+  (logit scale 16-26 with these weights, all range-attention channels identical by quirk F5), so single ELEMENTS of the per-bin
+  gradients move by tens of percent (measured: regressor.4.weight 0.44 max-abs) while direction and size of every gradient stay
+  put (measured: cosine >= 0.996, norm ratio 0.98 .. 1.005 over all 74 parameters).  Asserted: cosine >= 0.99, norm within 5 %.
+  The layer itself is checked element-wise against the fp32 layer kernels in tests/test_gpu_gemm_v2.py (1e-2 .. 2e-2).
 """
 import json
 import os
@@ -81,9 +88,12 @@ def _run(name, precision, cuda):
     return head, out, float(loss.detach())
 
 
+@pytest.mark.parametrize("token_bf16", [False, True], ids=["pixel_path_only", "pixel_and_token_path"])
 @pytest.mark.parametrize("name", ["train_adabins_small", "train_learned_bbox_wh_small"])
-def test_bf16_pixel_path_training_matches_fp32_path(cuda, name):
+def test_bf16_pixel_path_training_matches_fp32_path(cuda, name, token_bf16, monkeypatch):
+    from objcavit_b200 import engine_train
     h32, o32, l32 = _run(name, "fp32", cuda)
+    monkeypatch.setattr(engine_train, "TOKEN_BF16", token_bf16)
     h16, o16, l16 = _run(name, "bf16", cuda)
     assert rel_err(o16.depth_pred.detach(), o32.depth_pred.detach()) < 2e-2
     assert rel_err(o16.bin_edges.detach(), o32.bin_edges.detach()) < 2e-2      # fp32 token path fed by the bf16 patch embedding
@@ -99,6 +109,13 @@ def test_bf16_pixel_path_training_matches_fp32_path(cuda, name):
         a, r = p.grad.double().flatten(), g32[k].double().flatten()
         if float(r.abs().max()) == 0.0:                      # e.g. the object encoder of a 1-SACA head
             assert float(a.abs().max()) == 0.0, k
+            continue
+        if token_bf16:
+            cos = float((a @ r) / (a.norm() * r.norm()).clamp_min(1e-300))
+            worst_cos = min(worst_cos, cos)
+            small = float(r.abs().max()) < 1e-3 * gmax               # rounding-noise gradients: no direction to compare
+            if not small and (cos < 0.99 or abs(float(a.norm() / r.norm()) - 1.0) > 0.05):
+                bad.append(f"{k}: cosine {cos:.4f}, norm ratio {float(a.norm() / r.norm()):.3f}")
             continue
         if ".linear1." in k:
             # behind a ReLU gate of the token path: the bf16 patch embedding moves pre-activations by ~4e-3 relative, a few
