@@ -5,7 +5,7 @@
 // stream next to the image branch (patch embedding, image encoder) and an event join before the cross-attention.
 // Everything is launch-only (no allocation, no synchronisation), so a caller may capture the call in a CUDA graph.
 // Contract: include/objcavit_b200.h (ocv_head_*).
-#include "common.cuh"
+#include "tc_common.cuh"
 
 #include <algorithm>
 #include <cstdio>
@@ -100,6 +100,13 @@ struct ocv_head {
     bool used = false;
     // the token path of a lane is replayed from a CUDA graph once the same call signature has been seen twice
     cudaGraphExec_t gexec = nullptr;
+    // The captured launches bake in ONE caller address: the feature map (argument 0 of the patch-embedding GEMM, a TMA
+    // descriptor).  A serving loop hands over a freshly allocated tensor every call, so the lane keeps the source graph alive,
+    // remembers that kernel node and re-points it with cudaGraphExecKernelNodeSetParams when the address differs.
+    cudaGraph_t graph = nullptr;
+    cudaGraphNode_t pe_node = nullptr;
+    cudaKernelNodeParams pe_params = {};
+    const void* graph_x = nullptr;
     unsigned long long sig[8] = {0, 0, 0, 0, 0, 0, 0, 0}, cand[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     int graph_launches = 0;
     bool graph_failed = false;
@@ -215,6 +222,7 @@ extern "C" void ocv_head_destroy(ocv_head* H) {
     for (auto& e : l.ev)
       if (e) cudaEventDestroy(e);
     if (l.gexec) cudaGraphExecDestroy(l.gexec);
+    if (l.graph) cudaGraphDestroy(l.graph);
     if (l.tok_done) cudaEventDestroy(l.tok_done);
     if (l.pix_done) cudaEventDestroy(l.pix_done);
     release_stream(l.tok);
@@ -233,6 +241,9 @@ extern "C" int ocv_head_set_param(ocv_head* H, const char* key, const float* ptr
   for (auto& l : H->lane) {  // captured launch sequences hold the old pointers
     if (l.gexec) cudaGraphExecDestroy(l.gexec);
     l.gexec = nullptr;
+    if (l.graph) cudaGraphDestroy(l.graph);
+    l.graph = nullptr;
+    l.pe_node = nullptr;
     l.cand[5] = 0;
     l.graph_failed = false;
   }
@@ -663,14 +674,25 @@ extern "C" int ocv_head_forward(ocv_head* H, const void* X, const float* obj_fea
     if (int st = token_path()) return st;
   } else if (c.ok()) {
     // signature of the launch sequence: everything the token path's kernels were given
-    const unsigned long long sig[8] = {(unsigned long long)(uintptr_t)X, (unsigned long long)(uintptr_t)workspace,
+    const unsigned long long sig[8] = {0ull /* the input address is NOT part of it: see Lane::pe_node */, (unsigned long long)(uintptr_t)workspace,
                                        ((unsigned long long)B << 40) | ((unsigned long long)h << 20) | (unsigned long long)w,
                                        ((unsigned long long)total << 32) | (unsigned long long)n_max,
                                        (unsigned long long)(uintptr_t)H->packed, 1ull, 0ull, 0ull};
     bool replayed = false;
     if (H->use_graphs && !lane->graph_failed) {
       if (lane->gexec && memcmp(sig, lane->sig, sizeof(sig)) == 0) {
-        cudaError_t e = cudaGraphLaunch(lane->gexec, ocv_stream(s0));
+        cudaError_t e = cudaSuccess;
+        if (X != lane->graph_x) {   // same shapes, new input tensor: re-point the one node that reads it
+          CUtensorMap tmX;
+          if (int st = ocv_patch_embed_xmap(&tmX, X, B, E, h, w, P)) return st;
+          cudaKernelNodeParams kp = lane->pe_params;
+          void* args[3] = {&tmX, lane->pe_params.kernelParams[1], lane->pe_params.kernelParams[2]};
+          kp.kernelParams = args;
+          e = cudaGraphExecKernelNodeSetParams(lane->gexec, lane->pe_node, &kp);
+          if (e != cudaSuccess) return (int)e;
+          lane->graph_x = X;
+        }
+        e = cudaGraphLaunch(lane->gexec, ocv_stream(s0));
         if (e != cudaSuccess) return (int)e;
         H->launches += lane->graph_launches;
         replayed = true;
@@ -680,6 +702,11 @@ extern "C" int ocv_head_forward(ocv_head* H, const void* X, const float* obj_fea
           cudaGraphExecDestroy(lane->gexec);
           lane->gexec = nullptr;
         }
+        if (lane->graph) {
+          cudaGraphDestroy(lane->graph);
+          lane->graph = nullptr;
+        }
+        lane->pe_node = nullptr;
         cudaGraph_t g = nullptr;
         cudaError_t e = cudaStreamBeginCapture(ocv_stream(s0), cudaStreamCaptureModeThreadLocal);
         int st = OCV_OK;
@@ -688,13 +715,36 @@ extern "C" int ocv_head_forward(ocv_head* H, const void* X, const float* obj_fea
           st = token_path();
           e = cudaStreamEndCapture(ocv_stream(s0), &g);
           if (st == OCV_OK && e == cudaSuccess) e = cudaGraphInstantiate(&lane->gexec, g, 0);
-          if (g) cudaGraphDestroy(g);
+          if (st == OCV_OK && e == cudaSuccess) {   // find the patch-embedding launch (the only reader of X inside the graph)
+            size_t nn = 0;
+            e = cudaGraphGetNodes(g, nullptr, &nn);
+            std::vector<cudaGraphNode_t> nodes(nn);
+            if (e == cudaSuccess && nn) e = cudaGraphGetNodes(g, nodes.data(), &nn);
+            for (size_t i = 0; i < nn && e == cudaSuccess; ++i) {
+              cudaGraphNodeType ty;
+              if (cudaGraphNodeGetType(nodes[i], &ty) != cudaSuccess || ty != cudaGraphNodeTypeKernel) continue;
+              cudaKernelNodeParams kp;
+              if (cudaGraphKernelNodeGetParams(nodes[i], &kp) != cudaSuccess) continue;
+              if (ocv_patch_embed_is_kernel(kp.func)) {
+                lane->pe_node = nodes[i];
+                lane->pe_params = kp;   // kernelParams points into the graph's own argument storage: the graph stays alive
+              }
+            }
+            if (e == cudaSuccess && !lane->pe_node) e = cudaErrorInvalidValue;   // cannot re-point: do not replay at all
+          }
+          if (e == cudaSuccess && st == OCV_OK) {
+            lane->graph = g;
+            lane->graph_x = X;
+          } else if (g) {
+            cudaGraphDestroy(g);
+          }
           lane->graph_launches = H->launches - before;
           H->launches = before;
         }
         if (getenv("OCV_DEBUG")) fprintf(stderr, "[ocv] lane capture: status %d cuda %d (%s) nodes %d\n", st, (int)e, cudaGetErrorString(e), lane->graph_launches);
         if (st != OCV_OK || e != cudaSuccess || !lane->gexec) {
           cudaGetLastError();
+          if (lane->gexec) cudaGraphExecDestroy(lane->gexec);
           lane->gexec = nullptr;
           lane->graph_failed = true;  // fall back to eager sequencing for this lane
           c.status = OCV_OK;

@@ -253,6 +253,30 @@ PePlan pe_plan(int B, int C, int h, int w, int P) {
 
 }  // namespace
 
+// The 5-D view of the NHWC feature map the kernel's A operand is read through: (kx*C + c, tx, ky, ty, b); merged: the (ty, b) axes
+// collapse into one axis of gh*B patch rows.  Also used by the head executor to re-point a CAPTURED launch at a new feature
+// tensor (csrc/head_exec.cu: the lane graphs must not depend on the caller's input address).
+int ocv_patch_embed_xmap(CUtensorMap* out, const void* X, int B, int C, int h, int w, int P) {
+  tc::EncodeTiledFn enc = tc::get_encode_tiled();
+  if (!enc) return OCV_E_DRIVER;
+  if (reinterpret_cast<uintptr_t>(X) & 15) return OCV_E_ALIGN;
+  const PePlan q = pe_plan(B, C, h, w, P);
+  const int gh = h / P, gw = w / P;
+  cuuint64_t dims[5] = {(cuuint64_t)P * C, (cuuint64_t)gw, (cuuint64_t)P, (cuuint64_t)(q.merged ? gh * B : gh),
+                        (cuuint64_t)(q.merged ? 1 : B)};
+  cuuint64_t strides[4] = {(cuuint64_t)P * C * 2, (cuuint64_t)w * C * 2, (cuuint64_t)P * w * C * 2,
+                           (cuuint64_t)h * w * C * 2};
+  cuuint32_t box[5] = {PE_GK, (cuuint32_t)gw, 1, (cuuint32_t)q.tyb, 1};
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(X), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? OCV_OK : OCV_E_DRIVER;
+}
+
+// true iff `func` (cudaKernelNodeParams::func of a captured launch) is the patch-embedding GEMM; its argument 0 is the feature map
+bool ocv_patch_embed_is_kernel(const void* func) { return func == reinterpret_cast<const void*>(&patch_embed_kernel); }
+
 extern "C" int ocv_pack_patch_weights_bf16(const float* W, void* Wp, int E, int C, int P, void* stream) {
   OCV_CHECK_ARG(W && Wp && E > 0 && C > 0 && P > 0);
   if (int s = ocv_require_sm100()) return s;
@@ -283,19 +307,7 @@ extern "C" int ocv_patch_embed_bf16(const void* X, const void* Wp, const float* 
   if (!enc) return OCV_E_DRIVER;
   const PePlan q = pe_plan(B, C, h, w, P);
   CUtensorMap tmX, tmW;
-  {
-    // (kx*C + c, tx, ky, ty, b); merged: the (ty, b) axes collapse into one axis of gh*B patch rows
-    cuuint64_t dims[5] = {(cuuint64_t)P * C, (cuuint64_t)gw, (cuuint64_t)P, (cuuint64_t)(q.merged ? gh * B : gh),
-                          (cuuint64_t)(q.merged ? 1 : B)};
-    cuuint64_t strides[4] = {(cuuint64_t)P * C * 2, (cuuint64_t)w * C * 2, (cuuint64_t)P * w * C * 2,
-                             (cuuint64_t)h * w * C * 2};
-    cuuint32_t box[5] = {PE_GK, (cuuint32_t)gw, 1, (cuuint32_t)q.tyb, 1};
-    cuuint32_t estr[5] = {1, 1, 1, 1, 1};
-    CUresult r = enc(&tmX, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(X), dims, strides, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return OCV_E_DRIVER;
-  }
+  if (int s = ocv_patch_embed_xmap(&tmX, X, B, C, h, w, P)) return s;
   const int K = P * P * C;
   if (int s = tc::make_tmap_2d_bf16(&tmW, Wp, E, K, K, PE_E, PE_GK, CU_TENSOR_MAP_SWIZZLE_128B)) return s;
   static bool attr_set = false;

@@ -159,3 +159,7 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t rows, uint64_
                       uint32_t box_rows, uint32_t box_cols, CUtensorMapSwizzle swz);
 
 }  // namespace tc
+
+// csrc/patch_embed_bf16.cu: feature-map tensor map of the patch-embedding GEMM / identification of its captured launch
+int ocv_patch_embed_xmap(CUtensorMap* out, const void* X, int B, int C, int h, int w, int P);
+bool ocv_patch_embed_is_kernel(const void* func);

@@ -192,7 +192,7 @@ def objcavit_tokens(P, pk, pre, x_nhwc, object_features, object_xywh_list, strat
     return t32
 
 
-def head_forward(head, P, pre, x, object_features, object_xywh_list, lo, hi, mutate_inputs=True):
+def head_forward(head, P, pre, x, object_features, object_xywh_list, lo, hi, mutate_inputs=True, fingerprint=None):
     """-> (depth [B,1,h,w] fp32, bin_edges [B,K+1] fp32): ONE native call (``ocv_head_forward``) sequences every kernel;
     python only marshals the ragged object lists into CSR form."""
     x_nhwc = features_nhwc_bf16(x)
@@ -208,16 +208,15 @@ def head_forward(head, P, pre, x, object_features, object_xywh_list, lo, hi, mut
         pipe = head.__dict__.get("_ocv_pipeline")
         if pipe:
             nh.set_pipeline(*pipe)
-    nh.bind(P)
+    nh.bind(P, fingerprint)
     if object_features is None:
         return nh.forward(x_nhwc, None, None, None, 0, 0)
     feats, boxes, counts = engine.marshal_objects(object_features, object_xywh_list, x_nhwc.device)
     batch = engine.ObjectBatch(feats, counts)
     obj_tok = torch.empty(feats.shape[0], E, device=feats.device, dtype=torch.float32) if mutate_inputs else None
     depth, edges = nh.forward(x_nhwc, feats, boxes, batch.offsets, feats.shape[0], batch.n_max, obj_tok)
-    if mutate_inputs:  # F11: the reference overwrites the caller's list with the embedded tokens
-        for i in range(batch.B):
-            object_features[i] = obj_tok[batch.offsets_host[i]:batch.offsets_host[i + 1]]
+    if mutate_inputs:  # F11: the reference overwrites the caller's list with the embedded tokens (one split: B views)
+        object_features[:] = torch.split(obj_tok, counts)
     return depth, edges
 
 

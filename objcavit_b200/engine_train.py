@@ -604,6 +604,9 @@ def _pixel_prologue_rest(P: Params, pre: str, t, x: torch.Tensor) -> None:
     t.xh_keep = None
 
 
+# split-K of the conv3x3 weight-gradient GEMM (9 output tiles x split CTAs, each holding an SM's whole register file for ~100 us):
+# with 32 the GEMM fills every SM twice over and the chain's small kernels queue behind it
+DW3_SPLIT = int(_os.environ.get("OCV_DW3_SPLIT", "32"))
 FUSED_TAIL = _os.environ.get("OCV_FUSED_TAIL", "1") == "1"   # 0: the round-1 path with materialised logits (kept as the general fallback)
 
 
@@ -697,7 +700,7 @@ def _pixel_bwd_bf16_rest(P: Params, G: Params, t, dlT, dtok: torch.Tensor, dMb=N
                 ops.gemm_bf16(MbT16[b], dl[b], out=dx[:, b * Pn:(b + 1) * Pn])
             del dl
         col = ops.im2col3x3_bf16(ops.cast_bf16(x))
-        skw = max(1, min(32, (B * Pn) // 8192))
+        skw = max(1, min(DW3_SPLIT, (B * Pn) // 8192))
         ops.gemm_bf16(dx, col[:C * 9], residual=gw, out=gw, split_k=skw)
         db = ops.gemm_bf16(dx, col[C * 9:], split_k=skw)                      # [C,8]: column 0 = sum over pixels, the rest 0
         ops.reduce_channels(db, gb, 1, 1, C, 8, beta=1.0)

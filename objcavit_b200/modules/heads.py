@@ -82,10 +82,10 @@ class AdaBinsHead(_HeadBase):
         if self._wants_grad(unet_out):
             depth, edges = self._train_forward(dict(kind="adabins", min_depth=lo, max_depth=hi), unet_out, None, None)
             return self.ReturnType(depth_pred=depth, bin_edges=edges)
-        P = self._params()
+        P, fp = self._param_state()
         if self.precision == "bf16":
             from .. import engine_bf16
-            depth, edges = engine_bf16.head_forward(self, P, "adaptive_bins_layer.", unet_out, None, None, lo, hi)
+            depth, edges = engine_bf16.head_forward(self, P, "adaptive_bins_layer.", unet_out, None, None, lo, hi, fingerprint=fp)
         else:
             x = unet_out.contiguous().float()
             widths, ram = engine.mvit_forward(P, "adaptive_bins_layer.", x, 128, 'linear')
@@ -116,11 +116,11 @@ class GraphBinsHead(_HeadBase):
                        max_depth=hi)
             depth, edges = self._train_forward(cfg, dense_features, object_features, object_xywh_list)
             return self.ReturnType(depth_pred=depth, bin_edges=edges, detections=detections)
-        P = self._params()
+        P, fp = self._param_state()
         if self.precision == "bf16":
             from .. import engine_bf16
             depth, edges = engine_bf16.head_forward(self, P, "objcavit.", dense_features, object_features,
-                                                    object_xywh_list, lo, hi)
+                                                    object_xywh_list, lo, hi, fingerprint=fp)
         else:
             x = dense_features.contiguous().float()
             widths, ram = engine.objcavit_forward(P, "objcavit.", x, object_features, object_xywh_list, oc.strategy,

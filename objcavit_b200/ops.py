@@ -514,9 +514,10 @@ class NativeHead:
                 raise _lib.OcvError(f"objcavit_b200 {what}: parameter '{key}' was not registered")
         _lib.check(status, what)
 
-    def bind(self, P):
-        """(Re)register the parameters and rebuild the derived copies when any storage / version changed."""
-        sig = tuple((v.data_ptr(), v._version) for v in P.values())
+    def bind(self, P, fingerprint=None):
+        """(Re)register the parameters and rebuild the derived copies when any storage / version changed.  ``fingerprint``: the
+        change detector ``KernelModule._param_state`` already computed for these views (else it is derived here)."""
+        sig = fingerprint if fingerprint is not None else tuple((v.data_ptr(), v._version) for v in P.values())
         if sig == self.sig:
             return
         L = _lib.lib()

@@ -87,7 +87,7 @@ class HeadTrainer:
         self.step_index = 0
         self.ranges = None
         self.keys = [k for k, p in head.named_parameters() if p.requires_grad]
-        head.__dict__.pop("_ocv_param_cache", None)
+        head.invalidate_caches()
         oc = getattr(head, "objcavit", None)
         lo, hi = head._depth_range()
         if oc is None:
