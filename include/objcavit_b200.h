@@ -159,6 +159,16 @@ int ocv_mha_core_bf16(const void* q, const void* k, const void* v, void* out, co
                       int B, int Sq, int Sk, int heads, int d,
                       long long q_bstride, int q_rstride, long long k_bstride, int k_rstride,
                       long long v_bstride, int v_rstride, long long o_bstride, int o_rstride, void* stream);
+/* The same attention core on tcgen05 (csrc/attn_tc.cu; ocv_mha_core_bf16 dispatches to it when the shape is covered: 4 heads x 32,
+ * Sk <= 448, strides multiples of 8 elements, out 16-byte aligned).  One CTA = 128 query rows x a pair of heads; S = Q K^T and
+ * O = P V as tcgen05.mma with fp32 accumulators in TMEM, V read as an MN-major operand.  Extras for the training step: out32 (fp32
+ * copy of the output, same strides; or NULL), stats [B,heads,Sq,2] = (row max, row sum of 2^(s - max)) of the scaled log2-domain
+ * scores (or NULL), and dropout of the attention probabilities after the normaliser (drop_p, drop_seed: the mask of element
+ * ((b*heads + h)*Sq + q)*Sk + k, as ocv_mha_core_dropout_f32). */
+int ocv_mha_core_tc_bf16(const void* q, const void* k, const void* v, void* out16, float* out32, float* stats,
+                         const uint8_t* key_padding_mask, int B, int Sq, int Sk, int heads, int d, long long q_bstride,
+                         int q_rstride, long long k_bstride, int k_rstride, long long v_bstride, int v_rstride, long long o_bstride,
+                         int o_rstride, float drop_p, unsigned long long drop_seed, void* stream);
 
 /* Patch embedding from the NHWC bf16 feature map (tcgen05 GEMM, A operand fetched by a 5-D TMA box, split-K over ky):
  *   Wp = ocv_pack_patch_weights_bf16(W [E,C,P,P] fp32) -> bf16 [E, (ky,kx,c)];

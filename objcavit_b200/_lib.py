@@ -41,6 +41,8 @@ PROTOTYPES = {
     "ocv_nchw_to_nhwc_bf16": (i32, [p, p, i32, i32, i32, i32, i32, p]),
     "ocv_gemm_bf16_workspace": (i64, [i32, i32, i32, i32]),
     "ocv_gemm_bf16": (i32, [p, p, p, p, p, i32, i32, i32, i32, i32, i32, i32, i32, i32, p, p]),
+    "ocv_mha_core_tc_bf16": (i32, [p, p, p, p, p, p, p, i32, i32, i32, i32, i32, i64, i32, i64, i32, i64, i32, i64, i32, f32,
+                                    C.c_ulonglong, p]),
     "ocv_mha_core_bf16": (i32, [p, p, p, p, p, i32, i32, i32, i32, i32, i64, i32, i64, i32, i64, i32, i64, i32, p]),
     "ocv_pack_patch_weights_bf16": (i32, [p, p, i32, i32, i32, p]),
     "ocv_patch_embed_bf16_workspace": (i64, [i32, i32, i32, i32]),

@@ -1,0 +1,361 @@
+// Attention core of nn.MultiheadAttention on tcgen05 (bf16 operands, fp32 accumulation in TMEM), d = 32, 4 heads, Sk <= 448.
+//
+// One CTA = 128 query rows of one image x one PAIR of heads.  Two 32-wide heads share a 128-byte row, so Q, K and V are TMA
+// boxes [128 rows x 64 columns] under the 128-byte swizzle and a head is a +0 / +64 byte start offset of the UMMA descriptors
+// (probes/probe_mn_major.cu, cases 4-6).  Per head:
+//   S = Q K^T          M128 x N=Sk x K32: A = Q tile, B = all keys (both K-major), one or two MMAs of N <= 256 into TMEM
+//   softmax            256 threads: thread = query row (TMEM lane) x half of the keys; row max and row sum merged through shared
+//                      memory; masked keys (key_padding_mask, or beyond Sk) are -inf; an all-masked row gives NaN like torch
+//   O = P V            P (bf16, un-normalised, optionally dropped out) goes through a ring of [128 x 64-key] K-major tiles; V is
+//                      read where TMA put it as the MN-major B operand (N = 32 channels, K = key rows): no transposed copy
+//   out = O / rowsum   bf16 (and optionally fp32) rows, optional softmax statistics for a backward pass
+// replaces: the attention core inside nn.TransformerEncoderLayer.self_attn and the two cross-attention MHAs
+// (modules/ObjCAViT.py:155-169, 188, 195-207; modules/layers.py:8-9, 23).  Contract: include/objcavit_b200.h.
+#include "tc_common.cuh"
+#include <math.h>
+
+namespace {
+
+using namespace tc;
+
+constexpr int QT = 128, HD = 32, SKMAX = 448, CHK = 64;
+constexpr int SLAB = 128 * 128;              // [128 rows x 64 bf16]
+constexpr int KV_BOXES = 4;                  // 512 key rows of shared memory each for K and V
+constexpr int N_SOFT = 256, THREADS = 128 + N_SOFT;
+constexpr uint32_t TM_S = 0, TM_O = 448, TM_COLS = 512;
+constexpr int SMEM = SLAB /*Q*/ + 2 * KV_BOXES * SLAB /*K, V*/ + 4 * SLAB /*P ring: 2 halves x 2 slots*/ + 512 * 4 /*mask*/ +
+                     4 * 128 * 4 /*row max / sum exchange*/ + 1024 + 256;
+
+struct AttnParams {
+  __nv_bfloat16* out16;
+  float* out32;
+  float* stats;            // [B, heads, Sq, 2] (row max, row sum of 2^(s - max)) in the log2 domain, or NULL
+  const uint8_t* mask;     // [B, Sk] 1 = padding, or NULL
+  int Sq, Sk, heads;
+  long long o_bs;
+  int o_rs;
+  float qk_scale;          // log2(e) / sqrt(d)
+  uint32_t drop_thr;
+  float drop_scale;
+  unsigned long long drop_seed;
+  const unsigned long long* drop_salt;
+};
+
+__device__ __forceinline__ void tma_load_3d_(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2) {
+  tma_load_3d(smem_dst, m, bar, c0, c1, c2);
+}
+__device__ __forceinline__ float ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ void soft_bar() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+__global__ void __launch_bounds__(THREADS, 1)
+mha_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+              const __grid_constant__ CUtensorMap tmV, AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base_u32 = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024 - (base_u32 & 1023)) & 1023);
+  uint8_t* Qs = smem;
+  uint8_t* Ks = Qs + SLAB;
+  uint8_t* Vs = Ks + KV_BOXES * SLAB;
+  uint8_t* Ps = Vs + KV_BOXES * SLAB;                                  // [half][slot]
+  float* madd = reinterpret_cast<float*>(Ps + 4 * SLAB);              // [512] 0 = key takes part, -inf = masked / beyond Sk
+  float* red = madd + 512;                                            // [2 (max | sum)][2 halves][128 rows]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(red + 4 * 128);
+  uint64_t* qk_full = bars;
+  uint64_t* v_full = qk_full + 1;
+  uint64_t* m_full = v_full + 1;
+  uint64_t* s_full = m_full + 1;
+  uint64_t* s_empty = s_full + 1;
+  uint64_t* o_full = s_empty + 1;
+  uint64_t* o_empty = o_full + 1;
+  uint64_t* p_full = o_empty + 1;      // [2][2]
+  uint64_t* p_empty = p_full + 4;      // [2][2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(p_empty + 4);
+
+  pdl_launch();
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int q0 = blockIdx.x * QT, hp = blockIdx.y, b = blockIdx.z;
+  const int Sk = p.Sk, Skp = (Sk + 15) & ~15;
+  const int nchunks = (Skp + CHK - 1) / CHK;
+  const int nc0 = (nchunks + 1) / 2;                                   // chunks of key half 0; half 1 takes the rest
+  const int nb = (Sk + 127) / 128;                                     // K / V boxes
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(qk_full, 1);
+    mbar_init(v_full, 1);
+    mbar_init(m_full, 32);
+    mbar_init(s_full, 1);
+    mbar_init(s_empty, N_SOFT);
+    mbar_init(o_full, 1);
+    mbar_init(o_empty, 128);
+    for (int i = 0; i < 4; ++i) {
+      mbar_init(&p_full[i], 128);
+      mbar_init(&p_empty[i], 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, TM_COLS);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      pdl_wait();   // q / k / v are the previous kernel's output
+      mbar_arrive_expect_tx(qk_full, (1 + nb) * SLAB);
+      tma_load_3d_(Qs, &tmQ, qk_full, hp * 64, q0, b);
+      for (int i = 0; i < nb; ++i) tma_load_3d_(Ks + i * SLAB, &tmK, qk_full, hp * 64, i * 128, b);
+      mbar_arrive_expect_tx(v_full, nb * SLAB);
+      for (int i = 0; i < nb; ++i) tma_load_3d_(Vs + i * SLAB, &tmV, v_full, hp * 64, i * 128, b);
+    }
+  } else if (warp == 3) {
+    pdl_wait();
+    for (int k = lane; k < 512; k += 32)
+      madd[k] = (k < Sk && !(p.mask && p.mask[(long long)b * Sk + k])) ? 0.f : -INFINITY;
+    mbar_arrive(m_full);
+  } else if (warp == 1) {
+    if (elect_one()) {
+      const uint32_t qa = smem_u32(Qs), ka = smem_u32(Ks), va = smem_u32(Vs), pa = smem_u32(Ps);
+      const uint32_t id_pv = make_idesc_bf16(128, HD, 0, 1);
+      uint32_t cons[2] = {0, 0};
+      mbar_wait(qk_full, 0);
+      tc_fence_after();
+      for (int hd = 0; hd < 2; ++hd) {
+        const uint32_t hb = hd * 64;                                   // byte offset of the head inside a 128-byte row
+        if (hd == 1) {
+          mbar_wait(s_empty, 0);                                       // head 0's scores have been read out of TMEM
+          tc_fence_after();
+        }
+        // S = Q K^T: K rows are contiguous across the TMA boxes, so one descriptor spans up to 256 keys
+        for (int n0 = 0; n0 < Skp; n0 += 256) {
+          const int N = min(256, Skp - n0);
+          const uint32_t id = make_idesc_bf16(128, N, 0, 0);
+#pragma unroll
+          for (int kk = 0; kk < 2; ++kk)
+            umma_bf16(tmem + TM_S + n0, desc_kmajor_sw128(qa + hb + kk * 32), desc_kmajor_sw128(ka + n0 * 128 + hb + kk * 32), id, kk);
+        }
+        umma_commit(s_full);
+        if (hd == 0) {
+          mbar_wait(v_full, 0);
+        } else {
+          mbar_wait(o_empty, 0);                                       // head 0's output has left TMEM
+        }
+        tc_fence_after();
+        // O += P V, 64-key tiles of P in the order the two softmax halves produce them
+        bool first = true;
+        const int cnt[2] = {nc0, nchunks - nc0};
+        for (int i = 0; i < nc0; ++i)
+          for (int g = 0; g < 2; ++g) {
+            if (i >= cnt[g]) continue;
+            const uint32_t n = cons[g]++;
+            const int slot = n & 1, c = (g ? nc0 : 0) + i;
+            mbar_wait(&p_full[g * 2 + slot], (n >> 1) & 1);
+            tc_fence_after();
+            const uint32_t a0 = pa + (g * 2 + slot) * SLAB;
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+              umma_bf16(tmem + TM_O, desc_kmajor_sw128(a0 + kk * 32),
+                        make_smem_desc(va + (c * CHK + kk * 16) * 128 + hb, SLAB, 1024, LAYOUT_SW128), id_pv, !first);
+              first = false;
+            }
+            umma_commit(&p_empty[g * 2 + slot]);
+          }
+        umma_commit(o_full);
+      }
+    }
+  } else if (warp >= 4) {
+    const int e = warp - 4, qd = e & 3, g = e >> 2;
+    const int row = qd * 32 + lane;
+    const uint32_t lane_base = (uint32_t)(qd * 32) << 16;
+    const int cb = g ? nc0 : 0, ce = g ? nchunks : nc0;
+    const float sc = p.qk_scale;
+    const unsigned long long dseed = p.drop_thr ? ocv_salted(p.drop_seed, p.drop_salt) : 0ull;
+    uint32_t prod = 0;
+    pdl_wait();
+    mbar_wait(m_full, 0);
+    for (int hd = 0; hd < 2; ++hd) {
+      const int head = blockIdx.y * 2 + hd;
+      mbar_wait(s_full, hd);
+      tc_fence_after();
+      // ---- pass 1: row maximum over this thread's half of the keys
+      float mx = -INFINITY;
+      for (int c = cb; c < ce; ++c)
+        for (int sub = 0; sub < 2; ++sub) {
+          const int col0 = c * CHK + sub * 32;
+          if (col0 >= Skp) break;
+          uint32_t r[32];
+          tmem_ld32(tmem + lane_base + TM_S + col0, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (madd[col0 + j] == 0.f) mx = fmaxf(mx, __uint_as_float(r[j]));
+        }
+      red[g * 128 + row] = mx;
+      soft_bar();
+      const float m_row = fmaxf(red[row], red[128 + row]);
+      const float m_sc = m_row * sc;
+      // ---- pass 2: p = 2^(s*c - m*c); row sum of the un-dropped p; P tiles -> shared memory
+      float sum = 0.f;
+      const unsigned long long drow = (((unsigned long long)b * p.heads + head) * p.Sq + (unsigned long long)min(q0 + row, p.Sq - 1)) *
+                                      (unsigned long long)Sk;
+      for (int c = cb; c < ce; ++c) {
+        const uint32_t n = prod++;
+        const int slot = n & 1;
+        uint32_t pk[32];
+#pragma unroll
+        for (int sub = 0; sub < 2; ++sub) {
+          const int col0 = c * CHK + sub * 32;
+          if (col0 < Skp) {
+            uint32_t r[32];
+            tmem_ld32(tmem + lane_base + TM_S + col0, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; j += 2) {
+              float e0 = 0.f, e1 = 0.f;
+              if (madd[col0 + j] == 0.f && m_row != -INFINITY) e0 = ex2(__uint_as_float(r[j]) * sc - m_sc);
+              if (madd[col0 + j + 1] == 0.f && m_row != -INFINITY) e1 = ex2(__uint_as_float(r[j + 1]) * sc - m_sc);
+              sum += e0 + e1;
+              if (p.drop_thr) {
+                e0 = ocv_drop_keep(dseed, drow + col0 + j, p.drop_thr) ? e0 * p.drop_scale : 0.f;
+                e1 = ocv_drop_keep(dseed, drow + col0 + j + 1, p.drop_thr) ? e1 * p.drop_scale : 0.f;
+              }
+              pk[sub * 16 + j / 2] = pack_bf16(e0, e1);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) pk[sub * 16 + j] = 0u;
+          }
+        }
+        if (c == ce - 1) {                     // last read of the scores by this thread
+          tc_fence_before();
+          mbar_arrive(s_empty);
+        }
+        mbar_wait(&p_empty[g * 2 + slot], ((n >> 1) & 1) ^ 1);
+        uint8_t* prow = Ps + (g * 2 + slot) * SLAB + row * 128;
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch)
+          *reinterpret_cast<uint4*>(prow + ((ch ^ (row & 7)) << 4)) = make_uint4(pk[ch * 4], pk[ch * 4 + 1], pk[ch * 4 + 2], pk[ch * 4 + 3]);
+        fence_proxy_async_smem();
+        mbar_arrive(&p_full[g * 2 + slot]);
+      }
+      if (cb == ce) {                          // a half without keys (Sk <= 64): nothing read, still release the scores
+        tc_fence_before();
+        mbar_arrive(s_empty);
+      }
+      red[256 + g * 128 + row] = sum;
+      soft_bar();
+      if (g == 0) {
+        const float tot = red[256 + row] + red[384 + row];
+        mbar_wait(o_full, hd);
+        tc_fence_after();
+        uint32_t r[32];
+        tmem_ld32(tmem + lane_base + TM_O, r);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(o_empty);
+        const int qi = q0 + row;
+        if (qi < p.Sq) {
+          const float inv = 1.f / tot;         // every key masked: 0 * inf = NaN, like torch's softmax over all -inf
+          const long long o = (long long)b * p.o_bs + (long long)qi * p.o_rs + head * HD;
+          uint4* d16 = reinterpret_cast<uint4*>(p.out16 + o);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            d16[j] = make_uint4(pack_bf16(__uint_as_float(r[8 * j]) * inv, __uint_as_float(r[8 * j + 1]) * inv),
+                                pack_bf16(__uint_as_float(r[8 * j + 2]) * inv, __uint_as_float(r[8 * j + 3]) * inv),
+                                pack_bf16(__uint_as_float(r[8 * j + 4]) * inv, __uint_as_float(r[8 * j + 5]) * inv),
+                                pack_bf16(__uint_as_float(r[8 * j + 6]) * inv, __uint_as_float(r[8 * j + 7]) * inv));
+          if (p.out32) {
+            float4* d32 = reinterpret_cast<float4*>(p.out32 + o);
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+              d32[j] = make_float4(__uint_as_float(r[4 * j]) * inv, __uint_as_float(r[4 * j + 1]) * inv,
+                                   __uint_as_float(r[4 * j + 2]) * inv, __uint_as_float(r[4 * j + 3]) * inv);
+          }
+          if (p.stats) {
+            float2* st = reinterpret_cast<float2*>(p.stats) + ((long long)b * p.heads + head) * p.Sq + qi;
+            *st = make_float2(m_sc, tot);
+          }
+        }
+      }
+      soft_bar();   // the exchange buffers are reused by the next head
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, TM_COLS);
+}
+
+// rows of [*, 128] bf16 with arbitrary row / batch strides (elements): (64-column slice, row, image)
+int make_tmap_rows(CUtensorMap* out, const void* base, int S, int B, long long bs, int rs) {
+  EncodeTiledFn enc = get_encode_tiled();
+  if (!enc) return OCV_E_DRIVER;
+  cuuint64_t dims[3] = {128, (cuuint64_t)S, (cuuint64_t)B};
+  cuuint64_t strides[2] = {(cuuint64_t)rs * 2, (cuuint64_t)(B > 1 ? bs : (long long)rs * S) * 2};
+  cuuint32_t box[3] = {64, 128, 1};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? OCV_OK : OCV_E_DRIVER;
+}
+
+}  // namespace
+
+// 1 when the tcgen05 kernel covers the shape (else the caller keeps the mma.sync kernel)
+bool ocv_mha_tc_supported(int Sq, int Sk, int heads, int d, long long q_bs, int q_rs, long long k_bs, int k_rs, long long v_bs,
+                          int v_rs, long long o_bs, int o_rs) {
+  static int enabled = -1;
+  if (enabled < 0) {
+    const char* e = getenv("OCV_ATTN_TC");
+    enabled = (e && e[0] == '0') ? 0 : 1;
+  }
+  return enabled && heads == 4 && d == HD && Sk >= 1 && Sk <= SKMAX && Sq >= 1 &&
+         ((q_bs | k_bs | v_bs | q_rs | k_rs | v_rs) & 7) == 0 && ((o_bs | o_rs) & 7) == 0;
+}
+
+extern "C" int ocv_mha_core_tc_bf16(const void* q, const void* k, const void* v, void* out16, float* out32, float* stats,
+                                    const uint8_t* key_padding_mask, int B, int Sq, int Sk, int heads, int d, long long q_bstride,
+                                    int q_rstride, long long k_bstride, int k_rstride, long long v_bstride, int v_rstride,
+                                    long long o_bstride, int o_rstride, float drop_p, unsigned long long drop_seed, void* stream) {
+  OCV_CHECK_ARG(q && k && v && out16 && B > 0 && Sq > 0 && Sk > 0 && drop_p >= 0.f && drop_p < 1.f);
+  OCV_CHECK_SHAPE(ocv_mha_tc_supported(Sq, Sk, heads, d, q_bstride, q_rstride, k_bstride, k_rstride, v_bstride, v_rstride, o_bstride,
+                                       o_rstride) && B <= 65535);
+  const uintptr_t al = reinterpret_cast<uintptr_t>(q) | reinterpret_cast<uintptr_t>(k) | reinterpret_cast<uintptr_t>(v) |
+                       reinterpret_cast<uintptr_t>(out16) | reinterpret_cast<uintptr_t>(out32);
+  OCV_CHECK_ALIGN((al & 15) == 0 && (reinterpret_cast<uintptr_t>(stats) & 7) == 0);
+  if (int s = ocv_require_sm100()) return s;
+  CUtensorMap tmQ, tmK, tmV;
+  if (int s = make_tmap_rows(&tmQ, q, Sq, B, q_bstride, q_rstride)) return s;
+  if (int s = make_tmap_rows(&tmK, k, Sk, B, k_bstride, k_rstride)) return s;
+  if (int s = make_tmap_rows(&tmV, v, Sk, B, v_bstride, v_rstride)) return s;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(mha_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+    if (e != cudaSuccess) return (int)e;
+    attr = true;
+  }
+  AttnParams p{};
+  p.out16 = static_cast<__nv_bfloat16*>(out16); p.out32 = out32; p.stats = stats; p.mask = key_padding_mask;
+  p.Sq = Sq; p.Sk = Sk; p.heads = heads; p.o_bs = o_bstride; p.o_rs = o_rstride;
+  p.qk_scale = 1.4426950408889634f / sqrtf((float)d);
+  if (drop_p > 0.f) {
+    p.drop_thr = ocv_drop_threshold(drop_p);
+    p.drop_scale = 1.f / (1.f - drop_p);
+    p.drop_seed = drop_seed;
+    p.drop_salt = ocv_dropout_salt();
+  }
+  return ocv_launch_pdl(mha_tc_kernel, dim3(ceil_div(Sq, QT), heads / 2, B), dim3(THREADS), SMEM, stream, tmQ, tmK, tmV, p);
+}

@@ -22,6 +22,10 @@ int ocv_require_sm100();
 int ocv_pad_objects_impl(const float* src, const int32_t* offsets, const int32_t* mask_offsets, float* dst, void* dst16,
                          uint8_t* mask, int B, int L, int Nmax, int E, float pad_value, int left_pad, void* stream);
 
+// csrc/attn_tc.cu: does the tcgen05 attention kernel cover this shape / these strides (elements)?
+bool ocv_mha_tc_supported(int Sq, int Sk, int heads, int d, long long q_bs, int q_rs, long long k_bs, int k_rs, long long v_bs, int v_rs,
+                          long long o_bs, int o_rs);
+
 static inline cudaStream_t ocv_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
 __device__ __forceinline__ float warp_sum(float v) {

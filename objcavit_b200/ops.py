@@ -395,6 +395,27 @@ def mha_core_bf16(q, k, v, key_padding_mask=None, heads: int = 4):
     return out
 
 
+def mha_core_tc_bf16(q, k, v, key_padding_mask=None, heads: int = 4, want32: bool = False, want_stats: bool = False, drop=None):
+    """The tcgen05 attention core directly (``ocv_mha_core_tc_bf16``): -> (out bf16 [B,Sq,E], out fp32 | None, stats [B,H,Sq,2] | None).
+    ``drop`` = (p, seed): dropout of the attention probabilities (training)."""
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _chk(t, torch.bfloat16, n)
+        assert t.dim() == 3 and t.stride(2) == 1
+    B, Sq, E = q.shape
+    Sk = k.shape[1]
+    out = torch.empty(B, Sq, E, device=q.device, dtype=torch.bfloat16)
+    out32 = torch.empty(B, Sq, E, device=q.device, dtype=torch.float32) if want32 else None
+    stats = torch.empty(B, heads, Sq, 2, device=q.device, dtype=torch.float32) if want_stats else None
+    if key_padding_mask is not None:
+        _chk(key_padding_mask, torch.uint8, "key_padding_mask")
+        assert key_padding_mask.is_contiguous() and key_padding_mask.shape == (B, Sk)
+    p_drop, seed = drop if drop is not None else (0.0, 0)
+    _call("ocv_mha_core_tc_bf16", q.data_ptr(), k.data_ptr(), v.data_ptr(), out.data_ptr(), _ptr(out32), _ptr(stats),
+          _ptr(key_padding_mask), B, Sq, Sk, heads, E // heads, q.stride(0), q.stride(1), k.stride(0), k.stride(1), v.stride(0),
+          v.stride(1), out.stride(0), out.stride(1), float(p_drop), int(seed), _stream())
+    return out, out32, stats
+
+
 def pack_patch_weights_bf16(w: torch.Tensor) -> torch.Tensor:
     _chk(w, torch.float32, "w")
     assert w.is_contiguous() and w.dim() == 4 and w.shape[2] == w.shape[3]

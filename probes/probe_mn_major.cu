@@ -8,6 +8,10 @@
 //   1: D[m,n] = sum_k A[k,m]  B[k,n]   A MN-major, B MN-major
 //   2: D[m,n] = sum_k A[m,k]  B[k,n]   A K-major,  B MN-major with N = 256 (four blocks)
 //   3: D[m,n] = sum_k A[k,m]  B[n,k]   A MN-major, B K-major
+//   4: D[m,n] = sum_{k<32} A[m,32+k] B[n,32+k]   both K-major, start address +64 B inside the 128-byte row (the second of two
+//      32-wide heads packed in one swizzled row), K = 32
+//   5: D[m,n] = sum_k A[m,k] B[k,32+n], n < 32   B MN-major with N = 32 (half a 64-element block) at +64 B
+//   6: D[m,n] = sum_k A[k,m] B[k,32+n], n < 32   A MN-major, B MN-major N = 32 at +64 B
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O2 -I../include -o probe_mn_major.bin probe_mn_major.cu ../objcavit_b200/csrc/tc_gemm.cu ../objcavit_b200/csrc/api.cu
 #include "../objcavit_b200/csrc/tc_common.cuh"
 #include <vector>
@@ -20,7 +24,7 @@ constexpr int SLAB = 128 * 128;   // [128 rows x 64 bf16] = 16 KB
 __device__ __forceinline__ uint64_t desc_mn(uint32_t saddr, uint32_t lbo, uint32_t sbo) { return make_smem_desc(saddr, lbo, sbo, LAYOUT_SW128); }
 
 __global__ void __launch_bounds__(128, 1)
-probe_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmX, float* out /*[4][128][256]*/) {
+probe_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmX, float* out /*[7][128][256]*/) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base_u32 = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024 - (base_u32 & 1023)) & 1023);
@@ -47,7 +51,7 @@ probe_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CU
   }
   mbar_wait(bar_load, 0);
   __syncthreads();
-  for (int c = 0; c < 4; ++c) {
+  for (int c = 0; c < 7; ++c) {
     if (threadIdx.x == 0) {
       tc_fence_after();
       const uint32_t p0 = smem_u32(sP), x0 = smem_u32(sX);
@@ -60,6 +64,10 @@ probe_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CU
         if (c == 1) umma_bf16(tmem_d, a_mn, b_mn, make_idesc_bf16(128, 128, 1, 1), kk != 0);
         if (c == 2) umma_bf16(tmem_d, a_k, b_mn, make_idesc_bf16(128, 256, 0, 1), kk != 0);
         if (c == 3) umma_bf16(tmem_d, a_mn, b_k, make_idesc_bf16(128, 128, 1, 0), kk != 0);
+        if (c == 4 && kk < 2) umma_bf16(tmem_d, desc_kmajor_sw128(p0 + 64 + kk * 32), desc_kmajor_sw128(x0 + 64 + kk * 32),
+                                        make_idesc_bf16(128, 128, 0, 0), kk != 0);
+        if (c == 5) umma_bf16(tmem_d, a_k, desc_mn(x0 + 64 + kk * 2048, SLAB, 1024), make_idesc_bf16(128, 32, 0, 1), kk != 0);
+        if (c == 6) umma_bf16(tmem_d, a_mn, desc_mn(x0 + 64 + kk * 2048, SLAB, 1024), make_idesc_bf16(128, 32, 1, 1), kk != 0);
       }
       umma_commit(bar_mma);
     }
@@ -88,8 +96,8 @@ int main() {
   float* dO;
   cudaMalloc(&dP, hP.size() * 2);
   cudaMalloc(&dX, hX.size() * 2);
-  cudaMalloc(&dO, 4 * 128 * 256 * 4);
-  cudaMemset(dO, 0, 4 * 128 * 256 * 4);
+  cudaMalloc(&dO, 7 * 128 * 256 * 4);
+  cudaMemset(dO, 0, 7 * 128 * 256 * 4);
   cudaMemcpy(dP, hP.data(), hP.size() * 2, cudaMemcpyHostToDevice);
   cudaMemcpy(dX, hX.data(), hX.size() * 2, cudaMemcpyHostToDevice);
   CUtensorMap tmP, tmX;
@@ -100,20 +108,22 @@ int main() {
   probe_kernel<<<1, 128, smem>>>(tmP, tmX, dO);
   cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) { printf("CUDA error: %s\n", cudaGetErrorString(e)); return 1; }
-  std::vector<float> hO(4 * 128 * 256);
+  std::vector<float> hO(7 * 128 * 256);
   cudaMemcpy(hO.data(), dO, hO.size() * 4, cudaMemcpyDeviceToHost);
-  const char* names[4] = {"A K-major,  B MN-major, N=128", "A MN-major, B MN-major, N=128", "A K-major,  B MN-major, N=256",
-                          "A MN-major, B K-major,  N=128"};
+  const char* names[7] = {"A K-major,  B MN-major, N=128", "A MN-major, B MN-major, N=128", "A K-major,  B MN-major, N=256",
+                          "A MN-major, B K-major,  N=128", "K-major +64 B, K=32", "B MN-major N=32 +64 B", "A MN, B MN N=32 +64 B"};
   int rc = 0;
-  for (int c = 0; c < 4; ++c) {
-    const int N = c == 2 ? 256 : 128;
+  for (int c = 0; c < 7; ++c) {
+    const int N = c == 2 ? 256 : (c >= 5 ? 32 : 128);
     int bad = 0;
     for (int m = 0; m < 128; ++m)
       for (int n = 0; n < N; ++n) {
         float want = 0.f;
-        for (int k = 0; k < 128; ++k) {
-          const float a = (c == 0 || c == 2) ? fP[m * 128 + k] : fP[k * 128 + m];
-          const float b = c == 3 ? fX[n * 256 + k] : fX[k * 256 + n];
+        for (int k = 0; k < (c == 4 ? 32 : 128); ++k) {
+          float a = (c == 0 || c == 2 || c == 5) ? fP[m * 128 + k] : fP[k * 128 + m];
+          float b = c == 3 ? fX[n * 256 + k] : fX[k * 256 + n];
+          if (c == 4) { a = fP[m * 128 + 32 + k]; b = fX[n * 256 + 32 + k]; }
+          if (c >= 5) b = fX[k * 256 + 32 + n];
           want += a * b;
         }
         if (want != hO[((size_t)c * 128 + m) * 256 + n]) ++bad;
