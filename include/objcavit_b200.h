@@ -169,6 +169,15 @@ int ocv_mha_core_tc_bf16(const void* q, const void* k, const void* v, void* out1
                          const uint8_t* key_padding_mask, int B, int Sq, int Sk, int heads, int d, long long q_bstride,
                          int q_rstride, long long k_bstride, int k_rstride, long long v_bstride, int v_rstride, long long o_bstride,
                          int o_rstride, float drop_p, unsigned long long drop_seed, void* stream);
+/* Backward of the attention core on tcgen05 (one CTA per (image, head); Sq, Sk <= 256): from q / k / v (bf16), the forward output
+ * o16 and its gradient do16 (bf16, strides o_*), and the forward's statistics: dq / dk / dv in fp32 (strides g_*) and bf16 copies.
+ * S and dO V^T per 128 x 128 tile in TMEM, P and dS recomputed in registers (dropout masks regenerated), dV += Pd^T dO,
+ * dK += dS^T Q, dQ += dS K with the bf16 tiles read as MN-major operands.  Nothing of size Sq x Sk reaches HBM. */
+int ocv_mha_core_bwd_tc_bf16(const void* q16, const void* k16, const void* v16, const void* o16, const void* do16, const float* stats,
+                             const uint8_t* key_padding_mask, float* dq32, float* dk32, float* dv32, void* dq16, void* dk16,
+                             void* dv16, int B, int Sq, int Sk, int heads, int d, long long q_bstride, int q_rstride,
+                             long long kv_bstride, int kv_rstride, long long o_bstride, int o_rstride, long long g_bstride,
+                             int g_rstride, float drop_p, unsigned long long drop_seed, void* stream);
 
 /* Patch embedding from the NHWC bf16 feature map (tcgen05 GEMM, A operand fetched by a 5-D TMA box, split-K over ky):
  *   Wp = ocv_pack_patch_weights_bf16(W [E,C,P,P] fp32) -> bf16 [E, (ky,kx,c)];
@@ -363,10 +372,13 @@ int ocv_encoder_layer_bwd_train_f32(const float* const* W, float* const* G, cons
  * h16 / out16: bf16 copies of the corresponding activations ([B*S, 128 | F]) — outputs of the forward, inputs of the backward. */
 int ocv_encoder_layer_fwd_train_bf16(const float* const* W, const void* const* W16, const float* x, const void* x16,
                                      const uint8_t* mask, int B, int S, int F, float drop_p, const unsigned long long* seeds,
-                                     float* qkv, float* att, void* att16, float* y, float* x1, void* x1_16, float* h, void* h16,
-                                     float* y2, float* out, void* out16, void* stream);
+                                     float* qkv, void* qkv16 /* [B*S,384] bf16, or NULL: fp32 attention core */,
+                                     float* att_stats /* [B,4,S,2] softmax statistics of the tcgen05 attention core, or NULL */,
+                                     float* att, void* att16, float* y, float* x1, void* x1_16, float* h, void* h16, float* y2,
+                                     float* out, void* out16, void* stream);
 long long ocv_encoder_layer_bwd_train_bf16_workspace(int B, int S, int F);
 int ocv_encoder_layer_bwd_train_bf16(const float* const* W, const void* const* W16, float* const* G, const void* x16, const float* qkv,
+                                     const void* qkv16, const float* att_stats /* both from the forward, or NULL: fp32 attention backward */,
                                      const float* att, const void* att16, const float* y, const void* x1_16, const float* h,
                                      const void* h16, const float* y2, const uint8_t* mask, const float* dout, float* dx, int B, int S,
                                      int F, float drop_p, const unsigned long long* seeds, void* workspace, void* stream,

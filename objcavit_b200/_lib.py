@@ -77,9 +77,11 @@ PROTOTYPES = {
     "ocv_encoder_layer_fwd_train_workspace": (i64, [i32, i32, i32]),
     "ocv_encoder_layer_fwd_train_f32": (i32, [p, p, p, i32, i32, i32, f32, p, p, p, p, p, p, p, p, p, p]),
     "ocv_encoder_layer_bwd_train_workspace": (i64, [i32, i32, i32]),
-    "ocv_encoder_layer_fwd_train_bf16": (i32, [p, p, p, p, p, i32, i32, i32, f32, p, p, p, p, p, p, p, p, p, p, p, p, p]),
+    "ocv_encoder_layer_fwd_train_bf16": (i32, [p, p, p, p, p, i32, i32, i32, f32, p, p, p, p, p, p, p, p, p, p, p, p, p, p, p]),
+    "ocv_mha_core_bwd_tc_bf16": (i32, [p, p, p, p, p, p, p, p, p, p, p, p, p, i32, i32, i32, i32, i32, i64, i32, i64, i32, i64, i32,
+                                        i64, i32, f32, C.c_ulonglong, p]),
     "ocv_encoder_layer_bwd_train_bf16_workspace": (i64, [i32, i32, i32]),
-    "ocv_encoder_layer_bwd_train_bf16": (i32, [p, p, p, p, p, p, p, p, p, p, p, p, p, p, p, i32, i32, i32, f32, p, p, p, p]),
+    "ocv_encoder_layer_bwd_train_bf16": (i32, [p, p, p, p, p, p, p, p, p, p, p, p, p, p, p, p, p, i32, i32, i32, f32, p, p, p, p]),
     "ocv_encoder_layer_bwd_train_f32": (i32, [p, p, p, p, p, p, p, p, p, p, p, p, i32, i32, i32, f32, p, p, p, p]),
     "ocv_grid_sample_pos_bwd_f32": (i32, [p, p, p, i32, i32, i32, i32, i32, f32, f32, p]),
     "ocv_ps_roi_align_pos_bwd_f32": (i32, [p, p, p, i32, i32, i32, i32, f32, i32, p]),

@@ -65,8 +65,8 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
   uint8_t* Ks = Qs + SLAB;
   uint8_t* Vs = Ks + KV_BOXES * SLAB;
   uint8_t* Ps = Vs + KV_BOXES * SLAB;                                  // [half][slot]
-  float* madd = reinterpret_cast<float*>(Ps + 4 * SLAB);              // [512] 0 = key takes part, -inf = masked / beyond Sk
-  float* red = madd + 512;                                            // [2 (max | sum)][2 halves][128 rows]
+  uint32_t* valid = reinterpret_cast<uint32_t*>(Ps + 4 * SLAB);       // [16] bit j of word w: key 32 w + j takes part (not masked, < Sk)
+  float* red = reinterpret_cast<float*>(valid) + 512;                 // [2 (max | sum)][2 halves][128 rows]
   uint64_t* bars = reinterpret_cast<uint64_t*>(red + 4 * 128);
   uint64_t* qk_full = bars;
   uint64_t* v_full = qk_full + 1;
@@ -123,8 +123,12 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
     }
   } else if (warp == 3) {
     pdl_wait();
-    for (int k = lane; k < 512; k += 32)
-      madd[k] = (k < Sk && !(p.mask && p.mask[(long long)b * Sk + k])) ? 0.f : -INFINITY;
+    for (int w = 0; w < 16; ++w) {
+      const int k = w * 32 + lane;
+      const bool ok = k < Sk && !(p.mask && p.mask[(long long)b * Sk + k]);
+      const uint32_t bits = __ballot_sync(0xffffffffu, ok);
+      if (lane == 0) valid[w] = bits;
+    }
     mbar_arrive(m_full);
   } else if (warp == 1) {
     if (elect_one()) {
@@ -199,9 +203,15 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
           uint32_t r[32];
           tmem_ld32(tmem + lane_base + TM_S + col0, r);
           tmem_ld_wait();
+          const uint32_t vb = valid[col0 >> 5];          // the same word for every thread: warp-uniform branches
+          if (vb == 0xffffffffu) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (madd[col0 + j] == 0.f) mx = fmaxf(mx, __uint_as_float(r[j]));
+            for (int j = 0; j < 32; j += 2) mx = fmaxf(mx, fmaxf(__uint_as_float(r[j]), __uint_as_float(r[j + 1])));
+          } else if (vb) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if ((vb >> j) & 1u) mx = fmaxf(mx, __uint_as_float(r[j]));
+          }
         }
       red[g * 128 + row] = mx;
       soft_bar();
@@ -222,17 +232,30 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
             uint32_t r[32];
             tmem_ld32(tmem + lane_base + TM_S + col0, r);
             tmem_ld_wait();
+            const uint32_t vb = (m_row != -INFINITY) ? valid[col0 >> 5] : 0u;
+            if (vb == 0xffffffffu && !p.drop_thr) {          // the common case: no masked key in the group, inference
+              float s0 = 0.f, s1 = 0.f;
 #pragma unroll
-            for (int j = 0; j < 32; j += 2) {
-              float e0 = 0.f, e1 = 0.f;
-              if (madd[col0 + j] == 0.f && m_row != -INFINITY) e0 = ex2(__uint_as_float(r[j]) * sc - m_sc);
-              if (madd[col0 + j + 1] == 0.f && m_row != -INFINITY) e1 = ex2(__uint_as_float(r[j + 1]) * sc - m_sc);
-              sum += e0 + e1;
-              if (p.drop_thr) {
-                e0 = ocv_drop_keep(dseed, drow + col0 + j, p.drop_thr) ? e0 * p.drop_scale : 0.f;
-                e1 = ocv_drop_keep(dseed, drow + col0 + j + 1, p.drop_thr) ? e1 * p.drop_scale : 0.f;
+              for (int j = 0; j < 32; j += 2) {
+                const float e0 = ex2(fmaf(__uint_as_float(r[j]), sc, -m_sc)), e1 = ex2(fmaf(__uint_as_float(r[j + 1]), sc, -m_sc));
+                s0 += e0;
+                s1 += e1;
+                pk[sub * 16 + j / 2] = pack_bf16(e0, e1);
               }
-              pk[sub * 16 + j / 2] = pack_bf16(e0, e1);
+              sum += s0 + s1;
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; j += 2) {
+                float e0 = 0.f, e1 = 0.f;
+                if ((vb >> j) & 1u) e0 = ex2(fmaf(__uint_as_float(r[j]), sc, -m_sc));
+                if ((vb >> (j + 1)) & 1u) e1 = ex2(fmaf(__uint_as_float(r[j + 1]), sc, -m_sc));
+                sum += e0 + e1;
+                if (p.drop_thr) {
+                  e0 = ocv_drop_keep(dseed, drow + col0 + j, p.drop_thr) ? e0 * p.drop_scale : 0.f;
+                  e1 = ocv_drop_keep(dseed, drow + col0 + j + 1, p.drop_thr) ? e1 * p.drop_scale : 0.f;
+                }
+                pk[sub * 16 + j / 2] = pack_bf16(e0, e1);
+              }
             }
           } else {
 #pragma unroll
@@ -358,4 +381,354 @@ extern "C" int ocv_mha_core_tc_bf16(const void* q, const void* k, const void* v,
     p.drop_salt = ocv_dropout_salt();
   }
   return ocv_launch_pdl(mha_tc_kernel, dim3(ceil_div(Sq, QT), heads / 2, B), dim3(THREADS), SMEM, stream, tmQ, tmK, tmV, p);
+}
+
+// ======================================================= backward =======================================================
+// One CTA = one (image, head), Sq, Sk <= 256 (two 128-row tiles each: the training shapes 221 / 242 / 32).  For every
+// (key tile u, query tile t):
+//   S = Q_t K_u^T and dPd = dO_t V_u^T        two small MMAs into TMEM (K = 32)
+//   epilogue (thread = query row x 64 keys)    P = 2^(c s - m) / sum from the forward's statistics, dropout mask regenerated,
+//                                              Pd = P o D', dS = P o (dPd o D' - delta), delta = rowsum(dO o O)
+//                                              -> two bf16 tiles [128 q x 128 k] in shared memory
+//   dV_u += Pd^T dO_t, dK_u += dS^T Q_t        the tiles read as MN-major A operands (M = keys), dO / Q as MN-major B (N = 32)
+//   dQ_t += dS K_u                             dS K-major, K_u as MN-major B
+// dV / dK accumulate in TMEM over the query tiles, dQ over the key tiles; nothing of size Sq x Sk touches HBM.
+namespace {
+
+constexpr int BW_MAXS = 256;
+constexpr uint32_t TB_S = 0, TB_DP = 128, TB_DV = 256, TB_DK = 288, TB_DQ = 320, TB_COLS = 512;
+constexpr int BW_SMEM = 8 * SLAB /*Q, K, V, dO: two tiles each*/ + 4 * SLAB /*Pd, dS tiles*/ + 3 * BW_MAXS * 4 /*m, 1/sum, delta*/ +
+                        64 /*valid bits*/ + 1024 + 256;
+
+struct AttnBwdParams {
+  const __nv_bfloat16* o16;      // forward output [B,Sq,128] (for delta)
+  const __nv_bfloat16* do16;     // its gradient (same strides)
+  const float* stats;            // [B,heads,Sq,2] from the forward
+  const uint8_t* mask;
+  float *dq32, *dk32, *dv32;     // fp32 gradients (strides g_bs / g_rs) — and their bf16 copies
+  __nv_bfloat16 *dq16, *dk16, *dv16;
+  int Sq, Sk, heads;
+  long long o_bs, g_bs;
+  int o_rs, g_rs;
+  float qk_scale, scale;         // log2(e)/sqrt(d), 1/sqrt(d)
+  uint32_t drop_thr;
+  float drop_scale;
+  unsigned long long drop_seed;
+  const unsigned long long* drop_salt;
+};
+
+__global__ void __launch_bounds__(THREADS, 1)
+mha_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
+                  const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO, AttnBwdParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base_u32 = smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + ((1024 - (base_u32 & 1023)) & 1023);
+  uint8_t* Qs = smem;                    // [2 tiles]
+  uint8_t* Ks = Qs + 2 * SLAB;
+  uint8_t* Vs = Ks + 2 * SLAB;
+  uint8_t* DOs = Vs + 2 * SLAB;
+  uint8_t* Pt = DOs + 2 * SLAB;          // Pd tile: [2 key halves] of [128 q rows x 64 keys]
+  uint8_t* St = Pt + 2 * SLAB;           // dS tile
+  float* rm = reinterpret_cast<float*>(St + 2 * SLAB);   // [256] row max (log2 domain)
+  float* ri = rm + BW_MAXS;                               // [256] 1 / row sum
+  float* dl = ri + BW_MAXS;                               // [256] delta
+  uint32_t* valid = reinterpret_cast<uint32_t*>(dl + BW_MAXS);   // [8 words]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(valid + 16);
+  uint64_t* ld_full = bars;
+  uint64_t* sd_full = ld_full + 1;
+  uint64_t* sd_empty = sd_full + 1;
+  uint64_t* tile_full = sd_empty + 1;
+  uint64_t* tile_empty = tile_full + 1;
+  uint64_t* kv_full = tile_empty + 1;
+  uint64_t* kv_empty = kv_full + 1;
+  uint64_t* q_full = kv_empty + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_full + 1);
+
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int head = blockIdx.x, b = blockIdx.y;
+  const int hp = head >> 1;
+  const uint32_t hb = (head & 1) * 64;
+  const int Sq = p.Sq, Sk = p.Sk;
+  const int nt = (Sq + 127) / 128, nu = (Sk + 127) / 128;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmQ);
+    tma_prefetch_desc(&tmK);
+    tma_prefetch_desc(&tmV);
+    tma_prefetch_desc(&tmDO);
+  }
+  if (warp == 1 && lane == 0) {
+    mbar_init(ld_full, 1);
+    mbar_init(sd_full, 1);
+    mbar_init(sd_empty, N_SOFT);
+    mbar_init(tile_full, N_SOFT);
+    mbar_init(tile_empty, 1);
+    mbar_init(kv_full, 1);
+    mbar_init(kv_empty, N_SOFT);
+    mbar_init(q_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, TB_COLS);
+  if (warp == 3) {
+    for (int w = 0; w < 8; ++w) {
+      const int k = w * 32 + lane;
+      const bool ok = k < Sk && !(p.mask && p.mask[(long long)b * Sk + k]);
+      const uint32_t bits = __ballot_sync(0xffffffffu, ok);
+      if (lane == 0) valid[w] = bits;
+    }
+  }
+  if (warp >= 4) {
+    // per-row statistics of the forward and delta = rowsum(dO o O)
+    const int i = threadIdx.x - 128;
+    if (i < Sq) {
+      const float2 st = reinterpret_cast<const float2*>(p.stats)[((long long)b * p.heads + head) * Sq + i];
+      rm[i] = st.x;
+      ri[i] = 1.f / st.y;
+      const long long o = (long long)b * p.o_bs + (long long)i * p.o_rs + head * HD;
+      const uint4* po = reinterpret_cast<const uint4*>(p.o16 + o);
+      const uint4* pd = reinterpret_cast<const uint4*>(p.do16 + o);
+      float acc = 0.f;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const uint4 a = __ldg(po + j), g4 = __ldg(pd + j);
+        const __nv_bfloat162* ah = reinterpret_cast<const __nv_bfloat162*>(&a);
+        const __nv_bfloat162* gh = reinterpret_cast<const __nv_bfloat162*>(&g4);
+#pragma unroll
+        for (int t2 = 0; t2 < 4; ++t2) {
+          const float2 x = __bfloat1622float2(ah[t2]), y = __bfloat1622float2(gh[t2]);
+          acc = fmaf(x.x, y.x, fmaf(x.y, y.y, acc));
+        }
+      }
+      dl[i] = acc;
+    } else if (i < BW_MAXS) {
+      rm[i] = 0.f;
+      ri[i] = 0.f;
+      dl[i] = 0.f;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      mbar_arrive_expect_tx(ld_full, (2 * nt + 2 * nu) * SLAB);
+      for (int t = 0; t < nt; ++t) {
+        tma_load_3d(Qs + t * SLAB, &tmQ, ld_full, hp * 64, t * 128, b);
+        tma_load_3d(DOs + t * SLAB, &tmDO, ld_full, hp * 64, t * 128, b);
+      }
+      for (int u = 0; u < nu; ++u) {
+        tma_load_3d(Ks + u * SLAB, &tmK, ld_full, hp * 64, u * 128, b);
+        tma_load_3d(Vs + u * SLAB, &tmV, ld_full, hp * 64, u * 128, b);
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      const uint32_t qa = smem_u32(Qs), ka = smem_u32(Ks), va = smem_u32(Vs), da = smem_u32(DOs), pt = smem_u32(Pt), st = smem_u32(St);
+      constexpr uint32_t id_s = make_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t id_nn = make_idesc_bf16(128, HD, 1, 1);
+      constexpr uint32_t id_kn = make_idesc_bf16(128, HD, 0, 1);
+      mbar_wait(ld_full, 0);
+      tc_fence_after();
+      uint32_t n = 0;
+      for (int u = 0; u < nu; ++u) {
+        mbar_wait(kv_empty, (u & 1) ^ 1);               // the previous key tile's dV / dK have been drained
+        tc_fence_after();
+        for (int t = 0; t < nt; ++t, ++n) {
+          mbar_wait(sd_empty, (n & 1) ^ 1);
+          tc_fence_after();
+#pragma unroll
+          for (int kk = 0; kk < 2; ++kk) {
+            umma_bf16(tmem + TB_S, desc_kmajor_sw128(qa + t * SLAB + hb + kk * 32), desc_kmajor_sw128(ka + u * SLAB + hb + kk * 32), id_s, kk);
+            umma_bf16(tmem + TB_DP, desc_kmajor_sw128(da + t * SLAB + hb + kk * 32), desc_kmajor_sw128(va + u * SLAB + hb + kk * 32), id_s, kk);
+          }
+          umma_commit(sd_full);
+          mbar_wait(tile_full, n & 1);
+          tc_fence_after();
+#pragma unroll
+          for (int kk = 0; kk < 8; ++kk) {
+            // dV_u += Pd^T dO_t ; dK_u += dS^T Q_t : A = the tile as MN-major (M = keys: two 64-key blocks SLAB apart), K = query rows
+            umma_bf16(tmem + TB_DV, make_smem_desc(pt + kk * 2048, SLAB, 1024, LAYOUT_SW128),
+                      make_smem_desc(da + t * SLAB + kk * 2048 + hb, SLAB, 1024, LAYOUT_SW128), id_nn, (t | kk) != 0);
+            umma_bf16(tmem + TB_DK, make_smem_desc(st + kk * 2048, SLAB, 1024, LAYOUT_SW128),
+                      make_smem_desc(qa + t * SLAB + kk * 2048 + hb, SLAB, 1024, LAYOUT_SW128), id_nn, (t | kk) != 0);
+            // dQ_t += dS K_u : A = dS K-major (keys: two slabs x four steps), B = K_u MN-major (N = 32, K = key rows)
+            umma_bf16(tmem + TB_DQ + t * HD, desc_kmajor_sw128(st + (kk >> 2) * SLAB + (kk & 3) * 32),
+                      make_smem_desc(ka + u * SLAB + kk * 2048 + hb, SLAB, 1024, LAYOUT_SW128), id_kn, (u | kk) != 0);
+          }
+          umma_commit(tile_empty);
+        }
+        umma_commit(kv_full);
+      }
+      umma_commit(q_full);
+    }
+  } else if (warp >= 4) {
+    const int e = warp - 4, qd = e & 3, g = e >> 2;
+    const int row = qd * 32 + lane;
+    const uint32_t lane_base = (uint32_t)(qd * 32) << 16;
+    const float c = p.qk_scale;
+    const unsigned long long dseed = p.drop_thr ? ocv_salted(p.drop_seed, p.drop_salt) : 0ull;
+    uint32_t n = 0;
+    for (int u = 0; u < nu; ++u) {
+      for (int t = 0; t < nt; ++t, ++n) {
+        const int r = t * 128 + row;
+        const bool rok = r < Sq;
+        const float m_r = rm[min(r, BW_MAXS - 1)], inv_r = ri[min(r, BW_MAXS - 1)], d_r = dl[min(r, BW_MAXS - 1)];
+        const unsigned long long drow = (((unsigned long long)b * p.heads + head) * Sq + (unsigned long long)min(r, Sq - 1)) *
+                                        (unsigned long long)Sk;
+        mbar_wait(sd_full, n & 1);
+        tc_fence_after();
+        uint32_t s0[32], s1[32], g0[32], g1[32];
+        tmem_ld32(tmem + lane_base + TB_S + g * 64, s0);
+        tmem_ld32(tmem + lane_base + TB_S + g * 64 + 32, s1);
+        tmem_ld32(tmem + lane_base + TB_DP + g * 64, g0);
+        tmem_ld32(tmem + lane_base + TB_DP + g * 64 + 32, g1);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(sd_empty);
+        mbar_wait(tile_empty, (n & 1) ^ 1);            // the previous step's gradient MMAs have read the tiles
+        uint8_t* prow = Pt + g * SLAB + row * 128;
+        uint8_t* srow = St + g * SLAB + row * 128;
+#pragma unroll
+        for (int ch = 0; ch < 8; ++ch) {
+          uint32_t pp[4], ss[4];
+#pragma unroll
+          for (int j2 = 0; j2 < 4; ++j2) {
+            float pd[2], ds[2];
+#pragma unroll
+            for (int h2 = 0; h2 < 2; ++h2) {
+              const int j = ch * 8 + j2 * 2 + h2;                       // key within this thread's 64
+              const int k = u * 128 + g * 64 + j;
+              const float sv = __uint_as_float(j < 32 ? s0[j] : s1[j - 32]);
+              const float gv = __uint_as_float(j < 32 ? g0[j] : g1[j - 32]);
+              const bool kv = (valid[k >> 5] >> (k & 31)) & 1u;
+              float pr = (rok && kv) ? ex2(fmaf(sv, c, -m_r)) * inv_r : 0.f;
+              float keep = 1.f;
+              if (p.drop_thr) keep = ocv_drop_keep(dseed, drow + k, p.drop_thr) ? p.drop_scale : 0.f;
+              pd[h2] = pr * keep;
+              ds[h2] = pr * (gv * keep - d_r);
+            }
+            pp[j2] = pack_bf16(pd[0], pd[1]);
+            ss[j2] = pack_bf16(ds[0], ds[1]);
+          }
+          *reinterpret_cast<uint4*>(prow + ((ch ^ (row & 7)) << 4)) = make_uint4(pp[0], pp[1], pp[2], pp[3]);
+          *reinterpret_cast<uint4*>(srow + ((ch ^ (row & 7)) << 4)) = make_uint4(ss[0], ss[1], ss[2], ss[3]);
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(tile_full);
+      }
+      // dV_u (warpgroup 0) and dK_u (warpgroup 1): lane = key row
+      mbar_wait(kv_full, u & 1);
+      tc_fence_after();
+      {
+        uint32_t r32[32];
+        tmem_ld32(tmem + lane_base + (g == 0 ? TB_DV : TB_DK), r32);
+        tmem_ld_wait();
+        tc_fence_before();
+        mbar_arrive(kv_empty);
+        const int key = u * 128 + row;
+        if (key < Sk) {
+          const float f = g == 0 ? 1.f : p.scale;
+          const long long o = (long long)b * p.g_bs + (long long)key * p.g_rs + head * HD;
+          float4* d32 = reinterpret_cast<float4*>((g == 0 ? p.dv32 : p.dk32) + o);
+          uint4* d16 = reinterpret_cast<uint4*>((g == 0 ? p.dv16 : p.dk16) + o);
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            d32[j] = make_float4(f * __uint_as_float(r32[4 * j]), f * __uint_as_float(r32[4 * j + 1]), f * __uint_as_float(r32[4 * j + 2]),
+                                 f * __uint_as_float(r32[4 * j + 3]));
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            d16[j] = make_uint4(pack_bf16(f * __uint_as_float(r32[8 * j]), f * __uint_as_float(r32[8 * j + 1])),
+                                pack_bf16(f * __uint_as_float(r32[8 * j + 2]), f * __uint_as_float(r32[8 * j + 3])),
+                                pack_bf16(f * __uint_as_float(r32[8 * j + 4]), f * __uint_as_float(r32[8 * j + 5])),
+                                pack_bf16(f * __uint_as_float(r32[8 * j + 6]), f * __uint_as_float(r32[8 * j + 7])));
+        }
+      }
+    }
+    // dQ: warpgroup g drains query tile g
+    mbar_wait(q_full, 0);
+    tc_fence_after();
+    if (g < nt) {
+      uint32_t r32[32];
+      tmem_ld32(tmem + lane_base + TB_DQ + g * HD, r32);
+      tmem_ld_wait();
+      const int r = g * 128 + row;
+      if (r < Sq) {
+        const float f = p.scale;
+        const long long o = (long long)b * p.g_bs + (long long)r * p.g_rs + head * HD;
+        float4* d32 = reinterpret_cast<float4*>(p.dq32 + o);
+        uint4* d16 = reinterpret_cast<uint4*>(p.dq16 + o);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          d32[j] = make_float4(f * __uint_as_float(r32[4 * j]), f * __uint_as_float(r32[4 * j + 1]), f * __uint_as_float(r32[4 * j + 2]),
+                               f * __uint_as_float(r32[4 * j + 3]));
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          d16[j] = make_uint4(pack_bf16(f * __uint_as_float(r32[8 * j]), f * __uint_as_float(r32[8 * j + 1])),
+                              pack_bf16(f * __uint_as_float(r32[8 * j + 2]), f * __uint_as_float(r32[8 * j + 3])),
+                              pack_bf16(f * __uint_as_float(r32[8 * j + 4]), f * __uint_as_float(r32[8 * j + 5])),
+                              pack_bf16(f * __uint_as_float(r32[8 * j + 6]), f * __uint_as_float(r32[8 * j + 7])));
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem, TB_COLS);
+}
+
+}  // namespace
+
+bool ocv_mha_bwd_tc_supported(int Sq, int Sk, int heads, int d) {
+  static int enabled = -1;
+  if (enabled < 0) {
+    const char* e = getenv("OCV_ATTN_BWD_TC");
+    enabled = (e && e[0] == '0') ? 0 : 1;
+  }
+  return enabled && heads == 4 && d == HD && Sq >= 1 && Sq <= BW_MAXS && Sk >= 1 && Sk <= BW_MAXS;
+}
+
+extern "C" int ocv_mha_core_bwd_tc_bf16(const void* q16, const void* k16, const void* v16, const void* o16, const void* do16,
+                                        const float* stats, const uint8_t* key_padding_mask, float* dq32, float* dk32, float* dv32,
+                                        void* dq16, void* dk16, void* dv16, int B, int Sq, int Sk, int heads, int d,
+                                        long long q_bstride, int q_rstride, long long kv_bstride, int kv_rstride, long long o_bstride,
+                                        int o_rstride, long long g_bstride, int g_rstride, float drop_p, unsigned long long drop_seed,
+                                        void* stream) {
+  OCV_CHECK_ARG(q16 && k16 && v16 && o16 && do16 && stats && dq32 && dk32 && dv32 && dq16 && dk16 && dv16 && B > 0 && drop_p >= 0.f &&
+                drop_p < 1.f);
+  OCV_CHECK_SHAPE(ocv_mha_bwd_tc_supported(Sq, Sk, heads, d) && B <= 65535);
+  OCV_CHECK_SHAPE(((q_bstride | kv_bstride | o_bstride | g_bstride | q_rstride | kv_rstride | o_rstride | g_rstride) & 7) == 0);
+  const uintptr_t al = reinterpret_cast<uintptr_t>(q16) | reinterpret_cast<uintptr_t>(k16) | reinterpret_cast<uintptr_t>(v16) |
+                       reinterpret_cast<uintptr_t>(o16) | reinterpret_cast<uintptr_t>(do16) | reinterpret_cast<uintptr_t>(dq32) |
+                       reinterpret_cast<uintptr_t>(dk32) | reinterpret_cast<uintptr_t>(dv32) | reinterpret_cast<uintptr_t>(dq16) |
+                       reinterpret_cast<uintptr_t>(dk16) | reinterpret_cast<uintptr_t>(dv16);
+  OCV_CHECK_ALIGN((al & 15) == 0 && (reinterpret_cast<uintptr_t>(stats) & 7) == 0);
+  if (int s = ocv_require_sm100()) return s;
+  CUtensorMap tmQ, tmK, tmV, tmDO;
+  if (int s = make_tmap_rows(&tmQ, q16, Sq, B, q_bstride, q_rstride)) return s;
+  if (int s = make_tmap_rows(&tmK, k16, Sk, B, kv_bstride, kv_rstride)) return s;
+  if (int s = make_tmap_rows(&tmV, v16, Sk, B, kv_bstride, kv_rstride)) return s;
+  if (int s = make_tmap_rows(&tmDO, do16, Sq, B, o_bstride, o_rstride)) return s;
+  static bool attr = false;
+  if (!attr) {
+    cudaError_t e = cudaFuncSetAttribute(mha_bwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BW_SMEM);
+    if (e != cudaSuccess) return (int)e;
+    attr = true;
+  }
+  AttnBwdParams p{};
+  p.o16 = static_cast<const __nv_bfloat16*>(o16); p.do16 = static_cast<const __nv_bfloat16*>(do16); p.stats = stats;
+  p.mask = key_padding_mask;
+  p.dq32 = dq32; p.dk32 = dk32; p.dv32 = dv32;
+  p.dq16 = static_cast<__nv_bfloat16*>(dq16); p.dk16 = static_cast<__nv_bfloat16*>(dk16); p.dv16 = static_cast<__nv_bfloat16*>(dv16);
+  p.Sq = Sq; p.Sk = Sk; p.heads = heads; p.o_bs = o_bstride; p.o_rs = o_rstride; p.g_bs = g_bstride; p.g_rs = g_rstride;
+  p.scale = 1.f / sqrtf((float)d);
+  p.qk_scale = 1.4426950408889634f * p.scale;
+  if (drop_p > 0.f) {
+    p.drop_thr = ocv_drop_threshold(drop_p);
+    p.drop_scale = 1.f / (1.f - drop_p);
+    p.drop_seed = drop_seed;
+    p.drop_salt = ocv_dropout_salt();
+  }
+  mha_bwd_tc_kernel<<<dim3(heads, B), THREADS, BW_SMEM, ocv_stream(stream)>>>(tmQ, tmK, tmV, tmDO, p);
+  return ocv_launch_status();
 }

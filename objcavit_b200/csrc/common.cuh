@@ -26,6 +26,8 @@ int ocv_pad_objects_impl(const float* src, const int32_t* offsets, const int32_t
 bool ocv_mha_tc_supported(int Sq, int Sk, int heads, int d, long long q_bs, int q_rs, long long k_bs, int k_rs, long long v_bs, int v_rs,
                           long long o_bs, int o_rs);
 
+bool ocv_mha_bwd_tc_supported(int Sq, int Sk, int heads, int d);
+
 static inline cudaStream_t ocv_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -242,7 +242,7 @@ extern "C" long long ocv_encoder_layer_bwd_train_bf16_workspace(int B, int S, in
   bytes += 4 * al((size_t)M * LE * 4);            // dy2, df, dsa, datt
   bytes += 2 * al((size_t)M * F * 4);             // dh, dh2
   bytes += al((size_t)M * 3 * LE * 4);            // dqkv
-  bytes += 2 * al((size_t)M * LE * 2) + al((size_t)M * F * 2) + al((size_t)M * 3 * LE * 2);   // bf16 copies: df, dsa, dh2, dqkv
+  bytes += 3 * al((size_t)M * LE * 2) + al((size_t)M * F * 2) + al((size_t)M * 3 * LE * 2);   // bf16 copies: df, dsa, datt, dh2, dqkv
   bytes += al((size_t)B * LH * S * 3 * 4);        // attention statistics
   bytes += 2 * al((size_t)(M * 2 + 32 * LE) * 4); // LayerNorm row statistics + parameter partials
   bytes += 2 * al((size_t)8 * F * 3 * LE * 4);    // split-K partials of the weight-gradient GEMMs (side stream), generous
@@ -251,9 +251,9 @@ extern "C" long long ocv_encoder_layer_bwd_train_bf16_workspace(int B, int S, in
 
 extern "C" int ocv_encoder_layer_fwd_train_bf16(const float* const* W, const void* const* W16, const float* x, const void* x16,
                                                 const uint8_t* mask, int B, int S, int F, float drop_p,
-                                                const unsigned long long* seeds, float* qkv, float* att, void* att16, float* y,
-                                                float* x1, void* x1_16, float* h, void* h16, float* y2, float* out, void* out16,
-                                                void* stream) {
+                                                const unsigned long long* seeds, float* qkv, void* qkv16, float* att_stats, float* att,
+                                                void* att16, float* y, float* x1, void* x1_16, float* h, void* h16, float* y2,
+                                                float* out, void* out16, void* stream) {
   OCV_CHECK_ARG(W && W16 && x && x16 && qkv && att && att16 && y && x1 && x1_16 && h && h16 && y2 && out && out16 && B > 0 && S > 0 && F > 0);
   OCV_CHECK_ARG(drop_p >= 0.f && drop_p < 1.f && (drop_p == 0.f || seeds));
   for (int i = 0; i < N_LAYER_TENSORS; ++i) OCV_CHECK_ARG(W[i] != nullptr);
@@ -261,13 +261,23 @@ extern "C" int ocv_encoder_layer_fwd_train_bf16(const float* const* W, const voi
   const int M = B * S;
   const bool drop = drop_p > 0.f;
   const float p = drop ? drop_p : 0.f;
-  // qkv = x W_in^T + b  (fp32 out: the attention core and its backward read it)
-  TRY(gemm16(x16, W16[W16_IN], 0, 0, W[B_IN], nullptr, nullptr, nullptr, nullptr, qkv, nullptr, M, 3 * LE, LE, LE, LE, OCV_ACT_NONE,
-             0.f, 0ull, 1, nullptr, stream));
-  TRY(ocv_mha_core_dropout_f32(qkv, qkv + LE, qkv + 2 * LE, att, mask, B, S, S, LH, LD, (long long)S * 3 * LE, 3 * LE,
-                               (long long)S * 3 * LE, 3 * LE, (long long)S * 3 * LE, 3 * LE, (long long)S * LE, LE, p,
-                               drop ? seeds[0] : 0ull, stream));
-  TRY(ocv_cast_f32_to_bf16(att, att16, (long long)M * LE, stream));
+  // qkv = x W_in^T + b  (fp32: the attention backward reads it; bf16: the tensor-core attention core below)
+  const bool tc_att = ocv_mha_tc_supported(S, S, LH, LD, (long long)S * 3 * LE, 3 * LE, (long long)S * 3 * LE, 3 * LE, (long long)S * 3 * LE,
+                                           3 * LE, (long long)S * LE, LE) && qkv16 != nullptr;
+  TRY(gemm16(x16, W16[W16_IN], 0, 0, W[B_IN], nullptr, nullptr, nullptr, nullptr, qkv, tc_att ? qkv16 : nullptr, M, 3 * LE, LE, LE, LE,
+             OCV_ACT_NONE, 0.f, 0ull, 1, nullptr, stream));
+  if (tc_att) {
+    // attention core on tcgen05: same dropout masks as the fp32 kernel (its backward regenerates them), fp32 + bf16 output
+    const __nv_bfloat16* q16 = static_cast<const __nv_bfloat16*>(qkv16);
+    TRY(ocv_mha_core_tc_bf16(q16, q16 + LE, q16 + 2 * LE, att16, att, att_stats, mask, B, S, S, LH, LD, (long long)S * 3 * LE, 3 * LE,
+                             (long long)S * 3 * LE, 3 * LE, (long long)S * 3 * LE, 3 * LE, (long long)S * LE, LE, p,
+                             drop ? seeds[0] : 0ull, stream));
+  } else {
+    TRY(ocv_mha_core_dropout_f32(qkv, qkv + LE, qkv + 2 * LE, att, mask, B, S, S, LH, LD, (long long)S * 3 * LE, 3 * LE,
+                                 (long long)S * 3 * LE, 3 * LE, (long long)S * 3 * LE, 3 * LE, (long long)S * LE, LE, p,
+                                 drop ? seeds[0] : 0ull, stream));
+    TRY(ocv_cast_f32_to_bf16(att, att16, (long long)M * LE, stream));
+  }
   // y = x + dropout1(att W_out^T + b); x1 = LN1(y)      — one GEMM, three outputs (y, x1, bf16 x1)
   TRY(gemm16(att16, W16[W16_OUT], 0, 0, W[B_OUT], x, W[G_1], W[BE_1], y, x1, x1_16, M, LE, LE, LE, LE, OCV_ACT_NONE, p,
              drop ? seeds[1] : 0ull, 1, nullptr, stream));
@@ -280,7 +290,8 @@ extern "C" int ocv_encoder_layer_fwd_train_bf16(const float* const* W, const voi
 }
 
 extern "C" int ocv_encoder_layer_bwd_train_bf16(const float* const* W, const void* const* W16, float* const* G, const void* x16,
-                                                const float* qkv, const float* att, const void* att16, const float* y,
+                                                const float* qkv, const void* qkv16, const float* att_stats, const float* att,
+                                                const void* att16, const float* y,
                                                 const void* x1_16, const float* h, const void* h16, const float* y2,
                                                 const uint8_t* mask, const float* dout, float* dx, int B, int S, int F, float drop_p,
                                                 const unsigned long long* seeds, void* workspace, void* stream, void* side_stream) {
@@ -306,6 +317,7 @@ extern "C" int ocv_encoder_layer_bwd_train_bf16(const float* const* W, const voi
   void* dsa16 = take(ME * 2);
   void* dh2_16 = take(MF * 2);
   void* dqkv16 = take(ME * 3 * 2);
+  void* datt16 = take(ME * 2);
   void* stats = take((size_t)B * LH * S * 3 * 4);
   void* lnws2 = take((size_t)((long long)M * 2 + 32 * LE) * 4);
   void* lnws1 = take((size_t)((long long)M * 2 + 32 * LE) * 4);
@@ -346,13 +358,27 @@ extern "C" int ocv_encoder_layer_bwd_train_bf16(const float* const* W, const voi
   TRY(order_after(sd, st));
   TRY(ocv_layernorm_bwd_params_f32(dy2, y, G[G_1], G[BE_1], M, LE, 1.f, lnws1, sd));
   TRY(wgrad16(dsa16, dsa, att16, G[W_OUT], G[B_OUT], M, LE, LE, ws_side, sd));                         // dWout += dsa^T att
-  TRY(gemm16(dsa16, W16[W16_OUT], 0, 1, nullptr, nullptr, nullptr, nullptr, nullptr, datt, nullptr, M, LE, LE, LE, LE, OCV_ACT_NONE,
-             0.f, 0ull, 1, nullptr, st));                                                              // datt = dsa W_out
+  // attention core backward on tcgen05 when the forward ran there (its statistics and bf16 qkv were kept) and the shape fits
+  const bool tc_att = qkv16 && att_stats && ocv_mha_bwd_tc_supported(S, S, LH, LD) &&
+                      ocv_mha_tc_supported(S, S, LH, LD, (long long)S * 3 * LE, 3 * LE, (long long)S * 3 * LE, 3 * LE, (long long)S * 3 * LE,
+                                           3 * LE, (long long)S * LE, LE);   // i.e. the forward ran on the tensor-core kernel too
   const long long qs = (long long)S * 3 * LE;
-  TRY(ocv_mha_core_bwd_dropout_f32(qkv, qkv + LE, qkv + 2 * LE, att, datt, mask, dqkv, dqkv + LE, dqkv + 2 * LE, B, S, S, LH, LD, qs,
-                                   3 * LE, qs, 3 * LE, qs, 3 * LE, (long long)S * LE, LE, qs, 3 * LE, qs, 3 * LE, qs, 3 * LE,
-                                   drop ? drop_p : 0.f, drop ? seeds[0] : 0ull, stats, st));
-  TRY(ocv_cast_f32_to_bf16(dqkv, dqkv16, ME * 3, st));
+  if (tc_att) {
+    TRY(gemm16(dsa16, W16[W16_OUT], 0, 1, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, datt16, M, LE, LE,
+               LE, LE, OCV_ACT_NONE, 0.f, 0ull, 1, nullptr, st));                                       // datt = dsa W_out
+    const __nv_bfloat16* q16 = static_cast<const __nv_bfloat16*>(qkv16);
+    __nv_bfloat16* g16 = static_cast<__nv_bfloat16*>(dqkv16);
+    TRY(ocv_mha_core_bwd_tc_bf16(q16, q16 + LE, q16 + 2 * LE, att16, datt16, att_stats, mask, dqkv, dqkv + LE, dqkv + 2 * LE, g16, g16 + LE,
+                                 g16 + 2 * LE, B, S, S, LH, LD, qs, 3 * LE, qs, 3 * LE, (long long)S * LE, LE, qs, 3 * LE,
+                                 drop ? drop_p : 0.f, drop ? seeds[0] : 0ull, st));
+  } else {
+    TRY(gemm16(dsa16, W16[W16_OUT], 0, 1, nullptr, nullptr, nullptr, nullptr, nullptr, datt, nullptr, M, LE, LE, LE, LE, OCV_ACT_NONE,
+               0.f, 0ull, 1, nullptr, st));                                                              // datt = dsa W_out
+    TRY(ocv_mha_core_bwd_dropout_f32(qkv, qkv + LE, qkv + 2 * LE, att, datt, mask, dqkv, dqkv + LE, dqkv + 2 * LE, B, S, S, LH, LD, qs,
+                                     3 * LE, qs, 3 * LE, qs, 3 * LE, (long long)S * LE, LE, qs, 3 * LE, qs, 3 * LE, qs, 3 * LE,
+                                     drop ? drop_p : 0.f, drop ? seeds[0] : 0ull, stats, st));
+    TRY(ocv_cast_f32_to_bf16(dqkv, dqkv16, ME * 3, st));
+  }
   TRY(order_after(sd, st));
   TRY(wgrad16(dqkv16, dqkv, x16, G[W_IN], G[B_IN], M, 3 * LE, LE, ws_side, sd));                       // dWin [384,128] += dqkv^T x
   if (!drop) TRY(order_after(st, sd));                                             // dsa aliases dy, updated in place next

@@ -416,6 +416,26 @@ def mha_core_tc_bf16(q, k, v, key_padding_mask=None, heads: int = 4, want32: boo
     return out, out32, stats
 
 
+def mha_core_bwd_tc_bf16(q, k, v, out16, dout16, stats, key_padding_mask=None, heads: int = 4, drop=None):
+    """Backward of the tcgen05 attention core (``ocv_mha_core_bwd_tc_bf16``): q / k / v / out16 / dout16 bf16 [B,S,E] views,
+    ``stats`` from the forward.  -> (dq, dk, dv) fp32 [B,S,E] each and their bf16 copies (dq16, dk16, dv16)."""
+    for t, n in ((q, "q"), (k, "k"), (v, "v"), (out16, "out16"), (dout16, "dout16")):
+        _chk(t, torch.bfloat16, n)
+        assert t.dim() == 3 and t.stride(2) == 1
+    _chk(stats, torch.float32, "stats")
+    B, Sq, E = q.shape
+    Sk = k.shape[1]
+    assert k.stride() == v.stride() and out16.stride() == dout16.stride()
+    g32 = torch.empty(3, B, max(Sq, Sk), E, device=q.device, dtype=torch.float32)
+    g16 = torch.empty(3, B, max(Sq, Sk), E, device=q.device, dtype=torch.bfloat16)
+    p_drop, seed = drop if drop is not None else (0.0, 0)
+    _call("ocv_mha_core_bwd_tc_bf16", q.data_ptr(), k.data_ptr(), v.data_ptr(), out16.data_ptr(), dout16.data_ptr(), stats.data_ptr(),
+          _ptr(key_padding_mask), g32[0].data_ptr(), g32[1].data_ptr(), g32[2].data_ptr(), g16[0].data_ptr(), g16[1].data_ptr(),
+          g16[2].data_ptr(), B, Sq, Sk, heads, E // heads, q.stride(0), q.stride(1), k.stride(0), k.stride(1), out16.stride(0),
+          out16.stride(1), g32.stride(1), g32.stride(2), float(p_drop), int(seed), _stream())
+    return (g32[0, :, :Sq], g32[1, :, :Sk], g32[2, :, :Sk]), (g16[0, :, :Sq], g16[1, :, :Sk], g16[2, :, :Sk])
+
+
 def pack_patch_weights_bf16(w: torch.Tensor) -> torch.Tensor:
     _chk(w, torch.float32, "w")
     assert w.is_contiguous() and w.dim() == 4 and w.shape[2] == w.shape[3]
@@ -1209,17 +1229,20 @@ def encoder_layer_fwd_train_bf16(W, W16, x: torch.Tensor, x16: torch.Tensor, mas
     b16 = lambda *s: torch.empty(*s, device=dev, dtype=torch.bfloat16)
     qkv, att, y, x1, y2, out, h = f32(B, S, 3 * E), f32(M, E), f32(M, E), f32(M, E), f32(M, E), f32(M, E), f32(M, F_)
     att16, x1_16, out16, h16 = b16(M, E), b16(M, E), b16(M, E), b16(M, F_)
+    qkv16 = b16(M, 3 * E)            # operand of the tensor-core attention core, forward and backward
+    stats = f32(B, 4, S, 2)          # its softmax statistics (row max, row sum): the backward recomputes P from them
     sd = (C.c_ulonglong * 4)(*[int(v) for v in seeds]) if drop_p > 0 else None
     _call("ocv_encoder_layer_fwd_train_bf16", _ptr_array(W), _ptr_array(W16), x.data_ptr(), x16.data_ptr(), _ptr(mask), B, S, F_,
-          float(drop_p), sd, qkv.data_ptr(), att.data_ptr(), att16.data_ptr(), y.data_ptr(), x1.data_ptr(), x1_16.data_ptr(),
-          h.data_ptr(), h16.data_ptr(), y2.data_ptr(), out.data_ptr(), out16.data_ptr(), _stream(), launches=7)
-    return out.view(B, S, E), out16.view(B, S, E), (x16, qkv, att.view(B, S, E), att16, y, x1_16, h, h16, y2)
+          float(drop_p), sd, qkv.data_ptr(), qkv16.data_ptr(), stats.data_ptr(), att.data_ptr(), att16.data_ptr(), y.data_ptr(),
+          x1.data_ptr(), x1_16.data_ptr(), h.data_ptr(), h16.data_ptr(), y2.data_ptr(), out.data_ptr(), out16.data_ptr(), _stream(),
+          launches=6)
+    return out.view(B, S, E), out16.view(B, S, E), (x16, qkv, att.view(B, S, E), att16, y, x1_16, h, h16, y2, qkv16, stats)
 
 
 def encoder_layer_bwd_train_bf16(W, W16, G, saved, mask, dout: torch.Tensor, drop_p: float, seeds, side_stream=None):
     """Explicit backward of the layer on the tensor cores: -> dx [B,S,128]; parameter gradients ACCUMULATED into ``G``."""
     import ctypes as C
-    x16, qkv, att, att16, y, x1_16, h, h16, y2 = saved
+    x16, qkv, att, att16, y, x1_16, h, h16, y2, qkv16, stats = saved
     _chk(dout, torch.float32, "dout")
     B, S, E3 = qkv.shape
     E = E3 // 3
@@ -1231,9 +1254,9 @@ def encoder_layer_bwd_train_bf16(W, W16, G, saved, mask, dout: torch.Tensor, dro
     ws = torch.empty(_lib.lib().ocv_encoder_layer_bwd_train_bf16_workspace(B, S, F_), device=dev, dtype=torch.uint8)
     sd = (C.c_ulonglong * 4)(*[int(v) for v in seeds]) if drop_p > 0 else None
     _call("ocv_encoder_layer_bwd_train_bf16", _ptr_array(W), _ptr_array(W16), _ptr_array(G), x16.data_ptr(), qkv.data_ptr(),
-          att.data_ptr(), att16.data_ptr(), y.data_ptr(), x1_16.data_ptr(), h.data_ptr(), h16.data_ptr(), y2.data_ptr(), _ptr(mask),
+          qkv16.data_ptr(), stats.data_ptr(), att.data_ptr(), att16.data_ptr(), y.data_ptr(), x1_16.data_ptr(), h.data_ptr(), h16.data_ptr(), y2.data_ptr(), _ptr(mask),
           d.data_ptr(), dx.data_ptr(), B, S, F_, float(drop_p), sd, ws.data_ptr(), _stream(),
-          None if side_stream is None else side_stream.cuda_stream, launches=33)
+          None if side_stream is None else side_stream.cuda_stream, launches=30)
     if side_stream is not None:
         for t in (ws, x16, att16, x1_16, h16):
             t.record_stream(side_stream)

@@ -85,3 +85,52 @@ def test_probability_dropout_uses_the_fp32_kernels_masks(cuda):
     _, got, _ = ops.mha_core_tc_bf16(qb[:, :, 0:E], qb[:, :, E:2 * E], qb[:, :, 2 * E:], None, want32=True, drop=(p, seed))
     torch.cuda.synchronize()
     assert float((got - want).abs().max()) < 3e-2 * float(want.abs().max())
+
+
+@pytest.mark.parametrize("B,Sq,Sk,masked,p", [
+    (8, 221, 221, False, 0.0),       # config 5 image encoder
+    (8, 32, 32, True, 0.0),          # object encoder with key padding
+    (3, 242, 242, False, 0.0),       # KITTI-train tokens
+    (2, 130, 200, True, 0.0),        # Sq != Sk, ragged tiles
+    (4, 221, 221, False, 0.2),       # probability dropout: masks regenerated from (seed, element)
+])
+def test_attention_backward_on_tcgen05(cuda, B, Sq, Sk, masked, p):
+    """dq / dk / dv of the tcgen05 backward against fp64 autograd through softmax attention on the same bf16 q / k / v and the
+    same dropout masks (those of the forward kernel, recovered from its output).  Tolerance 2e-2 of the largest |gradient|: P and
+    dS are rounded to bf16 before the three gradient GEMMs."""
+    g = torch.Generator().manual_seed(Sq * 7 + Sk)
+    E, H, d = 128, 4, 32
+    q = torch.randn(B, Sq, E, generator=g).to(cuda).bfloat16()
+    k = torch.randn(B, Sk, E, generator=g).to(cuda).bfloat16()
+    v = torch.randn(B, Sk, E, generator=g).to(cuda).bfloat16()
+    dout = torch.randn(B, Sq, E, generator=g).to(cuda).bfloat16()
+    mask = None
+    if masked:
+        mask = torch.zeros(B, Sk, dtype=torch.uint8, device=cuda)
+        for b in range(B):
+            mask[b, max(1, (b * 5 + 9) % Sk):] = 1
+    seed = 424242
+    drop = (p, seed) if p > 0 else None
+    out16, out32, stats = ops.mha_core_tc_bf16(q, k, v, mask, want32=True, want_stats=True, drop=drop)
+    (dq, dk, dv), (dq16, dk16, dv16) = ops.mha_core_bwd_tc_bf16(q, k, v, out16, dout, stats, mask, drop=drop)
+    torch.cuda.synchronize()
+    # reference: fp64 autograd; the dropout keep mask of element (b,h,q,k) is regenerated with the elementwise kernel's convention
+    q64, k64, v64 = (t.double().requires_grad_(True) for t in (q, k, v))
+    qh = q64.view(B, Sq, H, d).transpose(1, 2)
+    kh = k64.view(B, Sk, H, d).transpose(1, 2)
+    vh = v64.view(B, Sk, H, d).transpose(1, 2)
+    s = qh @ kh.transpose(-1, -2) / math.sqrt(d)
+    if mask is not None:
+        s = s.masked_fill(mask.bool()[:, None, None, :], float("-inf"))
+    P = torch.softmax(s, dim=-1)
+    if p > 0:
+        ones = torch.ones(B * H * Sq * Sk, device=cuda)
+        keep = ops.dropout(ones, p, seed).view(B, H, Sq, Sk).double()         # 0 or 1 / (1 - p)
+        P = P * keep
+    o = (P @ vh).transpose(1, 2).reshape(B, Sq, E)
+    (o * dout.double()).sum().backward()
+    for name, got, got16, want in (("dq", dq, dq16, q64.grad), ("dk", dk, dk16, k64.grad), ("dv", dv, dv16, v64.grad)):
+        scale = float(want.abs().max())
+        err = float((got.double() - want).abs().max()) / scale
+        err16 = float((got16.double() - want).abs().max()) / scale
+        assert err < 2e-2 and err16 < 2.5e-2, (name, err, err16)
