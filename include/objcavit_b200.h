@@ -197,6 +197,12 @@ int ocv_patch_embed_bf16(const void* X_nhwc_bf16, const void* Wp, const float* b
 int ocv_mlp_f32(const float* x, long long x_ld, int R, int n_layers, const float* const* weights_host,
                 const float* const* biases_host, const int* dims_host, const float* residual, float* out32,
                 void* out16, void* stream);
+/* One Linear (+ LeakyReLU(0.01) when `leaky`) layer over FEW rows (R x K, K <= 512, K % 4 == 0): output neurons spread over the
+ * grid, every weight read once chip-wide (~5 us against 10-45 us for a tiled GEMM at 8-500 rows).  The training step runs the
+ * regressor and positional MLPs through it layer by layer, keeping each layer's output for the backward.
+ * replaces: nn.Linear (+ nn.LeakyReLU) of self.regressor / self.positional_encoder (modules/ObjCAViT.py:257-282, 299-303). */
+int ocv_linear_rows_f32(const float* x, long long x_ld, int R, const float* W, const float* bias, int K, int N, int leaky, float* out,
+                        int out_ld, void* stream);
 /* Same chain for FEW rows (R ~ batch size: the regressor): one launch per layer, output neurons spread over the grid so each
  * weight is read once.  Every dims[l] % 4 == 0 and <= 512 for l < n_layers; x 16-byte aligned, x_ld % 4 == 0.
  * workspace: ocv_mlp_rows_f32_workspace() bytes (ping-pong activations). */

@@ -49,6 +49,7 @@ PROTOTYPES = {
     "ocv_patch_embed_bf16": (i32, [p, p, p, p, p, p, i32, i32, i32, i32, i32, i32, p, p]),
     "ocv_mlp_f32": (i32, [p, i64, i32, i32, p, p, p, p, p, p, p]),
     "ocv_cast_f32_to_bf16": (i32, [p, p, i64, p]),
+    "ocv_linear_rows_f32": (i32, [p, i64, i32, p, p, i32, i32, i32, p, i32, p]),
     "ocv_mlp_rows_f32_workspace": (i64, [i32, i32, p]),
     "ocv_mlp_rows_f32": (i32, [p, i64, i32, i32, p, p, p, p, p, p]),
     "ocv_gemm_bf16_v2": (i32, [p, p, i32, i32, p, p, i32, p, p, p, i32, p, i32, p, i32, i32, i32, i32, i32, i32, i32, f32, C.c_ulonglong,

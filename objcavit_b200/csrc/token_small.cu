@@ -224,6 +224,17 @@ extern "C" int ocv_cast_f32_to_bf16(const float* src, void* dst, long long n, vo
                         stream, src, static_cast<__nv_bfloat16*>(dst), n);
 }
 
+// one Linear (+ LeakyReLU 0.01) layer for few rows: the training step keeps every layer's output for its backward
+extern "C" int ocv_linear_rows_f32(const float* x, long long x_ld, int R, const float* W, const float* bias, int K, int N, int leaky,
+                                   float* out, int out_ld, void* stream) {
+  OCV_CHECK_ARG(x && W && out && R > 0 && N > 0);
+  OCV_CHECK_SHAPE(K > 0 && K <= MLPL_MAXK && K % 4 == 0 && out_ld >= N);
+  OCV_CHECK_ALIGN(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(W)) & 15) == 0 && x_ld % 4 == 0);
+  if (int s = ocv_require_sm100()) return s;
+  return ocv_launch_pdl(mlp_layer_kernel, dim3(ceil_div(N, 8), ceil_div(R, MLPL_ROWS)), dim3(256), 0, stream, x, x_ld, W, bias, out,
+                        out_ld, R, K, N, leaky ? 1 : 0);
+}
+
 extern "C" long long ocv_mlp_rows_f32_workspace(int R, int n_layers, const int* dims) {
   if (R <= 0 || n_layers < 1 || !dims) return 0;
   int mx = 0;

@@ -220,17 +220,28 @@ int gemm16(const void* A, const void* B, int a_mn, int b_mn, const float* bias, 
   return ocv_gemm_bf16_v2(A, B, a_mn, b_mn, bias, res, N, g, be, pre, N, c32, N, c16, N, M, N, K, lda, ldb, act, drop_p, seed, split, ws, st);
 }
 
-inline int wsplit(int Mtok) {  // split-K of the weight-gradient GEMMs (K = token rows, 1-8 output tiles): off the critical path
-  int s = Mtok / 512;
+inline int wsplit(int Mtok) {  // split-K of the weight-gradient GEMMs (K = token rows): only for long token counts — at the
+  int s = Mtok / 4096;         // config-5 size (1768 rows = 28 k-steps) one CTA per output tile is faster than GEMM + reduction
   return s < 1 ? 1 : (s > 8 ? 8 : s);
 }
 
-// dW [N,K] += dY^T X (both operands MN-major), dB [N] += column sums of dY (fp32)
-int wgrad16(const void* dy16, const float* dy32, const void* x16, float* dw, float* db, int Mtok, int N, int K, void* ws, void* st) {
+// second weight-gradient queue (bias-gradient column sums, LayerNorm parameter reductions): these 2-12 us kernels would otherwise
+// queue behind the weight-gradient GEMMs on the one side stream and become the tail of the step.  One per device, never destroyed.
+cudaStream_t second_side_stream() {
+  static cudaStream_t s[16] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 16) return nullptr;
+  if (!s[dev] && cudaStreamCreateWithFlags(&s[dev], cudaStreamNonBlocking) != cudaSuccess) s[dev] = nullptr;
+  return s[dev];
+}
+
+// dW [N,K] += dY^T X (both operands MN-major) on `st`; dB [N] += column sums of dY (fp32) on `st2`
+int wgrad16(const void* dy16, const float* dy32, const void* x16, float* dw, float* db, int Mtok, int N, int K, void* ws, void* st,
+            void* st2) {
   const int sp = wsplit(Mtok);
   TRY(ocv_gemm_bf16_v2(dy16, x16, 1, 1, nullptr, dw, K, nullptr, nullptr, nullptr, 0, dw, K, nullptr, 0, N, K, Mtok, N, K, OCV_ACT_NONE,
                        0.f, 0ull, sp, ws, st));
-  return ocv_reduce_channels_f32(dy32, db, 1, Mtok, N, 1, 1.f, st);
+  return ocv_reduce_channels_f32(dy32, db, 1, Mtok, N, 1, 1.f, st2);
 }
 
 }  // namespace
@@ -304,6 +315,17 @@ extern "C" int ocv_encoder_layer_bwd_train_bf16(const float* const* W, const voi
   const long long ME = (long long)M * LE, MF = (long long)M * F;
   const bool drop = drop_p > 0.f;
   cudaStream_t st = ocv_stream(stream), sd = side_stream ? ocv_stream(side_stream) : st;
+  cudaStream_t sd2 = sd;
+  if (side_stream) {
+    if (cudaStream_t s2 = second_side_stream()) sd2 = s2;
+  }
+  // sd2 joins sd at every point sd is ordered after the main stream (and once more at the end): a caller that joins `side_stream`
+  // has joined both
+  auto fork_side = [&]() -> int {
+    TRY(order_after(sd, st));
+    if (sd2 != sd) TRY(order_after(sd2, st));
+    return OCV_OK;
+  };
   uint8_t* p = static_cast<uint8_t*>(workspace);
   auto take = [&](size_t bytes) { void* r = p; p += al(bytes); return r; };
   float* dy2 = static_cast<float*>(take(ME * 4));
@@ -332,18 +354,21 @@ extern "C" int ocv_encoder_layer_bwd_train_bf16(const float* const* W, const voi
     TRY(ocv_layernorm_bwd_f32(dout, y2, W[G_2], dy2, nullptr, nullptr, M, LE, 1.f, lnws2, st));
   }
   TRY(ocv_cast_f32_to_bf16(df, df16, ME, st));
-  TRY(order_after(sd, st));
-  TRY(ocv_layernorm_bwd_params_f32(dout, y2, G[G_2], G[BE_2], M, LE, 1.f, lnws2, sd));
-  TRY(wgrad16(df16, df, h16, G[W_2], G[B_2], M, LE, F, ws_side, sd));                                   // dW2 [128,F] += df^T h
+  TRY(fork_side());
+  TRY(ocv_layernorm_bwd_params_f32(dout, y2, G[G_2], G[BE_2], M, LE, 1.f, lnws2, sd2));
+  TRY(wgrad16(df16, df, h16, G[W_2], G[B_2], M, LE, F, ws_side, sd, sd2));                                   // dW2 [128,F] += df^T h
   // dh [M,F] = df [M,128] W_2 [128,F]   (B = W_2 as stored: contraction index = row -> MN-major)
   TRY(gemm16(df16, W16[W16_2], 0, 1, nullptr, nullptr, nullptr, nullptr, nullptr, dh, nullptr, M, F, LE, LE, F, OCV_ACT_NONE, 0.f, 0ull,
              1, nullptr, st));
   if (drop) TRY(ocv_dropout_act_bwd_f32(dh, h, dh2, MF, OCV_ACT_RELU, drop_p, seeds[2], st));   // h is post-dropout: h > 0 <=> kept & positive
   else TRY(ocv_act_bwd_f32(dh, h, dh2, MF, OCV_ACT_RELU, st));
   TRY(ocv_cast_f32_to_bf16(dh2, dh2_16, MF, st));
-  TRY(order_after(sd, st));
-  TRY(wgrad16(dh2_16, dh2, x1_16, G[W_1], G[B_1], M, F, LE, ws_side, sd));                             // dW1 [F,128] += dh2^T x1
-  if (!drop) TRY(order_after(st, sd));     // the side stream's bias-gradient sums read df = dy2, which is updated in place next
+  TRY(fork_side());
+  TRY(wgrad16(dh2_16, dh2, x1_16, G[W_1], G[B_1], M, F, LE, ws_side, sd, sd2));                        // dW1 [F,128] += dh2^T x1
+  if (!drop) {
+    TRY(order_after(st, sd));
+    TRY(order_after(st, sd2));
+  }     // the side stream's bias-gradient sums read df = dy2, which is updated in place next
   // dy2 += dh2 [M,F] W_1 [F,128]        (residual + FFN branch; in place: the tile is read before it is written)
   TRY(gemm16(dh2_16, W16[W16_1], 0, 1, nullptr, dy2, nullptr, nullptr, nullptr, dy2, nullptr, M, LE, F, F, LE, OCV_ACT_NONE, 0.f, 0ull,
              1, nullptr, st));
@@ -355,9 +380,9 @@ extern "C" int ocv_encoder_layer_bwd_train_bf16(const float* const* W, const voi
     TRY(ocv_layernorm_bwd_f32(dy2, y, W[G_1], dy, nullptr, nullptr, M, LE, 1.f, lnws1, st));
   }
   TRY(ocv_cast_f32_to_bf16(dsa, dsa16, ME, st));
-  TRY(order_after(sd, st));
-  TRY(ocv_layernorm_bwd_params_f32(dy2, y, G[G_1], G[BE_1], M, LE, 1.f, lnws1, sd));
-  TRY(wgrad16(dsa16, dsa, att16, G[W_OUT], G[B_OUT], M, LE, LE, ws_side, sd));                         // dWout += dsa^T att
+  TRY(fork_side());
+  TRY(ocv_layernorm_bwd_params_f32(dy2, y, G[G_1], G[BE_1], M, LE, 1.f, lnws1, sd2));
+  TRY(wgrad16(dsa16, dsa, att16, G[W_OUT], G[B_OUT], M, LE, LE, ws_side, sd, sd2));                         // dWout += dsa^T att
   // attention core backward on tcgen05 when the forward ran there (its statistics and bf16 qkv were kept) and the shape fits
   const bool tc_att = qkv16 && att_stats && ocv_mha_bwd_tc_supported(S, S, LH, LD) &&
                       ocv_mha_tc_supported(S, S, LH, LD, (long long)S * 3 * LE, 3 * LE, (long long)S * 3 * LE, 3 * LE, (long long)S * 3 * LE,
@@ -379,8 +404,9 @@ extern "C" int ocv_encoder_layer_bwd_train_bf16(const float* const* W, const voi
                                      drop ? drop_p : 0.f, drop ? seeds[0] : 0ull, stats, st));
     TRY(ocv_cast_f32_to_bf16(dqkv, dqkv16, ME * 3, st));
   }
-  TRY(order_after(sd, st));
-  TRY(wgrad16(dqkv16, dqkv, x16, G[W_IN], G[B_IN], M, 3 * LE, LE, ws_side, sd));                       // dWin [384,128] += dqkv^T x
+  TRY(fork_side());
+  TRY(wgrad16(dqkv16, dqkv, x16, G[W_IN], G[B_IN], M, 3 * LE, LE, ws_side, sd, sd2));                  // dWin [384,128] += dqkv^T x
+  if (sd2 != sd) TRY(order_after(sd, sd2));                                        // whoever joins `side_stream` has joined both queues
   if (!drop) TRY(order_after(st, sd));                                             // dsa aliases dy, updated in place next
   // dy += dqkv [M,384] W_in [384,128]   (residual + attention branch)
   return gemm16(dqkv16, W16[W16_IN], 0, 1, nullptr, dy, nullptr, nullptr, nullptr, dy, nullptr, M, LE, 3 * LE, 3 * LE, LE, OCV_ACT_NONE,

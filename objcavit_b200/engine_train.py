@@ -199,11 +199,18 @@ NO_DROP = DropCtx(0.0, 0)
 # MLP chains (positional encoder, regressor)
 # ----------------------------------------------------------------------------------------------------------------------
 
+FAST_ROWS = False       # set per forward (precision "bf16"): few-row Linear layers through ocv_linear_rows_f32 instead of tiled GEMMs
+
+
 def mlp_fwd(P: Params, pre: str, x: torch.Tensor, idxs):
     saved = []
     for j, i in enumerate(idxs):
         act = LEAKY if j < len(idxs) - 1 else NONE
-        y = ops.linear(x, P[f"{pre}{i}.weight"], P[f"{pre}{i}.bias"], act=act)
+        w = P[f"{pre}{i}.weight"]
+        if FAST_ROWS and ops.linear_rows_ok(x, w):        # 8-500 rows: ~5 us per layer against 10-45 us for the tiled fp32 GEMM
+            y = ops.linear_rows(x, w, P[f"{pre}{i}.bias"], leaky=act == LEAKY)
+        else:
+            y = ops.linear(x, w, P[f"{pre}{i}.bias"], act=act)
         saved.append((x, y))
         x = y
     return x, saved
@@ -381,6 +388,63 @@ def cross_bwd(P: Params, G: Params, pre: str, saved, dout: torch.Tensor, acc_q, 
 
 
 # ----------------------------------------------------------------------------------------------------------------------
+# nn.MultiheadAttention as cross attention on the tensor cores (precision "bf16"): projections and their gradients through
+# ocv_gemm_bf16_v2, the attention core and its backward through the tcgen05 kernels (csrc/attn_tc.cu).  Sq, Sk <= 256.
+# ----------------------------------------------------------------------------------------------------------------------
+
+def _cross_tc_ok(Sq: int, Sk: int) -> bool:
+    return TOKEN_BF16 and Sq <= 256 and Sk <= 256
+
+
+def cross_fwd16(P: Params, P16, pre: str, q_in, k_in, v_in, mask):
+    w16, b = P16[pre + "in_proj_weight"], P[pre + "in_proj_bias"]
+    B, Sq, _ = q_in.shape
+    Sk = k_in.shape[1]
+    q_in16 = ops.cast_bf16(q_in.contiguous()).view(B * Sq, E)
+    k_in16 = ops.cast_bf16(k_in.contiguous()).view(B * Sk, E)
+    v_in16 = q_in16 if v_in is q_in else (k_in16 if v_in is k_in else ops.cast_bf16(v_in.contiguous()).view(-1, E))
+    proj = lambda x16, lo: ops.gemm_bf16_v2(x16, w16[lo:lo + E], bias=b[lo:lo + E], want32=False, want16=True)[2]
+    q16 = proj(q_in16, 0).view(B, Sq, E)
+    k16 = proj(k_in16, E).view(B, Sk, E)
+    v16 = proj(v_in16, 2 * E).view(B, Sk, E)
+    att16, _, stats = ops.mha_core_tc_bf16(q16, k16, v16, mask, HEADS, want_stats=True)
+    out = ops.gemm_bf16_v2(att16.view(B * Sq, E), P16[pre + "out_proj.weight"], bias=P[pre + "out_proj.bias"])[1].view(B, Sq, E)
+    return out, ("bf16", q_in16, k_in16, v_in16, q16, k16, v16, att16, stats, mask)
+
+
+def cross_bwd16(P: Params, P16, G: Params, pre: str, saved, dout: torch.Tensor, acc_q, acc_k, acc_v):
+    _, q_in16, k_in16, v_in16, q16, k16, v16, att16, stats, mask = saved
+    B, Sq, _ = q16.shape
+    Sk = k16.shape[1]
+    w16 = P16[pre + "in_proj_weight"]
+    gw, gb = G[pre + "in_proj_weight"], G[pre + "in_proj_bias"]
+    d = dout.reshape(B * Sq, E).contiguous()
+    d16 = ops.cast_bf16(d)
+    a16 = att16.view(B * Sq, E)
+    go, gob = G[pre + "out_proj.weight"], G[pre + "out_proj.bias"]
+
+    def out_wgrad():
+        ops.gemm_bf16_v2(d16, a16, a_mn=True, b_mn=True, residual=go, out32=go)            # dWout += d^T att
+        ops.reduce_channels(d, gob, 1, B * Sq, E, 1, beta=1.0)
+
+    on_side(out_wgrad, d16, a16, d)
+    datt16 = ops.gemm_bf16_v2(d16, P16[pre + "out_proj.weight"], b_mn=True, want32=False, want16=True)[2].view(B, Sq, E)
+    (dq, dk, dv), (dq16, dk16, dv16) = ops.mha_core_bwd_tc_bf16(q16, k16, v16, att16, datt16, stats, mask, HEADS)
+    for dz, dz16, z16, lo, acc, rows in ((dq, dq16, q_in16, 0, acc_q, B * Sq), (dk, dk16, k_in16, E, acc_k, B * Sk),
+                                          (dv, dv16, v_in16, 2 * E, acc_v, B * Sk)):
+        dz2, dz216 = dz.reshape(rows, E), dz16.reshape(rows, E)
+
+        def in_wgrad(dz2=dz2, dz216=dz216, z16=z16, lo=lo):
+            ops.gemm_bf16_v2(dz216, z16, a_mn=True, b_mn=True, residual=gw[lo:lo + E], out32=gw[lo:lo + E])
+            ops.reduce_channels(dz2.contiguous(), gb[lo:lo + E], 1, rows, E, 1, beta=1.0)
+
+        on_side(in_wgrad, dz216, z16, dz2)
+        if acc is not None:
+            tgt = acc[0].view(rows, E)
+            ops.gemm_bf16_v2(dz216, w16[lo:lo + E], b_mn=True, residual=tgt if acc[1] else None, out32=tgt)
+
+
+# ----------------------------------------------------------------------------------------------------------------------
 # SelfAttnCrossAttn (modules/ObjCAViT.py:167-213)
 # ----------------------------------------------------------------------------------------------------------------------
 
@@ -414,10 +478,17 @@ def saca_fwd(P: Params, pre: str, img_tok: torch.Tensor, objs, no_obj_sa: bool, 
         kpm = None
         geom = ("dense",)
     join_branch(dev, fork, att_obj_s, kpm)
-    final_img, sv_c1 = cross_fwd(P, pre + "cross_attn_obj_im.", att_img, att_obj_s, att_img, kpm)          # :195-201
+    tc = P16 is not None and _cross_tc_ok(S, S)
+    if tc:
+        final_img, sv_c1 = cross_fwd16(P, P16, pre + "cross_attn_obj_im.", att_img, att_obj_s, att_img, kpm)   # :195-201
+    else:
+        final_img, sv_c1 = cross_fwd(P, pre + "cross_attn_obj_im.", att_img, att_obj_s, att_img, kpm)          # :195-201
     final_obj, sv_c2 = None, None
     if need_object_output:
-        final_obj, sv_c2 = cross_fwd(P, pre + "cross_attn_im_obj.", att_obj_s, att_img, att_obj_s, None)   # :202-207
+        if tc:
+            final_obj, sv_c2 = cross_fwd16(P, P16, pre + "cross_attn_im_obj.", att_obj_s, att_img, att_obj_s, None)
+        else:
+            final_obj, sv_c2 = cross_fwd(P, pre + "cross_attn_im_obj.", att_obj_s, att_img, att_obj_s, None)   # :202-207
     return final_img, final_obj, (sv_img, sv_obj, sv_c1, sv_c2, geom, (B, S))
 
 
@@ -427,9 +498,10 @@ def saca_bwd(P: Params, G: Params, pre: str, saved, d_final_img: torch.Tensor, d
     dev = d_final_img.device
     d_att_img = torch.empty(B, S, E, device=dev, dtype=torch.float32)
     d_att_obj_s = torch.empty(B, S, E, device=dev, dtype=torch.float32)
-    cross_bwd(P, G, pre + "cross_attn_obj_im.", sv_c1, d_final_img, (d_att_img, 0.0), (d_att_obj_s, 0.0), (d_att_img, 1.0))
+    xb = (lambda *a: cross_bwd16(P, P16, G, *a)) if sv_c1[0] == "bf16" else (lambda *a: cross_bwd(P, G, *a))
+    xb(pre + "cross_attn_obj_im.", sv_c1, d_final_img, (d_att_img, 0.0), (d_att_obj_s, 0.0), (d_att_img, 1.0))
     if sv_c2 is not None and d_final_obj is not None:
-        cross_bwd(P, G, pre + "cross_attn_im_obj.", sv_c2, d_final_obj, (d_att_obj_s, 1.0), (d_att_img, 1.0), (d_att_obj_s, 1.0))
+        xb(pre + "cross_attn_im_obj.", sv_c2, d_final_obj, (d_att_obj_s, 1.0), (d_att_img, 1.0), (d_att_obj_s, 1.0))
     fork = fork_branch(dev, 2)
     d_img_tok = encoder_bwd(P, G, pre + "image_transformer_encoder.", sv_img, d_att_img, P16)
     with on_branch(dev, fork, d_att_obj_s):
@@ -468,12 +540,20 @@ def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_
     else:
         P16 = None
     t.P16 = P16
+    global FAST_ROWS
+    FAST_ROWS = cfg.get("pixel") == "bf16"
     B, C, h, w = x.shape
     t.shape = (B, C, h, w)
     # ``cfg["prefix"]``: key prefix of the mViT / ObjCAViT parameters ("" when the inner module itself is the boundary)
     pre = cfg.get("prefix", "adaptive_bins_layer." if cfg["kind"] == "adabins" else "objcavit.")
     if cfg.get("pixel") == "bf16":
         t.late_P, t.late_pre = P, pre
+        # the patch-embedding weights in the tensor-core kernel's (ky, kx, c) order: depends on the weights only — its own branch
+        # from the very start of the step instead of 25 us on the chain right before the patch embedding
+        wkey = pre + ("patch_transformer.embedding_convPxP.weight" if cfg["kind"] == "adabins" else "image_embedding_convPxP.weight")
+        t.wp_fork = fork_branch(x.device, 4)
+        with on_branch(x.device, t.wp_fork, P[wkey], name="pack"):
+            t.wp = ops.pack_patch_weights_bf16(P[wkey])
         _pixel_prologue(P, pre, t, x)
     if cfg["kind"] == "adabins":
         pt = pre + "patch_transformer."
@@ -559,7 +639,9 @@ def _patch_embed(t, x: torch.Tensor, w: torch.Tensor, bias, pos, patch_size: int
         if t.xh_ready is not None:                   # t.xh was made on the pixel branch (_pixel_prologue)
             cur.wait_event(t.xh_ready)
             t.xh.record_stream(cur)
-        tok = ops.patch_embed_bf16(t.xh, ops.pack_patch_weights_bf16(w), bias, pos, patch_size, want32=True, want16=False)[0]
+        join_branch(x.device, t.wp_fork, t.wp, name="pack")
+        tok = ops.patch_embed_bf16(t.xh, t.wp, bias, pos, patch_size, want32=True, want16=False)[0]
+        t.wp = None
         if getattr(t, "pixel_rest_pending", False):      # the rest of the pixel branch, ordered after the patch embedding
             t.pixel_rest_pending = False
             t.xh_keep = t.xh

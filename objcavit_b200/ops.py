@@ -107,6 +107,23 @@ def linear(a: torch.Tensor, w: torch.Tensor, bias=None, act: int = ACT_NONE, res
     return out
 
 
+def linear_rows(a: torch.Tensor, w: torch.Tensor, bias=None, leaky: bool = False):
+    """out[R,N] = [leaky_relu](a[R,K] @ w[N,K]^T + bias) for few rows (``ocv_linear_rows_f32``; K <= 512, K % 4 == 0)."""
+    _chk(a, torch.float32, "a"); _chk(w, torch.float32, "w")
+    R, K, lda = _row_major_2d(a, "a")
+    N, K2, ldb = _row_major_2d(w, "w")
+    assert K == K2 and ldb == K
+    out = torch.empty(R, N, device=a.device, dtype=torch.float32)
+    _call("ocv_linear_rows_f32", a.data_ptr(), lda, R, w.data_ptr(), _ptr(bias), K, N, int(leaky), out.data_ptr(), N, _stream())
+    return out
+
+
+def linear_rows_ok(a: torch.Tensor, w: torch.Tensor) -> bool:
+    K = a.shape[-1]
+    return (a.shape[0] <= 1024 and K <= 512 and K % 4 == 0 and a.stride(-1) == 1 and a.stride(0) % 4 == 0 and a.data_ptr() % 16 == 0
+            and w.is_contiguous() and w.data_ptr() % 16 == 0)
+
+
 def batched_matmul_nn(a: torch.Tensor, b: torch.Tensor, out=None):
     """out[n] = a[n] ([M,K], any batch/row stride) @ b[n] ([K,N] contiguous)   (fp32)."""
     _chk(a, torch.float32, "a"); _chk(b, torch.float32, "b")
