@@ -230,17 +230,6 @@ int ocv_gemm_bf16_ex(const void* A, const void* Wt, const float* bias, const flo
                      const float* ln_gamma, const float* ln_beta, const uint8_t* zero_rows, float* C32, int ldc32,
                      void* C16, int ldc16, int M, int N, int K, int lda, int ldb, int act, void* stream);
 
-/* Fused feed-forward block of a post-norm encoder layer (one tcgen05 kernel, objcavit_b200/csrc/ffn_fused_bf16.cu):
- *   out = LayerNorm_128( residual + relu(X W1^T + b1) W2^T + b2 ) * gamma + beta,  rows flagged in zero_rows written as 0.
- *   X16 [M,128] bf16 (row pitch lda), W1 [F,128] bf16, W2 [128,F] bf16 (nn.Linear layouts), F % 128 == 0, F <= 2048;
- *   residual [M,128] fp32 (pitch ldr) = the fp32 copy of X; outputs fp32 C32 (pitch ldc32) and/or bf16 C16 (pitch ldc16).
- *   The [M,F] hidden activations stay in shared memory / TMEM (bf16-rounded exactly like the two-GEMM path wrote them).
- * replaces: linear1 + ReLU + linear2 + residual + norm2 of nn.TransformerEncoderLayer (modules/layers.py:8;
- *   modules/ObjCAViT.py:155-161). */
-int ocv_ffn_fused_bf16(const void* X16, int lda, const void* W1, const float* b1, const void* W2, const float* b2,
-                       const float* residual, int ldr, const float* ln_gamma, const float* ln_beta, const uint8_t* zero_rows,
-                       float* C32, int ldc32, void* C16, int ldc16, int M, int F, void* stream);
-
 /* Fused pixel kernel (one persistent tcgen05 kernel, objcavit_b200/csrc/pixel_fused_bf16.cu):
  *   conv3x3 (implicit GEMM over an NHWC bf16 halo tile, 9 shifted smem descriptors) -> per-image logits GEMM with
  *   Mb[b] = s * Wout @ Q[b] (bins x channels, bf16) -> per-pixel softmax over K=256 bins -> sum p*centre.

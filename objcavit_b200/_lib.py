@@ -55,7 +55,6 @@ PROTOTYPES = {
     "ocv_gemm_bf16_v2": (i32, [p, p, i32, i32, p, p, i32, p, p, p, i32, p, i32, p, i32, i32, i32, i32, i32, i32, i32, f32, C.c_ulonglong,
                                 i32, p, p]),
     "ocv_gemm_bf16_ex": (i32, [p, p, p, p, i32, p, p, p, p, i32, p, i32, i32, i32, i32, i32, i32, i32, p]),
-    "ocv_ffn_fused_bf16": (i32, [p, i32, p, p, p, p, p, i32, p, p, p, p, i32, p, i32, i32, i32, p]),
     "ocv_pack_conv3x3_bf16": (i32, [p, p, p]),
     "ocv_fold_queries_bf16": (i32, [p, p, p, i64, i32, p, f32, p, p, i32, i32, i32, i32, p]),
     "ocv_pixel_fused_bf16": (i32, [p, p, p, p, p, p, i32, i32, i32, i32, p]),

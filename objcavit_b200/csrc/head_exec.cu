@@ -112,9 +112,6 @@ struct ocv_head {
     bool graph_failed = false;
   } lane[4];
   bool use_graphs = true;
-  // A-B switch: OCV_FFN_FUSION=1 runs the feed-forward block as ONE kernel (csrc/ffn_fused_bf16.cu).  Off by default: measured
-  // 24.6 us vs 14.3 + 10.1 us for the two GEMMs at M = 4800 (ncu, cold) and no change of the step time, see DESIGN.md §4.3.
-  bool fuse_ffn = getenv("OCV_FFN_FUSION") != nullptr;
   int lanes = 0;  // 0 = classic: everything on the caller's stream
   int pixel_ctas = 0;
   cudaStream_t pix = nullptr;
@@ -366,15 +363,10 @@ int encoder(Ctx& c, const std::string& pre, Scratch& s, int cur, int B, int S, c
                             3 * E, (long long)S * 3 * E, 3 * E, (long long)S * 3 * E, 3 * E, (long long)S * E, E, st));
     c.run(ocv_gemm_bf16_ex(s.att, w_out, b_out, s.x32[cur], E, g1, e1, nullptr, s.x32[y], E, s.x16[y], E, M, E, E, E, E,
                            OCV_ACT_NONE, st));
-    if (H->fuse_ffn) {
-      c.run(ocv_ffn_fused_bf16(s.x16[y], E, w_1, b_1, w_2, b_2, s.x32[y], E, g2, e2, l == 3 ? mask : nullptr, s.x32[z], E,
-                               s.x16[z], E, M, FFN, st));
-    } else {
-      c.run(ocv_gemm_bf16_ex(s.x16[y], w_1, b_1, nullptr, 0, nullptr, nullptr, nullptr, nullptr, 0, s.h, FFN, M, FFN, E, E,
-                             E, OCV_ACT_RELU, st));
-      c.run(ocv_gemm_bf16_ex(s.h, w_2, b_2, s.x32[y], E, g2, e2, l == 3 ? mask : nullptr, s.x32[z], E, s.x16[z], E, M, E,
-                             FFN, FFN, FFN, OCV_ACT_NONE, st));
-    }
+    c.run(ocv_gemm_bf16_ex(s.x16[y], w_1, b_1, nullptr, 0, nullptr, nullptr, nullptr, nullptr, 0, s.h, FFN, M, FFN, E, E,
+                           E, OCV_ACT_RELU, st));
+    c.run(ocv_gemm_bf16_ex(s.h, w_2, b_2, s.x32[y], E, g2, e2, l == 3 ? mask : nullptr, s.x32[z], E, s.x16[z], E, M, E,
+                           FFN, FFN, FFN, OCV_ACT_NONE, st));
     cur = z;
   }
   return cur;

@@ -939,20 +939,6 @@ def conv3x3_nhwc_bf16(x_nhwc: torch.Tensor, w3p: torch.Tensor, bias: torch.Tenso
     return y
 
 
-def ffn_fused_bf16(x16: torch.Tensor, x32: torch.Tensor, w1: torch.Tensor, b1, w2: torch.Tensor, b2, gamma, beta, zero_rows=None):
-    """LayerNorm(x32 + relu(x16 W1^T + b1) W2^T + b2): -> (fp32 [M,128], bf16 [M,128]); the hidden activations stay on chip."""
-    _chk(x16, torch.bfloat16, "x16"); _chk(x32, torch.float32, "x32"); _chk(w1, torch.bfloat16, "w1"); _chk(w2, torch.bfloat16, "w2")
-    M, E_ = x16.shape
-    F_ = w1.shape[0]
-    assert E_ == 128 and x16.is_contiguous() and x32.is_contiguous() and w1.is_contiguous() and w2.is_contiguous()
-    assert w1.shape == (F_, 128) and w2.shape == (128, F_) and x32.shape == (M, 128)
-    o32 = torch.empty(M, 128, device=x16.device, dtype=torch.float32)
-    o16 = torch.empty(M, 128, device=x16.device, dtype=torch.bfloat16)
-    _call("ocv_ffn_fused_bf16", x16.data_ptr(), 128, w1.data_ptr(), b1.data_ptr(), w2.data_ptr(), b2.data_ptr(), x32.data_ptr(), 128,
-          gamma.data_ptr(), beta.data_ptr(), _ptr(zero_rows), o32.data_ptr(), 128, o16.data_ptr(), 128, M, F_, _stream())
-    return o32, o16
-
-
 def dropout(x: torch.Tensor, p: float, seed: int, residual=None, out=None) -> torch.Tensor:
     """out = residual + dropout(x) with the counter-based mask of site ``seed`` (``ocv_dropout_f32``); on a gradient: its backward."""
     _chk(x, torch.float32, "x")

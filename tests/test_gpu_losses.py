@@ -78,3 +78,25 @@ def test_loss_fixture_and_wrapper(cuda):
     want.backward()
     assert rel_err(total.detach(), want.detach()) < 1e-5
     assert rel_err(out.depth_pred.grad, dp.grad) < 1e-4 and rel_err(out.bin_edges.grad, de.grad) < 1e-4
+
+
+def test_bins_chamfer_edge_cases(cuda):
+    """An image without valid ground truth (contributes 0; the batch mean still divides by B), constant ground truth, one valid pixel
+    beyond the last bin: kernel == the three CPU statements of the loss (tests/test_oracle_golden.py), gradient == autograd."""
+    g = torch.Generator().manual_seed(11)
+    widths = torch.rand(4, 256, generator=g) + 0.05
+    edges, _ = oh.bin_edges_and_centres(widths / widths.sum(1, keepdim=True), 0.001, 10.0)
+    gt, _ = synth.make_gt(4, 24, 32, 10.0, seed=5)
+    gt[1] = 0.0
+    gt[2] = torch.where(gt[2] > 0, torch.full_like(gt[2], 3.25), gt[2])
+    gt[3] = 0.0
+    gt[3, 0, 5, 7] = 25.0
+    mask = gt > 0.001
+    e = edges.clone().requires_grad_(True)
+    want = oh.bins_chamfer_loss(e, gt, mask)
+    want.backward()
+    loss, grad = ops.bins_chamfer(edges.to(cuda), gt.to(cuda), mask.to(cuda), want_grad=True)
+    assert rel_err(loss.view(()), want.detach()) < 1e-5
+    assert abs(float(loss) - oh.bins_chamfer_loss_np(edges, gt, mask)) < 1e-5 * abs(float(loss))
+    assert rel_err(grad, e.grad) < 1e-4
+    assert float(grad[1].abs().max()) == 0.0          # the empty image has no gradient

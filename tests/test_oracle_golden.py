@@ -54,3 +54,31 @@ def test_losses_fixture():
     gt, mask = synth.make_gt(2, 24, 32, 10.0)
     assert abs(float(oh.silog_loss(g["depth"], gt, mask)) - float(g["silog"])) < 1e-5
     assert abs(float(oh.bins_chamfer_loss(g["edges"], gt, mask)) - float(g["chamfer"])) < 1e-6
+
+
+def test_chamfer_stated_three_ways_and_edge_cases():
+    """pytorch3d 0.7.0 (``losses/BinsChamferLoss.py:11,36``) cannot be installed here: the chamfer term stays UNPINNED against the
+    library.  Its published definition is stated three times by different routes — searchsorted (torch), O(P T) distance matrix
+    (torch), sorted ground truth + Voronoi cells of the centres (numpy fp64) — and they must agree, including the edge cases: an
+    image without any valid ground truth (contributes 0 to both directions, the batch mean still divides by B), constant ground
+    truth, ground truth outside the bin range, a single valid pixel."""
+    import torch
+    from oracle import head as oh
+    from oracle import synth
+    g = torch.Generator().manual_seed(11)
+    widths = torch.rand(4, 256, generator=g) + 0.05
+    edges, _ = oh.bin_edges_and_centres(widths / widths.sum(1, keepdim=True), 0.001, 10.0)
+    gt, mask = synth.make_gt(4, 24, 32, 10.0, seed=5)
+    gt[1] = 0.0                     # image 1: no valid pixel at all
+    gt[2] = torch.where(gt[2] > 0, torch.full_like(gt[2], 3.25), gt[2])      # image 2: constant ground truth
+    gt[3] = 0.0
+    gt[3, 0, 5, 7] = 25.0           # image 3: ONE valid pixel, beyond the last bin edge
+    mask = gt > 0.001
+    a = float(oh.bins_chamfer_loss(edges, gt, mask))
+    b = float(oh.bins_chamfer_loss_bruteforce(edges, gt, mask))
+    c = oh.bins_chamfer_loss_np(edges, gt, mask)
+    assert abs(a - c) < 1e-5 * abs(c) and abs(b - c) < 1e-5 * abs(c), (a, b, c)
+    # the empty image contributes nothing: dropping it and rescaling the batch mean gives the same value
+    keep = [0, 2, 3]
+    d = oh.bins_chamfer_loss_np(edges[keep], gt[keep], mask[keep])
+    assert abs(c - d * 3 / 4) < 1e-9 * abs(c)
