@@ -11,6 +11,7 @@ from objcavit_b200 import ops
 from objcavit_b200.config import AttrDict
 from objcavit_b200.losses import BinsChamferLoss, LossWrapper, SILogLoss
 from oracle import head as oh
+from oracle import synth
 
 pytestmark = pytest.mark.gpu
 
