@@ -193,8 +193,10 @@ extern "C" int ocv_mha_core_bf16(const void* q, const void* k, const void* v, vo
   OCV_CHECK_ALIGN(((q_bstride | k_bstride | v_bstride | q_rstride | k_rstride | v_rstride) & 7) == 0 &&
                   ((o_bstride | o_rstride) & 1) == 0);
   if (int s = ocv_require_sm100()) return s;
-  // d = 32, 4 heads, Sk <= 448 (every reference configuration except the full-resolution AdaBins variant): the tcgen05 kernel
-  if (ocv_mha_tc_supported(Sq, Sk, heads, d, q_bstride, q_rstride, k_bstride, k_rstride, v_bstride, v_rstride, o_bstride, o_rstride) &&
+  // OCV_ATTN_TC=1: the tcgen05 kernel for every covered shape (d = 32, 4 heads, Sk <= 448); by default this entry point keeps the
+  // mma.sync kernel, which is the faster one for self attention at the reference sizes (see ocv_attn_tc_policy)
+  if (ocv_attn_tc_policy() == 1 &&
+      ocv_mha_tc_supported(Sq, Sk, heads, d, q_bstride, q_rstride, k_bstride, k_rstride, v_bstride, v_rstride, o_bstride, o_rstride) &&
       (reinterpret_cast<uintptr_t>(out) & 15) == 0)
     return ocv_mha_core_tc_bf16(q, k, v, out, nullptr, nullptr, key_padding_mask, B, Sq, Sk, heads, d, q_bstride, q_rstride, k_bstride,
                                 k_rstride, v_bstride, v_rstride, o_bstride, o_rstride, 0.f, 0ull, stream);

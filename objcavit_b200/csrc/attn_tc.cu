@@ -194,16 +194,21 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
       const int head = blockIdx.y * 2 + hd;
       mbar_wait(s_full, hd);
       tc_fence_after();
-      // ---- pass 1: row maximum over this thread's half of the keys
+      // ---- pass 1: row maximum over this thread's half of the keys.  TMEM loads have a few hundred cycles of latency each:
+      // both 32-column loads of a 64-key chunk are in flight before the one wait (half the round trips)
       float mx = -INFINITY;
-      for (int c = cb; c < ce; ++c)
+      for (int c = cb; c < ce; ++c) {
+        const int col0 = c * CHK;
+        const bool two = col0 + 32 < Skp;
+        uint32_t r0[32], r1[32];
+        tmem_ld32(tmem + lane_base + TM_S + col0, r0);
+        if (two) tmem_ld32(tmem + lane_base + TM_S + col0 + 32, r1);
+        tmem_ld_wait();
+#pragma unroll
         for (int sub = 0; sub < 2; ++sub) {
-          const int col0 = c * CHK + sub * 32;
-          if (col0 >= Skp) break;
-          uint32_t r[32];
-          tmem_ld32(tmem + lane_base + TM_S + col0, r);
-          tmem_ld_wait();
-          const uint32_t vb = valid[col0 >> 5];          // the same word for every thread: warp-uniform branches
+          if (sub == 1 && !two) break;
+          const uint32_t* r = sub ? r1 : r0;
+          const uint32_t vb = valid[(col0 >> 5) + sub];          // the same word for every thread: warp-uniform branches
           if (vb == 0xffffffffu) {
 #pragma unroll
             for (int j = 0; j < 32; j += 2) mx = fmaxf(mx, fmaxf(__uint_as_float(r[j]), __uint_as_float(r[j + 1])));
@@ -213,6 +218,7 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
               if ((vb >> j) & 1u) mx = fmaxf(mx, __uint_as_float(r[j]));
           }
         }
+      }
       red[g * 128 + row] = mx;
       soft_bar();
       const float m_row = fmaxf(red[row], red[128 + row]);
@@ -225,13 +231,16 @@ mha_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ C
         const uint32_t n = prod++;
         const int slot = n & 1;
         uint32_t pk[32];
+        uint32_t ra[32], rb2[32];
+        const bool two = c * CHK + 32 < Skp;
+        tmem_ld32(tmem + lane_base + TM_S + c * CHK, ra);
+        if (two) tmem_ld32(tmem + lane_base + TM_S + c * CHK + 32, rb2);
+        tmem_ld_wait();
 #pragma unroll
         for (int sub = 0; sub < 2; ++sub) {
           const int col0 = c * CHK + sub * 32;
-          if (col0 < Skp) {
-            uint32_t r[32];
-            tmem_ld32(tmem + lane_base + TM_S + col0, r);
-            tmem_ld_wait();
+          if (sub == 0 || two) {
+            const uint32_t* r = sub ? rb2 : ra;
             const uint32_t vb = (m_row != -INFINITY) ? valid[col0 >> 5] : 0u;
             if (vb == 0xffffffffu && !p.drop_thr) {          // the common case: no masked key in the group, inference
               float s0 = 0.f, s1 = 0.f;
@@ -337,15 +346,23 @@ int make_tmap_rows(CUtensorMap* out, const void* base, int S, int B, long long b
 
 }  // namespace
 
-// 1 when the tcgen05 kernel covers the shape (else the caller keeps the mma.sync kernel)
+// OCV_ATTN_TC: "0" = never take the tcgen05 attention kernels; "1" = take them wherever the shape is covered; unset = the measured
+// policy: cross attention of the inference head and every attention core of the training step on tcgen05, the inference encoders'
+// self attention on the mma.sync kernel (csrc/attn_bf16.cu), which is 4-6 us faster per launch at S = 300 / 418 (both are
+// latency-bound there: profiles/attn_tc_vs_mma_r02.txt).
+int ocv_attn_tc_policy() {
+  static int policy = -1;
+  if (policy < 0) {
+    const char* e = getenv("OCV_ATTN_TC");
+    policy = !e ? 2 : (e[0] == '0' ? 0 : 1);
+  }
+  return policy;
+}
+
+// true when the tcgen05 kernel covers the shape (else the caller keeps the mma.sync kernel)
 bool ocv_mha_tc_supported(int Sq, int Sk, int heads, int d, long long q_bs, int q_rs, long long k_bs, int k_rs, long long v_bs,
                           int v_rs, long long o_bs, int o_rs) {
-  static int enabled = -1;
-  if (enabled < 0) {
-    const char* e = getenv("OCV_ATTN_TC");
-    enabled = (e && e[0] == '0') ? 0 : 1;
-  }
-  return enabled && heads == 4 && d == HD && Sk >= 1 && Sk <= SKMAX && Sq >= 1 &&
+  return ocv_attn_tc_policy() != 0 && heads == 4 && d == HD && Sk >= 1 && Sk <= SKMAX && Sq >= 1 &&
          ((q_bs | k_bs | v_bs | q_rs | k_rs | v_rs) & 7) == 0 && ((o_bs | o_rs) & 7) == 0;
 }
 

@@ -27,6 +27,7 @@ bool ocv_mha_tc_supported(int Sq, int Sk, int heads, int d, long long q_bs, int 
                           long long o_bs, int o_rs);
 
 bool ocv_mha_bwd_tc_supported(int Sq, int Sk, int heads, int d);
+int ocv_attn_tc_policy();   // 0 never, 1 everywhere covered, 2 (default) cross attention + training step
 
 static inline cudaStream_t ocv_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 

@@ -388,6 +388,14 @@ void cross_attention(Ctx& c, const std::string& pre, Scratch& s, const bf16* qv1
                          OCV_ACT_NONE, st));
   c.run(ocv_gemm_bf16_ex(k16, w + (size_t)E * E, b + E, nullptr, 0, nullptr, nullptr, nullptr, nullptr, 0, s.kk, E, M, E, E,
                          E, E, OCV_ACT_NONE, st));
+  // patch x object cross attention: the tcgen05 attention core (north star); OCV_ATTN_TC=0 keeps the mma.sync kernel
+  if (ocv_attn_tc_policy() != 0 &&
+      ocv_mha_tc_supported(S, S, HEADS, E / HEADS, (long long)S * 3 * E, 3 * E, (long long)S * E, E, (long long)S * 3 * E, 3 * E,
+                           (long long)S * E, E))
+    c.run(ocv_mha_core_tc_bf16(s.qkv, s.kk, s.qkv + 2 * E, s.att, nullptr, nullptr, kpm, B, S, S, HEADS, E / HEADS,
+                               (long long)S * 3 * E, 3 * E, (long long)S * E, E, (long long)S * 3 * E, 3 * E, (long long)S * E, E, 0.f,
+                               0ull, st));
+  else
   c.run(ocv_mha_core_bf16(s.qkv, s.kk, s.qkv + 2 * E, s.att, kpm, B, S, S, HEADS, E / HEADS, (long long)S * 3 * E, 3 * E,
                           (long long)S * E, E, (long long)S * 3 * E, 3 * E, (long long)S * E, E, st));
   c.run(ocv_gemm_bf16_ex(s.att, wo, bo, nullptr, 0, nullptr, nullptr, nullptr, out32, E, out16, E, M, E, E, E, E,
