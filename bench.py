@@ -112,14 +112,15 @@ def make_inputs(B, rank, h=H, w=W, nobj=NOBJ):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled from before the first timed region until after the last one
-    (B200_PROFILING.md recipe).  One sample every 500 ms: the sampler shares rank 0's host cores with the launching thread."""
+    """nvidia-smi clocks / throttle reasons (B200_PROFILING.md recipe), one sample every 500 ms from process start to the end of the
+    last timed region.  The query is kept to the clock fields (power / utilisation queries take a driver lock for milliseconds and a
+    sample that lands inside a 12 ms timed window doubles it); samples are attributed to the timed windows by their timestamps."""
 
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,utilization.gpu,power.draw")
+    Q = ("timestamp,clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.windows = index, [], None, []
 
     def start(self):
         try:
@@ -132,23 +133,29 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
+
+    def window(self, t0, t1):
+        self.windows.append((t0, t1))
 
     def stop(self):
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.6)
         self.proc.terminate()
-        rows = [r for r in self.rows if r and r[0].isdigit()]
-        busy = [r for r in rows if len(r) > 6 and r[6].isdigit() and int(r[6]) >= 10] or rows     # samples taken under load
+        rows = [(t, r[1:]) for t, r in self.rows if len(r) >= 7 and r[1].isdigit()]
+        lo = min((w[0] for w in self.windows), default=0.0) - 0.6
+        hi = max((w[1] for w in self.windows), default=float("inf")) + 0.6
+        busy = [r for t, r in rows if lo <= t <= hi] or [r for _, r in rows]      # samples between the first and the last timed region
         sm = sorted(int(r[0]) for r in busy)
-        mx = [int(r[1]) for r in rows if len(r) > 1 and r[1].isdigit()]
+        mx = [int(r[1]) for _, r in rows if r[1].isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for r in rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
-        pw = [float(r[7]) for r in busy if len(r) > 7 and r[7].replace(".", "", 1).isdigit()]
+        reasons = sorted({n for r in busy for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(rows), "samples_under_load": len(busy) if busy is not rows else 0,
-                "power_w_max": max(pw) if pw else None}
+                "samples": len(rows), "samples_in_timed_span": len(busy)}
+
+
+_SAMPLER = None
 
 
 # ---- the reference's own CPU implementation of the path -----------------------------------------------------------------
@@ -348,11 +355,14 @@ class Ctx:
         """CUDA events around ``steps`` calls of ``fn``, barrier + synchronize on both sides -> (MAX over ranks ms, per-rank ms)."""
         self.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0 = time.time()
         e0.record()
         for _ in range(steps):
             fn()
         e1.record()
         self.barrier()
+        if _SAMPLER is not None:
+            _SAMPLER.window(w0, time.time())
         ms = e0.elapsed_time(e1)
         if self.dist is None:
             return ms, [ms]
@@ -569,9 +579,10 @@ def measure_train(ctx, a, K, W_, with_breakdown=True, with_e2e=True):
 
 def run_train(a):
     """--workload train: the training step as the headline of the line."""
+    global _SAMPLER
     ctx = Ctx()
     W_, K = max(a.warmup, 3), a.steps
-    sampler = ClockSampler(ctx.local).start() if ctx.rank == 0 else None
+    sampler = _SAMPLER = ClockSampler(ctx.local).start() if ctx.rank == 0 else None      # NVML start-up is over before anything is timed
     out = measure_train(ctx, a, K, W_)
     out["clocks"] = sampler.stop() if sampler else None
     if ctx.rank == 0 and ctx.world == 1 and not a.no_cpu_baseline:
@@ -726,8 +737,10 @@ def main():
     from objcavit_b200.config import builtin_args
     from objcavit_b200.modules import build_head
 
+    global _SAMPLER
     ctx = Ctx()
     world, rank, dev = ctx.world, ctx.rank, ctx.dev
+    sampler = _SAMPLER = ClockSampler(ctx.local).start() if rank == 0 else None      # NVML start-up is over before anything is timed
     precision = a.precision
     if precision is None:
         try:
@@ -752,8 +765,6 @@ def main():
         objs_dev, boxes_dev = [o.to(dev) for o in objs], [b.to(dev) for b in boxes]
     objs_host = [o.pin_memory() for o in objs]
     boxes_host = [b.pin_memory() for b in boxes]
-
-    sampler = ClockSampler(ctx.local).start() if rank == 0 else None
 
     # ---- device-resident throughput (`value`) ------------------------------------------------------
     # classic mode first (one call = one stream-ordered pass: the single-call latency), then the pipelined serving mode

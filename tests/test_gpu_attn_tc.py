@@ -67,10 +67,10 @@ def test_attention_core_on_tcgen05(cuda, B, Sq, Sk, packed, masked):
     assert float((stats[..., 0].double()[rows] - mx[rows]).abs().max()) < 2e-2
     sm = torch.exp2(s2 - mx[..., None]).sum(-1)
     assert float(((stats[..., 1].double()[rows] - sm[rows]).abs() / sm[rows]).max()) < 1e-2
-    # the dispatching entry point takes the same kernel for these shapes
+    # the dispatching entry point (mma.sync kernel by default, tcgen05 with OCV_ATTN_TC=1) agrees to bf16 rounding
     again = ops.mha_core_bf16(q, k, v, mask)
     torch.cuda.synchronize()
-    assert torch.equal(again[ok], out16[ok])
+    assert float((again.double()[ok] - out16.double()[ok]).abs().max()) < 1.5e-2 * scale
 
 
 def test_probability_dropout_uses_the_fp32_kernels_masks(cuda):
