@@ -223,11 +223,16 @@ def _pixel_reference(x, w3, b3, wout, bout, queries, centres):
     return (p * centres[:, :, None, None]).sum(1, keepdim=True)
 
 
-@pytest.mark.parametrize("B,h,w,max_ctas", [(1, 16, 8, 0), (2, 48, 40, 0), (3, 37, 29, 2), (2, 64, 96, 5)])
-def test_pixel_fused_bf16(cuda, B, h, w, max_ctas):
+@pytest.mark.parametrize("transposed", [1, 0])
+@pytest.mark.parametrize("B,h,w,max_ctas", [(1, 16, 8, 0), (2, 48, 40, 0), (3, 37, 29, 2), (2, 64, 96, 5), (1, 240, 24, 3), (2, 176, 40, 0),
+                                            (1, 30, 8, 0)])
+def test_pixel_fused_bf16(cuda, monkeypatch, B, h, w, max_ctas, transposed):
     """The fused tcgen05 pixel kernel (conv3x3 halo tile + logits GEMM + softmax + expectation), incl. image
-    borders (zero padding through TMA OOB fill), ragged tiles and CTAs that loop over many tiles."""
+    borders (zero padding through TMA OOB fill), ragged tiles and CTAs that loop over many tiles.  Both formulations: the
+    transposed one (channels on M, N = 8 x th pixels per MMA: block heights 16 / 24 / 20 / 32 / 30 / 30 / 30 for these shapes) that
+    ocv_pixel_fused_bf16 launches by default and the pixels-on-M one (OCV_PIXEL_T=0)."""
     from objcavit_b200 import ops
+    monkeypatch.setenv("OCV_PIXEL_T", str(transposed))
     x = torch.randn(B, 128, h, w, generator=g(1))
     w3 = torch.randn(128, 128, 3, 3, generator=g(2)) * 0.03; b3 = torch.randn(128, generator=g(3)) * 0.1
     wout = torch.randn(256, 128, 1, 1, generator=g(4)) * 0.1; bout = torch.randn(256, generator=g(5)) * 0.1
