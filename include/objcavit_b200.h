@@ -438,6 +438,8 @@ int ocv_im2col3x3_bf16(const void* x_planar_bf16, void* col_bf16, int B, int C, 
  *     pitch ld (elements) >= B*S; columns >= B*S are left untouched (zero them once when ld is padded).
  *   ocv_transpose_cast_f32_bf16: dst[c][r] = bf16(src[r][c]) for any R, C (pitches in elements). */
 int ocv_patch_unfold_bf16(const float* x, void* out_bf16, int B, int C, int h, int w, int P, long long ld, void* stream);
+/* the same operand from the NHWC bf16 copy of the features (xh [B,h,w,C], C % 32 == 0, 16-byte aligned): half the input bytes */
+int ocv_patch_unfold_nhwc_bf16(const void* xh_bf16, void* out_bf16, int B, int C, int h, int w, int P, long long ld, void* stream);
 int ocv_transpose_cast_f32_bf16(const float* src, void* dst_bf16, int R, int C, long long src_ld, long long dst_ld, void* stream);
 /* Adjoint of ocv_pad_objects_f32: dsrc[offsets[b]+j, :] = beta * dsrc + dpadded[b, left+j, :] for j < n_b (left = L-Nmax when
  * left_pad else 0); pad rows carry no gradient. */

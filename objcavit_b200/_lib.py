@@ -97,6 +97,7 @@ PROTOTYPES = {
     "ocv_transpose_bf16": (i32, [p, p, i32, i32, i32, i64, i64, i64, i64, p]),
     "ocv_im2col3x3_bf16": (i32, [p, p, i32, i32, i32, i32, p]),
     "ocv_patch_unfold_bf16": (i32, [p, p, i32, i32, i32, i32, i32, i64, p]),
+    "ocv_patch_unfold_nhwc_bf16": (i32, [p, p, i32, i32, i32, i32, i32, i64, p]),
     "ocv_transpose_cast_f32_bf16": (i32, [p, p, i32, i32, i64, i64, p]),
     "ocv_mha_core_dropout_f32": (i32, [p, p, p, p, p, i32, i32, i32, i32, i32, i64, i32, i64, i32, i64, i32, i64, i32, f32,
                                        C.c_ulonglong, p]),

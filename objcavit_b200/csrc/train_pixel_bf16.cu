@@ -421,6 +421,72 @@ extern "C" int ocv_patch_unfold_bf16(const float* x, void* out_bf16, int B, int 
   return ocv_launch_status();
 }
 
+// unfold from the NHWC bf16 copy of the features (what the tensor-core path already holds): half the bytes of the fp32 NCHW read,
+// 64-byte channel chunks in, runs of (rows x gw) tokens out.  Block = (group of patch rows, py, 32-channel chunk, image): the pixel
+// rows y = sy*P + py of the group go to shared memory as [token][px][16 channel-pair words] (+1 pad word per token: a warp reading
+// one (px, channel pair) for 32 consecutive tokens hits 32 banks), then every warp writes token-contiguous rows of the output.
+__global__ void __launch_bounds__(256)
+patch_unfold_nhwc_kernel(const __nv_bfloat16* __restrict__ xh, __nv_bfloat16* __restrict__ out, int C, int h, int w, int Pp, int TG,
+                         long long ld) {
+  extern __shared__ uint32_t utile[];  // [tokens of the group][Pp * 16 + 1]
+  const int gh = h / Pp, gw = w / Pp, S = gh * gw;
+  const int sy0 = blockIdx.x * TG, py = blockIdx.y;
+  const int chunks = C / 32;
+  const int b = blockIdx.z / chunks, c0 = (blockIdx.z - b * chunks) * 32;
+  const int rows = min(TG, gh - sy0);
+  const int ntok = rows * gw;
+  const int tstride = Pp * 16 + 1;
+  // load: one 16-byte piece (8 channels) per thread and step
+  const int npix = rows * gw * Pp;      // pixels of the group's rows that belong to whole patches
+  for (int i = threadIdx.x; i < npix * 4; i += 256) {
+    const int pix = i >> 2, part = i & 3;
+    const int r = pix / (gw * Pp), xx = pix - r * gw * Pp;
+    const int sx = xx / Pp, px = xx - sx * Pp;
+    const uint4 v = *reinterpret_cast<const uint4*>(xh + (((long long)b * h + (long long)(sy0 + r) * Pp + py) * w + xx) * C + c0 + part * 8);
+    uint32_t* d = utile + (r * gw + sx) * tstride + px * 16 + part * 4;
+    d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  unsigned short* o16 = reinterpret_cast<unsigned short*>(out);
+  const long long col0 = (long long)b * S + (long long)sy0 * gw;
+  for (int item = warp; item < Pp * 16; item += 8) {      // (px, channel pair)
+    const int px = item >> 4, cw = item & 15;
+    const long long row_lo = ((long long)(c0 + 2 * cw) * Pp + py) * Pp + px;
+    unsigned short* d_lo = o16 + row_lo * ld + col0;
+    unsigned short* d_hi = d_lo + (long long)Pp * Pp * ld;
+    for (int t = lane; t < ntok; t += 32) {
+      const uint32_t v = utile[t * tstride + px * 16 + cw];
+      d_lo[t] = (unsigned short)(v & 0xFFFFu);
+      d_hi[t] = (unsigned short)(v >> 16);
+    }
+  }
+}
+
+extern "C" int ocv_patch_unfold_nhwc_bf16(const void* xh_bf16, void* out_bf16, int B, int C, int h, int w, int P, long long ld, void* stream) {
+  OCV_CHECK_ARG(xh_bf16 && out_bf16 && B > 0 && C > 0 && h > 0 && w > 0 && P > 0);
+  OCV_CHECK_SHAPE(h >= P && w >= P && C % 32 == 0 && ld >= (long long)B * (h / P) * (w / P) && P <= 65535 && (long long)B * (C / 32) <= 65535);
+  OCV_CHECK_ALIGN((reinterpret_cast<uintptr_t>(xh_bf16) & 15) == 0);
+  if (int s = ocv_require_sm100()) return s;
+  const int gh = h / P, gw = w / P;
+  const size_t per_row = (size_t)gw * (P * 16 + 1) * sizeof(uint32_t);   // one row of patches
+  OCV_CHECK_SHAPE(per_row <= 200 * 1024);
+  int tg_max = (int)((200 * 1024) / per_row);
+  tg_max = tg_max > gh ? gh : tg_max;
+  const int groups = ceil_div(gh, tg_max);
+  const int TG = ceil_div(gh, groups);
+  const size_t smem = per_row * TG;
+  static size_t smem_set = 0;
+  if (smem > 48 * 1024 && smem > smem_set) {
+    cudaError_t e = cudaFuncSetAttribute(patch_unfold_nhwc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
+    smem_set = smem;
+  }
+  patch_unfold_nhwc_kernel<<<dim3(groups, P, B * (C / 32)), 256, smem, ocv_stream(stream)>>>(
+      static_cast<const __nv_bfloat16*>(xh_bf16), static_cast<__nv_bfloat16*>(out_bf16), C, h, w, P, TG, ld);
+  return ocv_launch_status();
+}
+
 extern "C" int ocv_transpose_cast_f32_bf16(const float* src, void* dst_bf16, int R, int C, long long src_ld, long long dst_ld,
                                            void* stream) {
   OCV_CHECK_ARG(src && dst_bf16 && R > 0 && C > 0 && src_ld >= C && dst_ld >= R);

@@ -675,11 +675,16 @@ def _pixel_prologue_rest(P: Params, pre: str, t, x: torch.Tensor) -> None:
     """conv3x3 and the two x-only operands of the backward; called inside the "pixel" branch.  With ``PIXEL_LATE`` the forward calls
     it after the patch embedding has been issued (ordered after it), so that these whole-GPU kernels (a persistent 148-CTA conv,
     0.5 ms of HBM-bound copies) run under the encoder chain instead of delaying the positional MLPs and the patch embedding."""
-    t.x3h = ops.conv3x3_nhwc_bf16(t.xh_keep if getattr(t, "xh_keep", None) is not None else t.xh,
-                                  ops.pack_conv3x3_bf16(P[pre + "conv3x3.weight"]), P[pre + "conv3x3.bias"])
-    # B operand of the patch-embedding weight gradient (backward): needs only x; 0.23 ms of HBM-bound work that fits under the
-    # latency-bound encoder chain here, while anywhere in the backward it competes with the HBM-bound tail kernels
-    t.unf = ops.patch_unfold_bf16(x, 16) if UNFOLD_IN_FORWARD else None
+    xh = t.xh_keep if getattr(t, "xh_keep", None) is not None else t.xh
+    t.x3h = ops.conv3x3_nhwc_bf16(xh, ops.pack_conv3x3_bf16(P[pre + "conv3x3.weight"]), P[pre + "conv3x3.bias"])
+    # the forward chain needs only x3h from this branch: it waits for THIS point, not for the backward operands made below
+    t.x3_ready = None
+    if t.conv_fork is not None:
+        t.x3_ready = torch.cuda.Event()
+        t.x3_ready.record(torch.cuda.current_stream(x.device))
+    # B operand of the patch-embedding weight gradient (backward): a function of the features only, made from their NHWC bf16 copy
+    # (half the bytes of the fp32 map) under the latency-bound encoder chain; the backward joins the branch where it reads it
+    t.unf = ops.patch_unfold_nhwc_bf16(xh, 16) if UNFOLD_IN_FORWARD else None
     # channel-major copy of the conv output (B operand of the dMb GEMMs of the backward): also a function of x only
     Bq, hq, wq, Cq = t.x3h.shape
     t.x3T = ops.transpose_bf16(t.x3h.view(Bq, hq * wq, Cq)) if (UNFOLD_IN_FORWARD and not _fused_tail(hq * wq)) else None
@@ -702,8 +707,15 @@ def _pixel_fwd_bf16(P: Params, pre: str, t, x: torch.Tensor, tok: torch.Tensor, 
     Pn, S = h * w, tok.shape[1]
     Wout = P["conv_out.0.weight"].view(-1, Q)
     K = Wout.shape[0]
-    join_branch(x.device, t.conv_fork, t.x3h, name="pixel")
     t.fused_tail = _fused_tail(Pn) and K == 256 and Q == 128
+    t.pixel_joined = True
+    if t.fused_tail and getattr(t, "x3_ready", None) is not None:
+        cur = torch.cuda.current_stream(x.device)
+        cur.wait_event(t.x3_ready)                       # conv3x3 done; the unfold behind it on that stream is joined by the backward
+        t.x3h.record_stream(cur)
+        t.pixel_joined = False
+    else:
+        join_branch(x.device, t.conv_fork, t.x3h, name="pixel")
     if t.fused_tail:
         # logits never reach HBM: Mb2 = log2e * Wout @ queries[b] (bf16) and blog2 = log2e * bout from one small kernel, then ONE
         # tcgen05 kernel over 128-pixel tiles of x3: logits in TMEM -> softmax in registers -> depth + (max, sum) per pixel
@@ -926,7 +938,10 @@ def _token_bwd(P: Params, G: Params, t: Tape, dtok: torch.Tensor) -> None:
     dt2 = dtok0.contiguous().view(B * S, E)
     Pp = 16
     if t.pixel == "bf16":
-        unf = getattr(t, "unf", None)        # made on the pixel branch in the forward (joined there by _pixel_fwd_bf16)
+        unf = getattr(t, "unf", None)        # made on the pixel branch in the forward
+        if not getattr(t, "pixel_joined", True):
+            join_branch(dev, t.conv_fork, name="pixel")
+            t.pixel_joined = True
         if unf is not None:
             unf.record_stream(torch.cuda.current_stream(dev))
         ops.patch_embed_wgrad_bf16(dt2, x, G[wkey], Pp, unf=unf)

@@ -1077,6 +1077,19 @@ def patch_unfold_bf16(x: torch.Tensor, P: int = 16) -> torch.Tensor:
     return unf
 
 
+def patch_unfold_nhwc_bf16(xh: torch.Tensor, P: int = 16) -> torch.Tensor:
+    """``patch_unfold_bf16`` from the NHWC bf16 copy of the features ``xh`` [B,h,w,C] (what the tensor-core path already holds)."""
+    _chk(xh, torch.bfloat16, "xh")
+    assert xh.is_contiguous()
+    B, h, wd, Cc = xh.shape
+    BS = B * (h // P) * (wd // P)
+    ld = (BS + 7) // 8 * 8
+    alloc = torch.empty if ld == BS else torch.zeros
+    unf = alloc(Cc * P * P, ld, device=xh.device, dtype=torch.bfloat16)
+    _call("ocv_patch_unfold_nhwc_bf16", xh.data_ptr(), unf.data_ptr(), B, Cc, h, wd, P, ld, _stream())
+    return unf
+
+
 def patch_embed_wgrad_bf16(dtok: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, P: int = 16, unf: Optional[torch.Tensor] = None):
     """dw [E, C, P, P] += dtok [B*S, E]^T @ unfold(x): the patch-embedding weight gradient as ONE tcgen05 GEMM (bf16 operands).
     ``unf``: a precomputed ``patch_unfold_bf16(x, P)``."""

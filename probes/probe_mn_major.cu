@@ -12,6 +12,9 @@
 //      32-wide heads packed in one swizzled row), K = 32
 //   5: D[m,n] = sum_k A[m,k] B[k,32+n], n < 32   B MN-major with N = 32 (half a 64-element block) at +64 B
 //   6: D[m,n] = sum_k A[k,m] B[k,32+n], n < 32   A MN-major, B MN-major N = 32 at +64 B
+//   7: D[m,n] = sum_{k<112} A[m,k] B[k+1,n]     B MN-major with the start address shifted by ONE K row (+128 B): a window that
+//      slides over the rows of a tile (the implicit conv3x3 weight gradient reads its 3 horizontal taps this way)
+//   8: the same with a shift of 2 rows
 //   nvcc -gencode arch=compute_100a,code=sm_100a -O2 -I../include -o probe_mn_major.bin probe_mn_major.cu ../objcavit_b200/csrc/tc_gemm.cu ../objcavit_b200/csrc/api.cu
 #include "../objcavit_b200/csrc/tc_common.cuh"
 #include <vector>
@@ -24,7 +27,7 @@ constexpr int SLAB = 128 * 128;   // [128 rows x 64 bf16] = 16 KB
 __device__ __forceinline__ uint64_t desc_mn(uint32_t saddr, uint32_t lbo, uint32_t sbo) { return make_smem_desc(saddr, lbo, sbo, LAYOUT_SW128); }
 
 __global__ void __launch_bounds__(128, 1)
-probe_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmX, float* out /*[7][128][256]*/) {
+probe_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CUtensorMap tmX, float* out /*[9][128][256]*/) {
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base_u32 = smem_u32(smem_raw);
   uint8_t* smem = smem_raw + ((1024 - (base_u32 & 1023)) & 1023);
@@ -51,7 +54,7 @@ probe_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CU
   }
   mbar_wait(bar_load, 0);
   __syncthreads();
-  for (int c = 0; c < 7; ++c) {
+  for (int c = 0; c < 9; ++c) {
     if (threadIdx.x == 0) {
       tc_fence_after();
       const uint32_t p0 = smem_u32(sP), x0 = smem_u32(sX);
@@ -68,6 +71,7 @@ probe_kernel(const __grid_constant__ CUtensorMap tmP, const __grid_constant__ CU
                                         make_idesc_bf16(128, 128, 0, 0), kk != 0);
         if (c == 5) umma_bf16(tmem_d, a_k, desc_mn(x0 + 64 + kk * 2048, SLAB, 1024), make_idesc_bf16(128, 32, 0, 1), kk != 0);
         if (c == 6) umma_bf16(tmem_d, a_mn, desc_mn(x0 + 64 + kk * 2048, SLAB, 1024), make_idesc_bf16(128, 32, 1, 1), kk != 0);
+        if (c >= 7 && kk < 7) umma_bf16(tmem_d, a_k, desc_mn(x0 + (c - 6) * 128 + kk * 2048, SLAB, 1024), make_idesc_bf16(128, 128, 0, 1), kk != 0);
       }
       umma_commit(bar_mma);
     }
@@ -96,8 +100,8 @@ int main() {
   float* dO;
   cudaMalloc(&dP, hP.size() * 2);
   cudaMalloc(&dX, hX.size() * 2);
-  cudaMalloc(&dO, 7 * 128 * 256 * 4);
-  cudaMemset(dO, 0, 7 * 128 * 256 * 4);
+  cudaMalloc(&dO, 9 * 128 * 256 * 4);
+  cudaMemset(dO, 0, 9 * 128 * 256 * 4);
   cudaMemcpy(dP, hP.data(), hP.size() * 2, cudaMemcpyHostToDevice);
   cudaMemcpy(dX, hX.data(), hX.size() * 2, cudaMemcpyHostToDevice);
   CUtensorMap tmP, tmX;
@@ -108,22 +112,24 @@ int main() {
   probe_kernel<<<1, 128, smem>>>(tmP, tmX, dO);
   cudaError_t e = cudaDeviceSynchronize();
   if (e != cudaSuccess) { printf("CUDA error: %s\n", cudaGetErrorString(e)); return 1; }
-  std::vector<float> hO(7 * 128 * 256);
+  std::vector<float> hO(9 * 128 * 256);
   cudaMemcpy(hO.data(), dO, hO.size() * 4, cudaMemcpyDeviceToHost);
-  const char* names[7] = {"A K-major,  B MN-major, N=128", "A MN-major, B MN-major, N=128", "A K-major,  B MN-major, N=256",
-                          "A MN-major, B K-major,  N=128", "K-major +64 B, K=32", "B MN-major N=32 +64 B", "A MN, B MN N=32 +64 B"};
+  const char* names[9] = {"A K-major,  B MN-major, N=128", "A MN-major, B MN-major, N=128", "A K-major,  B MN-major, N=256",
+                          "A MN-major, B K-major,  N=128", "K-major +64 B, K=32", "B MN-major N=32 +64 B", "A MN, B MN N=32 +64 B",
+                          "B MN-major, K rows shifted by 1", "B MN-major, K rows shifted by 2"};
   int rc = 0;
-  for (int c = 0; c < 7; ++c) {
-    const int N = c == 2 ? 256 : (c >= 5 ? 32 : 128);
+  for (int c = 0; c < 9; ++c) {
+    const int N = c == 2 ? 256 : ((c == 5 || c == 6) ? 32 : 128);
     int bad = 0;
     for (int m = 0; m < 128; ++m)
       for (int n = 0; n < N; ++n) {
         float want = 0.f;
-        for (int k = 0; k < (c == 4 ? 32 : 128); ++k) {
+        for (int k = 0; k < (c == 4 ? 32 : (c >= 7 ? 112 : 128)); ++k) {
           float a = (c == 0 || c == 2 || c == 5) ? fP[m * 128 + k] : fP[k * 128 + m];
           float b = c == 3 ? fX[n * 256 + k] : fX[k * 256 + n];
           if (c == 4) { a = fP[m * 128 + 32 + k]; b = fX[n * 256 + 32 + k]; }
-          if (c >= 5) b = fX[k * 256 + 32 + n];
+          if (c == 5 || c == 6) b = fX[k * 256 + 32 + n];
+          if (c >= 7) { a = fP[m * 128 + k]; b = fX[(k + c - 6) * 256 + n]; }
           want += a * b;
         }
         if (want != hO[((size_t)c * 128 + m) * 256 + n]) ++bad;
