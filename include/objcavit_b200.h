@@ -438,6 +438,14 @@ int ocv_im2col3x3_bf16(const void* x_planar_bf16, void* col_bf16, int B, int C, 
  *     pitch ld (elements) >= B*S; columns >= B*S are left untouched (zero them once when ld is padded).
  *   ocv_transpose_cast_f32_bf16: dst[c][r] = bf16(src[r][c]) for any R, C (pitches in elements). */
 int ocv_patch_unfold_bf16(const float* x, void* out_bf16, int B, int C, int h, int w, int P, long long ld, void* stream);
+/* conv3x3 weight + bias gradient as an implicit GEMM over pixels (csrc/conv_wgrad_bf16.cu), no im2col buffer:
+ *   gw[co][ci][ky][kx] = beta*gw + sum_{b,y,x} dY[b,y,x,co] X[b,y+ky-1,x+kx-1,ci],  gb[co] = beta*gb + sum dY   (gb may be NULL)
+ * dyT_bf16: dY channel-major [128, ld_dy] bf16 (column = (b*h + y)*w + x; what ocv_tail_fused_bwd_bf16 writes), x_nhwc_bf16 [B,h,w,128],
+ * w % 8 == 0, workspace of ocv_conv3x3_wgrad_bf16_workspace bytes (256-byte aligned).  Deterministic (fixed-order partial sums).
+ * replaces autograd of nn.Conv2d(128,128,3,padding=1) w.r.t. its parameters: modules/ObjCAViT.py:374, modules/miniViT.py:25. */
+long long ocv_conv3x3_wgrad_bf16_workspace(int B, int h, int w);
+int ocv_conv3x3_wgrad_bf16(const void* dyT_bf16, long long ld_dy, const void* x_nhwc_bf16, float* gw, float* gb, int B, int h, int w,
+                           float beta, void* workspace, void* stream);
 /* the same operand from the NHWC bf16 copy of the features (xh [B,h,w,C], C % 32 == 0, 16-byte aligned): half the input bytes */
 int ocv_patch_unfold_nhwc_bf16(const void* xh_bf16, void* out_bf16, int B, int C, int h, int w, int P, long long ld, void* stream);
 int ocv_transpose_cast_f32_bf16(const float* src, void* dst_bf16, int R, int C, long long src_ld, long long dst_ld, void* stream);

@@ -98,6 +98,8 @@ PROTOTYPES = {
     "ocv_im2col3x3_bf16": (i32, [p, p, i32, i32, i32, i32, p]),
     "ocv_patch_unfold_bf16": (i32, [p, p, i32, i32, i32, i32, i32, i64, p]),
     "ocv_patch_unfold_nhwc_bf16": (i32, [p, p, i32, i32, i32, i32, i32, i64, p]),
+    "ocv_conv3x3_wgrad_bf16_workspace": (i64, [i32, i32, i32]),
+    "ocv_conv3x3_wgrad_bf16": (i32, [p, i64, p, p, p, i32, i32, i32, f32, p, p]),
     "ocv_transpose_cast_f32_bf16": (i32, [p, p, i32, i32, i64, i64, p]),
     "ocv_mha_core_dropout_f32": (i32, [p, p, p, p, p, i32, i32, i32, i32, i32, i64, i32, i64, i32, i64, i32, i64, i32, f32,
                                        C.c_ulonglong, p]),

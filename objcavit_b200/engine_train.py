@@ -676,6 +676,7 @@ def _pixel_prologue_rest(P: Params, pre: str, t, x: torch.Tensor) -> None:
     it after the patch embedding has been issued (ordered after it), so that these whole-GPU kernels (a persistent 148-CTA conv,
     0.5 ms of HBM-bound copies) run under the encoder chain instead of delaying the positional MLPs and the patch embedding."""
     xh = t.xh_keep if getattr(t, "xh_keep", None) is not None else t.xh
+    t.xh_saved = xh if IMPLICIT_DW3 else None            # the backward's conv3x3 weight gradient reads the features in this layout
     t.x3h = ops.conv3x3_nhwc_bf16(xh, ops.pack_conv3x3_bf16(P[pre + "conv3x3.weight"]), P[pre + "conv3x3.bias"])
     # the forward chain needs only x3h from this branch: it waits for THIS point, not for the backward operands made below
     t.x3_ready = None
@@ -694,6 +695,7 @@ def _pixel_prologue_rest(P: Params, pre: str, t, x: torch.Tensor) -> None:
 # split-K of the conv3x3 weight-gradient GEMM (9 output tiles x split CTAs, each holding an SM's whole register file for ~100 us):
 # with 32 the GEMM fills every SM twice over and the chain's small kernels queue behind it
 DW3_SPLIT = int(_os.environ.get("OCV_DW3_SPLIT", "32"))
+IMPLICIT_DW3 = _os.environ.get("OCV_IMPLICIT_DW3", "1") == "1"   # 0: conv3x3 weight gradient through an im2col buffer + GEMM (round 1)
 FUSED_TAIL = _os.environ.get("OCV_FUSED_TAIL", "1") == "1"   # 0: the round-1 path with materialised logits (kept as the general fallback)
 
 
@@ -793,13 +795,18 @@ def _pixel_bwd_bf16_rest(P: Params, G: Params, t, dlT, dtok: torch.Tensor, dMb=N
             for b in range(B):
                 ops.gemm_bf16(MbT16[b], dl[b], out=dx[:, b * Pn:(b + 1) * Pn])
             del dl
+        xh = getattr(t, "xh_saved", None)
+        if xh is not None and w % 8 == 0 and C == 128:
+            # implicit GEMM over pixels: dx (channel-major) and the NHWC features are both read as stored, no im2col buffer
+            ops.conv3x3_wgrad_bf16(dx, xh, gw, gb, beta=1.0)
+            return
         col = ops.im2col3x3_bf16(ops.cast_bf16(x))
         skw = max(1, min(DW3_SPLIT, (B * Pn) // 8192))
         ops.gemm_bf16(dx, col[:C * 9], residual=gw, out=gw, split_k=skw)
         db = ops.gemm_bf16(dx, col[C * 9:], split_k=skw)                      # [C,8]: column 0 = sum over pixels, the rest 0
         ops.reduce_channels(db, gb, 1, 1, C, 8, beta=1.0)
 
-    reads = [r for r in (dlT, Mb16, dx3T, x) if r is not None]
+    reads = [r for r in (dlT, Mb16, dx3T, x, getattr(t, "xh_saved", None)) if r is not None]
     on_side(conv_wgrad, *reads, name="conv3x3")       # its own queue: HBM-bound work the layer wgrads must not wait behind
 
 

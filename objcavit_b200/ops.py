@@ -1077,6 +1077,21 @@ def patch_unfold_bf16(x: torch.Tensor, P: int = 16) -> torch.Tensor:
     return unf
 
 
+def conv3x3_wgrad_bf16(dyT: torch.Tensor, xh: torch.Tensor, gw: torch.Tensor, gb: Optional[torch.Tensor], beta: float = 1.0) -> None:
+    """gw [128,128,3,3] (+ gb [128]) = beta * (.) + conv3x3 weight / bias gradient from dY channel-major ``dyT`` [128, >= B*h*w] bf16 and
+    the NHWC bf16 features ``xh`` [B,h,w,128]: implicit GEMM over pixels on tcgen05, no im2col (csrc/conv_wgrad_bf16.cu)."""
+    _chk(dyT, torch.bfloat16, "dyT"); _chk(xh, torch.bfloat16, "xh"); _chk(gw, torch.float32, "gw")
+    B, h, wd, Cc = xh.shape
+    assert Cc == 128 and xh.is_contiguous() and dyT.dim() == 2 and dyT.shape[0] == 128 and dyT.stride(1) == 1 and gw.is_contiguous()
+    assert gw.numel() == 128 * 128 * 9 and wd % 8 == 0
+    if gb is not None:
+        _chk(gb, torch.float32, "gb")
+        assert gb.is_contiguous() and gb.numel() == 128
+    ws = _workspace(_lib.lib().ocv_conv3x3_wgrad_bf16_workspace(B, h, wd), xh.device, "conv3x3_wgrad")
+    _call("ocv_conv3x3_wgrad_bf16", dyT.data_ptr(), dyT.stride(0), xh.data_ptr(), gw.data_ptr(), 0 if gb is None else gb.data_ptr(),
+          B, h, wd, float(beta), ws.data_ptr(), _stream())
+
+
 def patch_unfold_nhwc_bf16(xh: torch.Tensor, P: int = 16) -> torch.Tensor:
     """``patch_unfold_bf16`` from the NHWC bf16 copy of the features ``xh`` [B,h,w,C] (what the tensor-core path already holds)."""
     _chk(xh, torch.bfloat16, "xh")

@@ -147,6 +147,50 @@ def test_patch_embed_wgrad_bf16(cuda):
     assert rel_err(dw, ref) < 1e-2
 
 
+@pytest.mark.parametrize("B,C,h,w", [(2, 128, 48, 80), (1, 32, 208, 272), (3, 64, 40, 33)])
+def test_patch_unfold_from_nhwc_is_the_unfold_of_the_fp32_map(cuda, B, C, h, w):
+    """Both unfold kernels write the same operand (bit-equal: each element is one bf16 rounding of one input value); incl. a
+    partial last patch column / row (w = 33, h = 40) and several patch-row groups per image."""
+    torch.manual_seed(5)
+    x = torch.randn(B, C, h, w, device=cuda)
+    want = ops.patch_unfold_bf16(x[:, :, :h // 16 * 16, :w // 16 * 16].contiguous(), 16)
+    got = ops.patch_unfold_nhwc_bf16(ops.nchw_to_nhwc_bf16(x), 16)
+    assert got.shape == want.shape and torch.equal(got, want)
+    ref = torch.nn.functional.unfold(x, 16, stride=16).permute(1, 0, 2).reshape(C * 256, -1)          # [C*P*P, B*S]
+    assert torch.equal(got[:, :ref.shape[1]].float(), ref.bfloat16().float())
+
+
+@pytest.mark.parametrize("B,h,w,beta", [(2, 24, 64, 0.0), (3, 17, 40, 1.0), (1, 208, 272, 1.0), (2, 9, 8, 1.0)])
+def test_conv3x3_wgrad_implicit_gemm(cuda, B, h, w, beta):
+    """Weight + bias gradient of the 3x3 convolution as an implicit GEMM over pixels (no im2col): against fp64 autograd of
+    F.conv2d on the SAME bf16-rounded operands; strips that end inside a 64-pixel box (w = 40, 272, 8), all image borders, a
+    pitch larger than B*h*w, accumulate (beta = 1) and overwrite (beta = 0); twice for bit-identical results (fixed-order sums)."""
+    torch.manual_seed(11)
+    Cc = 128
+    x = (torch.randn(B, Cc, h, w, device=cuda) * 0.7).bfloat16()
+    dy = (torch.randn(B, Cc, h, w, device=cuda) * 0.5).bfloat16()
+    xh = x.permute(0, 2, 3, 1).contiguous()
+    n = B * h * w
+    ld = (n + 15) // 8 * 8
+    dyT = torch.full((Cc, ld), 7.0, device=cuda, dtype=torch.bfloat16)            # garbage beyond the last pixel must not be read as data
+    dyT[:, :n] = dy.permute(1, 0, 2, 3).reshape(Cc, n)
+    xd = x.double().requires_grad_(False)
+    wt = torch.zeros(Cc, Cc, 3, 3, device=cuda, dtype=torch.float64, requires_grad=True)
+    bs = torch.zeros(Cc, device=cuda, dtype=torch.float64, requires_grad=True)
+    torch.nn.functional.conv2d(xd, wt, bs, padding=1).backward(dy.double())
+    gw0 = torch.randn(Cc, Cc, 3, 3, device=cuda)
+    gb0 = torch.randn(Cc, device=cuda)
+    outs = []
+    for _ in range(2):
+        gw, gb = gw0.clone(), gb0.clone()
+        ops.conv3x3_wgrad_bf16(dyT[:, :n] if ld == n else dyT, xh, gw, gb, beta=beta)
+        outs.append((gw, gb))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    gw, gb = outs[0]
+    assert rel_err(gw, (beta * gw0.double() + wt.grad).float()) < 2e-5 * max(1.0, (n / 4096) ** 0.5)
+    assert rel_err(gb, (beta * gb0.double() + bs.grad).float()) < 2e-5 * max(1.0, (n / 4096) ** 0.5)
+
+
 def test_prefetcher_and_lagged_scalars(cuda):
     from objcavit_b200.prefetch import DevicePrefetcher, LaggedScalars
     host = [(torch.full((4, 3), float(i)).pin_memory(), [torch.full((2,), float(10 * i)).pin_memory(), None], {"k": i}) for i in range(5)]
