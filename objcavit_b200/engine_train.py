@@ -528,11 +528,15 @@ class Tape:
 
 
 def forward(P: Params, cfg: dict, x: torch.Tensor, object_features=None, object_xywh_list=None, mutate_inputs: bool = True,
-            patch_size: int = 16, n_query: int = 128, drop: DropCtx = NO_DROP, P16=None):
+            patch_size: int = 16, n_query: int = 128, drop: DropCtx = NO_DROP, P16=None, xh=None):
     """-> (depth_pred [B,1,h,w], bin_edges [B,K+1], tape).  ``cfg``: kind ('adabins' | 'graphbins'), strategy, no_obj_sa,
-    use_2_saca, min_depth, max_depth."""
+    use_2_saca, min_depth, max_depth.  ``xh``: the features already converted to NHWC bf16 [B,h,w,C] (tensor-core mode only: every
+    consumer of the features reads that copy, so ``x`` is then used for its shape alone and may be a storage-less placeholder —
+    ``features_nhwc_ok`` says when)."""
     t = Tape()
     t.cfg, t.x = cfg, x
+    assert xh is None or features_nhwc_ok(cfg, x.shape), "xh= needs the tensor-core path with every reader of x on the NHWC copy"
+    t.xh_given = xh
     # precision "bf16": the encoder layers' GEMMs run on tcgen05 with bf16 copies of the weights (P16: given by the trainer as views
     # of one bf16 mirror of its flat parameter buffer, else cast lazily here)
     if cfg.get("pixel") == "bf16" and TOKEN_BF16 and NATIVE_LAYER:
@@ -646,11 +650,19 @@ def _patch_embed(t, x: torch.Tensor, w: torch.Tensor, bias, pos, patch_size: int
             t.pixel_rest_pending = False
             t.xh_keep = t.xh
             late = fork_branch(x.device, 4)
-            with on_branch(x.device, late, x, t.xh, name="pixel"):
+            with on_branch(x.device, late, None if getattr(t, "xh_given", None) is not None else x, t.xh, name="pixel"):
                 _pixel_prologue_rest(t.late_P, t.late_pre, t, x)
         t.xh = None
         return tok
     return ops.patch_embed(x, w, bias, pos, patch_size)
+
+
+def features_nhwc_ok(cfg: dict, shape) -> bool:
+    """True when no kernel of the step reads the fp32 NCHW features except the layout conversion (so a caller may hand the NHWC
+    bf16 copy in as ``forward(..., xh=)``): tensor-core pixel + token path, unfold in the forward, implicit conv3x3 weight gradient."""
+    B, C, h, w = shape
+    return (cfg.get("pixel") == "bf16" and cfg.get("surface", "head") == "head" and UNFOLD_IN_FORWARD and IMPLICIT_DW3 and C == 128
+            and w % 8 == 0)
 
 
 def _pixel_prologue(P: Params, pre: str, t, x: torch.Tensor) -> None:
@@ -661,9 +673,10 @@ def _pixel_prologue(P: Params, pre: str, t, x: torch.Tensor) -> None:
     dev = x.device
     t.conv_fork = fork_branch(dev, 4)
     t.xh_ready = None
-    with on_branch(dev, t.conv_fork, x, name="pixel"):
-        t.xh = xh = ops.nchw_to_nhwc_bf16(x)
-        if t.conv_fork is not None:
+    given = getattr(t, "xh_given", None)
+    with on_branch(dev, t.conv_fork, None if given is not None else x, name="pixel"):
+        t.xh = xh = given if given is not None else ops.nchw_to_nhwc_bf16(x)
+        if t.conv_fork is not None and given is None:
             t.xh_ready = torch.cuda.Event()
             t.xh_ready.record(torch.cuda.current_stream(dev))
         t.pixel_rest_pending = PIXEL_LATE and t.conv_fork is not None

@@ -288,10 +288,13 @@ def tail(ram: torch.Tensor, w_out: torch.Tensor, b_out, centres: torch.Tensor):
 
 # ---- bf16 tensor-core path --------------------------------------------------------------------------
 
-def nchw_to_nhwc_bf16(x: torch.Tensor):
+def nchw_to_nhwc_bf16(x: torch.Tensor, out: Optional[torch.Tensor] = None):
     assert x.is_cuda and x.is_contiguous() and x.dtype in (torch.float32, torch.bfloat16)
     B, Cc, h, wd = x.shape
-    out = torch.empty(B, h, wd, Cc, device=x.device, dtype=torch.bfloat16)
+    if out is None:
+        out = torch.empty(B, h, wd, Cc, device=x.device, dtype=torch.bfloat16)
+    else:
+        assert out.shape == (B, h, wd, Cc) and out.dtype == torch.bfloat16 and out.is_contiguous() and out.device == x.device
     _call("ocv_nchw_to_nhwc_bf16", x.data_ptr(), out.data_ptr(), B, Cc, h, wd, int(x.dtype == torch.bfloat16), _stream())
     return out
 
@@ -1108,8 +1111,11 @@ def patch_unfold_nhwc_bf16(xh: torch.Tensor, P: int = 16) -> torch.Tensor:
 def patch_embed_wgrad_bf16(dtok: torch.Tensor, x: torch.Tensor, dw: torch.Tensor, P: int = 16, unf: Optional[torch.Tensor] = None):
     """dw [E, C, P, P] += dtok [B*S, E]^T @ unfold(x): the patch-embedding weight gradient as ONE tcgen05 GEMM (bf16 operands).
     ``unf``: a precomputed ``patch_unfold_bf16(x, P)``."""
-    _chk(dtok, torch.float32, "dtok"); _chk(x, torch.float32, "x"); _chk(dw, torch.float32, "dw")
-    assert dtok.is_contiguous() and x.is_contiguous() and dw.is_contiguous()
+    _chk(dtok, torch.float32, "dtok"); _chk(dw, torch.float32, "dw")
+    assert dtok.is_contiguous() and dw.is_contiguous()
+    if unf is None:                       # with a precomputed unfold, x gives the shape only (it may be a storage-less placeholder)
+        _chk(x, torch.float32, "x")
+        assert x.is_contiguous()
     B, Cc, h, wd = x.shape
     BS, E = dtok.shape
     assert BS == B * (h // P) * (wd // P) and dw.numel() == E * Cc * P * P

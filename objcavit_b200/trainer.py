@@ -121,16 +121,18 @@ class HeadTrainer:
             return P, G, self._P16
         return P, G, None
 
-    def forward_backward(self, features, object_features, object_xywh_list, depth_gt, depth_mask):
-        """Local forward + loss + backward; gradients accumulate into the flat buffer.  Returns the loss (device scalar)."""
+    def forward_backward(self, features, object_features, object_xywh_list, depth_gt, depth_mask, xh=None):
+        """Local forward + loss + backward; gradients accumulate into the flat buffer.  Returns the loss (device scalar).
+        ``xh``: the features already in NHWC bf16 (graph mode converts the caller's tensor straight into its static buffer);
+        ``features`` is then a shape placeholder."""
         P, G, P16 = self._maps()
         if P16 is not None:
             ops.cast_bf16(self.flat_params, out=self.flat16)
-        x = features.contiguous().float()
+        x = features if xh is not None else features.contiguous().float()
         p_drop = float(self.head.dropout) if self.head.training else 0.0      # encoder-layer dropout, as the reference in train()
         drop = engine_train.DropCtx(p_drop, draw_dropout_seed() if p_drop > 0 else 0)
         gt = depth_gt.contiguous().float()                # before the forward: the chamfer branch below forks inside it
-        depth, edges, tape = engine_train.forward(P, self.cfg, x, object_features, object_xywh_list, drop=drop, P16=P16)
+        depth, edges, tape = engine_train.forward(P, self.cfg, x, object_features, object_xywh_list, drop=drop, P16=P16, xh=xh)
         # the chamfer loss needs only the bin edges (ready before the pixel path of the forward) and the ground truth: it runs on a
         # branch stream from that point, next to the pixel forward; SILog (needs the depth map) stays on the launching stream
         dev, fork = depth.device, getattr(tape, "edges_ready", None)
@@ -204,9 +206,19 @@ class HeadTrainer:
         entry = self._graphs.get(sig)
         dev = self.flat_params.device
         if entry is None:
-            st = {"x": torch.empty(features.shape, device=dev, dtype=torch.float32),
+            # tensor-core mode: the layout conversion NCHW fp32 -> NHWC bf16 is the only reader of the caller's features, so it runs
+            # eagerly from the caller's tensor into a static bf16 buffer right before the replay — no 232 MB device-to-device copy
+            # into a static fp32 buffer, and the captured step starts from the converted map ("x" is a storage-less shape carrier)
+            nhwc = engine_train.features_nhwc_ok(self.cfg, features.shape) and features.dtype in (torch.float32, torch.bfloat16)
+            if nhwc:
+                Bf, Cf, hf, wf = features.shape
+                st = {"x": torch.empty(1, device=dev, dtype=torch.float32).as_strided(tuple(features.shape), (0, 0, 0, 0)),
+                      "xh": torch.empty(Bf, hf, wf, Cf, device=dev, dtype=torch.bfloat16)}
+            else:
+                st = {"x": torch.empty(features.shape, device=dev, dtype=torch.float32)}
+            st.update({
                   "gt": torch.empty(depth_gt.shape, device=dev, dtype=torch.float32),
-                  "mask": torch.empty(depth_mask.shape, device=dev, dtype=depth_mask.dtype)}
+                  "mask": torch.empty(depth_mask.shape, device=dev, dtype=depth_mask.dtype)})
             if object_features is not None:
                 counts = [int(o.shape[0]) for o in object_features]
                 st["feats"] = torch.empty(sum(counts), object_features[0].shape[1], device=dev, dtype=torch.float32)
@@ -231,7 +243,8 @@ class HeadTrainer:
                     self._salt.add_(-7046029254386353131)       # 0x9E3779B97F4A7C15 as int64: a new mask stream per replay
                     self.grads.zero()
                     l1, l2 = self.forward_backward(st["x"], None if object_features is None else list(st["obj_views"]),
-                                                   None if object_features is None else list(st["box_views"]), st["gt"], st["mask"])
+                                                   None if object_features is None else list(st["box_views"]), st["gt"], st["mask"],
+                                                   xh=st.get("xh"))
             finally:
                 engine.offsets_capture_refs = None
             st["_offset_refs"] = refs
@@ -249,7 +262,9 @@ class HeadTrainer:
 
     @staticmethod
     def _load_static(st, features, object_features, object_xywh_list, depth_gt, depth_mask) -> None:
-        if features.data_ptr() != st["x"].data_ptr():
+        if "xh" in st:
+            ops.nchw_to_nhwc_bf16(features.contiguous(), out=st["xh"])
+        elif features.data_ptr() != st["x"].data_ptr():
             st["x"].copy_(features, non_blocking=True)
         st["gt"].copy_(depth_gt, non_blocking=True)
         st["mask"].copy_(depth_mask, non_blocking=True)
