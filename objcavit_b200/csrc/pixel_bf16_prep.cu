@@ -109,6 +109,37 @@ __global__ void fold_queries_kernel(const float* __restrict__ Wout, const float*
   }
 }
 
+// fast path of the layout conversion: fp32 [B,128,P] -> bf16 [B,P,128] over tiles of 64 flat pixels (P % 64 == 0, 16-byte aligned):
+// 8 independent 16-byte loads per thread (4 pixels of one channel), bf16 tile in shared memory (row pitch 272 B), 256 contiguous
+// bytes per pixel out as 16-byte stores.
+constexpr int CV_TP = 64, CV_PITCH = 136;   // bf16 elements per tile row (128 + 8: 16-byte aligned rows, conflict-light columns)
+__global__ void __launch_bounds__(256)
+nchw_to_nhwc_c128_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long P) {
+  __shared__ __align__(16) __nv_bfloat16 tile[CV_TP * CV_PITCH];
+  const int b = blockIdx.y;
+  const long long p0 = (long long)blockIdx.x * CV_TP;
+  const float* s = src + (long long)b * 128 * P + p0;
+  const int t = threadIdx.x, q = t & 15, c0 = t >> 4;      // q: group of 4 pixels, c0 + 16 j: channel
+  float4 v[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) v[j] = __ldcs(reinterpret_cast<const float4*>(s + (long long)(c0 + 16 * j) * P) + q);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = c0 + 16 * j;
+    tile[(4 * q + 0) * CV_PITCH + c] = __float2bfloat16(v[j].x);
+    tile[(4 * q + 1) * CV_PITCH + c] = __float2bfloat16(v[j].y);
+    tile[(4 * q + 2) * CV_PITCH + c] = __float2bfloat16(v[j].z);
+    tile[(4 * q + 3) * CV_PITCH + c] = __float2bfloat16(v[j].w);
+  }
+  __syncthreads();
+  uint4* d = reinterpret_cast<uint4*>(dst + ((long long)b * P + p0) * 128);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int idx = k * 256 + t, px = idx >> 4, part = idx & 15;
+    d[idx] = *reinterpret_cast<const uint4*>(tile + px * CV_PITCH + part * 8);
+  }
+}
+
 }  // namespace
 
 extern "C" int ocv_nchw_to_nhwc_bf16(const void* src, void* dst_bf16, int B, int C, int h, int w, int src_is_bf16,
@@ -116,6 +147,13 @@ extern "C" int ocv_nchw_to_nhwc_bf16(const void* src, void* dst_bf16, int B, int
   OCV_CHECK_ARG(src && dst_bf16 && B > 0 && h > 0 && w > 0);
   OCV_CHECK_SHAPE(C > 0 && C % 2 == 0 && C <= 256 && B <= 65535 && h <= 65535);
   if (int s = ocv_require_sm100()) return s;
+  const long long Pn = (long long)h * w;
+  if (!src_is_bf16 && C == 128 && Pn % CV_TP == 0 && Pn / CV_TP < (1ll << 31) &&
+      ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst_bf16)) & 15) == 0) {
+    nchw_to_nhwc_c128_kernel<<<dim3((unsigned)(Pn / CV_TP), B), 256, 0, ocv_stream(stream)>>>(
+        static_cast<const float*>(src), static_cast<__nv_bfloat16*>(dst_bf16), Pn);
+    return ocv_launch_status();
+  }
   dim3 grid(ceil_div(w, 32), h, B), block(32, 8);
   const size_t smem = 32 * (C + 1) * sizeof(float);
   if (src_is_bf16)

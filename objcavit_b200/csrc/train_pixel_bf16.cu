@@ -438,13 +438,29 @@ patch_unfold_nhwc_kernel(const __nv_bfloat16* __restrict__ xh, __nv_bfloat16* __
   const int tstride = Pp * 16 + 1;
   // load: one 16-byte piece (8 channels) per thread and step
   const int npix = rows * gw * Pp;      // pixels of the group's rows that belong to whole patches
-  for (int i = threadIdx.x; i < npix * 4; i += 256) {
-    const int pix = i >> 2, part = i & 3;
-    const int r = pix / (gw * Pp), xx = pix - r * gw * Pp;
-    const int sx = xx / Pp, px = xx - sx * Pp;
-    const uint4 v = *reinterpret_cast<const uint4*>(xh + (((long long)b * h + (long long)(sy0 + r) * Pp + py) * w + xx) * C + c0 + part * 8);
-    uint32_t* d = utile + (r * gw + sx) * tstride + px * 16 + part * 4;
-    d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
+  const int n16 = npix * 4;
+  for (int i0 = threadIdx.x; i0 < n16; i0 += 256 * 8) {    // 8 independent 16-byte loads in flight per thread
+    uint4 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = i0 + u * 256;
+      if (i < n16) {
+        const int pix = i >> 2, part = i & 3;
+        const int r = pix / (gw * Pp), xx = pix - r * gw * Pp;
+        v[u] = __ldcs(reinterpret_cast<const uint4*>(xh + (((long long)b * h + (long long)(sy0 + r) * Pp + py) * w + xx) * C + c0 + part * 8));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = i0 + u * 256;
+      if (i < n16) {
+        const int pix = i >> 2, part = i & 3;
+        const int r = pix / (gw * Pp), xx = pix - r * gw * Pp;
+        const int sx = xx / Pp, px = xx - sx * Pp;
+        uint32_t* d = utile + (r * gw + sx) * tstride + px * 16 + part * 4;
+        d[0] = v[u].x; d[1] = v[u].y; d[2] = v[u].z; d[3] = v[u].w;
+      }
+    }
   }
   __syncthreads();
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;

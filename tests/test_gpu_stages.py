@@ -201,6 +201,9 @@ def test_layout_and_weight_packing(cuda):
     assert torch.equal(got.cpu(), x.permute(0, 2, 3, 1).contiguous().bfloat16())
     got = ops.nchw_to_nhwc_bf16(x.bfloat16().to(cuda))
     assert torch.equal(got.cpu(), x.bfloat16().permute(0, 2, 3, 1).contiguous())
+    xb = torch.randn(3, 128, 24, 40, generator=g(5))               # h*w % 64 == 0, fp32, 128 channels: the tiled fast path
+    got = ops.nchw_to_nhwc_bf16(xb.to(cuda))
+    assert torch.equal(got.cpu(), xb.permute(0, 2, 3, 1).contiguous().bfloat16())
     w = torch.randn(128, 128, 3, 3, generator=g(2))
     assert torch.equal(ops.pack_conv3x3_bf16(w.to(cuda)).cpu(), w.permute(2, 3, 0, 1).reshape(9, 128, 128).bfloat16())
     wout = torch.randn(256, 128, 1, 1, generator=g(3)); bout = torch.randn(256, generator=g(4))
