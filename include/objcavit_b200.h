@@ -30,6 +30,7 @@ extern "C" {
 #define OCV_E_ALIGN (-3)    /* pointer or stride alignment                  */
 #define OCV_E_ARCH (-4)     /* device is not sm_100                         */
 #define OCV_E_DRIVER (-5)   /* driver entry point (tensor map encode) unavailable */
+#define OCV_E_CAPACITY (-6) /* larger than the fixed scratch built into a *_noalloc_* entry point */
 
 /* activation codes for ocv_linear_f32 */
 #define OCV_ACT_NONE 0
@@ -297,6 +298,25 @@ int ocv_layernorm_bwd_dropout_f32(const float* dy, const float* z, const float* 
  * row statistics into `workspace`), then this on the same dy / z / workspace — possibly on another stream, ordered after it. */
 int ocv_layernorm_bwd_params_f32(const float* dy, const float* z, float* dgamma, float* dbeta, int rows, int E, float beta,
                                  void* workspace, void* stream);
+/* ocv_layernorm_bwd_f32 for hosts that may not allocate device memory.  (No counterpart in the reference: there torch's caching
+ * allocator provides every temporary.  This exists for the integration cases listed below, nothing in the package calls it.)
+ *   Who needs it: code that receives its input and output buffers from someone else and has no way to obtain more — an operator
+ *   plugin inside an inference runtime whose memory plan is fixed when the engine is built, a callback entered while the host
+ *   framework holds its allocator lock, a control loop whose rules ban cudaMalloc once it is running (cudaMalloc synchronises the
+ *   device and can fail at an arbitrary later time).  Such a caller cannot produce the `workspace` argument of
+ *   ocv_layernorm_bwd_f32, so this variant takes none: the rows*2 + 32*E floats of scratch come from an array compiled into the
+ *   library.  The entry point calls no cudaMalloc / cudaFree and no library routine that allocates.
+ *   Cost and limit: the array holds OCV_LN_BWD_NOALLOC_MAX_ROWS rows at E <= 512 = 192 KB, resident on every GPU that loads the
+ *   library until the process ends.  rows > OCV_LN_BWD_NOALLOC_MAX_ROWS returns OCV_E_CAPACITY and launches nothing.
+ *   First call: the first call on each device (with that device current) looks up the array's device address; make that call
+ *   during set-up, before any stream capture begins on that device.
+ *   Sharing: all calls on one device use the same array, and it keeps whatever the previous call left in it.  No part of it needs
+ *   zeroing (every slot is written before it is read within a call), but calls that overlap on the GPU — two streams, two
+ *   threads — race on it and give wrong gradients.  Serialise them (one stream, or events).
+ *   Arguments, shapes and results are those of ocv_layernorm_bwd_f32 (bit-identical output). */
+#define OCV_LN_BWD_NOALLOC_MAX_ROWS 16384
+int ocv_layernorm_bwd_noalloc_f32(const float* dy, const float* z, const float* gamma, float* dz, float* dgamma, float* dbeta,
+                                  int rows, int E, float beta, void* stream);
 /* Backward of ocv_mha_core_f32 (same view conventions; `out` = its forward result): dq, dk, dv.  workspace B*heads*Sq*3 floats. */
 int ocv_mha_core_bwd_f32(const float* q, const float* k, const float* v, const float* out, const float* dout,
                          const uint8_t* key_padding_mask, float* dq, float* dk, float* dv, int B, int Sq, int Sk, int heads, int d,

@@ -66,6 +66,7 @@ PROTOTYPES = {
     "ocv_reduce_channels_f32": (i32, [p, p, i32, i32, i32, i64, f32, p]),
     "ocv_act_bwd_f32": (i32, [p, p, p, i64, i32, p]),
     "ocv_layernorm_bwd_f32": (i32, [p, p, p, p, p, p, i32, i32, f32, p, p]),
+    "ocv_layernorm_bwd_noalloc_f32": (i32, [p, p, p, p, p, p, i32, i32, f32, p]),
     "ocv_layernorm_bwd_params_f32": (i32, [p, p, p, p, i32, i32, f32, p, p]),
     "ocv_layernorm_bwd_dropout_f32": (i32, [p, p, p, p, p, i32, i32, f32, C.c_ulonglong, p, p]),
     "ocv_mha_core_bwd_f32": (i32, [p, p, p, p, p, p, p, p, p, i32, i32, i32, i32, i32, i64, i32, i64, i32, i64, i32, i64, i32,

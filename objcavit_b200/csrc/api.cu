@@ -53,6 +53,7 @@ extern "C" const char* ocv_status_string(int status) {
     case OCV_E_ALIGN: return "misaligned pointer or stride";
     case OCV_E_ARCH: return "device is not sm_100 (no fallback path exists)";
     case OCV_E_DRIVER: return "CUDA driver entry point unavailable";
+    case OCV_E_CAPACITY: return "size exceeds the fixed capacity built into a no-allocation entry point";
     default: return status > 0 ? cudaGetErrorString((cudaError_t)status) : "unknown status";
   }
 }

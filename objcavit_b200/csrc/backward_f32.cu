@@ -5,6 +5,7 @@
 // the flat gradient buffer.  Contract: include/objcavit_b200.h.
 #include "common.cuh"
 #include <math.h>
+#include <mutex>
 
 namespace {
 
@@ -641,4 +642,74 @@ extern "C" int ocv_bins_bwd_ex_f32(const float* y_raw, const float* grad_edges, 
 extern "C" int ocv_bins_bwd_f32(const float* y_raw, const float* grad_edges, const float* grad_centres, float* grad_y, int B, int K,
                                 float min_depth, float max_depth, void* stream) {
   return ocv_bins_bwd_ex_f32(y_raw, grad_edges, grad_centres, nullptr, grad_y, B, K, min_depth, max_depth, stream);
+}
+
+// ---- LayerNorm backward for callers that have no device memory to lend ------------------------------------------------------
+// ocv_layernorm_bwd_f32 needs rows*2 + 32*E floats of scratch (per-row mean / rstd, then the fixed-order partial sums of dgamma and
+// dbeta) and expects the caller to bring it.  Some hosts cannot: a plugin that is handed its input and output buffers by a runtime
+// whose memory plan was frozen at load time, a callback that runs while the owning framework holds its allocator lock, a real-time
+// loop whose policy forbids cudaMalloc after start-up (it synchronises the whole device and may fail late).  For them the scratch
+// lives inside the library image: a file-scope device array of fixed size.  Every device that loads the library carries these
+// OCV_LN_BWD_NOALLOC_MAX_ROWS*2 + 32*512 floats (192 KB) until the process exits, whether or not the entry point is ever called.
+//
+// `g_ln_bwd_scratch` below is two things.  In device code it is the array.  In host code the same identifier is only a handle the
+// runtime uses to look the array up: it is NOT a device address, and a kernel given `g_ln_bwd_scratch` from the host side would
+// fault (or, on a system where the GPU can reach host memory, quietly scribble over the wrong bytes).  So the host asks the runtime
+// for the real address once per device, with that device current, and hands the kernels that.
+namespace {
+
+constexpr int LN_NOALLOC_MAX_E = 512;                                           // the kernels' own limit
+constexpr long long LN_NOALLOC_FLOATS = 2ll * OCV_LN_BWD_NOALLOC_MAX_ROWS + 32ll * LN_NOALLOC_MAX_E;
+static __device__ __align__(256) float g_ln_bwd_scratch[LN_NOALLOC_FLOATS];
+
+constexpr int LN_NOALLOC_MAX_DEVICES = 64;
+std::mutex g_ln_scratch_mu;
+float* g_ln_scratch_addr[LN_NOALLOC_MAX_DEVICES] = {};   // device address of g_ln_bwd_scratch on device i, once resolved
+
+// Device address of the scratch array on the CURRENT device; resolved on the first call per device (this is what may load the
+// module on that device, hence "first call before any stream capture").  Returns a status, never allocates.
+int ln_noalloc_scratch(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= LN_NOALLOC_MAX_DEVICES) return OCV_E_CAPACITY;
+  std::lock_guard<std::mutex> lock(g_ln_scratch_mu);
+  if (!g_ln_scratch_addr[dev]) {
+    float* ptr = nullptr;
+    e = cudaGetSymbolAddress((void**)&ptr, g_ln_bwd_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (!ptr) return OCV_E_DRIVER;
+    g_ln_scratch_addr[dev] = ptr;
+  }
+  *out = g_ln_scratch_addr[dev];
+  return OCV_OK;
+}
+
+}  // namespace
+
+// Same arithmetic, same kernels, same launch shapes as ocv_layernorm_bwd_f32 — only the scratch pointer differs, so the results
+// are bit-identical to it.  Nothing in the scratch has to start at zero: the row kernel writes every (mean, rstd) pair and the
+// partial-sum kernel writes every [LNG][2][E] slot before the final kernel reads them, so stale contents of an earlier call are
+// overwritten, never accumulated into.  What the shared array does NOT give is isolation: two calls in flight at once on one device
+// (different streams, or different host threads) write the same floats and corrupt each other — order them.
+extern "C" int ocv_layernorm_bwd_noalloc_f32(const float* dy, const float* z, const float* gamma, float* dz, float* dgamma,
+                                             float* dbeta, int rows, int E, float beta, void* stream) {
+  OCV_CHECK_ARG(dy && z && gamma && dz && rows > 0);
+  OCV_CHECK_SHAPE(E > 0 && E % 32 == 0 && E <= LN_NOALLOC_MAX_E);
+  OCV_CHECK_ARG((dgamma == nullptr) == (dbeta == nullptr));
+  if (rows > OCV_LN_BWD_NOALLOC_MAX_ROWS) return OCV_E_CAPACITY;   // would run past the built-in array: refuse, do not truncate
+  if (int s = ocv_require_sm100()) return s;
+  float* stats = nullptr;
+  if (int s = ln_noalloc_scratch(&stats)) return s;
+  layernorm_bwd_rows_kernel<<<ceil_div(rows, 8), 256, 0, ocv_stream(stream)>>>(dy, z, gamma, dz, stats, rows, E, nullptr, 0u, 1.f, 0ull,
+                                                                               nullptr);
+  if (int s = ocv_launch_status()) return s;
+  if (dgamma) {
+    float* part = stats + 2 * (long long)rows;
+    layernorm_bwd_params_kernel<<<dim3(ceil_div(E, 32), LNG), dim3(32, 8), 0, ocv_stream(stream)>>>(dy, z, stats, part, rows, E);
+    if (int s = ocv_launch_status()) return s;
+    layernorm_bwd_params_final_kernel<<<ceil_div(E, 128), 128, 0, ocv_stream(stream)>>>(part, dgamma, dbeta, E, beta);
+    return ocv_launch_status();
+  }
+  return OCV_OK;
 }
