@@ -20,6 +20,8 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",
          "-I", INCLUDE]
+# measurement builds only, e.g. OCV_NVCC_EXTRA=-DOCV_PROBES python -m objcavit_b200.build -f  (see probes/time_pixel_dbg.py)
+FLAGS += os.environ.get("OCV_NVCC_EXTRA", "").split()
 
 
 def sources():

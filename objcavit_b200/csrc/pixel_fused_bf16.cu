@@ -937,7 +937,9 @@ static int pixel_launch(const void* X, const void* W3p, const void* Mb, const fl
   p.conv_out = static_cast<__nv_bfloat16*>(conv_out); p.conv_bias = conv_bias;
   p.B = B; p.h = h; p.w = w;
   p.th = th;
+#ifdef OCV_PROBES   // measurement build only (probes/time_pixel_dbg.py): with a knob set the results are wrong on purpose
   if (const char* e = getenv("OCV_PIXEL_DEBUG")) p.debug = atoi(e);
+#endif
   p.tiles_x = transposed ? ceil_div(w, TWT) : ceil_div(w, PW);
   p.tiles_y = transposed ? ceil_div(h, th) : ceil_div(h, TH);
   const long long nt = (long long)p.tiles_x * p.tiles_y * B;
@@ -946,7 +948,10 @@ static int pixel_launch(const void* X, const void* W3p, const void* Mb, const fl
   int grid = n_sm;
   if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
   if (grid > p.n_tiles) grid = p.n_tiles;
+#ifdef OCV_PROBES
   if (transposed && (p.debug & 8)) {   // measurement aid: synchronous launch + wait breakdown of the MMA issuer on stderr
+    if (argmax) return OCV_E_ARG;      // the timing instantiation has no argmax output
+    if (grid > 148) grid = 148;        // one 16-counter row per CTA in the fixed buffer below
     static long long* dbg = nullptr;
     if (!dbg) cudaMalloc(&dbg, 148 * 16 * sizeof(long long));
     cudaMemset(dbg, 0, 148 * 16 * sizeof(long long));
@@ -964,6 +969,7 @@ static int pixel_launch(const void* X, const void* W3p, const void* Mb, const fl
             acc[2] / acc[7], acc[3] / acc[7], acc[4] / acc[7], acc[5] / acc[7]);
     return st;
   }
+#endif
   if (transposed) {
     if (argmax) return ocv_launch_pdl(pixel_fused_t_kernel<1>, dim3(grid), dim3(THREADS), SMEM_T_BYTES, stream, tmX, tmW, tmMb, p);
     return ocv_launch_pdl(pixel_fused_t_kernel<0>, dim3(grid), dim3(THREADS), SMEM_T_BYTES, stream, tmX, tmW, tmMb, p);

@@ -1214,7 +1214,8 @@ def encoder_layer_bwd_train(W, G, x, qkv, att, y, x1, h, y2, mask, dout: torch.T
           x1.data_ptr(), h.data_ptr(), y2.data_ptr(), _ptr(mask), d.data_ptr(), dx.data_ptr(), B, S, F_, float(drop_p), sd,
           ws.data_ptr(), _stream(), None if side_stream is None else side_stream.cuda_stream, launches=29)
     if side_stream is not None:
-        for t in (ws, x, att, x1, h):
+        # the LayerNorm-parameter sums on the side stream read dout / y2 / y as well (the caller frees dout right after this call)
+        for t in (ws, x, att, x1, h, d, y2, y):
             t.record_stream(side_stream)
     return dx.view(B, S, E)
 
@@ -1295,6 +1296,7 @@ def encoder_layer_bwd_train_bf16(W, W16, G, saved, mask, dout: torch.Tensor, dro
           d.data_ptr(), dx.data_ptr(), B, S, F_, float(drop_p), sd, ws.data_ptr(), _stream(),
           None if side_stream is None else side_stream.cuda_stream, launches=30)
     if side_stream is not None:
-        for t in (ws, x16, att16, x1_16, h16):
+        # the LayerNorm-parameter sums on the side queues read dout / y2 / y as well (the caller frees dout right after this call)
+        for t in (ws, x16, att16, x1_16, h16, d, y2, y):
             t.record_stream(side_stream)
     return dx.view(B, S, E)

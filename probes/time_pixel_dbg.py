@@ -1,5 +1,8 @@
 """Probe: where does the transposed pixel kernel's time go?  Runs ocv_pixel_fused_bf16 at the bench shape with the
-measurement knobs of OCV_PIXEL_DEBUG (results are wrong with any knob set; only the time matters)."""
+measurement knobs of OCV_PIXEL_DEBUG (results are wrong with any knob set; only the time matters).
+
+The shipped library ignores OCV_PIXEL_DEBUG: build a measurement library first with
+``OCV_NVCC_EXTRA=-DOCV_PROBES python -m objcavit_b200.build -f`` (and rebuild without it afterwards)."""
 import os, sys, torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from objcavit_b200 import ops
