@@ -19,6 +19,7 @@
 // kernel (deterministic), which also scatters them into the [co][ci][ky][kx] weight layout.
 // Contract: include/objcavit_b200.h.
 #include "tc_common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -215,12 +216,22 @@ extern "C" int ocv_conv3x3_wgrad_bf16(const void* dyT_bf16, long long ld_dy, con
   OCV_CHECK_ALIGN(((reinterpret_cast<uintptr_t>(dyT_bf16) | reinterpret_cast<uintptr_t>(x_nhwc_bf16)) & 15) == 0 &&
                   (reinterpret_cast<uintptr_t>(workspace) & 255) == 0);
   if (int s = ocv_require_sm100()) return s;
-  // strip width: the multiple of 16 (<= 64) that covers the image row with the fewest K-steps
+  // strip width: a multiple of 16 (<= 64).  Every strip costs a fixed stage (a 64-pixel dY box + two haloed feature planes through
+  // TMA and one mbarrier round trip) whatever its width, every 16 pixels one K-step (4 MMAs).  Measured on the B200 at 8x208x272
+  // (profiles/wgrad_sw_r03.txt): 16 -> 188 us, 32 -> 136, 48 -> 128, 64 -> 129, i.e. about 7 units per strip against 4 per K-step;
+  // the earlier "fewest K-steps" rule chose 16 there.  Ties go to the wider strip.
   int sw = 64, best = -1;
   for (int cand = 64; cand >= 16; cand -= 16) {
-    const int steps = ceil_div(w, cand) * (cand / 16);
-    if (best < 0 || steps < best) { best = steps; sw = cand; }
+    const int strips = ceil_div(w, cand);
+    const int cost = 7 * strips + 4 * strips * (cand / 16);
+    if (best < 0 || cost < best) { best = cost; sw = cand; }
   }
+#ifdef OCV_PROBES   // measurement build only (probes/time_conv_wgrad.py): force a strip width
+  if (const char* e = getenv("OCV_WGRAD_SW")) {
+    const int v = atoi(e);
+    if (v == 16 || v == 32 || v == 48 || v == 64) sw = v;
+  }
+#endif
   CUtensorMap tmD, tmX;
   {
     EncodeTiledFn enc = get_encode_tiled();

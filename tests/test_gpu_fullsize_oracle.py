@@ -31,6 +31,7 @@ pytestmark = pytest.mark.gpu
 
 FP32_TOL = 1e-4          # north star, fp32 path
 BF16_TOL = 2e-2          # north star, bf16 path
+PIXEL_MAX_FACTOR = 2.0   # the single worst pixel of a batch may be at most this many tolerances off in per-pixel relative terms
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 # BASELINE.json configs[0..3] at their own batch sizes
@@ -114,6 +115,14 @@ def test_baseline_configs_against_the_oracle(cuda, label, name, B, h, w, n_obj):
         per = ((got_d - want_d).abs().flatten(1).max(1).values / want_d.abs().flatten(1).max(1).values)
         res[prec]["worst_image_rel_err"] = float(per.max())
         assert float(per.max()) < tol
+        # per-PIXEL relative error |got - want| / |want| (the max-norm figure above forgives a large error on a near pixel when a far
+        # pixel sets the scale): median, 99th percentile and maximum over every pixel of the batch, bounded by the same tolerance
+        pix = ((got_d - want_d).abs() / want_d.abs().clamp_min(1e-6)).flatten().double()
+        q = torch.quantile(pix[:: max(1, pix.numel() // 4_000_000)], torch.tensor([0.5, 0.99], dtype=torch.float64))
+        res[prec]["pixel_rel_err"] = {"p50": float(q[0]), "p99": float(q[1]), "max": float(pix.max()),
+                                      "depth_min": float(want_d.min()), "depth_max": float(want_d.max())}
+        assert float(q[1]) < tol, f"{label} {prec}: per-pixel relative depth error p99 {float(q[1]):.3e} (tolerance {tol})"
+        assert float(pix.max()) < PIXEL_MAX_FACTOR * tol, f"{label} {prec}: per-pixel relative depth error max {float(pix.max()):.3e}"
         del head
     _record(label, res)
     print(label, json.dumps(res))
@@ -133,8 +142,11 @@ def test_bin_argmax_against_the_oracle_logits(cuda, label, name, B, h, w, n_obj)
     ``conv_out(range_attention_maps)`` computed on the CPU in fp32.  Under quirk F5 all 128 range-attention channels of the
     ObjCAViT heads are identical, so a pixel's 256 logits are ``a_k * r + b_k`` for ONE scalar r: wherever two of those lines
     cross, the two best bins tie and ANY rounding (bf16 operands: 2^-8 relative) flips the decision.  Both numbers are therefore
-    asserted: the overall agreement that is actually reached (floor from the measured value), and >= 99.9 % on the pixels whose
-    oracle top-2 margin exceeds the bf16 logit error bound."""
+    asserted: the overall agreement that is actually reached (the headline; floor from the measured value), and >= 99.9 % on the
+    pixels whose oracle top-2 margin exceeds 2^-7 of the logit scale (two bf16 roundings) — the tight bound, which keeps 69-85 % of
+    the image; the looser 2e-2 split is recorded only.  (Rescaling ``conv_out`` does not move those fractions: measured on the
+    oracle, x1..x16 on the weight and log-uniform row norms up to x256 leave 2^-7-decisive at 0.47-0.76 for the ObjCAViT heads —
+    under F5 the two best bins for r > 0 are the two largest slopes, whose gap does not grow with the scale.  DESIGN.md §7.)"""
     args, sd, feats, objs, boxes = _inputs(name, B, h, w, n_obj, seed=777, weight_seed=5)
     cfg = case_cfg({}, args)
     _, _, ram = _oracle(sd, cfg, feats, objs, boxes, want_ram=True)
@@ -161,14 +173,22 @@ def test_bin_argmax_against_the_oracle_logits(cuda, label, name, B, h, w, n_obj)
     on_decisive = float(agree[decisive].float().mean()) if frac_decisive > 0 else 1.0
     # the same split with the tighter bound 2^-7 (two bf16 roundings) for the record
     tight = margin > (2.0 ** -7) * scale
-    res = {"images": B, "overall_agreement": overall, "decisive_fraction": frac_decisive, "decisive_agreement": on_decisive,
-           "decisive_fraction_2^-7": float(tight.float().mean()),
-           "decisive_agreement_2^-7": float(agree[tight].float().mean()) if bool(tight.any()) else 1.0,
+    frac_tight = float(tight.float().mean())
+    on_tight = float(agree[tight].float().mean()) if bool(tight.any()) else 1.0
+    # where the decisions differ, how far apart are the two bins?  (a tie between neighbours moves the depth by one bin width)
+    differ = ~agree
+    bin_dist = (amax16.cpu().long() - amax_ref).abs()[differ].float()
+    res = {"images": B, "headline_overall_agreement": overall, "overall_agreement": overall,
+           "decisive_fraction_2^-7": frac_tight, "decisive_agreement_2^-7": on_tight,
+           "decisive_fraction": frac_decisive, "decisive_agreement": on_decisive,
+           "disagreeing_pixels_oracle_margin_max_over_scale": float((margin[differ] / scale).max()) if bool(differ.any()) else 0.0,
+           "disagreeing_pixels_mean_bin_distance": float(bin_dist.mean()) if bin_dist.numel() else 0.0,
            "logit_scale": scale, "median_top2_margin": float(margin.median())}
     _record("argmax_" + label, res)
     print("argmax", label, json.dumps(res))
+    assert on_tight >= 0.999, res                  # the asserted criterion: 2^-7 margin
+    assert frac_tight > 0.6, res                   # ... on most of the image (measured 0.69-0.85)
     assert on_decisive >= 0.999, res
-    assert frac_decisive > 0.3, res
     assert overall >= ARGMAX_OVERALL_FLOOR[label], res
 
 
