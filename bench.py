@@ -379,6 +379,24 @@ class Ctx:
         runs = sorted((self.timed(fn, steps) for _ in range(repeats)), key=lambda r: r[0])
         return runs[len(runs) // 2]
 
+    def timed_windows(self, fn, steps, min_total_ms=1000.0, min_windows=3, max_windows=400):
+        """``timed`` over back-to-back windows of exactly ``steps`` steps each until the windows add up to ``min_total_ms`` of
+        device time (max over ranks, so every rank stops at the same window).  -> (median window ms, its per-rank ms, stats):
+        a headline taken from 3 windows of 12 ms depended on a quiet host for those 36 ms (round 2: the same code gave 13.2k and
+        27.3k maps/s on two boxes); one second of windows shows the spread instead of sampling it."""
+        runs, total = [], 0.0
+        while len(runs) < min_windows or (total < min_total_ms and len(runs) < max_windows):
+            r = self.timed(fn, steps)
+            runs.append(r)
+            total += r[0]
+        runs.sort(key=lambda r: r[0])
+        q = lambda f: runs[min(len(runs) - 1, int(f * len(runs)))][0] / steps
+        stats = {"windows": len(runs), "steps_per_window": steps, "device_time_s": total / 1e3,
+                 "ms_per_step": {"min": q(0.0), "p10": q(0.1), "median": q(0.5), "p90": q(0.9), "max": runs[-1][0] / steps},
+                 "spread_p90_over_p10": q(0.9) / q(0.1)}
+        med = runs[len(runs) // 2]
+        return med[0], med[1], stats
+
     def close(self):
         if self.dist is not None:
             self.dist.destroy_process_group()
@@ -403,7 +421,7 @@ def head_call(head, x, ob, bx):
         return head(x) if ob is None else head(x, list(ob), bx)
 
 
-def pipelined_rate(ctx, head, x, ob, bx, B, K, W_, lanes, pixel_ctas=0, want_classic=True):
+def pipelined_rate(ctx, head, x, ob, bx, B, K, W_, lanes, pixel_ctas=0, want_classic=True, min_total_ms=0.0):
     """Device-resident throughput of a bf16 head: classic calls (single-call latency), then the pipelined serving mode.
     ``x``: one input tensor, or a list of equal tensors at different addresses that the calls rotate over (inputs smaller than
     L2: the rotation makes every call read its features from HBM, like a flush would)."""
@@ -425,16 +443,32 @@ def pipelined_rate(ctx, head, x, ob, bx, B, K, W_, lanes, pixel_ctas=0, want_cla
         head.join()
     l0 = ops.launch_count
 
+    issue = []                                        # host time spent issuing the K calls of a window (before the join)
+
     def timed_steps():
+        t0 = time.perf_counter()
         for _ in range(K):
             call()
+        issue.append((time.perf_counter() - t0) * 1e3)
         head.join()                                   # every one of the K steps has finished when the stop event fires
 
-    ms, per = ctx.timed_median(timed_steps, 1)
-    launches = (ops.launch_count - l0) // 3
+    stats = None
+    if min_total_ms > 0:                              # the headline: windows of exactly K steps until >= min_total_ms of device time
+        ms, per, stats = ctx.timed_windows(timed_steps, 1, min_total_ms)
+        stats["steps_per_window"] = K
+        for k in stats["ms_per_step"]:
+            stats["ms_per_step"][k] /= K
+        n_windows = stats["windows"]
+    else:
+        ms, per = ctx.timed_median(timed_steps, 1)
+        n_windows = 3
+    launches = (ops.launch_count - l0) // n_windows
+    issue.sort()
+    host_ms = issue[len(issue) // 2] / K
     if lanes:
         head.enable_pipeline(0)
-    return dict(ms=ms, per=per, ms_classic=ms_classic, launches=launches, value=ctx.world * B * K / (ms * 1e-3))
+    return dict(ms=ms, per=per, ms_classic=ms_classic, launches=launches, value=ctx.world * B * K / (ms * 1e-3), windows=stats,
+                host_issue_ms_per_call=host_ms, host_bound=bool(host_ms > 0.8 * ms / K))
 
 
 def measure_other_configs(ctx, K, W_, lanes, pk):
@@ -729,6 +763,9 @@ def main():
     ap.add_argument("--workload", default="infer", choices=["infer", "train"],
                     help="infer = BASELINE.json configs[1] as the headline (the line also carries train / configs sub-records); "
                          "train = configs[4] as the headline")
+    ap.add_argument("--min-timed-ms", type=float, default=1000.0,
+                    help="headline: keep timing windows of exactly --steps steps until they add up to this much device time "
+                         "(0 = three windows, for runs under a profiler)")
     ap.add_argument("--only-headline", action="store_true", help="skip the train / configs / baseline sub-records")
     a = ap.parse_args()
     capture_stdout()
@@ -779,7 +816,7 @@ def main():
     # classic mode first (one call = one stream-ordered pass: the single-call latency), then the pipelined serving mode
     # (consecutive calls overlap: token path of call i+1 next to the pixel kernel of call i) which is what `value` reports.
     lanes = a.lanes if precision == "bf16" else 0
-    r = pipelined_rate(ctx, head, x_dev, objs_dev, boxes_dev, B, K, W_, lanes, a.pixel_ctas)
+    r = pipelined_rate(ctx, head, x_dev, objs_dev, boxes_dev, B, K, W_, lanes, a.pixel_ctas, min_total_ms=a.min_timed_ms)
     ms, ms_classic, launches, value = r["ms"], r["ms_classic"], r["launches"], r["value"]
     # the same pipelined loop with a FRESHLY ALLOCATED input tensor every call (a serving loop does not reuse pointers)
     fresh = None
@@ -811,7 +848,7 @@ def main():
     durs = []
     if precision == "bf16":
         from objcavit_b200 import _lib
-        dom = "pixel_fused_kernel (inside ocv_head_forward)"
+        dom = "pixel_fused_t_kernel<0> (inside ocv_head_forward)"
         nh = head.__dict__["_ocv_native"]
         _lib.check(_lib.lib().ocv_head_enable_timing(nh._h, 1), "ocv_head_enable_timing")
         for _ in range(min(K, 10)):
@@ -906,8 +943,10 @@ def main():
                    "pipeline": (f"{lanes} lanes (calls overlap on the head's own streams, token path replayed from a CUDA graph), "
                                 f"pixel kernel grid cap {a.pixel_ctas or 148}") if lanes else "off",
                    "ms_per_step_single_call": ms_classic / K,
-                   "timing": "every figure = the median of 3 back-to-back windows of exactly `steps` steps (CUDA events, barrier + "
-                             "synchronize on both sides, max over ranks per window)"},
+                   "timing": "`value` / `ms_per_step` = the MEDIAN window of back-to-back windows of exactly `steps` steps each, run "
+                             "until they add up to >= --min-timed-ms of device time (`windows`); every other figure = the median of 3 "
+                             "such windows (CUDA events, barrier + synchronize on both sides, max over ranks per window)",
+                   "windows": r["windows"], "host_issue_ms_per_call": r["host_issue_ms_per_call"], "host_bound": r["host_bound"]},
         "gpu_launches": launches, "roofline": roofline,
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / K, "input_format": "pinned bf16 NHWC host features (the decoder hand-off format, DESIGN.md §5c)"
