@@ -148,7 +148,7 @@ def test_bin_argmax_against_the_oracle_logits(cuda, label, name, B, h, w, n_obj)
     pixels whose oracle top-2 margin exceeds 2^-7 of the logit scale (two bf16 roundings) — the tight bound, which keeps 69-85 % of
     the image; the looser 2e-2 split is recorded only.  (Rescaling ``conv_out`` does not move those fractions: measured on the
     oracle, x1..x16 on the weight and log-uniform row norms up to x256 leave 2^-7-decisive at 0.47-0.76 for the ObjCAViT heads —
-    under F5 the two best bins for r > 0 are the two largest slopes, whose gap does not grow with the scale.  DESIGN.md §7.)"""
+    under F5 the two best bins for r > 0 are the two largest slopes, whose gap does not grow with the scale.  DESIGN.md §7.9.)"""
     args, sd, feats, objs, boxes = _inputs(name, B, h, w, n_obj, seed=777, weight_seed=5)
     cfg = case_cfg({}, args)
     _, _, ram = _oracle(sd, cfg, feats, objs, boxes, want_ram=True)
